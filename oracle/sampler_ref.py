@@ -1,0 +1,235 @@
+"""Oracle: mixing-SDE math, predictor / corrector updates and the PC sampler loop.
+
+TEST INFRASTRUCTURE (see ``oracle/__init__.py``).  Restates
+
+* ``MixSDE``                 -- src/sdes/sdes.py:182-351
+* ``OUVESDE``                -- src/sdes/sdes.py:595-698
+* ``SDE.discretize`` / ``RSDE.discretize``  -- src/sdes/sdes.py:94-108, 165-173
+* ``ReverseDiffusionPredictor.update_fn``   -- src/sdes/predictors.py:60-66
+* ``AnnealedLangevinDynamics2.update_fn``   -- src/sdes/correctors.py:102-121
+* ``AnnealedLangevinDynamics.update_fn``    -- src/sdes/correctors.py:70-84
+* ``get_pc_sampler``         -- src/sdes/__init__.py:133-193
+* ``normalize_batch``        -- src/utils/separate.py:56-67
+
+with the matrix algebra written out the way the reference does it (2x2 / nxn
+``std @ x`` products), NOT in the closed form the CUDA kernel uses, so that the
+closed form is checked against an independent formulation.  Noise comes from a
+"tape": a callable ``noise(i, like)`` returning the i-th draw, so the oracle,
+the reference and the CUDA path consume identical noise.
+"""
+from __future__ import annotations
+
+import math
+from typing import Callable, List, Optional, Tuple
+
+import numpy as np
+import torch
+
+Tensor = torch.Tensor
+NoiseFn = Callable[[int, Tensor], Tensor]
+
+
+class NoiseTape:
+    """Deterministic noise source: draw i is ``randn(shape, Generator(seed + i))`` on
+    CPU (fp32), so any draw can be regenerated independently and in any order."""
+
+    def __init__(self, seed: int = 4321):
+        self.seed = seed
+        self.count = 0
+
+    def draw(self, i: int, shape) -> Tensor:
+        g = torch.Generator().manual_seed(self.seed + 1000003 * i)
+        return torch.empty(tuple(shape), dtype=torch.float32).normal_(generator=g)
+
+    def __call__(self, i: int, like: Tensor) -> Tensor:
+        self.count = max(self.count, i + 1)
+        return self.draw(i, like.shape).to(like.device)
+
+
+# --------------------------------------------------------------------------- MixSDE
+class MixSDERef:
+    """sdes.py:182-351."""
+
+    def __init__(self, ndim=2, d_lambda=2.0, sigma_min=0.05, sigma_max=0.5, N=30):
+        self.ndim, self.d_lambda = ndim, d_lambda
+        self.sigma_min, self.sigma_max = sigma_min, sigma_max
+        self.ratiosig = sigma_max / sigma_min
+        self.logsig = math.log(self.ratiosig)
+        self.N = N
+        ones = torch.ones((ndim, 1))
+        self.A = (ones @ ones.T / ndim)[None]          # :244-250 averaging matrix
+        self.Pn = (torch.eye(ndim) - self.A[0])[None]  # projector on its null space
+        self.T = 1.0
+
+    def sde(self, x, t):
+        """:277-286."""
+        drift = -self.d_lambda * self.Pn @ x
+        sigma = self.sigma_min * self.ratiosig ** t
+        return drift, sigma * np.sqrt(2 * self.logsig)
+
+    def cov_eigval(self, t):
+        """:298-311."""
+        mult = self.sigma_min ** 2
+        srp = self.ratiosig ** (2 * t)
+        ev1 = mult * (srp - 1)
+        ev2 = mult * (srp - torch.exp(-2.0 * self.d_lambda * t)) / (1.0 + self.d_lambda / self.logsig)
+        return ev1, ev2
+
+    def std(self, t):
+        """:317-322."""
+        ev1, ev2 = self.cov_eigval(t)
+        return ev1[:, None, None].sqrt() * self.A + ev2[:, None, None].sqrt() * self.Pn
+
+    def mean(self, x0, t):
+        """:288-296."""
+        decay = torch.exp(-t[:, None, None] * self.d_lambda)
+        return (self.A + decay * self.Pn) @ x0
+
+    def prior_sampling(self, y, noise: Tensor):
+        """:336-348 (hard-codes 2 sources, mean 0.5*y)."""
+        t = torch.ones((y.shape[0],)) * self.T
+        mean = torch.broadcast_to(0.5 * y, (y.shape[0], 2, y.shape[2]))
+        return mean + self.std(t) @ noise
+
+
+class OUVESDERef:
+    """sdes.py:595-698."""
+
+    def __init__(self, theta=1.5, sigma_min=0.05, sigma_max=0.5, N=30):
+        self.theta, self.sigma_min, self.sigma_max = theta, sigma_min, sigma_max
+        self.logsig = np.log(sigma_max / sigma_min)
+        self.N = N
+        self.T = 1
+
+    def sde(self, x, t, y):
+        """:652-660."""
+        drift = self.theta * (y - x)
+        sigma = self.sigma_min * (self.sigma_max / self.sigma_min) ** t
+        return drift, sigma * np.sqrt(2 * self.logsig)
+
+    def std(self, t):
+        """:670-682."""
+        s, th, ls = self.sigma_min, self.theta, self.logsig
+        return torch.sqrt(s ** 2 * torch.exp(-2 * th * t) * (torch.exp(2 * (th + ls) * t) - 1) * ls / (th + ls))
+
+    def prior_sampling(self, y, noise: Tensor):
+        """:687-695: y + randn(shape) * std(1)."""
+        std = self.std(torch.ones((y.shape[0],)))
+        pad = (...,) + (None,) * (y.ndim - std.ndim)
+        return y + noise * std[pad]
+
+
+# --------------------------------------------------------------------------- update rules
+def _pad(v: Tensor, like: Tensor) -> Tensor:
+    return v[(...,) + (None,) * (like.ndim - v.ndim)]
+
+
+def corrector_ald2_ref(sde: MixSDERef, x, t, score, noise, snr):
+    """correctors.py:102-121 for one step: grad = L @ (L @ score);
+    x_mean = x + 2 snr^2 grad; x = x_mean + (2 snr L) @ noise."""
+    L = sde.std(t)
+    grad = L @ (L @ score)
+    x_mean = x + 2 * snr ** 2 * grad
+    return x_mean + (2 * snr * L) @ noise, x_mean
+
+
+def corrector_ald_ref(sde, x, t, score, noise, snr):
+    """correctors.py:70-84 for one step with a scalar std (OUVESDE)."""
+    std = sde.std(t)
+    step = (snr * std) ** 2 * 2
+    x_mean = x + _pad(step, x) * score
+    return x_mean + noise * _pad(torch.sqrt(step * 2), x), x_mean
+
+
+def predictor_rd_ref(sde, x, t, y, score, noise):
+    """predictors.py:60-66 + sdes.py:94-108,165-173.  dt is always 1/N (the
+    ``getattr(kwargs, "dt", ...)`` on a dict never finds the key -- quirk Q2)."""
+    dt = 1 / sde.N
+    drift, diffusion = sde.sde(x, t) if isinstance(sde, MixSDERef) else sde.sde(x, t, y)
+    f = drift * dt
+    G = diffusion * torch.sqrt(torch.tensor(dt))
+    rev_f = f - _pad(G, f) ** 2 * score
+    x_mean = x - rev_f
+    return x_mean + _pad(G, x) * noise, x_mean
+
+
+def pc_sampler_ref(score_fn, sde, y: Tensor, noise: NoiseFn, corrector: str = "ald2",
+                   eps: float = 3e-2, snr: float = 0.5, corrector_steps: int = 1, denoise: bool = True,
+                   n_spkrs: int = 2, on_score: Optional[Callable] = None) -> Tuple[Tensor, int]:
+    """``get_pc_sampler`` closure (src/sdes/__init__.py:168-191) with the
+    ``reverse_diffusion`` predictor.  Noise draw order (quirk Q3): #0 prior, then per
+    step i: corrector draws 1+2i.., predictor draw; 1 + N*(corrector_steps+1) draws.
+    ``on_score(k, x, t, score)`` is called after each of the N*(corrector_steps+1)
+    score evaluations."""
+    with torch.no_grad():
+        shape = (y.shape[0], n_spkrs, *y.shape[2:])
+        draw = 0
+        z = noise(draw, torch.empty(shape)); draw += 1
+        xt = sde.prior_sampling(y, z)
+        timesteps = torch.linspace(sde.T, eps, sde.N)
+        k = 0
+        xt_mean = xt
+        for i in range(sde.N):
+            vec_t = torch.ones(y.shape[0]) * timesteps[i]
+            for _ in range(corrector_steps):
+                s = score_fn(xt, vec_t, y)
+                if on_score:
+                    on_score(k, xt, vec_t, s)
+                k += 1
+                z = noise(draw, xt); draw += 1
+                if corrector == "ald2":
+                    xt, xt_mean = corrector_ald2_ref(sde, xt, vec_t, s, z, snr)
+                elif corrector == "ald":
+                    xt, xt_mean = corrector_ald_ref(sde, xt, vec_t, s, z, snr)
+                else:
+                    raise ValueError(corrector)
+            s = score_fn(xt, vec_t, y)
+            if on_score:
+                on_score(k, xt, vec_t, s)
+            k += 1
+            z = noise(draw, xt); draw += 1
+            xt, xt_mean = predictor_rd_ref(sde, xt, vec_t, y, s, z)
+        return (xt_mean if denoise else xt), sde.N * (corrector_steps + 1)
+
+
+def normalize_batch_ref(mix: Tensor):
+    """src/utils/separate.py:56-63: per-item mean / unbiased std over (chan, time), clamp 1e-5."""
+    mean = mix.mean(dim=(1, 2), keepdim=True)
+    std = mix.std(dim=(1, 2), keepdim=True).clamp(min=1e-5)
+    return (mix - mean) / std, mean, std
+
+
+# --------------------------------------------------------------------------- metric
+def si_sdr_pit_ref(ref: Tensor, est: Tensor) -> Tuple[Tensor, List[Tuple[int, ...]]]:
+    """Scale-invariant SDR with the best source permutation.
+
+    Restates ``fast_bss_eval.si_bss_eval_sources(ref, est, zero_mean=False,
+    compute_permutation=True)`` as called at src/evaluate_mp.py:173-175 (third-party
+    package fast-bss-eval==0.1.4, env/environment.yaml:294, not installed here):
+    alpha = <est,ref>/<ref,ref>, SI-SDR = 10 log10(|alpha ref|^2 / |est - alpha ref|^2),
+    permutation maximising the mean.  Parity unpinned against the package; only
+    DIFFERENCES of two SI-SDRs computed by this same function are asserted.
+    ref, est: (B, n_src, T) -> (B, n_src) dB, per-item permutation."""
+    import itertools
+
+    b, n, _ = ref.shape
+    ref = ref.double()
+    est = est.double()
+    out = torch.empty(b, n, dtype=torch.float64)
+    perms = []
+    for bi in range(b):
+        best, best_p, best_v = -float("inf"), None, None
+        for p in itertools.permutations(range(n)):
+            vals = []
+            for r in range(n):
+                e = est[bi, p[r]]
+                rr = ref[bi, r]
+                alpha = (e @ rr) / (rr @ rr).clamp(min=1e-30)
+                tgt = alpha * rr
+                vals.append(10 * torch.log10((tgt @ tgt) / ((e - tgt) @ (e - tgt)).clamp(min=1e-30)))
+            v = torch.stack(vals)
+            if float(v.mean()) > best:
+                best, best_p, best_v = float(v.mean()), p, v
+        out[bi] = best_v
+        perms.append(best_p)
+    return out.float(), perms
