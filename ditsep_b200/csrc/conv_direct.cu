@@ -1,0 +1,140 @@
+// CUDA-core implicit-GEMM convolution (3x3 pad 1 / 1x1, stride 1, NHWC), fp32 accumulate.
+//
+// Role: (1) the fp32 score network (parity target rel-L2 <= 1e-3 needs fp32/tf32
+// arithmetic, BASELINE.json north_star) and (2) the narrow layers whose channel counts do
+// not fill a tensor-core tile (input conv 6->nf, Combine 1x1 6->C).  The wide bf16 layers go
+// through the tcgen05 kernel in conv_tc.cu.  Same fused epilogue as there:
+//   out = out_scale * (conv + bias[co] + bias_b[b,co] + residual)
+// (res-block tail, layerspp.py:314-328; Combine sum layerspp.py:57-62).
+//
+// GEMM view: M = B*H*W pixels, N = Cout, K = taps*Cin with k = tap*Cin + ci; weights are
+// [Cout][taps][Cin] fp32 (K contiguous).  64x64 block tile, BK = 16, 256 threads, 4x4
+// micro-tile per thread, A gathered on the fly (zero outside the image).
+#include "common.cuh"
+
+namespace ditsep {
+
+constexpr int BM = 64, BN = 64, BK = 16;
+
+template <typename TI, typename TO, typename TR>
+__global__ void __launch_bounds__(256) conv_direct_kernel(const TI* __restrict__ in, int B, int H, int W, int Cin,
+                                                          int ld_in, const float* __restrict__ w,
+                                                          const float* __restrict__ bias,
+                                                          const float* __restrict__ bias_b, int ld_bias_b,
+                                                          const TR* __restrict__ residual, int ld_res, float out_scale,
+                                                          int Cout, int ksize, TO* __restrict__ out, int ld_out) {
+  __shared__ float As[BK][BM + 4];
+  __shared__ float Bs[BK][BN + 4];
+  const int taps = ksize * ksize, K = taps * Cin, pad = ksize / 2;
+  const int64_t M = (int64_t)B * H * W;
+  const int64_t m0 = (int64_t)blockIdx.x * BM;
+  const int n0 = blockIdx.y * BN;
+  const int tid = threadIdx.x;
+  const int tx = tid % 16, ty = tid / 16;  // tx -> n micro-tile, ty -> m micro-tile
+
+  // A gather assignment: 64 pixels x 16 k = 1024 elements, 4 per thread: k = tid % 16 (channels are
+  // contiguous in NHWC, so half-warps read 16 consecutive channels), pixel = tid / 16 + 16 j.
+  const int a_k = tid % BK, a_p0 = tid / BK;
+  int ab[4], ay[4], ax[4];
+  bool a_ok[4];
+#pragma unroll
+  for (int j = 0; j < 4; ++j) {
+    const int64_t am = m0 + a_p0 + 16 * j;
+    a_ok[j] = am < M;
+    ab[j] = ay[j] = ax[j] = 0;
+    if (a_ok[j]) {
+      ax[j] = (int)(am % W);
+      int64_t r = am / W;
+      ay[j] = (int)(r % H);
+      ab[j] = (int)(r / H);
+    }
+  }
+  // B load assignment: 64 cout x 16 k, 4 per thread: k = tid % 16, co = tid / 16 + 16 j
+  const int b_k = tid % BK, b_c0 = tid / BK;
+
+  float acc[4][4];
+#pragma unroll
+  for (int i = 0; i < 4; ++i)
+#pragma unroll
+    for (int j = 0; j < 4; ++j) acc[i][j] = 0.f;
+
+  for (int k0 = 0; k0 < K; k0 += BK) {
+    {
+      const int k = k0 + a_k;
+      const int tap = k / Cin, ci = k - tap * Cin;
+      const int dy = tap / ksize - pad, dx = tap % ksize - pad;
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        float v = 0.f;
+        const int yy = ay[j] + dy, xx = ax[j] + dx;
+        if (a_ok[j] && k < K && yy >= 0 && yy < H && xx >= 0 && xx < W)
+          v = to_f<TI>(in[(((int64_t)ab[j] * H + yy) * W + xx) * ld_in + ci]);
+        As[a_k][a_p0 + 16 * j] = v;
+      }
+    }
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      const int co = n0 + b_c0 + 16 * j, k = k0 + b_k;
+      Bs[b_k][b_c0 + 16 * j] = (co < Cout && k < K) ? w[(int64_t)co * K + k] : 0.f;
+    }
+    __syncthreads();
+#pragma unroll
+    for (int kk = 0; kk < BK; ++kk) {
+      float a[4], bb[4];
+#pragma unroll
+      for (int i = 0; i < 4; ++i) a[i] = As[kk][ty * 4 + i];
+#pragma unroll
+      for (int j = 0; j < 4; ++j) bb[j] = Bs[kk][tx * 4 + j];
+#pragma unroll
+      for (int i = 0; i < 4; ++i)
+#pragma unroll
+        for (int j = 0; j < 4; ++j) acc[i][j] = fmaf(a[i], bb[j], acc[i][j]);
+    }
+    __syncthreads();
+  }
+#pragma unroll
+  for (int i = 0; i < 4; ++i) {
+    const int64_t m = m0 + ty * 4 + i;
+    if (m >= M) continue;
+    const int b = (int)(m / ((int64_t)H * W));
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      const int co = n0 + tx * 4 + j;
+      if (co >= Cout) continue;
+      float v = acc[i][j];
+      if (bias) v += bias[co];
+      if (bias_b) v += bias_b[(int64_t)b * ld_bias_b + co];
+      if (residual) v += to_f<TR>(residual[m * ld_res + co]);
+      out[m * ld_out + co] = from_f<TO>(v * out_scale);
+    }
+  }
+}
+
+}  // namespace ditsep
+
+using namespace ditsep;
+
+extern "C" int ditsep_conv_direct(const void* in, int dtype, int B, int H, int W, int Cin, int ld_in, const float* w,
+                                  const float* bias, const float* bias_b, int ld_bias_b, const void* residual,
+                                  int ld_res, float out_scale, int Cout, int ksize, void* out, int out_dtype,
+                                  int ld_out, void* stream) {
+  DITSEP_REQUIRE(in && w && out, "conv_direct: null pointer");
+  DITSEP_REQUIRE(ksize == 1 || ksize == 3, "conv_direct: ksize=%d (1 or 3)", ksize);
+  DITSEP_REQUIRE(B > 0 && H > 0 && W > 0 && Cin > 0 && Cout > 0, "conv_direct: empty problem");
+  DITSEP_REQUIRE(ld_in >= Cin && ld_out >= Cout, "conv_direct: strides smaller than channel counts");
+  const int64_t M = (int64_t)B * H * W;
+  dim3 grid(ceil_div(M, BM), ceil_div(Cout, BN));
+  cudaStream_t st = (cudaStream_t)stream;
+  // residual shares the OUTPUT dtype (it is an activation tensor of the same network)
+#define LAUNCH(TI, TO)                                                                                              \
+  conv_direct_kernel<TI, TO, TO><<<grid, 256, 0, st>>>((const TI*)in, B, H, W, Cin, ld_in, w, bias, bias_b, ld_bias_b, \
+                                                       (const TO*)residual, ld_res, out_scale, Cout, ksize, (TO*)out,  \
+                                                       ld_out)
+  if (dtype == DITSEP_F32 && out_dtype == DITSEP_F32) LAUNCH(float, float);
+  else if (dtype == DITSEP_BF16 && out_dtype == DITSEP_BF16) LAUNCH(bf16, bf16);
+  else if (dtype == DITSEP_BF16 && out_dtype == DITSEP_F32) LAUNCH(bf16, float);
+  else if (dtype == DITSEP_F32 && out_dtype == DITSEP_BF16) LAUNCH(float, bf16);
+  else DITSEP_REQUIRE(false, "conv_direct: unknown dtype %d/%d", dtype, out_dtype);
+#undef LAUNCH
+  return check_launch("conv_direct_kernel");
+}

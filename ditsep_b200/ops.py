@@ -1,0 +1,247 @@
+"""Tensor-level wrappers over the C ABI (torch is plumbing: device memory + streams).
+
+Every function takes CUDA tensors, launches on torch's current stream and raises on any
+error; CPU tensors are rejected (there is no CPU path).
+Activations are NHWC views: a tensor of shape (B, H, W, C) whose last-dim stride is 1 and
+whose pixel stride ``ld`` may exceed C (a channel slice of a wider concat buffer).
+"""
+from __future__ import annotations
+
+import ctypes as C
+from typing import Optional, Tuple
+
+import torch
+
+from . import _lib
+from ._lib import SdeParams, check
+
+F32, BF16 = 0, 1
+_DT = {torch.float32: F32, torch.bfloat16: BF16}
+
+
+def _stream() -> int:
+    return torch.cuda.current_stream().cuda_stream
+
+
+def _ptr(t: Optional[torch.Tensor]):
+    return None if t is None else t.data_ptr()
+
+
+def _cuda(*ts):
+    for t in ts:
+        if t is not None and not t.is_cuda:
+            raise _lib.DitsepError("ditsep_b200 kernels need CUDA tensors; there is no CPU fallback")
+
+
+def _dt(t: torch.Tensor) -> int:
+    try:
+        return _DT[t.dtype]
+    except KeyError:
+        raise _lib.DitsepError(f"unsupported activation dtype {t.dtype}") from None
+
+
+def nhwc_ld(t: torch.Tensor) -> int:
+    """Pixel stride of an NHWC view (B,H,W,C); checks that pixels are laid out densely in B,H,W."""
+    b, h, w, c = t.shape
+    sb, sh, sw, sc = t.stride()
+    if c > 1 and sc != 1:
+        raise _lib.DitsepError("NHWC view must have unit channel stride")
+    ld = sw
+    if (w > 1 and False) or (h > 1 and sh != w * ld) or (b > 1 and sb != h * w * ld):
+        raise _lib.DitsepError(f"NHWC view is not pixel-dense: shape {tuple(t.shape)} strides {t.stride()}")
+    return ld
+
+
+def launch_count() -> int:
+    return int(_lib.load().ditsep_launch_count())
+
+
+# ------------------------------------------------------------------ SDE updates
+def _f32c(t: Optional[torch.Tensor], name: str):
+    if t is None:
+        return
+    if t.dtype != torch.float32 or not t.is_contiguous():
+        raise _lib.DitsepError(f"{name} must be contiguous float32")
+
+
+def _state_dims(x: torch.Tensor, p: SdeParams) -> Tuple[int, int]:
+    B = x.shape[0]
+    if x.shape[1] != p.n_src:
+        raise _lib.DitsepError(f"state has {x.shape[1]} sources, SDE params say {p.n_src}")
+    L = x[0, 0].numel()
+    return B, L
+
+
+def pc_corrector(p: SdeParams, x, score, t, noise=None, seed=0, draw=0, x_mean=None):
+    _cuda(x, score, t, noise, x_mean)
+    for n, v in (("x", x), ("score", score), ("t", t), ("noise", noise), ("x_mean", x_mean)):
+        _f32c(v, n)
+    B, L = _state_dims(x, p)
+    check(_lib.load().ditsep_pc_corrector(C.byref(p), _ptr(x), _ptr(score), _ptr(noise), seed, draw, _ptr(t),
+                                          _ptr(x_mean), B, L, _stream()), "pc_corrector")
+
+
+def pc_predictor(p: SdeParams, x, score, t, y, noise=None, seed=0, draw=0, x_mean=None):
+    _cuda(x, score, t, y, noise, x_mean)
+    for n, v in (("x", x), ("score", score), ("t", t), ("y", y), ("noise", noise), ("x_mean", x_mean)):
+        _f32c(v, n)
+    B, L = _state_dims(x, p)
+    check(_lib.load().ditsep_pc_predictor(C.byref(p), _ptr(x), _ptr(score), _ptr(noise), seed, draw, _ptr(t), _ptr(y),
+                                          _ptr(x_mean), B, L, _stream()), "pc_predictor")
+
+
+def pc_prior(p: SdeParams, x, y, noise=None, seed=0, draw=0):
+    _cuda(x, y, noise)
+    for n, v in (("x", x), ("y", y), ("noise", noise)):
+        _f32c(v, n)
+    B, L = _state_dims(x, p)
+    check(_lib.load().ditsep_pc_prior(C.byref(p), _ptr(x), _ptr(noise), seed, draw, _ptr(y), B, L, _stream()),
+          "pc_prior")
+
+
+def philox_normal(out: torch.Tensor, seed: int, draw: int):
+    _cuda(out)
+    _f32c(out, "out")
+    check(_lib.load().ditsep_philox_normal(_ptr(out), out.numel(), seed, draw, _stream()), "philox_normal")
+
+
+# ------------------------------------------------------------------ spectral
+def stft_compress(xt, mix, window, feat, exponent: float, factor: float, affine: bool):
+    """xt (B,n,T), mix (B,1,T) f32 -> feat NHWC (B,256,W,2(n+1)) f32|bf16 (dense)."""
+    _cuda(xt, mix, window, feat)
+    for n, v in (("xt", xt), ("mix", mix), ("window", window)):
+        _f32c(v, n)
+    B, n_src, T = xt.shape
+    if not feat.is_contiguous() or feat.shape[0] != B or feat.shape[1] != 256 or feat.shape[3] != 2 * (n_src + 1):
+        raise _lib.DitsepError(f"feat must be dense (B,256,W,{2 * (n_src + 1)}), got {tuple(feat.shape)}")
+    check(_lib.load().ditsep_stft_compress(_ptr(xt), _ptr(mix), _ptr(window), _ptr(feat), _dt(feat), B, n_src, T,
+                                           feat.shape[2], exponent, factor, int(affine), _stream()), "stft_compress")
+
+
+def expand_istft(spec, window, out, exponent: float, factor: float):
+    """spec NHWC (B,256,W,2n) f32 dense -> out (B,n,T) f32."""
+    _cuda(spec, window, out)
+    for n, v in (("spec", spec), ("window", window), ("out", out)):
+        _f32c(v, n)
+    B, n_src, T = out.shape
+    if spec.shape[0] != B or spec.shape[1] != 256 or spec.shape[3] != 2 * n_src:
+        raise _lib.DitsepError(f"spec must be (B,256,W,{2 * n_src}), got {tuple(spec.shape)}")
+    check(_lib.load().ditsep_expand_istft(_ptr(spec), _ptr(window), _ptr(out), B, n_src, T, spec.shape[2], exponent,
+                                          factor, _stream()), "expand_istft")
+
+
+# ------------------------------------------------------------------ norm / resample
+def gn_nsplit(B: int, HW: int, C: int) -> int:
+    ppb = max(1, 256 // (C // 8))
+    want = max(1, (4 * 148 + B - 1) // B)
+    return int(max(1, min(want, HW // (ppb * 4) if HW >= ppb * 4 else 1)))
+
+
+def gn_stats(x, G: int, gamma, beta, eps: float, partial, scale_shift):
+    """x NHWC (B,H,W,C) -> scale_shift (B,2,C) f32.  partial: f32 scratch >= B*nsplit*C*2."""
+    _cuda(x, gamma, beta, partial, scale_shift)
+    B, H, W, Cc = x.shape
+    nsplit = gn_nsplit(B, H * W, Cc)
+    if partial.numel() < B * nsplit * Cc * 2:
+        raise _lib.DitsepError("gn_stats: partial scratch too small")
+    check(_lib.load().ditsep_gn_stats(_ptr(x), _dt(x), B, H * W, Cc, nhwc_ld(x), G, _ptr(gamma), _ptr(beta), eps,
+                                      _ptr(partial), nsplit, _ptr(scale_shift), _stream()), "gn_stats")
+
+
+def gn_apply(x, scale_shift, silu: bool, y):
+    _cuda(x, scale_shift, y)
+    B, H, W, Cc = x.shape
+    if y.dtype != x.dtype:
+        raise _lib.DitsepError("gn_apply: dtype mismatch")
+    check(_lib.load().ditsep_gn_apply(_ptr(x), _dt(x), B, H * W, Cc, nhwc_ld(x), _ptr(scale_shift), int(silu), _ptr(y),
+                                      nhwc_ld(y), _stream()), "gn_apply")
+
+
+def fir_resample(x, up: bool, out_x=None, scale_shift=None, out_h=None):
+    _cuda(x, out_x, scale_shift, out_h)
+    B, H, W, Cc = x.shape
+    check(_lib.load().ditsep_fir_resample(_ptr(x), _dt(x), B, H, W, Cc, nhwc_ld(x), int(up), _ptr(scale_shift),
+                                          _ptr(out_x), 0 if out_x is None else nhwc_ld(out_x), _ptr(out_h),
+                                          0 if out_h is None else nhwc_ld(out_h), _stream()), "fir_resample")
+
+
+# ------------------------------------------------------------------ convolution
+def conv_direct(x, w, bias, out, ksize: int, bias_b=None, residual=None, out_scale: float = 1.0):
+    """x NHWC, w (Cout, taps, Cin) f32, out NHWC.  out = out_scale*(conv + bias + bias_b[b] + residual)."""
+    _cuda(x, w, bias, out, bias_b, residual)
+    B, H, W, Cin = x.shape
+    Cout = out.shape[3]
+    if w.dtype != torch.float32 or not w.is_contiguous() or w.shape != (Cout, ksize * ksize, Cin):
+        raise _lib.DitsepError(f"conv_direct: weights must be f32 (Cout,taps,Cin)={Cout, ksize * ksize, Cin}, got {tuple(w.shape)}")
+    if residual is not None and residual.dtype != out.dtype:
+        raise _lib.DitsepError("conv_direct: residual dtype must equal output dtype")
+    check(_lib.load().ditsep_conv_direct(_ptr(x), _dt(x), B, H, W, Cin, nhwc_ld(x), _ptr(w), _ptr(bias), _ptr(bias_b),
+                                         0 if bias_b is None else bias_b.stride(0), _ptr(residual),
+                                         0 if residual is None else nhwc_ld(residual), out_scale, Cout, ksize,
+                                         _ptr(out), _dt(out), nhwc_ld(out), _stream()), "conv_direct")
+
+
+class ConvTcPlan:
+    """Owns a ditsep_conv_plan (TMA descriptors for one input tensor + weight binding)."""
+
+    def __init__(self, x: torch.Tensor, w_bf16: torch.Tensor, Cout: int, ksize: int):
+        _cuda(x, w_bf16)
+        B, H, W, Cin = x.shape
+        if x.dtype != torch.bfloat16 or w_bf16.dtype != torch.bfloat16 or not w_bf16.is_contiguous():
+            raise _lib.DitsepError("conv_tc: bf16 activations and packed bf16 weights required")
+        self._h = C.c_void_p()
+        self._keep = (x, w_bf16)
+        self.Cout = Cout
+        self.shape = (B, H, W)
+        check(_lib.load().ditsep_conv_tc_plan_create(C.byref(self._h), _ptr(x), B, H, W, Cin, nhwc_ld(x), _ptr(w_bf16),
+                                                     Cout, ksize), "conv_tc_plan_create")
+
+    def run(self, bias, out, bias_b=None, residual=None, out_scale: float = 1.0):
+        _cuda(bias, out, bias_b, residual)
+        check(_lib.load().ditsep_conv_tc_run(self._h, _ptr(bias), _ptr(bias_b),
+                                             0 if bias_b is None else bias_b.stride(0), _ptr(residual),
+                                             0 if residual is None else _dt(residual),
+                                             0 if residual is None else nhwc_ld(residual), out_scale, _ptr(out),
+                                             _dt(out), nhwc_ld(out), _stream()), "conv_tc_run")
+
+    def __del__(self):
+        h = getattr(self, "_h", None)
+        if h is not None and h.value:
+            try:
+                _lib.load().ditsep_conv_tc_plan_destroy(h)
+            except Exception:
+                pass
+            self._h = None
+
+
+# ------------------------------------------------------------------ attention / temb / output
+def attention(q, k, v, o):
+    """q,k,v,o: NHWC views (B,H,W,C) sharing one pixel stride for q/k/v."""
+    _cuda(q, k, v, o)
+    B, H, W, Cc = q.shape
+    ld = nhwc_ld(q)
+    if nhwc_ld(k) != ld or nhwc_ld(v) != ld:
+        raise _lib.DitsepError("attention: q, k, v must share the pixel stride")
+    check(_lib.load().ditsep_attention(_ptr(q), _ptr(k), _ptr(v), _dt(q), B, H * W, Cc, ld, _ptr(o), nhwc_ld(o),
+                                       _stream()), "attention")
+
+
+def temb_mlp(t, gfp_w, w1, b1, w2, b2, act_temb):
+    _cuda(t, gfp_w, w1, b1, w2, b2, act_temb)
+    check(_lib.load().ditsep_temb_mlp(_ptr(t), _ptr(gfp_w), _ptr(w1), _ptr(b1), _ptr(w2), _ptr(b2), _ptr(act_temb),
+                                      t.shape[0], gfp_w.shape[0], _stream()), "temb_mlp")
+
+
+def temb_dense(act_temb, dense_w, dense_b, out):
+    _cuda(act_temb, dense_w, dense_b, out)
+    B, K = act_temb.shape
+    check(_lib.load().ditsep_temb_dense(_ptr(act_temb), _ptr(dense_w), _ptr(dense_b), _ptr(out), B, K,
+                                        dense_w.shape[0], _stream()), "temb_dense")
+
+
+def output_layer(x, t, w, bias, out, scale_by_sigma: bool):
+    """x NHWC (B,H,W,Cin) -> out dense (B,H,W,Cout) f32."""
+    _cuda(x, t, w, bias, out)
+    B, H, W, Cin = x.shape
+    check(_lib.load().ditsep_output_layer(_ptr(x), _dt(x), B, H * W, Cin, nhwc_ld(x), _ptr(t), int(scale_by_sigma),
+                                          _ptr(w), _ptr(bias), out.shape[3], _ptr(out), _stream()), "output_layer")

@@ -1,0 +1,157 @@
+/*
+ * ditsep_b200 -- C ABI of the B200 (sm_100a) kernels behind the DiffSep
+ * predictor-corrector separation sampler.
+ *
+ * The reference (eduardburlacu/DiTSep) has no FFI for this path: its boundary is a
+ * Python object API.  This library is what the Python mirror
+ * of that API (ditsep_b200/{sdes,models,diffsep.py}) binds with ctypes; every
+ * entry point cites the reference code it replaces.  Conventions:
+ *   - plain pointers and sizes only; all pointers are DEVICE pointers unless named
+ *     host_*; buffers are caller-allocated; nothing is freed or retained
+ *     (except ditsep_conv_plan objects, which own their tensor maps);
+ *   - every launch goes to the cudaStream_t passed as `stream` (void*);
+ *   - return value 0 = success, non-zero = error (ditsep_last_error() has the text);
+ *     no C++ exception crosses the ABI;
+ *   - activations are NHWC ("pixels-major"): [B][H][W][ld] with `ld` >= C the pixel
+ *     stride in elements, which lets a tensor live inside a wider concat buffer;
+ *   - `dtype` of activations: DITSEP_F32 (0) or DITSEP_BF16 (1).
+ * There is no CPU fallback anywhere in this library.
+ */
+#ifndef DITSEP_B200_H
+#define DITSEP_B200_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define DITSEP_F32 0
+#define DITSEP_BF16 1
+
+#define DITSEP_SDE_MIX 0  /* sdes.sdes.MixSDE   (src/sdes/sdes.py:182-351) */
+#define DITSEP_SDE_OUVE 1 /* sdes.sdes.OUVESDE  (src/sdes/sdes.py:595-698) */
+
+/* SDE + sampler scalars.  p0 = d_lambda (mix) or theta (ouve). */
+typedef struct {
+  int32_t sde;     /* DITSEP_SDE_* */
+  int32_t n_src;   /* sources per mixture (rows that are averaged by the mixing matrix) */
+  float p0;        /* d_lambda | theta */
+  float sigma_min;
+  float sigma_max;
+  int32_t N;       /* discretisation steps; dt = 1/N always (reference quirk, sdes.py:104) */
+  float snr;       /* corrector snr */
+} ditsep_sde_params;
+
+int ditsep_abi_version(void);
+const char* ditsep_last_error(void);
+/* Number of kernel launches issued through this library since load (bench "gpu_launches"). */
+int64_t ditsep_launch_count(void);
+
+/* ---- fused SDE / predictor / corrector updates (fp32 state) ----------------------
+ * x, score, x_mean: (B, n_src, L) contiguous; y: (B, 1, L); t: (B,).
+ * noise: (B, n_src, L) tape draw, or NULL -> in-register Philox4x32-10 normals keyed by
+ * (seed, draw): element e of the state uses counter (e/4, draw) lane e%4.
+ * x is updated in place; x_mean (nullable) receives the noise-free update.
+ */
+/* AnnealedLangevinDynamics2.update_fn (mix, src/sdes/correctors.py:102-121) or
+ * AnnealedLangevinDynamics.update_fn (ouve, correctors.py:70-84), one step. */
+int ditsep_pc_corrector(const ditsep_sde_params* host_p, float* x, const float* score, const float* noise,
+                        uint64_t seed, uint64_t draw, const float* t, float* x_mean, int B, int64_t L,
+                        void* stream);
+/* ReverseDiffusionPredictor.update_fn (src/sdes/predictors.py:60-66) with
+ * SDE.discretize / RSDE.discretize (src/sdes/sdes.py:94-108,165-173). */
+int ditsep_pc_predictor(const ditsep_sde_params* host_p, float* x, const float* score, const float* noise,
+                        uint64_t seed, uint64_t draw, const float* t, const float* y, float* x_mean, int B,
+                        int64_t L, void* stream);
+/* MixSDE.prior_sampling (sdes.py:336-348, n_src must be 2) / OUVESDE.prior_sampling (:687-695). */
+int ditsep_pc_prior(const ditsep_sde_params* host_p, float* x, const float* noise, uint64_t seed, uint64_t draw,
+                    const float* y, int B, int64_t L, void* stream);
+/* Standard normals from the same Philox stream as above (tests / statistics). */
+int ditsep_philox_normal(float* out, int64_t n, uint64_t seed, uint64_t draw, void* stream);
+
+/* ---- STFT + compression / expansion + iSTFT --------------------------------------
+ * ScoreModelNCSNpp.pre_process (src/models/diffsep/score_models.py:107-116):
+ * cat(xt, mix) -> right pad n_fft-hop -> STFT(n_fft=510, hop=128, periodic Hann, centre
+ * zero pad, onesided) -> |X|^e e^{j arg X} * factor -> channels [Re c0..cn, Im c0..cn]
+ * -> frames zero-padded to W; optional NCSNpp "2x-1" (ncsnpp.py:348-350) folded in.
+ * xt: (B, n_src, T) f32, mix: (B, 1, T) f32, window: (510,) f32.
+ * feat: NHWC [B][256][W][2(n_src+1)] of `dtype`.  n_frames = 1 + (T+382)/128 <= W. */
+int ditsep_stft_compress(const float* xt, const float* mix, const float* window, void* feat, int dtype, int B,
+                         int n_src, int64_t T, int W, float exponent, float factor, int affine_2x_minus_1,
+                         void* stream);
+/* ScoreModelNCSNpp.post_process (score_models.py:118-124): net output NHWC
+ * [B][256][W][2 n_src] f32 (channel k pairs with k+n_src) -> /factor -> |S|^{1/e} e^{j arg S}
+ * -> iSTFT (torch.istft centre=True) -> first T samples.  out: (B, n_src, T) f32. */
+int ditsep_expand_istft(const float* spec, const float* window, float* out, int B, int n_src, int64_t T, int W,
+                        float exponent, float factor, void* stream);
+
+/* ---- GroupNorm (+SiLU) -------------------------------------------------------------
+ * nn.GroupNorm(G, C, eps=1e-6) statistics + affine folded to per-(b,c) scale/shift
+ * (layerspp.py:269-271,283-285,297,318).  x: NHWC [B][HW][ld]; partial: scratch
+ * (B*nsplit*C*2 floats); scale_shift out: [B][2][C] f32. */
+int ditsep_gn_stats(const void* x, int dtype, int B, int64_t HW, int C, int ld, int G, const float* gamma,
+                    const float* beta, float eps, float* partial, int nsplit, float* scale_shift, void* stream);
+/* y = act(x*scale + shift), act = SiLU if silu else identity.  y: NHWC with stride ld_y. */
+int ditsep_gn_apply(const void* x, int dtype, int B, int64_t HW, int C, int ld_x, const float* scale_shift,
+                    int silu, void* y, int ld_y, void* stream);
+
+/* ---- FIR resampling ([1,3,3,1] separable, factor 2) ----------------------------------
+ * upsample_2d / downsample_2d (ncsnpp_utils/up_or_down_sampling.py:206-273) =
+ * upfirdn2d (op/upfirdn2d_kernel.cu:107-207 / op/upfirdn2d.py:159-200).
+ * x: NHWC [B][H][W][ld_x], C channels.  out_x (nullable) = FIR(x);
+ * out_h (nullable) = FIR(SiLU(x*scale+shift)) with scale_shift [B][2][C] (the res-block
+ * applies the resampler to both, layerspp.py:299-312).  up=1: output 2H x 2W; up=0: H/2 x W/2.
+ * acc (nullable, same layout as out_x): out_x += acc (progressive pyramid sum, ncsnpp.py:436-441). */
+int ditsep_fir_resample(const void* x, int dtype, int B, int H, int W, int C, int ld_x, int up,
+                        const float* scale_shift, void* out_x, int ld_ox, void* out_h, int ld_oh, void* stream);
+
+/* ---- convolution (3x3 pad 1 / 1x1, stride 1), NHWC ------------------------------------
+ * nn.Conv2d via ddpm_conv3x3 / ddpm_conv1x1 (ncsnpp_utils/layers.py:112-156), NIN
+ * (layers.py:678-689) with the res-block epilogue fused (layerspp.py:314-328):
+ *   out[b,p,co] = out_scale * ( sum_{tap,ci} in[b,p+tap,ci] * w[co,tap,ci] + bias[co]
+ *                               + bias_b[b,co] + residual[b,p,co] )
+ * CUDA-core fp32 path: any Cin/Cout; weights w: [Cout][taps][Cin] f32. */
+int ditsep_conv_direct(const void* in, int dtype, int B, int H, int W, int Cin, int ld_in, const float* w,
+                       const float* bias, const float* bias_b, int ld_bias_b, const void* residual, int ld_res,
+                       float out_scale, int Cout, int ksize, void* out, int out_dtype, int ld_out, void* stream);
+
+/* tcgen05 implicit-GEMM path (bf16 operands, fp32 TMEM accumulators, TMA-fed).
+ * Requirements: Cin % 64 == 0, Cout <= 256 (padded to a multiple of 16 inside `w`),
+ * `in` 16-byte aligned with ld_in % 8 == 0.  w: [CoutPad][taps][Cin] bf16.
+ * A plan holds the encoded TMA descriptors for one (tensor, shape) binding. */
+typedef struct ditsep_conv_plan ditsep_conv_plan;
+int ditsep_conv_tc_plan_create(ditsep_conv_plan** plan, const void* in, int B, int H, int W, int Cin, int ld_in,
+                               const void* w_bf16, int Cout, int ksize);
+void ditsep_conv_tc_plan_destroy(ditsep_conv_plan* plan);
+int ditsep_conv_tc_run(const ditsep_conv_plan* plan, const float* bias, const float* bias_b, int ld_bias_b,
+                       const void* residual, int res_dtype, int ld_res, float out_scale, void* out, int out_dtype,
+                       int ld_out, void* stream);
+
+/* ---- attention (single head, all H*W tokens) ------------------------------------------
+ * AttnBlockpp.forward core (layerspp.py:88-92): o = softmax(q k^T / sqrt(C)) v per image.
+ * q, k, v, o: NHWC [B][S][ld] with C channels. */
+int ditsep_attention(const void* q, const void* k, const void* v, int dtype, int B, int S, int C, int ld_qkv,
+                     void* o, int ld_o, void* stream);
+
+/* ---- time embedding ---------------------------------------------------------------------
+ * ncsnpp.py:325-346 + layerspp.py:44-46: act_temb = SiLU(Linear2(SiLU(Linear1(
+ * [sin, cos](2 pi W log t))))) -- the SiLU every res-block applies before Dense_0
+ * (layerspp.py:317) is folded in.  W: (nf,), w1: (4nf, 2nf), w2: (4nf, 4nf).  out: (B, 4nf). */
+int ditsep_temb_mlp(const float* t, const float* gfp_w, const float* w1, const float* b1, const float* w2,
+                    const float* b2, float* act_temb, int B, int nf, void* stream);
+/* All res-blocks' Dense_0 at once: out[b, r] = dense_w[r, :] . act_temb[b, :] + dense_b[r],
+ * dense_w: (R, 4nf) rows of all blocks concatenated.  out: (B, R). */
+int ditsep_temb_dense(const float* act_temb, const float* dense_w, const float* dense_b, float* out, int B, int K,
+                      int R, void* stream);
+
+/* ---- small elementwise helpers ------------------------------------------------------------
+ * output layer (ncsnpp.py:473-477): out[b,p,:] = Wout (x[b,p,:] / t[b]) + bout, 1x1 conv
+ * Cin -> Cout on the progressive pyramid, fp32 out.  x NHWC of `dtype`. */
+int ditsep_output_layer(const void* x, int dtype, int B, int64_t HW, int Cin, int ld_x, const float* t,
+                        int scale_by_sigma, const float* w, const float* bias, int Cout, float* out, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* DITSEP_B200_H */
