@@ -1,0 +1,443 @@
+"""Execution engine of the NCSN++ score network: NHWC activations, one plan per input shape.
+
+``NcsnppEngine`` turns ``NCSNpp.forward`` (src/models/diffsep/ncsnpp.py:320-478) into a
+fixed list of kernel launches through the C ABI (``ops``):
+
+* weights are re-packed once per parameter version: conv filters to ``[Cout][tap][Cin]``
+  (fp32 for the CUDA-core path, bf16 for the tcgen05 path), the three attention
+  projections q/k/v to one ``[3C][C]`` 1x1 filter, all res-blocks' ``Dense_0`` to one
+  ``[R][4nf]`` matrix evaluated by a single launch per step;
+* activations are NHWC (pixel-major) so that channel vectors are contiguous for the
+  implicit-GEMM K dimension and for the 8-channel vector packs of the HBM-bound kernels;
+* the U-Net skip concatenations (``torch.cat([h, hs.pop()], dim=1)``, ncsnpp.py:413) cost
+  nothing: every down-path tensor is produced directly inside the channel slice of the
+  concat buffer that its up-path consumer reads (pixel stride ``ld`` > C);
+* the res-block tail ``(shortcut + h) / sqrt(2)`` (layerspp.py:322-328), the temb bias add
+  (:316-317) and the Combine / progressive-pyramid sums are conv epilogues.
+
+A plan is a list of ``(fn, args, kwargs)`` built once per (B, H, W); executing it issues
+only kernel launches (no allocation, no host sync), which makes it CUDA-graph capturable.
+"""
+from __future__ import annotations
+
+import math
+from dataclasses import dataclass
+from typing import Dict, List, Optional, Tuple
+
+import torch
+
+from ... import ops
+
+
+@dataclass
+class ModuleSpec:
+    """One entry of ``NCSNpp.all_modules`` (ncsnpp.py:107-309)."""
+
+    kind: str  # gfp | linear | conv3x3 | resblock | attn | combine | gn
+    in_ch: int = 0
+    out_ch: int = 0
+    up: bool = False
+    down: bool = False
+
+
+def layout_of(m) -> List[ModuleSpec]:
+    """Order and shapes of ``all_modules`` for the supported configuration family."""
+    nf, R = m.nf, m.num_resolutions
+    channels = m.num_channels_in
+    mods = [ModuleSpec("gfp", out_ch=nf), ModuleSpec("linear", 2 * nf, 4 * nf), ModuleSpec("linear", 4 * nf, 4 * nf),
+            ModuleSpec("conv3x3", channels, nf)]
+    hs_c = [nf]
+    in_ch = nf
+    for lvl in range(R):
+        for _ in range(m.num_res_blocks):
+            out_ch = nf * m.ch_mult[lvl]
+            mods.append(ModuleSpec("resblock", in_ch, out_ch))
+            in_ch = out_ch
+            if m.all_resolutions[lvl] in m.attn_resolutions:
+                mods.append(ModuleSpec("attn", in_ch, in_ch))
+            hs_c.append(in_ch)
+        if lvl != R - 1:
+            mods.append(ModuleSpec("resblock", in_ch, in_ch, down=True))
+            mods.append(ModuleSpec("combine", channels, in_ch))
+            hs_c.append(in_ch)
+    in_ch = hs_c[-1]
+    mods += [ModuleSpec("resblock", in_ch, in_ch), ModuleSpec("attn", in_ch, in_ch), ModuleSpec("resblock", in_ch, in_ch)]
+    for lvl in reversed(range(R)):
+        for _ in range(m.num_res_blocks + 1):
+            out_ch = nf * m.ch_mult[lvl]
+            mods.append(ModuleSpec("resblock", in_ch + hs_c.pop(), out_ch))
+            in_ch = out_ch
+        if m.all_resolutions[lvl] in m.attn_resolutions:
+            mods.append(ModuleSpec("attn", in_ch, in_ch))
+        mods.append(ModuleSpec("gn", in_ch, in_ch))
+        mods.append(ModuleSpec("conv3x3", in_ch, channels))
+        if lvl != 0:
+            mods.append(ModuleSpec("resblock", in_ch, in_ch, up=True))
+    assert not hs_c
+    return mods
+
+
+class _Pool:
+    """Shape-keyed pool of temporaries used while a plan is being built."""
+
+    def __init__(self, device):
+        self.device = device
+        self.free: Dict[Tuple, List[torch.Tensor]] = {}
+        self.total_bytes = 0
+
+    def get(self, shape, dtype) -> torch.Tensor:
+        key = (tuple(shape), dtype)
+        lst = self.free.get(key)
+        if lst:
+            return lst.pop()
+        t = torch.empty(shape, device=self.device, dtype=dtype)
+        self.total_bytes += t.numel() * t.element_size()
+        return t
+
+    def put(self, t: torch.Tensor):
+        self.free.setdefault((tuple(t.shape), t.dtype), []).append(t)
+
+
+class _ConvW:
+    """Packed filter of one convolution."""
+
+    def __init__(self, w_f32, bias, ksize, w_bf16=None):
+        self.w, self.bias, self.ksize, self.w_bf16 = w_f32, bias, ksize, w_bf16
+        self.cout, self.cin = w_f32.shape[0], w_f32.shape[2]
+
+
+def _pack_conv(weight: torch.Tensor, bias: torch.Tensor, want_bf16: bool) -> _ConvW:
+    """(Cout, Cin, kh, kw) -> [Cout][tap][Cin] fp32 (+ bf16 copy with Cout padded to 16)."""
+    cout, cin, kh, kw = weight.shape
+    w = weight.detach().float().permute(0, 2, 3, 1).reshape(cout, kh * kw, cin).contiguous()
+    wb = None
+    if want_bf16 and cin % 64 == 0:
+        cp = (cout + 15) // 16 * 16
+        wb = torch.zeros(cp, kh * kw, cin, device=w.device, dtype=torch.bfloat16)
+        wb[:cout] = w.to(torch.bfloat16)
+    return _ConvW(w, bias.detach().float().contiguous(), kh, wb)
+
+
+class NcsnppEngine:
+    def __init__(self, model):
+        self.m = model
+        self._wkey = None
+        self._plans: Dict[Tuple, "_Plan"] = {}
+        self.w: Dict[str, object] = {}
+
+    # ------------------------------------------------------------------ weights
+    def _weights_key(self):
+        ps = list(self.m.parameters())
+        return (self.m.precision, tuple((p.data_ptr(), p._version) for p in ps))
+
+    def _pack(self):
+        key = self._weights_key()
+        if key == self._wkey:
+            return
+        m = self.m
+        bf = m.precision == "bf16"
+        w: Dict[str, object] = {}
+        am = m.all_modules
+        dense_w, dense_b, off = [], [], 0
+        for i, spec in enumerate(m.layout):
+            mod = am[i]
+            if spec.kind == "gfp":
+                w["gfp"] = mod.W.detach().float().contiguous()
+            elif spec.kind == "linear":
+                w[f"lin{i}"] = (mod.weight.detach().float().contiguous(), mod.bias.detach().float().contiguous())
+            elif spec.kind == "conv3x3":
+                w[f"conv{i}"] = _pack_conv(mod.weight, mod.bias, bf)
+            elif spec.kind == "gn":
+                w[f"gn{i}"] = (mod.weight.detach().float().contiguous(), mod.bias.detach().float().contiguous())
+            elif spec.kind == "combine":
+                w[f"conv{i}"] = _pack_conv(mod.Conv_0.weight, mod.Conv_0.bias, bf)
+            elif spec.kind == "attn":
+                w[f"gn{i}"] = (mod.GroupNorm_0.weight.detach().float().contiguous(),
+                               mod.GroupNorm_0.bias.detach().float().contiguous())
+                # NIN: y = x W + b with W (in, out) -> 1x1 filter [out][in]
+                wq = torch.cat([mod.NIN_0.W.detach().t(), mod.NIN_1.W.detach().t(), mod.NIN_2.W.detach().t()], dim=0)
+                bq = torch.cat([mod.NIN_0.b.detach(), mod.NIN_1.b.detach(), mod.NIN_2.b.detach()], dim=0)
+                w[f"qkv{i}"] = _pack_conv(wq[:, :, None, None], bq, bf)
+                w[f"proj{i}"] = _pack_conv(mod.NIN_3.W.detach().t()[:, :, None, None], mod.NIN_3.b, bf)
+            elif spec.kind == "resblock":
+                w[f"gn{i}a"] = (mod.GroupNorm_0.weight.detach().float().contiguous(),
+                                mod.GroupNorm_0.bias.detach().float().contiguous())
+                w[f"gn{i}b"] = (mod.GroupNorm_1.weight.detach().float().contiguous(),
+                                mod.GroupNorm_1.bias.detach().float().contiguous())
+                w[f"conv{i}a"] = _pack_conv(mod.Conv_0.weight, mod.Conv_0.bias, bf)
+                w[f"conv{i}b"] = _pack_conv(mod.Conv_1.weight, mod.Conv_1.bias, bf)
+                if hasattr(mod, "Conv_2"):
+                    w[f"conv{i}c"] = _pack_conv(mod.Conv_2.weight, mod.Conv_2.bias, bf)
+                dense_w.append(mod.Dense_0.weight.detach().float())
+                dense_b.append(mod.Dense_0.bias.detach().float())
+                w[f"dense_off{i}"] = off
+                off += spec.out_ch
+        w["dense_w"] = torch.cat(dense_w, dim=0).contiguous()
+        w["dense_b"] = torch.cat(dense_b, dim=0).contiguous()
+        w["dense_rows"] = off
+        ol = m.output_layer
+        w["out_w"] = ol.weight.detach().float().reshape(ol.weight.shape[0], ol.weight.shape[1]).contiguous()
+        w["out_b"] = ol.bias.detach().float().contiguous()
+        self.w = w
+        self._wkey = key
+        self._plans.clear()  # plans hold pointers to the packed tensors
+
+    # ------------------------------------------------------------------ entry points
+    def plan(self, B: int, H: int, W: int, device) -> "_Plan":
+        self._pack()
+        key = (B, H, W, str(device))
+        p = self._plans.get(key)
+        if p is None:
+            p = _Plan(self, B, H, W, device)
+            self._plans[key] = p
+        return p
+
+    def forward_nhwc(self, feat: torch.Tensor, time_cond: torch.Tensor, affine_done: bool = True) -> torch.Tensor:
+        """feat: (B, H, W, Cin) fp32 NHWC, with NCSN++'s ``2x-1`` (ncsnpp.py:348-350) already
+        applied unless the model is ``centered``.  Returns the plan's output buffer
+        (B, H, W, Cout) fp32 -- valid until the next call."""
+        if not feat.is_cuda and not ops.EMULATED:
+            raise ops.DitsepError("NCSNpp runs on sm_100a only; there is no CPU fallback")
+        if not affine_done and not self.m.centered:
+            feat = 2 * feat - 1.0
+        B, H, W, C = feat.shape
+        p = self.plan(B, H, W, feat.device)
+        if feat.data_ptr() != p.feat.data_ptr():
+            p.feat.copy_(feat)
+        p.t.copy_(time_cond)
+        p.run()
+        return p.out
+
+
+class _Plan:
+    """Buffers + launch list for one (B, H, W)."""
+
+    def __init__(self, eng: NcsnppEngine, B: int, H: int, W: int, device):
+        m, w = eng.m, eng.w
+        self.eng, self.B, self.H, self.W, self.device = eng, B, H, W, device
+        self.steps: List[Tuple] = []
+        adt = torch.bfloat16 if m.precision == "bf16" else torch.float32
+        self.adt = adt
+        f32 = torch.float32
+        nf, R = m.nf, m.num_resolutions
+        if H % (1 << (R - 1)) or W % (1 << (R - 1)):
+            raise ops.DitsepError(f"NCSNpp input {H}x{W} must be divisible by {1 << (R - 1)}")
+        pool = _Pool(device)
+        self.pool = pool
+        new = lambda *shape, dtype=adt: torch.empty(shape, device=device, dtype=dtype)  # noqa: E731
+        Cin0 = m.num_channels_in
+        self.feat = new(B, H, W, Cin0, dtype=f32)
+        self.t = new(B, dtype=f32)
+        self.out = new(B, H, W, m.num_channels_out, dtype=f32)
+        self.act_temb = new(B, 4 * nf, dtype=f32)
+        self.dense = new(B, w["dense_rows"], dtype=f32)
+        cmax = max(max(s.in_ch, s.out_ch) for s in m.layout)
+        self.gn_partial = new((4 * ops.NUM_SMS + B) * cmax * 2 * 2, dtype=f32)
+        self._tc_plans = []
+        add = self.steps.append
+
+        # ---- time embedding (ncsnpp.py:325-346) + every res-block's Dense_0 (layerspp.py:316-317)
+        add((ops.temb_mlp, (self.t, w["gfp"], *w["lin1"], *w["lin2"], self.act_temb), {}))
+        add((ops.temb_dense, (self.act_temb, w["dense_w"], w["dense_b"], self.dense), {}))
+
+        # ---- where does every U-Net tensor live?  (static replay of the hs push / pop order)
+        layout = m.layout
+        res = [(H >> l, W >> l) for l in range(R)]
+        # down-path pushes: (level, channels)
+        pushes = [(0, nf)]
+        i = 4
+        in_ch = nf
+        for lvl in range(R):
+            for _ in range(m.num_res_blocks):
+                in_ch = layout[i].out_ch
+                i += 1
+                if layout[i].kind == "attn":
+                    i += 1
+                pushes.append((lvl, in_ch))
+            if lvl != R - 1:
+                i += 2
+                pushes.append((lvl + 1, in_ch))
+        # up-path consumers pop in reverse order; consumer j reads cat[h_j, push[n-1-j]]
+        n_up = len(pushes)
+        i_mid = i
+        up_specs = [s for s in layout[i_mid + 3:] if s.kind == "resblock" and not s.up]
+        assert len(up_specs) == n_up
+        self.concat: List[torch.Tensor] = []
+        for j, spec in enumerate(up_specs):
+            lvl, cs = pushes[n_up - 1 - j]
+            hh, ww = res[lvl]
+            self.concat.append(new(B, hh, ww, spec.in_ch))
+        def skip_slot(k):  # destination of push k  # noqa: E306
+            j = n_up - 1 - k
+            cs = pushes[k][1]
+            return self.concat[j][..., self.concat[j].shape[3] - cs:]
+        def h_slot(j):  # destination of the main-path tensor feeding up-block j  # noqa: E306
+            cs = pushes[n_up - 1 - j][1]
+            return self.concat[j][..., :self.concat[j].shape[3] - cs]
+
+        # ---- down path (ncsnpp.py:352-397)
+        pyr_in = self.feat
+        k = 0
+        cur = skip_slot(k)
+        self._conv(self.feat, w["conv3"], cur)
+        k += 1
+        i = 4
+        for lvl in range(R):
+            for _ in range(m.num_res_blocks):
+                spec = layout[i]
+                if layout[i + 1].kind == "attn":
+                    hh, ww = res[lvl]
+                    tmp = pool.get((B, hh, ww, spec.out_ch), adt)
+                    self._resblock(i, spec, cur, tmp)
+                    dst = skip_slot(k)
+                    self._attn(i + 1, layout[i + 1], tmp, dst)
+                    pool.put(tmp)
+                    i += 2
+                else:
+                    dst = skip_slot(k)
+                    self._resblock(i, spec, cur, dst)
+                    i += 1
+                cur = dst
+                k += 1
+            if lvl != R - 1:
+                spec = layout[i]
+                dst = skip_slot(k)
+                self._resblock(i, spec, cur, dst)
+                hh, ww = res[lvl + 1]
+                nxt = new(B, hh, ww, Cin0, dtype=f32)  # FIR-downsampled input pyramid (ncsnpp.py:387)
+                add((ops.fir_resample, (pyr_in, False), {"out_x": nxt}))
+                pyr_in = nxt
+                # Combine "sum" (layerspp.py:57-62): dst = Conv_0(pyramid) + dst
+                self._conv(pyr_in, w[f"conv{i + 1}"], dst, residual=dst)
+                i += 2
+                cur = dst
+                k += 1
+        assert k == n_up and i == i_mid
+
+        # ---- middle (ncsnpp.py:399-405)
+        hh, ww = res[R - 1]
+        c = layout[i].out_ch
+        t1, t2 = pool.get((B, hh, ww, c), adt), pool.get((B, hh, ww, c), adt)
+        self._resblock(i, layout[i], cur, t1)
+        self._attn(i + 1, layout[i + 1], t1, t2)
+        self._resblock(i + 2, layout[i + 2], t2, h_slot(0))
+        pool.put(t1)
+        pool.put(t2)
+        i += 3
+
+        # ---- up path (ncsnpp.py:410-460)
+        pyramid = None
+        j = 0
+        for lvl in reversed(range(R)):
+            hh, ww = res[lvl]
+            for b in range(m.num_res_blocks + 1):
+                spec = layout[i]
+                last_of_level = b == m.num_res_blocks
+                if last_of_level:
+                    dst = pool.get((B, hh, ww, spec.out_ch), adt)
+                else:
+                    dst = h_slot(j + 1)
+                self._resblock(i, spec, self.concat[j], dst)
+                cur = dst
+                i += 1
+                j += 1
+            if layout[i].kind == "attn":
+                tmp = pool.get((B, hh, ww, layout[i].in_ch), adt)
+                self._attn(i, layout[i], cur, tmp)
+                pool.put(cur)
+                cur = tmp
+                i += 1
+            # progressive output skip: GN -> SiLU -> conv3x3(C -> Cin0), summed over levels
+            cch = layout[i].in_ch
+            ss = new(B, 2, cch, dtype=f32)
+            g = w[f"gn{i}"]
+            add((ops.gn_stats, (cur, min(cch // 4, 32), g[0], g[1], 1e-6, self.gn_partial, ss), {}))
+            hact = pool.get((B, hh, ww, cch), adt)
+            add((ops.gn_apply, (cur, ss, True, hact), {}))
+            i += 1
+            newpyr = new(B, hh, ww, Cin0, dtype=f32)
+            if pyramid is None:
+                self._conv(hact, w[f"conv{i}"], newpyr)
+            else:
+                add((ops.fir_resample, (pyramid, True), {"out_x": newpyr}))
+                self._conv(hact, w[f"conv{i}"], newpyr, residual=newpyr)
+            pool.put(hact)
+            pyramid = newpyr
+            i += 1
+            if lvl != 0:
+                spec = layout[i]
+                self._resblock(i, spec, cur, h_slot(j))
+                pool.put(cur)
+                i += 1
+            else:
+                pool.put(cur)
+        assert i == len(layout) and j == n_up
+        add((ops.output_layer, (pyramid, self.t, w["out_w"], w["out_b"], self.out, bool(m.scale_by_sigma)), {}))
+
+    # ------------------------------------------------------------------ building blocks
+    def _conv(self, x, cw: _ConvW, out, bias_b=None, residual=None, out_scale: float = 1.0):
+        """3x3 / 1x1 conv with the fused epilogue; tcgen05 path when the shape allows it."""
+        use_tc = (cw.w_bf16 is not None and x.dtype == torch.bfloat16 and not ops.EMULATED and ops.tc_enabled())
+        if use_tc:
+            plan = ops.ConvTcPlan(x, cw.w_bf16, cw.cout, cw.ksize)
+            self._tc_plans.append(plan)
+            self.steps.append((plan.run, (cw.bias, out), {"bias_b": bias_b, "residual": residual, "out_scale": out_scale}))
+        else:
+            self.steps.append((ops.conv_direct, (x, cw.w, cw.bias, out, cw.ksize),
+                               {"bias_b": bias_b, "residual": residual, "out_scale": out_scale}))
+
+    def _resblock(self, i: int, spec: ModuleSpec, x, out):
+        """ResnetBlockBigGANpp.forward (layerspp.py:296-328)."""
+        w, pool, add = self.eng.w, self.pool, self.steps.append
+        B, H, W, cin = x.shape
+        cout = spec.out_ch
+        f32 = torch.float32
+        ss0 = torch.empty(B, 2, cin, device=self.device, dtype=f32)
+        g0, g1 = w[f"gn{i}a"], w[f"gn{i}b"]
+        add((ops.gn_stats, (x, min(cin // 4, 32), g0[0], g0[1], 1e-6, self.gn_partial, ss0), {}))
+        if spec.up or spec.down:
+            Ho, Wo = (2 * H, 2 * W) if spec.up else (H // 2, W // 2)
+            xr = pool.get((B, Ho, Wo, cin), self.adt)
+            hA = pool.get((B, Ho, Wo, cin), self.adt)
+            add((ops.fir_resample, (x, spec.up), {"out_x": xr, "scale_shift": ss0, "out_h": hA}))
+        else:
+            Ho, Wo = H, W
+            xr = x
+            hA = pool.get((B, H, W, cin), self.adt)
+            add((ops.gn_apply, (x, ss0, True, hA), {}))
+        h1 = pool.get((B, Ho, Wo, cout), self.adt)
+        off = w[f"dense_off{i}"]
+        self._conv(hA, w[f"conv{i}a"], h1, bias_b=self.dense[:, off:off + cout])
+        pool.put(hA)
+        ss1 = torch.empty(B, 2, cout, device=self.device, dtype=f32)
+        add((ops.gn_stats, (h1, min(cout // 4, 32), g1[0], g1[1], 1e-6, self.gn_partial, ss1), {}))
+        add((ops.gn_apply, (h1, ss1, True, h1), {}))  # in place
+        if f"conv{i}c" in w:
+            self._conv(xr, w[f"conv{i}c"], out)
+            res = out
+        else:
+            res = xr
+        self._conv(h1, w[f"conv{i}b"], out, residual=res, out_scale=1.0 / math.sqrt(2.0))
+        pool.put(h1)
+        if xr is not x:
+            pool.put(xr)
+
+    def _attn(self, i: int, spec: ModuleSpec, x, out):
+        """AttnBlockpp.forward (layerspp.py:81-97)."""
+        w, pool, add = self.eng.w, self.pool, self.steps.append
+        B, H, W, C = x.shape
+        ss = torch.empty(B, 2, C, device=self.device, dtype=torch.float32)
+        g = w[f"gn{i}"]
+        add((ops.gn_stats, (x, min(C // 4, 32), g[0], g[1], 1e-6, self.gn_partial, ss), {}))
+        hn = pool.get((B, H, W, C), self.adt)
+        add((ops.gn_apply, (x, ss, False, hn), {}))
+        qkv = pool.get((B, H, W, 3 * C), self.adt)
+        self._conv(hn, w[f"qkv{i}"], qkv)
+        add((ops.attention, (qkv[..., :C], qkv[..., C:2 * C], qkv[..., 2 * C:], hn), {}))
+        self._conv(hn, w[f"proj{i}"], out, residual=x, out_scale=1.0 / math.sqrt(2.0))
+        pool.put(hn)
+        pool.put(qkv)
+
+    def run(self):
+        for fn, args, kwargs in self.steps:
+            fn(*args, **kwargs)

@@ -12,10 +12,22 @@ from typing import Optional, Tuple
 
 import torch
 
+import os
+
 from . import _lib
-from ._lib import SdeParams, check
+from ._lib import DitsepError, SdeParams, check  # noqa: F401  (re-exported)
 
 F32, BF16 = 0, 1
+NUM_SMS = 148
+# Set only by tests/emu_ops.py, which swaps these wrappers for torch restatements so the host
+# logic (launch plans, buffer aliasing, sampler loop) can be checked on a CPU-only box.
+EMULATED = False
+
+
+def tc_enabled() -> bool:
+    """tcgen05 convolution path on (default) unless DITSEP_DISABLE_TC=1 (debug aid)."""
+    return os.environ.get("DITSEP_DISABLE_TC", "0") != "1"
+
 _DT = {torch.float32: F32, torch.bfloat16: BF16}
 
 
@@ -192,6 +204,7 @@ class ConvTcPlan:
         self._h = C.c_void_p()
         self._keep = (x, w_bf16)
         self.Cout = Cout
+        self.K = ksize * ksize * Cin
         self.shape = (B, H, W)
         check(_lib.load().ditsep_conv_tc_plan_create(C.byref(self._h), _ptr(x), B, H, W, Cin, nhwc_ld(x), _ptr(w_bf16),
                                                      Cout, ksize), "conv_tc_plan_create")

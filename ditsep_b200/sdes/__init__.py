@@ -1,0 +1,74 @@
+"""Sampler factories (mirror of src/sdes/__init__.py).
+
+``get_pc_sampler`` (:133-193) keeps the reference signature and return convention
+``sampler() -> (x, nfe[, intermediates])``.  Two keyword extensions (absorbed by the
+reference's ``**kwargs``, so existing call sites stay valid):
+
+* ``noise_tape``: callable ``(i, like) -> tensor`` supplying draw i (parity runs);
+* ``seed``: Philox seed of the in-kernel noise (default: taken from torch's generator).
+
+The loop body is two fused-kernel launches plus two score-network evaluations per step;
+the state ``xt`` is updated in place and ``xt_mean`` is only materialised when it is
+consumed (last step with ``denoise=True``, or ``intermediate=True``).
+"""
+from __future__ import annotations
+
+import torch
+
+from .correctors import Corrector, CorrectorRegistry
+from .predictors import Predictor, PredictorRegistry, ReverseDiffusionPredictor
+from .sdes import SDE, MixSDE, NoiseSource, OUVESDE, SDERegistry
+
+__all__ = ["PredictorRegistry", "CorrectorRegistry", "SDERegistry", "Predictor", "Corrector", "SDE", "MixSDE",
+           "OUVESDE", "NoiseSource", "ReverseDiffusionPredictor", "get_pc_sampler", "get_pc_scheduled_sampler",
+           "get_ode_sampler", "get_sb_sampler"]
+
+
+def get_pc_sampler(predictor_name, corrector_name, sde, score_fn, y, true_mean=None, denoise=True, eps=3e-2, snr=0.1,
+                   corrector_steps=1, probability_flow: bool = False, intermediate=False, n_spkrs=2, noise_tape=None,
+                   seed=None, **kwargs):
+    """Create a Predictor-Corrector sampler (sdes/__init__.py:133-193)."""
+    predictor_cls = PredictorRegistry.get_by_name(predictor_name)
+    corrector_cls = CorrectorRegistry.get_by_name(corrector_name)
+    noise = NoiseSource(tape=noise_tape, seed=seed)
+    predictor = predictor_cls(sde, score_fn, probability_flow=probability_flow, noise=noise)
+    corrector = corrector_cls(sde, score_fn, snr=snr, n_steps=corrector_steps, noise=noise)
+
+    def pc_sampler():
+        im = [] if intermediate else None
+        noise.reset()
+        with torch.no_grad():
+            shape = torch.Size((y.shape[0], n_spkrs, *y.shape[2:]))
+            cond = true_mean if true_mean is not None else y
+            xt = sde.prior_sampling(shape, cond, noise=noise).to(cond.device)
+            # all N time vectors in one go (the reference builds ones(B) * t every step)
+            timesteps = torch.linspace(sde.T, eps, sde.N, device=y.device)
+            vec_ts = timesteps[:, None].expand(sde.N, y.shape[0]).contiguous()
+            xt_mean = xt
+            for i in range(sde.N):
+                vec_t = vec_ts[i]
+                last = i == sde.N - 1
+                xt, xt_mean = corrector.update_fn(xt, vec_t, y, _inplace=not intermediate, _want_mean=intermediate)
+                if intermediate:
+                    im.append((xt, xt_mean))
+                xt, xt_mean = predictor.update_fn(xt, vec_t, y, _inplace=not intermediate,
+                                                  _want_mean=intermediate or (last and denoise))
+            x_result = xt_mean if denoise else xt
+            ns = sde.N * (corrector.n_steps + 1)
+            if intermediate:
+                return x_result, ns, im
+            return x_result, ns
+
+    return pc_sampler
+
+
+def get_pc_scheduled_sampler(*args, **kwargs):
+    raise NotImplementedError("scheduled PC sampler (sdes/__init__.py:49-130) is SURVEY.md 8f item 2, not built yet")
+
+
+def get_ode_sampler(*args, **kwargs):
+    raise NotImplementedError("PF-ODE sampler (sdes/__init__.py:196-281) is SURVEY.md 8f item 2, not built yet")
+
+
+def get_sb_sampler(*args, **kwargs):
+    raise NotImplementedError("SB sampler (sdes/__init__.py:284-389) is SURVEY.md 8f item 2, not built yet")

@@ -1,0 +1,82 @@
+"""Predictors of the PC sampler (mirror of src/sdes/predictors.py).
+
+``reverse_diffusion`` (:55-66) runs as ONE fused sm_100a kernel per update
+(``csrc/pc_step.cu``): drift, diffusion, the score term, the noise draw and the state
+update in a single coalesced pass.  ``none`` (:69-76) is the identity.
+``euler_maruyama`` (:39-52) is not on the hot path and not fused yet.
+"""
+from __future__ import annotations
+
+import abc
+
+import torch
+
+from .. import ops
+from ..utils.registry import Registry
+from .sdes import NoiseSource
+
+PredictorRegistry = Registry("Predictor")
+
+
+class Predictor(abc.ABC):
+    """Abstract predictor (predictors.py:10-36).  ``noise`` is this repo's extension: the
+    shared ``NoiseSource`` of the sampler (tape or Philox); default = fresh Philox source."""
+
+    def __init__(self, sde, score_fn, probability_flow=False, noise: NoiseSource = None):
+        super().__init__()
+        self.sde = sde
+        self.rsde = sde.reverse(score_fn)
+        self.score_fn = score_fn
+        self.probability_flow = probability_flow
+        self.noise = noise
+
+    def _noise(self):
+        if self.noise is None:
+            self.noise = NoiseSource()
+        return self.noise
+
+    @abc.abstractmethod
+    def update_fn(self, x, t, *args):
+        pass
+
+    def debug_update_fn(self, x, t, *args):
+        raise NotImplementedError(f"Debug update function not implemented for predictor {self}.")
+
+
+@PredictorRegistry.register("reverse_diffusion")
+class ReverseDiffusionPredictor(Predictor):
+    def __init__(self, sde, score_fn, probability_flow=False, noise: NoiseSource = None):
+        super().__init__(sde, score_fn, probability_flow=probability_flow, noise=noise)
+        if probability_flow:
+            raise NotImplementedError("probability_flow=True has no fused kernel (not on the PC sampler path)")
+
+    def update_fn(self, x, t, *args, _inplace=False, _want_mean=True, **kwargs):
+        """x_mean = x - (f - G^2 score), x = x_mean + G z (predictors.py:60-66 with
+        sdes.py:94-108,165-173).  Returns (x, x_mean).  The private keywords let the sampler
+        update its own state in place and skip the x_mean store when it is not consumed."""
+        y = args[0] if args else None
+        score = self.score_fn(x, t, *args)
+        p = self.sde.fused_params(n_src=x.shape[1])
+        x_out = x if _inplace else x.clone()
+        x_mean = torch.empty_like(x_out) if _want_mean else None
+        z, seed, draw = self._noise().next(x_out)
+        ops.pc_predictor(p, x_out, score.contiguous(), t.contiguous(), None if y is None else y.contiguous(), noise=z,
+                         seed=seed, draw=draw, x_mean=x_mean)
+        return x_out, x_mean
+
+
+@PredictorRegistry.register("euler_maruyama")
+class EulerMaruyamaPredictor(Predictor):
+    def update_fn(self, x, t, *args, **kwargs):
+        raise NotImplementedError("euler_maruyama is outside the fused PC-sampler hot path (SURVEY.md 8f item 2)")
+
+
+@PredictorRegistry.register("none")
+class NonePredictor(Predictor):
+    """An empty predictor that does nothing (predictors.py:69-76)."""
+
+    def __init__(self, *args, **kwargs):
+        pass
+
+    def update_fn(self, x, t, *args, **kwargs):
+        return x, x

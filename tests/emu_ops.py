@@ -1,0 +1,215 @@
+"""CPU stand-ins for the C-ABI wrappers in ``ditsep_b200.ops`` -- TEST INFRASTRUCTURE.
+
+The product path has no CPU fallback.  To check the HOST logic (launch plans, NHWC buffer
+aliasing, concat-slot placement, weight packing, sampler loop, noise numbering) on a box
+without a GPU, the ``-m "not gpu"`` tests swap every ``ops.*`` kernel wrapper for a small
+torch restatement with the SAME calling convention (in-place writes into caller-allocated
+NHWC views).  Each stand-in documents the kernel it mirrors; the ``-m gpu`` tests then check
+the real kernels against the oracle.
+"""
+from __future__ import annotations
+
+import contextlib
+import math
+
+import torch
+import torch.nn.functional as F
+
+from ditsep_b200 import ops
+
+_NAMES = ["pc_corrector", "pc_predictor", "pc_prior", "philox_normal", "stft_compress", "expand_istft", "gn_stats",
+          "gn_apply", "fir_resample", "conv_direct", "attention", "temb_mlp", "temb_dense", "output_layer"]
+
+
+def _coef(p, mode, t):
+    """make_coef of csrc/pc_step.cu, vectorised over the batch (t: (B,))."""
+    ratio = p.sigma_max / p.sigma_min
+    logsig = math.log(ratio)
+    dt = 1.0 / p.N
+    z = torch.zeros_like(t)
+    c = dict(a0=z + 1, a1=z, a2=z, a3=z, a4=z, b0=z, b1=z)
+    if p.sde == 0:
+        lam = p.p0
+        srp = ratio ** (2 * t)
+        mult = p.sigma_min ** 2
+        ev1 = mult * (srp - 1)
+        ev2 = mult * (srp - torch.exp(-2 * lam * t)) / (1 + lam / logsig)
+        r1, r2 = ev1.sqrt(), ev2.sqrt()
+        if mode == "corrector":
+            st = 2 * p.snr ** 2
+            c.update(a2=st * ev2, a3=st * (ev1 - ev2), b0=2 * p.snr * r2, b1=2 * p.snr * (r1 - r2))
+        elif mode == "predictor":
+            G = p.sigma_min * ratio ** t * math.sqrt(2 * logsig) * math.sqrt(dt)
+            c.update(a0=z + 1 + lam * dt, a1=z - lam * dt, a2=G * G, b0=G)
+        else:
+            c.update(a0=z, a4=z + 0.5, b0=r2, b1=r1 - r2)
+    else:
+        th = p.p0
+        std = torch.sqrt(p.sigma_min ** 2 * torch.exp(-2 * th * t) * (torch.exp(2 * (th + logsig) * t) - 1) * logsig
+                         / (th + logsig))
+        if mode == "corrector":
+            eps = 2 * (p.snr * std) ** 2
+            c.update(a2=eps, b0=torch.sqrt(2 * eps))
+        elif mode == "predictor":
+            G = p.sigma_min * ratio ** t * math.sqrt(2 * logsig) * math.sqrt(dt)
+            c.update(a0=z + 1 + th * dt, a4=z - th * dt, a2=G * G, b0=G)
+        else:
+            c.update(a0=z, a4=z + 1, b0=std)
+    return c
+
+
+def _pc(p, mode, x, score, t, y, noise, x_mean):
+    if noise is None:
+        raise AssertionError("the CPU stand-in needs a noise tape (Philox lives in the kernel)")
+    B = x.shape[0]
+    tt = torch.ones(B) if t is None else t
+    c = _coef(p, mode, tt.double())
+    v = lambda a: a.reshape(B, *([1] * (x.ndim - 1)))  # noqa: E731
+    xs = torch.zeros_like(x, dtype=torch.float64) if mode == "prior" else x.double()
+    s = torch.zeros_like(xs) if score is None else score.double()
+    z = noise.double()
+    xb, sb, zb = (a.mean(dim=1, keepdim=True) for a in (xs, s, z))
+    yy = 0.0 if y is None else y.double().reshape(B, 1, *x.shape[2:])
+    m = v(c["a0"]) * xs + v(c["a1"]) * xb + v(c["a2"]) * s + v(c["a3"]) * sb + v(c["a4"]) * yy
+    x.copy_((m + v(c["b0"]) * z + v(c["b1"]) * zb).float())
+    if x_mean is not None:
+        x_mean.copy_(m.float())
+
+
+def pc_corrector(p, x, score, t, noise=None, seed=0, draw=0, x_mean=None):
+    _pc(p, "corrector", x, score, t, None, noise, x_mean)
+
+
+def pc_predictor(p, x, score, t, y, noise=None, seed=0, draw=0, x_mean=None):
+    _pc(p, "predictor", x, score, t, y if p.sde == 1 else None, noise, x_mean)
+
+
+def pc_prior(p, x, y, noise=None, seed=0, draw=0):
+    _pc(p, "prior", x, None, None, y, noise, None)
+
+
+def philox_normal(out, seed, draw):
+    out.normal_(generator=torch.Generator().manual_seed(seed * 1000003 + draw))
+
+
+def stft_compress(xt, mix, window, feat, exponent, factor, affine):
+    """ditsep_stft_compress: right pad 382, STFT 510/128 centre zero pad, |X|^e e^{j arg} f,
+    [Re.., Im..], frames zero-padded to W, optional 2x-1 over the whole tile."""
+    x = torch.cat((xt, mix), dim=1)
+    B, C, T = x.shape
+    z = F.pad(x.reshape(B * C, T), (255, 255 + 382))
+    s = torch.stft(z, 510, hop_length=128, win_length=510, window=window, center=False, onesided=True,
+                   return_complex=True).reshape(B, C, 256, -1)
+    if exponent != 1:
+        s = s.abs() ** exponent * torch.exp(1j * s.angle())
+    s = s * factor
+    f = torch.cat((s.real, s.imag), dim=1)  # (B, 2C, 256, frames)
+    f = F.pad(f, (0, feat.shape[2] - f.shape[-1]))
+    if affine:
+        f = 2 * f - 1
+    feat.copy_(f.permute(0, 2, 3, 1).to(feat.dtype))
+
+
+def expand_istft(spec, window, out, exponent, factor):
+    B, n, T = out.shape
+    frames = 1 + (T + 382) // 128
+    s = spec[:, :, :frames, :].permute(0, 3, 1, 2)  # (B, 2n, 256, frames)
+    c = torch.complex(s[:, :n].contiguous(), s[:, n:].contiguous()) / abs(factor)
+    if exponent != 1:
+        c = c.abs() ** (1 / exponent) * torch.exp(1j * c.angle())
+    y = torch.istft(c.reshape(B * n, 256, frames), 510, hop_length=128, win_length=510, window=window, center=True,
+                    onesided=True).reshape(B, n, -1)
+    out.copy_(y[..., :T])
+
+
+def gn_stats(x, G, gamma, beta, eps, partial, scale_shift):
+    B, H, W, C = x.shape
+    xf = x.double().reshape(B, H * W, G, C // G)
+    mean = xf.mean(dim=(1, 3))
+    var = xf.var(dim=(1, 3), unbiased=False)
+    rstd = 1 / torch.sqrt(var + eps)
+    sc = rstd.repeat_interleave(C // G, dim=1) * gamma.double()
+    sh = beta.double() - mean.repeat_interleave(C // G, dim=1) * sc
+    scale_shift[:, 0].copy_(sc.float())
+    scale_shift[:, 1].copy_(sh.float())
+
+
+def gn_apply(x, scale_shift, silu, y):
+    v = x.float() * scale_shift[:, 0][:, None, None, :] + scale_shift[:, 1][:, None, None, :]
+    y.copy_((F.silu(v) if silu else v).to(y.dtype))
+
+
+def _fir(x_nhwc, up):
+    """upfirdn2d with k = outer([1,3,3,1])/64 (x4 when upsampling), pads (2,1) up / (1,1) down."""
+    x = x_nhwc.float().permute(0, 3, 1, 2)
+    n, c, h, w = x.shape
+    k1 = torch.tensor([1.0, 3.0, 3.0, 1.0])
+    k = torch.outer(k1, k1) / 64.0
+    z = x.reshape(n * c, 1, h, w)
+    if up:
+        buf = z.new_zeros(n * c, 1, 2 * h, 2 * w)
+        buf[:, :, ::2, ::2] = z
+        z = F.conv2d(F.pad(buf, [2, 1, 2, 1]), (k * 4).flip(0, 1)[None, None])
+    else:
+        z = F.conv2d(F.pad(z, [1, 1, 1, 1]), k.flip(0, 1)[None, None])[:, :, ::2, ::2]
+    return z.reshape(n, c, z.shape[-2], z.shape[-1]).permute(0, 2, 3, 1)
+
+
+def fir_resample(x, up, out_x=None, scale_shift=None, out_h=None):
+    if out_x is not None:
+        out_x.copy_(_fir(x, up).to(out_x.dtype))
+    if out_h is not None:
+        v = F.silu(x.float() * scale_shift[:, 0][:, None, None, :] + scale_shift[:, 1][:, None, None, :])
+        out_h.copy_(_fir(v, up).to(out_h.dtype))
+
+
+def conv_direct(x, w, bias, out, ksize, bias_b=None, residual=None, out_scale=1.0):
+    cout, taps, cin = w.shape
+    wt = w.reshape(cout, ksize, ksize, cin).permute(0, 3, 1, 2)
+    y = F.conv2d(x.float().permute(0, 3, 1, 2), wt, bias, padding=ksize // 2).permute(0, 2, 3, 1)
+    if bias_b is not None:
+        y = y + bias_b[:, None, None, :]
+    if residual is not None:
+        y = y + residual.float()
+    out.copy_((y * out_scale).to(out.dtype))
+
+
+def attention(q, k, v, o):
+    B, H, W, C = q.shape
+    qf, kf, vf = (a.float().reshape(B, H * W, C) for a in (q, k, v))
+    p = torch.softmax(qf @ kf.transpose(1, 2) * C ** -0.5, dim=-1)
+    o.copy_((p @ vf).reshape(B, H, W, C).to(o.dtype))
+
+
+def temb_mlp(t, gfp_w, w1, b1, w2, b2, act_temb):
+    xp = torch.log(t)[:, None] * gfp_w[None, :] * 2 * math.pi
+    e = torch.cat([torch.sin(xp), torch.cos(xp)], dim=-1)
+    h = F.silu(F.linear(e, w1, b1))
+    act_temb.copy_(F.silu(F.linear(h, w2, b2)))
+
+
+def temb_dense(act_temb, dense_w, dense_b, out):
+    out.copy_(F.linear(act_temb, dense_w, dense_b))
+
+
+def output_layer(x, t, w, bias, out, scale_by_sigma):
+    v = x.float()
+    if scale_by_sigma:
+        v = v / t[:, None, None, None]
+    out.copy_(v @ w.t() + bias)
+
+
+@contextlib.contextmanager
+def emulated_ops():
+    """Swap the kernel wrappers for the stand-ins above (and back)."""
+    saved = {n: getattr(ops, n) for n in _NAMES}
+    saved_flag = ops.EMULATED
+    try:
+        for n in _NAMES:
+            setattr(ops, n, globals()[n])
+        ops.EMULATED = True
+        yield
+    finally:
+        for n, f in saved.items():
+            setattr(ops, n, f)
+        ops.EMULATED = saved_flag

@@ -1,0 +1,298 @@
+"""Per-kernel parity (-m gpu): every C-ABI entry point against a torch restatement of the
+reference op (tests/emu_ops.py, fp64/fp32 on the CPU) on the same seeded inputs.
+Tolerances are written next to each check: fp32 kernels ~1e-5 relative, bf16 storage 2^-8."""
+import math
+
+import pytest
+import torch
+
+import emu_ops as E
+from ditsep_b200 import ops
+from ditsep_b200._lib import SdeParams
+
+pytestmark = pytest.mark.gpu
+DEV = "cuda"
+
+
+def rel(a, b):
+    a, b = a.double().cpu(), b.double().cpu()
+    return float((a - b).norm() / b.norm().clamp(min=1e-30))
+
+
+def g(seed):
+    return torch.Generator().manual_seed(seed)
+
+
+# ------------------------------------------------------------------ fused SDE updates
+@pytest.mark.parametrize("sde,n_src", [(0, 2), (1, 2), (1, 3), (0, 3)])
+@pytest.mark.parametrize("L", [32000, 4099, 7])
+def test_pc_updates(sde, n_src, L):
+    B = 3
+    p = SdeParams(sde, n_src, 2.0 if sde == 0 else 1.5, 0.05, 0.5, 30, 0.5)
+    x = torch.randn(B, n_src, L, generator=g(1))
+    s = torch.randn(B, n_src, L, generator=g(2))
+    z = torch.randn(B, n_src, L, generator=g(3))
+    y = torch.randn(B, 1, L, generator=g(4))
+    t = torch.tensor([1.0, 0.5, 0.03])
+    for mode in ("corrector", "predictor", "prior"):
+        if mode == "prior" and sde == 0 and n_src != 2:
+            continue
+        xr, mr = x.clone(), torch.empty_like(x)
+        xd, md = x.clone().to(DEV), torch.empty_like(x).to(DEV)
+        if mode == "corrector":
+            E.pc_corrector(p, xr, s, t, noise=z, x_mean=mr)
+            ops.pc_corrector(p, xd, s.to(DEV), t.to(DEV), noise=z.to(DEV), x_mean=md)
+        elif mode == "predictor":
+            E.pc_predictor(p, xr, s, t, y, noise=z, x_mean=mr)
+            ops.pc_predictor(p, xd, s.to(DEV), t.to(DEV), y.to(DEV), noise=z.to(DEV), x_mean=md)
+        else:
+            E.pc_prior(p, xr, y, noise=z)
+            ops.pc_prior(p, xd, y.to(DEV), noise=z.to(DEV))
+        assert rel(xd, xr) < 2e-6, (mode, rel(xd, xr))  # fp32 elementwise, coefficients via powf/expf
+        if mode != "prior":
+            assert rel(md, mr) < 2e-6, mode
+
+
+def test_pc_philox_noise_is_standard_normal_and_keyed():
+    n = 1 << 22
+    a = torch.empty(n, device=DEV)
+    b = torch.empty(n, device=DEV)
+    ops.philox_normal(a, seed=4321, draw=0)
+    ops.philox_normal(b, seed=4321, draw=0)
+    assert torch.equal(a, b)  # deterministic in (seed, draw)
+    ops.philox_normal(b, seed=4321, draw=1)
+    assert abs(float((a * b).mean())) < 5e-3  # draws are independent
+    m, v = float(a.mean()), float(a.var())
+    k = float(((a - m) ** 4).mean() / v ** 2)
+    assert abs(m) < 3e-3 and abs(v - 1) < 5e-3 and abs(k - 3) < 3e-2
+    # the fused update with noise=None consumes the same stream: x = 0 + 1*z for OUVE prior with y = 0
+    p = SdeParams(1, 2, 1.5, 0.05, 0.5, 30, 0.5)
+    x = torch.empty(2, 2, 1024, device=DEV)
+    ops.pc_prior(p, x, torch.zeros(2, 1, 1024, device=DEV), noise=None, seed=7, draw=3)
+    z = torch.empty(2 * 2 * 1024, device=DEV)
+    ops.philox_normal(z, seed=7, draw=3)
+    std1 = math.sqrt(0.05 ** 2 * math.exp(-3.0) * (math.exp(2 * (1.5 + math.log(10)) * 1.0) - 1) * math.log(10) / (1.5 + math.log(10)))
+    assert rel(x.flatten(), z * std1) < 1e-5
+
+
+# ------------------------------------------------------------------ spectral
+@pytest.mark.parametrize("B,n_src,T", [(1, 2, 32000), (2, 2, 7810), (3, 3, 5001), (1, 1, 300)])
+@pytest.mark.parametrize("affine", [False, True])
+def test_stft_compress(B, n_src, T, affine):
+    xt = torch.randn(B, n_src, T, generator=g(5))
+    mix = torch.randn(B, 1, T, generator=g(6))
+    win = torch.hann_window(510)
+    frames = 1 + (T + 382) // 128
+    W = (frames + 63) // 64 * 64
+    C2 = 2 * (n_src + 1)
+    ref = torch.empty(B, 256, W, C2)
+    E.stft_compress(xt, mix, win, ref, 0.5, 0.15, affine)
+    out = torch.empty(B, 256, W, C2, device=DEV)
+    ops.stft_compress(xt.to(DEV), mix.to(DEV), win.to(DEV), out, 0.5, 0.15, affine)
+    # sqrt compression amplifies the relative error of small bins: 1e-4 in rel-L2 over the tile
+    assert rel(out, ref) < 1e-4, rel(out, ref)
+    assert float((out.cpu() - ref).abs().max()) < 5e-3
+    outb = torch.empty(B, 256, W, C2, device=DEV, dtype=torch.bfloat16)
+    ops.stft_compress(xt.to(DEV), mix.to(DEV), win.to(DEV), outb, 0.5, 0.15, affine)
+    assert rel(outb.float(), ref) < 6e-3  # bf16 storage
+    # exponent 1 path = plain STFT
+    E.stft_compress(xt, mix, win, ref, 1.0, 1.0, False)
+    ops.stft_compress(xt.to(DEV), mix.to(DEV), win.to(DEV), out, 1.0, 1.0, False)
+    assert rel(out, ref) < 2e-5
+
+
+@pytest.mark.parametrize("B,n_src,T", [(1, 2, 32000), (2, 2, 7810), (2, 3, 5001)])
+def test_expand_istft(B, n_src, T):
+    frames = 1 + (T + 382) // 128
+    W = (frames + 63) // 64 * 64
+    spec = 0.1 * torch.randn(B, 256, W, 2 * n_src, generator=g(7))
+    win = torch.hann_window(510)
+    ref = torch.empty(B, n_src, T)
+    E.expand_istft(spec, win, ref, 0.5, 0.15)
+    out = torch.empty(B, n_src, T, device=DEV)
+    ops.expand_istft(spec.to(DEV), win.to(DEV), out, 0.5, 0.15)
+    assert rel(out, ref) < 2e-5, rel(out, ref)
+
+
+def test_stft_roundtrip_full_size():
+    """size-independent property at the benchmark shape: iSTFT(expand(compress(STFT(x)))) == x."""
+    B, n, T = 32, 2, 32000
+    xt = torch.randn(B, n + 1, T, generator=g(8)).to(DEV)
+    win = torch.hann_window(510, device=DEV)
+    feat = torch.empty(B, 256, 256, 2 * (n + 1), device=DEV)
+    ops.stft_compress(xt[:, :n].contiguous(), xt[:, n:].contiguous(), win, feat, 0.5, 0.15, False)
+    out = torch.empty(B, n + 1, T, device=DEV)
+    ops.expand_istft(feat, win, out, 0.5, 0.15)
+    assert rel(out, xt) < 1e-5
+
+
+# ------------------------------------------------------------------ GroupNorm / FIR
+@pytest.mark.parametrize("C,ld,H,W,B", [(64, 64, 32, 32, 2), (128, 192, 16, 8, 3), (192, 192, 8, 8, 1), (256, 256, 4, 4, 2),
+                                        (64, 128, 256, 256, 1)])
+@pytest.mark.parametrize("dtype", [torch.float32, torch.bfloat16])
+def test_groupnorm(C, ld, H, W, B, dtype):
+    buf = (torch.randn(B, H, W, ld, generator=g(9)) * 2 + 0.5).to(dtype)
+    x = buf[..., ld - C:]
+    gamma = 1 + 0.1 * torch.randn(C, generator=g(10))
+    beta = 0.1 * torch.randn(C, generator=g(11))
+    G = min(C // 4, 32)
+    ss_ref = torch.empty(B, 2, C)
+    E.gn_stats(x, G, gamma, beta, 1e-6, None, ss_ref)
+    xd = buf.to(DEV)[..., ld - C:]
+    ss = torch.empty(B, 2, C, device=DEV)
+    partial = torch.empty((4 * 148 + B) * C * 4, device=DEV)
+    ops.gn_stats(xd, G, gamma.to(DEV), beta.to(DEV), 1e-6, partial, ss)
+    assert rel(ss, ss_ref) < 1e-5
+    for silu in (False, True):
+        y_ref = torch.empty(B, H, W, C, dtype=dtype)
+        E.gn_apply(x, ss_ref, silu, y_ref)
+        y = torch.empty(B, H, W, C, device=DEV, dtype=dtype)
+        ops.gn_apply(xd, ss, silu, y)
+        assert rel(y.float(), y_ref.float()) < (1e-5 if dtype == torch.float32 else 6e-3)
+    # in place
+    ybuf = buf.to(DEV).clone()
+    yv = ybuf[..., ld - C:]
+    ops.gn_apply(yv, ss, True, yv)
+    assert rel(yv.float(), y_ref.float()) < (1e-5 if dtype == torch.float32 else 6e-3)
+
+
+@pytest.mark.parametrize("up", [False, True])
+@pytest.mark.parametrize("dtype", [torch.float32, torch.bfloat16])
+def test_fir_resample(up, dtype):
+    B, H, W, C = 2, 16, 8, 64
+    x = torch.randn(B, H, W, C, generator=g(12)).to(dtype)
+    ss = torch.stack([1 + 0.1 * torch.randn(B, C, generator=g(13)), 0.1 * torch.randn(B, C, generator=g(14))], dim=1)
+    Ho, Wo = (2 * H, 2 * W) if up else (H // 2, W // 2)
+    rx, rh = torch.empty(B, Ho, Wo, C, dtype=dtype), torch.empty(B, Ho, Wo, C, dtype=dtype)
+    E.fir_resample(x, up, out_x=rx, scale_shift=ss, out_h=rh)
+    ox = torch.empty(B, Ho, Wo, C, device=DEV, dtype=dtype)
+    oh = torch.empty(B, Ho, Wo, C, device=DEV, dtype=dtype)
+    ops.fir_resample(x.to(DEV), up, out_x=ox, scale_shift=ss.to(DEV), out_h=oh)
+    tol = 1e-5 if dtype == torch.float32 else 6e-3
+    assert rel(ox.float(), rx.float()) < tol and rel(oh.float(), rh.float()) < tol
+    ox.zero_()
+    ops.fir_resample(x.to(DEV), up, out_x=ox)
+    assert rel(ox.float(), rx.float()) < tol
+    # narrow (6-channel pyramid) path, fp32
+    xn = torch.randn(B, H, W, 6, generator=g(15))
+    rn = torch.empty(B, Ho, Wo, 6)
+    E.fir_resample(xn, up, out_x=rn)
+    on = torch.empty(B, Ho, Wo, 6, device=DEV)
+    ops.fir_resample(xn.to(DEV), up, out_x=on)
+    assert rel(on, rn) < 1e-5
+
+
+# ------------------------------------------------------------------ convolutions
+def _conv_case(B, H, W, Cin, Cout, k, seed, ld_extra=0):
+    buf = torch.randn(B, H, W, Cin + ld_extra, generator=g(seed))
+    w = torch.randn(Cout, k * k, Cin, generator=g(seed + 1)) / math.sqrt(k * k * Cin)
+    bias = 0.1 * torch.randn(Cout, generator=g(seed + 2))
+    bias_b = 0.1 * torch.randn(B, Cout + 5, generator=g(seed + 3))
+    res = torch.randn(B, H, W, Cout, generator=g(seed + 4))
+    return buf, w, bias, bias_b, res
+
+
+@pytest.mark.parametrize("B,H,W,Cin,Cout,k", [(2, 16, 16, 64, 64, 3), (1, 9, 13, 6, 64, 3), (2, 8, 8, 6, 128, 1),
+                                              (1, 32, 32, 128, 6, 3), (3, 4, 4, 256, 128, 1)])
+def test_conv_direct(B, H, W, Cin, Cout, k):
+    buf, w, bias, bias_b, res = _conv_case(B, H, W, Cin, Cout, k, 20, ld_extra=8)
+    x = buf[..., 8:]
+    ref = torch.empty(B, H, W, Cout)
+    E.conv_direct(x, w, bias, ref, k, bias_b=bias_b[:, 5:], residual=res, out_scale=0.7)
+    out = torch.empty(B, H, W, Cout, device=DEV)
+    ops.conv_direct(buf.to(DEV)[..., 8:], w.to(DEV), bias.to(DEV), out, k, bias_b=bias_b.to(DEV)[:, 5:],
+                    residual=res.to(DEV), out_scale=0.7)
+    assert rel(out, ref) < 1e-5
+    # in-place residual + plain
+    out2 = res.to(DEV).clone()
+    ops.conv_direct(buf.to(DEV)[..., 8:], w.to(DEV), bias.to(DEV), out2, k, residual=out2)
+    E.conv_direct(x, w, bias, ref, k, residual=res)
+    assert rel(out2, ref) < 1e-5
+
+
+TC_CASES = [
+    # B, H, W, Cin, ld_extra, Cout, k
+    (2, 16, 16, 64, 0, 64, 3),
+    (1, 64, 64, 128, 64, 128, 3),     # channel slice of a concat buffer
+    (1, 256, 256, 64, 0, 64, 3),      # the dominant shape of the score net
+    (2, 32, 32, 192, 0, 64, 3),
+    (3, 4, 4, 256, 0, 128, 3),        # deepest level, batch not a multiple of the batch box
+    (1, 8, 24, 128, 0, 128, 3),       # non power-of-two width (variable-length utterances)
+    (2, 16, 16, 128, 0, 384, 1),      # fused q/k/v projection (three N tiles)
+    (1, 32, 32, 64, 0, 6, 3),         # progressive-output conv (N padded to 16)
+    (2, 16, 16, 128, 0, 64, 1),
+]
+
+
+@pytest.mark.parametrize("B,H,W,Cin,ld_extra,Cout,k", TC_CASES)
+def test_conv_tc(B, H, W, Cin, ld_extra, Cout, k):
+    buf, w, bias, bias_b, res = _conv_case(B, H, W, Cin, Cout, k, 30, ld_extra=ld_extra)
+    xb = buf.to(torch.bfloat16)
+    wb = w.to(torch.bfloat16)
+    x = xb[..., ld_extra:]
+    ref = torch.empty(B, H, W, Cout)
+    E.conv_direct(x.float(), wb.float(), bias, ref, k, bias_b=bias_b[:, 5:], residual=res, out_scale=0.7)
+    cp = (Cout + 15) // 16 * 16
+    wpad = torch.zeros(cp, k * k, Cin, dtype=torch.bfloat16)
+    wpad[:Cout] = wb
+    xd = xb.to(DEV)[..., ld_extra:]
+    plan = ops.ConvTcPlan(xd, wpad.to(DEV), Cout, k)
+    out = torch.empty(B, H, W, Cout, device=DEV)
+    plan.run(bias.to(DEV), out, bias_b=bias_b.to(DEV)[:, 5:], residual=res.to(DEV), out_scale=0.7)
+    torch.cuda.synchronize()
+    # same bf16 operands, fp32 accumulation on both sides: only summation order differs
+    assert rel(out, ref) < 2e-5, rel(out, ref)
+    outb = torch.empty(B, H, W, Cout, device=DEV, dtype=torch.bfloat16)
+    resb = res.to(torch.bfloat16)
+    plan.run(bias.to(DEV), outb, residual=resb.to(DEV))
+    E.conv_direct(x.float(), wb.float(), bias, ref, k, residual=resb.float())
+    assert rel(outb.float(), ref) < 4e-3  # bf16 output rounding
+    # in-place residual (Combine / res-block shortcut pattern)
+    out2 = resb.to(DEV).clone()
+    plan.run(bias.to(DEV), out2, residual=out2)
+    assert rel(out2.float(), ref) < 4e-3
+
+
+# ------------------------------------------------------------------ attention / temb / output layer
+@pytest.mark.parametrize("B,H,W,C", [(2, 16, 16, 128), (1, 4, 4, 128), (1, 16, 80, 128), (2, 4, 5, 64)])
+@pytest.mark.parametrize("dtype", [torch.float32, torch.bfloat16])
+def test_attention(B, H, W, C, dtype):
+    qkv = torch.randn(B, H, W, 3 * C, generator=g(40)).to(dtype)
+    ref = torch.empty(B, H, W, C, dtype=dtype)
+    E.attention(qkv[..., :C], qkv[..., C:2 * C], qkv[..., 2 * C:], ref)
+    d = qkv.to(DEV)
+    out = torch.empty(B, H, W, C, device=DEV, dtype=dtype)
+    ops.attention(d[..., :C], d[..., C:2 * C], d[..., 2 * C:], out)
+    assert rel(out.float(), ref.float()) < (2e-5 if dtype == torch.float32 else 6e-3)
+
+
+def test_temb_and_output_layer():
+    B, nf = 3, 64
+    t = torch.tensor([1.0, 0.4, 0.03])
+    gfp = 16 * torch.randn(nf, generator=g(50))
+    w1, b1 = torch.randn(4 * nf, 2 * nf, generator=g(51)) / 12, 0.1 * torch.randn(4 * nf, generator=g(52))
+    w2, b2 = torch.randn(4 * nf, 4 * nf, generator=g(53)) / 16, 0.1 * torch.randn(4 * nf, generator=g(54))
+    ref = torch.empty(B, 4 * nf)
+    E.temb_mlp(t, gfp, w1, b1, w2, b2, ref)
+    out = torch.empty(B, 4 * nf, device=DEV)
+    ops.temb_mlp(*(a.to(DEV) for a in (t, gfp, w1, b1, w2, b2)), out)
+    # sin/cos of arguments up to ~16*2pi*|log t|*3 ~ 1e3 rad in fp32: 1e-4
+    assert rel(out, ref) < 2e-4, rel(out, ref)
+    dw, db = torch.randn(777, 4 * nf, generator=g(55)) / 16, torch.randn(777, generator=g(56))
+    dref = torch.empty(B, 777)
+    E.temb_dense(ref, dw, db, dref)
+    dout = torch.empty(B, 777, device=DEV)
+    ops.temb_dense(ref.to(DEV), dw.to(DEV), db.to(DEV), dout)
+    assert rel(dout, dref) < 1e-5
+    x = torch.randn(B, 8, 8, 6, generator=g(57))
+    w, b = torch.randn(4, 6, generator=g(58)), torch.randn(4, generator=g(59))
+    oref = torch.empty(B, 8, 8, 4)
+    E.output_layer(x, t, w, b, oref, True)
+    o = torch.empty(B, 8, 8, 4, device=DEV)
+    ops.output_layer(x.to(DEV), t.to(DEV), w.to(DEV), b.to(DEV), o, True)
+    assert rel(o, oref) < 1e-5
+
+
+def test_cpu_tensors_are_rejected():
+    with pytest.raises(ops.DitsepError):
+        ops.gn_apply(torch.zeros(1, 2, 2, 8), torch.zeros(1, 2, 8), True, torch.zeros(1, 2, 2, 8))
