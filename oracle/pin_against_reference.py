@@ -101,7 +101,11 @@ class TapedRandn:
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--full", action="store_true", help="also run the full N=30 C1 sampler (~3 min)")
+    ap.add_argument("--init-scale", type=float, default=1.0,
+                    help="scale of the reference's init_scale=0 tensors (Conv_1, NIN_3, pyramid convs); 1.0 = worst case "
+                         "for rounding-error growth, 0.01 = 'trained-like' set used by the bf16 parity tests")
     args = ap.parse_args()
+    tag = "" if args.init_scale == 1.0 else f"_s{args.init_scale:g}".replace(".", "p")
 
     sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
     from oracle import ncsnpp_ref as R
@@ -136,7 +140,7 @@ def main():
 
     # ---- b. one score evaluation ---------------------------------------------------
     cfg = R.ScoreConfig()
-    sd = R.make_state_dict(cfg.backbone, seed=0)
+    sd = R.make_state_dict(cfg.backbone, seed=0, init_scale=args.init_scale)
     ref = build_ref(64)
     ref.load_state_dict(sd, strict=True)
     golden = {}
@@ -198,7 +202,7 @@ def main():
     golden["sampler_small_sisdr"] = sis.numpy()
     if args.full:
         x_ref, scores, sis = run_pair(32000, 1, 30, "C1")
-        np.savez_compressed(os.path.join(GOLDEN, "sampler_c1.npz"), out=x_ref.numpy().astype(np.float32),
+        np.savez_compressed(os.path.join(GOLDEN, f"sampler_c1{tag}.npz"), out=x_ref.numpy().astype(np.float32),
                             score_norms=np.array(scores), sisdr=sis.numpy())
 
     # ---- d. OUVESDE + ald with a synthetic score function ---------------------------
@@ -246,7 +250,7 @@ def main():
     assert rel_l2(o_orc, o_ref) < 2e-5
     golden["latent_out"] = o_ref.numpy()
 
-    np.savez_compressed(os.path.join(GOLDEN, "reference_outputs.npz"), **golden)
+    np.savez_compressed(os.path.join(GOLDEN, f"reference_outputs{tag}.npz"), **golden)
     print("fixtures written to", GOLDEN)
 
 
