@@ -39,17 +39,19 @@ SIGNATURES = {
                                     c_void_p]),
     "ditsep_gn_stats": (c_int, [c_void_p, c_int, c_int, c_int64, c_int, c_int, c_int, c_void_p, c_void_p, c_float,
                                 c_void_p, c_int, c_void_p, c_void_p]),
+    "ditsep_gn_finalize": (c_int, [c_void_p, c_int, c_int, c_int64, c_int, c_int, c_void_p, c_void_p, c_float, c_void_p,
+                                   c_void_p]),
     "ditsep_gn_apply": (c_int, [c_void_p, c_int, c_int, c_int64, c_int, c_int, c_void_p, c_int, c_void_p, c_int,
                                 c_void_p]),
     "ditsep_fir_resample": (c_int, [c_void_p, c_int, c_int, c_int, c_int, c_int, c_int, c_int, c_void_p, c_void_p,
                                     c_int, c_void_p, c_int, c_void_p]),
     "ditsep_conv_direct": (c_int, [c_void_p, c_int, c_int, c_int, c_int, c_int, c_int, c_void_p, c_void_p, c_void_p,
-                                   c_int, c_void_p, c_int, c_float, c_int, c_int, c_void_p, c_int, c_int, c_void_p]),
+                                   c_int, c_void_p, c_int, c_float, c_int, c_int, c_void_p, c_int, c_int, c_void_p, c_int, c_void_p]),
     "ditsep_conv_tc_plan_create": (c_int, [C.POINTER(c_void_p), c_void_p, c_int, c_int, c_int, c_int, c_int, c_void_p,
                                            c_int, c_int]),
     "ditsep_conv_tc_plan_destroy": (None, [c_void_p]),
     "ditsep_conv_tc_run": (c_int, [c_void_p, c_void_p, c_void_p, c_int, c_void_p, c_int, c_int, c_float, c_void_p,
-                                   c_int, c_int, c_void_p]),
+                                   c_int, c_int, c_void_p, c_int, c_void_p]),
     "ditsep_attention": (c_int, [c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_int, c_int, c_void_p, c_int,
                                  c_void_p]),
     "ditsep_temb_mlp": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_int,

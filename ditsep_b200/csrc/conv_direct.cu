@@ -22,9 +22,11 @@ __global__ void __launch_bounds__(256) conv_direct_kernel(const TI* __restrict__
                                                           const float* __restrict__ bias,
                                                           const float* __restrict__ bias_b, int ld_bias_b,
                                                           const TR* __restrict__ residual, int ld_res, float out_scale,
-                                                          int Cout, int ksize, TO* __restrict__ out, int ld_out) {
+                                                          int Cout, int ksize, TO* __restrict__ out, int ld_out,
+                                                          float* __restrict__ stats, int ld_stats) {
   __shared__ float As[BK][BM + 4];
   __shared__ float Bs[BK][BN + 4];
+  __shared__ float red[2][BN];
   const int taps = ksize * ksize, K = taps * Cin, pad = ksize / 2;
   const int64_t M = (int64_t)B * H * W;
   const int64_t m0 = (int64_t)blockIdx.x * BM;
@@ -92,11 +94,21 @@ __global__ void __launch_bounds__(256) conv_direct_kernel(const TI* __restrict__
     }
     __syncthreads();
   }
+  // GroupNorm statistics of the stored output (per image, per channel): block-level reduction in
+  // shared memory when the 64-pixel tile lies inside one image, else per-thread reds.
+  const int64_t HWl = (int64_t)H * W;
+  const int64_t m_last = (m0 + BM - 1 < M ? m0 + BM - 1 : M - 1);
+  const bool one_image = stats != nullptr && (m0 / HWl) == (m_last / HWl);
+  if (stats) {
+    for (int i = tid; i < 2 * BN; i += 256) (&red[0][0])[i] = 0.f;
+    __syncthreads();
+  }
+  float cs[4] = {0.f, 0.f, 0.f, 0.f}, cq[4] = {0.f, 0.f, 0.f, 0.f};
 #pragma unroll
   for (int i = 0; i < 4; ++i) {
     const int64_t m = m0 + ty * 4 + i;
     if (m >= M) continue;
-    const int b = (int)(m / ((int64_t)H * W));
+    const int b = (int)(m / HWl);
 #pragma unroll
     for (int j = 0; j < 4; ++j) {
       const int co = n0 + tx * 4 + j;
@@ -105,7 +117,31 @@ __global__ void __launch_bounds__(256) conv_direct_kernel(const TI* __restrict__
       if (bias) v += bias[co];
       if (bias_b) v += bias_b[(int64_t)b * ld_bias_b + co];
       if (residual) v += to_f<TR>(residual[m * ld_res + co]);
-      out[m * ld_out + co] = from_f<TO>(v * out_scale);
+      const TO o = from_f<TO>(v * out_scale);
+      out[m * ld_out + co] = o;
+      if (stats) {
+        const float r = to_f<TO>(o);
+        if (one_image) {
+          cs[j] += r;
+          cq[j] += r * r;
+        } else {
+          atomicAdd(stats + ((int64_t)b * ld_stats + co) * 2, r);
+          atomicAdd(stats + ((int64_t)b * ld_stats + co) * 2 + 1, r * r);
+        }
+      }
+    }
+  }
+  if (one_image) {
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      atomicAdd(&red[0][tx * 4 + j], cs[j]);
+      atomicAdd(&red[1][tx * 4 + j], cq[j]);
+    }
+    __syncthreads();
+    const int b = (int)(m0 / HWl);
+    for (int i = tid; i < 2 * BN; i += 256) {
+      const int which = i / BN, c = i % BN;
+      if (n0 + c < Cout) atomicAdd(stats + ((int64_t)b * ld_stats + n0 + c) * 2 + which, red[which][c]);
     }
   }
 }
@@ -117,11 +153,12 @@ using namespace ditsep;
 extern "C" int ditsep_conv_direct(const void* in, int dtype, int B, int H, int W, int Cin, int ld_in, const float* w,
                                   const float* bias, const float* bias_b, int ld_bias_b, const void* residual,
                                   int ld_res, float out_scale, int Cout, int ksize, void* out, int out_dtype,
-                                  int ld_out, void* stream) {
+                                  int ld_out, float* stats, int ld_stats, void* stream) {
   DITSEP_REQUIRE(in && w && out, "conv_direct: null pointer");
   DITSEP_REQUIRE(ksize == 1 || ksize == 3, "conv_direct: ksize=%d (1 or 3)", ksize);
   DITSEP_REQUIRE(B > 0 && H > 0 && W > 0 && Cin > 0 && Cout > 0, "conv_direct: empty problem");
   DITSEP_REQUIRE(ld_in >= Cin && ld_out >= Cout, "conv_direct: strides smaller than channel counts");
+  DITSEP_REQUIRE(!stats || ld_stats >= Cout, "conv_direct: ld_stats=%d < Cout=%d", ld_stats, Cout);
   const int64_t M = (int64_t)B * H * W;
   dim3 grid(ceil_div(M, BM), ceil_div(Cout, BN));
   cudaStream_t st = (cudaStream_t)stream;
@@ -129,7 +166,7 @@ extern "C" int ditsep_conv_direct(const void* in, int dtype, int B, int H, int W
 #define LAUNCH(TI, TO)                                                                                              \
   conv_direct_kernel<TI, TO, TO><<<grid, 256, 0, st>>>((const TI*)in, B, H, W, Cin, ld_in, w, bias, bias_b, ld_bias_b, \
                                                        (const TO*)residual, ld_res, out_scale, Cout, ksize, (TO*)out,  \
-                                                       ld_out)
+                                                       ld_out, stats, ld_stats)
   if (dtype == DITSEP_F32 && out_dtype == DITSEP_F32) LAUNCH(float, float);
   else if (dtype == DITSEP_BF16 && out_dtype == DITSEP_BF16) LAUNCH(bf16, bf16);
   else if (dtype == DITSEP_BF16 && out_dtype == DITSEP_F32) LAUNCH(bf16, float);

@@ -24,6 +24,9 @@
 //    CTA's epilogue overlaps another's main loop.
 #include <cuda.h>
 
+#include <cstdlib>
+#include <cstring>
+
 #include "common.cuh"
 
 namespace ditsep {
@@ -47,6 +50,10 @@ struct ConvTcParams {
   float out_scale;
   void* out;
   int out_dtype, ld_out;
+  float* stats;            // nullable: per-(b, channel) {sum, sum of squares} of the OUTPUT, [B][ld_stats][2]
+  int ld_stats;
+  // halo mode (3x3): 8 x 16 pixel tiles, persistent CTAs, optional resident filter
+  int num_tiles, chunks, w_resident, a_stages, w_stages, base_off_mode;
 };
 
 // ---- PTX wrappers ------------------------------------------------------------------------
@@ -127,7 +134,131 @@ __device__ __forceinline__ uint64_t make_sw128_desc(uint32_t smem_addr) {
   return (uint64_t)((smem_addr >> 4) & 0x3FFF) | (1ull << 16) | (64ull << 32) | (1ull << 46) | (2ull << 61);
 }
 
-// ---- the kernel -----------------------------------------------------------------------------
+// ---- shared epilogue -----------------------------------------------------------------------
+// One thread = one output pixel (TMEM lane), 16 consecutive output channels per call.
+// v: raw fp32 accumulators.  Applies bias / per-image bias / residual / scale, stores, and (if
+// p.stats) accumulates the GroupNorm statistics of the stored tensor: a 4-step halving exchange
+// leaves each lane pair with one channel's sum over the warp's 32 pixels, then one red.add per
+// channel per warp.  `uniform_b`: all lanes of the warp belong to the same image.
+__device__ __forceinline__ void epilogue16(const ConvTcParams& p, const uint32_t (&v)[16], bool valid, int pb,
+                                           int64_t pix, int co0, bool uniform_b, int lane) {
+  const int nvalid = min(16, p.Cout - co0);  // > 0 guaranteed by the caller
+  float f[16];
+#pragma unroll
+  for (int j = 0; j < 16; ++j) {
+    float a = __uint_as_float(v[j]);
+    if (j < nvalid) {
+      if (p.bias) a += __ldg(p.bias + co0 + j);
+      if (p.bias_b && valid) a += __ldg(p.bias_b + (int64_t)pb * p.ld_bias_b + co0 + j);
+    }
+    f[j] = a;
+  }
+  if (valid) {
+    if (p.residual) {
+      if (p.res_dtype == DITSEP_BF16) {
+        const bf16* rp = reinterpret_cast<const bf16*>(p.residual) + pix * p.ld_res + co0;
+        if (nvalid == 16 && ((reinterpret_cast<uintptr_t>(rp) & 15) == 0)) {
+          float t[8];
+          Pack8<bf16>::load(rp, t);
+#pragma unroll
+          for (int j = 0; j < 8; ++j) f[j] += t[j];
+          Pack8<bf16>::load(rp + 8, t);
+#pragma unroll
+          for (int j = 0; j < 8; ++j) f[8 + j] += t[j];
+        } else {
+#pragma unroll
+          for (int j = 0; j < 16; ++j)
+            if (j < nvalid) f[j] += __bfloat162float(rp[j]);
+        }
+      } else {
+        const float* rp = reinterpret_cast<const float*>(p.residual) + pix * p.ld_res + co0;
+#pragma unroll
+        for (int j = 0; j < 16; ++j)
+          if (j < nvalid) f[j] += rp[j];
+      }
+    }
+#pragma unroll
+    for (int j = 0; j < 16; ++j) f[j] *= p.out_scale;
+    if (p.out_dtype == DITSEP_BF16) {
+      bf16* op = reinterpret_cast<bf16*>(p.out) + pix * p.ld_out + co0;
+      if (nvalid == 16 && ((reinterpret_cast<uintptr_t>(op) & 15) == 0)) {
+        float t[8];
+#pragma unroll
+        for (int j = 0; j < 8; ++j) t[j] = f[j];
+        Pack8<bf16>::store(op, t);
+#pragma unroll
+        for (int j = 0; j < 8; ++j) t[j] = f[8 + j];
+        Pack8<bf16>::store(op + 8, t);
+      } else {
+#pragma unroll
+        for (int j = 0; j < 16; ++j)
+          if (j < nvalid) op[j] = __float2bfloat16_rn(f[j]);
+      }
+      if (p.stats) {  // statistics of what the consumer will read: the bf16-rounded values
+#pragma unroll
+        for (int j = 0; j < 16; ++j) f[j] = __bfloat162float(__float2bfloat16_rn(f[j]));
+      }
+    } else {
+      float* op = reinterpret_cast<float*>(p.out) + pix * p.ld_out + co0;
+      if (nvalid == 16 && ((reinterpret_cast<uintptr_t>(op) & 15) == 0)) {
+#pragma unroll
+        for (int j = 0; j < 16; j += 4) *reinterpret_cast<float4*>(op + j) = make_float4(f[j], f[j + 1], f[j + 2], f[j + 3]);
+      } else {
+#pragma unroll
+        for (int j = 0; j < 16; ++j)
+          if (j < nvalid) op[j] = f[j];
+      }
+    }
+  }
+  if (p.stats == nullptr) return;
+  if (!uniform_b) {  // deep levels: a warp spans several images -> plain per-thread reds (few pixels)
+    if (valid) {
+      float* sp = p.stats + ((int64_t)pb * p.ld_stats + co0) * 2;
+#pragma unroll
+      for (int j = 0; j < 16; ++j)
+        if (j < nvalid) {
+          atomicAdd(sp + 2 * j, f[j]);
+          atomicAdd(sp + 2 * j + 1, f[j] * f[j]);
+        }
+    }
+    return;
+  }
+  float s[16], q[16];
+#pragma unroll
+  for (int j = 0; j < 16; ++j) {
+    s[j] = valid ? f[j] : 0.f;
+    q[j] = s[j] * s[j];
+  }
+  // halving exchange: after the steps with offsets 16, 8, 4, 2 lane l holds channel
+  // c = 8*b4 + 4*b3 + 2*b2 + b1 (bits of l) summed over the 16 lanes that share those bits' complement
+#pragma unroll
+  for (int step = 0; step < 4; ++step) {
+    const int off = 16 >> step;       // lane offset
+    const int half = 8 >> step;       // values kept
+    const bool upper = (lane & off) != 0;
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+      if (j < half) {
+        const float send_s = upper ? s[j] : s[j + half];
+        const float send_q = upper ? q[j] : q[j + half];
+        const float keep_s = upper ? s[j + half] : s[j];
+        const float keep_q = upper ? q[j + half] : q[j];
+        s[j] = keep_s + __shfl_xor_sync(0xffffffffu, send_s, off);
+        q[j] = keep_q + __shfl_xor_sync(0xffffffffu, send_q, off);
+      }
+    }
+  }
+  s[0] += __shfl_xor_sync(0xffffffffu, s[0], 1);
+  q[0] += __shfl_xor_sync(0xffffffffu, q[0], 1);
+  const int c = ((lane >> 4) & 1) * 8 + ((lane >> 3) & 1) * 4 + ((lane >> 2) & 1) * 2 + ((lane >> 1) & 1);
+  if ((lane & 1) == 0 && c < nvalid) {
+    float* sp = p.stats + ((int64_t)pb * p.ld_stats + co0 + c) * 2;
+    atomicAdd(sp, s[0]);
+    atomicAdd(sp + 1, q[0]);
+  }
+}
+
+// ---- kernel 1: one TMA box per (tap, 64-channel block) --------------------------------------
 __global__ void __launch_bounds__(kThreads) conv_tc_kernel(const __grid_constant__ CUtensorMap mapA,
                                                            const __grid_constant__ CUtensorMap mapW,
                                                            const ConvTcParams p) {
@@ -220,75 +351,188 @@ __global__ void __launch_bounds__(kThreads) conv_tc_kernel(const __grid_constant
     for (int c0 = 0; c0 < p.BN; c0 += 16) {
       uint32_t v[16];
       tmem_ld16(lane_base + (uint32_t)c0, v);
-      const int co0 = n0 + c0;
-      if (!valid || co0 >= p.Cout) continue;
-      const int nvalid = min(16, p.Cout - co0);
-      float f[16];
-#pragma unroll
-      for (int j = 0; j < 16; ++j) {
-        float a = __uint_as_float(v[j]);
-        if (j < nvalid) {
-          if (p.bias) a += __ldg(p.bias + co0 + j);
-          if (p.bias_b) a += __ldg(p.bias_b + (int64_t)pb * p.ld_bias_b + co0 + j);
-        }
-        f[j] = a;
-      }
-      if (p.residual) {
-        if (p.res_dtype == DITSEP_BF16) {
-          const bf16* rp = reinterpret_cast<const bf16*>(p.residual) + pix * p.ld_res + co0;
-          if (nvalid == 16 && ((reinterpret_cast<uintptr_t>(rp) & 15) == 0)) {
-            float t[8];
-            Pack8<bf16>::load(rp, t);
-#pragma unroll
-            for (int j = 0; j < 8; ++j) f[j] += t[j];
-            Pack8<bf16>::load(rp + 8, t);
-#pragma unroll
-            for (int j = 0; j < 8; ++j) f[8 + j] += t[j];
-          } else {
-#pragma unroll
-            for (int j = 0; j < 16; ++j)
-              if (j < nvalid) f[j] += __bfloat162float(rp[j]);
-          }
-        } else {
-          const float* rp = reinterpret_cast<const float*>(p.residual) + pix * p.ld_res + co0;
-#pragma unroll
-          for (int j = 0; j < 16; ++j)
-            if (j < nvalid) f[j] += rp[j];
-        }
-      }
-#pragma unroll
-      for (int j = 0; j < 16; ++j) f[j] *= p.out_scale;
-      if (p.out_dtype == DITSEP_BF16) {
-        bf16* op = reinterpret_cast<bf16*>(p.out) + pix * p.ld_out + co0;
-        if (nvalid == 16 && ((reinterpret_cast<uintptr_t>(op) & 15) == 0)) {
-          float t[8];
-#pragma unroll
-          for (int j = 0; j < 8; ++j) t[j] = f[j];
-          Pack8<bf16>::store(op, t);
-#pragma unroll
-          for (int j = 0; j < 8; ++j) t[j] = f[8 + j];
-          Pack8<bf16>::store(op + 8, t);
-        } else {
-#pragma unroll
-          for (int j = 0; j < 16; ++j)
-            if (j < nvalid) op[j] = __float2bfloat16_rn(f[j]);
-        }
-      } else {
-        float* op = reinterpret_cast<float*>(p.out) + pix * p.ld_out + co0;
-        if (nvalid == 16 && ((reinterpret_cast<uintptr_t>(op) & 15) == 0)) {
-#pragma unroll
-          for (int j = 0; j < 16; j += 4) *reinterpret_cast<float4*>(op + j) = make_float4(f[j], f[j + 1], f[j + 2], f[j + 3]);
-        } else {
-#pragma unroll
-          for (int j = 0; j < 16; ++j)
-            if (j < nvalid) op[j] = f[j];
-        }
-      }
+      if (n0 + c0 >= p.Cout) continue;
+      epilogue16(p, v, valid, pb, pix, n0 + c0, p.bb == 1, lane);
     }
   }
   tc_fence_before();
   __syncthreads();
   if (warp == 1) {
+    tc_fence_after();
+    tmem_dealloc(tmem_acc, (uint32_t)p.tmem_cols);
+  }
+}
+
+// ---- kernel 2: 3x3, halo tiles, persistent CTAs ----------------------------------------------
+// M tile = 8 (x) by 16 (y) output pixels of one image.  Per 64-channel block ONE TMA box
+// (64 ch, 10, 18) brings the tile plus its one-pixel halo: 180 rows of 128 bytes, swizzled.
+// The A operand of tap (dy,dx) is the SAME shared-memory tile read through a descriptor whose
+// start is shifted by ((1+dy)*10 + (1+dx)) rows and whose 8-row groups are 10 rows (1280 B)
+// apart -- every input element is fetched from L2 once per tile instead of nine times.
+// CTAs are persistent over M tiles (static stride); the filter slice of the CTA's N tile stays
+// resident in shared memory when it fits, else it streams through a small ring.  Two TMEM
+// accumulators alternate so the epilogue of tile i overlaps the MMAs of tile i+1.
+constexpr int kHaloW = 10, kHaloH = 18;
+constexpr int kHaloBytes = 23 * 1024;  // 180 rows x 128 B = 23040, padded to a 1024 multiple
+constexpr int kHaloThreads = 256;
+constexpr int kMaxAStages = 4, kMaxWStages = 4;
+
+__global__ void __launch_bounds__(kHaloThreads, 1) conv_tc_halo_kernel(const __grid_constant__ CUtensorMap mapA,
+                                                                       const __grid_constant__ CUtensorMap mapW,
+                                                                       const ConvTcParams p) {
+  extern __shared__ uint8_t smem_raw[];
+  __shared__ __align__(8) uint64_t bar_a_full[kMaxAStages], bar_a_empty[kMaxAStages];
+  __shared__ __align__(8) uint64_t bar_w_full[kMaxWStages], bar_w_empty[kMaxWStages];
+  __shared__ __align__(8) uint64_t bar_w_res, bar_acc_full[2], bar_acc_empty[2];
+  __shared__ uint32_t tmem_base_slot;
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const uint32_t base = (smem_u32(smem_raw) + 1023u) & ~1023u;
+  const uint32_t w_tile_bytes = (uint32_t)p.BN * 128u;
+  const int n_wtiles = p.w_resident ? p.chunks * 9 : p.w_stages;
+  const uint32_t a_ring = base + (uint32_t)n_wtiles * w_tile_bytes;  // stays 1024-aligned (BN % 16 == 0)
+  const int n0 = blockIdx.y * p.BN;
+  const int my_tiles = (p.num_tiles - (int)blockIdx.x + (int)gridDim.x - 1) / (int)gridDim.x;
+
+  if (threadIdx.x == 0) {
+    for (int s = 0; s < kMaxAStages; ++s) {
+      mbar_init(smem_u32(&bar_a_full[s]), 1);
+      mbar_init(smem_u32(&bar_a_empty[s]), 1);
+    }
+    for (int s = 0; s < kMaxWStages; ++s) {
+      mbar_init(smem_u32(&bar_w_full[s]), 1);
+      mbar_init(smem_u32(&bar_w_empty[s]), 1);
+    }
+    mbar_init(smem_u32(&bar_w_res), 1);
+    for (int s = 0; s < 2; ++s) {
+      mbar_init(smem_u32(&bar_acc_full[s]), 1);
+      mbar_init(smem_u32(&bar_acc_empty[s]), 4);  // one arrival per epilogue warp
+    }
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  if (warp == 2) tmem_alloc(smem_u32(&tmem_base_slot), (uint32_t)p.tmem_cols);
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_acc = tmem_base_slot;
+
+  if (warp == 0) {
+    if (lane == 0) {
+      asm volatile("prefetch.tensormap [%0];" ::"l"(&mapA) : "memory");
+      asm volatile("prefetch.tensormap [%0];" ::"l"(&mapW) : "memory");
+      if (p.w_resident) {
+        const uint32_t bar = smem_u32(&bar_w_res);
+        mbar_expect_tx(bar, (uint32_t)(p.chunks * 9) * w_tile_bytes);
+        for (int ch = 0; ch < p.chunks; ++ch)
+          for (int tap = 0; tap < 9; ++tap)
+            tma_load_2d(base + (uint32_t)(ch * 9 + tap) * w_tile_bytes, &mapW, bar, tap * p.Cin + ch * kBlockK, n0);
+      }
+      uint32_t ia = 0, iw = 0;  // running A-block / W-tile counters (ring position + phase)
+      for (int it = 0; it < my_tiles; ++it) {
+        int mt = (int)blockIdx.x + it * (int)gridDim.x;
+        const int tx = mt % p.tiles_x;
+        mt /= p.tiles_x;
+        const int ty = mt % p.tiles_y;
+        const int b = mt / p.tiles_y;
+        for (int ch = 0; ch < p.chunks; ++ch, ++ia) {
+          const int sa = (int)(ia % (uint32_t)p.a_stages);
+          mbar_wait(smem_u32(&bar_a_empty[sa]), ((ia / (uint32_t)p.a_stages) & 1u) ^ 1u);
+          const uint32_t full = smem_u32(&bar_a_full[sa]);
+          mbar_expect_tx(full, (uint32_t)(kHaloW * kHaloH * 128));
+          tma_load_4d(a_ring + (uint32_t)sa * kHaloBytes, &mapA, full, ch * kBlockK, tx * 8 - 1, ty * 16 - 1, b);
+          if (!p.w_resident) {
+            for (int tap = 0; tap < 9; ++tap, ++iw) {
+              const int sw = (int)(iw % (uint32_t)p.w_stages);
+              mbar_wait(smem_u32(&bar_w_empty[sw]), ((iw / (uint32_t)p.w_stages) & 1u) ^ 1u);
+              const uint32_t wfull = smem_u32(&bar_w_full[sw]);
+              mbar_expect_tx(wfull, w_tile_bytes);
+              tma_load_2d(base + (uint32_t)sw * w_tile_bytes, &mapW, wfull, tap * p.Cin + ch * kBlockK, n0);
+            }
+          }
+        }
+      }
+    }
+  } else if (warp == 1) {
+    if (lane == 0) {
+      const uint32_t idesc = (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(p.BN >> 3) << 17) |
+                             ((uint32_t)(kTileM >> 4) << 24);
+      // A: rows 128 B apart inside a group of 8 output pixels (one tile row), groups 10 rows apart
+      const uint64_t a_hi = (1ull << 16) | ((uint64_t)(kHaloW * 128 >> 4) << 32) | (1ull << 46) | (2ull << 61);
+      if (p.w_resident) {
+        mbar_wait(smem_u32(&bar_w_res), 0);
+        tc_fence_after();
+      }
+      uint32_t ia = 0, iw = 0;
+      for (int it = 0; it < my_tiles; ++it) {
+        const int ab = it & 1;
+        mbar_wait(smem_u32(&bar_acc_empty[ab]), (((uint32_t)it >> 1) & 1u) ^ 1u);
+        tc_fence_after();
+        const uint32_t tmem_d = tmem_acc + (uint32_t)(ab * p.BN);
+        for (int ch = 0; ch < p.chunks; ++ch, ++ia) {
+          const int sa = (int)(ia % (uint32_t)p.a_stages);
+          mbar_wait(smem_u32(&bar_a_full[sa]), (ia / (uint32_t)p.a_stages) & 1u);
+          tc_fence_after();
+          const uint32_t a_buf = a_ring + (uint32_t)sa * kHaloBytes;
+          for (int tap = 0; tap < 9; ++tap) {
+            uint32_t w_addr;
+            int sw = 0;
+            if (p.w_resident) {
+              w_addr = base + (uint32_t)(ch * 9 + tap) * w_tile_bytes;
+            } else {
+              sw = (int)(iw % (uint32_t)p.w_stages);
+              mbar_wait(smem_u32(&bar_w_full[sw]), (iw / (uint32_t)p.w_stages) & 1u);
+              tc_fence_after();
+              w_addr = base + (uint32_t)sw * w_tile_bytes;
+              ++iw;
+            }
+            const int dy = tap / 3, dx = tap % 3;  // already offset by the halo origin (-1, -1)
+            const uint32_t a_start = a_buf + (uint32_t)((dy * kHaloW + dx) * 128);
+            uint64_t da = a_hi | (uint64_t)((a_start >> 4) & 0x3FFF);
+            if (p.base_off_mode == 1) da |= (uint64_t)((a_start >> 7) & 7u) << 49;
+            const uint64_t db = make_sw128_desc(w_addr);
+#pragma unroll
+            for (int k = 0; k < kBlockK / 16; ++k)
+              umma_bf16(tmem_d, da + (uint64_t)(2 * k), db + (uint64_t)(2 * k), idesc, (ch | tap | k) != 0);
+            if (!p.w_resident) umma_commit(smem_u32(&bar_w_empty[sw]));
+          }
+          umma_commit(smem_u32(&bar_a_empty[sa]));
+        }
+        umma_commit(smem_u32(&bar_acc_full[ab]));
+      }
+    }
+  } else if (warp >= 4) {
+    const int q = warp & 3;
+    const int r = q * 32 + lane;
+    const int xo = r & 7, yo = r >> 3;
+    for (int it = 0; it < my_tiles; ++it) {
+      int mt = (int)blockIdx.x + it * (int)gridDim.x;
+      const int tx = mt % p.tiles_x;
+      mt /= p.tiles_x;
+      const int ty = mt % p.tiles_y;
+      const int pb = mt / p.tiles_y;
+      const int px = tx * 8 + xo, py = ty * 16 + yo;
+      const bool valid = px < p.W && py < p.H;
+      const int64_t pix = ((int64_t)pb * p.H + py) * p.W + px;
+      const int ab = it & 1;
+      mbar_wait(smem_u32(&bar_acc_full[ab]), ((uint32_t)it >> 1) & 1u);
+      tc_fence_after();
+      const uint32_t lane_base = tmem_acc + ((uint32_t)(q * 32) << 16) + (uint32_t)(ab * p.BN);
+      for (int c0 = 0; c0 < p.BN; c0 += 16) {
+        uint32_t v[16];
+        tmem_ld16(lane_base + (uint32_t)c0, v);
+        if (c0 + 16 >= p.BN) {  // last TMEM read of this tile: hand the accumulator back
+          tc_fence_before();
+          __syncwarp();
+          if (lane == 0) asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(&bar_acc_empty[ab])) : "memory");
+        }
+        if (n0 + c0 >= p.Cout) continue;
+        epilogue16(p, v, valid, pb, pix, n0 + c0, true, lane);
+      }
+    }
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 2) {
     tc_fence_after();
     tmem_dealloc(tmem_acc, (uint32_t)p.tmem_cols);
   }
@@ -326,6 +570,8 @@ struct ditsep_conv_plan {
   CUtensorMap mapA, mapW;
   ConvTcParams p;
   size_t smem;
+  int halo;      // 1 = conv_tc_halo_kernel
+  int grid_x;
 };
 
 extern "C" int ditsep_conv_tc_plan_create(ditsep_conv_plan** plan, const void* in, int B, int H, int W, int Cin,
@@ -374,13 +620,55 @@ extern "C" int ditsep_conv_tc_plan_create(ditsep_conv_plan** plan, const void* i
   const int num_kb = p.taps * (Cin / kBlockK);
   if (p.stages > num_kb) p.stages = num_kb;
 
+  // ---- halo mode: 3x3 on images of at least one 8 x 16 tile (DITSEP_CONV_MODE=tap disables it)
+  const char* mode_env = getenv("DITSEP_CONV_MODE");
+  int halo = (ksize == 3 && W >= 8 && H >= 16 && !(mode_env && strcmp(mode_env, "tap") == 0)) ? 1 : 0;
+  size_t smem = 1024 + (size_t)p.stages * stage_bytes;
+  int grid_x = 0;
+  if (halo) {
+    const char* bo = getenv("DITSEP_TC_BASEOFF");
+    p.base_off_mode = bo ? atoi(bo) : 0;
+    p.chunks = Cin / kBlockK;
+    p.tiles_x = ceil_div(W, 8);
+    p.tiles_y = ceil_div(H, 16);
+    p.tiles_b = B;
+    p.num_tiles = p.tiles_x * p.tiles_y * B;
+    p.bw = 8; p.bh = 16; p.bb = 1;
+    if (p.BN > 64 && cout_pad % 64 == 0) p.BN = 64;  // more M tiles per resident filter byte
+    p.n_tiles = ceil_div(cout_pad, p.BN);
+    p.tmem_cols = pow2_ceil(2 * p.BN) < 32 ? 32 : pow2_ceil(2 * p.BN);
+    const size_t w_tile = (size_t)p.BN * 128;
+    const size_t budget = 225 * 1024 - 1024;
+    const size_t w_all = (size_t)p.chunks * 9 * w_tile;
+    p.a_stages = p.chunks >= 2 ? 3 : 3;
+    if (w_all + (size_t)2 * kHaloBytes <= budget) {
+      p.w_resident = 1;
+      p.w_stages = 0;
+      while (p.a_stages > 2 && w_all + (size_t)p.a_stages * kHaloBytes > budget) --p.a_stages;
+      smem = 1024 + w_all + (size_t)p.a_stages * kHaloBytes;
+    } else {
+      p.w_resident = 0;
+      p.w_stages = 4;
+      p.a_stages = 4;
+      smem = 1024 + (size_t)p.w_stages * w_tile + (size_t)p.a_stages * kHaloBytes;
+    }
+    int dev = 0, sms = kNumSMs;
+    if (cudaGetDevice(&dev) == cudaSuccess) cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+    grid_x = sms / p.n_tiles;
+    if (grid_x < 1) grid_x = 1;
+    if (grid_x > p.num_tiles) grid_x = p.num_tiles;
+  }
+
   ditsep_conv_plan* pl = new ditsep_conv_plan();
   pl->p = p;
-  pl->smem = 1024 + (size_t)p.stages * stage_bytes;
+  pl->smem = smem;
+  pl->halo = halo;
+  pl->grid_x = grid_x;
   {
     cuuint64_t gdim[4] = {(cuuint64_t)Cin, (cuuint64_t)W, (cuuint64_t)H, (cuuint64_t)B};
     cuuint64_t gstr[3] = {(cuuint64_t)ld_in * 2, (cuuint64_t)W * ld_in * 2, (cuuint64_t)H * W * ld_in * 2};
     cuuint32_t box[4] = {(cuuint32_t)kBlockK, (cuuint32_t)p.bw, (cuuint32_t)p.bh, (cuuint32_t)p.bb};
+    if (halo) { box[1] = kHaloW; box[2] = kHaloH; box[3] = 1; }
     cuuint32_t estr[4] = {1, 1, 1, 1};
     CUresult r = encode(&pl->mapA, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 4, const_cast<void*>(in), gdim, gstr, box, estr,
                         CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
@@ -408,6 +696,7 @@ extern "C" int ditsep_conv_tc_plan_create(ditsep_conv_plan** plan, const void* i
   if (!attr_set) {
     DITSEP_CUDA(cudaFuncSetAttribute(conv_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                      1024 + kMaxStages * (kABytes + 128 * 128)));
+    DITSEP_CUDA(cudaFuncSetAttribute(conv_tc_halo_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 225 * 1024));
     attr_set = true;
   }
   *plan = pl;
@@ -418,15 +707,22 @@ extern "C" void ditsep_conv_tc_plan_destroy(ditsep_conv_plan* plan) { delete pla
 
 extern "C" int ditsep_conv_tc_run(const ditsep_conv_plan* plan, const float* bias, const float* bias_b, int ld_bias_b,
                                   const void* residual, int res_dtype, int ld_res, float out_scale, void* out,
-                                  int out_dtype, int ld_out, void* stream) {
+                                  int out_dtype, int ld_out, float* stats, int ld_stats, void* stream) {
   DITSEP_REQUIRE(plan && out, "conv_tc_run: null pointer");
   DITSEP_REQUIRE(out_dtype == DITSEP_F32 || out_dtype == DITSEP_BF16, "conv_tc_run: unknown out dtype %d", out_dtype);
   DITSEP_REQUIRE(!residual || res_dtype == DITSEP_F32 || res_dtype == DITSEP_BF16, "conv_tc_run: unknown residual dtype");
   DITSEP_REQUIRE(ld_out >= plan->p.Cout, "conv_tc_run: ld_out=%d < Cout=%d", ld_out, plan->p.Cout);
+  DITSEP_REQUIRE(!stats || ld_stats >= plan->p.Cout, "conv_tc_run: ld_stats=%d < Cout=%d", ld_stats, plan->p.Cout);
   ConvTcParams p = plan->p;
   p.bias = bias; p.bias_b = bias_b; p.ld_bias_b = ld_bias_b;
   p.residual = residual; p.res_dtype = res_dtype; p.ld_res = ld_res;
   p.out_scale = out_scale; p.out = out; p.out_dtype = out_dtype; p.ld_out = ld_out;
+  p.stats = stats; p.ld_stats = ld_stats;
+  if (plan->halo) {
+    dim3 grid((unsigned)plan->grid_x, (unsigned)p.n_tiles);
+    conv_tc_halo_kernel<<<grid, kHaloThreads, plan->smem, (cudaStream_t)stream>>>(plan->mapA, plan->mapW, p);
+    return check_launch("conv_tc_halo_kernel");
+  }
   dim3 grid((unsigned)((int64_t)p.tiles_x * p.tiles_y * p.tiles_b), (unsigned)p.n_tiles);
   conv_tc_kernel<<<grid, kThreads, plan->smem, (cudaStream_t)stream>>>(plan->mapA, plan->mapW, p);
   return check_launch("conv_tc_kernel");

@@ -99,6 +99,38 @@ __global__ void __launch_bounds__(256) gn_finalize_kernel(const float* __restric
   }
 }
 
+// Per-channel {sum, sum of squares} accumulated by the producing convolution's epilogue
+// (stats: [B][ld_stats][2]) -> per-(b,c) scale / shift.  grid B, block 256.
+__global__ void __launch_bounds__(256) gn_finalize_sums_kernel(const float* __restrict__ stats, int ld_stats, int64_t HW,
+                                                               int C, int G, const float* __restrict__ gamma,
+                                                               const float* __restrict__ beta, float eps,
+                                                               float* __restrict__ scale_shift) {
+  extern __shared__ double sh[];  // [G][2]
+  const int b = blockIdx.x;
+  const int cpg = C / G;
+  for (int g = threadIdx.x; g < G; g += blockDim.x) {
+    double a = 0.0, q = 0.0;
+    for (int i = 0; i < cpg; ++i) {
+      const float* src = stats + ((int64_t)b * ld_stats + g * cpg + i) * 2;
+      a += (double)src[0];
+      q += (double)src[1];
+    }
+    const double n = (double)HW * cpg;
+    const double mean = a / n;
+    double var = q / n - mean * mean;
+    if (var < 0.0) var = 0.0;
+    sh[2 * g] = mean;
+    sh[2 * g + 1] = 1.0 / sqrt(var + (double)eps);
+  }
+  __syncthreads();
+  for (int c = threadIdx.x; c < C; c += blockDim.x) {
+    const int g = c / cpg;
+    const double sc = sh[2 * g + 1] * (double)gamma[c];
+    scale_shift[((int64_t)b * 2) * C + c] = (float)sc;
+    scale_shift[((int64_t)b * 2 + 1) * C + c] = (float)((double)beta[c] - sh[2 * g] * sc);
+  }
+}
+
 // ------------------------------------------------------------------- normalise + SiLU
 template <typename T>
 __global__ void __launch_bounds__(256) gn_apply_kernel(const T* __restrict__ x, int64_t HW, int C, int ld_x,
@@ -407,6 +439,16 @@ extern "C" int ditsep_gn_stats(const void* x, int dtype, int B, int64_t HW, int 
   gn_finalize_kernel<<<B, 256, (size_t)(2 * C + 2 * G) * sizeof(double), st>>>(partial, nsplit, HW, C, G, gamma, beta,
                                                                                 eps, scale_shift);
   return check_launch("gn_finalize_kernel");
+}
+
+extern "C" int ditsep_gn_finalize(const float* stats, int ld_stats, int B, int64_t HW, int C, int G, const float* gamma,
+                                  const float* beta, float eps, float* scale_shift, void* stream) {
+  DITSEP_REQUIRE(stats && gamma && beta && scale_shift, "gn_finalize: null pointer");
+  DITSEP_REQUIRE(B > 0 && HW > 0 && G > 0 && C % G == 0 && ld_stats >= C, "gn_finalize: bad sizes C=%d G=%d ld=%d", C, G,
+                 ld_stats);
+  gn_finalize_sums_kernel<<<B, 256, (size_t)2 * G * sizeof(double), (cudaStream_t)stream>>>(stats, ld_stats, HW, C, G,
+                                                                                            gamma, beta, eps, scale_shift);
+  return check_launch("gn_finalize_sums_kernel");
 }
 
 extern "C" int ditsep_gn_apply(const void* x, int dtype, int B, int64_t HW, int C, int ld_x, const float* scale_shift,

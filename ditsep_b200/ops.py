@@ -160,6 +160,25 @@ def gn_stats(x, G: int, gamma, beta, eps: float, partial, scale_shift):
                                       _ptr(partial), nsplit, _ptr(scale_shift), _stream()), "gn_stats")
 
 
+def _stats_args(stats, B: int, Cout: int):
+    """stats: f32 view (B, Cout, 2) with strides (ld*2, 2, 1) -> (pointer, ld)."""
+    if stats is None:
+        return None, 0
+    if stats.dtype != torch.float32 or tuple(stats.shape) != (B, Cout, 2) or stats.stride(2) != 1 or stats.stride(1) != 2:
+        raise _lib.DitsepError(f"stats must be a float32 (B={B}, C={Cout}, 2) view with strides (ld*2, 2, 1)")
+    return stats.data_ptr(), (stats.stride(0) // 2 if B > 1 else Cout)
+
+
+def gn_finalize(stats, HW: int, G: int, gamma, beta, eps: float, scale_shift):
+    """stats (B, C, 2) per-channel {sum, sumsq} (a channel slice of a wider buffer is fine) ->
+    scale_shift (B, 2, C)."""
+    _cuda(stats, gamma, beta, scale_shift)
+    B, Cc, _ = stats.shape
+    ptr, ld = _stats_args(stats, B, Cc)
+    check(_lib.load().ditsep_gn_finalize(ptr, ld, B, HW, Cc, G, _ptr(gamma), _ptr(beta), eps, _ptr(scale_shift),
+                                         _stream()), "gn_finalize")
+
+
 def gn_apply(x, scale_shift, silu: bool, y):
     _cuda(x, scale_shift, y)
     B, H, W, Cc = x.shape
@@ -178,9 +197,10 @@ def fir_resample(x, up: bool, out_x=None, scale_shift=None, out_h=None):
 
 
 # ------------------------------------------------------------------ convolution
-def conv_direct(x, w, bias, out, ksize: int, bias_b=None, residual=None, out_scale: float = 1.0):
-    """x NHWC, w (Cout, taps, Cin) f32, out NHWC.  out = out_scale*(conv + bias + bias_b[b] + residual)."""
-    _cuda(x, w, bias, out, bias_b, residual)
+def conv_direct(x, w, bias, out, ksize: int, bias_b=None, residual=None, out_scale: float = 1.0, stats=None):
+    """x NHWC, w (Cout, taps, Cin) f32, out NHWC.  out = out_scale*(conv + bias + bias_b[b] + residual);
+    stats (B, Cout, 2) += per-channel {sum, sumsq} of out."""
+    _cuda(x, w, bias, out, bias_b, residual, stats)
     B, H, W, Cin = x.shape
     Cout = out.shape[3]
     if w.dtype != torch.float32 or not w.is_contiguous() or w.shape != (Cout, ksize * ksize, Cin):
@@ -190,7 +210,8 @@ def conv_direct(x, w, bias, out, ksize: int, bias_b=None, residual=None, out_sca
     check(_lib.load().ditsep_conv_direct(_ptr(x), _dt(x), B, H, W, Cin, nhwc_ld(x), _ptr(w), _ptr(bias), _ptr(bias_b),
                                          0 if bias_b is None else bias_b.stride(0), _ptr(residual),
                                          0 if residual is None else nhwc_ld(residual), out_scale, Cout, ksize,
-                                         _ptr(out), _dt(out), nhwc_ld(out), _stream()), "conv_direct")
+                                         _ptr(out), _dt(out), nhwc_ld(out), *_stats_args(stats, B, Cout), _stream()),
+          "conv_direct")
 
 
 class ConvTcPlan:
@@ -209,13 +230,14 @@ class ConvTcPlan:
         check(_lib.load().ditsep_conv_tc_plan_create(C.byref(self._h), _ptr(x), B, H, W, Cin, nhwc_ld(x), _ptr(w_bf16),
                                                      Cout, ksize), "conv_tc_plan_create")
 
-    def run(self, bias, out, bias_b=None, residual=None, out_scale: float = 1.0):
-        _cuda(bias, out, bias_b, residual)
+    def run(self, bias, out, bias_b=None, residual=None, out_scale: float = 1.0, stats=None):
+        _cuda(bias, out, bias_b, residual, stats)
         check(_lib.load().ditsep_conv_tc_run(self._h, _ptr(bias), _ptr(bias_b),
                                              0 if bias_b is None else bias_b.stride(0), _ptr(residual),
                                              0 if residual is None else _dt(residual),
                                              0 if residual is None else nhwc_ld(residual), out_scale, _ptr(out),
-                                             _dt(out), nhwc_ld(out), _stream()), "conv_tc_run")
+                                             _dt(out), nhwc_ld(out), *_stats_args(stats, self.shape[0], self.Cout),
+                                             _stream()), "conv_tc_run")
 
     def __del__(self):
         h = getattr(self, "_h", None)

@@ -221,6 +221,8 @@ TC_CASES = [
     (2, 16, 16, 128, 0, 384, 1),      # fused q/k/v projection (three N tiles)
     (1, 32, 32, 64, 0, 6, 3),         # progressive-output conv (N padded to 16)
     (2, 16, 16, 128, 0, 64, 1),
+    (1, 40, 20, 64, 0, 64, 3),        # halo tiles with ragged right / bottom edges
+    (2, 32, 16, 256, 0, 128, 3),      # four 64-channel blocks, filter streamed
 ]
 
 
@@ -238,10 +240,16 @@ def test_conv_tc(B, H, W, Cin, ld_extra, Cout, k):
     xd = xb.to(DEV)[..., ld_extra:]
     plan = ops.ConvTcPlan(xd, wpad.to(DEV), Cout, k)
     out = torch.empty(B, H, W, Cout, device=DEV)
-    plan.run(bias.to(DEV), out, bias_b=bias_b.to(DEV)[:, 5:], residual=res.to(DEV), out_scale=0.7)
+    stats_buf = torch.zeros(B, Cout + 3, 2, device=DEV)
+    plan.run(bias.to(DEV), out, bias_b=bias_b.to(DEV)[:, 5:], residual=res.to(DEV), out_scale=0.7,
+             stats=stats_buf[:, 3:])
     torch.cuda.synchronize()
     # same bf16 operands, fp32 accumulation on both sides: only summation order differs
     assert rel(out, ref) < 2e-5, rel(out, ref)
+    # fused GroupNorm statistics of the stored output: per-image, per-channel sum and sum of squares
+    assert rel(stats_buf[:, 3:, 0], ref.sum(dim=(1, 2))) < 1e-4 + 1e-3 * (ref.sum(dim=(1, 2)).abs().min() < 1)
+    assert rel(stats_buf[:, 3:, 1], (ref * ref).sum(dim=(1, 2))) < 1e-4
+    assert float(stats_buf[:, :3].abs().max()) == 0.0
     outb = torch.empty(B, H, W, Cout, device=DEV, dtype=torch.bfloat16)
     resb = res.to(torch.bfloat16)
     plan.run(bias.to(DEV), outb, residual=resb.to(DEV))
@@ -251,6 +259,46 @@ def test_conv_tc(B, H, W, Cin, ld_extra, Cout, k):
     out2 = resb.to(DEV).clone()
     plan.run(bias.to(DEV), out2, residual=out2)
     assert rel(out2.float(), ref) < 4e-3
+
+
+def test_conv_tc_halo_descriptor_probe(monkeypatch):
+    """Which UMMA descriptor convention reads a row-shifted view of a 128B-swizzled TMA tile?
+    mode 0: base_offset = 0 (swizzle keyed on absolute smem address bits), mode 1: base_offset =
+    (start >> 7) & 7.  The library default must be a mode that reproduces the convolution."""
+    B, H, W, Cin, Cout, k = 1, 32, 32, 64, 64, 3
+    buf, w, bias, bias_b, res = _conv_case(B, H, W, Cin, Cout, k, 77)
+    xb, wb = buf.to(torch.bfloat16), w.to(torch.bfloat16)
+    ref = torch.empty(B, H, W, Cout)
+    E.conv_direct(xb.float(), wb.float(), bias, ref, k)
+    errs = {}
+    for mode in ("0", "1"):
+        monkeypatch.setenv("DITSEP_TC_BASEOFF", mode)
+        plan = ops.ConvTcPlan(xb.to(DEV), wb.to(DEV), Cout, k)
+        out = torch.empty(B, H, W, Cout, device=DEV)
+        plan.run(bias.to(DEV), out)
+        torch.cuda.synchronize()
+        errs[mode] = rel(out, ref)
+    monkeypatch.delenv("DITSEP_TC_BASEOFF")
+    print("halo descriptor probe (rel-L2 per base-offset mode):", errs)
+    assert errs["0"] < 2e-5, errs
+
+
+def test_conv_direct_stats_and_gn_finalize():
+    B, H, W, Cin, Cout, k = 2, 16, 24, 6, 64, 3
+    buf, w, bias, bias_b, res = _conv_case(B, H, W, Cin, Cout, k, 88)
+    ref = torch.empty(B, H, W, Cout)
+    E.conv_direct(buf, w, bias, ref, k)
+    out = torch.empty(B, H, W, Cout, device=DEV, dtype=torch.bfloat16)
+    stats = torch.zeros(B, 2 * Cout, 2, device=DEV)
+    ops.conv_direct(buf.to(DEV), w.to(DEV), bias.to(DEV), out, k, stats=stats[:, Cout:])
+    o = out.float().cpu()
+    assert rel(stats[:, Cout:, 0], o.sum(dim=(1, 2))) < 1e-4 and rel(stats[:, Cout:, 1], (o * o).sum(dim=(1, 2))) < 1e-4
+    gamma, beta = 1 + 0.1 * torch.randn(Cout, generator=g(1)), 0.1 * torch.randn(Cout, generator=g(2))
+    ss_ref = torch.empty(B, 2, Cout)
+    E.gn_stats(o, 16, gamma, beta, 1e-6, None, ss_ref)
+    ss = torch.empty(B, 2, Cout, device=DEV)
+    ops.gn_finalize(stats[:, Cout:], H * W, 16, gamma.to(DEV), beta.to(DEV), 1e-6, ss)
+    assert rel(ss, ss_ref) < 1e-4
 
 
 # ------------------------------------------------------------------ attention / temb / output layer
