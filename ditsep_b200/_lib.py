@@ -21,6 +21,15 @@ class SdeParams(C.Structure):
                 ("sigma_max", C.c_float), ("N", C.c_int32), ("snr", C.c_float)]
 
 
+class StatsSrc(C.Structure):
+    """ditsep_stats_src (include/ditsep_b200.h): where a producer left per-channel {sum, sumsq}."""
+
+    _fields_ = [("ptr", C.c_void_p), ("kind", C.c_int32), ("C", C.c_int32), ("ld", C.c_int32), ("n_part", C.c_int32),
+                ("maxf", C.c_int32), ("tiles_per_image", C.c_int32), ("num_tiles", C.c_int32)]
+
+
+STATS_NONE, STATS_CONV_PARTIALS, STATS_SPLIT_SUMS = 0, 1, 2
+
 # name -> (restype, argtypes); must list EVERY symbol of include/ditsep_b200.h
 SIGNATURES = {
     "ditsep_abi_version": (c_int, []),
@@ -39,19 +48,21 @@ SIGNATURES = {
                                     c_void_p]),
     "ditsep_gn_stats": (c_int, [c_void_p, c_int, c_int, c_int64, c_int, c_int, c_int, c_void_p, c_void_p, c_float,
                                 c_void_p, c_int, c_void_p, c_void_p]),
-    "ditsep_gn_finalize": (c_int, [c_void_p, c_int, c_int, c_int64, c_int, c_int, c_void_p, c_void_p, c_float, c_void_p,
-                                   c_void_p]),
+    "ditsep_gn_partial_sums": (c_int, [c_void_p, c_int, c_int, c_int64, c_int, c_int, c_void_p, c_int, c_void_p]),
+    "ditsep_gn_finalize": (c_int, [C.POINTER(StatsSrc), c_int, c_int, c_int64, c_int, c_void_p, c_void_p, c_float,
+                                   c_void_p, c_void_p]),
     "ditsep_gn_apply": (c_int, [c_void_p, c_int, c_int, c_int64, c_int, c_int, c_void_p, c_int, c_void_p, c_int,
                                 c_void_p]),
     "ditsep_fir_resample": (c_int, [c_void_p, c_int, c_int, c_int, c_int, c_int, c_int, c_int, c_void_p, c_void_p,
                                     c_int, c_void_p, c_int, c_void_p]),
     "ditsep_conv_direct": (c_int, [c_void_p, c_int, c_int, c_int, c_int, c_int, c_int, c_void_p, c_void_p, c_void_p,
-                                   c_int, c_void_p, c_int, c_float, c_int, c_int, c_void_p, c_int, c_int, c_void_p, c_int, c_void_p]),
+                                   c_int, c_void_p, c_int, c_float, c_int, c_int, c_void_p, c_int, c_int, c_void_p]),
     "ditsep_conv_tc_plan_create": (c_int, [C.POINTER(c_void_p), c_void_p, c_int, c_int, c_int, c_int, c_int, c_void_p,
                                            c_int, c_int]),
     "ditsep_conv_tc_plan_destroy": (None, [c_void_p]),
+    "ditsep_conv_tc_stats_layout": (c_int, [c_void_p, C.POINTER(StatsSrc)]),
     "ditsep_conv_tc_run": (c_int, [c_void_p, c_void_p, c_void_p, c_int, c_void_p, c_int, c_int, c_float, c_void_p,
-                                   c_int, c_int, c_void_p, c_int, c_void_p]),
+                                   c_int, c_int, c_void_p, c_void_p]),
     "ditsep_attention": (c_int, [c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_int, c_int, c_void_p, c_int,
                                  c_void_p]),
     "ditsep_temb_mlp": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_int,

@@ -153,12 +153,11 @@ using namespace ditsep;
 extern "C" int ditsep_conv_direct(const void* in, int dtype, int B, int H, int W, int Cin, int ld_in, const float* w,
                                   const float* bias, const float* bias_b, int ld_bias_b, const void* residual,
                                   int ld_res, float out_scale, int Cout, int ksize, void* out, int out_dtype,
-                                  int ld_out, float* stats, int ld_stats, void* stream) {
+                                  int ld_out, void* stream) {
   DITSEP_REQUIRE(in && w && out, "conv_direct: null pointer");
   DITSEP_REQUIRE(ksize == 1 || ksize == 3, "conv_direct: ksize=%d (1 or 3)", ksize);
   DITSEP_REQUIRE(B > 0 && H > 0 && W > 0 && Cin > 0 && Cout > 0, "conv_direct: empty problem");
   DITSEP_REQUIRE(ld_in >= Cin && ld_out >= Cout, "conv_direct: strides smaller than channel counts");
-  DITSEP_REQUIRE(!stats || ld_stats >= Cout, "conv_direct: ld_stats=%d < Cout=%d", ld_stats, Cout);
   const int64_t M = (int64_t)B * H * W;
   dim3 grid(ceil_div(M, BM), ceil_div(Cout, BN));
   cudaStream_t st = (cudaStream_t)stream;
@@ -166,7 +165,7 @@ extern "C" int ditsep_conv_direct(const void* in, int dtype, int B, int H, int W
 #define LAUNCH(TI, TO)                                                                                              \
   conv_direct_kernel<TI, TO, TO><<<grid, 256, 0, st>>>((const TI*)in, B, H, W, Cin, ld_in, w, bias, bias_b, ld_bias_b, \
                                                        (const TO*)residual, ld_res, out_scale, Cout, ksize, (TO*)out,  \
-                                                       ld_out, stats, ld_stats)
+                                                       ld_out, nullptr, 0)
   if (dtype == DITSEP_F32 && out_dtype == DITSEP_F32) LAUNCH(float, float);
   else if (dtype == DITSEP_BF16 && out_dtype == DITSEP_BF16) LAUNCH(bf16, bf16);
   else if (dtype == DITSEP_BF16 && out_dtype == DITSEP_F32) LAUNCH(bf16, float);

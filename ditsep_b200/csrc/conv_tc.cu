@@ -7,27 +7,31 @@
 // ddpm_conv1x1 (ncsnpp_utils/layers.py:112-156), NIN (layers.py:678-689), with the
 // res-block tail (layerspp.py:314-328) fused as the epilogue.
 //
-// GEMM view: M = 128 output pixels per CTA (a bw x bh x bb box of the image batch),
-// N = BN <= 128 output channels, K = taps * Cin walked in blocks of 64 channels.
-//  * A operand: NO im2col.  The activation tensor is described to TMA as a 4-D tensor
-//    (C, W, H, B); the K-block of tap (dy,dx) is ONE cp.async.bulk.tensor box
-//    (64 ch, bw, bh, bb) at coordinates (c0, x0+dx, y0+dy, b0).  Out-of-image pixels are
-//    zero-filled by the TMA unit (that is the conv's zero padding), and the box lands in
-//    shared memory as 128 rows of 128 bytes with the 128-byte swizzle = the canonical
-//    K-major UMMA operand layout.
-//  * B operand: the filter as a 2-D tensor (K, CoutPad), box (64, BN), same swizzle.
-//  * warp 0 = TMA producer, warp 1 = TMEM allocator + single-thread tcgen05.mma issuer,
-//    warps 2-5 = epilogue (tcgen05.ld 32 lanes x 16 columns -> bias / temb / residual /
-//    scale -> global).  kStages-deep full/empty mbarrier ring between producer and MMA;
-//    tcgen05.commit releases a stage when the MMAs that read it have retired.
-//  * several CTAs are resident per SM (smem ring 72-128 KB, <= 128 TMEM columns each), so one
-//    CTA's epilogue overlaps another's main loop.
-#include <cuda.h>
-
+// GEMM view: M = 128 output pixels per tile, N = BN output channels, K = taps * Cin walked in
+// blocks of 64 channels.  NO im2col: the activation tensor is described to TMA as a 4-D tensor
+// (C, W, H, B); out-of-image pixels are zero-filled by the TMA unit (= the conv's zero padding)
+// and a box lands in shared memory as rows of 128 bytes with the 128-byte swizzle, which is the
+// canonical K-major UMMA operand layout.  Two kernels:
+//
+//  * conv_tc_tile_kernel (images of at least 8 x 16 pixels): the M tile is 8 (x) by 16 (y)
+//    pixels of one image.  Per 64-channel block ONE TMA box brings the tile plus its halo
+//    ((8+2h) x (16+2h) pixels, h = 1 for 3x3, 0 for 1x1); the A operand of tap (dy,dx) is the
+//    SAME shared-memory tile read through a UMMA descriptor whose start is shifted by
+//    (dy*(8+2h) + dx) rows and whose 8-row groups are (8+2h) rows apart -- every input element
+//    is fetched from L2 once per tile instead of nine times.  CTAs are persistent over a
+//    CONTIGUOUS range of tiles; the filter slice of the CTA's N tile stays resident in shared
+//    memory when it fits (else it streams through a ring).  Two TMEM accumulators alternate, and
+//    16 epilogue warps (4 per TMEM lane quadrant, 16 output channels each) drain one while the
+//    single MMA thread fills the other.  The epilogue also accumulates, in registers, the
+//    per-channel sum / sum of squares of what it stores (the GroupNorm statistics of the output
+//    tensor, layerspp.py:297,318) and writes them per (CTA, image) -- no atomics, so the
+//    statistics (and with them the whole bf16 network) are bit-reproducible.
+//  * conv_tc_kernel (smaller images, where a 128-pixel tile spans several images): one TMA box
+//    per (tap, 64-channel block), one tile per CTA.
 #include <cstdlib>
 #include <cstring>
 
-#include "common.cuh"
+#include "tc_ptx.cuh"
 
 namespace ditsep {
 
@@ -50,211 +54,108 @@ struct ConvTcParams {
   float out_scale;
   void* out;
   int out_dtype, ld_out;
-  float* stats;            // nullable: per-(b, channel) {sum, sum of squares} of the OUTPUT, [B][ld_stats][2]
-  int ld_stats;
-  // halo mode (3x3): 8 x 16 pixel tiles, persistent CTAs, optional resident filter
-  int num_tiles, chunks, w_resident, a_stages, w_stages, base_off_mode;
+  // tile kernel
+  int num_tiles, tiles_per_image, chunks, w_resident, a_stages, w_stages;
+  int halo, row_pitch, a_rows, a_stage_bytes;
+  float* stats;            // nullable: partial sums [grid_x][maxf][ld_part][2]
+  int maxf, ld_part;
 };
 
-// ---- PTX wrappers ------------------------------------------------------------------------
-__device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
-
-__device__ __forceinline__ void mbar_init(uint32_t bar, uint32_t count) {
-  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(bar), "r"(count) : "memory");
-}
-__device__ __forceinline__ void mbar_expect_tx(uint32_t bar, uint32_t bytes) {
-  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes) : "memory");
-}
-__device__ __forceinline__ bool mbar_try_wait(uint32_t bar, uint32_t parity) {
-  uint32_t ok;
-  asm volatile(
-      "{\n\t.reg .pred p;\n\t"
-      "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
-      "selp.u32 %0, 1, 0, p;\n\t}"
-      : "=r"(ok)
-      : "r"(bar), "r"(parity)
-      : "memory");
-  return ok != 0;
-}
-// Bounded wait: a protocol bug must not hang the GPU; after ~seconds it traps (sticky error).
-__device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
-  uint32_t spins = 0;
-  while (!mbar_try_wait(bar, parity)) {
-    if (++spins > (1u << 28)) __trap();
-  }
-}
-__device__ __forceinline__ void tma_load_4d(uint32_t dst, const CUtensorMap* map, uint32_t bar, int c0, int c1, int c2,
-                                            int c3) {
-  asm volatile(
-      "cp.async.bulk.tensor.4d.shared::cluster.global.tile.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4, %5, %6}], [%2];"
-      ::"r"(dst), "l"(map), "r"(bar), "r"(c0), "r"(c1), "r"(c2), "r"(c3)
-      : "memory");
-}
-__device__ __forceinline__ void tma_load_2d(uint32_t dst, const CUtensorMap* map, uint32_t bar, int c0, int c1) {
-  asm volatile(
-      "cp.async.bulk.tensor.2d.shared::cluster.global.tile.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];"
-      ::"r"(dst), "l"(map), "r"(bar), "r"(c0), "r"(c1)
-      : "memory");
-}
-__device__ __forceinline__ void tmem_alloc(uint32_t dst_smem, uint32_t ncols) {
-  asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(dst_smem), "r"(ncols) : "memory");
-  asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
-}
-__device__ __forceinline__ void tmem_dealloc(uint32_t taddr, uint32_t ncols) {
-  asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(taddr), "r"(ncols) : "memory");
-}
-__device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
-__device__ __forceinline__ void tc_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
-__device__ __forceinline__ void umma_bf16(uint32_t tmem_d, uint64_t desc_a, uint64_t desc_b, uint32_t idesc,
-                                          uint32_t accumulate) {
-  asm volatile(
-      "{\n\t.reg .pred p;\n\t"
-      "setp.ne.b32 p, %4, 0;\n\t"
-      "tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n\t}"
-      ::"r"(tmem_d), "l"(desc_a), "l"(desc_b), "r"(idesc), "r"(accumulate)
-      : "memory");
-}
-__device__ __forceinline__ void umma_commit(uint32_t bar) {
-  asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(bar) : "memory");
-}
-__device__ __forceinline__ void tmem_ld16(uint32_t taddr, uint32_t (&v)[16]) {
-  asm volatile(
-      "tcgen05.ld.sync.aligned.32x32b.x16.b32 {%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15}, [%16];"
-      : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]), "=r"(v[4]), "=r"(v[5]), "=r"(v[6]), "=r"(v[7]), "=r"(v[8]),
-        "=r"(v[9]), "=r"(v[10]), "=r"(v[11]), "=r"(v[12]), "=r"(v[13]), "=r"(v[14]), "=r"(v[15])
-      : "r"(taddr)
-      : "memory");
-  asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
-}
-
-// K-major, 128-byte-swizzled operand tile: rows of 128 bytes, 8-row groups 1024 bytes apart.
-// (cute::UMMA::SmemDescriptor: start>>4 [0,14), LBO>>4 [16,30), SBO>>4 [32,46), version=1 [46,48),
-//  layout SWIZZLE_128B=2 [61,64).)
-__device__ __forceinline__ uint64_t make_sw128_desc(uint32_t smem_addr) {
-  return (uint64_t)((smem_addr >> 4) & 0x3FFF) | (1ull << 16) | (64ull << 32) | (1ull << 46) | (2ull << 61);
-}
-
 // ---- shared epilogue -----------------------------------------------------------------------
-// One thread = one output pixel (TMEM lane), 16 consecutive output channels per call.
-// v: raw fp32 accumulators.  Applies bias / per-image bias / residual / scale, stores, and (if
-// p.stats) accumulates the GroupNorm statistics of the stored tensor: a 4-step halving exchange
-// leaves each lane pair with one channel's sum over the warp's 32 pixels, then one red.add per
-// channel per warp.  `uniform_b`: all lanes of the warp belong to the same image.
+// One thread = one output pixel (TMEM lane), 16 consecutive output channels.  v: raw fp32
+// accumulators.  Applies bias / per-image bias / residual / scale and stores; on return f[] holds
+// the values as stored (bf16-rounded for bf16 outputs; 0 for channels >= Cout or invalid pixels).
 __device__ __forceinline__ void epilogue16(const ConvTcParams& p, const uint32_t (&v)[16], bool valid, int pb,
-                                           int64_t pix, int co0, bool uniform_b, int lane) {
+                                           int64_t pix, int co0, float (&f)[16]) {
   const int nvalid = min(16, p.Cout - co0);  // > 0 guaranteed by the caller
-  float f[16];
 #pragma unroll
-  for (int j = 0; j < 16; ++j) {
-    float a = __uint_as_float(v[j]);
-    if (j < nvalid) {
-      if (p.bias) a += __ldg(p.bias + co0 + j);
-      if (p.bias_b && valid) a += __ldg(p.bias_b + (int64_t)pb * p.ld_bias_b + co0 + j);
-    }
-    f[j] = a;
-  }
-  if (valid) {
-    if (p.residual) {
-      if (p.res_dtype == DITSEP_BF16) {
-        const bf16* rp = reinterpret_cast<const bf16*>(p.residual) + pix * p.ld_res + co0;
-        if (nvalid == 16 && ((reinterpret_cast<uintptr_t>(rp) & 15) == 0)) {
-          float t[8];
-          Pack8<bf16>::load(rp, t);
+  for (int j = 0; j < 16; ++j) f[j] = __uint_as_float(v[j]);
+  if (p.bias) {
+    const float* bp = p.bias + co0;
+    if (nvalid == 16 && ((reinterpret_cast<uintptr_t>(bp) & 15) == 0)) {
 #pragma unroll
-          for (int j = 0; j < 8; ++j) f[j] += t[j];
-          Pack8<bf16>::load(rp + 8, t);
-#pragma unroll
-          for (int j = 0; j < 8; ++j) f[8 + j] += t[j];
-        } else {
-#pragma unroll
-          for (int j = 0; j < 16; ++j)
-            if (j < nvalid) f[j] += __bfloat162float(rp[j]);
-        }
-      } else {
-        const float* rp = reinterpret_cast<const float*>(p.residual) + pix * p.ld_res + co0;
-#pragma unroll
-        for (int j = 0; j < 16; ++j)
-          if (j < nvalid) f[j] += rp[j];
-      }
-    }
-#pragma unroll
-    for (int j = 0; j < 16; ++j) f[j] *= p.out_scale;
-    if (p.out_dtype == DITSEP_BF16) {
-      bf16* op = reinterpret_cast<bf16*>(p.out) + pix * p.ld_out + co0;
-      if (nvalid == 16 && ((reinterpret_cast<uintptr_t>(op) & 15) == 0)) {
-        float t[8];
-#pragma unroll
-        for (int j = 0; j < 8; ++j) t[j] = f[j];
-        Pack8<bf16>::store(op, t);
-#pragma unroll
-        for (int j = 0; j < 8; ++j) t[j] = f[8 + j];
-        Pack8<bf16>::store(op + 8, t);
-      } else {
-#pragma unroll
-        for (int j = 0; j < 16; ++j)
-          if (j < nvalid) op[j] = __float2bfloat16_rn(f[j]);
-      }
-      if (p.stats) {  // statistics of what the consumer will read: the bf16-rounded values
-#pragma unroll
-        for (int j = 0; j < 16; ++j) f[j] = __bfloat162float(__float2bfloat16_rn(f[j]));
+      for (int j = 0; j < 16; j += 4) {
+        const float4 t = __ldg(reinterpret_cast<const float4*>(bp + j));
+        f[j] += t.x; f[j + 1] += t.y; f[j + 2] += t.z; f[j + 3] += t.w;
       }
     } else {
-      float* op = reinterpret_cast<float*>(p.out) + pix * p.ld_out + co0;
-      if (nvalid == 16 && ((reinterpret_cast<uintptr_t>(op) & 15) == 0)) {
 #pragma unroll
-        for (int j = 0; j < 16; j += 4) *reinterpret_cast<float4*>(op + j) = make_float4(f[j], f[j + 1], f[j + 2], f[j + 3]);
+      for (int j = 0; j < 16; ++j)
+        if (j < nvalid) f[j] += __ldg(bp + j);
+    }
+  }
+  if (!valid) {
+#pragma unroll
+    for (int j = 0; j < 16; ++j) f[j] = 0.f;
+    return;
+  }
+  if (p.bias_b) {
+    const float* bp = p.bias_b + (int64_t)pb * p.ld_bias_b + co0;
+    if (nvalid == 16 && ((reinterpret_cast<uintptr_t>(bp) & 15) == 0)) {
+#pragma unroll
+      for (int j = 0; j < 16; j += 4) {
+        const float4 t = __ldg(reinterpret_cast<const float4*>(bp + j));
+        f[j] += t.x; f[j + 1] += t.y; f[j + 2] += t.z; f[j + 3] += t.w;
+      }
+    } else {
+#pragma unroll
+      for (int j = 0; j < 16; ++j)
+        if (j < nvalid) f[j] += __ldg(bp + j);
+    }
+  }
+  if (p.residual) {
+    if (p.res_dtype == DITSEP_BF16) {
+      const bf16* rp = reinterpret_cast<const bf16*>(p.residual) + pix * p.ld_res + co0;
+      if (nvalid == 16 && ((reinterpret_cast<uintptr_t>(rp) & 15) == 0)) {
+        float t[8];
+        Pack8<bf16>::load(rp, t);
+#pragma unroll
+        for (int j = 0; j < 8; ++j) f[j] += t[j];
+        Pack8<bf16>::load(rp + 8, t);
+#pragma unroll
+        for (int j = 0; j < 8; ++j) f[8 + j] += t[j];
       } else {
 #pragma unroll
         for (int j = 0; j < 16; ++j)
-          if (j < nvalid) op[j] = f[j];
+          if (j < nvalid) f[j] += __bfloat162float(rp[j]);
       }
-    }
-  }
-  if (p.stats == nullptr) return;
-  if (!uniform_b) {  // deep levels: a warp spans several images -> plain per-thread reds (few pixels)
-    if (valid) {
-      float* sp = p.stats + ((int64_t)pb * p.ld_stats + co0) * 2;
+    } else {
+      const float* rp = reinterpret_cast<const float*>(p.residual) + pix * p.ld_res + co0;
 #pragma unroll
       for (int j = 0; j < 16; ++j)
-        if (j < nvalid) {
-          atomicAdd(sp + 2 * j, f[j]);
-          atomicAdd(sp + 2 * j + 1, f[j] * f[j]);
-        }
-    }
-    return;
-  }
-  float s[16], q[16];
-#pragma unroll
-  for (int j = 0; j < 16; ++j) {
-    s[j] = valid ? f[j] : 0.f;
-    q[j] = s[j] * s[j];
-  }
-  // halving exchange: after the steps with offsets 16, 8, 4, 2 lane l holds channel
-  // c = 8*b4 + 4*b3 + 2*b2 + b1 (bits of l) summed over the 16 lanes that share those bits' complement
-#pragma unroll
-  for (int step = 0; step < 4; ++step) {
-    const int off = 16 >> step;       // lane offset
-    const int half = 8 >> step;       // values kept
-    const bool upper = (lane & off) != 0;
-#pragma unroll
-    for (int j = 0; j < 8; ++j) {
-      if (j < half) {
-        const float send_s = upper ? s[j] : s[j + half];
-        const float send_q = upper ? q[j] : q[j + half];
-        const float keep_s = upper ? s[j + half] : s[j];
-        const float keep_q = upper ? q[j + half] : q[j];
-        s[j] = keep_s + __shfl_xor_sync(0xffffffffu, send_s, off);
-        q[j] = keep_q + __shfl_xor_sync(0xffffffffu, send_q, off);
-      }
+        if (j < nvalid) f[j] += rp[j];
     }
   }
-  s[0] += __shfl_xor_sync(0xffffffffu, s[0], 1);
-  q[0] += __shfl_xor_sync(0xffffffffu, q[0], 1);
-  const int c = ((lane >> 4) & 1) * 8 + ((lane >> 3) & 1) * 4 + ((lane >> 2) & 1) * 2 + ((lane >> 1) & 1);
-  if ((lane & 1) == 0 && c < nvalid) {
-    float* sp = p.stats + ((int64_t)pb * p.ld_stats + co0 + c) * 2;
-    atomicAdd(sp, s[0]);
-    atomicAdd(sp + 1, q[0]);
+#pragma unroll
+  for (int j = 0; j < 16; ++j) f[j] = (j < nvalid) ? f[j] * p.out_scale : 0.f;
+  if (p.out_dtype == DITSEP_BF16) {
+    bf16* op = reinterpret_cast<bf16*>(p.out) + pix * p.ld_out + co0;
+    if (nvalid == 16 && ((reinterpret_cast<uintptr_t>(op) & 15) == 0)) {
+      float t[8];
+#pragma unroll
+      for (int j = 0; j < 8; ++j) t[j] = f[j];
+      Pack8<bf16>::store(op, t);
+#pragma unroll
+      for (int j = 0; j < 8; ++j) t[j] = f[8 + j];
+      Pack8<bf16>::store(op + 8, t);
+    } else {
+#pragma unroll
+      for (int j = 0; j < 16; ++j)
+        if (j < nvalid) op[j] = __float2bfloat16_rn(f[j]);
+    }
+    // statistics are those of what the consumer will read: the bf16-rounded values
+#pragma unroll
+    for (int j = 0; j < 16; ++j) f[j] = __bfloat162float(__float2bfloat16_rn(f[j]));
+  } else {
+    float* op = reinterpret_cast<float*>(p.out) + pix * p.ld_out + co0;
+    if (nvalid == 16 && ((reinterpret_cast<uintptr_t>(op) & 15) == 0)) {
+#pragma unroll
+      for (int j = 0; j < 16; j += 4) *reinterpret_cast<float4*>(op + j) = make_float4(f[j], f[j + 1], f[j + 2], f[j + 3]);
+    } else {
+#pragma unroll
+      for (int j = 0; j < 16; ++j)
+        if (j < nvalid) op[j] = f[j];
+    }
   }
 }
 
@@ -352,7 +253,8 @@ __global__ void __launch_bounds__(kThreads) conv_tc_kernel(const __grid_constant
       uint32_t v[16];
       tmem_ld16(lane_base + (uint32_t)c0, v);
       if (n0 + c0 >= p.Cout) continue;
-      epilogue16(p, v, valid, pb, pix, n0 + c0, p.bb == 1, lane);
+      float f[16];
+      epilogue16(p, v, valid, pb, pix, n0 + c0, f);
     }
   }
   tc_fence_before();
@@ -363,21 +265,16 @@ __global__ void __launch_bounds__(kThreads) conv_tc_kernel(const __grid_constant
   }
 }
 
-// ---- kernel 2: 3x3, halo tiles, persistent CTAs ----------------------------------------------
-// M tile = 8 (x) by 16 (y) output pixels of one image.  Per 64-channel block ONE TMA box
-// (64 ch, 10, 18) brings the tile plus its one-pixel halo: 180 rows of 128 bytes, swizzled.
-// The A operand of tap (dy,dx) is the SAME shared-memory tile read through a descriptor whose
-// start is shifted by ((1+dy)*10 + (1+dx)) rows and whose 8-row groups are 10 rows (1280 B)
-// apart -- every input element is fetched from L2 once per tile instead of nine times.
-// CTAs are persistent over M tiles (static stride); the filter slice of the CTA's N tile stays
-// resident in shared memory when it fits, else it streams through a small ring.  Two TMEM
-// accumulators alternate so the epilogue of tile i overlaps the MMAs of tile i+1.
-constexpr int kHaloW = 10, kHaloH = 18;
-constexpr int kHaloBytes = 23 * 1024;  // 180 rows x 128 B = 23040, padded to a 1024 multiple
-constexpr int kHaloThreads = 256;
+// ---- kernel 2: 8 x 16 pixel tiles with halo, persistent CTAs over contiguous tile ranges ------
+constexpr int kTileW = 8, kTileH = 16;
+constexpr int kCtrlWarps = 4;   // 0: TMA producer, 1: TMEM allocator + MMA issuer, 2-3: idle (the register file
+                                // is allocated in units of 4 warps: 20 warps x 96 registers fill it)
+constexpr int kEpiWarps = 16;   // warp w: TMEM lane quadrant w % 4, output channels [16*((w-4)/4), +16)
+constexpr int kTileThreads = (kCtrlWarps + kEpiWarps) * 32;
 constexpr int kMaxAStages = 4, kMaxWStages = 4;
+constexpr int kTileMaxBN = 64;
 
-__global__ void __launch_bounds__(kHaloThreads, 1) conv_tc_halo_kernel(const __grid_constant__ CUtensorMap mapA,
+__global__ void __launch_bounds__(kTileThreads, 1) conv_tc_tile_kernel(const __grid_constant__ CUtensorMap mapA,
                                                                        const __grid_constant__ CUtensorMap mapW,
                                                                        const ConvTcParams p) {
   extern __shared__ uint8_t smem_raw[];
@@ -385,14 +282,17 @@ __global__ void __launch_bounds__(kHaloThreads, 1) conv_tc_halo_kernel(const __g
   __shared__ __align__(8) uint64_t bar_w_full[kMaxWStages], bar_w_empty[kMaxWStages];
   __shared__ __align__(8) uint64_t bar_w_res, bar_acc_full[2], bar_acc_empty[2];
   __shared__ uint32_t tmem_base_slot;
+  __shared__ float red[4][kTileMaxBN][2];  // per-quadrant channel sums at a statistics flush
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const uint32_t base = (smem_u32(smem_raw) + 1023u) & ~1023u;
   const uint32_t w_tile_bytes = (uint32_t)p.BN * 128u;
-  const int n_wtiles = p.w_resident ? p.chunks * 9 : p.w_stages;
-  const uint32_t a_ring = base + (uint32_t)n_wtiles * w_tile_bytes;  // stays 1024-aligned (BN % 16 == 0)
+  const int n_wtiles = p.w_resident ? p.chunks * p.taps : p.w_stages;
+  const uint32_t a_ring = (base + (uint32_t)n_wtiles * w_tile_bytes + 1023u) & ~1023u;
   const int n0 = blockIdx.y * p.BN;
-  const int my_tiles = (p.num_tiles - (int)blockIdx.x + (int)gridDim.x - 1) / (int)gridDim.x;
+  const int t0 = (int)((int64_t)blockIdx.x * p.num_tiles / gridDim.x);
+  const int t1 = (int)((int64_t)(blockIdx.x + 1) * p.num_tiles / gridDim.x);
+  const int my_tiles = t1 - t0;
 
   if (threadIdx.x == 0) {
     for (int s = 0; s < kMaxAStages; ++s) {
@@ -406,11 +306,11 @@ __global__ void __launch_bounds__(kHaloThreads, 1) conv_tc_halo_kernel(const __g
     mbar_init(smem_u32(&bar_w_res), 1);
     for (int s = 0; s < 2; ++s) {
       mbar_init(smem_u32(&bar_acc_full[s]), 1);
-      mbar_init(smem_u32(&bar_acc_empty[s]), 4);  // one arrival per epilogue warp
+      mbar_init(smem_u32(&bar_acc_empty[s]), kEpiWarps);  // one arrival per epilogue warp
     }
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
-  if (warp == 2) tmem_alloc(smem_u32(&tmem_base_slot), (uint32_t)p.tmem_cols);
+  if (warp == 1) tmem_alloc(smem_u32(&tmem_base_slot), (uint32_t)p.tmem_cols);
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
@@ -422,26 +322,26 @@ __global__ void __launch_bounds__(kHaloThreads, 1) conv_tc_halo_kernel(const __g
       asm volatile("prefetch.tensormap [%0];" ::"l"(&mapW) : "memory");
       if (p.w_resident) {
         const uint32_t bar = smem_u32(&bar_w_res);
-        mbar_expect_tx(bar, (uint32_t)(p.chunks * 9) * w_tile_bytes);
+        mbar_expect_tx(bar, (uint32_t)(p.chunks * p.taps) * w_tile_bytes);
         for (int ch = 0; ch < p.chunks; ++ch)
-          for (int tap = 0; tap < 9; ++tap)
-            tma_load_2d(base + (uint32_t)(ch * 9 + tap) * w_tile_bytes, &mapW, bar, tap * p.Cin + ch * kBlockK, n0);
+          for (int tap = 0; tap < p.taps; ++tap)
+            tma_load_2d(base + (uint32_t)(ch * p.taps + tap) * w_tile_bytes, &mapW, bar, tap * p.Cin + ch * kBlockK, n0);
       }
       uint32_t ia = 0, iw = 0;  // running A-block / W-tile counters (ring position + phase)
       for (int it = 0; it < my_tiles; ++it) {
-        int mt = (int)blockIdx.x + it * (int)gridDim.x;
-        const int tx = mt % p.tiles_x;
-        mt /= p.tiles_x;
-        const int ty = mt % p.tiles_y;
-        const int b = mt / p.tiles_y;
+        const int mt = t0 + it;
+        const int b = mt / p.tiles_per_image;
+        const int rem = mt - b * p.tiles_per_image;
+        const int ty = rem / p.tiles_x, tx = rem - ty * p.tiles_x;
         for (int ch = 0; ch < p.chunks; ++ch, ++ia) {
           const int sa = (int)(ia % (uint32_t)p.a_stages);
           mbar_wait(smem_u32(&bar_a_empty[sa]), ((ia / (uint32_t)p.a_stages) & 1u) ^ 1u);
           const uint32_t full = smem_u32(&bar_a_full[sa]);
-          mbar_expect_tx(full, (uint32_t)(kHaloW * kHaloH * 128));
-          tma_load_4d(a_ring + (uint32_t)sa * kHaloBytes, &mapA, full, ch * kBlockK, tx * 8 - 1, ty * 16 - 1, b);
+          mbar_expect_tx(full, (uint32_t)(p.a_rows * 128));
+          tma_load_4d(a_ring + (uint32_t)(sa * p.a_stage_bytes), &mapA, full, ch * kBlockK, tx * kTileW - p.halo,
+                      ty * kTileH - p.halo, b);
           if (!p.w_resident) {
-            for (int tap = 0; tap < 9; ++tap, ++iw) {
+            for (int tap = 0; tap < p.taps; ++tap, ++iw) {
               const int sw = (int)(iw % (uint32_t)p.w_stages);
               mbar_wait(smem_u32(&bar_w_empty[sw]), ((iw / (uint32_t)p.w_stages) & 1u) ^ 1u);
               const uint32_t wfull = smem_u32(&bar_w_full[sw]);
@@ -456,8 +356,10 @@ __global__ void __launch_bounds__(kHaloThreads, 1) conv_tc_halo_kernel(const __g
     if (lane == 0) {
       const uint32_t idesc = (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(p.BN >> 3) << 17) |
                              ((uint32_t)(kTileM >> 4) << 24);
-      // A: rows 128 B apart inside a group of 8 output pixels (one tile row), groups 10 rows apart
-      const uint64_t a_hi = (1ull << 16) | ((uint64_t)(kHaloW * 128 >> 4) << 32) | (1ull << 46) | (2ull << 61);
+      // A: rows 128 B apart inside a group of 8 output pixels (one tile row), groups row_pitch rows apart.
+      // The swizzle is keyed on absolute shared-memory address bits, so a row-shifted start needs no
+      // base offset (measured: tests/test_gpu_kernels.py::test_conv_tc_halo_descriptor_probe).
+      const uint64_t a_hi = (1ull << 16) | ((uint64_t)((p.row_pitch * 128) >> 4) << 32) | (1ull << 46) | (2ull << 61);
       if (p.w_resident) {
         mbar_wait(smem_u32(&bar_w_res), 0);
         tc_fence_after();
@@ -472,12 +374,12 @@ __global__ void __launch_bounds__(kHaloThreads, 1) conv_tc_halo_kernel(const __g
           const int sa = (int)(ia % (uint32_t)p.a_stages);
           mbar_wait(smem_u32(&bar_a_full[sa]), (ia / (uint32_t)p.a_stages) & 1u);
           tc_fence_after();
-          const uint32_t a_buf = a_ring + (uint32_t)sa * kHaloBytes;
-          for (int tap = 0; tap < 9; ++tap) {
+          const uint32_t a_buf = a_ring + (uint32_t)(sa * p.a_stage_bytes);
+          for (int tap = 0; tap < p.taps; ++tap) {
             uint32_t w_addr;
             int sw = 0;
             if (p.w_resident) {
-              w_addr = base + (uint32_t)(ch * 9 + tap) * w_tile_bytes;
+              w_addr = base + (uint32_t)(ch * p.taps + tap) * w_tile_bytes;
             } else {
               sw = (int)(iw % (uint32_t)p.w_stages);
               mbar_wait(smem_u32(&bar_w_full[sw]), (iw / (uint32_t)p.w_stages) & 1u);
@@ -485,10 +387,9 @@ __global__ void __launch_bounds__(kHaloThreads, 1) conv_tc_halo_kernel(const __g
               w_addr = base + (uint32_t)sw * w_tile_bytes;
               ++iw;
             }
-            const int dy = tap / 3, dx = tap % 3;  // already offset by the halo origin (-1, -1)
-            const uint32_t a_start = a_buf + (uint32_t)((dy * kHaloW + dx) * 128);
-            uint64_t da = a_hi | (uint64_t)((a_start >> 4) & 0x3FFF);
-            if (p.base_off_mode == 1) da |= (uint64_t)((a_start >> 7) & 7u) << 49;
+            const int dy = tap / p.ksize, dx = tap - dy * p.ksize;  // already offset by the halo origin
+            const uint32_t a_start = a_buf + (uint32_t)((dy * p.row_pitch + dx) * 128);
+            const uint64_t da = a_hi | (uint64_t)((a_start >> 4) & 0x3FFF);
             const uint64_t db = make_sw128_desc(w_addr);
 #pragma unroll
             for (int k = 0; k < kBlockK / 16; ++k)
@@ -500,39 +401,93 @@ __global__ void __launch_bounds__(kHaloThreads, 1) conv_tc_halo_kernel(const __g
         umma_commit(smem_u32(&bar_acc_full[ab]));
       }
     }
-  } else if (warp >= 4) {
-    const int q = warp & 3;
+  } else if (warp >= kCtrlWarps) {
+    const int e = warp - kCtrlWarps;
+    const int q = warp & 3;            // TMEM lane quadrant this warp may read
+    const int c0 = (e >> 2) * 16;      // its 16 output channels inside the N tile
+    const bool active = c0 < p.BN && n0 + c0 < p.Cout;
     const int r = q * 32 + lane;
     const int xo = r & 7, yo = r >> 3;
+    const int etid = e * 32 + lane;    // 0..511
+    float s[16], sq[16];
+#pragma unroll
+    for (int j = 0; j < 16; ++j) s[j] = sq[j] = 0.f;
+    int cur_b = -1, flush_idx = 0;
+
+    auto flush = [&]() {
+      // warp-level transpose-reduce: after offsets 16, 8, 4, 2 lane l holds channel
+      // c = 8*b4 + 4*b3 + 2*b2 + b1 (bits of l) summed over 16 lanes; offset 1 completes it
+#pragma unroll
+      for (int step = 0; step < 4; ++step) {
+        const int off = 16 >> step, half = 8 >> step;
+        const bool upper = (lane & off) != 0;
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+          if (j < half) {
+            const float send_s = upper ? s[j] : s[j + half], send_q = upper ? sq[j] : sq[j + half];
+            const float keep_s = upper ? s[j + half] : s[j], keep_q = upper ? sq[j + half] : sq[j];
+            s[j] = keep_s + __shfl_xor_sync(0xffffffffu, send_s, off);
+            sq[j] = keep_q + __shfl_xor_sync(0xffffffffu, send_q, off);
+          }
+        }
+      }
+      s[0] += __shfl_xor_sync(0xffffffffu, s[0], 1);
+      sq[0] += __shfl_xor_sync(0xffffffffu, sq[0], 1);
+      const int c = ((lane >> 4) & 1) * 8 + ((lane >> 3) & 1) * 4 + ((lane >> 2) & 1) * 2 + ((lane >> 1) & 1);
+      if ((lane & 1) == 0 && c0 < p.BN) {
+        red[q][c0 + c][0] = s[0];
+        red[q][c0 + c][1] = sq[0];
+      }
+      named_bar_sync(1, kEpiWarps * 32);
+      if (etid < 2 * p.BN) {
+        const int ch = etid >> 1, k = etid & 1;
+        const float v = (red[0][ch][k] + red[1][ch][k]) + (red[2][ch][k] + red[3][ch][k]);
+        p.stats[(((int64_t)blockIdx.x * p.maxf + flush_idx) * p.ld_part + n0 + ch) * 2 + k] = v;
+      }
+      named_bar_sync(1, kEpiWarps * 32);
+#pragma unroll
+      for (int j = 0; j < 16; ++j) s[j] = sq[j] = 0.f;
+      ++flush_idx;
+    };
+
     for (int it = 0; it < my_tiles; ++it) {
-      int mt = (int)blockIdx.x + it * (int)gridDim.x;
-      const int tx = mt % p.tiles_x;
-      mt /= p.tiles_x;
-      const int ty = mt % p.tiles_y;
-      const int pb = mt / p.tiles_y;
-      const int px = tx * 8 + xo, py = ty * 16 + yo;
+      const int mt = t0 + it;
+      const int pb = mt / p.tiles_per_image;
+      const int rem = mt - pb * p.tiles_per_image;
+      const int ty = rem / p.tiles_x, tx = rem - ty * p.tiles_x;
+      if (pb != cur_b) {
+        if (cur_b >= 0 && p.stats) flush();
+        cur_b = pb;
+      }
+      const int px = tx * kTileW + xo, py = ty * kTileH + yo;
       const bool valid = px < p.W && py < p.H;
       const int64_t pix = ((int64_t)pb * p.H + py) * p.W + px;
       const int ab = it & 1;
       mbar_wait(smem_u32(&bar_acc_full[ab]), ((uint32_t)it >> 1) & 1u);
       tc_fence_after();
-      const uint32_t lane_base = tmem_acc + ((uint32_t)(q * 32) << 16) + (uint32_t)(ab * p.BN);
-      for (int c0 = 0; c0 < p.BN; c0 += 16) {
-        uint32_t v[16];
-        tmem_ld16(lane_base + (uint32_t)c0, v);
-        if (c0 + 16 >= p.BN) {  // last TMEM read of this tile: hand the accumulator back
-          tc_fence_before();
-          __syncwarp();
-          if (lane == 0) asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(&bar_acc_empty[ab])) : "memory");
+      uint32_t v[16];
+      if (c0 < p.BN) tmem_ld16(tmem_acc + ((uint32_t)(q * 32) << 16) + (uint32_t)(ab * p.BN + c0), v);
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(smem_u32(&bar_acc_empty[ab]));  // accumulator handed back
+      if (active) {
+        float f[16];
+        epilogue16(p, v, valid, pb, pix, n0 + c0, f);
+        if (p.stats) {
+#pragma unroll
+          for (int j = 0; j < 16; ++j) {
+            s[j] += f[j];
+            sq[j] = fmaf(f[j], f[j], sq[j]);
+          }
         }
-        if (n0 + c0 >= p.Cout) continue;
-        epilogue16(p, v, valid, pb, pix, n0 + c0, true, lane);
       }
     }
+    if (p.stats && cur_b >= 0) flush();
   }
   tc_fence_before();
   __syncthreads();
-  if (warp == 2) {
+  if (warp == 1) {
+    __syncwarp();
     tc_fence_after();
     tmem_dealloc(tmem_acc, (uint32_t)p.tmem_cols);
   }
@@ -570,7 +525,7 @@ struct ditsep_conv_plan {
   CUtensorMap mapA, mapW;
   ConvTcParams p;
   size_t smem;
-  int halo;      // 1 = conv_tc_halo_kernel
+  int tile;      // 1 = conv_tc_tile_kernel
   int grid_x;
 };
 
@@ -620,55 +575,68 @@ extern "C" int ditsep_conv_tc_plan_create(ditsep_conv_plan** plan, const void* i
   const int num_kb = p.taps * (Cin / kBlockK);
   if (p.stages > num_kb) p.stages = num_kb;
 
-  // ---- halo mode: 3x3 on images of at least one 8 x 16 tile (DITSEP_CONV_MODE=tap disables it)
+  // ---- tile kernel: images of at least one 8 x 16 tile, N tiles of at most 64 channels
+  // (DITSEP_CONV_MODE=tap forces the per-tap kernel: debug aid)
   const char* mode_env = getenv("DITSEP_CONV_MODE");
-  int halo = (ksize == 3 && W >= 8 && H >= 16 && !(mode_env && strcmp(mode_env, "tap") == 0)) ? 1 : 0;
+  int tile = (W >= kTileW && H >= kTileH && (cout_pad <= kTileMaxBN || cout_pad % kTileMaxBN == 0) &&
+              !(mode_env && strcmp(mode_env, "tap") == 0)) ? 1 : 0;
   size_t smem = 1024 + (size_t)p.stages * stage_bytes;
   int grid_x = 0;
-  if (halo) {
-    const char* bo = getenv("DITSEP_TC_BASEOFF");
-    p.base_off_mode = bo ? atoi(bo) : 0;
+  if (tile) {
+    p.halo = ksize / 2;
+    p.row_pitch = kTileW + 2 * p.halo;
+    p.a_rows = p.row_pitch * (kTileH + 2 * p.halo);
+    p.a_stage_bytes = (p.a_rows * 128 + 1023) / 1024 * 1024;
     p.chunks = Cin / kBlockK;
-    p.tiles_x = ceil_div(W, 8);
-    p.tiles_y = ceil_div(H, 16);
+    p.tiles_x = ceil_div(W, kTileW);
+    p.tiles_y = ceil_div(H, kTileH);
     p.tiles_b = B;
-    p.num_tiles = p.tiles_x * p.tiles_y * B;
-    p.bw = 8; p.bh = 16; p.bb = 1;
-    if (p.BN > 64 && cout_pad % 64 == 0) p.BN = 64;  // more M tiles per resident filter byte
+    p.tiles_per_image = p.tiles_x * p.tiles_y;
+    p.num_tiles = p.tiles_per_image * B;
+    p.bw = kTileW; p.bh = kTileH; p.bb = 1;
+    if (cout_pad > kTileMaxBN) p.BN = kTileMaxBN;
     p.n_tiles = ceil_div(cout_pad, p.BN);
+    p.ld_part = p.n_tiles * p.BN;
     p.tmem_cols = pow2_ceil(2 * p.BN) < 32 ? 32 : pow2_ceil(2 * p.BN);
     const size_t w_tile = (size_t)p.BN * 128;
-    const size_t budget = 225 * 1024 - 1024;
-    const size_t w_all = (size_t)p.chunks * 9 * w_tile;
-    p.a_stages = p.chunks >= 2 ? 3 : 3;
-    if (w_all + (size_t)2 * kHaloBytes <= budget) {
+    const size_t budget = 222 * 1024;  // dynamic; static (barriers + reduction scratch) is ~2.3 KB
+    const size_t w_all = (size_t)p.chunks * p.taps * w_tile;
+    if (w_all + 2 * (size_t)p.a_stage_bytes + 2048 <= budget) {
       p.w_resident = 1;
       p.w_stages = 0;
-      while (p.a_stages > 2 && w_all + (size_t)p.a_stages * kHaloBytes > budget) --p.a_stages;
-      smem = 1024 + w_all + (size_t)p.a_stages * kHaloBytes;
+      p.a_stages = kMaxAStages;
+      while (p.a_stages > 2 && w_all + (size_t)p.a_stages * p.a_stage_bytes + 2048 > budget) --p.a_stages;
+      smem = 2048 + w_all + (size_t)p.a_stages * p.a_stage_bytes;
     } else {
       p.w_resident = 0;
-      p.w_stages = 4;
-      p.a_stages = 4;
-      smem = 1024 + (size_t)p.w_stages * w_tile + (size_t)p.a_stages * kHaloBytes;
+      p.w_stages = kMaxWStages;
+      p.a_stages = kMaxAStages;
+      smem = 2048 + (size_t)p.w_stages * w_tile + (size_t)p.a_stages * p.a_stage_bytes;
     }
     int dev = 0, sms = kNumSMs;
     if (cudaGetDevice(&dev) == cudaSuccess) cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
     grid_x = sms / p.n_tiles;
     if (grid_x < 1) grid_x = 1;
     if (grid_x > p.num_tiles) grid_x = p.num_tiles;
+    // most images any CTA's contiguous tile range touches (= statistics flushes per CTA)
+    p.maxf = 1;
+    for (int c = 0; c < grid_x; ++c) {
+      const int64_t a = (int64_t)c * p.num_tiles / grid_x, b = (int64_t)(c + 1) * p.num_tiles / grid_x;
+      const int n = (int)((b - 1) / p.tiles_per_image - a / p.tiles_per_image) + 1;
+      if (n > p.maxf) p.maxf = n;
+    }
   }
 
   ditsep_conv_plan* pl = new ditsep_conv_plan();
   pl->p = p;
   pl->smem = smem;
-  pl->halo = halo;
+  pl->tile = tile;
   pl->grid_x = grid_x;
   {
     cuuint64_t gdim[4] = {(cuuint64_t)Cin, (cuuint64_t)W, (cuuint64_t)H, (cuuint64_t)B};
     cuuint64_t gstr[3] = {(cuuint64_t)ld_in * 2, (cuuint64_t)W * ld_in * 2, (cuuint64_t)H * W * ld_in * 2};
     cuuint32_t box[4] = {(cuuint32_t)kBlockK, (cuuint32_t)p.bw, (cuuint32_t)p.bh, (cuuint32_t)p.bb};
-    if (halo) { box[1] = kHaloW; box[2] = kHaloH; box[3] = 1; }
+    if (tile) { box[1] = (cuuint32_t)p.row_pitch; box[2] = (cuuint32_t)(kTileH + 2 * p.halo); box[3] = 1; }
     cuuint32_t estr[4] = {1, 1, 1, 1};
     CUresult r = encode(&pl->mapA, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 4, const_cast<void*>(in), gdim, gstr, box, estr,
                         CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
@@ -696,7 +664,7 @@ extern "C" int ditsep_conv_tc_plan_create(ditsep_conv_plan** plan, const void* i
   if (!attr_set) {
     DITSEP_CUDA(cudaFuncSetAttribute(conv_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                      1024 + kMaxStages * (kABytes + 128 * 128)));
-    DITSEP_CUDA(cudaFuncSetAttribute(conv_tc_halo_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 225 * 1024));
+    DITSEP_CUDA(cudaFuncSetAttribute(conv_tc_tile_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 224 * 1024));
     attr_set = true;
   }
   *plan = pl;
@@ -705,23 +673,37 @@ extern "C" int ditsep_conv_tc_plan_create(ditsep_conv_plan** plan, const void* i
 
 extern "C" void ditsep_conv_tc_plan_destroy(ditsep_conv_plan* plan) { delete plan; }
 
+extern "C" int ditsep_conv_tc_stats_layout(const ditsep_conv_plan* plan, ditsep_stats_src* layout) {
+  DITSEP_REQUIRE(plan && layout, "conv_tc_stats_layout: null pointer");
+  memset(layout, 0, sizeof(*layout));
+  if (!plan->tile) return 0;  // kind stays DITSEP_STATS_NONE: this plan cannot produce statistics
+  layout->kind = DITSEP_STATS_CONV_PARTIALS;
+  layout->C = plan->p.Cout;
+  layout->ld = plan->p.ld_part;
+  layout->n_part = plan->grid_x;
+  layout->maxf = plan->p.maxf;
+  layout->tiles_per_image = plan->p.tiles_per_image;
+  layout->num_tiles = plan->p.num_tiles;
+  return 0;
+}
+
 extern "C" int ditsep_conv_tc_run(const ditsep_conv_plan* plan, const float* bias, const float* bias_b, int ld_bias_b,
                                   const void* residual, int res_dtype, int ld_res, float out_scale, void* out,
-                                  int out_dtype, int ld_out, float* stats, int ld_stats, void* stream) {
+                                  int out_dtype, int ld_out, float* stats, void* stream) {
   DITSEP_REQUIRE(plan && out, "conv_tc_run: null pointer");
   DITSEP_REQUIRE(out_dtype == DITSEP_F32 || out_dtype == DITSEP_BF16, "conv_tc_run: unknown out dtype %d", out_dtype);
   DITSEP_REQUIRE(!residual || res_dtype == DITSEP_F32 || res_dtype == DITSEP_BF16, "conv_tc_run: unknown residual dtype");
   DITSEP_REQUIRE(ld_out >= plan->p.Cout, "conv_tc_run: ld_out=%d < Cout=%d", ld_out, plan->p.Cout);
-  DITSEP_REQUIRE(!stats || ld_stats >= plan->p.Cout, "conv_tc_run: ld_stats=%d < Cout=%d", ld_stats, plan->p.Cout);
+  DITSEP_REQUIRE(!stats || plan->tile, "conv_tc_run: this plan (image smaller than one 8x16 tile) cannot produce statistics");
   ConvTcParams p = plan->p;
   p.bias = bias; p.bias_b = bias_b; p.ld_bias_b = ld_bias_b;
   p.residual = residual; p.res_dtype = res_dtype; p.ld_res = ld_res;
   p.out_scale = out_scale; p.out = out; p.out_dtype = out_dtype; p.ld_out = ld_out;
-  p.stats = stats; p.ld_stats = ld_stats;
-  if (plan->halo) {
+  p.stats = stats;
+  if (plan->tile) {
     dim3 grid((unsigned)plan->grid_x, (unsigned)p.n_tiles);
-    conv_tc_halo_kernel<<<grid, kHaloThreads, plan->smem, (cudaStream_t)stream>>>(plan->mapA, plan->mapW, p);
-    return check_launch("conv_tc_halo_kernel");
+    conv_tc_tile_kernel<<<grid, kTileThreads, plan->smem, (cudaStream_t)stream>>>(plan->mapA, plan->mapW, p);
+    return check_launch("conv_tc_tile_kernel");
   }
   dim3 grid((unsigned)((int64_t)p.tiles_x * p.tiles_y * p.tiles_b), (unsigned)p.n_tiles);
   conv_tc_kernel<<<grid, kThreads, plan->smem, (cudaStream_t)stream>>>(plan->mapA, plan->mapW, p);

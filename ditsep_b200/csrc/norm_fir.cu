@@ -99,35 +99,77 @@ __global__ void __launch_bounds__(256) gn_finalize_kernel(const float* __restric
   }
 }
 
-// Per-channel {sum, sum of squares} accumulated by the producing convolution's epilogue
-// (stats: [B][ld_stats][2]) -> per-(b,c) scale / shift.  grid B, block 256.
-__global__ void __launch_bounds__(256) gn_finalize_sums_kernel(const float* __restrict__ stats, int ld_stats, int64_t HW,
-                                                               int C, int G, const float* __restrict__ gamma,
+// Per-channel {sum, sum of squares} left by the producers of the normalised tensor (up to 4
+// sources laid end to end along the channel axis, see ditsep_stats_src) -> per-(b,c) scale / shift.
+// grid B, block 256.  Fixed summation order, double accumulation.
+struct StatsSrcs {
+  ditsep_stats_src s[4];
+  int n;
+};
+
+__device__ __forceinline__ void stats_channel_sum(const ditsep_stats_src& src, int b, int c, double& a, double& q) {
+  a = 0.0;
+  q = 0.0;
+  if (src.kind == DITSEP_STATS_SPLIT_SUMS) {
+    for (int sidx = 0; sidx < src.n_part; ++sidx) {
+      const float* v = src.ptr + (((int64_t)b * src.n_part + sidx) * src.ld + c) * 2;
+      a += (double)v[0];
+      q += (double)v[1];
+    }
+  } else {  // DITSEP_STATS_CONV_PARTIALS: CTA k covered tiles [k*T/n, (k+1)*T/n)
+    const int64_t T = src.num_tiles, tpi = src.tiles_per_image;
+    const int64_t lo = (int64_t)b * tpi, hi = lo + tpi;
+    for (int k = 0; k < src.n_part; ++k) {
+      const int64_t t0 = (int64_t)k * T / src.n_part, t1 = (int64_t)(k + 1) * T / src.n_part;
+      if (t1 <= lo || t0 >= hi || t1 <= t0) continue;
+      const int f = b - (int)(t0 / tpi);
+      const float* v = src.ptr + (((int64_t)k * src.maxf + f) * src.ld + c) * 2;
+      a += (double)v[0];
+      q += (double)v[1];
+    }
+  }
+}
+
+__global__ void __launch_bounds__(256) gn_finalize_srcs_kernel(const StatsSrcs srcs, int64_t HW, int C, int G,
+                                                               const float* __restrict__ gamma,
                                                                const float* __restrict__ beta, float eps,
                                                                float* __restrict__ scale_shift) {
-  extern __shared__ double sh[];  // [G][2]
+  extern __shared__ double sh[];  // [C][2] then [G][2]
+  double* chs = sh;
+  double* grp = sh + 2 * C;
   const int b = blockIdx.x;
+  for (int c = threadIdx.x; c < C; c += blockDim.x) {
+    int cc = c, i = 0;
+    while (i < srcs.n - 1 && cc >= srcs.s[i].C) {
+      cc -= srcs.s[i].C;
+      ++i;
+    }
+    double a, q;
+    stats_channel_sum(srcs.s[i], b, cc, a, q);
+    chs[2 * c] = a;
+    chs[2 * c + 1] = q;
+  }
+  __syncthreads();
   const int cpg = C / G;
   for (int g = threadIdx.x; g < G; g += blockDim.x) {
     double a = 0.0, q = 0.0;
     for (int i = 0; i < cpg; ++i) {
-      const float* src = stats + ((int64_t)b * ld_stats + g * cpg + i) * 2;
-      a += (double)src[0];
-      q += (double)src[1];
+      a += chs[2 * (g * cpg + i)];
+      q += chs[2 * (g * cpg + i) + 1];
     }
     const double n = (double)HW * cpg;
     const double mean = a / n;
     double var = q / n - mean * mean;
     if (var < 0.0) var = 0.0;
-    sh[2 * g] = mean;
-    sh[2 * g + 1] = 1.0 / sqrt(var + (double)eps);
+    grp[2 * g] = mean;
+    grp[2 * g + 1] = 1.0 / sqrt(var + (double)eps);
   }
   __syncthreads();
   for (int c = threadIdx.x; c < C; c += blockDim.x) {
     const int g = c / cpg;
-    const double sc = sh[2 * g + 1] * (double)gamma[c];
+    const double sc = grp[2 * g + 1] * (double)gamma[c];
     scale_shift[((int64_t)b * 2) * C + c] = (float)sc;
-    scale_shift[((int64_t)b * 2 + 1) * C + c] = (float)((double)beta[c] - sh[2 * g] * sc);
+    scale_shift[((int64_t)b * 2 + 1) * C + c] = (float)((double)beta[c] - grp[2 * g] * sc);
   }
 }
 
@@ -416,17 +458,14 @@ static int grid_for(int64_t total, int threads = 256) {
 
 using namespace ditsep;
 
-extern "C" int ditsep_gn_stats(const void* x, int dtype, int B, int64_t HW, int C, int ld, int G, const float* gamma,
-                               const float* beta, float eps, float* partial, int nsplit, float* scale_shift,
-                               void* stream) {
-  DITSEP_REQUIRE(x && gamma && beta && partial && scale_shift, "gn_stats: null pointer");
-  DITSEP_REQUIRE(C % 8 == 0 && ld % 8 == 0 && C <= ld, "gn_stats: C=%d ld=%d must be multiples of 8, C<=ld", C, ld);
-  DITSEP_REQUIRE(G > 0 && C % G == 0, "gn_stats: C=%d not divisible by G=%d", C, G);
-  DITSEP_REQUIRE(B > 0 && HW > 0 && nsplit > 0 && nsplit <= HW, "gn_stats: bad B/HW/nsplit");
+static int launch_gn_partial(const void* x, int dtype, int B, int64_t HW, int C, int ld, float* partial, int nsplit,
+                             cudaStream_t st) {
+  DITSEP_REQUIRE(x && partial, "gn partial sums: null pointer");
+  DITSEP_REQUIRE(C % 8 == 0 && ld % 8 == 0 && C <= ld, "gn partial sums: C=%d ld=%d must be multiples of 8, C<=ld", C, ld);
+  DITSEP_REQUIRE(B > 0 && HW > 0 && nsplit > 0 && nsplit <= HW, "gn partial sums: bad B/HW/nsplit");
   const int cv = C / 8;
-  DITSEP_REQUIRE(cv <= 256, "gn_stats: C=%d too wide", C);
+  DITSEP_REQUIRE(cv <= 256, "gn partial sums: C=%d too wide", C);
   const int ppb = 256 / cv;
-  cudaStream_t st = (cudaStream_t)stream;
   dim3 grid(nsplit, B);
   size_t smem = (size_t)ppb * C * 2 * sizeof(float);
   if (dtype == DITSEP_F32)
@@ -434,21 +473,48 @@ extern "C" int ditsep_gn_stats(const void* x, int dtype, int B, int64_t HW, int 
   else if (dtype == DITSEP_BF16)
     gn_partial_kernel<bf16><<<grid, 256, smem, st>>>((const bf16*)x, HW, C, ld, cv, ppb, partial);
   else
-    DITSEP_REQUIRE(false, "gn_stats: unknown dtype %d", dtype);
-  if (int rc = check_launch("gn_partial_kernel")) return rc;
+    DITSEP_REQUIRE(false, "gn partial sums: unknown dtype %d", dtype);
+  return check_launch("gn_partial_kernel");
+}
+
+extern "C" int ditsep_gn_partial_sums(const void* x, int dtype, int B, int64_t HW, int C, int ld, float* partial,
+                                      int nsplit, void* stream) {
+  return launch_gn_partial(x, dtype, B, HW, C, ld, partial, nsplit, (cudaStream_t)stream);
+}
+
+extern "C" int ditsep_gn_stats(const void* x, int dtype, int B, int64_t HW, int C, int ld, int G, const float* gamma,
+                               const float* beta, float eps, float* partial, int nsplit, float* scale_shift,
+                               void* stream) {
+  DITSEP_REQUIRE(gamma && beta && scale_shift, "gn_stats: null pointer");
+  DITSEP_REQUIRE(G > 0 && C % G == 0, "gn_stats: C=%d not divisible by G=%d", C, G);
+  cudaStream_t st = (cudaStream_t)stream;
+  if (int rc = launch_gn_partial(x, dtype, B, HW, C, ld, partial, nsplit, st)) return rc;
   gn_finalize_kernel<<<B, 256, (size_t)(2 * C + 2 * G) * sizeof(double), st>>>(partial, nsplit, HW, C, G, gamma, beta,
                                                                                 eps, scale_shift);
   return check_launch("gn_finalize_kernel");
 }
 
-extern "C" int ditsep_gn_finalize(const float* stats, int ld_stats, int B, int64_t HW, int C, int G, const float* gamma,
-                                  const float* beta, float eps, float* scale_shift, void* stream) {
-  DITSEP_REQUIRE(stats && gamma && beta && scale_shift, "gn_finalize: null pointer");
-  DITSEP_REQUIRE(B > 0 && HW > 0 && G > 0 && C % G == 0 && ld_stats >= C, "gn_finalize: bad sizes C=%d G=%d ld=%d", C, G,
-                 ld_stats);
-  gn_finalize_sums_kernel<<<B, 256, (size_t)2 * G * sizeof(double), (cudaStream_t)stream>>>(stats, ld_stats, HW, C, G,
-                                                                                            gamma, beta, eps, scale_shift);
-  return check_launch("gn_finalize_sums_kernel");
+extern "C" int ditsep_gn_finalize(const ditsep_stats_src* host_srcs, int n_srcs, int B, int64_t HW, int G,
+                                  const float* gamma, const float* beta, float eps, float* scale_shift, void* stream) {
+  DITSEP_REQUIRE(host_srcs && gamma && beta && scale_shift, "gn_finalize: null pointer");
+  DITSEP_REQUIRE(n_srcs >= 1 && n_srcs <= 4, "gn_finalize: n_srcs=%d (1..4)", n_srcs);
+  StatsSrcs srcs;
+  srcs.n = n_srcs;
+  int C = 0;
+  for (int i = 0; i < n_srcs; ++i) {
+    const ditsep_stats_src& s = host_srcs[i];
+    DITSEP_REQUIRE(s.ptr && (s.kind == DITSEP_STATS_CONV_PARTIALS || s.kind == DITSEP_STATS_SPLIT_SUMS),
+                   "gn_finalize: source %d has no statistics (kind %d)", i, s.kind);
+    DITSEP_REQUIRE(s.C > 0 && s.ld >= s.C && s.n_part > 0, "gn_finalize: source %d: bad C/ld/n_part", i);
+    DITSEP_REQUIRE(s.kind != DITSEP_STATS_CONV_PARTIALS || (s.maxf > 0 && s.tiles_per_image > 0 && s.num_tiles > 0),
+                   "gn_finalize: source %d: bad conv-partials layout", i);
+    srcs.s[i] = s;
+    C += s.C;
+  }
+  DITSEP_REQUIRE(B > 0 && HW > 0 && G > 0 && C % G == 0, "gn_finalize: bad sizes C=%d G=%d", C, G);
+  gn_finalize_srcs_kernel<<<B, 256, (size_t)(2 * C + 2 * G) * sizeof(double), (cudaStream_t)stream>>>(
+      srcs, HW, C, G, gamma, beta, eps, scale_shift);
+  return check_launch("gn_finalize_srcs_kernel");
 }
 
 extern "C" int ditsep_gn_apply(const void* x, int dtype, int B, int64_t HW, int C, int ld_x, const float* scale_shift,

@@ -232,8 +232,11 @@ class _Plan:
         self.act_temb = new(B, 4 * nf, dtype=f32)
         self.dense = new(B, w["dense_rows"], dtype=f32)
         cmax = max(max(s.in_ch, s.out_ch) for s in m.layout)
-        self.gn_partial = new((4 * ops.NUM_SMS + B) * cmax * 2 * 2, dtype=f32)
+        self.gn_partial = new(B * 64 * cmax * 2, dtype=f32)  # scratch of the unfused statistics pass
         self._tc_plans = []
+        # (data_ptr, channels) of a produced NHWC view -> (statistics buffer, layout): where its producer
+        # left the per-channel sums GroupNorm needs (conv epilogue partials, or an explicit pass)
+        self.stat_src: Dict[Tuple[int, int], Tuple[torch.Tensor, object]] = {}
         add = self.steps.append
 
         # ---- time embedding (ncsnpp.py:325-346) + every res-block's Dense_0 (layerspp.py:316-317)
@@ -279,7 +282,7 @@ class _Plan:
         pyr_in = self.feat
         k = 0
         cur = skip_slot(k)
-        self._conv(self.feat, w["conv3"], cur)
+        self._conv(self.feat, w["conv3"], cur, want_stats=True)
         k += 1
         i = 4
         for lvl in range(R):
@@ -308,7 +311,7 @@ class _Plan:
                 add((ops.fir_resample, (pyr_in, False), {"out_x": nxt}))
                 pyr_in = nxt
                 # Combine "sum" (layerspp.py:57-62): dst = Conv_0(pyramid) + dst
-                self._conv(pyr_in, w[f"conv{i + 1}"], dst, residual=dst)
+                self._conv(pyr_in, w[f"conv{i + 1}"], dst, residual=dst, want_stats=True)
                 i += 2
                 cur = dst
                 k += 1
@@ -349,9 +352,7 @@ class _Plan:
                 i += 1
             # progressive output skip: GN -> SiLU -> conv3x3(C -> Cin0), summed over levels
             cch = layout[i].in_ch
-            ss = new(B, 2, cch, dtype=f32)
-            g = w[f"gn{i}"]
-            add((ops.gn_stats, (cur, min(cch // 4, 32), g[0], g[1], 1e-6, self.gn_partial, ss), {}))
+            ss = self._scale_shift(cur, w[f"gn{i}"])
             hact = pool.get((B, hh, ww, cch), adt)
             add((ops.gn_apply, (cur, ss, True, hact), {}))
             i += 1
@@ -375,26 +376,63 @@ class _Plan:
         add((ops.output_layer, (pyramid, self.t, w["out_w"], w["out_b"], self.out, bool(m.scale_by_sigma)), {}))
 
     # ------------------------------------------------------------------ building blocks
-    def _conv(self, x, cw: _ConvW, out, bias_b=None, residual=None, out_scale: float = 1.0):
-        """3x3 / 1x1 conv with the fused epilogue; tcgen05 path when the shape allows it."""
+    def _conv(self, x, cw: _ConvW, out, bias_b=None, residual=None, out_scale: float = 1.0, want_stats: bool = False):
+        """3x3 / 1x1 conv with the fused epilogue; tcgen05 path when the shape allows it.  want_stats:
+        GroupNorm will normalise `out` (alone or as part of a concat buffer) -- its per-channel sums come
+        from the conv epilogue when the kernel can leave them, else from one explicit pass over `out`."""
         use_tc = (cw.w_bf16 is not None and x.dtype == torch.bfloat16 and not ops.EMULATED and ops.tc_enabled())
+        kw = {"bias_b": bias_b, "residual": residual, "out_scale": out_scale}
+        key = (out.data_ptr(), out.shape[3])
+        self.stat_src.pop(key, None)  # whatever was known about this view is stale now
+        fused = False
         if use_tc:
             plan = ops.ConvTcPlan(x, cw.w_bf16, cw.cout, cw.ksize)
             self._tc_plans.append(plan)
-            self.steps.append((plan.run, (cw.bias, out), {"bias_b": bias_b, "residual": residual, "out_scale": out_scale}))
+            if want_stats and plan.stats_floats() > 0:
+                buf = torch.empty(plan.stats_floats(), device=self.device, dtype=torch.float32)
+                kw["stats"] = buf
+                self.stat_src[key] = (buf, plan.stats_layout())
+                fused = True
+            self.steps.append((plan.run, (cw.bias, out), kw))
         else:
-            self.steps.append((ops.conv_direct, (x, cw.w, cw.bias, out, cw.ksize),
-                               {"bias_b": bias_b, "residual": residual, "out_scale": out_scale}))
+            self.steps.append((ops.conv_direct, (x, cw.w, cw.bias, out, cw.ksize), kw))
+        if want_stats and not fused:
+            B, H, W, C = out.shape
+            buf = torch.empty(ops.gn_partial_floats(B, H * W, C), device=self.device, dtype=torch.float32)
+            self.steps.append((ops.gn_partial_sums, (out, buf), {}))
+            self.stat_src[key] = (buf, ops.split_sums_layout(H * W, C))
+
+    def _scale_shift(self, x, gnw) -> torch.Tensor:
+        """GroupNorm(min(C/4,32), C, eps=1e-6) of the NHWC view x folded to per-(b,c) scale/shift
+        (layerspp.py:269-271,297,318).  Uses the producers' recorded sums when every channel range of
+        x has one (a concat buffer = [main path | skip]); otherwise one statistics pass over x."""
+        B, H, W, C = x.shape
+        G = min(C // 4, 32)
+        ss = torch.empty(B, 2, C, device=self.device, dtype=torch.float32)
+        srcs, ptr, left = [], x.data_ptr(), C
+        while left > 0:
+            hit = None
+            for (p0, c0), v in self.stat_src.items():
+                if p0 == ptr and c0 <= left and (hit is None or c0 > hit[0]):
+                    hit = (c0, v)
+            if hit is None:
+                srcs = None
+                break
+            srcs.append(hit[1])
+            ptr += hit[0] * x.element_size()
+            left -= hit[0]
+        if srcs and len(srcs) <= 4:
+            self.steps.append((ops.gn_finalize, (srcs, B, H * W, G, gnw[0], gnw[1], 1e-6, ss), {}))
+        else:
+            self.steps.append((ops.gn_stats, (x, G, gnw[0], gnw[1], 1e-6, self.gn_partial, ss), {}))
+        return ss
 
     def _resblock(self, i: int, spec: ModuleSpec, x, out):
         """ResnetBlockBigGANpp.forward (layerspp.py:296-328)."""
         w, pool, add = self.eng.w, self.pool, self.steps.append
         B, H, W, cin = x.shape
         cout = spec.out_ch
-        f32 = torch.float32
-        ss0 = torch.empty(B, 2, cin, device=self.device, dtype=f32)
-        g0, g1 = w[f"gn{i}a"], w[f"gn{i}b"]
-        add((ops.gn_stats, (x, min(cin // 4, 32), g0[0], g0[1], 1e-6, self.gn_partial, ss0), {}))
+        ss0 = self._scale_shift(x, w[f"gn{i}a"])
         if spec.up or spec.down:
             Ho, Wo = (2 * H, 2 * W) if spec.up else (H // 2, W // 2)
             xr = pool.get((B, Ho, Wo, cin), self.adt)
@@ -407,17 +445,17 @@ class _Plan:
             add((ops.gn_apply, (x, ss0, True, hA), {}))
         h1 = pool.get((B, Ho, Wo, cout), self.adt)
         off = w[f"dense_off{i}"]
-        self._conv(hA, w[f"conv{i}a"], h1, bias_b=self.dense[:, off:off + cout])
+        self._conv(hA, w[f"conv{i}a"], h1, bias_b=self.dense[:, off:off + cout], want_stats=True)
         pool.put(hA)
-        ss1 = torch.empty(B, 2, cout, device=self.device, dtype=f32)
-        add((ops.gn_stats, (h1, min(cout // 4, 32), g1[0], g1[1], 1e-6, self.gn_partial, ss1), {}))
+        ss1 = self._scale_shift(h1, w[f"gn{i}b"])
         add((ops.gn_apply, (h1, ss1, True, h1), {}))  # in place
+        self.stat_src.pop((h1.data_ptr(), cout), None)
         if f"conv{i}c" in w:
             self._conv(xr, w[f"conv{i}c"], out)
             res = out
         else:
             res = xr
-        self._conv(h1, w[f"conv{i}b"], out, residual=res, out_scale=1.0 / math.sqrt(2.0))
+        self._conv(h1, w[f"conv{i}b"], out, residual=res, out_scale=1.0 / math.sqrt(2.0), want_stats=True)
         pool.put(h1)
         if xr is not x:
             pool.put(xr)
@@ -426,15 +464,13 @@ class _Plan:
         """AttnBlockpp.forward (layerspp.py:81-97)."""
         w, pool, add = self.eng.w, self.pool, self.steps.append
         B, H, W, C = x.shape
-        ss = torch.empty(B, 2, C, device=self.device, dtype=torch.float32)
-        g = w[f"gn{i}"]
-        add((ops.gn_stats, (x, min(C // 4, 32), g[0], g[1], 1e-6, self.gn_partial, ss), {}))
+        ss = self._scale_shift(x, w[f"gn{i}"])
         hn = pool.get((B, H, W, C), self.adt)
         add((ops.gn_apply, (x, ss, False, hn), {}))
         qkv = pool.get((B, H, W, 3 * C), self.adt)
         self._conv(hn, w[f"qkv{i}"], qkv)
         add((ops.attention, (qkv[..., :C], qkv[..., C:2 * C], qkv[..., 2 * C:], hn), {}))
-        self._conv(hn, w[f"proj{i}"], out, residual=x, out_scale=1.0 / math.sqrt(2.0))
+        self._conv(hn, w[f"proj{i}"], out, residual=x, out_scale=1.0 / math.sqrt(2.0), want_stats=True)
         pool.put(hn)
         pool.put(qkv)
 

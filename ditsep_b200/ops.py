@@ -143,39 +143,54 @@ def expand_istft(spec, window, out, exponent: float, factor: float):
 
 
 # ------------------------------------------------------------------ norm / resample
-def gn_nsplit(B: int, HW: int, C: int) -> int:
+def gn_nsplit(HW: int, C: int) -> int:
+    """Pixel splits of the statistics pass.  A function of the image shape only -- never of the batch --
+    so the summation order, and with it every bf16 rounding downstream, is batch-invariant."""
     ppb = max(1, 256 // (C // 8))
-    want = max(1, (4 * 148 + B - 1) // B)
-    return int(max(1, min(want, HW // (ppb * 4) if HW >= ppb * 4 else 1)))
+    return int(max(1, min(64, HW // (ppb * 8))))
 
 
 def gn_stats(x, G: int, gamma, beta, eps: float, partial, scale_shift):
     """x NHWC (B,H,W,C) -> scale_shift (B,2,C) f32.  partial: f32 scratch >= B*nsplit*C*2."""
     _cuda(x, gamma, beta, partial, scale_shift)
     B, H, W, Cc = x.shape
-    nsplit = gn_nsplit(B, H * W, Cc)
+    nsplit = gn_nsplit(H * W, Cc)
     if partial.numel() < B * nsplit * Cc * 2:
         raise _lib.DitsepError("gn_stats: partial scratch too small")
     check(_lib.load().ditsep_gn_stats(_ptr(x), _dt(x), B, H * W, Cc, nhwc_ld(x), G, _ptr(gamma), _ptr(beta), eps,
                                       _ptr(partial), nsplit, _ptr(scale_shift), _stream()), "gn_stats")
 
 
-def _stats_args(stats, B: int, Cout: int):
-    """stats: f32 view (B, Cout, 2) with strides (ld*2, 2, 1) -> (pointer, ld)."""
-    if stats is None:
-        return None, 0
-    if stats.dtype != torch.float32 or tuple(stats.shape) != (B, Cout, 2) or stats.stride(2) != 1 or stats.stride(1) != 2:
-        raise _lib.DitsepError(f"stats must be a float32 (B={B}, C={Cout}, 2) view with strides (ld*2, 2, 1)")
-    return stats.data_ptr(), (stats.stride(0) // 2 if B > 1 else Cout)
+def gn_partial_floats(B: int, HW: int, C: int) -> int:
+    return B * gn_nsplit(HW, C) * C * 2
 
 
-def gn_finalize(stats, HW: int, G: int, gamma, beta, eps: float, scale_shift):
-    """stats (B, C, 2) per-channel {sum, sumsq} (a channel slice of a wider buffer is fine) ->
-    scale_shift (B, 2, C)."""
-    _cuda(stats, gamma, beta, scale_shift)
-    B, Cc, _ = stats.shape
-    ptr, ld = _stats_args(stats, B, Cc)
-    check(_lib.load().ditsep_gn_finalize(ptr, ld, B, HW, Cc, G, _ptr(gamma), _ptr(beta), eps, _ptr(scale_shift),
+def split_sums_layout(HW: int, C: int) -> "_lib.StatsSrc":
+    """Statistics-source record (without pointer) of what gn_partial_sums leaves for an image of HW pixels."""
+    return _lib.StatsSrc(None, _lib.STATS_SPLIT_SUMS, C, C, gn_nsplit(HW, C), 0, 0, 0)
+
+
+def gn_partial_sums(x, partial):
+    """Per-channel {sum, sumsq} partials of x NHWC (B,H,W,C) into `partial` (f32, >= gn_partial_floats),
+    laid out as split_sums_layout(H*W, C) says."""
+    _cuda(x, partial)
+    B, H, W, Cc = x.shape
+    nsplit = gn_nsplit(H * W, Cc)
+    if partial.dtype != torch.float32 or partial.numel() < B * nsplit * Cc * 2:
+        raise _lib.DitsepError("gn_partial_sums: partial scratch too small")
+    check(_lib.load().ditsep_gn_partial_sums(_ptr(x), _dt(x), B, H * W, Cc, nhwc_ld(x), _ptr(partial), nsplit,
+                                             _stream()), "gn_partial_sums")
+
+
+def gn_finalize(srcs, B: int, HW: int, G: int, gamma, beta, eps: float, scale_shift):
+    """srcs: 1..4 pairs (buffer, StatsSrc layout) covering the normalised tensor's channels end to end
+    (a producer's statistics buffer and how it is laid out) -> scale_shift (B, 2, C)."""
+    _cuda(gamma, beta, scale_shift, *(t for t, _ in srcs))
+    arr = (_lib.StatsSrc * len(srcs))()
+    for i, (t, lay) in enumerate(srcs):
+        arr[i] = _lib.StatsSrc(t.data_ptr(), lay.kind, lay.C, lay.ld, lay.n_part, lay.maxf, lay.tiles_per_image,
+                               lay.num_tiles)
+    check(_lib.load().ditsep_gn_finalize(arr, len(srcs), B, HW, G, _ptr(gamma), _ptr(beta), eps, _ptr(scale_shift),
                                          _stream()), "gn_finalize")
 
 
@@ -197,10 +212,9 @@ def fir_resample(x, up: bool, out_x=None, scale_shift=None, out_h=None):
 
 
 # ------------------------------------------------------------------ convolution
-def conv_direct(x, w, bias, out, ksize: int, bias_b=None, residual=None, out_scale: float = 1.0, stats=None):
-    """x NHWC, w (Cout, taps, Cin) f32, out NHWC.  out = out_scale*(conv + bias + bias_b[b] + residual);
-    stats (B, Cout, 2) += per-channel {sum, sumsq} of out."""
-    _cuda(x, w, bias, out, bias_b, residual, stats)
+def conv_direct(x, w, bias, out, ksize: int, bias_b=None, residual=None, out_scale: float = 1.0):
+    """x NHWC, w (Cout, taps, Cin) f32, out NHWC.  out = out_scale*(conv + bias + bias_b[b] + residual)."""
+    _cuda(x, w, bias, out, bias_b, residual)
     B, H, W, Cin = x.shape
     Cout = out.shape[3]
     if w.dtype != torch.float32 or not w.is_contiguous() or w.shape != (Cout, ksize * ksize, Cin):
@@ -210,7 +224,7 @@ def conv_direct(x, w, bias, out, ksize: int, bias_b=None, residual=None, out_sca
     check(_lib.load().ditsep_conv_direct(_ptr(x), _dt(x), B, H, W, Cin, nhwc_ld(x), _ptr(w), _ptr(bias), _ptr(bias_b),
                                          0 if bias_b is None else bias_b.stride(0), _ptr(residual),
                                          0 if residual is None else nhwc_ld(residual), out_scale, Cout, ksize,
-                                         _ptr(out), _dt(out), nhwc_ld(out), *_stats_args(stats, B, Cout), _stream()),
+                                         _ptr(out), _dt(out), nhwc_ld(out), _stream()),
           "conv_direct")
 
 
@@ -230,14 +244,27 @@ class ConvTcPlan:
         check(_lib.load().ditsep_conv_tc_plan_create(C.byref(self._h), _ptr(x), B, H, W, Cin, nhwc_ld(x), _ptr(w_bf16),
                                                      Cout, ksize), "conv_tc_plan_create")
 
+    def stats_layout(self) -> "_lib.StatsSrc":
+        """Layout of the statistics partials this plan's run() can leave (kind STATS_NONE if it cannot);
+        ``ptr`` is left null for the caller to fill in."""
+        lay = _lib.StatsSrc()
+        check(_lib.load().ditsep_conv_tc_stats_layout(self._h, C.byref(lay)), "conv_tc_stats_layout")
+        return lay
+
+    def stats_floats(self) -> int:
+        lay = self.stats_layout()
+        return 0 if lay.kind == _lib.STATS_NONE else lay.n_part * lay.maxf * lay.ld * 2
+
     def run(self, bias, out, bias_b=None, residual=None, out_scale: float = 1.0, stats=None):
+        """stats: f32 buffer of >= stats_floats() elements receiving the per-CTA statistics partials."""
         _cuda(bias, out, bias_b, residual, stats)
+        if stats is not None and (stats.dtype != torch.float32 or stats.numel() < max(1, self.stats_floats())):
+            raise _lib.DitsepError("conv_tc: statistics buffer too small (or this plan cannot produce statistics)")
         check(_lib.load().ditsep_conv_tc_run(self._h, _ptr(bias), _ptr(bias_b),
                                              0 if bias_b is None else bias_b.stride(0), _ptr(residual),
                                              0 if residual is None else _dt(residual),
                                              0 if residual is None else nhwc_ld(residual), out_scale, _ptr(out),
-                                             _dt(out), nhwc_ld(out), *_stats_args(stats, self.shape[0], self.Cout),
-                                             _stream()), "conv_tc_run")
+                                             _dt(out), nhwc_ld(out), _ptr(stats), _stream()), "conv_tc_run")
 
     def __del__(self):
         h = getattr(self, "_h", None)

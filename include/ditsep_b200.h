@@ -89,12 +89,35 @@ int ditsep_expand_istft(const float* spec, const float* window, float* out, int 
 /* ---- GroupNorm (+SiLU) -------------------------------------------------------------
  * nn.GroupNorm(G, C, eps=1e-6) statistics + affine folded to per-(b,c) scale/shift
  * (layerspp.py:269-271,283-285,297,318).  x: NHWC [B][HW][ld]; partial: scratch
- * (B*nsplit*C*2 floats); scale_shift out: [B][2][C] f32. */
+ * (B*nsplit*C*2 floats); scale_shift out: [B][2][C] f32.  Summation order depends only on
+ * (HW, C, nsplit), never on B: results are batch-invariant and bit-reproducible. */
 int ditsep_gn_stats(const void* x, int dtype, int B, int64_t HW, int C, int ld, int G, const float* gamma,
                     const float* beta, float eps, float* partial, int nsplit, float* scale_shift, void* stream);
-/* Same scale/shift from per-channel sums accumulated by the producing convolution's epilogue:
- * stats [B][ld_stats][2] = {sum, sum of squares} over the HW pixels (see ditsep_conv_*: `stats`). */
-int ditsep_gn_finalize(const float* stats, int ld_stats, int B, int64_t HW, int C, int G, const float* gamma,
+/* First half of the above only: per-channel {sum, sum of squares} partials [B][nsplit][C][2]
+ * (a DITSEP_STATS_SPLIT_SUMS source for ditsep_gn_finalize). */
+int ditsep_gn_partial_sums(const void* x, int dtype, int B, int64_t HW, int C, int ld, float* partial, int nsplit,
+                           void* stream);
+
+/* Where the per-channel {sum, sum of squares} of a tensor (or of a channel range of a concat
+ * buffer) were left by its producer. */
+#define DITSEP_STATS_NONE 0
+#define DITSEP_STATS_CONV_PARTIALS 1 /* written by ditsep_conv_tc_run: [n_part][maxf][ld][2], one slot per
+                                        (CTA, image it touched); layout from ditsep_conv_tc_stats_layout */
+#define DITSEP_STATS_SPLIT_SUMS 2    /* [B][n_part][ld][2] (ditsep_gn_partial_sums; n_part = nsplit) */
+typedef struct {
+  const float* ptr;
+  int32_t kind;            /* DITSEP_STATS_* */
+  int32_t C;               /* channels this source covers (they are consecutive in the normalised tensor) */
+  int32_t ld;              /* channel stride of the source rows */
+  int32_t n_part;          /* CTAs (conv partials) or splits (split sums) */
+  int32_t maxf;            /* conv partials: slots per CTA */
+  int32_t tiles_per_image; /* conv partials */
+  int32_t num_tiles;       /* conv partials */
+} ditsep_stats_src;
+/* scale/shift of GroupNorm(G, C = sum of the sources' C) from up to 4 statistics sources laid end
+ * to end along the channel axis (torch.cat([h, skip], dim=1) feeding GroupNorm_0, ncsnpp.py:413 +
+ * layerspp.py:297).  Partials are added in a fixed order, in double. */
+int ditsep_gn_finalize(const ditsep_stats_src* host_srcs, int n_srcs, int B, int64_t HW, int G, const float* gamma,
                        const float* beta, float eps, float* scale_shift, void* stream);
 /* y = act(x*scale + shift), act = SiLU if silu else identity.  y: NHWC with stride ld_y. */
 int ditsep_gn_apply(const void* x, int dtype, int B, int64_t HW, int C, int ld_x, const float* scale_shift,
@@ -115,29 +138,31 @@ int ditsep_fir_resample(const void* x, int dtype, int B, int H, int W, int C, in
  * (layers.py:678-689) with the res-block epilogue fused (layerspp.py:314-328):
  *   out[b,p,co] = out_scale * ( sum_{tap,ci} in[b,p+tap,ci] * w[co,tap,ci] + bias[co]
  *                               + bias_b[b,co] + residual[b,p,co] )
- * `stats` (nullable): [B][ld_stats][2] float accumulators; the epilogue ADDS the per-image, per-channel
- * {sum, sum of squares} of the values it stores (the GroupNorm statistics of the output tensor,
- * layerspp.py:297,318), so the consumer's GroupNorm needs no extra pass.  Caller zeroes them.
  * CUDA-core fp32 path: any Cin/Cout; weights w: [Cout][taps][Cin] f32. */
 int ditsep_conv_direct(const void* in, int dtype, int B, int H, int W, int Cin, int ld_in, const float* w,
                        const float* bias, const float* bias_b, int ld_bias_b, const void* residual, int ld_res,
-                       float out_scale, int Cout, int ksize, void* out, int out_dtype, int ld_out, float* stats,
-                       int ld_stats, void* stream);
+                       float out_scale, int Cout, int ksize, void* out, int out_dtype, int ld_out, void* stream);
 
 /* tcgen05 implicit-GEMM path (bf16 operands, fp32 TMEM accumulators, TMA-fed).
  * Requirements: Cin % 64 == 0, Cout padded to a multiple of 16 inside `w` (and to a multiple of
  * 64 when > 128), `in` 16-byte aligned with ld_in % 8 == 0.  w: [CoutPad][taps][Cin] bf16.
- * A plan holds the encoded TMA descriptors for one (tensor, shape) binding.  3x3 convolutions on
- * images of at least 8 x 16 pixels run the halo kernel (one TMA box per 64-channel block brings
- * an 8 x 16 pixel tile plus its halo; the nine taps are shifted views of it; persistent CTAs,
- * filter resident in shared memory when it fits); everything else one TMA box per tap. */
+ * A plan holds the encoded TMA descriptors for one (tensor, shape) binding.  Images of at least
+ * 8 x 16 pixels run the tile kernel (one TMA box per 64-channel block brings an 8 x 16 pixel tile
+ * plus its halo; the taps are shifted views of it; persistent CTAs over contiguous tile ranges,
+ * filter resident in shared memory when it fits); smaller images one TMA box per tap.
+ * `stats` (nullable, tile kernel only): the epilogue also leaves the per-image, per-channel
+ * {sum, sum of squares} of the values it stores (the GroupNorm statistics of the output tensor,
+ * layerspp.py:297,318) as per-CTA partials, so the consumer's GroupNorm needs no extra pass over
+ * the tensor.  No atomics: bit-reproducible.  Size and layout: ditsep_conv_tc_stats_layout
+ * (n_part * maxf * ld * 2 floats; kind DITSEP_STATS_NONE if the plan cannot produce them). */
 typedef struct ditsep_conv_plan ditsep_conv_plan;
 int ditsep_conv_tc_plan_create(ditsep_conv_plan** plan, const void* in, int B, int H, int W, int Cin, int ld_in,
                                const void* w_bf16, int Cout, int ksize);
 void ditsep_conv_tc_plan_destroy(ditsep_conv_plan* plan);
+int ditsep_conv_tc_stats_layout(const ditsep_conv_plan* plan, ditsep_stats_src* layout);
 int ditsep_conv_tc_run(const ditsep_conv_plan* plan, const float* bias, const float* bias_b, int ld_bias_b,
                        const void* residual, int res_dtype, int ld_res, float out_scale, void* out, int out_dtype,
-                       int ld_out, float* stats, int ld_stats, void* stream);
+                       int ld_out, float* stats, void* stream);
 
 /* ---- attention (single head, all H*W tokens) ------------------------------------------
  * AttnBlockpp.forward core (layerspp.py:88-92): o = softmax(q k^T / sqrt(C)) v per image.

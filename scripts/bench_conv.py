@@ -29,8 +29,9 @@ for (H, W, Cin, Cout, k, fl) in SHAPES:
     out = torch.empty(B, H, W, Cout, device=dev, dtype=torch.bfloat16)
     res = torch.randn(B, H, W, Cout, generator=g).to(dev).to(torch.bfloat16) if "r" in fl else None
     bb = torch.randn(B, Cout, generator=g).to(dev) if "b" in fl else None
-    stats = torch.zeros(B, Cout, 2, device=dev) if fl else None
+    stats = None
     plan = ops.ConvTcPlan(x, w, Cout, k)
+    stats = torch.empty(plan.stats_floats(), device=dev) if (fl and plan.stats_floats()) else None
     kw = dict(bias_b=bb, residual=res, out_scale=0.7071, stats=stats)
     for _ in range(3):
         plan.run(bias, out, **kw)

@@ -12,10 +12,10 @@ def rel_l2(a, b):
     return float((a - b).norm() / b.norm().clamp(min=1e-30))
 
 
-def build_model(precision="fp32", device="cpu", nf=64, n_src=2, N=30, seed=0):
+def build_model(precision="fp32", device="cpu", nf=64, n_src=2, N=30, seed=0, init_scale=1.0):
     """DiffSepModel with the oracle's deterministic weights (same dict the reference was pinned with)."""
     cfg = R.ScoreConfig(num_sources=n_src, backbone=R.NCSNppConfig(nf=nf))
-    sd = R.make_state_dict(cfg.backbone, seed=seed)
+    sd = R.make_state_dict(cfg.backbone, seed=seed, init_scale=init_scale)
     model = DiffSepModel(default_config(nf=nf, n_src=n_src, N=N, precision=precision))
     model.score_model.load_state_dict(sd, strict=True)
     return model.to(device).eval(), sd, cfg

@@ -18,7 +18,7 @@ import torch.nn.functional as F
 from ditsep_b200 import ops
 
 _NAMES = ["pc_corrector", "pc_predictor", "pc_prior", "philox_normal", "stft_compress", "expand_istft", "gn_stats",
-          "gn_apply", "fir_resample", "conv_direct", "attention", "temb_mlp", "temb_dense", "output_layer"]
+          "gn_partial_sums", "gn_finalize", "gn_apply", "fir_resample", "conv_direct", "attention", "temb_mlp", "temb_dense", "output_layer"]
 
 
 def _coef(p, mode, t):
@@ -130,6 +130,38 @@ def gn_stats(x, G, gamma, beta, eps, partial, scale_shift):
     rstd = 1 / torch.sqrt(var + eps)
     sc = rstd.repeat_interleave(C // G, dim=1) * gamma.double()
     sh = beta.double() - mean.repeat_interleave(C // G, dim=1) * sc
+    scale_shift[:, 0].copy_(sc.float())
+    scale_shift[:, 1].copy_(sh.float())
+
+
+def gn_partial_sums(x, partial):
+    """ditsep_gn_partial_sums: [B][nsplit][C][2] partials; the stand-in puts everything in split 0."""
+    B, H, W, C = x.shape
+    ns = ops.gn_nsplit(H * W, C)
+    v = partial[:B * ns * C * 2].view(B, ns, C, 2)
+    v.zero_()
+    xf = x.double().reshape(B, H * W, C)
+    v[:, 0, :, 0] = xf.sum(dim=1).float()
+    v[:, 0, :, 1] = (xf * xf).sum(dim=1).float()
+
+
+def gn_finalize(srcs, B, HW, G, gamma, beta, eps, scale_shift):
+    """ditsep_gn_finalize for split-sums sources (the conv-partials kind only exists on the GPU)."""
+    sums = []
+    for t, lay in srcs:
+        assert lay.kind == 2, "CPU stand-in only knows split sums"
+        v = t[:B * lay.n_part * lay.ld * 2].view(B, lay.n_part, lay.ld, 2)[:, :, :lay.C].double().sum(dim=1)
+        sums.append(v)
+    s = torch.cat(sums, dim=1)  # (B, C, 2)
+    C = s.shape[1]
+    cpg = C // G
+    g = s.reshape(B, G, cpg, 2).sum(dim=2)
+    n = HW * cpg
+    mean = g[..., 0] / n
+    var = (g[..., 1] / n - mean * mean).clamp(min=0)
+    rstd = 1 / torch.sqrt(var + eps)
+    sc = rstd.repeat_interleave(cpg, dim=1) * gamma.double()
+    sh = beta.double() - mean.repeat_interleave(cpg, dim=1) * sc
     scale_shift[:, 0].copy_(sc.float())
     scale_shift[:, 1].copy_(sh.float())
 
