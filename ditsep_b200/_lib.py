@@ -24,11 +24,10 @@ class SdeParams(C.Structure):
 class StatsSrc(C.Structure):
     """ditsep_stats_src (include/ditsep_b200.h): where a producer left per-channel {sum, sumsq}."""
 
-    _fields_ = [("ptr", C.c_void_p), ("kind", C.c_int32), ("C", C.c_int32), ("ld", C.c_int32), ("n_part", C.c_int32),
-                ("maxf", C.c_int32), ("tiles_per_image", C.c_int32), ("num_tiles", C.c_int32)]
+    _fields_ = [("ptr", C.c_void_p), ("kind", C.c_int32), ("C", C.c_int32), ("ld", C.c_int32), ("n_part", C.c_int32)]
 
 
-STATS_NONE, STATS_CONV_PARTIALS, STATS_SPLIT_SUMS = 0, 1, 2
+STATS_NONE, STATS_SPLIT_SUMS = 0, 2
 
 # name -> (restype, argtypes); must list EVERY symbol of include/ditsep_b200.h
 SIGNATURES = {

@@ -19,13 +19,15 @@
 //    SAME shared-memory tile read through a UMMA descriptor whose start is shifted by
 //    (dy*(8+2h) + dx) rows and whose 8-row groups are (8+2h) rows apart -- every input element
 //    is fetched from L2 once per tile instead of nine times.  CTAs are persistent over a
-//    CONTIGUOUS range of tiles; the filter slice of the CTA's N tile stays resident in shared
-//    memory when it fits (else it streams through a ring).  Two TMEM accumulators alternate, and
-//    16 epilogue warps (4 per TMEM lane quadrant, 16 output channels each) drain one while the
-//    single MMA thread fills the other.  The epilogue also accumulates, in registers, the
-//    per-channel sum / sum of squares of what it stores (the GroupNorm statistics of the output
-//    tensor, layerspp.py:297,318) and writes them per (CTA, image) -- no atomics, so the
-//    statistics (and with them the whole bf16 network) are bit-reproducible.
+//    CONTIGUOUS range of segments (1-4 consecutive tiles of one image); the filter slice of the
+//    CTA's N tile stays resident in shared memory when it fits (else it streams through a ring).
+//    Two TMEM accumulators alternate, and 16 epilogue warps (4 per TMEM lane quadrant, 16 output
+//    channels each) drain one while the single MMA thread fills the other.  The epilogue also
+//    accumulates, in registers, the per-channel sum / sum of squares of what it stores (the
+//    GroupNorm statistics of the output tensor, layerspp.py:297,318) and writes them once per
+//    (segment, quadrant) -- no atomics, and a summation order that depends on the image shape
+//    only, so the statistics (and with them the whole bf16 network) are bit-reproducible and
+//    independent of the batch size.
 //  * conv_tc_kernel (smaller images, where a 128-pixel tile spans several images): one TMA box
 //    per (tap, 64-channel block), one tile per CTA.
 #include <cstdlib>
@@ -57,8 +59,8 @@ struct ConvTcParams {
   // tile kernel
   int num_tiles, tiles_per_image, chunks, w_resident, a_stages, w_stages;
   int halo, row_pitch, a_rows, a_stage_bytes;
-  float* stats;            // nullable: partial sums [grid_x][maxf][ld_part][2]
-  int maxf, ld_part;
+  float* stats;            // nullable: partial sums [B][segs_per_image][4][ld_part][2]
+  int seg_len, segs_per_image, ld_part;
 };
 
 // ---- shared epilogue -----------------------------------------------------------------------
@@ -157,6 +159,19 @@ __device__ __forceinline__ void epilogue16(const ConvTcParams& p, const uint32_t
         if (j < nvalid) op[j] = f[j];
     }
   }
+}
+
+// Out-of-line copy for the tile kernel's rare shapes (fewer than 16 real channels, fp32 output): keeps the
+// register budget of its hot path for the bf16 fast path.
+__device__ __noinline__ void epilogue16_slow(const ConvTcParams& p, const uint32_t* v, bool valid, int pb, int64_t pix,
+                                             int co0, float* f) {
+  uint32_t vv[16];
+  float ff[16];
+#pragma unroll
+  for (int j = 0; j < 16; ++j) vv[j] = v[j];
+  epilogue16(p, vv, valid, pb, pix, co0, ff);
+#pragma unroll
+  for (int j = 0; j < 16; ++j) f[j] = ff[j];
 }
 
 // ---- kernel 1: one TMA box per (tap, 64-channel block) --------------------------------------
@@ -265,7 +280,7 @@ __global__ void __launch_bounds__(kThreads) conv_tc_kernel(const __grid_constant
   }
 }
 
-// ---- kernel 2: 8 x 16 pixel tiles with halo, persistent CTAs over contiguous tile ranges ------
+// ---- kernel 2: 8 x 16 pixel tiles with halo, persistent CTAs over contiguous segment ranges ----
 constexpr int kTileW = 8, kTileH = 16;
 constexpr int kCtrlWarps = 4;   // 0: TMA producer, 1: TMEM allocator + MMA issuer, 2-3: idle (the register file
                                 // is allocated in units of 4 warps: 20 warps x 96 registers fill it)
@@ -274,25 +289,56 @@ constexpr int kTileThreads = (kCtrlWarps + kEpiWarps) * 32;
 constexpr int kMaxAStages = 4, kMaxWStages = 4;
 constexpr int kTileMaxBN = 64;
 
+// The unit of work is a SEGMENT: seg_len consecutive tiles of one image (segs_per_image per image; both are
+// functions of the image shape only).  CTA c walks segments [c*S/G, (c+1)*S/G), S = B * segs_per_image.
+// The GroupNorm partial sums are flushed once per segment, so which pixels are summed together -- and in
+// which order -- never depends on the batch size or on the grid: batch-invariant, bit-reproducible.
+struct TileWalk {
+  int seg, seg_end, b, sidx, lt, lt_end, tx, ty;
+  __device__ __forceinline__ void start_segment(const ConvTcParams& p) {
+    b = seg / p.segs_per_image;
+    sidx = seg - b * p.segs_per_image;
+    lt = sidx * p.seg_len;
+    lt_end = min(lt + p.seg_len, p.tiles_per_image);
+    ty = lt / p.tiles_x;
+    tx = lt - ty * p.tiles_x;
+  }
+  __device__ __forceinline__ void init(const ConvTcParams& p) {
+    const int64_t S = (int64_t)p.B * p.segs_per_image;
+    seg = (int)((int64_t)blockIdx.x * S / gridDim.x);
+    seg_end = (int)((int64_t)(blockIdx.x + 1) * S / gridDim.x);
+    if (seg < seg_end) start_segment(p);
+  }
+  __device__ __forceinline__ bool done() const { return seg >= seg_end; }
+  __device__ __forceinline__ bool last_of_segment() const { return lt + 1 == lt_end; }
+  __device__ __forceinline__ void next(const ConvTcParams& p) {
+    if (++lt == lt_end) {
+      if (++seg < seg_end) start_segment(p);
+    } else if (++tx == p.tiles_x) {
+      tx = 0;
+      ++ty;
+    }
+  }
+};
+
+template <int KS, bool kRes, bool kFast>
 __global__ void __launch_bounds__(kTileThreads, 1) conv_tc_tile_kernel(const __grid_constant__ CUtensorMap mapA,
                                                                        const __grid_constant__ CUtensorMap mapW,
-                                                                       const ConvTcParams p) {
+                                                                       const __grid_constant__ ConvTcParams p) {
+  constexpr int kTaps = KS * KS, kHalo = KS / 2, kRowPitch = kTileW + 2 * kHalo;
   extern __shared__ uint8_t smem_raw[];
   __shared__ __align__(8) uint64_t bar_a_full[kMaxAStages], bar_a_empty[kMaxAStages];
   __shared__ __align__(8) uint64_t bar_w_full[kMaxWStages], bar_w_empty[kMaxWStages];
   __shared__ __align__(8) uint64_t bar_w_res, bar_acc_full[2], bar_acc_empty[2];
   __shared__ uint32_t tmem_base_slot;
-  __shared__ float red[4][kTileMaxBN][2];  // per-quadrant channel sums at a statistics flush
+  __shared__ __align__(16) float comb[2][kTileMaxBN];  // bias[co] + bias_b[b][co] of the image being stored
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const uint32_t base = (smem_u32(smem_raw) + 1023u) & ~1023u;
   const uint32_t w_tile_bytes = (uint32_t)p.BN * 128u;
-  const int n_wtiles = p.w_resident ? p.chunks * p.taps : p.w_stages;
+  const int n_wtiles = kRes ? p.chunks * kTaps : p.w_stages;
   const uint32_t a_ring = (base + (uint32_t)n_wtiles * w_tile_bytes + 1023u) & ~1023u;
   const int n0 = blockIdx.y * p.BN;
-  const int t0 = (int)((int64_t)blockIdx.x * p.num_tiles / gridDim.x);
-  const int t1 = (int)((int64_t)(blockIdx.x + 1) * p.num_tiles / gridDim.x);
-  const int my_tiles = t1 - t0;
 
   if (threadIdx.x == 0) {
     for (int s = 0; s < kMaxAStages; ++s) {
@@ -320,169 +366,243 @@ __global__ void __launch_bounds__(kTileThreads, 1) conv_tc_tile_kernel(const __g
     if (lane == 0) {
       asm volatile("prefetch.tensormap [%0];" ::"l"(&mapA) : "memory");
       asm volatile("prefetch.tensormap [%0];" ::"l"(&mapW) : "memory");
-      if (p.w_resident) {
+      if (kRes) {
         const uint32_t bar = smem_u32(&bar_w_res);
-        mbar_expect_tx(bar, (uint32_t)(p.chunks * p.taps) * w_tile_bytes);
+        mbar_expect_tx(bar, (uint32_t)(p.chunks * kTaps) * w_tile_bytes);
         for (int ch = 0; ch < p.chunks; ++ch)
-          for (int tap = 0; tap < p.taps; ++tap)
-            tma_load_2d(base + (uint32_t)(ch * p.taps + tap) * w_tile_bytes, &mapW, bar, tap * p.Cin + ch * kBlockK, n0);
+          for (int tap = 0; tap < kTaps; ++tap)
+            tma_load_2d(base + (uint32_t)(ch * kTaps + tap) * w_tile_bytes, &mapW, bar, tap * p.Cin + ch * kBlockK, n0);
       }
-      uint32_t ia = 0, iw = 0;  // running A-block / W-tile counters (ring position + phase)
-      for (int it = 0; it < my_tiles; ++it) {
-        const int mt = t0 + it;
-        const int b = mt / p.tiles_per_image;
-        const int rem = mt - b * p.tiles_per_image;
-        const int ty = rem / p.tiles_x, tx = rem - ty * p.tiles_x;
-        for (int ch = 0; ch < p.chunks; ++ch, ++ia) {
-          const int sa = (int)(ia % (uint32_t)p.a_stages);
-          mbar_wait(smem_u32(&bar_a_empty[sa]), ((ia / (uint32_t)p.a_stages) & 1u) ^ 1u);
+      int sa = 0, sw = 0;
+      uint32_t pa = 1, pw = 1;  // "empty" barriers start free: the first pass waits on the opposite parity
+      TileWalk tw;
+      for (tw.init(p); !tw.done(); tw.next(p)) {
+        for (int ch = 0; ch < p.chunks; ++ch) {
+          mbar_wait(smem_u32(&bar_a_empty[sa]), pa);
           const uint32_t full = smem_u32(&bar_a_full[sa]);
           mbar_expect_tx(full, (uint32_t)(p.a_rows * 128));
-          tma_load_4d(a_ring + (uint32_t)(sa * p.a_stage_bytes), &mapA, full, ch * kBlockK, tx * kTileW - p.halo,
-                      ty * kTileH - p.halo, b);
-          if (!p.w_resident) {
-            for (int tap = 0; tap < p.taps; ++tap, ++iw) {
-              const int sw = (int)(iw % (uint32_t)p.w_stages);
-              mbar_wait(smem_u32(&bar_w_empty[sw]), ((iw / (uint32_t)p.w_stages) & 1u) ^ 1u);
+          tma_load_4d(a_ring + (uint32_t)(sa * p.a_stage_bytes), &mapA, full, ch * kBlockK, tw.tx * kTileW - kHalo,
+                      tw.ty * kTileH - kHalo, tw.b);
+          if (++sa == p.a_stages) { sa = 0; pa ^= 1u; }
+          if (!kRes) {
+            for (int tap = 0; tap < kTaps; ++tap) {
+              mbar_wait(smem_u32(&bar_w_empty[sw]), pw);
               const uint32_t wfull = smem_u32(&bar_w_full[sw]);
               mbar_expect_tx(wfull, w_tile_bytes);
               tma_load_2d(base + (uint32_t)sw * w_tile_bytes, &mapW, wfull, tap * p.Cin + ch * kBlockK, n0);
+              if (++sw == p.w_stages) { sw = 0; pw ^= 1u; }
             }
           }
         }
       }
     }
   } else if (warp == 1) {
-    if (lane == 0) {
-      const uint32_t idesc = (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(p.BN >> 3) << 17) |
-                             ((uint32_t)(kTileM >> 4) << 24);
-      // A: rows 128 B apart inside a group of 8 output pixels (one tile row), groups row_pitch rows apart.
-      // The swizzle is keyed on absolute shared-memory address bits, so a row-shifted start needs no
-      // base offset (measured: tests/test_gpu_kernels.py::test_conv_tc_halo_descriptor_probe).
-      const uint64_t a_hi = (1ull << 16) | ((uint64_t)((p.row_pitch * 128) >> 4) << 32) | (1ull << 46) | (2ull << 61);
-      if (p.w_resident) {
-        mbar_wait(smem_u32(&bar_w_res), 0);
+    // All 32 lanes walk the loop (converged, so every operand lives in uniform registers); one elected lane
+    // issues.  ONE thread feeds a tensor pipe that retires a 128 x 64 x 16 MMA in 32 cycles: everything that can
+    // be a compile-time constant is one (tap offsets, K steps), ring positions are wrap-around counters, and
+    // descriptors are built from 32-bit low words (shared-memory addresses >> 4 fit 14 bits, so adding row / K
+    // offsets never carries into the next field).
+    const uint32_t idesc = (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(p.BN >> 3) << 17) |
+                           ((uint32_t)(kTileM >> 4) << 24);
+    // A: rows 128 B apart inside a group of 8 output pixels (one tile row), groups kRowPitch rows apart.
+    // The swizzle is keyed on absolute shared-memory address bits, so a row-shifted start needs no base
+    // offset (measured: tests/test_gpu_kernels.py::test_conv_tc_shifted_descriptor_views).
+    constexpr uint32_t a_hi = (uint32_t)((kRowPitch * 128) >> 4) | (1u << 14) | (2u << 29);
+    constexpr uint32_t b_hi = 64u | (1u << 14) | (2u << 29);
+    constexpr uint32_t lbo = 1u << 16;
+    const uint32_t w_step = w_tile_bytes >> 4;
+    if (kRes) {
+      mbar_wait(smem_u32(&bar_w_res), 0);
+      tc_fence_after();
+    }
+    int sa = 0, sw = 0;
+    uint32_t pa = 0, pw = 0, it = 0;
+    TileWalk tw;
+    for (tw.init(p); !tw.done(); tw.next(p), ++it) {
+      const uint32_t ab = it & 1u;
+      mbar_wait(smem_u32(&bar_acc_empty[ab]), ((it >> 1) & 1u) ^ 1u);
+      tc_fence_after();
+      const uint32_t tmem_d = tmem_acc + ab * (uint32_t)p.BN;
+      uint32_t w_lo = (base >> 4) | lbo;
+      for (int ch = 0; ch < p.chunks; ++ch) {
+        mbar_wait(smem_u32(&bar_a_full[sa]), pa);
         tc_fence_after();
-      }
-      uint32_t ia = 0, iw = 0;
-      for (int it = 0; it < my_tiles; ++it) {
-        const int ab = it & 1;
-        mbar_wait(smem_u32(&bar_acc_empty[ab]), (((uint32_t)it >> 1) & 1u) ^ 1u);
-        tc_fence_after();
-        const uint32_t tmem_d = tmem_acc + (uint32_t)(ab * p.BN);
-        for (int ch = 0; ch < p.chunks; ++ch, ++ia) {
-          const int sa = (int)(ia % (uint32_t)p.a_stages);
-          mbar_wait(smem_u32(&bar_a_full[sa]), (ia / (uint32_t)p.a_stages) & 1u);
-          tc_fence_after();
-          const uint32_t a_buf = a_ring + (uint32_t)(sa * p.a_stage_bytes);
-          for (int tap = 0; tap < p.taps; ++tap) {
-            uint32_t w_addr;
-            int sw = 0;
-            if (p.w_resident) {
-              w_addr = base + (uint32_t)(ch * p.taps + tap) * w_tile_bytes;
-            } else {
-              sw = (int)(iw % (uint32_t)p.w_stages);
-              mbar_wait(smem_u32(&bar_w_full[sw]), (iw / (uint32_t)p.w_stages) & 1u);
-              tc_fence_after();
-              w_addr = base + (uint32_t)sw * w_tile_bytes;
-              ++iw;
-            }
-            const int dy = tap / p.ksize, dx = tap - dy * p.ksize;  // already offset by the halo origin
-            const uint32_t a_start = a_buf + (uint32_t)((dy * p.row_pitch + dx) * 128);
-            const uint64_t da = a_hi | (uint64_t)((a_start >> 4) & 0x3FFF);
-            const uint64_t db = make_sw128_desc(w_addr);
+        const uint32_t a_lo = ((a_ring + (uint32_t)(sa * p.a_stage_bytes)) >> 4) | lbo;
 #pragma unroll
-            for (int k = 0; k < kBlockK / 16; ++k)
-              umma_bf16(tmem_d, da + (uint64_t)(2 * k), db + (uint64_t)(2 * k), idesc, (ch | tap | k) != 0);
-            if (!p.w_resident) umma_commit(smem_u32(&bar_w_empty[sw]));
+        for (int tap = 0; tap < kTaps; ++tap) {
+          if (!kRes) {
+            mbar_wait(smem_u32(&bar_w_full[sw]), pw);
+            tc_fence_after();
+            w_lo = ((base + (uint32_t)sw * w_tile_bytes) >> 4) | lbo;
           }
-          umma_commit(smem_u32(&bar_a_empty[sa]));
+          constexpr int kRow16 = 128 >> 4;
+          const uint32_t a_tap = a_lo + (uint32_t)(((tap / KS) * kRowPitch + (tap % KS)) * kRow16);
+          if (elect_one_sync()) {
+#pragma unroll
+            for (int k = 0; k < kBlockK / 16; ++k) {
+              const uint64_t da = ((uint64_t)a_hi << 32) | (uint64_t)(a_tap + 2 * k);
+              const uint64_t db = ((uint64_t)b_hi << 32) | (uint64_t)(w_lo + 2 * k);
+              umma_bf16(tmem_d, da, db, idesc, (tap | k) != 0 ? 1u : (uint32_t)(ch != 0));
+            }
+            if (!kRes) umma_commit(smem_u32(&bar_w_empty[sw]));
+            if (tap == kTaps - 1) {
+              umma_commit(smem_u32(&bar_a_empty[sa]));
+              if (ch == p.chunks - 1) umma_commit(smem_u32(&bar_acc_full[ab]));
+            }
+          }
+          __syncwarp();
+          if (!kRes) {
+            if (++sw == p.w_stages) { sw = 0; pw ^= 1u; }
+          } else {
+            w_lo += w_step;
+          }
         }
-        umma_commit(smem_u32(&bar_acc_full[ab]));
+        if (++sa == p.a_stages) { sa = 0; pa ^= 1u; }
       }
     }
   } else if (warp >= kCtrlWarps) {
     const int e = warp - kCtrlWarps;
     const int q = warp & 3;            // TMEM lane quadrant this warp may read
     const int c0 = (e >> 2) * 16;      // its 16 output channels inside the N tile
-    const bool active = c0 < p.BN && n0 + c0 < p.Cout;
+    const bool has_cols = c0 < p.BN;
+    const int nvalid = min(16, p.Cout - (n0 + c0));
+    const bool active = has_cols && nvalid > 0;
     const int r = q * 32 + lane;
     const int xo = r & 7, yo = r >> 3;
     const int etid = e * 32 + lane;    // 0..511
+    // kFast (host-checked): Cout a multiple of 16, bf16 output (and residual) whose 32-byte channel runs are
+    // 16-byte aligned.  The general path lives in a separate instantiation so that it costs the hot one no registers.
+    constexpr bool fast = kFast;
+    const uint32_t tmem_lane = tmem_acc + ((uint32_t)(q * 32) << 16) + (uint32_t)c0;
     float s[16], sq[16];
 #pragma unroll
     for (int j = 0; j < 16; ++j) s[j] = sq[j] = 0.f;
-    int cur_b = -1, flush_idx = 0;
-
-    auto flush = [&]() {
-      // warp-level transpose-reduce: after offsets 16, 8, 4, 2 lane l holds channel
-      // c = 8*b4 + 4*b3 + 2*b2 + b1 (bits of l) summed over 16 lanes; offset 1 completes it
-#pragma unroll
-      for (int step = 0; step < 4; ++step) {
-        const int off = 16 >> step, half = 8 >> step;
-        const bool upper = (lane & off) != 0;
-#pragma unroll
-        for (int j = 0; j < 8; ++j) {
-          if (j < half) {
-            const float send_s = upper ? s[j] : s[j + half], send_q = upper ? sq[j] : sq[j + half];
-            const float keep_s = upper ? s[j + half] : s[j], keep_q = upper ? sq[j + half] : sq[j];
-            s[j] = keep_s + __shfl_xor_sync(0xffffffffu, send_s, off);
-            sq[j] = keep_q + __shfl_xor_sync(0xffffffffu, send_q, off);
-          }
-        }
-      }
-      s[0] += __shfl_xor_sync(0xffffffffu, s[0], 1);
-      sq[0] += __shfl_xor_sync(0xffffffffu, sq[0], 1);
-      const int c = ((lane >> 4) & 1) * 8 + ((lane >> 3) & 1) * 4 + ((lane >> 2) & 1) * 2 + ((lane >> 1) & 1);
-      if ((lane & 1) == 0 && c0 < p.BN) {
-        red[q][c0 + c][0] = s[0];
-        red[q][c0 + c][1] = sq[0];
-      }
-      named_bar_sync(1, kEpiWarps * 32);
-      if (etid < 2 * p.BN) {
-        const int ch = etid >> 1, k = etid & 1;
-        const float v = (red[0][ch][k] + red[1][ch][k]) + (red[2][ch][k] + red[3][ch][k]);
-        p.stats[(((int64_t)blockIdx.x * p.maxf + flush_idx) * p.ld_part + n0 + ch) * 2 + k] = v;
-      }
-      named_bar_sync(1, kEpiWarps * 32);
-#pragma unroll
-      for (int j = 0; j < 16; ++j) s[j] = sq[j] = 0.f;
-      ++flush_idx;
-    };
-
-    for (int it = 0; it < my_tiles; ++it) {
-      const int mt = t0 + it;
-      const int pb = mt / p.tiles_per_image;
-      const int rem = mt - pb * p.tiles_per_image;
-      const int ty = rem / p.tiles_x, tx = rem - ty * p.tiles_x;
-      if (pb != cur_b) {
-        if (cur_b >= 0 && p.stats) flush();
+    int cur_b = -1;
+    uint32_t it = 0, nimg = 0;
+    const float* cb = comb[0];
+    TileWalk tw;
+    for (tw.init(p); !tw.done(); tw.next(p), ++it) {
+      const int pb = tw.b;
+      if (pb != cur_b) {  // same tile sequence in every epilogue warp: uniform across the 16 warps
         cur_b = pb;
+        float* cw = comb[nimg & 1u];
+        if (etid < p.BN) {
+          float a = 0.f;
+          if (n0 + etid < p.Cout) {
+            if (p.bias) a += __ldg(p.bias + n0 + etid);
+            if (p.bias_b) a += __ldg(p.bias_b + (int64_t)pb * p.ld_bias_b + n0 + etid);
+          }
+          cw[etid] = a;
+        }
+        // one barrier per image: the buffer being overwritten was last read two images ago
+        named_bar_sync(1, kEpiWarps * 32);
+        cb = cw;
+        ++nimg;
       }
-      const int px = tx * kTileW + xo, py = ty * kTileH + yo;
+      const int px = tw.tx * kTileW + xo, py = tw.ty * kTileH + yo;
       const bool valid = px < p.W && py < p.H;
-      const int64_t pix = ((int64_t)pb * p.H + py) * p.W + px;
-      const int ab = it & 1;
-      mbar_wait(smem_u32(&bar_acc_full[ab]), ((uint32_t)it >> 1) & 1u);
+      const int64_t pix = (int64_t)((pb * p.H + py) * p.W + px);  // B*H*W < 2^31 pixels
+      uint4 r0 = make_uint4(0, 0, 0, 0), r1 = r0;
+      if (fast && active && valid && p.residual) {  // issued before the accumulator wait: latency overlaps the MMAs
+        const uint4* rp = reinterpret_cast<const uint4*>(reinterpret_cast<const bf16*>(p.residual) + pix * p.ld_res + n0 + c0);
+        r0 = rp[0];
+        r1 = rp[1];
+      }
+      const uint32_t ab = it & 1u;
+      mbar_wait(smem_u32(&bar_acc_full[ab]), (it >> 1) & 1u);
       tc_fence_after();
-      uint32_t v[16];
-      if (c0 < p.BN) tmem_ld16(tmem_acc + ((uint32_t)(q * 32) << 16) + (uint32_t)(ab * p.BN + c0), v);
-      tc_fence_before();
-      __syncwarp();
-      if (lane == 0) mbar_arrive(smem_u32(&bar_acc_empty[ab]));  // accumulator handed back
-      if (active) {
-        float f[16];
-        epilogue16(p, v, valid, pb, pix, n0 + c0, f);
-        if (p.stats) {
+      if constexpr (fast) {
+        // two passes of 8 channels keep the live set small: v[8] -> 4 packed bf16 pairs -> one 16-byte store
+        uint32_t va[8], vb[8];
+        if (has_cols) {
+          tmem_ld8_nowait(tmem_lane + ab * (uint32_t)p.BN, va);
+          tmem_ld8_nowait(tmem_lane + ab * (uint32_t)p.BN + 8u, vb);
+          tmem_ld_wait();
+        }
+        tc_fence_before();
+        __syncwarp();
+        if (lane == 0) mbar_arrive(smem_u32(&bar_acc_empty[ab]));  // accumulator handed back
+        if (active) {
+          uint4* op = reinterpret_cast<uint4*>(reinterpret_cast<bf16*>(p.out) + pix * p.ld_out + n0 + c0);
 #pragma unroll
-          for (int j = 0; j < 16; ++j) {
-            s[j] += f[j];
-            sq[j] = fmaf(f[j], f[j], sq[j]);
+          for (int h = 0; h < 2; ++h) {
+            const uint32_t (&v)[8] = h ? vb : va;
+            const uint4 rq = h ? r1 : r0;
+            const uint32_t rr[4] = {rq.x, rq.y, rq.z, rq.w};
+            const float4 t0 = *reinterpret_cast<const float4*>(cb + c0 + 8 * h);
+            const float4 t1 = *reinterpret_cast<const float4*>(cb + c0 + 8 * h + 4);
+            const float cbv[8] = {t0.x, t0.y, t0.z, t0.w, t1.x, t1.y, t1.z, t1.w};
+            uint32_t o[4];
+#pragma unroll
+            for (int j = 0; j < 4; ++j) {
+              const float a = (__uint_as_float(v[2 * j]) + cbv[2 * j] + __uint_as_float(rr[j] << 16)) * p.out_scale;
+              const float b = (__uint_as_float(v[2 * j + 1]) + cbv[2 * j + 1] + __uint_as_float(rr[j] & 0xffff0000u)) *
+                              p.out_scale;
+              const __nv_bfloat162 hh = __floats2bfloat162_rn(a, b);
+              o[j] = *reinterpret_cast<const uint32_t*>(&hh);
+            }
+            if (valid) {
+              op[h] = make_uint4(o[0], o[1], o[2], o[3]);
+              if (p.stats) {  // statistics of what the consumer will read: the bf16-rounded values
+#pragma unroll
+                for (int j = 0; j < 4; ++j) {
+                  const float a = __uint_as_float(o[j] << 16), b = __uint_as_float(o[j] & 0xffff0000u);
+                  s[8 * h + 2 * j] += a;
+                  sq[8 * h + 2 * j] = fmaf(a, a, sq[8 * h + 2 * j]);
+                  s[8 * h + 2 * j + 1] += b;
+                  sq[8 * h + 2 * j + 1] = fmaf(b, b, sq[8 * h + 2 * j + 1]);
+                }
+              }
+            }
           }
         }
+      } else {
+        uint32_t v[16];
+        if (has_cols) tmem_ld16(tmem_lane + ab * (uint32_t)p.BN, v);
+        tc_fence_before();
+        __syncwarp();
+        if (lane == 0) mbar_arrive(smem_u32(&bar_acc_empty[ab]));  // accumulator handed back
+        if (active) {
+          float f[16];
+          epilogue16(p, v, valid, pb, pix, n0 + c0, f);
+          if (p.stats) {
+#pragma unroll
+            for (int j = 0; j < 16; ++j) {
+              s[j] += f[j];
+              sq[j] = fmaf(f[j], f[j], sq[j]);
+            }
+          }
+        }
+      }
+      if (p.stats && tw.last_of_segment()) {
+        // warp-level transpose-reduce: after offsets 16, 8, 4, 2 lane l holds channel
+        // c = 8*b4 + 4*b3 + 2*b2 + b1 (bits of l) summed over 16 lanes; offset 1 completes it
+#pragma unroll
+        for (int step = 0; step < 4; ++step) {
+          const int off = 16 >> step, half = 8 >> step;
+          const bool upper = (lane & off) != 0;
+#pragma unroll
+          for (int j = 0; j < 8; ++j) {
+            if (j < half) {
+              const float send_s = upper ? s[j] : s[j + half], send_q = upper ? sq[j] : sq[j + half];
+              const float keep_s = upper ? s[j + half] : s[j], keep_q = upper ? sq[j + half] : sq[j];
+              s[j] = keep_s + __shfl_xor_sync(0xffffffffu, send_s, off);
+              sq[j] = keep_q + __shfl_xor_sync(0xffffffffu, send_q, off);
+            }
+          }
+        }
+        s[0] += __shfl_xor_sync(0xffffffffu, s[0], 1);
+        sq[0] += __shfl_xor_sync(0xffffffffu, sq[0], 1);
+        const int c = ((lane >> 4) & 1) * 8 + ((lane >> 3) & 1) * 4 + ((lane >> 2) & 1) * 2 + ((lane >> 1) & 1);
+        if ((lane & 1) == 0 && has_cols) {  // partials [B][segs_per_image][4 quadrants][ld_part][2]
+          float2* dst = reinterpret_cast<float2*>(p.stats) +
+                        ((int64_t)(pb * p.segs_per_image + tw.sidx) * 4 + q) * p.ld_part + n0 + c0 + c;
+          *dst = make_float2(s[0], sq[0]);
+        }
+#pragma unroll
+        for (int j = 0; j < 16; ++j) s[j] = sq[j] = 0.f;
       }
     }
-    if (p.stats && cur_b >= 0) flush();
   }
   tc_fence_before();
   __syncthreads();
@@ -492,6 +612,7 @@ __global__ void __launch_bounds__(kTileThreads, 1) conv_tc_tile_kernel(const __g
     tmem_dealloc(tmem_acc, (uint32_t)p.tmem_cols);
   }
 }
+
 
 // ---- host side ------------------------------------------------------------------------------
 typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
@@ -615,16 +736,13 @@ extern "C" int ditsep_conv_tc_plan_create(ditsep_conv_plan** plan, const void* i
     }
     int dev = 0, sms = kNumSMs;
     if (cudaGetDevice(&dev) == cudaSuccess) cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+    // segments: the unit of work AND of the statistics partials; a function of the image shape only
+    p.seg_len = p.tiles_per_image >= 512 ? 4 : (p.tiles_per_image >= 128 ? 2 : 1);
+    p.segs_per_image = ceil_div(p.tiles_per_image, p.seg_len);
+    const int64_t n_segs = (int64_t)B * p.segs_per_image;
     grid_x = sms / p.n_tiles;
     if (grid_x < 1) grid_x = 1;
-    if (grid_x > p.num_tiles) grid_x = p.num_tiles;
-    // most images any CTA's contiguous tile range touches (= statistics flushes per CTA)
-    p.maxf = 1;
-    for (int c = 0; c < grid_x; ++c) {
-      const int64_t a = (int64_t)c * p.num_tiles / grid_x, b = (int64_t)(c + 1) * p.num_tiles / grid_x;
-      const int n = (int)((b - 1) / p.tiles_per_image - a / p.tiles_per_image) + 1;
-      if (n > p.maxf) p.maxf = n;
-    }
+    if (grid_x > n_segs) grid_x = (int)n_segs;
   }
 
   ditsep_conv_plan* pl = new ditsep_conv_plan();
@@ -664,7 +782,13 @@ extern "C" int ditsep_conv_tc_plan_create(ditsep_conv_plan** plan, const void* i
   if (!attr_set) {
     DITSEP_CUDA(cudaFuncSetAttribute(conv_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                      1024 + kMaxStages * (kABytes + 128 * 128)));
-    DITSEP_CUDA(cudaFuncSetAttribute(conv_tc_tile_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 224 * 1024));
+#define DITSEP_TILE_ATTR(KS, RES, FAST)                                                                              \
+  DITSEP_CUDA(cudaFuncSetAttribute(conv_tc_tile_kernel<KS, RES, FAST>, cudaFuncAttributeMaxDynamicSharedMemorySize, \
+                                   224 * 1024))
+    DITSEP_TILE_ATTR(1, true, true); DITSEP_TILE_ATTR(1, true, false); DITSEP_TILE_ATTR(1, false, true);
+    DITSEP_TILE_ATTR(1, false, false); DITSEP_TILE_ATTR(3, true, true); DITSEP_TILE_ATTR(3, true, false);
+    DITSEP_TILE_ATTR(3, false, true); DITSEP_TILE_ATTR(3, false, false);
+#undef DITSEP_TILE_ATTR
     attr_set = true;
   }
   *plan = pl;
@@ -677,13 +801,11 @@ extern "C" int ditsep_conv_tc_stats_layout(const ditsep_conv_plan* plan, ditsep_
   DITSEP_REQUIRE(plan && layout, "conv_tc_stats_layout: null pointer");
   memset(layout, 0, sizeof(*layout));
   if (!plan->tile) return 0;  // kind stays DITSEP_STATS_NONE: this plan cannot produce statistics
-  layout->kind = DITSEP_STATS_CONV_PARTIALS;
+  // [B][segs_per_image][4 TMEM lane quadrants][ld][2]: one partial per (segment, quadrant)
+  layout->kind = DITSEP_STATS_SPLIT_SUMS;
   layout->C = plan->p.Cout;
   layout->ld = plan->p.ld_part;
-  layout->n_part = plan->grid_x;
-  layout->maxf = plan->p.maxf;
-  layout->tiles_per_image = plan->p.tiles_per_image;
-  layout->num_tiles = plan->p.num_tiles;
+  layout->n_part = plan->p.segs_per_image * 4;
   return 0;
 }
 
@@ -702,7 +824,21 @@ extern "C" int ditsep_conv_tc_run(const ditsep_conv_plan* plan, const float* bia
   p.stats = stats;
   if (plan->tile) {
     dim3 grid((unsigned)plan->grid_x, (unsigned)p.n_tiles);
-    conv_tc_tile_kernel<<<grid, kTileThreads, plan->smem, (cudaStream_t)stream>>>(plan->mapA, plan->mapW, p);
+    cudaStream_t st = (cudaStream_t)stream;
+    const bool fast = p.Cout % 16 == 0 && out_dtype == DITSEP_BF16 && (ld_out & 7) == 0 &&
+                      (reinterpret_cast<uintptr_t>(out) & 15) == 0 &&
+                      (!residual || (res_dtype == DITSEP_BF16 && (ld_res & 7) == 0 &&
+                                     (reinterpret_cast<uintptr_t>(residual) & 15) == 0));
+#define DITSEP_TILE_LAUNCH(KS, RES, FAST) \
+  conv_tc_tile_kernel<KS, RES, FAST><<<grid, kTileThreads, plan->smem, st>>>(plan->mapA, plan->mapW, p)
+    if (p.ksize == 3) {
+      if (p.w_resident) { if (fast) DITSEP_TILE_LAUNCH(3, true, true); else DITSEP_TILE_LAUNCH(3, true, false); }
+      else { if (fast) DITSEP_TILE_LAUNCH(3, false, true); else DITSEP_TILE_LAUNCH(3, false, false); }
+    } else {
+      if (p.w_resident) { if (fast) DITSEP_TILE_LAUNCH(1, true, true); else DITSEP_TILE_LAUNCH(1, true, false); }
+      else { if (fast) DITSEP_TILE_LAUNCH(1, false, true); else DITSEP_TILE_LAUNCH(1, false, false); }
+    }
+#undef DITSEP_TILE_LAUNCH
     return check_launch("conv_tc_tile_kernel");
   }
   dim3 grid((unsigned)((int64_t)p.tiles_x * p.tiles_y * p.tiles_b), (unsigned)p.n_tiles);

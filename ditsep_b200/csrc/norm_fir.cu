@@ -107,45 +107,42 @@ struct StatsSrcs {
   int n;
 };
 
-__device__ __forceinline__ void stats_channel_sum(const ditsep_stats_src& src, int b, int c, double& a, double& q) {
-  a = 0.0;
-  q = 0.0;
-  if (src.kind == DITSEP_STATS_SPLIT_SUMS) {
-    for (int sidx = 0; sidx < src.n_part; ++sidx) {
-      const float* v = src.ptr + (((int64_t)b * src.n_part + sidx) * src.ld + c) * 2;
-      a += (double)v[0];
-      q += (double)v[1];
-    }
-  } else {  // DITSEP_STATS_CONV_PARTIALS: CTA k covered tiles [k*T/n, (k+1)*T/n)
-    const int64_t T = src.num_tiles, tpi = src.tiles_per_image;
-    const int64_t lo = (int64_t)b * tpi, hi = lo + tpi;
-    for (int k = 0; k < src.n_part; ++k) {
-      const int64_t t0 = (int64_t)k * T / src.n_part, t1 = (int64_t)(k + 1) * T / src.n_part;
-      if (t1 <= lo || t0 >= hi || t1 <= t0) continue;
-      const int f = b - (int)(t0 / tpi);
-      const float* v = src.ptr + (((int64_t)k * src.maxf + f) * src.ld + c) * 2;
-      a += (double)v[0];
-      q += (double)v[1];
-    }
-  }
-}
-
-__global__ void __launch_bounds__(256) gn_finalize_srcs_kernel(const StatsSrcs srcs, int64_t HW, int C, int G,
+__global__ void __launch_bounds__(512) gn_finalize_srcs_kernel(const StatsSrcs srcs, int64_t HW, int C, int G,
                                                                const float* __restrict__ gamma,
                                                                const float* __restrict__ beta, float eps,
                                                                float* __restrict__ scale_shift) {
-  extern __shared__ double sh[];  // [C][2] then [G][2]
+  extern __shared__ double sh[];  // [C][2], [G][2], [nj][C][2]
   double* chs = sh;
   double* grp = sh + 2 * C;
   const int b = blockIdx.x;
-  for (int c = threadIdx.x; c < C; c += blockDim.x) {
+  // thread -> (channel c, slice j of nj): slice j adds partials j, j+nj, ... ; the nj slice sums of a channel
+  // are then added in order.  nj depends on (C, blockDim) only: fixed order, bit-reproducible.
+  double* slice = sh + 2 * C + 2 * G;  // [nj][C][2]
+  const int nj = max(1, (int)blockDim.x / C);
+  for (int idx = threadIdx.x; idx < nj * C; idx += blockDim.x) {
+    const int c = idx % C, j = idx / C;
     int cc = c, i = 0;
     while (i < srcs.n - 1 && cc >= srcs.s[i].C) {
       cc -= srcs.s[i].C;
       ++i;
     }
-    double a, q;
-    stats_channel_sum(srcs.s[i], b, cc, a, q);
+    const ditsep_stats_src& src = srcs.s[i];
+    double a = 0.0, q = 0.0;
+    for (int k = j; k < src.n_part; k += nj) {
+      const float2 v = *reinterpret_cast<const float2*>(src.ptr + (((int64_t)b * src.n_part + k) * src.ld + cc) * 2);
+      a += (double)v.x;
+      q += (double)v.y;
+    }
+    slice[(j * C + c) * 2] = a;
+    slice[(j * C + c) * 2 + 1] = q;
+  }
+  __syncthreads();
+  for (int c = threadIdx.x; c < C; c += blockDim.x) {
+    double a = 0.0, q = 0.0;
+    for (int j = 0; j < nj; ++j) {
+      a += slice[(j * C + c) * 2];
+      q += slice[(j * C + c) * 2 + 1];
+    }
     chs[2 * c] = a;
     chs[2 * c + 1] = q;
   }
@@ -503,16 +500,16 @@ extern "C" int ditsep_gn_finalize(const ditsep_stats_src* host_srcs, int n_srcs,
   int C = 0;
   for (int i = 0; i < n_srcs; ++i) {
     const ditsep_stats_src& s = host_srcs[i];
-    DITSEP_REQUIRE(s.ptr && (s.kind == DITSEP_STATS_CONV_PARTIALS || s.kind == DITSEP_STATS_SPLIT_SUMS),
-                   "gn_finalize: source %d has no statistics (kind %d)", i, s.kind);
+    DITSEP_REQUIRE(s.ptr && s.kind == DITSEP_STATS_SPLIT_SUMS, "gn_finalize: source %d has no statistics (kind %d)", i,
+                   s.kind);
     DITSEP_REQUIRE(s.C > 0 && s.ld >= s.C && s.n_part > 0, "gn_finalize: source %d: bad C/ld/n_part", i);
-    DITSEP_REQUIRE(s.kind != DITSEP_STATS_CONV_PARTIALS || (s.maxf > 0 && s.tiles_per_image > 0 && s.num_tiles > 0),
-                   "gn_finalize: source %d: bad conv-partials layout", i);
     srcs.s[i] = s;
     C += s.C;
   }
   DITSEP_REQUIRE(B > 0 && HW > 0 && G > 0 && C % G == 0, "gn_finalize: bad sizes C=%d G=%d", C, G);
-  gn_finalize_srcs_kernel<<<B, 256, (size_t)(2 * C + 2 * G) * sizeof(double), (cudaStream_t)stream>>>(
+  DITSEP_REQUIRE(C <= 512, "gn_finalize: C=%d too wide", C);
+  const int threads = 512, nj = threads / C > 0 ? threads / C : 1;
+  gn_finalize_srcs_kernel<<<B, threads, (size_t)(2 * C + 2 * G + 2 * nj * C) * sizeof(double), (cudaStream_t)stream>>>(
       srcs, HW, C, G, gamma, beta, eps, scale_shift);
   return check_launch("gn_finalize_srcs_kernel");
 }

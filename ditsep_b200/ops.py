@@ -167,7 +167,7 @@ def gn_partial_floats(B: int, HW: int, C: int) -> int:
 
 def split_sums_layout(HW: int, C: int) -> "_lib.StatsSrc":
     """Statistics-source record (without pointer) of what gn_partial_sums leaves for an image of HW pixels."""
-    return _lib.StatsSrc(None, _lib.STATS_SPLIT_SUMS, C, C, gn_nsplit(HW, C), 0, 0, 0)
+    return _lib.StatsSrc(None, _lib.STATS_SPLIT_SUMS, C, C, gn_nsplit(HW, C))
 
 
 def gn_partial_sums(x, partial):
@@ -188,8 +188,7 @@ def gn_finalize(srcs, B: int, HW: int, G: int, gamma, beta, eps: float, scale_sh
     _cuda(gamma, beta, scale_shift, *(t for t, _ in srcs))
     arr = (_lib.StatsSrc * len(srcs))()
     for i, (t, lay) in enumerate(srcs):
-        arr[i] = _lib.StatsSrc(t.data_ptr(), lay.kind, lay.C, lay.ld, lay.n_part, lay.maxf, lay.tiles_per_image,
-                               lay.num_tiles)
+        arr[i] = _lib.StatsSrc(t.data_ptr(), lay.kind, lay.C, lay.ld, lay.n_part)
     check(_lib.load().ditsep_gn_finalize(arr, len(srcs), B, HW, G, _ptr(gamma), _ptr(beta), eps, _ptr(scale_shift),
                                          _stream()), "gn_finalize")
 
@@ -253,10 +252,10 @@ class ConvTcPlan:
 
     def stats_floats(self) -> int:
         lay = self.stats_layout()
-        return 0 if lay.kind == _lib.STATS_NONE else lay.n_part * lay.maxf * lay.ld * 2
+        return 0 if lay.kind == _lib.STATS_NONE else self.shape[0] * lay.n_part * lay.ld * 2
 
     def run(self, bias, out, bias_b=None, residual=None, out_scale: float = 1.0, stats=None):
-        """stats: f32 buffer of >= stats_floats() elements receiving the per-CTA statistics partials."""
+        """stats: f32 buffer of >= stats_floats() elements receiving the per-segment statistics partials."""
         _cuda(bias, out, bias_b, residual, stats)
         if stats is not None and (stats.dtype != torch.float32 or stats.numel() < max(1, self.stats_floats())):
             raise _lib.DitsepError("conv_tc: statistics buffer too small (or this plan cannot produce statistics)")

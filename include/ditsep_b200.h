@@ -101,18 +101,15 @@ int ditsep_gn_partial_sums(const void* x, int dtype, int B, int64_t HW, int C, i
 /* Where the per-channel {sum, sum of squares} of a tensor (or of a channel range of a concat
  * buffer) were left by its producer. */
 #define DITSEP_STATS_NONE 0
-#define DITSEP_STATS_CONV_PARTIALS 1 /* written by ditsep_conv_tc_run: [n_part][maxf][ld][2], one slot per
-                                        (CTA, image it touched); layout from ditsep_conv_tc_stats_layout */
-#define DITSEP_STATS_SPLIT_SUMS 2    /* [B][n_part][ld][2] (ditsep_gn_partial_sums; n_part = nsplit) */
+#define DITSEP_STATS_SPLIT_SUMS 2 /* [B][n_part][ld][2] partial sums: ditsep_gn_partial_sums (n_part = nsplit) or the
+                                     epilogue of ditsep_conv_tc_run (n_part = segments per image x 4, see
+                                     ditsep_conv_tc_stats_layout) */
 typedef struct {
   const float* ptr;
-  int32_t kind;            /* DITSEP_STATS_* */
-  int32_t C;               /* channels this source covers (they are consecutive in the normalised tensor) */
-  int32_t ld;              /* channel stride of the source rows */
-  int32_t n_part;          /* CTAs (conv partials) or splits (split sums) */
-  int32_t maxf;            /* conv partials: slots per CTA */
-  int32_t tiles_per_image; /* conv partials */
-  int32_t num_tiles;       /* conv partials */
+  int32_t kind;   /* DITSEP_STATS_* */
+  int32_t C;      /* channels this source covers (they are consecutive in the normalised tensor) */
+  int32_t ld;     /* channel stride of the source rows */
+  int32_t n_part; /* partials per image */
 } ditsep_stats_src;
 /* scale/shift of GroupNorm(G, C = sum of the sources' C) from up to 4 statistics sources laid end
  * to end along the channel axis (torch.cat([h, skip], dim=1) feeding GroupNorm_0, ncsnpp.py:413 +
@@ -153,8 +150,9 @@ int ditsep_conv_direct(const void* in, int dtype, int B, int H, int W, int Cin, 
  * `stats` (nullable, tile kernel only): the epilogue also leaves the per-image, per-channel
  * {sum, sum of squares} of the values it stores (the GroupNorm statistics of the output tensor,
  * layerspp.py:297,318) as per-CTA partials, so the consumer's GroupNorm needs no extra pass over
- * the tensor.  No atomics: bit-reproducible.  Size and layout: ditsep_conv_tc_stats_layout
- * (n_part * maxf * ld * 2 floats; kind DITSEP_STATS_NONE if the plan cannot produce them). */
+ * the tensor.  No atomics, and a summation order fixed by the image shape: bit-reproducible and
+ * batch-invariant.  Size and layout: ditsep_conv_tc_stats_layout (B * n_part * ld * 2 floats; kind
+ * DITSEP_STATS_NONE if the plan cannot produce them). */
 typedef struct ditsep_conv_plan ditsep_conv_plan;
 int ditsep_conv_tc_plan_create(ditsep_conv_plan** plan, const void* in, int B, int H, int W, int Cin, int ld_in,
                                const void* w_bf16, int Cout, int ksize);
