@@ -258,6 +258,9 @@ def profile_score_step(model, B, dev):
         plan = model.score_model.backbone.engine().plan(B, 256, 256, dev)
         rows = []
         evs = []
+        # park the GPU behind a ~30 ms spin so that the host (ctypes launch path, ~15 us per launch) runs ahead
+        # and every event interval below is pure device time, not launch latency
+        torch.cuda._sleep(int(30e-3 * 1.9e9))
         for fn, a, kw in plan.steps:
             e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
             e0.record()

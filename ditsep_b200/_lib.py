@@ -34,6 +34,7 @@ SIGNATURES = {
     "ditsep_abi_version": (c_int, []),
     "ditsep_last_error": (C.c_char_p, []),
     "ditsep_launch_count": (c_int64, []),
+    "ditsep_note_launches": (None, [c_int64]),
     "ditsep_pc_corrector": (c_int, [C.POINTER(SdeParams), c_void_p, c_void_p, c_void_p, c_uint64, c_uint64, c_void_p,
                                     c_void_p, c_int, c_int64, c_void_p]),
     "ditsep_pc_predictor": (c_int, [C.POINTER(SdeParams), c_void_p, c_void_p, c_void_p, c_uint64, c_uint64, c_void_p,

@@ -20,3 +20,4 @@ void set_error(const char* fmt, ...) {
 extern "C" int ditsep_abi_version(void) { return 1; }
 extern "C" const char* ditsep_last_error(void) { return ditsep::g_err; }
 extern "C" int64_t ditsep_launch_count(void) { return ditsep::g_launches.load(); }
+extern "C" void ditsep_note_launches(int64_t n) { ditsep::g_launches.fetch_add(n); }

@@ -128,8 +128,20 @@ __global__ void __launch_bounds__(512) gn_finalize_srcs_kernel(const StatsSrcs s
     }
     const ditsep_stats_src& src = srcs.s[i];
     double a = 0.0, q = 0.0;
-    for (int k = j; k < src.n_part; k += nj) {
-      const float2 v = *reinterpret_cast<const float2*>(src.ptr + (((int64_t)b * src.n_part + k) * src.ld + cc) * 2);
+    const float2* sp = reinterpret_cast<const float2*>(src.ptr) + (int64_t)b * src.n_part * src.ld + cc;
+    int k = j;
+    for (; k + 7 * nj < src.n_part; k += 8 * nj) {  // 8 independent loads in flight, added in index order
+      float2 v[8];
+#pragma unroll
+      for (int u = 0; u < 8; ++u) v[u] = sp[(int64_t)(k + u * nj) * src.ld];
+#pragma unroll
+      for (int u = 0; u < 8; ++u) {
+        a += (double)v[u].x;
+        q += (double)v[u].y;
+      }
+    }
+    for (; k < src.n_part; k += nj) {
+      const float2 v = sp[(int64_t)k * src.ld];
       a += (double)v.x;
       q += (double)v.y;
     }
@@ -171,26 +183,46 @@ __global__ void __launch_bounds__(512) gn_finalize_srcs_kernel(const StatsSrcs s
 }
 
 // ------------------------------------------------------------------- normalise + SiLU
+// grid (blocks per image, B); block = cv * ppb threads (cv = C/8 channel packs, ppb pixels in flight).  A thread
+// keeps ONE channel pack for its whole life, so the per-(b,c) scale / shift sit in registers and the loop body is
+// load 16 B (bf16) -> 8 fma + SiLU -> store 16 B, four pixels in flight per thread.
 template <typename T>
 __global__ void __launch_bounds__(256) gn_apply_kernel(const T* __restrict__ x, int64_t HW, int C, int ld_x,
                                                        const float* __restrict__ scale_shift, int silu,
-                                                       T* __restrict__ y, int ld_y, int64_t total_packs) {
-  const int cv = C / 8;
-  for (int64_t idx = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; idx < total_packs;
-       idx += (int64_t)gridDim.x * blockDim.x) {
-    const int v = (int)(idx % cv);
-    const int64_t pix = idx / cv;  // b * HW + p
-    const int b = (int)(pix / HW);
-    float f[8], sc[8], sh[8];
-    Pack8<T>::load(x + pix * ld_x + v * 8, f);
-    Pack8<float>::load(scale_shift + ((int64_t)b * 2) * C + v * 8, sc);
-    Pack8<float>::load(scale_shift + ((int64_t)b * 2 + 1) * C + v * 8, sh);
+                                                       T* __restrict__ y, int ld_y, int cv, int ppb) {
+  const int b = blockIdx.y;
+  const int v = threadIdx.x % cv, pp = threadIdx.x / cv;
+  if (pp >= ppb) return;
+  float sc[8], sh[8];
+  Pack8<float>::load(scale_shift + ((int64_t)b * 2) * C + v * 8, sc);
+  Pack8<float>::load(scale_shift + ((int64_t)b * 2 + 1) * C + v * 8, sh);
+  const T* xb = x + (int64_t)b * HW * ld_x + v * 8;
+  T* yb = y + (int64_t)b * HW * ld_y + v * 8;
+  const int64_t stride = (int64_t)gridDim.x * ppb;
+  int64_t p = (int64_t)blockIdx.x * ppb + pp;
+  for (; p + 3 * stride < HW; p += 4 * stride) {
+    float f[4][8];
+#pragma unroll
+    for (int u = 0; u < 4; ++u) Pack8<T>::load(xb + (p + u * stride) * ld_x, f[u]);
+#pragma unroll
+    for (int u = 0; u < 4; ++u) {
+#pragma unroll
+      for (int i = 0; i < 8; ++i) {
+        const float t = fmaf(f[u][i], sc[i], sh[i]);
+        f[u][i] = silu ? silu_f(t) : t;
+      }
+      Pack8<T>::store(yb + (p + u * stride) * ld_y, f[u]);
+    }
+  }
+  for (; p < HW; p += stride) {
+    float f[8];
+    Pack8<T>::load(xb + p * ld_x, f);
 #pragma unroll
     for (int i = 0; i < 8; ++i) {
-      float t = fmaf(f[i], sc[i], sh[i]);
+      const float t = fmaf(f[i], sc[i], sh[i]);
       f[i] = silu ? silu_f(t) : t;
     }
-    Pack8<T>::store(y + pix * ld_y + v * 8, f);
+    Pack8<T>::store(yb + p * ld_y, f);
   }
 }
 
@@ -518,14 +550,20 @@ extern "C" int ditsep_gn_apply(const void* x, int dtype, int B, int64_t HW, int 
                                int silu, void* y, int ld_y, void* stream) {
   DITSEP_REQUIRE(x && y && scale_shift, "gn_apply: null pointer");
   DITSEP_REQUIRE(C % 8 == 0 && ld_x % 8 == 0 && ld_y % 8 == 0, "gn_apply: C/ld must be multiples of 8");
-  const int64_t total = (int64_t)B * HW * (C / 8);
+  const int cv = C / 8;
+  DITSEP_REQUIRE(cv <= 256, "gn_apply: C=%d too wide", C);
+  const int ppb = 256 / cv;
+  // enough blocks to fill the machine a few times over, but at least 4 pixels per thread where the image allows
+  int64_t gx = (HW + (int64_t)ppb * 4 - 1) / ((int64_t)ppb * 4);
+  const int64_t cap = ((int64_t)kNumSMs * 16 + B - 1) / B;
+  if (gx > cap) gx = cap;
+  if (gx < 1) gx = 1;
+  dim3 grid((unsigned)gx, (unsigned)B);
   cudaStream_t st = (cudaStream_t)stream;
   if (dtype == DITSEP_F32)
-    gn_apply_kernel<float><<<grid_for(total), 256, 0, st>>>((const float*)x, HW, C, ld_x, scale_shift, silu, (float*)y,
-                                                            ld_y, total);
+    gn_apply_kernel<float><<<grid, 256, 0, st>>>((const float*)x, HW, C, ld_x, scale_shift, silu, (float*)y, ld_y, cv, ppb);
   else if (dtype == DITSEP_BF16)
-    gn_apply_kernel<bf16><<<grid_for(total), 256, 0, st>>>((const bf16*)x, HW, C, ld_x, scale_shift, silu, (bf16*)y,
-                                                           ld_y, total);
+    gn_apply_kernel<bf16><<<grid, 256, 0, st>>>((const bf16*)x, HW, C, ld_x, scale_shift, silu, (bf16*)y, ld_y, cv, ppb);
   else
     DITSEP_REQUIRE(false, "gn_apply: unknown dtype %d", dtype);
   return check_launch("gn_apply_kernel");

@@ -21,6 +21,7 @@ only kernel launches (no allocation, no host sync), which makes it CUDA-graph ca
 from __future__ import annotations
 
 import math
+import os
 from dataclasses import dataclass
 from typing import Dict, List, Optional, Tuple
 
@@ -234,6 +235,7 @@ class _Plan:
         cmax = max(max(s.in_ch, s.out_ch) for s in m.layout)
         self.gn_partial = new(B * 64 * cmax * 2, dtype=f32)  # scratch of the unfused statistics pass
         self._tc_plans = []
+        self._graph, self._graph_launches, self._runs = None, 0, 0
         # (data_ptr, channels) of a produced NHWC view -> (statistics buffer, layout): where its producer
         # left the per-channel sums GroupNorm needs (conv epilogue partials, or an explicit pass)
         self.stat_src: Dict[Tuple[int, int], Tuple[torch.Tensor, object]] = {}
@@ -474,6 +476,32 @@ class _Plan:
         pool.put(hn)
         pool.put(qkv)
 
-    def run(self):
+    def run_eager(self):
         for fn, args, kwargs in self.steps:
             fn(*args, **kwargs)
+
+    def run(self):
+        """One score-network evaluation.  The launch list touches only the plan's own buffers, so after one
+        eager pass it is captured into a CUDA graph and replayed: ~430 launches per evaluation become one
+        graph launch (at batch 1 the host launch path, not the GPU, bounds an eager step).
+        DITSEP_GRAPH=0 keeps it eager (debugging, per-launch timing)."""
+        if ops.EMULATED or os.environ.get("DITSEP_GRAPH", "1") == "0":
+            return self.run_eager()
+        if self._graph is None:
+            if self._runs == 0:  # first call: plain launches (loads modules, surfaces launch errors eagerly)
+                self._runs = 1
+                return self.run_eager()
+            n0 = ops.launch_count()
+            g = torch.cuda.CUDAGraph()
+            cur = torch.cuda.current_stream()
+            side = torch.cuda.Stream(device=self.device)
+            side.wait_stream(cur)
+            with torch.cuda.stream(side):
+                with torch.cuda.graph(g, stream=side, capture_error_mode="thread_local"):
+                    self.run_eager()
+            cur.wait_stream(side)
+            self._graph = g
+            self._graph_launches = ops.launch_count() - n0
+            ops.note_launches(-self._graph_launches)  # capture issued no work; replays are counted below
+        self._graph.replay()
+        ops.note_launches(self._graph_launches)

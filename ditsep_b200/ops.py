@@ -68,6 +68,11 @@ def launch_count() -> int:
     return int(_lib.load().ditsep_launch_count())
 
 
+def note_launches(n: int):
+    """Account for kernel launches the library did not see one by one (a captured CUDA graph being replayed)."""
+    _lib.load().ditsep_note_launches(n)
+
+
 # ------------------------------------------------------------------ SDE updates
 def _f32c(t: Optional[torch.Tensor], name: str):
     if t is None:

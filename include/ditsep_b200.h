@@ -47,6 +47,9 @@ int ditsep_abi_version(void);
 const char* ditsep_last_error(void);
 /* Number of kernel launches issued through this library since load (bench "gpu_launches"). */
 int64_t ditsep_launch_count(void);
+/* Adds n to that count: the host side calls it when it replays a captured CUDA graph of n library launches
+ * (and with -n after the capture pass, which issues no work). */
+void ditsep_note_launches(int64_t n);
 
 /* ---- fused SDE / predictor / corrector updates (fp32 state) ----------------------
  * x, score, x_mean: (B, n_src, L) contiguous; y: (B, 1, L); t: (B,).
