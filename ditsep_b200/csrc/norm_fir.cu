@@ -101,27 +101,31 @@ __global__ void __launch_bounds__(256) gn_finalize_kernel(const float* __restric
 
 // Per-channel {sum, sum of squares} left by the producers of the normalised tensor (up to 4
 // sources laid end to end along the channel axis, see ditsep_stats_src) -> per-(b,c) scale / shift.
-// grid B, block 256.  Fixed summation order, double accumulation.
+// grid (group chunks, B), block 256: a CTA owns gpc whole groups (nch = gpc * C/G channels) so that many
+// CTAs share the partial-sum traffic of one image (one CTA per image was latency-bound: 18 us for 8 MB,
+// r1e ncu).  Fixed summation order (a function of C, G and n_part only), double accumulation.
 struct StatsSrcs {
   ditsep_stats_src s[4];
   int n;
 };
 
-__global__ void __launch_bounds__(512) gn_finalize_srcs_kernel(const StatsSrcs srcs, int64_t HW, int C, int G,
+__global__ void __launch_bounds__(256) gn_finalize_srcs_kernel(const StatsSrcs srcs, int64_t HW, int C, int G, int gpc,
                                                                const float* __restrict__ gamma,
                                                                const float* __restrict__ beta, float eps,
                                                                float* __restrict__ scale_shift) {
-  extern __shared__ double sh[];  // [C][2], [G][2], [nj][C][2]
-  double* chs = sh;
-  double* grp = sh + 2 * C;
-  const int b = blockIdx.x;
-  // thread -> (channel c, slice j of nj): slice j adds partials j, j+nj, ... ; the nj slice sums of a channel
-  // are then added in order.  nj depends on (C, blockDim) only: fixed order, bit-reproducible.
-  double* slice = sh + 2 * C + 2 * G;  // [nj][C][2]
-  const int nj = max(1, (int)blockDim.x / C);
-  for (int idx = threadIdx.x; idx < nj * C; idx += blockDim.x) {
-    const int c = idx % C, j = idx / C;
-    int cc = c, i = 0;
+  extern __shared__ double sh[];  // [nj][nch][2]
+  __shared__ double grp[32][2];
+  const int b = blockIdx.y;
+  const int cpg = C / G;
+  const int g0 = blockIdx.x * gpc;
+  const int ng = min(gpc, G - g0);
+  const int c0 = g0 * cpg, nch = ng * cpg;
+  // thread -> (channel c of the chunk, slice j of nj): slice j adds partials j, j+nj, ...; the nj slice sums of
+  // a channel are then added in order
+  const int nj = max(1, (int)blockDim.x / (gpc * cpg));
+  for (int idx = threadIdx.x; idx < nj * nch; idx += blockDim.x) {
+    const int cl = idx % nch, j = idx / nch;
+    int cc = c0 + cl, i = 0;
     while (i < srcs.n - 1 && cc >= srcs.s[i].C) {
       cc -= srcs.s[i].C;
       ++i;
@@ -145,40 +149,31 @@ __global__ void __launch_bounds__(512) gn_finalize_srcs_kernel(const StatsSrcs s
       a += (double)v.x;
       q += (double)v.y;
     }
-    slice[(j * C + c) * 2] = a;
-    slice[(j * C + c) * 2 + 1] = q;
+    sh[(j * nch + cl) * 2] = a;
+    sh[(j * nch + cl) * 2 + 1] = q;
   }
   __syncthreads();
-  for (int c = threadIdx.x; c < C; c += blockDim.x) {
+  if ((int)threadIdx.x < ng) {
+    const int g = threadIdx.x;
     double a = 0.0, q = 0.0;
-    for (int j = 0; j < nj; ++j) {
-      a += slice[(j * C + c) * 2];
-      q += slice[(j * C + c) * 2 + 1];
-    }
-    chs[2 * c] = a;
-    chs[2 * c + 1] = q;
-  }
-  __syncthreads();
-  const int cpg = C / G;
-  for (int g = threadIdx.x; g < G; g += blockDim.x) {
-    double a = 0.0, q = 0.0;
-    for (int i = 0; i < cpg; ++i) {
-      a += chs[2 * (g * cpg + i)];
-      q += chs[2 * (g * cpg + i) + 1];
-    }
+    for (int i = 0; i < cpg; ++i)
+      for (int j = 0; j < nj; ++j) {
+        a += sh[(j * nch + g * cpg + i) * 2];
+        q += sh[(j * nch + g * cpg + i) * 2 + 1];
+      }
     const double n = (double)HW * cpg;
     const double mean = a / n;
     double var = q / n - mean * mean;
     if (var < 0.0) var = 0.0;
-    grp[2 * g] = mean;
-    grp[2 * g + 1] = 1.0 / sqrt(var + (double)eps);
+    grp[g][0] = mean;
+    grp[g][1] = 1.0 / sqrt(var + (double)eps);
   }
   __syncthreads();
-  for (int c = threadIdx.x; c < C; c += blockDim.x) {
-    const int g = c / cpg;
-    const double sc = grp[2 * g + 1] * (double)gamma[c];
+  for (int cl = threadIdx.x; cl < nch; cl += blockDim.x) {
+    const int g = cl / cpg, c = c0 + cl;
+    const double sc = grp[g][1] * (double)gamma[c];
     scale_shift[((int64_t)b * 2) * C + c] = (float)sc;
-    scale_shift[((int64_t)b * 2 + 1) * C + c] = (float)((double)beta[c] - grp[2 * g] * sc);
+    scale_shift[((int64_t)b * 2 + 1) * C + c] = (float)((double)beta[c] - grp[g][0] * sc);
   }
 }
 
@@ -229,118 +224,208 @@ __global__ void __launch_bounds__(256) gn_apply_kernel(const T* __restrict__ x, 
 // ------------------------------------------------------------------- FIR x2 resampling
 // Separable [1,3,3,1]: down = taps (1,3,3,1)/8 per axis at input 2o-1..2o+2 (zero outside);
 // up = polyphase: out[2i] = (x[i-1] + 3 x[i])/4, out[2i+1] = (3 x[i] + x[i+1])/4 per axis.
-// One thread = one channel pack of one OUTPUT pixel (down) or one INPUT pixel -> 2x2 outputs
-// (up).  If scale_shift != nullptr a second output gets FIR(SiLU(x*scale+shift)).
+// If scale_shift != nullptr a second output gets FIR(SiLU(x*scale+shift)).
+//
+// Column-strip kernels: a thread owns one 8-channel pack of one output column (down) / input column (up)
+// and walks a segment of rows.  Each input row is filtered horizontally ONCE per thread and its result is
+// added into the (at most two) output rows it contributes to, so SiLU is evaluated 2x (down) / 3x (up) per
+// input element instead of 4x / 9x for a one-thread-per-output-pixel stencil (that version was issue-bound at
+// 9 % of HBM peak, r1e ncu); neighbouring threads re-read the overlapping pixels from L1.  Channel packs are
+// the fastest thread index: a warp reads whole 128-byte pixel rows.
+template <typename T, bool kDual>
+__device__ __forceinline__ void fir_load_px(const T* __restrict__ p, bool ok, const float (&sc)[8], const float (&sh)[8],
+                                            float (&f)[8], float (&h)[8]) {
+  if (ok) {
+    Pack8<T>::load(p, f);
+    if (kDual) {
+#pragma unroll
+      for (int i = 0; i < 8; ++i) h[i] = silu_f(fmaf(f[i], sc[i], sh[i]));
+    }
+  } else {  // zero padding applies to the activated tensor too (the FIR pads AFTER GroupNorm + SiLU)
+#pragma unroll
+    for (int i = 0; i < 8; ++i) f[i] = h[i] = 0.f;
+  }
+}
+
 template <typename T, bool kDual>
 __global__ void __launch_bounds__(256) fir_down_kernel(const T* __restrict__ x, int H, int W, int C, int ld_x,
                                                        const float* __restrict__ scale_shift, T* __restrict__ out_x,
-                                                       int ld_ox, T* __restrict__ out_h, int ld_oh, int64_t total) {
+                                                       int ld_ox, T* __restrict__ out_h, int ld_oh, int seg_rows,
+                                                       int n_seg, int64_t total) {
   const int cv = C / 8, Ho = H / 2, Wo = W / 2;
+  const int64_t idx = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (idx >= total) return;
+  const int v = (int)(idx % cv);
+  int64_t r = idx / cv;
+  const int ox = (int)(r % Wo);
+  r /= Wo;
+  const int seg = (int)(r % n_seg);
+  const int b = (int)(r / n_seg);
+  const int oy0 = seg * seg_rows, oy1 = min(oy0 + seg_rows, Ho);
+  float sc[8], sh[8];
+  if (kDual) {
+    Pack8<float>::load(scale_shift + ((int64_t)b * 2) * C + v * 8, sc);
+    Pack8<float>::load(scale_shift + ((int64_t)b * 2 + 1) * C + v * 8, sh);
+  }
   const float kw[4] = {0.125f, 0.375f, 0.375f, 0.125f};
-  for (int64_t idx = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; idx < total;
-       idx += (int64_t)gridDim.x * blockDim.x) {
-    const int v = (int)(idx % cv);
-    int64_t r = idx / cv;
-    const int ox = (int)(r % Wo);
-    r /= Wo;
-    const int oy = (int)(r % Ho);
-    const int b = (int)(r / Ho);
-    float sc[8], sh[8];
-    if (kDual) {
-      Pack8<float>::load(scale_shift + ((int64_t)b * 2) * C + v * 8, sc);
-      Pack8<float>::load(scale_shift + ((int64_t)b * 2 + 1) * C + v * 8, sh);
-    }
-    float ax[8], ah[8];
+  const T* xb = x + (int64_t)b * H * W * ld_x + v * 8;
+  // acc0: output row oy (receives input rows 2oy-1 .. 2oy+2), acc1: output row oy+1
+  float ax0[8], ah0[8], ax1[8], ah1[8];
 #pragma unroll
-    for (int i = 0; i < 8; ++i) ax[i] = ah[i] = 0.f;
+  for (int i = 0; i < 8; ++i) ax0[i] = ah0[i] = ax1[i] = ah1[i] = 0.f;
+  const int ix0 = 2 * ox - 1;
+  for (int iy = 2 * oy0 - 1; iy <= 2 * oy1; ++iy) {
+    // horizontal pass of input row iy at this output column
+    float hx[8], hh[8];
 #pragma unroll
-    for (int a = 0; a < 4; ++a) {
-      const int iy = 2 * oy + a - 1;
-      if (iy < 0 || iy >= H) continue;
+    for (int i = 0; i < 8; ++i) hx[i] = hh[i] = 0.f;
+    if (iy >= 0 && iy < H) {
+      const T* row = xb + (int64_t)iy * W * ld_x;
+      float f[4][8], g[4][8];
 #pragma unroll
       for (int c = 0; c < 4; ++c) {
-        const int ix = 2 * ox + c - 1;
-        if (ix < 0 || ix >= W) continue;
-        float f[8];
-        Pack8<T>::load(x + (((int64_t)b * H + iy) * W + ix) * ld_x + v * 8, f);
-        const float w = kw[a] * kw[c];
+        const int ix = ix0 + c;
+        fir_load_px<T, kDual>(row + (int64_t)ix * ld_x, ix >= 0 && ix < W, sc, sh, f[c], g[c]);
+      }
+#pragma unroll
+      for (int c = 0; c < 4; ++c)
 #pragma unroll
         for (int i = 0; i < 8; ++i) {
-          ax[i] = fmaf(w, f[i], ax[i]);
-          if (kDual) ah[i] = fmaf(w, silu_f(fmaf(f[i], sc[i], sh[i])), ah[i]);
+          hx[i] = fmaf(kw[c], f[c][i], hx[i]);
+          if (kDual) hh[i] = fmaf(kw[c], g[c][i], hh[i]);
         }
+    }
+    // vertical: row iy is tap a0 = iy - (2oy-1) of output row oy and tap a0-2 of row oy+1 (oy = (iy+1)/2 rounded down
+    // for the newer one).  Walk: rel = iy - (2*oy0 - 1); the current "acc0" row is o = oy0 + (rel >> 1) - 1 ... kept
+    // simple by tracking the tap index explicitly.
+    const int rel = iy - (2 * oy0 - 1);      // 0, 1, 2, ...
+    const int a_new = rel & 1;               // tap of the newer output row (acc1): 0 or 1; the older row (acc0) is at tap + 2
+    const float w_new = a_new ? 0.375f : 0.125f, w_old = a_new ? 0.125f : 0.375f;
+#pragma unroll
+    for (int i = 0; i < 8; ++i) {
+      ax0[i] = fmaf(w_old, hx[i], ax0[i]);
+      ax1[i] = fmaf(w_new, hx[i], ax1[i]);
+      if (kDual) {
+        ah0[i] = fmaf(w_old, hh[i], ah0[i]);
+        ah1[i] = fmaf(w_new, hh[i], ah1[i]);
       }
     }
-    const int64_t opix = ((int64_t)b * Ho + oy) * Wo + ox;
-    if (out_x) Pack8<T>::store(out_x + opix * ld_ox + v * 8, ax);
-    if (kDual) Pack8<T>::store(out_h + opix * ld_oh + v * 8, ah);
+    if (a_new == 1) {  // acc0 has seen its last tap (3): emit output row o = oy0 + rel/2 - 1, then shift
+      const int o = oy0 + (rel >> 1) - 1;
+      if (o >= oy0 && o < oy1) {
+        const int64_t opix = ((int64_t)b * Ho + o) * Wo + ox;
+        if (out_x) Pack8<T>::store(out_x + opix * ld_ox + v * 8, ax0);
+        if (kDual) Pack8<T>::store(out_h + opix * ld_oh + v * 8, ah0);
+      }
+#pragma unroll
+      for (int i = 0; i < 8; ++i) {
+        ax0[i] = ax1[i];
+        ah0[i] = ah1[i];
+        ax1[i] = ah1[i] = 0.f;
+      }
+    }
   }
 }
 
 template <typename T, bool kDual>
 __global__ void __launch_bounds__(256) fir_up_kernel(const T* __restrict__ x, int H, int W, int C, int ld_x,
                                                      const float* __restrict__ scale_shift, T* __restrict__ out_x,
-                                                     int ld_ox, T* __restrict__ out_h, int ld_oh, int64_t total) {
+                                                     int ld_ox, T* __restrict__ out_h, int ld_oh, int seg_rows, int n_seg,
+                                                     int64_t total) {
   const int cv = C / 8, Ho = 2 * H, Wo = 2 * W;
-  for (int64_t idx = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; idx < total;
-       idx += (int64_t)gridDim.x * blockDim.x) {
-    const int v = (int)(idx % cv);
-    int64_t r = idx / cv;
-    const int ix = (int)(r % W);
-    r /= W;
-    const int iy = (int)(r % H);
-    const int b = (int)(r / H);
-    float sc[8], sh[8];
-    if (kDual) {
-      Pack8<float>::load(scale_shift + ((int64_t)b * 2) * C + v * 8, sc);
-      Pack8<float>::load(scale_shift + ((int64_t)b * 2 + 1) * C + v * 8, sh);
-    }
-    // out[2i+dy][2j+dx] = sum over (ry, rx) in the 3x3 neighbourhood with per-axis weights
-    // dy=0: rows (i-1: 1/4, i: 3/4) ; dy=1: rows (i: 3/4, i+1: 1/4)
-    float ox[4][8], oh[4][8];
+  const int64_t idx = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (idx >= total) return;
+  const int v = (int)(idx % cv);
+  int64_t r = idx / cv;
+  const int ix = (int)(r % W);
+  r /= W;
+  const int seg = (int)(r % n_seg);
+  const int b = (int)(r / n_seg);
+  const int r0 = seg * seg_rows, r1 = min(r0 + seg_rows, H);
+  float sc[8], sh[8];
+  if (kDual) {
+    Pack8<float>::load(scale_shift + ((int64_t)b * 2) * C + v * 8, sc);
+    Pack8<float>::load(scale_shift + ((int64_t)b * 2 + 1) * C + v * 8, sh);
+  }
+  const T* xb = x + (int64_t)b * H * W * ld_x + v * 8;
+  // horizontally filtered previous input row: [even output column 2ix | odd output column 2ix+1]
+  float pxe[8], pxo[8], phe[8], pho[8];
 #pragma unroll
-    for (int o = 0; o < 4; ++o)
+  for (int i = 0; i < 8; ++i) pxe[i] = pxo[i] = phe[i] = pho[i] = 0.f;
+  for (int iy = r0 - 1; iy <= r1; ++iy) {
+    float cxe[8], cxo[8], che[8], cho[8];
+    if (iy >= 0 && iy < H) {
+      const T* row = xb + (int64_t)iy * W * ld_x;
+      float f[3][8], g[3][8];
 #pragma unroll
-      for (int i = 0; i < 8; ++i) ox[o][i] = oh[o][i] = 0.f;
+      for (int c = 0; c < 3; ++c) {
+        const int xx = ix + c - 1;
+        fir_load_px<T, kDual>(row + (int64_t)xx * ld_x, xx >= 0 && xx < W, sc, sh, f[c], g[c]);
+      }
 #pragma unroll
-    for (int ry = -1; ry <= 1; ++ry) {
-      const int yy = iy + ry;
-      if (yy < 0 || yy >= H) continue;
-      const float wy0 = (ry == -1) ? 0.25f : (ry == 0 ? 0.75f : 0.f);
-      const float wy1 = (ry == 1) ? 0.25f : (ry == 0 ? 0.75f : 0.f);
-#pragma unroll
-      for (int rx = -1; rx <= 1; ++rx) {
-        const int xx = ix + rx;
-        if (xx < 0 || xx >= W) continue;
-        const float wx0 = (rx == -1) ? 0.25f : (rx == 0 ? 0.75f : 0.f);
-        const float wx1 = (rx == 1) ? 0.25f : (rx == 0 ? 0.75f : 0.f);
-        float f[8];
-        Pack8<T>::load(x + (((int64_t)b * H + yy) * W + xx) * ld_x + v * 8, f);
-        const float w00 = wy0 * wx0, w01 = wy0 * wx1, w10 = wy1 * wx0, w11 = wy1 * wx1;
-#pragma unroll
-        for (int i = 0; i < 8; ++i) {
-          ox[0][i] = fmaf(w00, f[i], ox[0][i]);
-          ox[1][i] = fmaf(w01, f[i], ox[1][i]);
-          ox[2][i] = fmaf(w10, f[i], ox[2][i]);
-          ox[3][i] = fmaf(w11, f[i], ox[3][i]);
-          if (kDual) {
-            const float hh = silu_f(fmaf(f[i], sc[i], sh[i]));
-            oh[0][i] = fmaf(w00, hh, oh[0][i]);
-            oh[1][i] = fmaf(w01, hh, oh[1][i]);
-            oh[2][i] = fmaf(w10, hh, oh[2][i]);
-            oh[3][i] = fmaf(w11, hh, oh[3][i]);
-          }
+      for (int i = 0; i < 8; ++i) {
+        cxe[i] = fmaf(0.75f, f[1][i], 0.25f * f[0][i]);
+        cxo[i] = fmaf(0.75f, f[1][i], 0.25f * f[2][i]);
+        if (kDual) {
+          che[i] = fmaf(0.75f, g[1][i], 0.25f * g[0][i]);
+          cho[i] = fmaf(0.75f, g[1][i], 0.25f * g[2][i]);
         }
       }
+    } else {
+#pragma unroll
+      for (int i = 0; i < 8; ++i) cxe[i] = cxo[i] = che[i] = cho[i] = 0.f;
+    }
+    // on arrival of filtered row iy: output row 2(iy-1)+1 = (3 prev + cur)/4, output row 2iy = (prev + 3 cur)/4
+    float o0[8], o1[8];
+    if (iy - 1 >= r0) {
+      const int64_t opix = ((int64_t)b * Ho + 2 * (iy - 1) + 1) * Wo + 2 * ix;
+      if (out_x) {
+#pragma unroll
+        for (int i = 0; i < 8; ++i) {
+          o0[i] = fmaf(0.75f, pxe[i], 0.25f * cxe[i]);
+          o1[i] = fmaf(0.75f, pxo[i], 0.25f * cxo[i]);
+        }
+        Pack8<T>::store(out_x + opix * ld_ox + v * 8, o0);
+        Pack8<T>::store(out_x + (opix + 1) * ld_ox + v * 8, o1);
+      }
+      if (kDual) {
+#pragma unroll
+        for (int i = 0; i < 8; ++i) {
+          o0[i] = fmaf(0.75f, phe[i], 0.25f * che[i]);
+          o1[i] = fmaf(0.75f, pho[i], 0.25f * cho[i]);
+        }
+        Pack8<T>::store(out_h + opix * ld_oh + v * 8, o0);
+        Pack8<T>::store(out_h + (opix + 1) * ld_oh + v * 8, o1);
+      }
+    }
+    if (iy >= r0 && iy < r1) {
+      const int64_t opix = ((int64_t)b * Ho + 2 * iy) * Wo + 2 * ix;
+      if (out_x) {
+#pragma unroll
+        for (int i = 0; i < 8; ++i) {
+          o0[i] = fmaf(0.75f, cxe[i], 0.25f * pxe[i]);
+          o1[i] = fmaf(0.75f, cxo[i], 0.25f * pxo[i]);
+        }
+        Pack8<T>::store(out_x + opix * ld_ox + v * 8, o0);
+        Pack8<T>::store(out_x + (opix + 1) * ld_ox + v * 8, o1);
+      }
+      if (kDual) {
+#pragma unroll
+        for (int i = 0; i < 8; ++i) {
+          o0[i] = fmaf(0.75f, che[i], 0.25f * phe[i]);
+          o1[i] = fmaf(0.75f, cho[i], 0.25f * pho[i]);
+        }
+        Pack8<T>::store(out_h + opix * ld_oh + v * 8, o0);
+        Pack8<T>::store(out_h + (opix + 1) * ld_oh + v * 8, o1);
+      }
     }
 #pragma unroll
-    for (int dy = 0; dy < 2; ++dy)
-#pragma unroll
-      for (int dx = 0; dx < 2; ++dx) {
-        const int64_t opix = ((int64_t)b * Ho + 2 * iy + dy) * Wo + 2 * ix + dx;
-        if (out_x) Pack8<T>::store(out_x + opix * ld_ox + v * 8, ox[dy * 2 + dx]);
-        if (kDual) Pack8<T>::store(out_h + opix * ld_oh + v * 8, oh[dy * 2 + dx]);
-      }
+    for (int i = 0; i < 8; ++i) {
+      pxe[i] = cxe[i];
+      pxo[i] = cxo[i];
+      phe[i] = che[i];
+      pho[i] = cho[i];
+    }
   }
 }
 
@@ -540,9 +625,15 @@ extern "C" int ditsep_gn_finalize(const ditsep_stats_src* host_srcs, int n_srcs,
   }
   DITSEP_REQUIRE(B > 0 && HW > 0 && G > 0 && C % G == 0, "gn_finalize: bad sizes C=%d G=%d", C, G);
   DITSEP_REQUIRE(C <= 512, "gn_finalize: C=%d too wide", C);
-  const int threads = 512, nj = threads / C > 0 ? threads / C : 1;
-  gn_finalize_srcs_kernel<<<B, threads, (size_t)(2 * C + 2 * G + 2 * nj * C) * sizeof(double), (cudaStream_t)stream>>>(
-      srcs, HW, C, G, gamma, beta, eps, scale_shift);
+  const int cpg = C / G;
+  DITSEP_REQUIRE(cpg <= 256, "gn_finalize: %d channels per group is too wide", cpg);
+  int gpc = 16 / cpg;  // ~16 channels per CTA
+  if (gpc < 1) gpc = 1;
+  if (gpc > 32) gpc = 32;
+  const int threads = 256, nj = threads / (gpc * cpg) > 0 ? threads / (gpc * cpg) : 1;
+  dim3 grid((unsigned)ceil_div(G, gpc), (unsigned)B);
+  gn_finalize_srcs_kernel<<<grid, threads, (size_t)(2 * nj * gpc * cpg) * sizeof(double), (cudaStream_t)stream>>>(
+      srcs, HW, C, G, gpc, gamma, beta, eps, scale_shift);
   return check_launch("gn_finalize_srcs_kernel");
 }
 
@@ -582,19 +673,24 @@ static int fir_dispatch(const T* x, int B, int H, int W, int C, int ld_x, int up
   DITSEP_REQUIRE((out_x == nullptr || ld_ox % 8 == 0) && (out_h == nullptr || ld_oh % 8 == 0),
                  "fir_resample: output strides must be multiples of 8");
   const int cv = C / 8;
+  // rows per strip: long strips amortise the 2-row warm-up, but keep >= ~8 threads per SM lane-slot in flight
+  const int cols = up ? W : W / 2, rows = up ? H : H / 2;
+  int seg_rows = rows;
+  while (seg_rows > 4 && (int64_t)B * cols * cv * ceil_div(rows, seg_rows) < (int64_t)kNumSMs * 2048) seg_rows = (seg_rows + 1) / 2;
+  const int n_seg = ceil_div(rows, seg_rows);
+  const int64_t total = (int64_t)B * n_seg * cols * cv;
+  const unsigned grid = (unsigned)((total + 255) / 256);
   if (up) {
-    const int64_t total = (int64_t)B * H * W * cv;
     if (ss)
-      fir_up_kernel<T, true><<<grid_for(total), 256, 0, st>>>(x, H, W, C, ld_x, ss, out_x, ld_ox, out_h, ld_oh, total);
+      fir_up_kernel<T, true><<<grid, 256, 0, st>>>(x, H, W, C, ld_x, ss, out_x, ld_ox, out_h, ld_oh, seg_rows, n_seg, total);
     else
-      fir_up_kernel<T, false><<<grid_for(total), 256, 0, st>>>(x, H, W, C, ld_x, ss, out_x, ld_ox, out_h, ld_oh, total);
+      fir_up_kernel<T, false><<<grid, 256, 0, st>>>(x, H, W, C, ld_x, ss, out_x, ld_ox, out_h, ld_oh, seg_rows, n_seg, total);
     return check_launch("fir_up_kernel");
   }
-  const int64_t total = (int64_t)B * (H / 2) * (W / 2) * cv;
   if (ss)
-    fir_down_kernel<T, true><<<grid_for(total), 256, 0, st>>>(x, H, W, C, ld_x, ss, out_x, ld_ox, out_h, ld_oh, total);
+    fir_down_kernel<T, true><<<grid, 256, 0, st>>>(x, H, W, C, ld_x, ss, out_x, ld_ox, out_h, ld_oh, seg_rows, n_seg, total);
   else
-    fir_down_kernel<T, false><<<grid_for(total), 256, 0, st>>>(x, H, W, C, ld_x, ss, out_x, ld_ox, out_h, ld_oh, total);
+    fir_down_kernel<T, false><<<grid, 256, 0, st>>>(x, H, W, C, ld_x, ss, out_x, ld_ox, out_h, ld_oh, seg_rows, n_seg, total);
   return check_launch("fir_down_kernel");
 }
 

@@ -33,6 +33,25 @@ __device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
     if (++spins > (1u << 28)) __trap();
   }
 }
+// Same, for the many warps that wait a long time (16 epilogue warps on "accumulator full", the TMA producer on
+// "stage empty"): the suspend-time hint parks the thread in hardware until the phase completes instead of
+// re-issuing the probe -- the polling loops were 16 % of all issued instructions of the conv kernel (r1e ncu).
+__device__ __forceinline__ void mbar_wait_sleep(uint32_t bar, uint32_t parity) {
+  long long t0 = 0;
+  for (uint32_t spins = 0;; ++spins) {
+    uint32_t ok;
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2, %3;\n\t"
+        "selp.u32 %0, 1, 0, p;\n\t}"
+        : "=r"(ok)
+        : "r"(bar), "r"(parity), "r"(20000u)
+        : "memory");
+    if (ok) return;
+    if (spins == 0) t0 = clock64();
+    else if ((spins & 63u) == 0 && clock64() - t0 > 6000000000ll) __trap();  // ~3 s: a protocol bug must not hang the GPU
+  }
+}
 __device__ __forceinline__ void tma_load_4d(uint32_t dst, const CUtensorMap* map, uint32_t bar, int c0, int c1, int c2,
                                             int c3) {
   asm volatile(
