@@ -98,9 +98,16 @@ struct Pack8<bf16> {
   }
 };
 
-// SiLU with two MUFU ops (ex2, rcp) and three FP32 ops; __fdividef avoids the IEEE-division slow path
-// (which made the GroupNorm-apply kernel issue-bound: 22 instructions per element, r1e ncu).  2 ulp.
-__device__ __forceinline__ float silu_f(float x) { return __fdividef(x, 1.0f + __expf(-x)); }
+// SiLU in exactly five instructions (FMUL, MUFU.EX2, FADD, MUFU.RCP, FMUL): explicit .ftz approximations,
+// because `x / (1 + __expf(-x))` compiles to an IEEE division (GroupNorm-apply was issue-bound at 22
+// instructions per element, r1e ncu) and even __fdividef / __expf carry denormal-range fix-ups without -ftz.
+// ex2.approx and rcp.approx are good to 2 ulp; x -> -inf gives x * rcp(inf) = -0, x -> +inf gives x.
+__device__ __forceinline__ float silu_f(float x) {
+  float e, r;
+  asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(e) : "f"(x * -1.4426950408889634f));
+  asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(1.0f + e));
+  return x * r;
+}
 
 __device__ __forceinline__ float warp_sum(float v) {
 #pragma unroll

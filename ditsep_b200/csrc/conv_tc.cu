@@ -429,33 +429,59 @@ __global__ void __launch_bounds__(kTileThreads, 1) conv_tc_tile_kernel(const __g
         mbar_wait(smem_u32(&bar_a_full[sa]), pa);
         tc_fence_after();
         const uint32_t a_lo = ((a_ring + (uint32_t)(sa * p.a_stage_bytes)) >> 4) | lbo;
+        constexpr int kRow16 = 128 >> 4;
+        if constexpr (kRes) {
+          // Resident filter: nothing to wait for between taps, so ONE elected region issues all kTaps * 4 MMAs of
+          // the chunk back to back.  (With an elect / reconverge per tap the issuing warp spent ~34 instructions,
+          // six of them R2UR, per 4 MMAs: ~310 cycles per tap against 128 cycles of tensor work -- r1g ncu: the MMA
+          // warp never waited on a barrier and the pipe was 42 % busy.)
+          if (elect_one_sync()) {
+            // The tap loop stays ROLLED: fully unrolled, ptxas hoists all 72 descriptor words to the front and
+            // spills uniform registers (MOV.SPILL / R2UR.FILL), 7 instructions per MMA.  Rolled, a tap is 4 MMAs
+            // plus a handful of uniform adds; the descriptors advance incrementally.
+            uint32_t a_cur = a_lo, w_cur = w_lo, acc = (uint32_t)(ch != 0);
+#pragma unroll 1
+            for (int row = 0; row < KS; ++row) {   // one filter row (KS taps, 4 MMAs each) per trip
 #pragma unroll
-        for (int tap = 0; tap < kTaps; ++tap) {
-          if (!kRes) {
+              for (int col = 0; col < KS; ++col) {
+#pragma unroll
+                for (int k = 0; k < kBlockK / 16; ++k) {
+                  const uint64_t da = ((uint64_t)a_hi << 32) | (uint64_t)(a_cur + col * kRow16 + 2 * k);
+                  const uint64_t db = ((uint64_t)b_hi << 32) | (uint64_t)(w_cur + 2 * k);
+                  umma_bf16(tmem_d, da, db, idesc, (col | k) != 0 ? 1u : acc);
+                }
+                w_cur += w_step;
+              }
+              acc = 1u;
+              a_cur += (uint32_t)(kRowPitch * kRow16);
+            }
+            umma_commit(smem_u32(&bar_a_empty[sa]));
+            if (ch == p.chunks - 1) umma_commit(smem_u32(&bar_acc_full[ab]));
+          }
+          __syncwarp();
+          w_lo += (uint32_t)kTaps * w_step;
+        } else {
+#pragma unroll
+          for (int tap = 0; tap < kTaps; ++tap) {
             mbar_wait(smem_u32(&bar_w_full[sw]), pw);
             tc_fence_after();
             w_lo = ((base + (uint32_t)sw * w_tile_bytes) >> 4) | lbo;
-          }
-          constexpr int kRow16 = 128 >> 4;
-          const uint32_t a_tap = a_lo + (uint32_t)(((tap / KS) * kRowPitch + (tap % KS)) * kRow16);
-          if (elect_one_sync()) {
+            const uint32_t a_tap = a_lo + (uint32_t)(((tap / KS) * kRowPitch + (tap % KS)) * kRow16);
+            if (elect_one_sync()) {
 #pragma unroll
-            for (int k = 0; k < kBlockK / 16; ++k) {
-              const uint64_t da = ((uint64_t)a_hi << 32) | (uint64_t)(a_tap + 2 * k);
-              const uint64_t db = ((uint64_t)b_hi << 32) | (uint64_t)(w_lo + 2 * k);
-              umma_bf16(tmem_d, da, db, idesc, (tap | k) != 0 ? 1u : (uint32_t)(ch != 0));
+              for (int k = 0; k < kBlockK / 16; ++k) {
+                const uint64_t da = ((uint64_t)a_hi << 32) | (uint64_t)(a_tap + 2 * k);
+                const uint64_t db = ((uint64_t)b_hi << 32) | (uint64_t)(w_lo + 2 * k);
+                umma_bf16(tmem_d, da, db, idesc, (tap | k) != 0 ? 1u : (uint32_t)(ch != 0));
+              }
+              umma_commit(smem_u32(&bar_w_empty[sw]));
+              if (tap == kTaps - 1) {
+                umma_commit(smem_u32(&bar_a_empty[sa]));
+                if (ch == p.chunks - 1) umma_commit(smem_u32(&bar_acc_full[ab]));
+              }
             }
-            if (!kRes) umma_commit(smem_u32(&bar_w_empty[sw]));
-            if (tap == kTaps - 1) {
-              umma_commit(smem_u32(&bar_a_empty[sa]));
-              if (ch == p.chunks - 1) umma_commit(smem_u32(&bar_acc_full[ab]));
-            }
-          }
-          __syncwarp();
-          if (!kRes) {
+            __syncwarp();
             if (++sw == p.w_stages) { sw = 0; pw ^= 1u; }
-          } else {
-            w_lo += w_step;
           }
         }
         if (++sa == p.a_stages) { sa = 0; pa ^= 1u; }

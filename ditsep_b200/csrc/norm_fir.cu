@@ -248,10 +248,36 @@ __device__ __forceinline__ void fir_load_px(const T* __restrict__ p, bool ok, co
 }
 
 template <typename T, bool kDual>
-__global__ void __launch_bounds__(256) fir_down_kernel(const T* __restrict__ x, int H, int W, int C, int ld_x,
-                                                       const float* __restrict__ scale_shift, T* __restrict__ out_x,
-                                                       int ld_ox, T* __restrict__ out_h, int ld_oh, int seg_rows,
-                                                       int n_seg, int64_t total) {
+__device__ __forceinline__ void fir_down_hrow(const T* __restrict__ xb, int iy, int H, int W, int ld_x, int ix0,
+                                              const float (&sc)[8], const float (&sh)[8], float (&hx)[8], float (&hh)[8]) {
+  // horizontal pass of input row iy at one output column: taps (1,3,3,1)/8 at ix0 .. ix0+3
+#pragma unroll
+  for (int i = 0; i < 8; ++i) hx[i] = hh[i] = 0.f;
+  if (iy < 0 || iy >= H) return;
+  const T* row = xb + (int64_t)iy * W * ld_x;
+#pragma unroll
+  for (int c = 0; c < 4; ++c) {
+    const int ix = ix0 + c;
+    const float w = (c == 0 || c == 3) ? 0.125f : 0.375f;
+    float f[8], g[8];
+    fir_load_px<T, kDual>(row + (int64_t)ix * ld_x, ix >= 0 && ix < W, sc, sh, f, g);
+#pragma unroll
+    for (int i = 0; i < 8; ++i) {
+      hx[i] = fmaf(w, f[i], hx[i]);
+      if (kDual) hh[i] = fmaf(w, g[i], hh[i]);
+    }
+  }
+}
+
+// r1g ncu of the first strip version: 146 registers -> one CTA (8 warps) per SM, 12 % occupancy, latency-bound at
+// 11 % of HBM peak with 46 instructions per input element.  Now: two CTAs per SM (launch bound), and the row loop
+// advances TWO input rows per trip so the vertical taps are compile-time constants and the accumulator hand-over
+// (row oy+1 becomes row oy) is a register rename instead of a select + copy.
+template <typename T, bool kDual>
+__global__ void __launch_bounds__(256, 2) fir_down_kernel(const T* __restrict__ x, int H, int W, int C, int ld_x,
+                                                          const float* __restrict__ scale_shift, T* __restrict__ out_x,
+                                                          int ld_ox, T* __restrict__ out_h, int ld_oh, int seg_rows,
+                                                          int n_seg, int64_t total) {
   const int cv = C / 8, Ho = H / 2, Wo = W / 2;
   const int64_t idx = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
   if (idx >= total) return;
@@ -267,63 +293,38 @@ __global__ void __launch_bounds__(256) fir_down_kernel(const T* __restrict__ x, 
     Pack8<float>::load(scale_shift + ((int64_t)b * 2) * C + v * 8, sc);
     Pack8<float>::load(scale_shift + ((int64_t)b * 2 + 1) * C + v * 8, sh);
   }
-  const float kw[4] = {0.125f, 0.375f, 0.375f, 0.125f};
   const T* xb = x + (int64_t)b * H * W * ld_x + v * 8;
-  // acc0: output row oy (receives input rows 2oy-1 .. 2oy+2), acc1: output row oy+1
-  float ax0[8], ah0[8], ax1[8], ah1[8];
-#pragma unroll
-  for (int i = 0; i < 8; ++i) ax0[i] = ah0[i] = ax1[i] = ah1[i] = 0.f;
   const int ix0 = 2 * ox - 1;
-  for (int iy = 2 * oy0 - 1; iy <= 2 * oy1; ++iy) {
-    // horizontal pass of input row iy at this output column
-    float hx[8], hh[8];
-#pragma unroll
-    for (int i = 0; i < 8; ++i) hx[i] = hh[i] = 0.f;
-    if (iy >= 0 && iy < H) {
-      const T* row = xb + (int64_t)iy * W * ld_x;
-      float f[4][8], g[4][8];
-#pragma unroll
-      for (int c = 0; c < 4; ++c) {
-        const int ix = ix0 + c;
-        fir_load_px<T, kDual>(row + (int64_t)ix * ld_x, ix >= 0 && ix < W, sc, sh, f[c], g[c]);
-      }
-#pragma unroll
-      for (int c = 0; c < 4; ++c)
-#pragma unroll
-        for (int i = 0; i < 8; ++i) {
-          hx[i] = fmaf(kw[c], f[c][i], hx[i]);
-          if (kDual) hh[i] = fmaf(kw[c], g[c][i], hh[i]);
-        }
-    }
-    // vertical: row iy is tap a0 = iy - (2oy-1) of output row oy and tap a0-2 of row oy+1 (oy = (iy+1)/2 rounded down
-    // for the newer one).  Walk: rel = iy - (2*oy0 - 1); the current "acc0" row is o = oy0 + (rel >> 1) - 1 ... kept
-    // simple by tracking the tap index explicitly.
-    const int rel = iy - (2 * oy0 - 1);      // 0, 1, 2, ...
-    const int a_new = rel & 1;               // tap of the newer output row (acc1): 0 or 1; the older row (acc0) is at tap + 2
-    const float w_new = a_new ? 0.375f : 0.125f, w_old = a_new ? 0.125f : 0.375f;
+  // output row oy = 1/8 r(2oy-1) + 3/8 r(2oy) + 3/8 r(2oy+1) + 1/8 r(2oy+2), r() = horizontally filtered input row.
+  // carry = 1/8 r(2oy-1) + 3/8 r(2oy): the part of row oy that the previous trip already saw.
+  float cx[8], chh[8];
+  {
+    float ax[8], ah[8], bx[8], bh[8];
+    fir_down_hrow<T, kDual>(xb, 2 * oy0 - 1, H, W, ld_x, ix0, sc, sh, ax, ah);
+    fir_down_hrow<T, kDual>(xb, 2 * oy0, H, W, ld_x, ix0, sc, sh, bx, bh);
 #pragma unroll
     for (int i = 0; i < 8; ++i) {
-      ax0[i] = fmaf(w_old, hx[i], ax0[i]);
-      ax1[i] = fmaf(w_new, hx[i], ax1[i]);
-      if (kDual) {
-        ah0[i] = fmaf(w_old, hh[i], ah0[i]);
-        ah1[i] = fmaf(w_new, hh[i], ah1[i]);
-      }
+      cx[i] = fmaf(0.375f, bx[i], 0.125f * ax[i]);
+      chh[i] = fmaf(0.375f, bh[i], 0.125f * ah[i]);
     }
-    if (a_new == 1) {  // acc0 has seen its last tap (3): emit output row o = oy0 + rel/2 - 1, then shift
-      const int o = oy0 + (rel >> 1) - 1;
-      if (o >= oy0 && o < oy1) {
-        const int64_t opix = ((int64_t)b * Ho + o) * Wo + ox;
-        if (out_x) Pack8<T>::store(out_x + opix * ld_ox + v * 8, ax0);
-        if (kDual) Pack8<T>::store(out_h + opix * ld_oh + v * 8, ah0);
-      }
+  }
+  for (int oy = oy0; oy < oy1; ++oy) {
+    float ax[8], ah[8], bx[8], bh[8];  // rows 2oy+1 and 2oy+2
+    fir_down_hrow<T, kDual>(xb, 2 * oy + 1, H, W, ld_x, ix0, sc, sh, ax, ah);
+    fir_down_hrow<T, kDual>(xb, 2 * oy + 2, H, W, ld_x, ix0, sc, sh, bx, bh);
+    float ox_[8], oh_[8];
 #pragma unroll
-      for (int i = 0; i < 8; ++i) {
-        ax0[i] = ax1[i];
-        ah0[i] = ah1[i];
-        ax1[i] = ah1[i] = 0.f;
+    for (int i = 0; i < 8; ++i) {
+      ox_[i] = fmaf(0.125f, bx[i], fmaf(0.375f, ax[i], cx[i]));
+      cx[i] = fmaf(0.375f, bx[i], 0.125f * ax[i]);  // rows 2oy+1, 2oy+2 are taps 0, 1 of output row oy+1
+      if (kDual) {
+        oh_[i] = fmaf(0.125f, bh[i], fmaf(0.375f, ah[i], chh[i]));
+        chh[i] = fmaf(0.375f, bh[i], 0.125f * ah[i]);
       }
     }
+    const int64_t opix = ((int64_t)b * Ho + oy) * Wo + ox;
+    if (out_x) Pack8<T>::store(out_x + opix * ld_ox + v * 8, ox_);
+    if (kDual) Pack8<T>::store(out_h + opix * ld_oh + v * 8, oh_);
   }
 }
 
