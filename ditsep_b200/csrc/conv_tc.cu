@@ -43,6 +43,7 @@ constexpr int kBlockK = 64;  // bf16 elements = 128 bytes = one swizzle row
 constexpr int kABytes = kTileM * kBlockK * 2;
 constexpr int kMaxStages = 6;
 constexpr int kThreads = 192;
+constexpr int kTraceTiles = 96, kTraceCtas = 4;
 
 struct ConvTcParams {
   int B, H, W, Cin, Cout, taps, ksize;
@@ -62,7 +63,13 @@ struct ConvTcParams {
   int halo, row_pitch, a_rows, a_stage_bytes;
   float* stats;            // nullable: partial sums [B][segs_per_image][4][ld_part][2]
   int seg_len, segs_per_image, ld_part;
+  long long* trace;        // debug (ditsep_debug_conv_trace): [4 CTAs][kTraceTiles][8] clock64 stamps, else nullptr
 };
+
+__device__ __forceinline__ void trace_stamp(const ConvTcParams& p, uint32_t it, int slot) {
+  if (p.trace && blockIdx.x < kTraceCtas && blockIdx.y == 0 && it < kTraceTiles)
+    p.trace[((int64_t)blockIdx.x * kTraceTiles + it) * 8 + slot] = clock64();
+}
 
 // ---- shared epilogue -----------------------------------------------------------------------
 // One thread = one output pixel (TMEM lane), 16 consecutive output channels.  v: raw fp32
@@ -377,9 +384,11 @@ __global__ void __launch_bounds__(kTileThreads, 1) conv_tc_tile_kernel(const __g
       int sa = 0, sw = 0;
       uint32_t pa = 1, pw = 1;  // "empty" barriers start free: the first pass waits on the opposite parity
       TileWalk tw;
-      for (tw.init(p); !tw.done(); tw.next(p)) {
+      uint32_t itp = 0;
+      for (tw.init(p); !tw.done(); tw.next(p), ++itp) {
         for (int ch = 0; ch < p.chunks; ++ch) {
           mbar_wait_sleep(smem_u32(&bar_a_empty[sa]), pa);
+          if (ch == 0) trace_stamp(p, itp, 6);
           const uint32_t full = smem_u32(&bar_a_full[sa]);
           mbar_expect_tx(full, (uint32_t)(p.a_rows * 128));
           tma_load_4d(a_ring + (uint32_t)(sa * p.a_stage_bytes), &mapA, full, ch * kBlockK, tw.tx * kTileW - kHalo,
@@ -423,11 +432,13 @@ __global__ void __launch_bounds__(kTileThreads, 1) conv_tc_tile_kernel(const __g
       const uint32_t ab = it & 1u;
       mbar_wait(smem_u32(&bar_acc_empty[ab]), ((it >> 1) & 1u) ^ 1u);
       tc_fence_after();
+      if (lane == 0) trace_stamp(p, it, 0);
       const uint32_t tmem_d = tmem_acc + ab * (uint32_t)p.BN;
       uint32_t w_lo = (base >> 4) | lbo;
       for (int ch = 0; ch < p.chunks; ++ch) {
         mbar_wait(smem_u32(&bar_a_full[sa]), pa);
         tc_fence_after();
+        if (ch == 0 && lane == 0) trace_stamp(p, it, 1);
         const uint32_t a_lo = ((a_ring + (uint32_t)(sa * p.a_stage_bytes)) >> 4) | lbo;
         constexpr int kRow16 = 128 >> 4;
         if constexpr (kRes) {
@@ -486,6 +497,7 @@ __global__ void __launch_bounds__(kTileThreads, 1) conv_tc_tile_kernel(const __g
         }
         if (++sa == p.a_stages) { sa = 0; pa ^= 1u; }
       }
+      if (lane == 0) trace_stamp(p, it, 2);
     }
   } else if (warp >= kCtrlWarps) {
     const int e = warp - kCtrlWarps;
@@ -538,6 +550,7 @@ __global__ void __launch_bounds__(kTileThreads, 1) conv_tc_tile_kernel(const __g
       const uint32_t ab = it & 1u;
       mbar_wait_sleep(smem_u32(&bar_acc_full[ab]), (it >> 1) & 1u);
       tc_fence_after();
+      if (e == 0 && lane == 0) trace_stamp(p, it, 3);
       if constexpr (fast) {
         // two passes of 8 channels keep the live set small: v[8] -> 4 packed bf16 pairs -> one 16-byte store
         uint32_t va[8], vb[8];
@@ -549,6 +562,7 @@ __global__ void __launch_bounds__(kTileThreads, 1) conv_tc_tile_kernel(const __g
         tc_fence_before();
         __syncwarp();
         if (lane == 0) mbar_arrive(smem_u32(&bar_acc_empty[ab]));  // accumulator handed back
+        if (e == 0 && lane == 0) trace_stamp(p, it, 4);
         if (active) {
           uint4* op = reinterpret_cast<uint4*>(reinterpret_cast<bf16*>(p.out) + pix * p.ld_out + n0 + c0);
           const float osc = p.out_scale;
@@ -616,6 +630,7 @@ __global__ void __launch_bounds__(kTileThreads, 1) conv_tc_tile_kernel(const __g
           }
         }
       }
+      if (e == 0 && lane == 0) trace_stamp(p, it, 5);
       if (p.stats && tw.last_of_segment()) {
         // warp-level transpose-reduce: after offsets 16, 8, 4, 2 lane l holds channel
         // c = 8*b4 + 4*b3 + 2*b2 + b1 (bits of l) summed over 16 lanes; offset 1 completes it
@@ -837,6 +852,9 @@ extern "C" int ditsep_conv_tc_plan_create(ditsep_conv_plan** plan, const void* i
   return 0;
 }
 
+static long long* g_conv_trace = nullptr;
+extern "C" void ditsep_debug_conv_trace(void* buf) { g_conv_trace = reinterpret_cast<long long*>(buf); }
+
 extern "C" void ditsep_conv_tc_plan_destroy(ditsep_conv_plan* plan) { delete plan; }
 
 extern "C" int ditsep_conv_tc_stats_layout(const ditsep_conv_plan* plan, ditsep_stats_src* layout) {
@@ -864,6 +882,7 @@ extern "C" int ditsep_conv_tc_run(const ditsep_conv_plan* plan, const float* bia
   p.residual = residual; p.res_dtype = res_dtype; p.ld_res = ld_res;
   p.out_scale = out_scale; p.out = out; p.out_dtype = out_dtype; p.ld_out = ld_out;
   p.stats = stats;
+  p.trace = g_conv_trace;
   if (plan->tile) {
     dim3 grid((unsigned)plan->grid_x, (unsigned)p.n_tiles);
     cudaStream_t st = (cudaStream_t)stream;

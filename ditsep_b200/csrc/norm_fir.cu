@@ -477,6 +477,38 @@ __global__ void __launch_bounds__(256) fir_narrow_kernel(const T* __restrict__ x
   }
 }
 
+// ------------------------------------------------------------------- hi/lo split of a narrow fp32 tensor
+// The network's first layer has 2(n+1) = 6 input channels: too narrow for the tensor-core kernel (K blocks of 64)
+// and, on CUDA cores, 1.06 ms per score step at batch 32 (r1g ncu).  This kernel widens it to a 64-channel bf16
+// tensor the tcgen05 kernel accepts WITHOUT giving up fp32 input accuracy: channels [0,C) = hi = bf16(x),
+// [C,2C) = lo = bf16(x - hi), [2C,3C) = hi again, the rest zero; against filter channels [wh | wh | wl]
+// (w = wh + wl) the tensor core computes xh*wh + xl*wh + xh*wl = x*w to ~2^-16.
+// One thread = 8 output channels (16 bytes) of one pixel.
+__global__ void __launch_bounds__(256) split_hilo_kernel(const float* __restrict__ x, int64_t npix, int C, bf16* __restrict__ out,
+                                                         int ld) {
+  const int cv = ld / 8;
+  const int64_t total = npix * cv;
+  for (int64_t idx = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; idx < total;
+       idx += (int64_t)gridDim.x * blockDim.x) {
+    const int v = (int)(idx % cv);
+    const int64_t pix = idx / cv;
+    float f[8];
+#pragma unroll
+    for (int i = 0; i < 8; ++i) {
+      const int j = v * 8 + i;
+      float val = 0.f;
+      if (j < 3 * C) {
+        const int kind = j / C;
+        const float xv = __ldg(x + pix * C + (j - kind * C));
+        const float hi = __bfloat162float(__float2bfloat16_rn(xv));
+        val = (kind == 1) ? xv - hi : hi;
+      }
+      f[i] = val;
+    }
+    Pack8<bf16>::store(out + pix * ld + v * 8, f);
+  }
+}
+
 // ------------------------------------------------------------------- time embedding
 // grid B, block 256.  smem: feat[2nf] | hid[4nf]
 __global__ void __launch_bounds__(256) temb_mlp_kernel(const float* __restrict__ t, const float* __restrict__ gfp_w,
@@ -710,6 +742,14 @@ extern "C" int ditsep_fir_resample(const void* x, int dtype, int B, int H, int W
     return fir_dispatch<bf16>((const bf16*)x, B, H, W, C, ld_x, up, scale_shift, (bf16*)out_x, ld_ox, (bf16*)out_h,
                               ld_oh, st);
   DITSEP_REQUIRE(false, "fir_resample: unknown dtype %d", dtype);
+}
+
+extern "C" int ditsep_split_hilo(const float* x, int64_t npix, int C, void* out_bf16, int ld, void* stream) {
+  DITSEP_REQUIRE(x && out_bf16, "split_hilo: null pointer");
+  DITSEP_REQUIRE(npix > 0 && C > 0 && ld % 8 == 0 && 3 * C <= ld, "split_hilo: need 3*C <= ld, ld %% 8 == 0 (C=%d ld=%d)", C, ld);
+  DITSEP_REQUIRE((reinterpret_cast<uintptr_t>(out_bf16) & 15) == 0, "split_hilo: output must be 16-byte aligned");
+  split_hilo_kernel<<<grid_for(npix * (ld / 8)), 256, 0, (cudaStream_t)stream>>>(x, npix, C, (bf16*)out_bf16, ld);
+  return check_launch("split_hilo_kernel");
 }
 
 extern "C" int ditsep_temb_mlp(const float* t, const float* gfp_w, const float* w1, const float* b1, const float* w2,

@@ -119,6 +119,23 @@ def _pack_conv(weight: torch.Tensor, bias: torch.Tensor, want_bf16: bool) -> _Co
     return _ConvW(w, bias.detach().float().contiguous(), kh, wb)
 
 
+def _pack_conv_hilo(weight: torch.Tensor, bias: torch.Tensor, width: int = 64) -> Optional[_ConvW]:
+    """First-layer filter for the tensor-core path (ops.split_hilo): input channels [wh | wh | wl | 0] with
+    w = wh + wl in bf16, matching activations [xh | xl | xh | 0]; (Cout, Cin, kh, kw) -> [CoutPad][tap][width]."""
+    cout, cin, kh, kw = weight.shape
+    if 3 * cin > width:
+        return None
+    w = weight.detach().float().permute(0, 2, 3, 1).reshape(cout, kh * kw, cin)
+    wh = w.to(torch.bfloat16)
+    wl = (w - wh.float()).to(torch.bfloat16)
+    cp = (cout + 15) // 16 * 16
+    wb = torch.zeros(cp, kh * kw, width, device=w.device, dtype=torch.bfloat16)
+    wb[:cout, :, 0:cin] = wh
+    wb[:cout, :, cin:2 * cin] = wh
+    wb[:cout, :, 2 * cin:3 * cin] = wl
+    return _ConvW(wb[:cout].float(), bias.detach().float().contiguous(), kh, wb)
+
+
 class NcsnppEngine:
     def __init__(self, model):
         self.m = model
@@ -148,6 +165,8 @@ class NcsnppEngine:
                 w[f"lin{i}"] = (mod.weight.detach().float().contiguous(), mod.bias.detach().float().contiguous())
             elif spec.kind == "conv3x3":
                 w[f"conv{i}"] = _pack_conv(mod.weight, mod.bias, bf)
+                if bf and i == 3:  # the input conv: tensor-core variant over the hi/lo-split features
+                    w["conv3_hilo"] = _pack_conv_hilo(mod.weight, mod.bias)
             elif spec.kind == "gn":
                 w[f"gn{i}"] = (mod.weight.detach().float().contiguous(), mod.bias.detach().float().contiguous())
             elif spec.kind == "combine":
@@ -284,7 +303,15 @@ class _Plan:
         pyr_in = self.feat
         k = 0
         cur = skip_slot(k)
-        self._conv(self.feat, w["conv3"], cur, want_stats=True)
+        hilo = w.get("conv3_hilo")
+        if hilo is not None and adt == torch.bfloat16 and not ops.EMULATED and ops.tc_enabled():
+            # first layer on the tensor cores: 6 fp32 channels widened to [hi | lo | hi | 0] bf16 (ops.split_hilo);
+            # channels >= 3*Cin0 are zeroed once here and never written again
+            self.feat_tc = torch.zeros(B, H, W, hilo.cin, device=device, dtype=torch.bfloat16)
+            add((ops.split_hilo, (self.feat, self.feat_tc), {}))
+            self._conv(self.feat_tc, hilo, cur, want_stats=True)
+        else:
+            self._conv(self.feat, w["conv3"], cur, want_stats=True)
         k += 1
         i = 4
         for lvl in range(R):

@@ -232,6 +232,15 @@ def conv_direct(x, w, bias, out, ksize: int, bias_b=None, residual=None, out_sca
           "conv_direct")
 
 
+def split_hilo(x, out):
+    """x (B,H,W,C) f32 contiguous -> out (B,H,W,ld) bf16 = [hi | lo | hi | 0] (ditsep_split_hilo)."""
+    _cuda(x, out)
+    if x.dtype != torch.float32 or out.dtype != torch.bfloat16 or not x.is_contiguous() or not out.is_contiguous():
+        raise _lib.DitsepError("split_hilo: x must be contiguous f32, out contiguous bf16")
+    B, H, W, Cc = x.shape
+    check(_lib.load().ditsep_split_hilo(_ptr(x), B * H * W, Cc, _ptr(out), out.shape[3], _stream()), "split_hilo")
+
+
 class ConvTcPlan:
     """Owns a ditsep_conv_plan (TMA descriptors for one input tensor + weight binding)."""
 

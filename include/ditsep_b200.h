@@ -143,6 +143,12 @@ int ditsep_conv_direct(const void* in, int dtype, int B, int H, int W, int Cin, 
                        const float* bias, const float* bias_b, int ld_bias_b, const void* residual, int ld_res,
                        float out_scale, int Cout, int ksize, void* out, int out_dtype, int ld_out, void* stream);
 
+/* Widens a narrow fp32 NHWC tensor x [npix][C] (the 2(n+1)-channel STFT features feeding the network's first
+ * ddpm_conv3x3, ncsnpp.py:352-356) to a bf16 tensor [npix][ld] the tcgen05 path accepts, keeping fp32 accuracy:
+ * channels [0,C) = hi = bf16(x), [C,2C) = lo = bf16(x - hi), [2C,3C) = hi, [3C,ld) = 0.  Pair it with a filter whose
+ * input channels are [wh | wh | wl] (w = wh + wl in bf16).  Needs 3*C <= ld, ld % 8 == 0. */
+int ditsep_split_hilo(const float* x, int64_t npix, int C, void* out_bf16, int ld, void* stream);
+
 /* tcgen05 implicit-GEMM path (bf16 operands, fp32 TMEM accumulators, TMA-fed).
  * Requirements: Cin % 64 == 0, Cout padded to a multiple of 16 inside `w` (and to a multiple of
  * 64 when > 128), `in` 16-byte aligned with ld_in % 8 == 0.  w: [CoutPad][taps][Cin] bf16.
@@ -164,6 +170,11 @@ int ditsep_conv_tc_stats_layout(const ditsep_conv_plan* plan, ditsep_stats_src* 
 int ditsep_conv_tc_run(const ditsep_conv_plan* plan, const float* bias, const float* bias_b, int ld_bias_b,
                        const void* residual, int res_dtype, int ld_res, float out_scale, void* out, int out_dtype,
                        int ld_out, float* stats, void* stream);
+
+/* Debug aid (scripts/trace_conv.py): while buf != NULL, the tile kernel's first 4 CTAs write clock64() stamps of their
+ * first 96 tiles to buf ([4][96][8] int64: 0 accumulator free, 1 first A tile landed, 2 MMAs issued, 3 accumulator
+ * full seen by the epilogue, 4 TMEM read + handed back, 5 tile stored, 6 TMA issued).  NULL disarms it. */
+void ditsep_debug_conv_trace(void* buf);
 
 /* ---- attention (single head, all H*W tokens) ------------------------------------------
  * AttnBlockpp.forward core (layerspp.py:88-92): o = softmax(q k^T / sqrt(C)) v per image.

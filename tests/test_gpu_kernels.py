@@ -298,6 +298,32 @@ def test_conv_tc(B, H, W, Cin, ld_extra, Cout, k):
     assert rel(out2.float(), ref) < 4e-3
 
 
+def test_first_layer_hilo_split_on_tensor_cores():
+    """ops.split_hilo + the [wh | wh | wl] filter (engine._pack_conv_hilo): the 6-channel fp32 input conv run by the
+    tcgen05 kernel must match the fp32 convolution to fp32-class accuracy, not bf16-class."""
+    from ditsep_b200.models.diffsep.engine import _pack_conv_hilo
+    B, H, W, Cin, Cout = 2, 32, 24, 6, 64
+    x = torch.randn(B, H, W, Cin, generator=g(70))
+    weight = torch.randn(Cout, Cin, 3, 3, generator=g(71)) / math.sqrt(9 * Cin)
+    bias = 0.1 * torch.randn(Cout, generator=g(72))
+    wide = torch.full((B, H, W, 64), 7.0, device=DEV, dtype=torch.bfloat16)
+    ops.split_hilo(x.to(DEV), wide)
+    hi = x.to(torch.bfloat16)
+    lo = (x - hi.float()).to(torch.bfloat16)
+    assert torch.equal(wide[..., :6].cpu(), hi) and torch.equal(wide[..., 6:12].cpu(), lo)
+    assert torch.equal(wide[..., 12:18].cpu(), hi) and not wide[..., 18:].any()
+    cw = _pack_conv_hilo(weight.to(DEV), bias.to(DEV))
+    assert cw.cout == Cout and cw.cin == 64
+    plan = ops.ConvTcPlan(wide, cw.w_bf16, Cout, 3)
+    out = torch.empty(B, H, W, Cout, device=DEV)
+    plan.run(cw.bias, out)
+    ref = torch.empty(B, H, W, Cout)
+    E.conv_direct(x, weight.permute(0, 2, 3, 1).reshape(Cout, 9, Cin).contiguous(), bias, ref, 3)
+    e = rel(out, ref)
+    print(f"hi/lo first layer vs fp32 conv: rel-L2 {e:.3e}")
+    assert e < 5e-5, e
+
+
 def test_gn_finalize_concat_sources():
     """GroupNorm over torch.cat([h, skip]) (ncsnpp.py:413) from two producers' statistics: a conv
     epilogue's partials for h (128 ch) and an explicit split-sums pass for skip (64 ch); 6-channel groups
