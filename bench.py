@@ -222,6 +222,16 @@ def run_ours(args):
         k = name.split(":")[0]
         by_kind[k] = by_kind.get(k, 0.0) + ms
     roofline["ms_by_kernel_class"] = {k: round(v, 3) for k, v in sorted(by_kind.items(), key=lambda kv: -kv[1])}
+    dump = os.environ.get("DITSEP_BENCH_DUMP")
+    if dump and rank == 0:  # per-launch-shape table of the profiled score step (count, total ms, TFLOP/s)
+        agg = {}
+        for name, ms, fl in prof:
+            c = agg.setdefault(name, [0, 0.0, 0.0])
+            c[0] += 1; c[1] += ms; c[2] += fl
+        with open(dump, "w") as f:
+            for name, (cnt, ms, fl) in sorted(agg.items(), key=lambda kv: -kv[1][1]):
+                f.write(f"{name:44s} n={cnt:3d} total {ms:8.3f} ms  avg {1e3 * ms / cnt:8.1f} us"
+                        + (f"  {fl / ms / 1e9:7.1f} TFLOP/s" if fl else "") + "\n")
 
     line = None
     if rank == 0:
@@ -280,6 +290,8 @@ def profile_score_step(model, B, dev):
                 x, w = a[0], a[1]
                 fl = 2.0 * x.shape[0] * x.shape[1] * x.shape[2] * w.shape[0] * w.shape[1] * w.shape[2]
                 name = f"conv_direct:{x.shape[1]}x{x.shape[2]}:{w.shape[1] * w.shape[2]}->{w.shape[0]}"
+            elif a and hasattr(a[0], "shape") and len(a[0].shape) == 4:
+                name = f"{name}:{a[0].shape[1]}x{a[0].shape[2]}x{a[0].shape[3]}"
             rows.append((name, e0.elapsed_time(e1), fl))
     return rows
 

@@ -428,50 +428,102 @@ __global__ void __launch_bounds__(kTileThreads, 1) conv_tc_tile_kernel(const __g
     int sa = 0, sw = 0;
     uint32_t pa = 0, pw = 0, it = 0;
     TileWalk tw;
-    for (tw.init(p); !tw.done(); tw.next(p), ++it) {
-      const uint32_t ab = it & 1u;
-      mbar_wait(smem_u32(&bar_acc_empty[ab]), ((it >> 1) & 1u) ^ 1u);
-      tc_fence_after();
-      if (lane == 0) trace_stamp(p, it, 0);
-      const uint32_t tmem_d = tmem_acc + ab * (uint32_t)p.BN;
-      uint32_t w_lo = (base >> 4) | lbo;
-      for (int ch = 0; ch < p.chunks; ++ch) {
-        mbar_wait(smem_u32(&bar_a_full[sa]), pa);
+    if constexpr (kRes) {
+      // Resident filter.  A step = one K chunk of one tile = KS filter rows of KS * 4 MMAs.  The tensor pipe's queue is
+      // only a few MMAs deep, and a barrier probe + tcgen05 fence costs the issuing thread several hundred cycles
+      // even when the phase completed long ago (r1i clock64 trace: ~760 idle cycles between the last MMA of a tile
+      // and the first of the next).  So the readiness of step s+1 (its A stage, and its accumulator when it opens a
+      // new tile) is awaited BEFORE the last filter row of step s is issued: the probes run under a full queue.
+      constexpr int kRow16 = 128 >> 4;
+      tw.init(p);
+      bool more = !tw.done();
+      if (more) {
+        mbar_wait(smem_u32(&bar_acc_empty[0]), 1u);
+        mbar_wait(smem_u32(&bar_a_full[0]), 0u);
         tc_fence_after();
-        if (ch == 0 && lane == 0) trace_stamp(p, it, 1);
-        const uint32_t a_lo = ((a_ring + (uint32_t)(sa * p.a_stage_bytes)) >> 4) | lbo;
-        constexpr int kRow16 = 128 >> 4;
-        if constexpr (kRes) {
-          // Resident filter: nothing to wait for between taps, so ONE elected region issues all kTaps * 4 MMAs of
-          // the chunk back to back.  (With an elect / reconverge per tap the issuing warp spent ~34 instructions,
-          // six of them R2UR, per 4 MMAs: ~310 cycles per tap against 128 cycles of tensor work -- r1g ncu: the MMA
-          // warp never waited on a barrier and the pipe was 42 % busy.)
-          if (elect_one_sync()) {
-            // The tap loop stays ROLLED: fully unrolled, ptxas hoists all 72 descriptor words to the front and
-            // spills uniform registers (MOV.SPILL / R2UR.FILL), 7 instructions per MMA.  Rolled, a tap is 4 MMAs
-            // plus a handful of uniform adds; the descriptors advance incrementally.
-            uint32_t a_cur = a_lo, w_cur = w_lo, acc = (uint32_t)(ch != 0);
+      }
+      while (more) {
+        const uint32_t ab = it & 1u;
+        if (lane == 0) trace_stamp(p, it, 0);
+        const uint32_t tmem_d = tmem_acc + ab * (uint32_t)p.BN;
+        uint32_t w_lo = (base >> 4) | lbo;
+        for (int ch = 0; ch < p.chunks; ++ch) {
+          const bool last_ch = ch == p.chunks - 1;
+          const uint32_t a_lo = ((a_ring + (uint32_t)(sa * p.a_stage_bytes)) >> 4) | lbo;
+          if constexpr (KS > 1) {
+            if (elect_one_sync()) {
+              // The row loop stays ROLLED: fully unrolled, ptxas hoists all descriptor words to the front and spills
+              // uniform registers.  Rolled, a tap is 4 MMAs plus a handful of uniform adds.
+              uint32_t a_cur = a_lo, w_cur = w_lo, acc = (uint32_t)(ch != 0);
 #pragma unroll 1
-            for (int row = 0; row < KS; ++row) {   // one filter row (KS taps, 4 MMAs each) per trip
+              for (int row = 0; row < KS - 1; ++row) {
 #pragma unroll
-              for (int col = 0; col < KS; ++col) {
+                for (int col = 0; col < KS; ++col) {
 #pragma unroll
-                for (int k = 0; k < kBlockK / 16; ++k) {
-                  const uint64_t da = ((uint64_t)a_hi << 32) | (uint64_t)(a_cur + col * kRow16 + 2 * k);
-                  const uint64_t db = ((uint64_t)b_hi << 32) | (uint64_t)(w_cur + 2 * k);
-                  umma_bf16(tmem_d, da, db, idesc, (col | k) != 0 ? 1u : acc);
+                  for (int k = 0; k < kBlockK / 16; ++k) {
+                    const uint64_t da = ((uint64_t)a_hi << 32) | (uint64_t)(a_cur + col * kRow16 + 2 * k);
+                    const uint64_t db = ((uint64_t)b_hi << 32) | (uint64_t)(w_cur + 2 * k);
+                    umma_bf16(tmem_d, da, db, idesc, (col | k) != 0 ? 1u : acc);
+                  }
+                  w_cur += w_step;
                 }
-                w_cur += w_step;
+                acc = 1u;
+                a_cur += (uint32_t)(kRowPitch * kRow16);
               }
-              acc = 1u;
-              a_cur += (uint32_t)(kRowPitch * kRow16);
+            }
+            __syncwarp();
+          }
+          // readiness of the next step, probed while the rows above are still queued
+          int nsa = sa + 1;
+          uint32_t npa = pa;
+          if (nsa == p.a_stages) { nsa = 0; npa ^= 1u; }
+          bool next_more = true;
+          if (last_ch) {
+            tw.next(p);
+            next_more = !tw.done();
+            if (next_more) mbar_wait(smem_u32(&bar_acc_empty[ab ^ 1u]), (((it + 1) >> 1) & 1u) ^ 1u);
+          }
+          if (next_more) mbar_wait(smem_u32(&bar_a_full[nsa]), npa);
+          tc_fence_after();
+          if (lane == 0 && last_ch) trace_stamp(p, it, 1);
+          if (elect_one_sync()) {
+            const uint32_t a_cur = a_lo + (uint32_t)((KS - 1) * kRowPitch * kRow16);
+            uint32_t w_cur = w_lo + (uint32_t)((KS - 1) * KS) * w_step;
+#pragma unroll
+            for (int col = 0; col < KS; ++col) {
+#pragma unroll
+              for (int k = 0; k < kBlockK / 16; ++k) {
+                const uint64_t da = ((uint64_t)a_hi << 32) | (uint64_t)(a_cur + col * kRow16 + 2 * k);
+                const uint64_t db = ((uint64_t)b_hi << 32) | (uint64_t)(w_cur + 2 * k);
+                umma_bf16(tmem_d, da, db, idesc,
+                          (KS > 1 || (col | k) != 0) ? 1u : (uint32_t)(ch != 0));
+              }
+              w_cur += w_step;
             }
             umma_commit(smem_u32(&bar_a_empty[sa]));
-            if (ch == p.chunks - 1) umma_commit(smem_u32(&bar_acc_full[ab]));
+            if (last_ch) umma_commit(smem_u32(&bar_acc_full[ab]));
           }
           __syncwarp();
           w_lo += (uint32_t)kTaps * w_step;
-        } else {
+          sa = nsa;
+          pa = npa;
+          if (last_ch) more = next_more;
+        }
+        if (lane == 0) trace_stamp(p, it, 2);
+        ++it;
+      }
+    } else {
+      for (tw.init(p); !tw.done(); tw.next(p), ++it) {
+        const uint32_t ab = it & 1u;
+        mbar_wait(smem_u32(&bar_acc_empty[ab]), ((it >> 1) & 1u) ^ 1u);
+        tc_fence_after();
+        const uint32_t tmem_d = tmem_acc + ab * (uint32_t)p.BN;
+        uint32_t w_lo;
+        for (int ch = 0; ch < p.chunks; ++ch) {
+          mbar_wait(smem_u32(&bar_a_full[sa]), pa);
+          tc_fence_after();
+          const uint32_t a_lo = ((a_ring + (uint32_t)(sa * p.a_stage_bytes)) >> 4) | lbo;
+          constexpr int kRow16 = 128 >> 4;
 #pragma unroll
           for (int tap = 0; tap < kTaps; ++tap) {
             mbar_wait(smem_u32(&bar_w_full[sw]), pw);
@@ -494,10 +546,9 @@ __global__ void __launch_bounds__(kTileThreads, 1) conv_tc_tile_kernel(const __g
             __syncwarp();
             if (++sw == p.w_stages) { sw = 0; pw ^= 1u; }
           }
+          if (++sa == p.a_stages) { sa = 0; pa ^= 1u; }
         }
-        if (++sa == p.a_stages) { sa = 0; pa ^= 1u; }
       }
-      if (lane == 0) trace_stamp(p, it, 2);
     }
   } else if (warp >= kCtrlWarps) {
     const int e = warp - kCtrlWarps;
