@@ -60,6 +60,8 @@ SIGNATURES = {
     "ditsep_split_hilo": (c_int, [c_void_p, c_int64, c_int, c_void_p, c_int, c_void_p]),
     "ditsep_conv_tc_plan_create": (c_int, [C.POINTER(c_void_p), c_void_p, c_int, c_int, c_int, c_int, c_int, c_void_p,
                                            c_int, c_int]),
+    "ditsep_conv_tc_plan_create_sc": (c_int, [C.POINTER(c_void_p), c_void_p, c_int, c_int, c_int, c_int, c_int, c_void_p,
+                                              c_int, c_int, c_void_p, c_int, c_int]),
     "ditsep_debug_conv_trace": (None, [c_void_p]),
     "ditsep_conv_tc_plan_destroy": (None, [c_void_p]),
     "ditsep_conv_tc_stats_layout": (c_int, [c_void_p, C.POINTER(StatsSrc)]),

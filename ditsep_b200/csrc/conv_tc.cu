@@ -61,6 +61,7 @@ struct ConvTcParams {
   // tile kernel
   int num_tiles, tiles_per_image, chunks, w_resident, a_stages, w_stages;
   int halo, row_pitch, a_rows, a_stage_bytes;
+  int xchunks;             // fused shortcut: 64-channel blocks of a second input x accumulated as a 1x1 tap (0 = none)
   float* stats;            // nullable: partial sums [B][segs_per_image][4][ld_part][2]
   int seg_len, segs_per_image, ld_part;
   long long* trace;        // debug (ditsep_debug_conv_trace): [4 CTAs][kTraceTiles][8] clock64 stamps, else nullptr
@@ -68,7 +69,7 @@ struct ConvTcParams {
 
 __device__ __forceinline__ void trace_stamp(const ConvTcParams& p, uint32_t it, int slot) {
   if (p.trace && blockIdx.x < kTraceCtas && blockIdx.y == 0 && it < kTraceTiles)
-    p.trace[((int64_t)blockIdx.x * kTraceTiles + it) * 8 + slot] = clock64();
+    p.trace[((int64_t)blockIdx.x * kTraceTiles + it) * 16 + slot] = clock64();
 }
 
 // ---- shared epilogue -----------------------------------------------------------------------
@@ -290,7 +291,7 @@ __global__ void __launch_bounds__(kThreads) conv_tc_kernel(const __grid_constant
 
 // ---- kernel 2: 8 x 16 pixel tiles with halo, persistent CTAs over contiguous segment ranges ----
 constexpr int kTileW = 8, kTileH = 16;
-constexpr int kCtrlWarps = 4;   // 0: TMA producer, 1: TMEM allocator + MMA issuer, 2-3: idle (the register file
+constexpr int kCtrlWarps = 4;   // 0: TMA producer, 1: TMEM allocator + MMA issuer (even tiles), 2: MMA issuer (odd tiles), 3: idle (the register file
                                 // is allocated in units of 4 warps: 20 warps x 96 registers fill it)
 constexpr int kEpiWarps = 16;   // warp w: TMEM lane quadrant w % 4, output channels [16*((w-4)/4), +16)
 constexpr int kTileThreads = (kCtrlWarps + kEpiWarps) * 32;
@@ -332,19 +333,20 @@ struct TileWalk {
 template <int KS, bool kRes, bool kFast>
 __global__ void __launch_bounds__(kTileThreads, 1) conv_tc_tile_kernel(const __grid_constant__ CUtensorMap mapA,
                                                                        const __grid_constant__ CUtensorMap mapW,
+                                                                       const __grid_constant__ CUtensorMap mapX,
                                                                        const __grid_constant__ ConvTcParams p) {
   constexpr int kTaps = KS * KS, kHalo = KS / 2, kRowPitch = kTileW + 2 * kHalo;
   extern __shared__ uint8_t smem_raw[];
   __shared__ __align__(8) uint64_t bar_a_full[kMaxAStages], bar_a_empty[kMaxAStages];
   __shared__ __align__(8) uint64_t bar_w_full[kMaxWStages], bar_w_empty[kMaxWStages];
-  __shared__ __align__(8) uint64_t bar_w_res, bar_acc_full[2], bar_acc_empty[2];
+  __shared__ __align__(8) uint64_t bar_w_res, bar_acc_full[2], bar_acc_empty[2], bar_turn[2];
   __shared__ uint32_t tmem_base_slot;
   __shared__ __align__(16) float comb[2][kTileMaxBN];  // bias[co] + bias_b[b][co] of the image being stored
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const uint32_t base = (smem_u32(smem_raw) + 1023u) & ~1023u;
   const uint32_t w_tile_bytes = (uint32_t)p.BN * 128u;
-  const int n_wtiles = kRes ? p.chunks * kTaps : p.w_stages;
+  const int n_wtiles = kRes ? p.chunks * kTaps + p.xchunks : p.w_stages;
   const uint32_t a_ring = (base + (uint32_t)n_wtiles * w_tile_bytes + 1023u) & ~1023u;
   const int n0 = blockIdx.y * p.BN;
 
@@ -359,6 +361,7 @@ __global__ void __launch_bounds__(kTileThreads, 1) conv_tc_tile_kernel(const __g
     }
     mbar_init(smem_u32(&bar_w_res), 1);
     for (int s = 0; s < 2; ++s) {
+      mbar_init(smem_u32(&bar_turn[s]), 1);
       mbar_init(smem_u32(&bar_acc_full[s]), 1);
       mbar_init(smem_u32(&bar_acc_empty[s]), kEpiWarps);  // one arrival per epilogue warp
     }
@@ -376,16 +379,30 @@ __global__ void __launch_bounds__(kTileThreads, 1) conv_tc_tile_kernel(const __g
       asm volatile("prefetch.tensormap [%0];" ::"l"(&mapW) : "memory");
       if (kRes) {
         const uint32_t bar = smem_u32(&bar_w_res);
-        mbar_expect_tx(bar, (uint32_t)(p.chunks * kTaps) * w_tile_bytes);
+        mbar_expect_tx(bar, (uint32_t)(p.chunks * kTaps + p.xchunks) * w_tile_bytes);
         for (int ch = 0; ch < p.chunks; ++ch)
           for (int tap = 0; tap < kTaps; ++tap)
             tma_load_2d(base + (uint32_t)(ch * kTaps + tap) * w_tile_bytes, &mapW, bar, tap * p.Cin + ch * kBlockK, n0);
+        for (int cx = 0; cx < p.xchunks; ++cx)  // shortcut filter: K columns past the taps
+          tma_load_2d(base + (uint32_t)(p.chunks * kTaps + cx) * w_tile_bytes, &mapW, bar, kTaps * p.Cin + cx * kBlockK, n0);
+        if (p.xchunks) asm volatile("prefetch.tensormap [%0];" ::"l"(&mapX) : "memory");
       }
       int sa = 0, sw = 0;
       uint32_t pa = 1, pw = 1;  // "empty" barriers start free: the first pass waits on the opposite parity
       TileWalk tw;
       uint32_t itp = 0;
+      const bool xfirst = kRes && p.xchunks > 0 && p.a_stages >= p.xchunks + 2;  // unit order of the MMA warp
+      auto load_shortcut = [&](const TileWalk& t) {  // shortcut input: the tile's own 8 x 16 pixels, no halo
+        for (int cx = 0; cx < p.xchunks; ++cx) {
+          mbar_wait_sleep(smem_u32(&bar_a_empty[sa]), pa);
+          const uint32_t full = smem_u32(&bar_a_full[sa]);
+          mbar_expect_tx(full, (uint32_t)(kTileM * 128));
+          tma_load_4d(a_ring + (uint32_t)(sa * p.a_stage_bytes), &mapX, full, cx * kBlockK, t.tx * kTileW, t.ty * kTileH, t.b);
+          if (++sa == p.a_stages) { sa = 0; pa ^= 1u; }
+        }
+      };
       for (tw.init(p); !tw.done(); tw.next(p), ++itp) {
+        if (xfirst) load_shortcut(tw);
         for (int ch = 0; ch < p.chunks; ++ch) {
           mbar_wait_sleep(smem_u32(&bar_a_empty[sa]), pa);
           if (ch == 0) trace_stamp(p, itp, 6);
@@ -404,11 +421,12 @@ __global__ void __launch_bounds__(kTileThreads, 1) conv_tc_tile_kernel(const __g
             }
           }
         }
+        if (!xfirst) load_shortcut(tw);
       }
     }
-  } else if (warp == 1) {
+  } else if (warp == 1 || (kRes && warp == 2)) {
     // All 32 lanes walk the loop (converged, so every operand lives in uniform registers); one elected lane
-    // issues.  ONE thread feeds a tensor pipe that retires a 128 x 64 x 16 MMA in 32 cycles: everything that can
+    // issues.  Everything that can
     // be a compile-time constant is one (tap offsets, K steps), ring positions are wrap-around counters, and
     // descriptors are built from 32-bit low words (shared-memory addresses >> 4 fit 14 bits, so adding row / K
     // offsets never carries into the next field).
@@ -419,6 +437,7 @@ __global__ void __launch_bounds__(kTileThreads, 1) conv_tc_tile_kernel(const __g
     // offset (measured: tests/test_gpu_kernels.py::test_conv_tc_shifted_descriptor_views).
     constexpr uint32_t a_hi = (uint32_t)((kRowPitch * 128) >> 4) | (1u << 14) | (2u << 29);
     constexpr uint32_t b_hi = 64u | (1u << 14) | (2u << 29);
+    constexpr uint32_t a_hi_x = (uint32_t)((kTileW * 128) >> 4) | (1u << 14) | (2u << 29);
     constexpr uint32_t lbo = 1u << 16;
     const uint32_t w_step = w_tile_bytes >> 4;
     if (kRes) {
@@ -429,34 +448,53 @@ __global__ void __launch_bounds__(kTileThreads, 1) conv_tc_tile_kernel(const __g
     uint32_t pa = 0, pw = 0, it = 0;
     TileWalk tw;
     if constexpr (kRes) {
-      // Resident filter.  A step = one K chunk of one tile = KS filter rows of KS * 4 MMAs.  The tensor pipe's queue is
-      // only a few MMAs deep, and a barrier probe + tcgen05 fence costs the issuing thread several hundred cycles
-      // even when the phase completed long ago (r1i clock64 trace: ~760 idle cycles between the last MMA of a tile
-      // and the first of the next).  So the readiness of step s+1 (its A stage, and its accumulator when it opens a
-      // new tile) is awaited BEFORE the last filter row of step s is issued: the probes run under a full queue.
+      // Resident filter.  The work of this CTA is a flat sequence of UNITS: per tile, the shortcut chunks (one 1x1 tap
+      // of 4 MMAs each) and the main K chunks (KS * KS taps of 4 MMAs each), each unit owning one stage of the A ring.
+      // Measured (r1k/r1l clock64 traces, scripts/umma_probe.cu): a 128 x 64 x 16 MMA takes 75 cycles in SS mode, the
+      // tensor pipe's queue is only ~4 MMAs deep, and every dependent instruction of an issuing warp costs 4-6 cycles,
+      // so the barrier probes + fence + loop bookkeeping between two units (300-700 cycles) drain the queue whatever
+      // their position in the loop (two software-pipelined variants were measured and were no faster).  Hence TWO
+      // issuing warps: warp 1 takes the even tiles of this CTA, warp 2 the odd ones (accumulator = tile parity), and
+      // one warp's bookkeeping runs under the other's MMAs.  MMAs of different threads are unordered, which is fine:
+      // they touch different accumulators and different stages; each warp commits its own stages and accumulator.
+      // The A ring stays a single in-order queue: a warp probes its tile's stages only once the other warp has passed
+      // the probe of ITS last stage (bar_turn hand-over) -- a parity wait is only meaningful for the very next phase
+      // of a barrier, and a warp probing a whole tile ahead would alias phases.
       constexpr int kRow16 = 128 >> 4;
-      tw.init(p);
-      bool more = !tw.done();
-      if (more) {
-        mbar_wait(smem_u32(&bar_acc_empty[0]), 1u);
-        mbar_wait(smem_u32(&bar_a_full[0]), 0u);
-        tc_fence_after();
-      }
-      while (more) {
+      const uint32_t my = (uint32_t)(warp - 1);
+      int n_my = 0;
+      for (tw.init(p); !tw.done(); tw.next(p)) ++n_my;
+      const int nc = p.chunks, nx = p.xchunks, nsteps = nc + nx;
+      const bool xfirst = nx > 0 && p.a_stages >= nx + 2;  // the producer follows the same order
+      const uint32_t w_base = (base >> 4) | lbo;
+      for (it = 0; it < (uint32_t)n_my; ++it) {
+        if ((it & 1u) != my) {  // the other warp's tile: step over its stages
+          for (int i = 0; i < nsteps; ++i)
+            if (++sa == p.a_stages) { sa = 0; pa ^= 1u; }
+          continue;
+        }
         const uint32_t ab = it & 1u;
+        mbar_wait(smem_u32(&bar_acc_empty[ab]), ((it >> 1) & 1u) ^ 1u);
+        if (it != 0) mbar_wait(smem_u32(&bar_turn[my]), (my ? (it >> 1) : ((it >> 1) - 1u)) & 1u);
         if (lane == 0) trace_stamp(p, it, 0);
         const uint32_t tmem_d = tmem_acc + ab * (uint32_t)p.BN;
-        uint32_t w_lo = (base >> 4) | lbo;
-        for (int ch = 0; ch < p.chunks; ++ch) {
-          const bool last_ch = ch == p.chunks - 1;
+        for (int pos = 0; pos < nsteps; ++pos) {
+          const bool is_x = xfirst ? pos < nx : pos >= nc;  // fused shortcut: a 1x1 tap over the tile's own pixels of x
+          const bool last_st = pos == nsteps - 1;
+          const int widx = is_x ? nc * kTaps + (xfirst ? pos : pos - nc) : (xfirst ? pos - nx : pos) * kTaps;
+          const uint32_t w_lo = w_base + (uint32_t)widx * w_step;
+          mbar_wait(smem_u32(&bar_a_full[sa]), pa);
+          if (last_st && lane == 0) mbar_arrive(smem_u32(&bar_turn[my ^ 1u]));  // the ring is the other warp's now
+          tc_fence_after();
+          if (pos == 0 && lane == 0) trace_stamp(p, it, 1);
           const uint32_t a_lo = ((a_ring + (uint32_t)(sa * p.a_stage_bytes)) >> 4) | lbo;
-          if constexpr (KS > 1) {
-            if (elect_one_sync()) {
+          if (elect_one_sync()) {
+            if (!is_x) {
               // The row loop stays ROLLED: fully unrolled, ptxas hoists all descriptor words to the front and spills
               // uniform registers.  Rolled, a tap is 4 MMAs plus a handful of uniform adds.
-              uint32_t a_cur = a_lo, w_cur = w_lo, acc = (uint32_t)(ch != 0);
+              uint32_t a_cur = a_lo, w_cur = w_lo, acc = (uint32_t)(pos != 0);
 #pragma unroll 1
-              for (int row = 0; row < KS - 1; ++row) {
+              for (int row = 0; row < KS; ++row) {
 #pragma unroll
                 for (int col = 0; col < KS; ++col) {
 #pragma unroll
@@ -470,49 +508,23 @@ __global__ void __launch_bounds__(kTileThreads, 1) conv_tc_tile_kernel(const __g
                 acc = 1u;
                 a_cur += (uint32_t)(kRowPitch * kRow16);
               }
-            }
-            __syncwarp();
-          }
-          // readiness of the next step, probed while the rows above are still queued
-          int nsa = sa + 1;
-          uint32_t npa = pa;
-          if (nsa == p.a_stages) { nsa = 0; npa ^= 1u; }
-          bool next_more = true;
-          if (last_ch) {
-            tw.next(p);
-            next_more = !tw.done();
-            if (next_more) mbar_wait(smem_u32(&bar_acc_empty[ab ^ 1u]), (((it + 1) >> 1) & 1u) ^ 1u);
-          }
-          if (next_more) mbar_wait(smem_u32(&bar_a_full[nsa]), npa);
-          tc_fence_after();
-          if (lane == 0 && last_ch) trace_stamp(p, it, 1);
-          if (elect_one_sync()) {
-            const uint32_t a_cur = a_lo + (uint32_t)((KS - 1) * kRowPitch * kRow16);
-            uint32_t w_cur = w_lo + (uint32_t)((KS - 1) * KS) * w_step;
+            } else {
 #pragma unroll
-            for (int col = 0; col < KS; ++col) {
-#pragma unroll
-              for (int k = 0; k < kBlockK / 16; ++k) {
-                const uint64_t da = ((uint64_t)a_hi << 32) | (uint64_t)(a_cur + col * kRow16 + 2 * k);
-                const uint64_t db = ((uint64_t)b_hi << 32) | (uint64_t)(w_cur + 2 * k);
-                umma_bf16(tmem_d, da, db, idesc,
-                          (KS > 1 || (col | k) != 0) ? 1u : (uint32_t)(ch != 0));
+              for (int k = 0; k < kBlockK / 16; ++k) {  // 8 x 16 box without halo: 8-row groups 1024 bytes apart
+                const uint64_t da = ((uint64_t)a_hi_x << 32) | (uint64_t)(a_lo + 2 * k);
+                const uint64_t db = ((uint64_t)b_hi << 32) | (uint64_t)(w_lo + 2 * k);
+                umma_bf16(tmem_d, da, db, idesc, k != 0 ? 1u : (uint32_t)(pos != 0));
               }
-              w_cur += w_step;
             }
             umma_commit(smem_u32(&bar_a_empty[sa]));
-            if (last_ch) umma_commit(smem_u32(&bar_acc_full[ab]));
+            if (last_st) umma_commit(smem_u32(&bar_acc_full[ab]));
           }
           __syncwarp();
-          w_lo += (uint32_t)kTaps * w_step;
-          sa = nsa;
-          pa = npa;
-          if (last_ch) more = next_more;
+          if (++sa == p.a_stages) { sa = 0; pa ^= 1u; }
         }
         if (lane == 0) trace_stamp(p, it, 2);
-        ++it;
       }
-    } else {
+    } else if (warp == 1) {
       for (tw.init(p); !tw.done(); tw.next(p), ++it) {
         const uint32_t ab = it & 1u;
         mbar_wait(smem_u32(&bar_acc_empty[ab]), ((it >> 1) & 1u) ^ 1u);
@@ -751,7 +763,7 @@ static int pow2_ceil(int v) {
 using namespace ditsep;
 
 struct ditsep_conv_plan {
-  CUtensorMap mapA, mapW;
+  CUtensorMap mapA, mapW, mapX;  // mapX: the fused shortcut's input (a copy of mapA when there is none)
   ConvTcParams p;
   size_t smem;
   int tile;      // 1 = conv_tc_tile_kernel
@@ -760,7 +772,16 @@ struct ditsep_conv_plan {
 
 extern "C" int ditsep_conv_tc_plan_create(ditsep_conv_plan** plan, const void* in, int B, int H, int W, int Cin,
                                           int ld_in, const void* w_bf16, int Cout, int ksize) {
+  return ditsep_conv_tc_plan_create_sc(plan, in, B, H, W, Cin, ld_in, w_bf16, Cout, ksize, nullptr, 0, 0);
+}
+
+extern "C" int ditsep_conv_tc_plan_create_sc(ditsep_conv_plan** plan, const void* in, int B, int H, int W, int Cin,
+                                             int ld_in, const void* w_bf16, int Cout, int ksize, const void* x_sc, int Cx,
+                                             int ld_x) {
   DITSEP_REQUIRE(plan && in && w_bf16, "conv_tc_plan_create: null pointer");
+  DITSEP_REQUIRE(!x_sc || (Cx > 0 && Cx % kBlockK == 0 && ld_x >= Cx && ld_x % 8 == 0 &&
+                           (reinterpret_cast<uintptr_t>(x_sc) & 15) == 0),
+                 "conv_tc: fused shortcut needs Cx %% 64 == 0, ld_x %% 8 == 0, 16-byte alignment (Cx=%d ld_x=%d)", Cx, ld_x);
   DITSEP_REQUIRE(ksize == 1 || ksize == 3, "conv_tc: ksize=%d (1 or 3)", ksize);
   DITSEP_REQUIRE(B > 0 && H > 0 && W > 0, "conv_tc: empty problem");
   DITSEP_REQUIRE(Cin > 0 && Cin % kBlockK == 0, "conv_tc: Cin=%d must be a multiple of %d", Cin, kBlockK);
@@ -811,6 +832,7 @@ extern "C" int ditsep_conv_tc_plan_create(ditsep_conv_plan** plan, const void* i
               !(mode_env && strcmp(mode_env, "tap") == 0)) ? 1 : 0;
   size_t smem = 1024 + (size_t)p.stages * stage_bytes;
   int grid_x = 0;
+  DITSEP_REQUIRE(!x_sc || tile, "conv_tc: fused shortcut needs the tile kernel (image >= 8 x 16)");
   if (tile) {
     p.halo = ksize / 2;
     p.row_pitch = kTileW + 2 * p.halo;
@@ -829,7 +851,8 @@ extern "C" int ditsep_conv_tc_plan_create(ditsep_conv_plan** plan, const void* i
     p.tmem_cols = pow2_ceil(2 * p.BN) < 32 ? 32 : pow2_ceil(2 * p.BN);
     const size_t w_tile = (size_t)p.BN * 128;
     const size_t budget = 222 * 1024;  // dynamic; static (barriers + reduction scratch) is ~2.3 KB
-    const size_t w_all = (size_t)p.chunks * p.taps * w_tile;
+    p.xchunks = x_sc ? Cx / kBlockK : 0;
+    const size_t w_all = ((size_t)p.chunks * p.taps + p.xchunks) * w_tile;
     if (w_all + 2 * (size_t)p.a_stage_bytes + 2048 <= budget) {
       p.w_resident = 1;
       p.w_stages = 0;
@@ -837,6 +860,7 @@ extern "C" int ditsep_conv_tc_plan_create(ditsep_conv_plan** plan, const void* i
       while (p.a_stages > 2 && w_all + (size_t)p.a_stages * p.a_stage_bytes + 2048 > budget) --p.a_stages;
       smem = 2048 + w_all + (size_t)p.a_stages * p.a_stage_bytes;
     } else {
+      DITSEP_REQUIRE(!x_sc, "conv_tc: fused shortcut needs the filter resident in shared memory (%zu bytes do not fit)", w_all);
       p.w_resident = 0;
       p.w_stages = kMaxWStages;
       p.a_stages = kMaxAStages;
@@ -873,7 +897,7 @@ extern "C" int ditsep_conv_tc_plan_create(ditsep_conv_plan** plan, const void* i
     }
   }
   {
-    const int K = p.taps * Cin;
+    const int K = p.taps * Cin + (x_sc ? Cx : 0);  // the shortcut filter rides behind the taps along K
     cuuint64_t gdim[2] = {(cuuint64_t)K, (cuuint64_t)cout_pad};
     cuuint64_t gstr[1] = {(cuuint64_t)K * 2};
     cuuint32_t box[2] = {(cuuint32_t)kBlockK, (cuuint32_t)p.BN};
@@ -884,6 +908,20 @@ extern "C" int ditsep_conv_tc_plan_create(ditsep_conv_plan** plan, const void* i
     if (r != CUDA_SUCCESS) {
       delete pl;
       DITSEP_REQUIRE(false, "conv_tc: cuTensorMapEncodeTiled(filter) failed with %d", (int)r);
+    }
+  }
+  pl->mapX = pl->mapA;
+  if (x_sc) {
+    cuuint64_t gdim[4] = {(cuuint64_t)Cx, (cuuint64_t)W, (cuuint64_t)H, (cuuint64_t)B};
+    cuuint64_t gstr[3] = {(cuuint64_t)ld_x * 2, (cuuint64_t)W * ld_x * 2, (cuuint64_t)H * W * ld_x * 2};
+    cuuint32_t box[4] = {(cuuint32_t)kBlockK, (cuuint32_t)kTileW, (cuuint32_t)kTileH, 1};
+    cuuint32_t estr[4] = {1, 1, 1, 1};
+    CUresult r = encode(&pl->mapX, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 4, const_cast<void*>(x_sc), gdim, gstr, box, estr,
+                        CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                        CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    if (r != CUDA_SUCCESS) {
+      delete pl;
+      DITSEP_REQUIRE(false, "conv_tc: cuTensorMapEncodeTiled(shortcut input) failed with %d", (int)r);
     }
   }
   static bool attr_set = false;
@@ -942,7 +980,7 @@ extern "C" int ditsep_conv_tc_run(const ditsep_conv_plan* plan, const float* bia
                       (!residual || (res_dtype == DITSEP_BF16 && (ld_res & 7) == 0 &&
                                      (reinterpret_cast<uintptr_t>(residual) & 15) == 0));
 #define DITSEP_TILE_LAUNCH(KS, RES, FAST) \
-  conv_tc_tile_kernel<KS, RES, FAST><<<grid, kTileThreads, plan->smem, st>>>(plan->mapA, plan->mapW, p)
+  conv_tc_tile_kernel<KS, RES, FAST><<<grid, kTileThreads, plan->smem, st>>>(plan->mapA, plan->mapW, plan->mapX, p)
     if (p.ksize == 3) {
       if (p.w_resident) { if (fast) DITSEP_TILE_LAUNCH(3, true, true); else DITSEP_TILE_LAUNCH(3, true, false); }
       else { if (fast) DITSEP_TILE_LAUNCH(3, false, true); else DITSEP_TILE_LAUNCH(3, false, false); }

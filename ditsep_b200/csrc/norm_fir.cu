@@ -483,29 +483,32 @@ __global__ void __launch_bounds__(256) fir_narrow_kernel(const T* __restrict__ x
 // tensor the tcgen05 kernel accepts WITHOUT giving up fp32 input accuracy: channels [0,C) = hi = bf16(x),
 // [C,2C) = lo = bf16(x - hi), [2C,3C) = hi again, the rest zero; against filter channels [wh | wh | wl]
 // (w = wh + wl) the tensor core computes xh*wh + xl*wh + xh*wl = x*w to ~2^-16.
-// One thread = 8 output channels (16 bytes) of one pixel.
-__global__ void __launch_bounds__(256) split_hilo_kernel(const float* __restrict__ x, int64_t npix, int C, bf16* __restrict__ out,
+// One thread = one pixel: C fp32 loads, 3C bf16 values in ceil(3C/8) 16-byte stores.  Channels >= 8*ceil(3C/8) are
+// NOT written: the caller zeroes the buffer once (engine: torch.zeros at plan build) and they stay zero.
+template <int C>
+__global__ void __launch_bounds__(256) split_hilo_kernel(const float* __restrict__ x, int64_t npix, bf16* __restrict__ out,
                                                          int ld) {
-  const int cv = ld / 8;
-  const int64_t total = npix * cv;
-  for (int64_t idx = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; idx < total;
-       idx += (int64_t)gridDim.x * blockDim.x) {
-    const int v = (int)(idx % cv);
-    const int64_t pix = idx / cv;
-    float f[8];
+  constexpr int kVec = (3 * C + 7) / 8;
+  for (int64_t pix = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; pix < npix; pix += (int64_t)gridDim.x * blockDim.x) {
+    float xv[C], f[kVec * 8];
 #pragma unroll
-    for (int i = 0; i < 8; ++i) {
-      const int j = v * 8 + i;
-      float val = 0.f;
-      if (j < 3 * C) {
-        const int kind = j / C;
-        const float xv = __ldg(x + pix * C + (j - kind * C));
-        const float hi = __bfloat162float(__float2bfloat16_rn(xv));
-        val = (kind == 1) ? xv - hi : hi;
-      }
-      f[i] = val;
+    for (int c = 0; c < C; ++c) xv[c] = __ldg(x + pix * C + c);
+#pragma unroll
+    for (int j = 0; j < kVec * 8; ++j) f[j] = 0.f;
+#pragma unroll
+    for (int c = 0; c < C; ++c) {
+      const float hi = __bfloat162float(__float2bfloat16_rn(xv[c]));
+      f[c] = hi;
+      f[C + c] = xv[c] - hi;
+      f[2 * C + c] = hi;
     }
-    Pack8<bf16>::store(out + pix * ld + v * 8, f);
+#pragma unroll
+    for (int v = 0; v < kVec; ++v) {
+      float t[8];
+#pragma unroll
+      for (int i = 0; i < 8; ++i) t[i] = f[v * 8 + i];
+      Pack8<bf16>::store(out + pix * ld + v * 8, t);
+    }
   }
 }
 
@@ -748,7 +751,13 @@ extern "C" int ditsep_split_hilo(const float* x, int64_t npix, int C, void* out_
   DITSEP_REQUIRE(x && out_bf16, "split_hilo: null pointer");
   DITSEP_REQUIRE(npix > 0 && C > 0 && ld % 8 == 0 && 3 * C <= ld, "split_hilo: need 3*C <= ld, ld %% 8 == 0 (C=%d ld=%d)", C, ld);
   DITSEP_REQUIRE((reinterpret_cast<uintptr_t>(out_bf16) & 15) == 0, "split_hilo: output must be 16-byte aligned");
-  split_hilo_kernel<<<grid_for(npix * (ld / 8)), 256, 0, (cudaStream_t)stream>>>(x, npix, C, (bf16*)out_bf16, ld);
+  DITSEP_REQUIRE(C == 6 || C == 8 || C == 3 || C == 4, "split_hilo: C=%d (built for 3, 4, 6, 8 input channels)", C);
+  const int grid = grid_for(npix);
+  cudaStream_t st = (cudaStream_t)stream;
+  if (C == 6) split_hilo_kernel<6><<<grid, 256, 0, st>>>(x, npix, (bf16*)out_bf16, ld);
+  else if (C == 8) split_hilo_kernel<8><<<grid, 256, 0, st>>>(x, npix, (bf16*)out_bf16, ld);
+  else if (C == 3) split_hilo_kernel<3><<<grid, 256, 0, st>>>(x, npix, (bf16*)out_bf16, ld);
+  else split_hilo_kernel<4><<<grid, 256, 0, st>>>(x, npix, (bf16*)out_bf16, ld);
   return check_launch("split_hilo_kernel");
 }
 

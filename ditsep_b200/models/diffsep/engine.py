@@ -119,6 +119,26 @@ def _pack_conv(weight: torch.Tensor, bias: torch.Tensor, want_bf16: bool) -> _Co
     return _ConvW(w, bias.detach().float().contiguous(), kh, wb)
 
 
+def _fuse_shortcut(main: _ConvW, sc: Optional[_ConvW], cx: int) -> Optional[_ConvW]:
+    """Filter of a res-block's second conv with its skip path riding behind the taps along K
+    (ditsep_conv_tc_plan_create_sc): [CoutPad][taps*Cin + Cx] bf16, the last Cx columns being Conv_2's 1x1 filter
+    (layerspp.py:322-324) or the identity (plain `x + h`, :325-327); bias = b_conv1 (+ b_conv2)."""
+    if main.w_bf16 is None or cx % 64 or (sc is None and cx != main.cout):
+        return None
+    cp, taps, cin = main.w_bf16.shape
+    wb = torch.zeros(cp, taps * cin + cx, device=main.w_bf16.device, dtype=torch.bfloat16)
+    wb[:, :taps * cin] = main.w_bf16.reshape(cp, taps * cin)
+    if sc is None:
+        wb[:main.cout, taps * cin:] = torch.eye(main.cout, device=wb.device, dtype=torch.bfloat16)
+        bias = main.bias
+    else:
+        wb[:main.cout, taps * cin:] = sc.w.reshape(main.cout, cx).to(torch.bfloat16)
+        bias = (main.bias + sc.bias).contiguous()
+    out = _ConvW(main.w, bias, main.ksize, wb)
+    out.cx = cx
+    return out
+
+
 def _pack_conv_hilo(weight: torch.Tensor, bias: torch.Tensor, width: int = 64) -> Optional[_ConvW]:
     """First-layer filter for the tensor-core path (ops.split_hilo): input channels [wh | wh | wl | 0] with
     w = wh + wl in bf16, matching activations [xh | xl | xh | 0]; (Cout, Cin, kh, kw) -> [CoutPad][tap][width]."""
@@ -188,6 +208,8 @@ class NcsnppEngine:
                 w[f"conv{i}b"] = _pack_conv(mod.Conv_1.weight, mod.Conv_1.bias, bf)
                 if hasattr(mod, "Conv_2"):
                     w[f"conv{i}c"] = _pack_conv(mod.Conv_2.weight, mod.Conv_2.bias, bf)
+                if bf:  # second conv with the skip path fused in (used where the kernel can keep the filter resident)
+                    w[f"conv{i}b_sc"] = _fuse_shortcut(w[f"conv{i}b"], w.get(f"conv{i}c"), spec.in_ch)
                 dense_w.append(mod.Dense_0.weight.detach().float())
                 dense_b.append(mod.Dense_0.bias.detach().float())
                 w[f"dense_off{i}"] = off
@@ -405,17 +427,29 @@ class _Plan:
         add((ops.output_layer, (pyramid, self.t, w["out_w"], w["out_b"], self.out, bool(m.scale_by_sigma)), {}))
 
     # ------------------------------------------------------------------ building blocks
-    def _conv(self, x, cw: _ConvW, out, bias_b=None, residual=None, out_scale: float = 1.0, want_stats: bool = False):
+    def _conv(self, x, cw: _ConvW, out, bias_b=None, residual=None, out_scale: float = 1.0, want_stats: bool = False,
+              shortcut=None) -> bool:
         """3x3 / 1x1 conv with the fused epilogue; tcgen05 path when the shape allows it.  want_stats:
         GroupNorm will normalise `out` (alone or as part of a concat buffer) -- its per-channel sums come
         from the conv epilogue when the kernel can leave them, else from one explicit pass over `out`."""
         use_tc = (cw.w_bf16 is not None and x.dtype == torch.bfloat16 and not ops.EMULATED and ops.tc_enabled())
         kw = {"bias_b": bias_b, "residual": residual, "out_scale": out_scale}
+        plan = None
+        if shortcut is not None:
+            # fused skip path (shortcut: the block input x, added through the 1x1 filter packed behind cw's taps):
+            # returns False -- nothing appended -- when this shape cannot be fused; the caller keeps the unfused steps
+            if not use_tc or shortcut.dtype != torch.bfloat16 or os.environ.get("DITSEP_FUSE_SHORTCUT", "1") == "0":
+                return False
+            try:
+                plan = ops.ConvTcPlan(x, cw.w_bf16, cw.cout, cw.ksize, shortcut=shortcut)
+            except ops.DitsepError:
+                return False
         key = (out.data_ptr(), out.shape[3])
         self.stat_src.pop(key, None)  # whatever was known about this view is stale now
         fused = False
         if use_tc:
-            plan = ops.ConvTcPlan(x, cw.w_bf16, cw.cout, cw.ksize)
+            if plan is None:
+                plan = ops.ConvTcPlan(x, cw.w_bf16, cw.cout, cw.ksize)
             self._tc_plans.append(plan)
             if want_stats and plan.stats_floats() > 0:
                 buf = torch.empty(plan.stats_floats(), device=self.device, dtype=torch.float32)
@@ -430,6 +464,7 @@ class _Plan:
             buf = torch.empty(ops.gn_partial_floats(B, H * W, C), device=self.device, dtype=torch.float32)
             self.steps.append((ops.gn_partial_sums, (out, buf), {}))
             self.stat_src[key] = (buf, ops.split_sums_layout(H * W, C))
+        return True
 
     def _scale_shift(self, x, gnw) -> torch.Tensor:
         """GroupNorm(min(C/4,32), C, eps=1e-6) of the NHWC view x folded to per-(b,c) scale/shift
@@ -479,12 +514,15 @@ class _Plan:
         ss1 = self._scale_shift(h1, w[f"gn{i}b"])
         add((ops.gn_apply, (h1, ss1, True, h1), {}))  # in place
         self.stat_src.pop((h1.data_ptr(), cout), None)
-        if f"conv{i}c" in w:
-            self._conv(xr, w[f"conv{i}c"], out)
-            res = out
-        else:
-            res = xr
-        self._conv(h1, w[f"conv{i}b"], out, residual=res, out_scale=1.0 / math.sqrt(2.0), want_stats=True)
+        fused = w.get(f"conv{i}b_sc")
+        if not (fused is not None and self._conv(h1, fused, out, shortcut=xr, out_scale=1.0 / math.sqrt(2.0),
+                                                 want_stats=True)):
+            if f"conv{i}c" in w:
+                self._conv(xr, w[f"conv{i}c"], out)
+                res = out
+            else:
+                res = xr
+            self._conv(h1, w[f"conv{i}b"], out, residual=res, out_scale=1.0 / math.sqrt(2.0), want_stats=True)
         pool.put(h1)
         if xr is not x:
             pool.put(xr)

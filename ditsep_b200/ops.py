@@ -244,18 +244,30 @@ def split_hilo(x, out):
 class ConvTcPlan:
     """Owns a ditsep_conv_plan (TMA descriptors for one input tensor + weight binding)."""
 
-    def __init__(self, x: torch.Tensor, w_bf16: torch.Tensor, Cout: int, ksize: int):
-        _cuda(x, w_bf16)
+    def __init__(self, x: torch.Tensor, w_bf16: torch.Tensor, Cout: int, ksize: int, shortcut: torch.Tensor = None):
+        """shortcut: optional second NHWC bf16 input (B,H,W,Cx) accumulated through the 1x1 filter packed behind the
+        taps of w_bf16 ([CoutPad][ksize^2*Cin + Cx]) -- ditsep_conv_tc_plan_create_sc.  Raises DitsepError when the
+        shape cannot be fused (filter not resident, image below one tile); callers fall back to the unfused path."""
+        _cuda(x, w_bf16, shortcut)
         B, H, W, Cin = x.shape
         if x.dtype != torch.bfloat16 or w_bf16.dtype != torch.bfloat16 or not w_bf16.is_contiguous():
             raise _lib.DitsepError("conv_tc: bf16 activations and packed bf16 weights required")
         self._h = C.c_void_p()
-        self._keep = (x, w_bf16)
+        self._keep = (x, w_bf16, shortcut)
         self.Cout = Cout
-        self.K = ksize * ksize * Cin
+        self.K = ksize * ksize * Cin + (0 if shortcut is None else shortcut.shape[3])
         self.shape = (B, H, W)
-        check(_lib.load().ditsep_conv_tc_plan_create(C.byref(self._h), _ptr(x), B, H, W, Cin, nhwc_ld(x), _ptr(w_bf16),
-                                                     Cout, ksize), "conv_tc_plan_create")
+        if w_bf16.numel() % self.K or w_bf16.numel() // self.K < Cout:
+            raise _lib.DitsepError(f"conv_tc: packed filter has {w_bf16.numel()} elements, K={self.K}, Cout={Cout}")
+        if shortcut is None:
+            check(_lib.load().ditsep_conv_tc_plan_create(C.byref(self._h), _ptr(x), B, H, W, Cin, nhwc_ld(x),
+                                                         _ptr(w_bf16), Cout, ksize), "conv_tc_plan_create")
+        else:
+            if shortcut.dtype != torch.bfloat16 or tuple(shortcut.shape[:3]) != (B, H, W):
+                raise _lib.DitsepError("conv_tc: shortcut must be bf16 NHWC with the input's B, H, W")
+            check(_lib.load().ditsep_conv_tc_plan_create_sc(C.byref(self._h), _ptr(x), B, H, W, Cin, nhwc_ld(x),
+                                                            _ptr(w_bf16), Cout, ksize, _ptr(shortcut), shortcut.shape[3],
+                                                            nhwc_ld(shortcut)), "conv_tc_plan_create_sc")
 
     def stats_layout(self) -> "_lib.StatsSrc":
         """Layout of the statistics partials this plan's run() can leave (kind STATS_NONE if it cannot);

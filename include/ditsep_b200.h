@@ -145,7 +145,8 @@ int ditsep_conv_direct(const void* in, int dtype, int B, int H, int W, int Cin, 
 
 /* Widens a narrow fp32 NHWC tensor x [npix][C] (the 2(n+1)-channel STFT features feeding the network's first
  * ddpm_conv3x3, ncsnpp.py:352-356) to a bf16 tensor [npix][ld] the tcgen05 path accepts, keeping fp32 accuracy:
- * channels [0,C) = hi = bf16(x), [C,2C) = lo = bf16(x - hi), [2C,3C) = hi, [3C,ld) = 0.  Pair it with a filter whose
+ * channels [0,C) = hi = bf16(x), [C,2C) = lo = bf16(x - hi), [2C,3C) = hi; channels [3C, 8*ceil(3C/8)) are written as 0 and
+ * channels beyond that are NOT touched (zero the buffer once; C in {3,4,6,8}).  Pair it with a filter whose
  * input channels are [wh | wh | wl] (w = wh + wl in bf16).  Needs 3*C <= ld, ld % 8 == 0. */
 int ditsep_split_hilo(const float* x, int64_t npix, int C, void* out_bf16, int ld, void* stream);
 
@@ -165,6 +166,16 @@ int ditsep_split_hilo(const float* x, int64_t npix, int C, void* out_bf16, int l
 typedef struct ditsep_conv_plan ditsep_conv_plan;
 int ditsep_conv_tc_plan_create(ditsep_conv_plan** plan, const void* in, int B, int H, int W, int Cin, int ld_in,
                                const void* w_bf16, int Cout, int ksize);
+
+/* Same, with a FUSED SHORTCUT: the res-block's skip path (ResnetBlockBigGANpp.forward, layerspp.py:322-327:
+ * `x = Conv_2(x)` when channels change, then `(x + h) / sqrt(2)`) is accumulated in the same TMEM accumulator as one
+ * extra 1x1 tap over a second input x_sc [B][H][W][ld_x] with Cx channels, instead of a separate 1x1 launch plus a
+ * residual read in the epilogue.  w: [CoutPad][taps*Cin + Cx] bf16 -- the shortcut filter (Conv_2's, or the identity
+ * for a plain residual) behind the taps along K; pass bias = b_conv + b_shortcut to ditsep_conv_tc_run.
+ * Needs the tile kernel with the whole filter resident in shared memory; returns a nonzero status (2) otherwise
+ * (the caller then keeps the unfused sequence). */
+int ditsep_conv_tc_plan_create_sc(ditsep_conv_plan** plan, const void* in, int B, int H, int W, int Cin, int ld_in,
+                                  const void* w_bf16, int Cout, int ksize, const void* x_sc, int Cx, int ld_x);
 void ditsep_conv_tc_plan_destroy(ditsep_conv_plan* plan);
 int ditsep_conv_tc_stats_layout(const ditsep_conv_plan* plan, ditsep_stats_src* layout);
 int ditsep_conv_tc_run(const ditsep_conv_plan* plan, const float* bias, const float* bias_b, int ld_bias_b,
@@ -172,7 +183,7 @@ int ditsep_conv_tc_run(const ditsep_conv_plan* plan, const float* bias, const fl
                        int ld_out, float* stats, void* stream);
 
 /* Debug aid (scripts/trace_conv.py): while buf != NULL, the tile kernel's first 4 CTAs write clock64() stamps of their
- * first 96 tiles to buf ([4][96][8] int64: 0 accumulator free, 1 first A tile landed, 2 MMAs issued, 3 accumulator
+ * first 96 tiles to buf ([4][96][16] int64: 0 accumulator free, 1 first A tile landed, 2 MMAs issued, 3 accumulator
  * full seen by the epilogue, 4 TMEM read + handed back, 5 tile stored, 6 TMA issued).  NULL disarms it. */
 void ditsep_debug_conv_trace(void* buf);
 

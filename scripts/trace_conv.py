@@ -9,18 +9,27 @@ Cout = int(sys.argv[2]) if len(sys.argv) > 2 else 64
 H = int(sys.argv[3]) if len(sys.argv) > 3 else 256
 B = int(sys.argv[4]) if len(sys.argv) > 4 else 32
 use_res = len(sys.argv) > 5 and sys.argv[5] == "1"
+Cx = int(sys.argv[6]) if len(sys.argv) > 6 else 0   # fused shortcut channels (0 = none)
 dev = "cuda"
 x = torch.randn(B, H, H, Cin, device=dev).to(torch.bfloat16)
-w = (torch.randn(Cout, 9, Cin, device=dev) / (9 * Cin) ** 0.5).to(torch.bfloat16)
+w = (torch.randn(Cout, 9 * Cin + Cx, device=dev) / (9 * Cin) ** 0.5).to(torch.bfloat16)
+xs = torch.randn(B, H, H, Cx, device=dev).to(torch.bfloat16) if Cx else None
 bias = torch.zeros(Cout, device=dev)
 out = torch.empty(B, H, H, Cout, device=dev, dtype=torch.bfloat16)
 res = torch.randn(B, H, H, Cout, device=dev).to(torch.bfloat16) if use_res else None
-plan = ops.ConvTcPlan(x, w, Cout, 3)
+plan = ops.ConvTcPlan(x, w, Cout, 3, shortcut=xs)
 stats = torch.empty(max(1, plan.stats_floats()), device=dev)
 for _ in range(3):
     plan.run(bias, out, residual=res, stats=stats)
 torch.cuda.synchronize()
-buf = torch.zeros(4, 96, 8, dtype=torch.int64, device=dev)
+e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+e0.record()
+for _ in range(10):
+    plan.run(bias, out, residual=res, stats=stats)
+e1.record()
+torch.cuda.synchronize()
+print(f"untraced: {e0.elapsed_time(e1) * 100:.1f} us per launch")
+buf = torch.zeros(4, 96, 16, dtype=torch.int64, device=dev)
 lib = _lib.load()
 lib.ditsep_debug_conv_trace(buf.data_ptr())
 plan.run(bias, out, residual=res, stats=stats)

@@ -19,7 +19,7 @@ __device__ __forceinline__ bool elect_one_sync() {
 
 __global__ void __launch_bounds__(128, 1) probe(int N, int mode, int iters, int sbo_bytes, long long* out) {
   extern __shared__ uint8_t raw[];
-  __shared__ __align__(8) uint64_t bar;
+  __shared__ __align__(8) uint64_t bar2[2];
   __shared__ uint32_t tmem_slot;
   const uint32_t base = (smem_u32(raw) + 1023u) & ~1023u;
   // A: up to 24 KB region (16 groups of 8 rows, group pitch sbo_bytes <= 1536); B: 256 rows x 128 B after it
@@ -31,7 +31,8 @@ __global__ void __launch_bounds__(128, 1) probe(int N, int mode, int iters, int 
     reinterpret_cast<uint32_t*>(raw + (base - smem_u32(raw)))[i] = v;
   }
   if (threadIdx.x == 0) {
-    asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(smem_u32(&bar)) : "memory");
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(smem_u32(&bar2[0])) : "memory");
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(smem_u32(&bar2[1])) : "memory");
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
   if (threadIdx.x < 32) {
@@ -43,7 +44,9 @@ __global__ void __launch_bounds__(128, 1) probe(int N, int mode, int iters, int 
   __syncthreads();
   asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
   const uint32_t tmem = tmem_slot;
-  if (threadIdx.x < 32) {
+  const int wid = threadIdx.x >> 5;
+  if (wid == 0 || (wid == 1 && (mode & 8))) {
+    uint64_t& bar = bar2[wid];
     const uint32_t idesc = (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(N >> 3) << 17) | ((128u >> 4) << 24);
     const uint64_t hi_a = (uint64_t)((uint32_t)(sbo_bytes >> 4) | (1u << 14) | (2u << 29)) << 32;
     const uint64_t hi_b = (uint64_t)(64u | (1u << 14) | (2u << 29)) << 32;
@@ -56,7 +59,7 @@ __global__ void __launch_bounds__(128, 1) probe(int N, int mode, int iters, int 
     for (int it = 0; it < iters; ++it) {
 #pragma unroll
       for (int k = 0; k < 4; ++k) {
-        const uint32_t d = tmem + ((alt && (k & 1)) ? (uint32_t)N : 0u);
+        const uint32_t d = tmem + (uint32_t)(wid * 224) + ((alt && (k & 1)) ? (uint32_t)N : 0u);
         const uint64_t db = hi_b | (uint64_t)(lo_b + 2 * k);
         if (cp) {  // refill the A slice this MMA reads: 128 rows x 32 B (one K = 16 step) from shared memory to TMEM
           const uint64_t dsrc = hi_a | (uint64_t)(lo_a + 2 * k);
@@ -89,7 +92,7 @@ __global__ void __launch_bounds__(128, 1) probe(int N, int mode, int iters, int 
           : "memory");
     }
     const long long t1 = clock64();
-    if (threadIdx.x == 0) out[blockIdx.x] = t1 - t0;
+    if (threadIdx.x == 0) out[blockIdx.x] = (mode & 8) ? (t1 - t0) / 2 : (t1 - t0);  // dual issue: per MMA of the pair
   }
   asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
   __syncthreads();
@@ -107,13 +110,14 @@ int main() {
   cudaFuncSetAttribute(probe, cudaFuncAttributeMaxDynamicSharedMemorySize, 70 * 1024);
   const int iters = 2000;
   const int Ns[] = {16, 32, 64, 96, 128, 192, 256};
-  const char* names[] = {"SS", "TS", "SS alt-acc", "TS alt-acc", "-", "TS+cp", "-", "TS+cp alt"};
+  const char* names[] = {"SS", "TS", "SS alt-acc", "TS alt-acc", "-", "TS+cp", "-", "TS+cp alt", "SS 2warps", "TS 2warps"};
   for (int sbo : {1024, 1280}) {
-    for (int mode = 0; mode < 8; ++mode) {
+    for (int mode = 0; mode < 10; ++mode) {
       if (mode == 4 || mode == 6 || (sbo == 1280 && mode != 0 && mode != 5)) continue;
       for (int N : Ns) {
         if ((mode & 2) && 2 * N > 384) continue;
         if ((mode & 4) && N > 192) continue;
+        if ((mode & 8) && N > 192) continue;
         for (int rep = 0; rep < 2; ++rep) probe<<<sms, 128, 70 * 1024>>>(N, mode, iters, sbo, d_out);
         cudaError_t e = cudaDeviceSynchronize();
         if (e != cudaSuccess) { printf("N=%d mode=%d: %s\n", N, mode, cudaGetErrorString(e)); return 1; }

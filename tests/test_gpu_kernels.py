@@ -298,6 +298,61 @@ def test_conv_tc(B, H, W, Cin, ld_extra, Cout, k):
     assert rel(out2.float(), ref) < 4e-3
 
 
+@pytest.mark.parametrize("B,H,W,Cin,Cout,Cx,k,ld_extra", [
+    (2, 32, 24, 64, 64, 64, 3, 0),      # identity-shaped shortcut (Cx == Cout)
+    (3, 48, 40, 64, 64, 128, 3, 64),    # up-path block: x = concat of 128 channels inside a wider buffer
+    (1, 16, 16, 128, 128, 128, 3, 0),   # two N tiles, two main chunks, two shortcut chunks
+    (2, 17, 21, 64, 48, 64, 1, 0),      # ragged image, 1x1 main conv, Cout not a multiple of 64
+])
+def test_conv_tc_fused_shortcut(B, H, W, Cin, Cout, Cx, k, ld_extra):
+    """ditsep_conv_tc_plan_create_sc: out = (conv_k(h) + conv_1x1(x) + bias + bias_b) * scale in ONE launch, the
+    shortcut accumulated in TMEM as an extra tap; statistics partials are those of the stored output."""
+    h = torch.randn(B, H, W, Cin, generator=g(80)).to(torch.bfloat16)
+    xbuf = torch.randn(B, H, W, Cx + ld_extra, generator=g(81)).to(torch.bfloat16)
+    x = xbuf[..., ld_extra:]
+    wm = (torch.randn(Cout, k * k, Cin, generator=g(82)) / math.sqrt(k * k * Cin)).to(torch.bfloat16)
+    wsc = (torch.randn(Cout, 1, Cx, generator=g(83)) / math.sqrt(Cx)).to(torch.bfloat16)
+    if Cx == Cout and k == 3 and B == 2:
+        wsc = torch.eye(Cout).reshape(Cout, 1, Cx).to(torch.bfloat16)  # plain residual as an identity filter
+    bias = 0.1 * torch.randn(Cout, generator=g(84))
+    bias_b = 0.1 * torch.randn(B, Cout, generator=g(85))
+    cp = (Cout + 15) // 16 * 16
+    wpad = torch.zeros(cp, k * k * Cin + Cx, dtype=torch.bfloat16)
+    wpad[:Cout, :k * k * Cin] = wm.reshape(Cout, -1)
+    wpad[:Cout, k * k * Cin:] = wsc.reshape(Cout, -1)
+    hd, xd = h.to(DEV), xbuf.to(DEV)[..., ld_extra:]
+    plan = ops.ConvTcPlan(hd, wpad.to(DEV), Cout, k, shortcut=xd)
+    lay = plan.stats_layout()
+    stats_buf = torch.zeros(max(1, plan.stats_floats()), device=DEV)
+    out = torch.empty(B, H, W, Cout, device=DEV)
+    plan.run(bias.to(DEV), out, bias_b=bias_b.to(DEV), out_scale=0.7, stats=stats_buf)
+    sc = torch.empty(B, H, W, Cout)
+    E.conv_direct(x.float(), wsc.float(), torch.zeros(Cout), sc, 1)
+    ref = torch.empty(B, H, W, Cout)
+    E.conv_direct(h.float(), wm.float(), bias, ref, k, bias_b=bias_b, residual=sc, out_scale=0.7)
+    assert rel(out, ref) < 2e-5, rel(out, ref)
+    sums = _conv_partials_to_sums(stats_buf, lay, B)
+    o = out.double().cpu()
+    assert rel(sums[..., 1], (o * o).sum(dim=(1, 2))) < 1e-5
+    # bf16 output + second run bit-identical
+    outb = torch.empty(B, H, W, Cout, device=DEV, dtype=torch.bfloat16)
+    plan.run(bias.to(DEV), outb, bias_b=bias_b.to(DEV), out_scale=0.7)
+    outb2 = torch.empty_like(outb)
+    plan.run(bias.to(DEV), outb2, bias_b=bias_b.to(DEV), out_scale=0.7)
+    assert torch.equal(outb, outb2) and rel(outb.float(), ref) < 4e-3
+
+
+def test_conv_tc_fused_shortcut_refuses_what_it_cannot_fuse():
+    x = torch.randn(1, 16, 16, 256, device=DEV).to(torch.bfloat16)
+    w = torch.zeros(128, 9 * 256 + 256, device=DEV, dtype=torch.bfloat16)
+    with pytest.raises(ops.DitsepError):   # 9 x 256 x 64 filter does not fit shared memory: no resident mode
+        ops.ConvTcPlan(x, w, 128, 3, shortcut=x)
+    xs = torch.randn(2, 4, 4, 64, device=DEV).to(torch.bfloat16)
+    ws = torch.zeros(64, 9 * 64 + 64, device=DEV, dtype=torch.bfloat16)
+    with pytest.raises(ops.DitsepError):   # image below one 8 x 16 tile
+        ops.ConvTcPlan(xs, ws, 64, 3, shortcut=xs)
+
+
 def test_first_layer_hilo_split_on_tensor_cores():
     """ops.split_hilo + the [wh | wh | wl] filter (engine._pack_conv_hilo): the 6-channel fp32 input conv run by the
     tcgen05 kernel must match the fp32 convolution to fp32-class accuracy, not bf16-class."""
@@ -306,7 +361,8 @@ def test_first_layer_hilo_split_on_tensor_cores():
     x = torch.randn(B, H, W, Cin, generator=g(70))
     weight = torch.randn(Cout, Cin, 3, 3, generator=g(71)) / math.sqrt(9 * Cin)
     bias = 0.1 * torch.randn(Cout, generator=g(72))
-    wide = torch.full((B, H, W, 64), 7.0, device=DEV, dtype=torch.bfloat16)
+    wide = torch.zeros(B, H, W, 64, device=DEV, dtype=torch.bfloat16)  # channels >= 24 are the caller's zeros
+    wide[..., :24] = 7.0
     ops.split_hilo(x.to(DEV), wide)
     hi = x.to(torch.bfloat16)
     lo = (x - hi.float()).to(torch.bfloat16)
