@@ -67,6 +67,8 @@ SIGNATURES = {
     "ditsep_conv_tc_stats_layout": (c_int, [c_void_p, C.POINTER(StatsSrc)]),
     "ditsep_conv_tc_run": (c_int, [c_void_p, c_void_p, c_void_p, c_int, c_void_p, c_int, c_int, c_float, c_void_p,
                                    c_int, c_int, c_void_p, c_void_p]),
+    "ditsep_conv_tc_run_gn": (c_int, [c_void_p, c_void_p, c_int, c_void_p, c_void_p, c_int, c_void_p, c_int, c_int,
+                                      c_float, c_void_p, c_int, c_int, c_void_p, c_void_p]),
     "ditsep_attention": (c_int, [c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_int, c_int, c_void_p, c_int,
                                  c_void_p]),
     "ditsep_temb_mlp": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_int,

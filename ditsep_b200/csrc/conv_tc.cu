@@ -61,6 +61,8 @@ struct ConvTcParams {
   // tile kernel
   int num_tiles, tiles_per_image, chunks, w_resident, a_stages, w_stages;
   int halo, row_pitch, a_rows, a_stage_bytes;
+  const float* in_ss;      // nullable: per-(image, input channel) scale / shift [B][2][Cin] applied to the INPUT tile
+  int in_silu;             //   in shared memory before the MMAs read it: a = silu?(x * scale + shift), zero outside the image
   int xchunks;             // fused shortcut: 64-channel blocks of a second input x accumulated as a 1x1 tap (0 = none)
   float* stats;            // nullable: partial sums [B][segs_per_image][4][ld_part][2]
   int seg_len, segs_per_image, ld_part;
@@ -291,10 +293,12 @@ __global__ void __launch_bounds__(kThreads) conv_tc_kernel(const __grid_constant
 
 // ---- kernel 2: 8 x 16 pixel tiles with halo, persistent CTAs over contiguous segment ranges ----
 constexpr int kTileW = 8, kTileH = 16;
-constexpr int kCtrlWarps = 4;   // 0: TMA producer, 1: TMEM allocator + MMA issuer (even tiles), 2: MMA issuer (odd tiles), 3: idle (the register file
-                                // is allocated in units of 4 warps: 20 warps x 96 registers fill it)
+// Warps: 0 TMA producer, 1 TMEM allocator + MMA issuer (even tiles), 2 MMA issuer (odd tiles), 3 idle; then, in the
+// kXf instantiation only, 4-7: GroupNorm + SiLU of the landed A tiles in place in shared memory; then 16 epilogue warps.
+// 20 warps x 96 registers fill the register file; the kXf variant runs 24 warps x 80 registers.
+constexpr int kXformWarp0 = 4, kXformWarps = 4;
 constexpr int kEpiWarps = 16;   // warp w: TMEM lane quadrant w % 4, output channels [16*((w-4)/4), +16)
-constexpr int kTileThreads = (kCtrlWarps + kEpiWarps) * 32;
+constexpr int tile_threads(bool xf) { return ((xf ? 8 : 4) + kEpiWarps) * 32; }
 constexpr int kMaxAStages = 4, kMaxWStages = 4;
 constexpr int kTileMaxBN = 64;
 
@@ -330,14 +334,15 @@ struct TileWalk {
   }
 };
 
-template <int KS, bool kRes, bool kFast>
-__global__ void __launch_bounds__(kTileThreads, 1) conv_tc_tile_kernel(const __grid_constant__ CUtensorMap mapA,
+template <int KS, bool kRes, bool kFast, bool kXf>
+__global__ void __launch_bounds__(tile_threads(kXf), 1) conv_tc_tile_kernel(const __grid_constant__ CUtensorMap mapA,
                                                                        const __grid_constant__ CUtensorMap mapW,
                                                                        const __grid_constant__ CUtensorMap mapX,
                                                                        const __grid_constant__ ConvTcParams p) {
   constexpr int kTaps = KS * KS, kHalo = KS / 2, kRowPitch = kTileW + 2 * kHalo;
+  constexpr int kCtrlWarps = kXf ? 8 : 4;
   extern __shared__ uint8_t smem_raw[];
-  __shared__ __align__(8) uint64_t bar_a_full[kMaxAStages], bar_a_empty[kMaxAStages];
+  __shared__ __align__(8) uint64_t bar_a_full[kMaxAStages], bar_a_empty[kMaxAStages], bar_a_ready[kMaxAStages];
   __shared__ __align__(8) uint64_t bar_w_full[kMaxWStages], bar_w_empty[kMaxWStages];
   __shared__ __align__(8) uint64_t bar_w_res, bar_acc_full[2], bar_acc_empty[2], bar_turn[2];
   __shared__ uint32_t tmem_base_slot;
@@ -354,6 +359,7 @@ __global__ void __launch_bounds__(kTileThreads, 1) conv_tc_tile_kernel(const __g
     for (int s = 0; s < kMaxAStages; ++s) {
       mbar_init(smem_u32(&bar_a_full[s]), 1);
       mbar_init(smem_u32(&bar_a_empty[s]), 1);
+      mbar_init(smem_u32(&bar_a_ready[s]), kXformWarps);
     }
     for (int s = 0; s < kMaxWStages; ++s) {
       mbar_init(smem_u32(&bar_w_full[s]), 1);
@@ -483,7 +489,7 @@ __global__ void __launch_bounds__(kTileThreads, 1) conv_tc_tile_kernel(const __g
           const bool last_st = pos == nsteps - 1;
           const int widx = is_x ? nc * kTaps + (xfirst ? pos : pos - nc) : (xfirst ? pos - nx : pos) * kTaps;
           const uint32_t w_lo = w_base + (uint32_t)widx * w_step;
-          mbar_wait(smem_u32(&bar_a_full[sa]), pa);
+          mbar_wait(smem_u32(kXf ? &bar_a_ready[sa] : &bar_a_full[sa]), pa);
           if (last_st && lane == 0) mbar_arrive(smem_u32(&bar_turn[my ^ 1u]));  // the ring is the other warp's now
           tc_fence_after();
           if (pos == 0 && lane == 0) trace_stamp(p, it, 1);
@@ -532,7 +538,7 @@ __global__ void __launch_bounds__(kTileThreads, 1) conv_tc_tile_kernel(const __g
         const uint32_t tmem_d = tmem_acc + ab * (uint32_t)p.BN;
         uint32_t w_lo;
         for (int ch = 0; ch < p.chunks; ++ch) {
-          mbar_wait(smem_u32(&bar_a_full[sa]), pa);
+          mbar_wait(smem_u32(kXf ? &bar_a_ready[sa] : &bar_a_full[sa]), pa);
           tc_fence_after();
           const uint32_t a_lo = ((a_ring + (uint32_t)(sa * p.a_stage_bytes)) >> 4) | lbo;
           constexpr int kRow16 = 128 >> 4;
@@ -558,6 +564,56 @@ __global__ void __launch_bounds__(kTileThreads, 1) conv_tc_tile_kernel(const __g
             __syncwarp();
             if (++sw == p.w_stages) { sw = 0; pw ^= 1u; }
           }
+          if (++sa == p.a_stages) { sa = 0; pa ^= 1u; }
+        }
+      }
+    }
+  } else if (kXf && warp >= kXformWarp0 && warp < kXformWarp0 + kXformWarps) {
+    // GroupNorm + SiLU of the conv INPUT, fused: the producing layer stored the raw tensor; its normalisation
+    // (layerspp.py:297,318: act(GroupNorm(x))) is applied here to each landed A tile, in place in shared memory, before
+    // the MMAs read it -- instead of a separate pass that reads and rewrites the whole tensor in HBM.
+    // One thread = one 16-byte channel pack (fixed for its whole life: scale / shift in registers) of every 16th row of
+    // the halo box.  Pixels outside the image stay zero (TMA zero fill): the conv pads the ACTIVATED tensor.
+    if (kXf) {
+      const int t = (int)threadIdx.x - kXformWarp0 * 32;
+      const int lc = t & 7;
+      const bool xfirst = kRes && p.xchunks > 0 && p.a_stages >= p.xchunks + 2;
+      const int nsteps = p.chunks + (kRes ? p.xchunks : 0);
+      uint8_t* const ring_ptr = smem_raw + (a_ring - smem_u32(smem_raw));
+      int sa = 0;
+      uint32_t pa = 0;
+      const bool silu = p.in_silu != 0;
+      TileWalk tw;
+      for (tw.init(p); !tw.done(); tw.next(p)) {
+        const int y0 = tw.ty * kTileH - kHalo, x0 = tw.tx * kTileW - kHalo;
+        for (int pos = 0; pos < nsteps; ++pos) {
+          const bool is_x = kRes && (xfirst ? pos < p.xchunks : pos >= p.chunks);
+          mbar_wait_sleep(smem_u32(&bar_a_full[sa]), pa);
+          if (!is_x) {
+            const int ch = xfirst ? pos - p.xchunks : pos;
+            float sc[8], sh[8];
+            const float* ssp = p.in_ss + ((int64_t)tw.b * 2) * p.Cin + ch * kBlockK + lc * 8;
+            Pack8<float>::load(ssp, sc);
+            Pack8<float>::load(ssp + p.Cin, sh);
+            uint8_t* const stage = ring_ptr + (size_t)sa * p.a_stage_bytes;
+#pragma unroll 3
+            for (int r = t >> 3; r < p.a_rows; r += kXformWarps * 4) {
+              const int hy = r / kRowPitch, hx = r - hy * kRowPitch;
+              const bool inside = (unsigned)(y0 + hy) < (unsigned)p.H && (unsigned)(x0 + hx) < (unsigned)p.W;
+              bf16* ptr = reinterpret_cast<bf16*>(stage + r * 128 + ((lc ^ (r & 7)) << 4));  // 128-byte swizzle
+              float f[8];
+              Pack8<bf16>::load(ptr, f);
+#pragma unroll
+              for (int i = 0; i < 8; ++i) {
+                const float v = fmaf(f[i], sc[i], sh[i]);
+                f[i] = silu ? silu_f(v) : v;
+              }
+              if (inside) Pack8<bf16>::store(ptr, f);
+            }
+            asm volatile("fence.proxy.async.shared::cta;" ::: "memory");  // generic writes -> visible to the tensor core
+          }
+          __syncwarp();
+          if (lane == 0) mbar_arrive(smem_u32(&bar_a_ready[sa]));
           if (++sa == p.a_stages) { sa = 0; pa ^= 1u; }
         }
       }
@@ -929,7 +985,9 @@ extern "C" int ditsep_conv_tc_plan_create_sc(ditsep_conv_plan** plan, const void
     DITSEP_CUDA(cudaFuncSetAttribute(conv_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                      1024 + kMaxStages * (kABytes + 128 * 128)));
 #define DITSEP_TILE_ATTR(KS, RES, FAST)                                                                              \
-  DITSEP_CUDA(cudaFuncSetAttribute(conv_tc_tile_kernel<KS, RES, FAST>, cudaFuncAttributeMaxDynamicSharedMemorySize, \
+  DITSEP_CUDA(cudaFuncSetAttribute(conv_tc_tile_kernel<KS, RES, FAST, false>,                                       \
+                                   cudaFuncAttributeMaxDynamicSharedMemorySize, 224 * 1024));                       \
+  DITSEP_CUDA(cudaFuncSetAttribute(conv_tc_tile_kernel<KS, RES, FAST, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, \
                                    224 * 1024))
     DITSEP_TILE_ATTR(1, true, true); DITSEP_TILE_ATTR(1, true, false); DITSEP_TILE_ATTR(1, false, true);
     DITSEP_TILE_ATTR(1, false, false); DITSEP_TILE_ATTR(3, true, true); DITSEP_TILE_ATTR(3, true, false);
@@ -961,7 +1019,17 @@ extern "C" int ditsep_conv_tc_stats_layout(const ditsep_conv_plan* plan, ditsep_
 extern "C" int ditsep_conv_tc_run(const ditsep_conv_plan* plan, const float* bias, const float* bias_b, int ld_bias_b,
                                   const void* residual, int res_dtype, int ld_res, float out_scale, void* out,
                                   int out_dtype, int ld_out, float* stats, void* stream) {
+  return ditsep_conv_tc_run_gn(plan, nullptr, 0, bias, bias_b, ld_bias_b, residual, res_dtype, ld_res, out_scale, out,
+                               out_dtype, ld_out, stats, stream);
+}
+
+extern "C" int ditsep_conv_tc_run_gn(const ditsep_conv_plan* plan, const float* in_scale_shift, int in_silu,
+                                     const float* bias, const float* bias_b, int ld_bias_b, const void* residual,
+                                     int res_dtype, int ld_res, float out_scale, void* out, int out_dtype, int ld_out,
+                                     float* stats, void* stream) {
   DITSEP_REQUIRE(plan && out, "conv_tc_run: null pointer");
+  DITSEP_REQUIRE(!in_scale_shift || plan->tile,
+                 "conv_tc_run_gn: the fused input GroupNorm needs the tile kernel (image >= 8 x 16)");
   DITSEP_REQUIRE(out_dtype == DITSEP_F32 || out_dtype == DITSEP_BF16, "conv_tc_run: unknown out dtype %d", out_dtype);
   DITSEP_REQUIRE(!residual || res_dtype == DITSEP_F32 || res_dtype == DITSEP_BF16, "conv_tc_run: unknown residual dtype");
   DITSEP_REQUIRE(ld_out >= plan->p.Cout, "conv_tc_run: ld_out=%d < Cout=%d", ld_out, plan->p.Cout);
@@ -971,6 +1039,7 @@ extern "C" int ditsep_conv_tc_run(const ditsep_conv_plan* plan, const float* bia
   p.residual = residual; p.res_dtype = res_dtype; p.ld_res = ld_res;
   p.out_scale = out_scale; p.out = out; p.out_dtype = out_dtype; p.ld_out = ld_out;
   p.stats = stats;
+  p.in_ss = in_scale_shift; p.in_silu = in_silu;
   p.trace = g_conv_trace;
   if (plan->tile) {
     dim3 grid((unsigned)plan->grid_x, (unsigned)p.n_tiles);
@@ -979,8 +1048,15 @@ extern "C" int ditsep_conv_tc_run(const ditsep_conv_plan* plan, const float* bia
                       (reinterpret_cast<uintptr_t>(out) & 15) == 0 &&
                       (!residual || (res_dtype == DITSEP_BF16 && (ld_res & 7) == 0 &&
                                      (reinterpret_cast<uintptr_t>(residual) & 15) == 0));
-#define DITSEP_TILE_LAUNCH(KS, RES, FAST) \
-  conv_tc_tile_kernel<KS, RES, FAST><<<grid, kTileThreads, plan->smem, st>>>(plan->mapA, plan->mapW, plan->mapX, p)
+#define DITSEP_TILE_LAUNCH(KS, RES, FAST)                                                                            \
+  do {                                                                                                               \
+    if (p.in_ss)                                                                                                     \
+      conv_tc_tile_kernel<KS, RES, FAST, true><<<grid, tile_threads(true), plan->smem, st>>>(plan->mapA, plan->mapW, \
+                                                                                              plan->mapX, p);        \
+    else                                                                                                             \
+      conv_tc_tile_kernel<KS, RES, FAST, false><<<grid, tile_threads(false), plan->smem, st>>>(plan->mapA, plan->mapW, \
+                                                                                                plan->mapX, p);      \
+  } while (0)
     if (p.ksize == 3) {
       if (p.w_resident) { if (fast) DITSEP_TILE_LAUNCH(3, true, true); else DITSEP_TILE_LAUNCH(3, true, false); }
       else { if (fast) DITSEP_TILE_LAUNCH(3, false, true); else DITSEP_TILE_LAUNCH(3, false, false); }

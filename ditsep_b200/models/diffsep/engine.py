@@ -404,16 +404,13 @@ class _Plan:
             # progressive output skip: GN -> SiLU -> conv3x3(C -> Cin0), summed over levels
             cch = layout[i].in_ch
             ss = self._scale_shift(cur, w[f"gn{i}"])
-            hact = pool.get((B, hh, ww, cch), adt)
-            add((ops.gn_apply, (cur, ss, True, hact), {}))
             i += 1
             newpyr = new(B, hh, ww, Cin0, dtype=f32)
             if pyramid is None:
-                self._conv(hact, w[f"conv{i}"], newpyr)
+                self._conv(cur, w[f"conv{i}"], newpyr, in_ss=ss)
             else:
                 add((ops.fir_resample, (pyramid, True), {"out_x": newpyr}))
-                self._conv(hact, w[f"conv{i}"], newpyr, residual=newpyr)
-            pool.put(hact)
+                self._conv(cur, w[f"conv{i}"], newpyr, residual=newpyr, in_ss=ss)
             pyramid = newpyr
             i += 1
             if lvl != 0:
@@ -428,7 +425,7 @@ class _Plan:
 
     # ------------------------------------------------------------------ building blocks
     def _conv(self, x, cw: _ConvW, out, bias_b=None, residual=None, out_scale: float = 1.0, want_stats: bool = False,
-              shortcut=None) -> bool:
+              shortcut=None, in_ss=None, in_silu: bool = True, gn_inplace: bool = False) -> bool:
         """3x3 / 1x1 conv with the fused epilogue; tcgen05 path when the shape allows it.  want_stats:
         GroupNorm will normalise `out` (alone or as part of a concat buffer) -- its per-channel sums come
         from the conv epilogue when the kernel can leave them, else from one explicit pass over `out`."""
@@ -444,6 +441,22 @@ class _Plan:
                 plan = ops.ConvTcPlan(x, cw.w_bf16, cw.cout, cw.ksize, shortcut=shortcut)
             except ops.DitsepError:
                 return False
+        if in_ss is not None:
+            # conv(act(GroupNorm(x))) (layerspp.py:297-298,318-320): the tile kernel CAN normalise the landed tiles in
+            # shared memory (ops.ConvTcPlan.run in_ss, bit-identical to gn_apply + conv).  Measured at batch 32 (r1m) the
+            # fused variant is SLOWER: 13.2 vs 12.3 ms per score step -- four transform warps are MUFU-bound at ~4400
+            # cycles per tile against 2850 of MMA work -- so it is opt-in (DITSEP_FUSE_GN=1) until the transform is faster
+            if use_tc and plan is None:
+                plan = ops.ConvTcPlan(x, cw.w_bf16, cw.cout, cw.ksize)
+            if plan is not None and plan.tile and os.environ.get("DITSEP_FUSE_GN", "0") == "1":
+                kw["in_ss"], kw["in_silu"] = in_ss, in_silu
+            else:
+                act = x if gn_inplace else self.pool.get(tuple(x.shape), x.dtype)
+                self.steps.append((ops.gn_apply, (x, in_ss, in_silu, act), {}))
+                if act is not x:
+                    self.pool.put(act)  # free again once this conv has run (the launch list is sequential)
+                x = act
+                plan = None if shortcut is None else ops.ConvTcPlan(x, cw.w_bf16, cw.cout, cw.ksize, shortcut=shortcut)
         key = (out.data_ptr(), out.shape[3])
         self.stat_src.pop(key, None)  # whatever was known about this view is stale now
         fused = False
@@ -505,24 +518,27 @@ class _Plan:
         else:
             Ho, Wo = H, W
             xr = x
-            hA = pool.get((B, H, W, cin), self.adt)
-            add((ops.gn_apply, (x, ss0, True, hA), {}))
+            hA = None
         h1 = pool.get((B, Ho, Wo, cout), self.adt)
         off = w[f"dense_off{i}"]
-        self._conv(hA, w[f"conv{i}a"], h1, bias_b=self.dense[:, off:off + cout], want_stats=True)
-        pool.put(hA)
+        if hA is None:  # act(GroupNorm_0(x)) rides in conv0's operand path
+            self._conv(x, w[f"conv{i}a"], h1, bias_b=self.dense[:, off:off + cout], want_stats=True, in_ss=ss0)
+        else:
+            self._conv(hA, w[f"conv{i}a"], h1, bias_b=self.dense[:, off:off + cout], want_stats=True)
+            pool.put(hA)
         ss1 = self._scale_shift(h1, w[f"gn{i}b"])
-        add((ops.gn_apply, (h1, ss1, True, h1), {}))  # in place
-        self.stat_src.pop((h1.data_ptr(), cout), None)
+        # act(GroupNorm_1(h)) rides in conv1's operand path (or, unfused, is applied to h1 in place)
+        gn1 = {"in_ss": ss1, "in_silu": True, "gn_inplace": True}
         fused = w.get(f"conv{i}b_sc")
         if not (fused is not None and self._conv(h1, fused, out, shortcut=xr, out_scale=1.0 / math.sqrt(2.0),
-                                                 want_stats=True)):
+                                                 want_stats=True, **gn1)):
             if f"conv{i}c" in w:
                 self._conv(xr, w[f"conv{i}c"], out)
                 res = out
             else:
                 res = xr
-            self._conv(h1, w[f"conv{i}b"], out, residual=res, out_scale=1.0 / math.sqrt(2.0), want_stats=True)
+            self._conv(h1, w[f"conv{i}b"], out, residual=res, out_scale=1.0 / math.sqrt(2.0), want_stats=True, **gn1)
+        self.stat_src.pop((h1.data_ptr(), cout), None)
         pool.put(h1)
         if xr is not x:
             pool.put(xr)
@@ -533,9 +549,8 @@ class _Plan:
         B, H, W, C = x.shape
         ss = self._scale_shift(x, w[f"gn{i}"])
         hn = pool.get((B, H, W, C), self.adt)
-        add((ops.gn_apply, (x, ss, False, hn), {}))
         qkv = pool.get((B, H, W, 3 * C), self.adt)
-        self._conv(hn, w[f"qkv{i}"], qkv)
+        self._conv(x, w[f"qkv{i}"], qkv, in_ss=ss, in_silu=False)  # GroupNorm_0 (no activation) in the operand path
         add((ops.attention, (qkv[..., :C], qkv[..., C:2 * C], qkv[..., 2 * C:], hn), {}))
         self._conv(hn, w[f"proj{i}"], out, residual=x, out_scale=1.0 / math.sqrt(2.0), want_stats=True)
         pool.put(hn)

@@ -254,7 +254,7 @@ class ConvTcPlan:
             raise _lib.DitsepError("conv_tc: bf16 activations and packed bf16 weights required")
         self._h = C.c_void_p()
         self._keep = (x, w_bf16, shortcut)
-        self.Cout = Cout
+        self.Cout, self.Cin = Cout, Cin
         self.K = ksize * ksize * Cin + (0 if shortcut is None else shortcut.shape[3])
         self.shape = (B, H, W)
         if w_bf16.numel() % self.K or w_bf16.numel() // self.K < Cout:
@@ -280,16 +280,27 @@ class ConvTcPlan:
         lay = self.stats_layout()
         return 0 if lay.kind == _lib.STATS_NONE else self.shape[0] * lay.n_part * lay.ld * 2
 
-    def run(self, bias, out, bias_b=None, residual=None, out_scale: float = 1.0, stats=None):
-        """stats: f32 buffer of >= stats_floats() elements receiving the per-segment statistics partials."""
-        _cuda(bias, out, bias_b, residual, stats)
+    @property
+    def tile(self) -> bool:
+        """True when this plan runs the persistent tile kernel (fused statistics, fused input GroupNorm)."""
+        return self.stats_layout().kind != _lib.STATS_NONE
+
+    def run(self, bias, out, bias_b=None, residual=None, out_scale: float = 1.0, stats=None, in_ss=None,
+            in_silu: bool = True):
+        """stats: f32 buffer of >= stats_floats() elements receiving the per-segment statistics partials.
+        in_ss: (B, 2, Cin) f32 scale / shift of the INPUT's GroupNorm, applied (+ SiLU if in_silu) to every A tile in
+        shared memory (ditsep_conv_tc_run_gn): the plan's input is then the raw, un-normalised tensor."""
+        _cuda(bias, out, bias_b, residual, stats, in_ss)
         if stats is not None and (stats.dtype != torch.float32 or stats.numel() < max(1, self.stats_floats())):
             raise _lib.DitsepError("conv_tc: statistics buffer too small (or this plan cannot produce statistics)")
-        check(_lib.load().ditsep_conv_tc_run(self._h, _ptr(bias), _ptr(bias_b),
+        if in_ss is not None and (in_ss.dtype != torch.float32 or not in_ss.is_contiguous()
+                                  or in_ss.numel() != self.shape[0] * 2 * self.Cin):
+            raise _lib.DitsepError("conv_tc: in_ss must be a contiguous f32 (B, 2, Cin) tensor")
+        check(_lib.load().ditsep_conv_tc_run_gn(self._h, _ptr(in_ss), int(bool(in_silu)), _ptr(bias), _ptr(bias_b),
                                              0 if bias_b is None else bias_b.stride(0), _ptr(residual),
                                              0 if residual is None else _dt(residual),
                                              0 if residual is None else nhwc_ld(residual), out_scale, _ptr(out),
-                                             _dt(out), nhwc_ld(out), _ptr(stats), _stream()), "conv_tc_run")
+                                                _dt(out), nhwc_ld(out), _ptr(stats), _stream()), "conv_tc_run")
 
     def __del__(self):
         h = getattr(self, "_h", None)

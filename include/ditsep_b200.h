@@ -182,6 +182,16 @@ int ditsep_conv_tc_run(const ditsep_conv_plan* plan, const float* bias, const fl
                        const void* residual, int res_dtype, int ld_res, float out_scale, void* out, int out_dtype,
                        int ld_out, float* stats, void* stream);
 
+/* Same, with the INPUT's GroupNorm (+ SiLU) fused: `in` holds the RAW tensor its producer stored, and every A tile is
+ * normalised in shared memory after it lands and before the MMAs read it -- a = silu?(x * scale + shift) per
+ * (image, input channel), zero outside the image (the conv pads the activated tensor) -- replacing the separate
+ * ditsep_gn_apply pass of ResnetBlockBigGANpp.forward's act(GroupNorm_0(x)) / act(GroupNorm_1(h)) (layerspp.py:297,318).
+ * in_scale_shift: [B][2][Cin] f32 from ditsep_gn_finalize / ditsep_gn_stats (NULL = plain ditsep_conv_tc_run);
+ * a fused shortcut input (plan_create_sc) is NOT normalised.  Tile-kernel plans only (status 2 otherwise). */
+int ditsep_conv_tc_run_gn(const ditsep_conv_plan* plan, const float* in_scale_shift, int in_silu, const float* bias,
+                          const float* bias_b, int ld_bias_b, const void* residual, int res_dtype, int ld_res,
+                          float out_scale, void* out, int out_dtype, int ld_out, float* stats, void* stream);
+
 /* Debug aid (scripts/trace_conv.py): while buf != NULL, the tile kernel's first 4 CTAs write clock64() stamps of their
  * first 96 tiles to buf ([4][96][16] int64: 0 accumulator free, 1 first A tile landed, 2 MMAs issued, 3 accumulator
  * full seen by the epilogue, 4 TMEM read + handed back, 5 tile stored, 6 TMA issued).  NULL disarms it. */

@@ -342,6 +342,62 @@ def test_conv_tc_fused_shortcut(B, H, W, Cin, Cout, Cx, k, ld_extra):
     assert torch.equal(outb, outb2) and rel(outb.float(), ref) < 4e-3
 
 
+@pytest.mark.parametrize("B,H,W,Cin,Cout,Cx,k,silu", [
+    (2, 32, 24, 64, 64, 0, 3, True),
+    (3, 40, 17, 128, 64, 0, 3, True),      # two K chunks, ragged width (tiles hang over the right edge)
+    (2, 16, 16, 128, 384, 0, 1, False),    # attention q/k/v projection: GroupNorm without SiLU, 1x1
+    (2, 48, 32, 64, 64, 128, 3, True),     # with a fused shortcut (which must NOT be normalised)
+    (1, 16, 8, 256, 128, 0, 3, True),      # streamed filter (not resident), smallest image of the tile kernel
+])
+def test_conv_tc_fused_input_groupnorm(B, H, W, Cin, Cout, Cx, k, silu):
+    """ditsep_conv_tc_run_gn: conv(silu?(x * scale + shift)) with the normalisation applied to the landed tiles in
+    shared memory must equal gn_apply followed by the plain conv on the same device -- bit for bit."""
+    x = torch.randn(B, H, W, Cin, generator=g(90)).to(torch.bfloat16).to(DEV)
+    ss = torch.stack([1.0 + 0.3 * torch.randn(B, Cin, generator=g(91)), 0.5 * torch.randn(B, Cin, generator=g(92))],
+                     dim=1).contiguous().to(DEV)
+    cp = (Cout + 15) // 16 * 16
+    w = torch.zeros(cp, k * k * Cin + Cx, dtype=torch.bfloat16)
+    w[:Cout] = (torch.randn(Cout, k * k * Cin + Cx, generator=g(93)) / math.sqrt(k * k * Cin)).to(torch.bfloat16)
+    w = w.to(DEV)
+    xs = torch.randn(B, H, W, Cx, generator=g(94)).to(torch.bfloat16).to(DEV) if Cx else None
+    bias = (0.1 * torch.randn(Cout, generator=g(95))).to(DEV)
+    act = torch.empty_like(x)
+    ops.gn_apply(x, ss, silu, act)
+    ref_plan = ops.ConvTcPlan(act, w, Cout, k, shortcut=xs)
+    ref = torch.empty(B, H, W, Cout, device=DEV, dtype=torch.bfloat16)
+    ref_plan.run(bias, ref)
+    plan = ops.ConvTcPlan(x, w, Cout, k, shortcut=xs)
+    assert plan.tile
+    st = torch.zeros(max(1, plan.stats_floats()), device=DEV)
+    st_ref = torch.zeros_like(st)
+    out = torch.empty_like(ref)
+    plan.run(bias, out, in_ss=ss, in_silu=silu, stats=st)
+    ref_plan.run(bias, ref, stats=st_ref)
+    assert torch.equal(out, ref), rel(out.float(), ref.float())
+    assert torch.equal(st, st_ref)
+    # and against the fp32 definition (bf16 rounding of the activation + output only)
+    a32 = x.float().cpu() * ss[:, 0].cpu()[:, None, None, :] + ss[:, 1].cpu()[:, None, None, :]
+    a32 = torch.nn.functional.silu(a32) if silu else a32
+    full = torch.empty(B, H, W, Cout)
+    wm = w[:Cout, :k * k * Cin].float().cpu().reshape(Cout, k * k, Cin)
+    E.conv_direct(a32, wm, bias.cpu(), full, k)
+    if Cx:
+        sc = torch.empty(B, H, W, Cout)
+        E.conv_direct(xs.float().cpu(), w[:Cout, k * k * Cin:].float().cpu().reshape(Cout, 1, Cx), torch.zeros(Cout), sc, 1)
+        full += sc
+    assert rel(out.float().cpu(), full) < 6e-3
+
+
+def test_conv_tc_fused_input_groupnorm_needs_tile_kernel():
+    x = torch.randn(2, 4, 4, 64, device=DEV).to(torch.bfloat16)
+    w = torch.zeros(64, 9 * 64, device=DEV, dtype=torch.bfloat16)
+    plan = ops.ConvTcPlan(x, w, 64, 3)
+    assert not plan.tile
+    with pytest.raises(ops.DitsepError):
+        plan.run(torch.zeros(64, device=DEV), torch.empty(2, 4, 4, 64, device=DEV),
+                 in_ss=torch.zeros(2, 2, 64, device=DEV))
+
+
 def test_conv_tc_fused_shortcut_refuses_what_it_cannot_fuse():
     x = torch.randn(1, 16, 16, 256, device=DEV).to(torch.bfloat16)
     w = torch.zeros(128, 9 * 256 + 256, device=DEV, dtype=torch.bfloat16)
