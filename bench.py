@@ -217,6 +217,21 @@ def run_ours(args):
                 "conv_share_of_score_step": conv_ms / total_ms if total_ms else None,
                 "score_step_ms_event_sum": total_ms,
                 "whole_path_frac": value / world * NFE * GFLOP_PER_SCORE_STEP * 1e9 / (tf_sust * 1e12)}
+    # the single dominant kernel of the step: the 3x3 64->64 convolution at 256x256 (with or without the fused shortcut
+    # tap).  traffic: dram__bytes_read.sum + dram__bytes_write.sum of one such launch from the committed ncu --set full
+    # capture (profiles/r1o_ncu_full_conv_tc_256x256_B32.txt: 303 MB read + 230 MB written at batch 32, against
+    # 2 * B * H * W * 64 * 2 B = 537 MB algorithmic), scaled to this run's batch.
+    dom = [(ms, fl) for name, ms, fl in prof if name.startswith("conv_tc:256x256:") and name.endswith("->64")
+           and name.split(":")[2].split("->")[0] in ("576", "640")]
+    if dom:
+        roofline["dominant_kernel"] = {
+            "name": "conv_tc_tile_kernel<3,resident,bf16> 256x256 64->64 3x3 (+identity shortcut tap)",
+            "launches_per_score_step": len(dom), "avg_us": 1e3 * sum(m for m, _ in dom) / len(dom),
+            "achieved_tflops": sum(f for _, f in dom) / sum(m for m, _ in dom) / 1e9,
+            "frac_of_sustained_peak": sum(f for _, f in dom) / sum(m for m, _ in dom) / 1e9 / tf_sust,
+            "ss_mode_floor_note": "tcgen05.mma SS mode costs 43 + N/2 cycles per 128xNx16 MMA (profiles/r1j_umma_probe.txt): "
+                                  "N = Cout = 64 caps this layer at 42.6 % of the 2.29 PFLOP/s nominal rate = 976 TFLOP/s"}
+        roofline["traffic"] = 533.1e6 * B / 32.0
     by_kind = {}
     for name, ms, fl in prof:
         k = name.split(":")[0]

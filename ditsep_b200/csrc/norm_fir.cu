@@ -328,140 +328,10 @@ __global__ void __launch_bounds__(256, 2) fir_down_kernel(const T* __restrict__ 
   }
 }
 
-// Down-sampling, pair version (r1o): the strip kernel above evaluates GroupNorm + SiLU twice per input element (the
-// 4-tap windows of neighbouring output columns overlap by two pixels) and was instruction-bound: 192 M warp
-// instructions, 20 % of HBM peak at 256x256x64 (r1g/r1n).  Here a thread owns the input pixel PAIR (2m, 2m+1) of one
-// 8-channel pack: it loads and activates each element exactly once, publishes the pair through shared memory and
-// reads pixel 2m-1 from its left neighbour and 2m+2 from its right one:
-//   r[m] = (3 (a + b) + b[m-1] + a[m+1]) / 8.
-// CTA = M = 256 / cv pairs x cv packs, one input row per __syncthreads (two buffers); the two edge columns of the
-// block fetch their outer neighbour themselves.  Shared layout: 8 planes of float4 ([a_x | b_x | a_h | b_h] x lo/hi),
-// each [M + 2 slots][cv] so that consecutive threads touch consecutive 16-byte words.
-template <typename T, bool kDual>
-__global__ void __launch_bounds__(256, 2) fir_down_pair_kernel(const T* __restrict__ x, int H, int W, int C, int ld_x,
-                                                               const float* __restrict__ scale_shift,
-                                                               T* __restrict__ out_x, int ld_ox, T* __restrict__ out_h,
-                                                               int ld_oh, int seg_rows) {
-  extern __shared__ float4 fir_sm[];
-  const int cv = C / 8, M = 256 / cv, Ho = H / 2, Wo = W / 2;
-  const int v = threadIdx.x % cv, ml = threadIdx.x / cv;
-  const int m = blockIdx.x * M + ml;
-  const int b = blockIdx.z;
-  const int oy0 = blockIdx.y * seg_rows, oy1 = min(oy0 + seg_rows, Ho);
-  const bool active = m < Wo;
-  const int plane = (M + 2) * cv;           // float4 words per plane
-  const int buf_words = 8 * plane;
-  // scale / shift live in shared memory (behind the two exchange buffers) and are re-read per row: keeping them in
-  // registers across the row loop pushed the dual variant over 128 registers (320 bytes of spills)
-  float* ss_sm = reinterpret_cast<float*>(fir_sm + 2 * buf_words);
-  if (kDual) {
-    for (int c = threadIdx.x; c < 2 * C; c += blockDim.x) ss_sm[c] = scale_shift[(int64_t)b * 2 * C + c];
-    __syncthreads();
-  }
-  const T* xb = x + (int64_t)b * H * W * ld_x + v * 8;
-  const bool edge_l = ml == 0, edge_r = (ml == M - 1) || (m == Wo - 1);
-
-  // horizontally filtered row iy at output column m, through buffer `buf`; all threads of the CTA call it together
-  auto hrow = [&](int iy, int buf, float (&rx)[8], float (&rh)[8]) {
-#pragma unroll
-    for (int i = 0; i < 8; ++i) rx[i] = rh[i] = 0.f;
-    if (iy < 0 || iy >= H) return;  // uniform over the CTA: zero row, no barrier
-    float4* sm = fir_sm + buf * buf_words;
-    float ax[8], ah[8], bx[8], bh[8];
-    const T* row = xb + (int64_t)iy * W * ld_x;
-    if (active) {
-      float sc[8], sh[8];
-      if (kDual) {
-        Pack8<float>::load(ss_sm + v * 8, sc);
-        Pack8<float>::load(ss_sm + C + v * 8, sh);
-      }
-      fir_load_px<T, kDual>(row + (int64_t)(2 * m) * ld_x, true, sc, sh, ax, ah);
-      fir_load_px<T, kDual>(row + (int64_t)(2 * m + 1) * ld_x, true, sc, sh, bx, bh);
-      const int w = (ml + 1) * cv + v;
-      sm[0 * plane + w] = make_float4(ax[0], ax[1], ax[2], ax[3]);
-      sm[1 * plane + w] = make_float4(ax[4], ax[5], ax[6], ax[7]);
-      sm[2 * plane + w] = make_float4(bx[0], bx[1], bx[2], bx[3]);
-      sm[3 * plane + w] = make_float4(bx[4], bx[5], bx[6], bx[7]);
-      if (kDual) {
-        sm[4 * plane + w] = make_float4(ah[0], ah[1], ah[2], ah[3]);
-        sm[5 * plane + w] = make_float4(ah[4], ah[5], ah[6], ah[7]);
-        sm[6 * plane + w] = make_float4(bh[0], bh[1], bh[2], bh[3]);
-        sm[7 * plane + w] = make_float4(bh[4], bh[5], bh[6], bh[7]);
-      }
-      if (edge_l) {  // pixel 2m-1 -> the "b" of slot 0
-        float fx[8], fh[8];
-        fir_load_px<T, kDual>(row + (int64_t)(2 * m - 1) * ld_x, 2 * m - 1 >= 0, sc, sh, fx, fh);
-        sm[2 * plane + v] = make_float4(fx[0], fx[1], fx[2], fx[3]);
-        sm[3 * plane + v] = make_float4(fx[4], fx[5], fx[6], fx[7]);
-        if (kDual) {
-          sm[6 * plane + v] = make_float4(fh[0], fh[1], fh[2], fh[3]);
-          sm[7 * plane + v] = make_float4(fh[4], fh[5], fh[6], fh[7]);
-        }
-      }
-      if (edge_r) {  // pixel 2m+2 -> the "a" of the slot after this one
-        float fx[8], fh[8];
-        fir_load_px<T, kDual>(row + (int64_t)(2 * m + 2) * ld_x, 2 * m + 2 < W, sc, sh, fx, fh);
-        const int w2 = (ml + 2) * cv + v;
-        sm[0 * plane + w2] = make_float4(fx[0], fx[1], fx[2], fx[3]);
-        sm[1 * plane + w2] = make_float4(fx[4], fx[5], fx[6], fx[7]);
-        if (kDual) {
-          sm[4 * plane + w2] = make_float4(fh[0], fh[1], fh[2], fh[3]);
-          sm[5 * plane + w2] = make_float4(fh[4], fh[5], fh[6], fh[7]);
-        }
-      }
-    }
-    __syncthreads();
-    if (active) {
-      const int wl = ml * cv + v, wr = (ml + 2) * cv + v;
-      const float4 l0 = sm[2 * plane + wl], l1 = sm[3 * plane + wl], r0 = sm[0 * plane + wr], r1 = sm[1 * plane + wr];
-      const float lx[8] = {l0.x, l0.y, l0.z, l0.w, l1.x, l1.y, l1.z, l1.w};
-      const float rxn[8] = {r0.x, r0.y, r0.z, r0.w, r1.x, r1.y, r1.z, r1.w};
-#pragma unroll
-      for (int i = 0; i < 8; ++i) rx[i] = fmaf(0.375f, ax[i] + bx[i], 0.125f * (lx[i] + rxn[i]));
-      if (kDual) {
-        const float4 hl0 = sm[6 * plane + wl], hl1 = sm[7 * plane + wl], hr0 = sm[4 * plane + wr], hr1 = sm[5 * plane + wr];
-        const float lh[8] = {hl0.x, hl0.y, hl0.z, hl0.w, hl1.x, hl1.y, hl1.z, hl1.w};
-        const float rhn[8] = {hr0.x, hr0.y, hr0.z, hr0.w, hr1.x, hr1.y, hr1.z, hr1.w};
-#pragma unroll
-        for (int i = 0; i < 8; ++i) rh[i] = fmaf(0.375f, ah[i] + bh[i], 0.125f * (lh[i] + rhn[i]));
-      }
-    }
-  };
-
-  // output row oy = 1/8 r(2oy-1) + 3/8 r(2oy) + 3/8 r(2oy+1) + 1/8 r(2oy+2); carry = the first two terms
-  float cx[8], chh[8];
-  {
-    float ax[8], ah[8], bx[8], bh[8];
-    hrow(2 * oy0 - 1, 0, ax, ah);
-    hrow(2 * oy0, 1, bx, bh);
-#pragma unroll
-    for (int i = 0; i < 8; ++i) {
-      cx[i] = fmaf(0.375f, bx[i], 0.125f * ax[i]);
-      chh[i] = fmaf(0.375f, bh[i], 0.125f * ah[i]);
-    }
-  }
-  for (int oy = oy0; oy < oy1; ++oy) {
-    float ax[8], ah[8], bx[8], bh[8];
-    hrow(2 * oy + 1, 0, ax, ah);
-    hrow(2 * oy + 2, 1, bx, bh);
-    float ox_[8], oh_[8];
-#pragma unroll
-    for (int i = 0; i < 8; ++i) {
-      ox_[i] = fmaf(0.125f, bx[i], fmaf(0.375f, ax[i], cx[i]));
-      cx[i] = fmaf(0.375f, bx[i], 0.125f * ax[i]);
-      if (kDual) {
-        oh_[i] = fmaf(0.125f, bh[i], fmaf(0.375f, ah[i], chh[i]));
-        chh[i] = fmaf(0.375f, bh[i], 0.125f * ah[i]);
-      }
-    }
-    if (active) {
-      const int64_t opix = ((int64_t)b * Ho + oy) * Wo + m;
-      if (out_x) Pack8<T>::store(out_x + opix * ld_ox + v * 8, ox_);
-      if (kDual) Pack8<T>::store(out_h + opix * ld_oh + v * 8, oh_);
-    }
-  }
-}
-
+// (r1o, measured and removed: a "pair" version in which a thread owns input pixels (2m, 2m+1), activates each element
+// once and exchanges the two neighbour pixels through shared memory -- half the SiLU evaluations of the strip kernel
+// above -- was correct but SLOWER, 340 vs 304 us at 256x256x64: one __syncthreads per input row serialises the load
+// latency.  The strip kernel's limit is therefore not its redundant arithmetic; see DESIGN.md.)
 template <typename T, bool kDual>
 __global__ void __launch_bounds__(256) fir_up_kernel(const T* __restrict__ x, int H, int W, int C, int ld_x,
                                                      const float* __restrict__ scale_shift, T* __restrict__ out_x,
@@ -856,25 +726,6 @@ static int fir_dispatch(const T* x, int B, int H, int W, int C, int ld_x, int up
     else
       fir_up_kernel<T, false><<<grid, 256, 0, st>>>(x, H, W, C, ld_x, ss, out_x, ld_ox, out_h, ld_oh, seg_rows, n_seg, total);
     return check_launch("fir_up_kernel");
-  }
-  if (256 % cv == 0 && W / 2 >= 256 / cv && !getenv("DITSEP_FIR_STRIP")) {
-    // pair kernel: every input element loaded and activated once; neighbours exchanged through shared memory
-    const int M = 256 / cv, nblk = ceil_div(W / 2, M);
-    int sr = rows;
-    while (sr > 4 && (int64_t)B * nblk * ceil_div(rows, sr) < (int64_t)kNumSMs * 8) sr = (sr + 1) / 2;
-    const dim3 g2((unsigned)nblk, (unsigned)ceil_div(rows, sr), (unsigned)B);
-    const size_t smem = (size_t)2 * 8 * (M + 2) * cv * sizeof(float4) + (size_t)2 * C * sizeof(float);
-    static bool attr_done = false;
-    if (!attr_done) {
-      DITSEP_CUDA(cudaFuncSetAttribute(fir_down_pair_kernel<T, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 100 * 1024));
-      DITSEP_CUDA(cudaFuncSetAttribute(fir_down_pair_kernel<T, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 100 * 1024));
-      attr_done = true;
-    }
-    if (ss)
-      fir_down_pair_kernel<T, true><<<g2, 256, smem, st>>>(x, H, W, C, ld_x, ss, out_x, ld_ox, out_h, ld_oh, sr);
-    else
-      fir_down_pair_kernel<T, false><<<g2, 256, smem, st>>>(x, H, W, C, ld_x, ss, out_x, ld_ox, out_h, ld_oh, sr);
-    return check_launch("fir_down_pair_kernel");
   }
   if (ss)
     fir_down_kernel<T, true><<<grid, 256, 0, st>>>(x, H, W, C, ld_x, ss, out_x, ld_ox, out_h, ld_oh, seg_rows, n_seg, total);
