@@ -146,6 +146,57 @@ __global__ void __launch_bounds__(256) conv_direct_kernel(const TI* __restrict__
   }
 }
 
+// Narrow 1x1 convolution (Combine: Conv_0 of the 2(n+1)-channel input pyramid, layerspp.py:57-62, fused with its sum):
+// out[p][co] = out_scale * (sum_ci w[co][ci] x[p][ci] + bias[co] + residual[p][co]).  Pure HBM streaming: a thread owns
+// 8 output channels of one pixel (one 16-byte residual load and store); the CIN <= 8 input values of a pixel are read
+// by the Cout/8 threads that share it (L1 broadcast) and the filter sits in shared memory.  The GEMM-tiled kernel above
+// spent 146 us on the 128x128 level at batch 32 (r1n) where the bytes allow ~25 us.
+template <typename TO, int CIN>
+__global__ void __launch_bounds__(256) conv1x1_narrow_kernel(const float* __restrict__ in, int64_t npix, int ld_in,
+                                                             const float* __restrict__ w, const float* __restrict__ bias,
+                                                             const TO* __restrict__ residual, int ld_res, float out_scale,
+                                                             int Cout, TO* __restrict__ out, int ld_out) {
+  extern __shared__ float wsm[];  // [Cout][CIN] then bias[Cout]
+  for (int i = threadIdx.x; i < Cout * CIN; i += blockDim.x) wsm[i] = w[i];
+  for (int i = threadIdx.x; i < Cout; i += blockDim.x) wsm[Cout * CIN + i] = bias ? bias[i] : 0.f;
+  __syncthreads();
+  const int cv = Cout / 8;
+  const int64_t total = npix * cv;
+  // the grid stride is a multiple of cv (host: Cout / 8 divides 256), so a thread keeps ONE channel pack for its whole
+  // life: its 8 x CIN filter values and 8 biases live in registers, the loop body is CIN loads + 8 CIN FMAs
+  const int v = (int)(((int64_t)blockIdx.x * blockDim.x + threadIdx.x) % cv);
+  float wreg[8][CIN], breg[8];
+#pragma unroll
+  for (int j = 0; j < 8; ++j) {
+    breg[j] = wsm[Cout * CIN + v * 8 + j];
+#pragma unroll
+    for (int c = 0; c < CIN; ++c) wreg[j][c] = wsm[(v * 8 + j) * CIN + c];
+  }
+  for (int64_t idx = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; idx < total; idx += (int64_t)gridDim.x * blockDim.x) {
+    const int64_t pix = idx / cv;
+    float xin[CIN];
+#pragma unroll
+    for (int c = 0; c < CIN; ++c) xin[c] = __ldg(in + pix * ld_in + c);
+    float f[8];
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+      float a = breg[j];
+#pragma unroll
+      for (int c = 0; c < CIN; ++c) a = fmaf(wreg[j][c], xin[c], a);
+      f[j] = a;
+    }
+    if (residual) {
+      float r[8];
+      Pack8<TO>::load(residual + pix * ld_res + v * 8, r);
+#pragma unroll
+      for (int j = 0; j < 8; ++j) f[j] += r[j];
+    }
+#pragma unroll
+    for (int j = 0; j < 8; ++j) f[j] *= out_scale;
+    Pack8<TO>::store(out + pix * ld_out + v * 8, f);
+  }
+}
+
 }  // namespace ditsep
 
 using namespace ditsep;
@@ -161,6 +212,25 @@ extern "C" int ditsep_conv_direct(const void* in, int dtype, int B, int H, int W
   const int64_t M = (int64_t)B * H * W;
   dim3 grid(ceil_div(M, BM), ceil_div(Cout, BN));
   cudaStream_t st = (cudaStream_t)stream;
+  if (ksize == 1 && dtype == DITSEP_F32 && (Cin == 6 || Cin == 8 || Cin == 4) && !bias_b && Cout % 8 == 0 &&
+      ld_out % 8 == 0 && 256 % (Cout / 8) == 0 && (!residual || ld_res % 8 == 0) && (reinterpret_cast<uintptr_t>(out) & 15) == 0 &&
+      (!residual || (reinterpret_cast<uintptr_t>(residual) & 15) == 0) && Cout <= 512) {
+    const int64_t total = M * (Cout / 8);
+    const unsigned g1 = (unsigned)((total + 255) / 256 < 148 * 16 ? (total + 255) / 256 : 148 * 16);
+    const size_t smem = (size_t)(Cout * Cin + Cout) * sizeof(float);
+#define LAUNCH1(TO, CIN)                                                                                              \
+  conv1x1_narrow_kernel<TO, CIN><<<g1, 256, smem, st>>>((const float*)in, M, ld_in, w, bias, (const TO*)residual, ld_res, \
+                                                        out_scale, Cout, (TO*)out, ld_out)
+    if (out_dtype == DITSEP_BF16) {
+      if (Cin == 6) LAUNCH1(bf16, 6); else if (Cin == 8) LAUNCH1(bf16, 8); else LAUNCH1(bf16, 4);
+    } else if (out_dtype == DITSEP_F32) {
+      if (Cin == 6) LAUNCH1(float, 6); else if (Cin == 8) LAUNCH1(float, 8); else LAUNCH1(float, 4);
+    } else {
+      DITSEP_REQUIRE(false, "conv_direct: unknown out dtype %d", out_dtype);
+    }
+#undef LAUNCH1
+    return check_launch("conv1x1_narrow_kernel");
+  }
   // residual shares the OUTPUT dtype (it is an activation tensor of the same network)
 #define LAUNCH(TI, TO)                                                                                              \
   conv_direct_kernel<TI, TO, TO><<<grid, 256, 0, st>>>((const TI*)in, B, H, W, Cin, ld_in, w, bias, bias_b, ld_bias_b, \

@@ -9,6 +9,11 @@
 // 316-317), output scaling + output_layer (ncsnpp.py:473-477).
 #include "common.cuh"
 
+// fir_down is latency-bound at 4 warps per scheduler (r1p ncu: long-scoreboard stall 4.8 per issue, 22 % occupancy at
+// 128 registers): 4 CTAs per SM with ~430 bytes of spills measured 251 us against 303 (2 CTAs, no spills) at 256x256x64.
+#ifndef DITSEP_FIR_MINB
+#define DITSEP_FIR_MINB 4
+#endif
 namespace ditsep {
 
 // ------------------------------------------------------------------- GroupNorm statistics
@@ -274,7 +279,7 @@ __device__ __forceinline__ void fir_down_hrow(const T* __restrict__ xb, int iy, 
 // advances TWO input rows per trip so the vertical taps are compile-time constants and the accumulator hand-over
 // (row oy+1 becomes row oy) is a register rename instead of a select + copy.
 template <typename T, bool kDual>
-__global__ void __launch_bounds__(256, 2) fir_down_kernel(const T* __restrict__ x, int H, int W, int C, int ld_x,
+__global__ void __launch_bounds__(256, DITSEP_FIR_MINB) fir_down_kernel(const T* __restrict__ x, int H, int W, int C, int ld_x,
                                                           const float* __restrict__ scale_shift, T* __restrict__ out_x,
                                                           int ld_ox, T* __restrict__ out_h, int ld_oh, int seg_rows,
                                                           int n_seg, int64_t total) {

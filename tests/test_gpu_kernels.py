@@ -210,6 +210,25 @@ def test_conv_direct(B, H, W, Cin, Cout, k):
     assert rel(out2, ref) < 1e-5
 
 
+@pytest.mark.parametrize("B,H,W,Cin,Cout,ld_extra", [(2, 16, 24, 6, 64, 0), (3, 5, 7, 6, 128, 64), (1, 8, 8, 8, 64, 0)])
+def test_conv1x1_narrow_combine_pattern(B, H, W, Cin, Cout, ld_extra):
+    """Combine "sum" (layerspp.py:57-62): dst = Conv1x1(fp32 input pyramid, 6 channels) + dst, bf16 dst inside a wider
+    concat buffer -- the streaming fast path of ditsep_conv_direct."""
+    x = torch.randn(B, H, W, Cin, generator=g(60))
+    w = torch.randn(Cout, 1, Cin, generator=g(61)) / math.sqrt(Cin)
+    bias = 0.1 * torch.randn(Cout, generator=g(62))
+    buf = torch.randn(B, H, W, Cout + ld_extra, generator=g(63)).to(torch.bfloat16)
+    dst = buf.to(DEV)[..., ld_extra:]
+    ref = torch.empty(B, H, W, Cout)
+    E.conv_direct(x, w, bias, ref, 1, residual=buf[..., ld_extra:].float())
+    ops.conv_direct(x.to(DEV), w.to(DEV), bias.to(DEV), dst, 1, residual=dst)
+    assert rel(dst.float(), ref) < 4e-3          # bf16 rounding of the stored sum
+    f32 = torch.empty(B, H, W, Cout, device=DEV)
+    ops.conv_direct(x.to(DEV), w.to(DEV), bias.to(DEV), f32, 1, out_scale=0.5)
+    E.conv_direct(x, w, bias, ref, 1, out_scale=0.5)
+    assert rel(f32, ref) < 1e-6
+
+
 TC_CASES = [
     # B, H, W, Cin, ld_extra, Cout, k
     (2, 16, 16, 64, 0, 64, 3),
