@@ -129,3 +129,66 @@ def test_full_size_batch_properties():
     # every reduction order (GroupNorm partials, conv K order, epilogue statistics) is a function of the image
     # shape only, so a mixture's result does not depend on what else is in the batch -- bit for bit
     assert torch.equal(full[5:6], one)
+
+
+# ------------------------------------------------------------------ widened configs (a7, a15, C3, C5)
+@pytest.mark.parametrize("n_src,shape", [(2, (2, 1, 16000)), (3, (2, 1, 9000)), (2, (2, 1, 64, 12))])
+def test_ouve_ald_sampler_vs_oracle(n_src, shape):
+    """OUVESDE + 'ald' corrector + reverse-diffusion predictor (sdes.py:595-698, correctors.py:70-84) through the
+    sampler entry point with a closed-form score: the fused update kernels against the oracle on the same noise tape,
+    for 2 and 3 speakers (Libri3mix-shaped, C5) and for a 4-D latent state (C4)."""
+    g = torch.Generator().manual_seed(21)
+    y = torch.randn(*shape, generator=g)
+    sde_args = dict(theta=1.5, sigma_min=0.05, sigma_max=0.5)
+    N = 6
+
+    def score(x, t, yy):
+        return -(x - 0.7 * yy) * (1.0 + t[(...,) + (None,) * (x.ndim - 1)])
+
+    sampler = sdes.get_pc_sampler("reverse_diffusion", "ald", sde=sdes.OUVESDE(N=N, **sde_args), score_fn=score,
+                                  y=y.to(DEV), snr=0.5, corrector_steps=1, n_spkrs=n_src, noise_tape=S.NoiseTape(91))
+    x, nfe = sampler()
+    x_ref, nfe_ref = S.pc_sampler_ref(score, S.OUVESDERef(N=N, **sde_args), y, S.NoiseTape(91), corrector="ald",
+                                      eps=0.03, snr=0.5, n_spkrs=n_src)
+    assert nfe == nfe_ref == 2 * N and tuple(x.shape) == (shape[0], n_src, *shape[2:])
+    assert float((x.cpu() - x_ref).abs().max()) < 2e-5 * float(x_ref.abs().max())
+
+
+@pytest.mark.parametrize("precision,tol", [("fp32", 1e-3), ("bf16", 4e-2)])
+def test_latent_wrapper_vs_reference_golden(golden, precision, tol):
+    """LatentScoreModelNCSNpp (score_models.py:141-186; config C4: centered NCSN++ over (B, 3, 64, L) latents, L padded
+    to a multiple of max_latent_length) on the GPU against the reference's committed output.  The golden model is the
+    small nf=32 one with full-scale random weights (worst case for bf16: documented 4e-2 bound as above)."""
+    from ditsep_b200.models.diffsep.score_models import LatentScoreModelNCSNpp
+    bcfg = R.NCSNppConfig(nf=32, ch_mult=(1, 2, 2), num_res_blocks=2, attn_resolutions=(16,), image_size=64,
+                          num_channels_in=3, num_channels_out=2, centered=True)
+    sdl = R.make_state_dict(bcfg, seed=3, with_window=None)
+    lat = LatentScoreModelNCSNpp(2, dict(_target_="models.diffsep.ncsnpp.NCSNpp", nf=32, ch_mult=[1, 2, 2],
+                                         num_res_blocks=2, attn_resolutions=[16], resamp_with_conv=True, image_size=64,
+                                         centered=True, precision=precision), max_latent_length=4).eval()
+    lat.load_state_dict(sdl, strict=True)
+    lat = lat.to(DEV)
+    g = torch.Generator().manual_seed(11)
+    xt = torch.randn(2, 2, 64, 14, generator=g)
+    mx = torch.randn(2, 1, 64, 14, generator=g)
+    t = torch.tensor([0.4, 0.9])
+    with torch.no_grad():
+        out = lat(xt.to(DEV), t.to(DEV), mx.to(DEV))
+    e = rel_l2(out, torch.tensor(golden["ref"]["latent_out"]))
+    print(f"latent wrapper {precision}: rel-L2 vs reference = {e:.3e}")
+    assert e < tol
+
+
+def test_variable_length_16k_shape_vs_oracle():
+    """C3-shaped input: a 16 kHz utterance whose frame count pads to W = 384 (not a power of two), fp32 and bf16 against
+    the oracle on the same inputs (no committed reference output at this size: the oracle is pinned at 7810 / 32000)."""
+    T = 47000  # 1 + (47000 + 382) // 128 = 371 frames -> 384
+    for precision, tol, init_scale in (("fp32", 1e-3, 1.0), ("bf16", 1e-2, 0.01)):
+        model, sd, cfg = build_model(precision, DEV, init_scale=init_scale)
+        xt, t, mixn = score_inputs(1, T)
+        with torch.no_grad():
+            out = model(xt.to(DEV), t.to(DEV), mixn.to(DEV))
+            ref = R.score_forward_ref(sd, cfg, xt, t, mixn)
+        e = rel_l2(out, ref)
+        print(f"C3-shaped score step {precision}: rel-L2 vs oracle = {e:.3e}")
+        assert tuple(out.shape) == (1, 2, T) and e < tol
