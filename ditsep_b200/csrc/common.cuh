@@ -109,6 +109,17 @@ __device__ __forceinline__ float silu_f(float x) {
   return x * r;
 }
 
+// SiLU with ONE MUFU: x * sigmoid(x) = h + h * tanh(h), h = x / 2 (FMUL, MUFU.TANH, FFMA).  tanh.approx.f32 is good to
+// ~2^-11 relative, i.e. an absolute error of |h| * 5e-4 on the result: below bf16 rounding for positive outputs, up to a
+// few bf16 ulps on the small negative tail.  Used only where the result is rounded to bf16 anyway AND the MUFU pipe is
+// the bottleneck (the conv kernel's in-shared-memory GroupNorm transform).
+__device__ __forceinline__ float silu_tanh_f(float x) {
+  const float h = 0.5f * x;
+  float t;
+  asm("tanh.approx.f32 %0, %1;" : "=f"(t) : "f"(h));
+  return fmaf(h, t, h);
+}
+
 __device__ __forceinline__ float warp_sum(float v) {
 #pragma unroll
   for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);

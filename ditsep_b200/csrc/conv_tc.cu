@@ -579,7 +579,6 @@ __global__ void __launch_bounds__(tile_threads(kXf), 1) conv_tc_tile_kernel(cons
       const int lc = t & 7;
       const bool xfirst = kRes && p.xchunks > 0 && p.a_stages >= p.xchunks + 2;
       const int nsteps = p.chunks + (kRes ? p.xchunks : 0);
-      uint8_t* const ring_ptr = smem_raw + (a_ring - smem_u32(smem_raw));
       int sa = 0;
       uint32_t pa = 0;
       const bool silu = p.in_silu != 0;
@@ -595,20 +594,47 @@ __global__ void __launch_bounds__(tile_threads(kXf), 1) conv_tc_tile_kernel(cons
             const float* ssp = p.in_ss + ((int64_t)tw.b * 2) * p.Cin + ch * kBlockK + lc * 8;
             Pack8<float>::load(ssp, sc);
             Pack8<float>::load(ssp + p.Cin, sh);
-            uint8_t* const stage = ring_ptr + (size_t)sa * p.a_stage_bytes;
-#pragma unroll 3
-            for (int r = t >> 3; r < p.a_rows; r += kXformWarps * 4) {
-              const int hy = r / kRowPitch, hx = r - hy * kRowPitch;
-              const bool inside = (unsigned)(y0 + hy) < (unsigned)p.H && (unsigned)(x0 + hx) < (unsigned)p.W;
-              bf16* ptr = reinterpret_cast<bf16*>(stage + r * 128 + ((lc ^ (r & 7)) << 4));  // 128-byte swizzle
-              float f[8];
-              Pack8<bf16>::load(ptr, f);
+            // Four rows per trip, ALL loads before any store: with one load-compute-store per trip the compiler must
+            // keep every load behind the previous trip's store (same shared array), which serialised ~400-cycle
+            // dependent chains -- 4400 cycles per chunk against 2850 of MMA work (r1m / r1t).
+            const uint32_t stage_u32 = a_ring + (uint32_t)(sa * p.a_stage_bytes);
+            constexpr int kStep = kXformWarps * 4, kBatch = 4;
+            for (int r0 = t >> 3; r0 < p.a_rows; r0 += kStep * kBatch) {
+              uint4 raw[kBatch];
+              uint32_t addr[kBatch];
+              bool ok[kBatch];
 #pragma unroll
-              for (int i = 0; i < 8; ++i) {
-                const float v = fmaf(f[i], sc[i], sh[i]);
-                f[i] = silu ? silu_f(v) : v;
+              for (int u = 0; u < kBatch; ++u) {
+                const int r = r0 + u * kStep;
+                const int hy = r / kRowPitch, hx = r - hy * kRowPitch;
+                ok[u] = r < p.a_rows && (unsigned)(y0 + hy) < (unsigned)p.H && (unsigned)(x0 + hx) < (unsigned)p.W;
+                addr[u] = stage_u32 + (uint32_t)(r * 128 + ((lc ^ (r & 7)) << 4));  // 128-byte swizzle
+                raw[u] = make_uint4(0, 0, 0, 0);
+                if (ok[u])
+                  asm volatile("ld.shared.v4.u32 {%0, %1, %2, %3}, [%4];"
+                               : "=r"(raw[u].x), "=r"(raw[u].y), "=r"(raw[u].z), "=r"(raw[u].w)
+                               : "r"(addr[u]));
               }
-              if (inside) Pack8<bf16>::store(ptr, f);
+#pragma unroll
+              for (int u = 0; u < kBatch; ++u) {
+                const uint32_t wv[4] = {raw[u].x, raw[u].y, raw[u].z, raw[u].w};
+                uint32_t o[4];
+#pragma unroll
+                for (int j = 0; j < 4; ++j) {
+                  float lo = fmaf(__uint_as_float(wv[j] << 16), sc[2 * j], sh[2 * j]);
+                  float hi = fmaf(__uint_as_float(wv[j] & 0xffff0000u), sc[2 * j + 1], sh[2 * j + 1]);
+                  if (silu) {
+                    lo = p.in_silu == 2 ? silu_tanh_f(lo) : silu_f(lo);
+                    hi = p.in_silu == 2 ? silu_tanh_f(hi) : silu_f(hi);
+                  }
+                  const __nv_bfloat162 hh = __floats2bfloat162_rn(lo, hi);
+                  o[j] = *reinterpret_cast<const uint32_t*>(&hh);
+                }
+                if (ok[u])
+                  asm volatile("st.shared.v4.u32 [%0], {%1, %2, %3, %4};" ::"r"(addr[u]), "r"(o[0]), "r"(o[1]), "r"(o[2]),
+                               "r"(o[3])
+                               : "memory");
+              }
             }
             asm volatile("fence.proxy.async.shared::cta;" ::: "memory");  // generic writes -> visible to the tensor core
           }

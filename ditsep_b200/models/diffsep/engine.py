@@ -443,13 +443,16 @@ class _Plan:
                 return False
         if in_ss is not None:
             # conv(act(GroupNorm(x))) (layerspp.py:297-298,318-320): the tile kernel CAN normalise the landed tiles in
-            # shared memory (ops.ConvTcPlan.run in_ss, bit-identical to gn_apply + conv).  Measured at batch 32 (r1m) the
-            # fused variant is SLOWER: 13.2 vs 12.3 ms per score step -- four transform warps are MUFU-bound at ~4400
-            # cycles per tile against 2850 of MMA work -- so it is opt-in (DITSEP_FUSE_GN=1) until the transform is faster
+            # shared memory (ops.ConvTcPlan.run in_ss, bit-identical to gn_apply + conv).  Measured at batch 32 (r1m, r1u)
+            # the fused variant is SLOWER -- 12.9-13.6 vs 11.7 ms per score step: four transform warps (one per
+            # scheduler) are issue-latency bound at ~5000 cycles per 64-channel chunk against 2850 of MMA work -- so it
+            # is opt-in (DITSEP_FUSE_GN=1; DITSEP_FUSE_GN_TANH=1 selects the one-MUFU SiLU) until the transform runs on
+            # the 16 epilogue warps
             if use_tc and plan is None:
                 plan = ops.ConvTcPlan(x, cw.w_bf16, cw.cout, cw.ksize)
             if plan is not None and plan.tile and os.environ.get("DITSEP_FUSE_GN", "0") == "1":
-                kw["in_ss"], kw["in_silu"] = in_ss, in_silu
+                kw["in_ss"] = in_ss
+                kw["in_silu"] = (2 if os.environ.get("DITSEP_FUSE_GN_TANH", "0") == "1" else 1) if in_silu else 0
             else:
                 act = x if gn_inplace else self.pool.get(tuple(x.shape), x.dtype)
                 self.steps.append((ops.gn_apply, (x, in_ss, in_silu, act), {}))

@@ -296,7 +296,7 @@ class ConvTcPlan:
         if in_ss is not None and (in_ss.dtype != torch.float32 or not in_ss.is_contiguous()
                                   or in_ss.numel() != self.shape[0] * 2 * self.Cin):
             raise _lib.DitsepError("conv_tc: in_ss must be a contiguous f32 (B, 2, Cin) tensor")
-        check(_lib.load().ditsep_conv_tc_run_gn(self._h, _ptr(in_ss), int(bool(in_silu)), _ptr(bias), _ptr(bias_b),
+        check(_lib.load().ditsep_conv_tc_run_gn(self._h, _ptr(in_ss), int(in_silu), _ptr(bias), _ptr(bias_b),
                                              0 if bias_b is None else bias_b.stride(0), _ptr(residual),
                                              0 if residual is None else _dt(residual),
                                              0 if residual is None else nhwc_ld(residual), out_scale, _ptr(out),
