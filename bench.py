@@ -77,11 +77,11 @@ class ClockSampler(threading.Thread):
 
 
 # ----------------------------------------------------------------------------------- CPU baseline
-def cpu_baseline(n_score_steps: int = 8):
+def cpu_baseline(n_score_steps: int = 60):
     """The reference's PyTorch CPU sampler restated by the oracle (kind "port"), all host cores,
     bounded sample: 1 warm-up + n score-network evaluations of ONE C1 mixture inside the real
-    sampler loop (prior draw, corrector and predictor updates included), extrapolated to the 60
-    evaluations of a full run."""
+    sampler loop (prior draw, corrector and predictor updates included); the default n = 60 is one
+    COMPLETE N=30 sampler run of one mixture (~15 s on 16 cores), smaller n is extrapolated."""
     import torch
 
     from common import sampler_inputs
@@ -114,7 +114,7 @@ def run_reference(args):
     per = []
     base = None
     for i in range(args.warmup + args.steps):
-        base = cpu_baseline(n_score_steps=4)
+        base = cpu_baseline(n_score_steps=60)  # one complete mixture per step
         if i >= args.warmup:
             per.append(base["value"])
     v = sum(per) / len(per)
