@@ -351,7 +351,7 @@ __global__ void __launch_bounds__(tile_threads(kXf), 1) conv_tc_tile_kernel(cons
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const uint32_t base = (smem_u32(smem_raw) + 1023u) & ~1023u;
   const uint32_t w_tile_bytes = (uint32_t)p.BN * 128u;
-  const int n_wtiles = kRes ? p.chunks * kTaps + p.xchunks : p.w_stages;
+  const int n_wtiles = kRes ? p.chunks * kTaps + p.xchunks : p.w_stages * KS;  // streamed: one stage = one filter ROW
   const uint32_t a_ring = (base + (uint32_t)n_wtiles * w_tile_bytes + 1023u) & ~1023u;
   const int n0 = blockIdx.y * p.BN;
 
@@ -418,11 +418,13 @@ __global__ void __launch_bounds__(tile_threads(kXf), 1) conv_tc_tile_kernel(cons
                       tw.ty * kTileH - kHalo, tw.b);
           if (++sa == p.a_stages) { sa = 0; pa ^= 1u; }
           if (!kRes) {
-            for (int tap = 0; tap < kTaps; ++tap) {
+            for (int row = 0; row < KS; ++row) {  // a filter row (KS taps) per stage: one barrier round trip per 4*KS MMAs
               mbar_wait(smem_u32(&bar_w_empty[sw]), pw);
               const uint32_t wfull = smem_u32(&bar_w_full[sw]);
-              mbar_expect_tx(wfull, w_tile_bytes);
-              tma_load_2d(base + (uint32_t)sw * w_tile_bytes, &mapW, wfull, tap * p.Cin + ch * kBlockK, n0);
+              mbar_expect_tx(wfull, (uint32_t)KS * w_tile_bytes);
+              for (int col = 0; col < KS; ++col)
+                tma_load_2d(base + (uint32_t)(sw * KS + col) * w_tile_bytes, &mapW, wfull,
+                            (row * KS + col) * p.Cin + ch * kBlockK, n0);
               if (++sw == p.w_stages) { sw = 0; pw ^= 1u; }
             }
           }
@@ -542,21 +544,27 @@ __global__ void __launch_bounds__(tile_threads(kXf), 1) conv_tc_tile_kernel(cons
           tc_fence_after();
           const uint32_t a_lo = ((a_ring + (uint32_t)(sa * p.a_stage_bytes)) >> 4) | lbo;
           constexpr int kRow16 = 128 >> 4;
+          // Streamed filter: the per-tap version waited on a barrier every 4 MMAs (~150 cycles of probe + fence per
+          // ~300 cycles of tensor work: the streamed layers ran at 550 TFLOP/s against 800-1000 resident, r1l); a
+          // stage is now a whole filter row.
 #pragma unroll
-          for (int tap = 0; tap < kTaps; ++tap) {
+          for (int row = 0; row < KS; ++row) {
             mbar_wait(smem_u32(&bar_w_full[sw]), pw);
             tc_fence_after();
-            w_lo = ((base + (uint32_t)sw * w_tile_bytes) >> 4) | lbo;
-            const uint32_t a_tap = a_lo + (uint32_t)(((tap / KS) * kRowPitch + (tap % KS)) * kRow16);
+            w_lo = ((base + (uint32_t)(sw * KS) * w_tile_bytes) >> 4) | lbo;
+            const uint32_t a_row = a_lo + (uint32_t)(row * kRowPitch * kRow16);
             if (elect_one_sync()) {
 #pragma unroll
-              for (int k = 0; k < kBlockK / 16; ++k) {
-                const uint64_t da = ((uint64_t)a_hi << 32) | (uint64_t)(a_tap + 2 * k);
-                const uint64_t db = ((uint64_t)b_hi << 32) | (uint64_t)(w_lo + 2 * k);
-                umma_bf16(tmem_d, da, db, idesc, (tap | k) != 0 ? 1u : (uint32_t)(ch != 0));
+              for (int col = 0; col < KS; ++col) {
+#pragma unroll
+                for (int k = 0; k < kBlockK / 16; ++k) {
+                  const uint64_t da = ((uint64_t)a_hi << 32) | (uint64_t)(a_row + col * kRow16 + 2 * k);
+                  const uint64_t db = ((uint64_t)b_hi << 32) | (uint64_t)(w_lo + (uint32_t)col * w_step + 2 * k);
+                  umma_bf16(tmem_d, da, db, idesc, (row | col | k) != 0 ? 1u : (uint32_t)(ch != 0));
+                }
               }
               umma_commit(smem_u32(&bar_w_empty[sw]));
-              if (tap == kTaps - 1) {
+              if (row == KS - 1) {
                 umma_commit(smem_u32(&bar_a_empty[sa]));
                 if (ch == p.chunks - 1) umma_commit(smem_u32(&bar_acc_full[ab]));
               }
@@ -944,9 +952,9 @@ extern "C" int ditsep_conv_tc_plan_create_sc(ditsep_conv_plan** plan, const void
     } else {
       DITSEP_REQUIRE(!x_sc, "conv_tc: fused shortcut needs the filter resident in shared memory (%zu bytes do not fit)", w_all);
       p.w_resident = 0;
-      p.w_stages = kMaxWStages;
+      p.w_stages = ksize == 3 ? 3 : kMaxWStages;  // a stage holds one filter row (ksize taps)
       p.a_stages = kMaxAStages;
-      smem = 2048 + (size_t)p.w_stages * w_tile + (size_t)p.a_stages * p.a_stage_bytes;
+      smem = 2048 + (size_t)p.w_stages * ksize * w_tile + (size_t)p.a_stages * p.a_stage_bytes;
     }
     int dev = 0, sms = kNumSMs;
     if (cudaGetDevice(&dev) == cudaSuccess) cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
