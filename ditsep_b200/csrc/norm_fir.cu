@@ -7,6 +7,8 @@
 // 283-285,297,318), upsample_2d / downsample_2d (up_or_down_sampling.py:206-273 ->
 // upfirdn2d, op/upfirdn2d_kernel.cu:107-207), temb (ncsnpp.py:325-346, layerspp.py:44-46,
 // 316-317), output scaling + output_layer (ncsnpp.py:473-477).
+#include <type_traits>
+
 #include "common.cuh"
 
 // fir_down is latency-bound at 4 warps per scheduler (r1p ncu: long-scoreboard stall 4.8 per issue, 22 % occupancy at
@@ -486,6 +488,71 @@ __global__ void __launch_bounds__(256) fir_narrow_kernel(const T* __restrict__ x
   }
 }
 
+// Narrow fp32 tensors with an even channel count (the 6-channel pyramids): one thread per OUTPUT PIXEL, all channels
+// as float2 loads, so the index arithmetic (three 64-bit divisions per element in the scalar kernel above: 60-73 us
+// per launch at batch 32 for 12-50 MB of data, r1x) is paid once per pixel.
+template <int C>
+__global__ void __launch_bounds__(256) fir_narrow_px_kernel(const float* __restrict__ x, int H, int W, int ld_x, int up,
+                                                            float* __restrict__ out, int ld_o, int64_t npix_out) {
+  static_assert(C % 2 == 0, "float2 path");
+  const int Ho = up ? 2 * H : H / 2, Wo = up ? 2 * W : W / 2;
+  const float kd[4] = {0.125f, 0.375f, 0.375f, 0.125f};
+  for (int64_t idx = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; idx < npix_out;
+       idx += (int64_t)gridDim.x * blockDim.x) {
+    const int ox = (int)(idx % Wo);
+    int64_t r = idx / Wo;
+    const int oy = (int)(r % Ho);
+    const int b = (int)(r / Ho);
+    float acc[C];
+#pragma unroll
+    for (int c = 0; c < C; ++c) acc[c] = 0.f;
+    const float* xb = x + (int64_t)b * H * W * ld_x;
+    if (!up) {
+#pragma unroll
+      for (int a = 0; a < 4; ++a) {
+        const int iy = 2 * oy + a - 1;
+        if (iy < 0 || iy >= H) continue;
+#pragma unroll
+        for (int d = 0; d < 4; ++d) {
+          const int ix = 2 * ox + d - 1;
+          if (ix < 0 || ix >= W) continue;
+          const float wgt = kd[a] * kd[d];
+          const float2* px = reinterpret_cast<const float2*>(xb + ((int64_t)iy * W + ix) * ld_x);
+#pragma unroll
+          for (int c = 0; c < C / 2; ++c) {
+            const float2 v = __ldg(px + c);
+            acc[2 * c] = fmaf(wgt, v.x, acc[2 * c]);
+            acc[2 * c + 1] = fmaf(wgt, v.y, acc[2 * c + 1]);
+          }
+        }
+      }
+    } else {
+      const int iy = oy >> 1, ix = ox >> 1;
+      const int ys[2] = {iy, (oy & 1) ? iy + 1 : iy - 1}, xs[2] = {ix, (ox & 1) ? ix + 1 : ix - 1};
+      const float ws[2] = {0.75f, 0.25f};
+#pragma unroll
+      for (int a = 0; a < 2; ++a) {
+        if (ys[a] < 0 || ys[a] >= H) continue;
+#pragma unroll
+        for (int d = 0; d < 2; ++d) {
+          if (xs[d] < 0 || xs[d] >= W) continue;
+          const float wgt = ws[a] * ws[d];
+          const float2* px = reinterpret_cast<const float2*>(xb + ((int64_t)ys[a] * W + xs[d]) * ld_x);
+#pragma unroll
+          for (int c = 0; c < C / 2; ++c) {
+            const float2 v = __ldg(px + c);
+            acc[2 * c] = fmaf(wgt, v.x, acc[2 * c]);
+            acc[2 * c + 1] = fmaf(wgt, v.y, acc[2 * c + 1]);
+          }
+        }
+      }
+    }
+    float2* po = reinterpret_cast<float2*>(out + idx * ld_o);
+#pragma unroll
+    for (int c = 0; c < C / 2; ++c) po[c] = make_float2(acc[2 * c], acc[2 * c + 1]);
+  }
+}
+
 // ------------------------------------------------------------------- hi/lo split of a narrow fp32 tensor
 // The network's first layer has 2(n+1) = 6 input channels: too narrow for the tensor-core kernel (K blocks of 64)
 // and, on CUDA cores, 1.06 ms per score step at batch 32 (r1g ncu).  This kernel widens it to a 64-channel bf16
@@ -712,6 +779,16 @@ static int fir_dispatch(const T* x, int B, int H, int W, int C, int ld_x, int up
     DITSEP_REQUIRE(ss == nullptr && out_h == nullptr && out_x != nullptr,
                    "fir_resample: narrow tensors (C=%d) support the plain path only", C);
     const int64_t total = (int64_t)B * (up ? 4 : 1) * H * W / (up ? 1 : 4) * C;
+    if constexpr (std::is_same<T, float>::value) {
+      if ((C == 6 || C == 4 || C == 8) && ld_x % 2 == 0 && ld_ox % 2 == 0 && (reinterpret_cast<uintptr_t>(x) & 7) == 0 &&
+          (reinterpret_cast<uintptr_t>(out_x) & 7) == 0) {
+        const int64_t npix = total / C;
+        if (C == 6) fir_narrow_px_kernel<6><<<grid_for(npix), 256, 0, st>>>(x, H, W, ld_x, up, out_x, ld_ox, npix);
+        else if (C == 4) fir_narrow_px_kernel<4><<<grid_for(npix), 256, 0, st>>>(x, H, W, ld_x, up, out_x, ld_ox, npix);
+        else fir_narrow_px_kernel<8><<<grid_for(npix), 256, 0, st>>>(x, H, W, ld_x, up, out_x, ld_ox, npix);
+        return check_launch("fir_narrow_px_kernel");
+      }
+    }
     fir_narrow_kernel<T><<<grid_for(total), 256, 0, st>>>(x, H, W, C, ld_x, up, out_x, ld_ox, total);
     return check_launch("fir_narrow_kernel");
   }
