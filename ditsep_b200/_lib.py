@@ -51,6 +51,8 @@ SIGNATURES = {
     "ditsep_gn_partial_sums": (c_int, [c_void_p, c_int, c_int, c_int64, c_int, c_int, c_void_p, c_int, c_void_p]),
     "ditsep_gn_finalize": (c_int, [C.POINTER(StatsSrc), c_int, c_int, c_int64, c_int, c_void_p, c_void_p, c_float,
                                    c_void_p, c_void_p]),
+    "ditsep_gn_small": (c_int, [c_void_p, c_int, c_int, c_int64, c_int, c_int, c_int, c_void_p, c_void_p, c_float, c_int,
+                                c_void_p, c_int, c_void_p]),
     "ditsep_gn_apply": (c_int, [c_void_p, c_int, c_int, c_int64, c_int, c_int, c_void_p, c_int, c_void_p, c_int,
                                 c_void_p]),
     "ditsep_fir_resample": (c_int, [c_void_p, c_int, c_int, c_int, c_int, c_int, c_int, c_int, c_void_p, c_void_p,

@@ -228,6 +228,95 @@ __global__ void __launch_bounds__(256) gn_apply_kernel(const T* __restrict__ x, 
   }
 }
 
+// ------------------------------------------------------------------- small images: statistics + normalise + SiLU in ONE launch
+// At the 16x16 .. 4x4 levels an image is a few tens of KB (L1 / L2 resident) and the three-launch sequence
+// partial sums -> finalize -> apply is pure launch latency (~100 tiny dependent launches per score step).  One CTA per
+// image: pass 1 accumulates per-channel sums (thread = one 8-channel pack x a strided set of pixels, fp32), the CTA
+// reduces them in shared memory (double from there on, as gn_finalize does), forms the per-channel scale / shift,
+// pass 2 re-reads the image and applies them.  y may alias x.
+template <typename T>
+__global__ void __launch_bounds__(256) gn_small_kernel(const T* __restrict__ x, int64_t HW, int C, int ld_x, int G,
+                                                       const float* __restrict__ gamma, const float* __restrict__ beta,
+                                                       float eps, int silu, T* __restrict__ y, int ld_y) {
+  __shared__ float red[2][256 * 8];     // [sum | sum of squares][pixel lane][channel] (ppb * C = 2048 floats each)
+  __shared__ double chan[2][256];
+  __shared__ double grp[2][64];
+  __shared__ float ss[2][256];
+  const int b = blockIdx.x, cv = C / 8, ppb = 256 / cv;
+  const int v = threadIdx.x % cv, pp = threadIdx.x / cv;
+  const T* xb = x + (int64_t)b * HW * ld_x + v * 8;
+  T* yb = y + (int64_t)b * HW * ld_y + v * 8;
+  float s[8], q[8];
+#pragma unroll
+  for (int i = 0; i < 8; ++i) s[i] = q[i] = 0.f;
+  if (pp < ppb) {
+    for (int64_t p = pp; p < HW; p += ppb) {
+      float f[8];
+      Pack8<T>::load(xb + p * ld_x, f);
+#pragma unroll
+      for (int i = 0; i < 8; ++i) {
+        s[i] += f[i];
+        q[i] = fmaf(f[i], f[i], q[i]);
+      }
+    }
+#pragma unroll
+    for (int i = 0; i < 8; ++i) {
+      red[0][pp * C + v * 8 + i] = s[i];
+      red[1][pp * C + v * 8 + i] = q[i];
+    }
+  }
+  __syncthreads();
+  for (int c = threadIdx.x; c < C; c += blockDim.x) {
+    double a = 0.0, d = 0.0;
+    for (int j = 0; j < ppb; ++j) {
+      a += (double)red[0][j * C + c];
+      d += (double)red[1][j * C + c];
+    }
+    chan[0][c] = a;
+    chan[1][c] = d;
+  }
+  __syncthreads();
+  const int cpg = C / G;
+  for (int g = threadIdx.x; g < G; g += blockDim.x) {
+    double a = 0.0, d = 0.0;
+    for (int i = 0; i < cpg; ++i) {
+      a += chan[0][g * cpg + i];
+      d += chan[1][g * cpg + i];
+    }
+    const double n = (double)HW * cpg, mean = a / n;
+    double var = d / n - mean * mean;
+    if (var < 0.0) var = 0.0;
+    grp[0][g] = mean;
+    grp[1][g] = 1.0 / sqrt(var + (double)eps);
+  }
+  __syncthreads();
+  for (int c = threadIdx.x; c < C; c += blockDim.x) {
+    const int g = c / cpg;
+    const double sc = grp[1][g] * (double)gamma[c];
+    ss[0][c] = (float)sc;
+    ss[1][c] = (float)((double)beta[c] - grp[0][g] * sc);
+  }
+  __syncthreads();
+  if (pp < ppb) {
+    float sc[8], sh[8];
+#pragma unroll
+    for (int i = 0; i < 8; ++i) {
+      sc[i] = ss[0][v * 8 + i];
+      sh[i] = ss[1][v * 8 + i];
+    }
+    for (int64_t p = pp; p < HW; p += ppb) {
+      float f[8];
+      Pack8<T>::load(xb + p * ld_x, f);
+#pragma unroll
+      for (int i = 0; i < 8; ++i) {
+        const float t = fmaf(f[i], sc[i], sh[i]);
+        f[i] = silu ? silu_f(t) : t;
+      }
+      Pack8<T>::store(yb + p * ld_y, f);
+    }
+  }
+}
+
 // ------------------------------------------------------------------- FIR x2 resampling
 // Separable [1,3,3,1]: down = taps (1,3,3,1)/8 per axis at input 2o-1..2o+2 (zero outside);
 // up = polyphase: out[2i] = (x[i-1] + 3 x[i])/4, out[2i+1] = (3 x[i] + x[i+1])/4 per axis.
@@ -747,6 +836,23 @@ extern "C" int ditsep_gn_finalize(const ditsep_stats_src* host_srcs, int n_srcs,
   gn_finalize_srcs_kernel<<<grid, threads, (size_t)(2 * nj * gpc * cpg) * sizeof(double), (cudaStream_t)stream>>>(
       srcs, HW, C, G, gpc, gamma, beta, eps, scale_shift);
   return check_launch("gn_finalize_srcs_kernel");
+}
+
+extern "C" int ditsep_gn_small(const void* x, int dtype, int B, int64_t HW, int C, int ld_x, int G, const float* gamma,
+                               const float* beta, float eps, int silu, void* y, int ld_y, void* stream) {
+  DITSEP_REQUIRE(x && y && gamma && beta, "gn_small: null pointer");
+  DITSEP_REQUIRE(C % 8 == 0 && ld_x % 8 == 0 && ld_y % 8 == 0 && C <= 256 && 256 % (C / 8) == 0,
+                 "gn_small: C=%d must be a multiple of 8 dividing 2048, strides multiples of 8", C);
+  DITSEP_REQUIRE(G > 0 && G <= 64 && C % G == 0, "gn_small: G=%d must divide C=%d (G <= 64)", G, C);
+  DITSEP_REQUIRE(B > 0 && HW > 0 && HW <= 4096, "gn_small: meant for small images (HW=%lld)", (long long)HW);
+  cudaStream_t st = (cudaStream_t)stream;
+  if (dtype == DITSEP_F32)
+    gn_small_kernel<float><<<B, 256, 0, st>>>((const float*)x, HW, C, ld_x, G, gamma, beta, eps, silu, (float*)y, ld_y);
+  else if (dtype == DITSEP_BF16)
+    gn_small_kernel<bf16><<<B, 256, 0, st>>>((const bf16*)x, HW, C, ld_x, G, gamma, beta, eps, silu, (bf16*)y, ld_y);
+  else
+    DITSEP_REQUIRE(false, "gn_small: unknown dtype %d", dtype);
+  return check_launch("gn_small_kernel");
 }
 
 extern "C" int ditsep_gn_apply(const void* x, int dtype, int B, int64_t HW, int C, int ld_x, const float* scale_shift,

@@ -403,14 +403,22 @@ class _Plan:
                 i += 1
             # progressive output skip: GN -> SiLU -> conv3x3(C -> Cin0), summed over levels
             cch = layout[i].in_ch
-            ss = self._scale_shift(cur, w[f"gn{i}"])
+            if self._small(cur):
+                hact = pool.get(tuple(cur.shape), adt)
+                self._gn_act(cur, w[f"gn{i}"], True, hact)
+                src, gnk = hact, {}
+            else:
+                hact = None
+                src, gnk = cur, {"in_ss": self._scale_shift(cur, w[f"gn{i}"])}
             i += 1
             newpyr = new(B, hh, ww, Cin0, dtype=f32)
             if pyramid is None:
-                self._conv(cur, w[f"conv{i}"], newpyr, in_ss=ss)
+                self._conv(src, w[f"conv{i}"], newpyr, **gnk)
             else:
                 add((ops.fir_resample, (pyramid, True), {"out_x": newpyr}))
-                self._conv(cur, w[f"conv{i}"], newpyr, residual=newpyr, in_ss=ss)
+                self._conv(src, w[f"conv{i}"], newpyr, residual=newpyr, **gnk)
+            if hact is not None:
+                pool.put(hact)
             pyramid = newpyr
             i += 1
             if lvl != 0:
@@ -476,10 +484,9 @@ class _Plan:
         else:
             self.steps.append((ops.conv_direct, (x, cw.w, cw.bias, out, cw.ksize), kw))
         if want_stats and not fused:
-            B, H, W, C = out.shape
-            buf = torch.empty(ops.gn_partial_floats(B, H * W, C), device=self.device, dtype=torch.float32)
-            self.steps.append((ops.gn_partial_sums, (out, buf), {}))
-            self.stat_src[key] = (buf, ops.split_sums_layout(H * W, C))
+            # LAZY: the explicit statistics pass is only appended when a consumer asks for scale / shift
+            # (_scale_shift); small-image consumers use the one-launch gn_small instead and never do
+            self.stat_src[key] = ("lazy", out)
         return True
 
     def _scale_shift(self, x, gnw) -> torch.Tensor:
@@ -498,6 +505,14 @@ class _Plan:
             if hit is None:
                 srcs = None
                 break
+            if isinstance(hit[1][0], str):  # "lazy": the producer left no statistics: one explicit pass over its output, now
+                t = hit[1][1]
+                Bt, Ht, Wt, Ct = t.shape
+                buf = torch.empty(ops.gn_partial_floats(Bt, Ht * Wt, Ct), device=self.device, dtype=torch.float32)
+                self.steps.append((ops.gn_partial_sums, (t, buf), {}))
+                val = (buf, ops.split_sums_layout(Ht * Wt, Ct))
+                self.stat_src[(t.data_ptr(), Ct)] = val
+                hit = (hit[0], val)
             srcs.append(hit[1])
             ptr += hit[0] * x.element_size()
             left -= hit[0]
@@ -507,12 +522,26 @@ class _Plan:
             self.steps.append((ops.gn_stats, (x, G, gnw[0], gnw[1], 1e-6, self.gn_partial, ss), {}))
         return ss
 
+    @staticmethod
+    def _small(x) -> bool:
+        """Images of at most 16 x 16 pixels: statistics + normalise + activation in ONE launch (ops.gn_small) instead
+        of partial sums -> finalize -> apply (or the conv's fused operand path)."""
+        B, H, W, C = x.shape
+        return H * W <= 256 and C <= 256 and C % 8 == 0 and 256 % (C // 8) == 0 and \
+            os.environ.get("DITSEP_GN_SMALL", "1") != "0"
+
+    def _gn_act(self, x, gnw, silu: bool, out):
+        """out = act?(GroupNorm(min(C/4, 32), C, eps=1e-6)(x)) for a small image (out may be x)."""
+        C = x.shape[3]
+        self.steps.append((ops.gn_small, (x, min(C // 4, 32), gnw[0], gnw[1], 1e-6, silu, out), {}))
+
     def _resblock(self, i: int, spec: ModuleSpec, x, out):
         """ResnetBlockBigGANpp.forward (layerspp.py:296-328)."""
         w, pool, add = self.eng.w, self.pool, self.steps.append
         B, H, W, cin = x.shape
         cout = spec.out_ch
-        ss0 = self._scale_shift(x, w[f"gn{i}a"])
+        small0 = self._small(x) and not (spec.up or spec.down)
+        ss0 = None if small0 else self._scale_shift(x, w[f"gn{i}a"])
         if spec.up or spec.down:
             Ho, Wo = (2 * H, 2 * W) if spec.up else (H // 2, W // 2)
             xr = pool.get((B, Ho, Wo, cin), self.adt)
@@ -524,14 +553,21 @@ class _Plan:
             hA = None
         h1 = pool.get((B, Ho, Wo, cout), self.adt)
         off = w[f"dense_off{i}"]
+        if small0:
+            hA = pool.get((B, H, W, cin), self.adt)
+            self._gn_act(x, w[f"gn{i}a"], True, hA)
         if hA is None:  # act(GroupNorm_0(x)) rides in conv0's operand path
             self._conv(x, w[f"conv{i}a"], h1, bias_b=self.dense[:, off:off + cout], want_stats=True, in_ss=ss0)
         else:
             self._conv(hA, w[f"conv{i}a"], h1, bias_b=self.dense[:, off:off + cout], want_stats=True)
             pool.put(hA)
-        ss1 = self._scale_shift(h1, w[f"gn{i}b"])
-        # act(GroupNorm_1(h)) rides in conv1's operand path (or, unfused, is applied to h1 in place)
-        gn1 = {"in_ss": ss1, "in_silu": True, "gn_inplace": True}
+        if self._small(h1):
+            self._gn_act(h1, w[f"gn{i}b"], True, h1)  # in place, one launch
+            gn1 = {}
+        else:
+            ss1 = self._scale_shift(h1, w[f"gn{i}b"])
+            # act(GroupNorm_1(h)) rides in conv1's operand path (or, unfused, is applied to h1 in place)
+            gn1 = {"in_ss": ss1, "in_silu": True, "gn_inplace": True}
         fused = w.get(f"conv{i}b_sc")
         if not (fused is not None and self._conv(h1, fused, out, shortcut=xr, out_scale=1.0 / math.sqrt(2.0),
                                                  want_stats=True, **gn1)):
@@ -550,10 +586,14 @@ class _Plan:
         """AttnBlockpp.forward (layerspp.py:81-97)."""
         w, pool, add = self.eng.w, self.pool, self.steps.append
         B, H, W, C = x.shape
-        ss = self._scale_shift(x, w[f"gn{i}"])
         hn = pool.get((B, H, W, C), self.adt)
         qkv = pool.get((B, H, W, 3 * C), self.adt)
-        self._conv(x, w[f"qkv{i}"], qkv, in_ss=ss, in_silu=False)  # GroupNorm_0 (no activation) in the operand path
+        if self._small(x):
+            self._gn_act(x, w[f"gn{i}"], False, hn)
+            self._conv(hn, w[f"qkv{i}"], qkv)
+        else:
+            ss = self._scale_shift(x, w[f"gn{i}"])
+            self._conv(x, w[f"qkv{i}"], qkv, in_ss=ss, in_silu=False)  # GroupNorm_0 (no activation) in the operand path
         add((ops.attention, (qkv[..., :C], qkv[..., C:2 * C], qkv[..., 2 * C:], hn), {}))
         self._conv(hn, w[f"proj{i}"], out, residual=x, out_scale=1.0 / math.sqrt(2.0), want_stats=True)
         pool.put(hn)

@@ -198,6 +198,16 @@ def gn_finalize(srcs, B: int, HW: int, G: int, gamma, beta, eps: float, scale_sh
                                          _stream()), "gn_finalize")
 
 
+def gn_small(x, G: int, gamma, beta, eps: float, silu: bool, y):
+    """act(GroupNorm(x)) of a small NHWC image batch in ONE launch (ditsep_gn_small); y may alias x."""
+    _cuda(x, gamma, beta, y)
+    B, H, W, Cc = x.shape
+    if y.dtype != x.dtype:
+        raise _lib.DitsepError("gn_small: dtype mismatch")
+    check(_lib.load().ditsep_gn_small(_ptr(x), _dt(x), B, H * W, Cc, nhwc_ld(x), G, _ptr(gamma), _ptr(beta), eps,
+                                      int(silu), _ptr(y), nhwc_ld(y), _stream()), "gn_small")
+
+
 def gn_apply(x, scale_shift, silu: bool, y):
     _cuda(x, scale_shift, y)
     B, H, W, Cc = x.shape

@@ -119,6 +119,12 @@ typedef struct {
  * layerspp.py:297).  Partials are added in a fixed order, in double. */
 int ditsep_gn_finalize(const ditsep_stats_src* host_srcs, int n_srcs, int B, int64_t HW, int G, const float* gamma,
                        const float* beta, float eps, float* scale_shift, void* stream);
+/* GroupNorm statistics + normalise (+ SiLU) of SMALL images in one launch (one CTA per image; y may alias x):
+ * act(GroupNorm(x)) of ResnetBlockBigGANpp.forward (layerspp.py:297,318) at the 16x16 .. 4x4 levels, where the
+ * three-launch sequence gn_partial_sums -> gn_finalize -> gn_apply is pure launch latency.  HW <= 4096, C <= 256. */
+int ditsep_gn_small(const void* x, int dtype, int B, int64_t HW, int C, int ld_x, int G, const float* gamma,
+                    const float* beta, float eps, int silu, void* y, int ld_y, void* stream);
+
 /* y = act(x*scale + shift), act = SiLU if silu else identity.  y: NHWC with stride ld_y. */
 int ditsep_gn_apply(const void* x, int dtype, int B, int64_t HW, int C, int ld_x, const float* scale_shift,
                     int silu, void* y, int ld_y, void* stream);

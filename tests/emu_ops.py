@@ -18,7 +18,7 @@ import torch.nn.functional as F
 from ditsep_b200 import ops
 
 _NAMES = ["pc_corrector", "pc_predictor", "pc_prior", "philox_normal", "stft_compress", "expand_istft", "gn_stats",
-          "gn_partial_sums", "gn_finalize", "gn_apply", "fir_resample", "conv_direct", "attention", "temb_mlp", "temb_dense", "output_layer"]
+          "gn_partial_sums", "gn_finalize", "gn_apply", "gn_small", "fir_resample", "conv_direct", "attention", "temb_mlp", "temb_dense", "output_layer"]
 
 
 def _coef(p, mode, t):
@@ -164,6 +164,13 @@ def gn_finalize(srcs, B, HW, G, gamma, beta, eps, scale_shift):
     sh = beta.double() - mean.repeat_interleave(cpg, dim=1) * sc
     scale_shift[:, 0].copy_(sc.float())
     scale_shift[:, 1].copy_(sh.float())
+
+
+def gn_small(x, G, gamma, beta, eps, silu, y):
+    B, H, W, C = x.shape
+    ss = torch.empty(B, 2, C)
+    gn_stats(x, G, gamma, beta, eps, None, ss)
+    gn_apply(x, ss, silu, y)
 
 
 def gn_apply(x, scale_shift, silu, y):

@@ -156,6 +156,28 @@ def test_groupnorm(C, ld, H, W, B, dtype):
     assert rel(yv.float(), y_ref.float()) < (1e-5 if dtype == torch.float32 else 6e-3)
 
 
+@pytest.mark.parametrize("B,H,W,C,ld,dtype,silu", [(3, 16, 16, 128, 128, torch.bfloat16, True),
+                                                   (2, 4, 4, 256, 256, torch.bfloat16, True),
+                                                   (2, 8, 8, 64, 192, torch.float32, False),
+                                                   (1, 16, 12, 64, 64, torch.float32, True)])
+def test_gn_small_one_launch(B, H, W, C, ld, dtype, silu):
+    """ditsep_gn_small = statistics + normalise (+ SiLU) of a small image in one launch, against the two-step
+    definition (emulated gn_stats + gn_apply); also in place and on a channel slice of a wider buffer."""
+    buf = (torch.randn(B, H, W, ld, generator=g(40)) * 1.7 + 0.3).to(dtype)
+    x = buf[..., ld - C:]
+    G = min(C // 4, 32)
+    gamma, beta = 1 + 0.1 * torch.randn(C, generator=g(41)), 0.1 * torch.randn(C, generator=g(42))
+    ref = torch.empty(B, H, W, C, dtype=dtype)
+    E.gn_small(x, G, gamma, beta, 1e-6, silu, ref)
+    xd = buf.to(DEV)[..., ld - C:]
+    out = torch.empty(B, H, W, C, device=DEV, dtype=dtype)
+    ops.gn_small(xd, G, gamma.to(DEV), beta.to(DEV), 1e-6, silu, out)
+    tol = 6e-3 if dtype == torch.bfloat16 else 2e-5
+    assert rel(out.float(), ref.float()) < tol
+    ops.gn_small(xd, G, gamma.to(DEV), beta.to(DEV), 1e-6, silu, xd)  # in place
+    assert torch.equal(xd, out)
+
+
 @pytest.mark.parametrize("up", [False, True])
 @pytest.mark.parametrize("dtype", [torch.float32, torch.bfloat16])
 def test_fir_resample(up, dtype):
