@@ -41,7 +41,7 @@ namespace ditsep {
 constexpr int kTileM = 128;
 constexpr int kBlockK = 64;  // bf16 elements = 128 bytes = one swizzle row
 constexpr int kABytes = kTileM * kBlockK * 2;
-constexpr int kMaxStages = 6;
+constexpr int kMaxStages = 8;
 constexpr int kThreads = 192;
 constexpr int kTraceTiles = 96, kTraceCtas = 4;
 
@@ -921,6 +921,20 @@ extern "C" int ditsep_conv_tc_plan_create_sc(ditsep_conv_plan** plan, const void
   int tile = (W >= kTileW && H >= kTileH && (cout_pad <= kTileMaxBN || cout_pad % kTileMaxBN == 0) &&
               !(mode_env && strcmp(mode_env, "tap") == 0)) ? 1 : 0;
   size_t smem = 1024 + (size_t)p.stages * stage_bytes;
+  if (!tile) {
+    // Small images give few M tiles (4 x 4 at batch 32: four), and a CTA that streams the whole filter through one
+    // SM's load path is latency-bound: narrow the N tile until about half the SMs have a CTA, and use the shared
+    // memory that frees for a deeper ring.
+    const int64_t m_tiles = (int64_t)p.tiles_x * p.tiles_y * p.tiles_b;
+    while (p.BN > 32 && p.BN % 32 == 0 && cout_pad % (p.BN / 2) == 0 && m_tiles * ceil_div(cout_pad, p.BN) < 74) p.BN /= 2;
+    p.n_tiles = ceil_div(cout_pad, p.BN);
+    p.tmem_cols = pow2_ceil(p.BN) < 32 ? 32 : pow2_ceil(p.BN);
+    const size_t sb = (size_t)kABytes + (size_t)p.BN * 128;
+    p.stages = (int)((size_t)(192 * 1024) / sb);
+    if (p.stages > kMaxStages) p.stages = kMaxStages;
+    if (p.stages > num_kb) p.stages = num_kb;
+    smem = 1024 + (size_t)p.stages * sb;
+  }
   int grid_x = 0;
   DITSEP_REQUIRE(!x_sc || tile, "conv_tc: fused shortcut needs the tile kernel (image >= 8 x 16)");
   if (tile) {
@@ -1017,7 +1031,7 @@ extern "C" int ditsep_conv_tc_plan_create_sc(ditsep_conv_plan** plan, const void
   static bool attr_set = false;
   if (!attr_set) {
     DITSEP_CUDA(cudaFuncSetAttribute(conv_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                     1024 + kMaxStages * (kABytes + 128 * 128)));
+                                     1024 + 192 * 1024));
 #define DITSEP_TILE_ATTR(KS, RES, FAST)                                                                              \
   DITSEP_CUDA(cudaFuncSetAttribute(conv_tc_tile_kernel<KS, RES, FAST, false>,                                       \
                                    cudaFuncAttributeMaxDynamicSharedMemorySize, 224 * 1024));                       \
