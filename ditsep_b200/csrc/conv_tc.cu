@@ -655,10 +655,13 @@ __global__ void __launch_bounds__(tile_threads(kXf), 1) conv_tc_tile_kernel(cons
   } else if (warp >= kCtrlWarps) {
     const int e = warp - kCtrlWarps;
     const int q = warp & 3;            // TMEM lane quadrant this warp may read
-    const int c0 = (e >> 2) * 16;      // its 16 output channels inside the N tile
-    const bool has_cols = c0 < p.BN;
+    // N tiles of 16 columns (the 6-channel pyramid outputs) would leave twelve of the sixteen warps idle and the
+    // other four serialised on global-memory latency: there the four warp groups take the tiles in turn instead.
+    const bool spread = p.BN <= 16 && p.stats == nullptr;
+    const uint32_t grp = (uint32_t)(e >> 2);
+    const int c0 = spread ? 0 : (e >> 2) * 16;  // its 16 output channels inside the N tile
+    const bool cols_any = c0 < p.BN;
     const int nvalid = min(16, p.Cout - (n0 + c0));
-    const bool active = has_cols && nvalid > 0;
     const int r = q * 32 + lane;
     const int xo = r & 7, yo = r >> 3;
     const int etid = e * 32 + lane;    // 0..511
@@ -691,6 +694,8 @@ __global__ void __launch_bounds__(tile_threads(kXf), 1) conv_tc_tile_kernel(cons
         cb = cw;
         ++nimg;
       }
+      const bool has_cols = cols_any && (!spread || (it & 3u) == grp);
+      const bool active = has_cols && nvalid > 0;
       const int px = tw.tx * kTileW + xo, py = tw.ty * kTileH + yo;
       const bool valid = px < p.W && py < p.H;
       const int64_t pix = (int64_t)((pb * p.H + py) * p.W + px);  // B*H*W < 2^31 pixels

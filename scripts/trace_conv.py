@@ -1,5 +1,5 @@
 """Per-tile timeline of conv_tc_tile_kernel (clock64 stamps, ditsep_debug_conv_trace).
-usage: python scripts/trace_conv.py [Cin] [Cout] [H] [B] [residual 0/1]"""
+usage: python scripts/trace_conv.py [Cin] [Cout] [H] [B] [residual 0/1] [Cx] [f32: fp32 output/residual, no statistics]"""
 import os, sys
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__))); sys.path.insert(0, ROOT)
 import torch
@@ -15,10 +15,12 @@ x = torch.randn(B, H, H, Cin, device=dev).to(torch.bfloat16)
 w = (torch.randn(Cout, 9 * Cin + Cx, device=dev) / (9 * Cin) ** 0.5).to(torch.bfloat16)
 xs = torch.randn(B, H, H, Cx, device=dev).to(torch.bfloat16) if Cx else None
 bias = torch.zeros(Cout, device=dev)
-out = torch.empty(B, H, H, Cout, device=dev, dtype=torch.bfloat16)
-res = torch.randn(B, H, H, Cout, device=dev).to(torch.bfloat16) if use_res else None
+f32 = len(sys.argv) > 7 and sys.argv[7] == "f32"   # the pyramid output convolutions: fp32 output and residual, no statistics
+odt = torch.float32 if f32 else torch.bfloat16
+out = torch.empty(B, H, H, Cout, device=dev, dtype=odt)
+res = torch.randn(B, H, H, Cout, device=dev).to(odt) if use_res else None
 plan = ops.ConvTcPlan(x, w, Cout, 3, shortcut=xs)
-stats = torch.empty(max(1, plan.stats_floats()), device=dev)
+stats = None if f32 else torch.empty(max(1, plan.stats_floats()), device=dev)
 for _ in range(3):
     plan.run(bias, out, residual=res, stats=stats)
 torch.cuda.synchronize()
