@@ -678,11 +678,30 @@ __global__ void __launch_bounds__(256) split_hilo_kernel(const float* __restrict
 }
 
 // ------------------------------------------------------------------- time embedding
-// grid B, block 256.  smem: feat[2nf] | hid[4nf]
-__global__ void __launch_bounds__(256) temb_mlp_kernel(const float* __restrict__ t, const float* __restrict__ gfp_w,
-                                                       const float* __restrict__ w1, const float* __restrict__ b1,
-                                                       const float* __restrict__ w2, const float* __restrict__ b2,
-                                                       float* __restrict__ act_temb, int nf) {
+// grid B, block 1024.  smem: feat[2nf] | hid[4nf].  A warp computes four output rows at a time so that their
+// weight loads are in flight together (the layer is a chain of global-load latencies, not of flops); the
+// summation order inside a row is lane-strided then warp_sum, whatever the row grouping.
+template <int ROWS>
+__device__ __forceinline__ void temb_rows(const float* __restrict__ w, const float* __restrict__ x, int K, int o0,
+                                          int ostride, int n_out, int lane, float (&acc)[ROWS]) {
+#pragma unroll
+  for (int r = 0; r < ROWS; ++r) acc[r] = 0.f;
+  for (int k = lane; k < K; k += 32) {
+    const float xv = x[k];
+#pragma unroll
+    for (int r = 0; r < ROWS; ++r) {
+      const int o = o0 + r * ostride;
+      if (o < n_out) acc[r] = fmaf(w[(int64_t)o * K + k], xv, acc[r]);
+    }
+  }
+#pragma unroll
+  for (int r = 0; r < ROWS; ++r) acc[r] = warp_sum(acc[r]);
+}
+
+__global__ void __launch_bounds__(1024) temb_mlp_kernel(const float* __restrict__ t, const float* __restrict__ gfp_w,
+                                                        const float* __restrict__ w1, const float* __restrict__ b1,
+                                                        const float* __restrict__ w2, const float* __restrict__ b2,
+                                                        float* __restrict__ act_temb, int nf) {
   extern __shared__ float sm[];
   float* feat = sm;
   float* hid = sm + 2 * nf;
@@ -698,43 +717,67 @@ __global__ void __launch_bounds__(256) temb_mlp_kernel(const float* __restrict__
   }
   __syncthreads();
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, nw = blockDim.x >> 5;
-  for (int o = warp; o < 4 * nf; o += nw) {
-    const float* wr = w1 + (int64_t)o * 2 * nf;
-    float acc = 0.f;
-    for (int k = lane; k < 2 * nf; k += 32) acc = fmaf(wr[k], feat[k], acc);
-    acc = warp_sum(acc);
+  constexpr int ROWS = 4;
+  float acc[ROWS];
+  for (int o0 = warp; o0 < 4 * nf; o0 += nw * ROWS) {
+    temb_rows<ROWS>(w1, feat, 2 * nf, o0, nw, 4 * nf, lane, acc);
     if (lane == 0) {
-      float h = acc + b1[o];
-      hid[o] = h / (1.0f + expf(-h));
+#pragma unroll
+      for (int r = 0; r < ROWS; ++r) {
+        const int o = o0 + r * nw;
+        if (o < 4 * nf) {
+          const float h = acc[r] + b1[o];
+          hid[o] = h / (1.0f + expf(-h));
+        }
+      }
     }
   }
   __syncthreads();
-  for (int o = warp; o < 4 * nf; o += nw) {
-    const float* wr = w2 + (int64_t)o * 4 * nf;
-    float acc = 0.f;
-    for (int k = lane; k < 4 * nf; k += 32) acc = fmaf(wr[k], hid[k], acc);
-    acc = warp_sum(acc);
+  for (int o0 = warp; o0 < 4 * nf; o0 += nw * ROWS) {
+    temb_rows<ROWS>(w2, hid, 4 * nf, o0, nw, 4 * nf, lane, acc);
     if (lane == 0) {
-      float h = acc + b2[o];
-      act_temb[(int64_t)b * 4 * nf + o] = h / (1.0f + expf(-h));
+#pragma unroll
+      for (int r = 0; r < ROWS; ++r) {
+        const int o = o0 + r * nw;
+        if (o < 4 * nf) {
+          const float h = acc[r] + b2[o];
+          act_temb[(int64_t)b * 4 * nf + o] = h / (1.0f + expf(-h));
+        }
+      }
     }
   }
 }
 
-// One warp per output row r (all res-blocks' Dense_0 rows concatenated), looping over B.
+// One warp per output row r (all res-blocks' Dense_0 rows concatenated).  The CTA stages `bchunk` rows of the
+// activated embedding in shared memory and every warp keeps its weight row in registers (K <= 512), so the
+// per-mixture work is shared-memory loads only.
 __global__ void __launch_bounds__(256) temb_dense_kernel(const float* __restrict__ act_temb,
                                                          const float* __restrict__ dense_w,
                                                          const float* __restrict__ dense_b, float* __restrict__ out,
-                                                         int B, int K, int R) {
-  const int warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
-  if (warp >= R) return;
-  const float* wr = dense_w + (int64_t)warp * K;
-  for (int b = 0; b < B; ++b) {
-    const float* a = act_temb + (int64_t)b * K;
-    float acc = 0.f;
-    for (int k = lane; k < K; k += 32) acc = fmaf(wr[k], a[k], acc);
-    acc = warp_sum(acc);
-    if (lane == 0) out[(int64_t)b * R + warp] = acc + dense_b[warp];
+                                                         int B, int K, int R, int bchunk) {
+  extern __shared__ float sa[];  // [bchunk][K]
+  const int row = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
+  const bool live = row < R;
+  constexpr int KR = 16;
+  float wv[KR];
+#pragma unroll
+  for (int j = 0; j < KR; ++j) wv[j] = (live && lane + 32 * j < K) ? dense_w[(int64_t)row * K + lane + 32 * j] : 0.f;
+  const float bias = live ? dense_b[row] : 0.f;
+  for (int b0 = 0; b0 < B; b0 += bchunk) {
+    const int nb = min(bchunk, B - b0);
+    __syncthreads();
+    for (int i = threadIdx.x; i < nb * K; i += blockDim.x) sa[i] = act_temb[(int64_t)b0 * K + i];
+    __syncthreads();
+    if (!live) continue;
+    for (int b = 0; b < nb; ++b) {
+      const float* a = sa + b * K;
+      float acc = 0.f;
+#pragma unroll
+      for (int j = 0; j < KR; ++j)
+        if (lane + 32 * j < K) acc = fmaf(wv[j], a[lane + 32 * j], acc);
+      acc = warp_sum(acc);
+      if (lane == 0) out[(int64_t)(b0 + b) * R + row] = acc + bias;
+    }
   }
 }
 
@@ -957,7 +1000,7 @@ extern "C" int ditsep_temb_mlp(const float* t, const float* gfp_w, const float* 
                                const float* b2, float* act_temb, int B, int nf, void* stream) {
   DITSEP_REQUIRE(t && gfp_w && w1 && b1 && w2 && b2 && act_temb, "temb_mlp: null pointer");
   DITSEP_REQUIRE(B > 0 && nf > 0 && nf <= 1024, "temb_mlp: bad B=%d nf=%d", B, nf);
-  temb_mlp_kernel<<<B, 256, (size_t)6 * nf * sizeof(float), (cudaStream_t)stream>>>(t, gfp_w, w1, b1, w2, b2, act_temb,
+  temb_mlp_kernel<<<B, 1024, (size_t)6 * nf * sizeof(float), (cudaStream_t)stream>>>(t, gfp_w, w1, b1, w2, b2, act_temb,
                                                                                     nf);
   return check_launch("temb_mlp_kernel");
 }
@@ -965,9 +1008,10 @@ extern "C" int ditsep_temb_mlp(const float* t, const float* gfp_w, const float* 
 extern "C" int ditsep_temb_dense(const float* act_temb, const float* dense_w, const float* dense_b, float* out, int B,
                                  int K, int R, void* stream) {
   DITSEP_REQUIRE(act_temb && dense_w && dense_b && out, "temb_dense: null pointer");
-  DITSEP_REQUIRE(B > 0 && K > 0 && R > 0, "temb_dense: bad sizes");
-  temb_dense_kernel<<<ceil_div((int64_t)R * 32, 256), 256, 0, (cudaStream_t)stream>>>(act_temb, dense_w, dense_b, out,
-                                                                                      B, K, R);
+  DITSEP_REQUIRE(B > 0 && K > 0 && K <= 512 && R > 0, "temb_dense: bad sizes (K <= 512)");
+  const int bchunk = std::max(1, std::min(B, 12288 / K));  // at most 48 KB of shared memory
+  temb_dense_kernel<<<ceil_div((int64_t)R * 32, 256), 256, (size_t)bchunk * K * sizeof(float), (cudaStream_t)stream>>>(
+      act_temb, dense_w, dense_b, out, B, K, R, bchunk);
   return check_launch("temb_dense_kernel");
 }
 
