@@ -250,7 +250,8 @@ def run_ours(args):
 
     line = None
     if rank == 0:
-        base = cpu_baseline() if not args.no_cpu_baseline else None
+        # the CPU baseline is timed at N=1 only: under torchrun the other ranks' processes share the host cores
+        base = cpu_baseline() if (world == 1 and not args.no_cpu_baseline) else None
         line = {"metric": METRIC, "value": value, "unit": "mixtures/s", "n_gpus": world, "steps": args.steps,
                 "warmup": args.warmup, "ms_per_step": ms_res / args.steps, "higher_is_better": True, "scaling": "weak",
                 "vs_baseline": None, "dtype": "bf16" if precision == "bf16" else "f32", "data": "synthetic",
