@@ -113,8 +113,14 @@ def run_reference(args):
         return
     per = []
     base = None
+    # One step = one complete mixture (60 score evaluations) when the whole run then stays within ~3 minutes of CPU
+    # time; otherwise a bounded, extrapolated sample of it (the sample is named in cpu_baseline.sample).
+    probe = cpu_baseline(n_score_steps=4)
+    budget_s = 180.0 / (args.warmup + args.steps)
+    n_eval = int(budget_s / (probe["ms_per_score_step"] * 1e-3)) // 2 * 2
+    n_eval = max(2, min(NFE, n_eval))
     for i in range(args.warmup + args.steps):
-        base = cpu_baseline(n_score_steps=60)  # one complete mixture per step
+        base = cpu_baseline(n_score_steps=n_eval)
         if i >= args.warmup:
             per.append(base["value"])
     v = sum(per) / len(per)
