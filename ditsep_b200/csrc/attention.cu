@@ -22,6 +22,7 @@ template <typename T, int CPL>
 __global__ void __launch_bounds__(256) attention_kernel(const T* __restrict__ q, const T* __restrict__ k,
                                                         const T* __restrict__ v, int S, int ld, T* __restrict__ o,
                                                         int ld_o, float scale) {
+  griddep_launch_dependents();
   constexpr int C = CPL * 32;
   extern __shared__ __align__(16) float sm[];
   float* Ks = sm;                                   // [kKTile][C + 1]

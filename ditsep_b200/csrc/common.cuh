@@ -113,6 +113,10 @@ __device__ __forceinline__ float silu_f(float x) {
 // ~2^-11 relative, i.e. an absolute error of |h| * 5e-4 on the result: below bf16 rounding for positive outputs, up to a
 // few bf16 ulps on the small negative tail.  Used only where the result is rounded to bf16 anyway AND the MUFU pipe is
 // the bottleneck (the conv kernel's in-shared-memory GroupNorm transform).
+// Programmatic dependent launch, primary side: lets a dependent kernel launched with the programmatic-stream-
+// serialization attribute (the conv tile kernel) be scheduled as this grid's CTAs retire.  A no-op otherwise.
+__device__ __forceinline__ void griddep_launch_dependents() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
+
 __device__ __forceinline__ float silu_tanh_f(float x) {
   const float h = 0.5f * x;
   float t;

@@ -69,6 +69,12 @@ struct ConvTcParams {
   long long* trace;        // debug (ditsep_debug_conv_trace): [4 CTAs][kTraceTiles][8] clock64 stamps, else nullptr
 };
 
+// Programmatic dependent launch: the tile kernel may start while the kernel before it in the stream drains (that
+// kernel calls griddep_launch_dependents early).  Everything before griddep_wait() -- barrier init, TMEM allocation,
+// tensor-map prefetch, the resident filter preload (static data) -- overlaps that tail; no thread touches a tensor the
+// predecessor writes, or writes anything at all to global memory, before it.
+__device__ __forceinline__ void griddep_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+
 __device__ __forceinline__ void trace_stamp(const ConvTcParams& p, uint32_t it, int slot) {
   if (p.trace && blockIdx.x < kTraceCtas && blockIdx.y == 0 && it < kTraceTiles)
     p.trace[((int64_t)blockIdx.x * kTraceTiles + it) * 16 + slot] = clock64();
@@ -393,6 +399,7 @@ __global__ void __launch_bounds__(tile_threads(kXf), 1) conv_tc_tile_kernel(cons
           tma_load_2d(base + (uint32_t)(p.chunks * kTaps + cx) * w_tile_bytes, &mapW, bar, kTaps * p.Cin + cx * kBlockK, n0);
         if (p.xchunks) asm volatile("prefetch.tensormap [%0];" ::"l"(&mapX) : "memory");
       }
+      griddep_wait();  // the activations are the predecessor's output
       int sa = 0, sw = 0;
       uint32_t pa = 1, pw = 1;  // "empty" barriers start free: the first pass waits on the opposite parity
       TileWalk tw;
@@ -583,6 +590,7 @@ __global__ void __launch_bounds__(tile_threads(kXf), 1) conv_tc_tile_kernel(cons
     // One thread = one 16-byte channel pack (fixed for its whole life: scale / shift in registers) of every 16th row of
     // the halo box.  Pixels outside the image stay zero (TMA zero fill): the conv pads the ACTIVATED tensor.
     if (kXf) {
+      griddep_wait();  // in_scale_shift comes from gn_finalize
       const int t = (int)threadIdx.x - kXformWarp0 * 32;
       const int lc = t & 7;
       const bool xfirst = kRes && p.xchunks > 0 && p.a_stages >= p.xchunks + 2;
@@ -653,6 +661,7 @@ __global__ void __launch_bounds__(tile_threads(kXf), 1) conv_tc_tile_kernel(cons
       }
     }
   } else if (warp >= kCtrlWarps) {
+    griddep_wait();  // bias_b, residual, out and the statistics buffer are shared with earlier kernels
     const int e = warp - kCtrlWarps;
     const int q = warp & 3;            // TMEM lane quadrant this warp may read
     // N tiles of 16 columns (the 6-channel pyramid outputs) would leave twelve of the sixteen warps idle and the
@@ -1101,14 +1110,28 @@ extern "C" int ditsep_conv_tc_run_gn(const ditsep_conv_plan* plan, const float* 
                       (reinterpret_cast<uintptr_t>(out) & 15) == 0 &&
                       (!residual || (res_dtype == DITSEP_BF16 && (ld_res & 7) == 0 &&
                                      (reinterpret_cast<uintptr_t>(residual) & 15) == 0));
+    // launched with the programmatic-stream-serialization attribute (see griddep_wait); DITSEP_PDL=0 turns it off
+    static const bool pdl = !(getenv("DITSEP_PDL") && strcmp(getenv("DITSEP_PDL"), "0") == 0);
+    cudaLaunchAttribute lattr[1];
+    lattr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    lattr[0].val.programmaticStreamSerializationAllowed = 1;
+    cudaLaunchConfig_t lcfg = {};
+    lcfg.gridDim = grid;
+    lcfg.dynamicSmemBytes = plan->smem;
+    lcfg.stream = st;
+    lcfg.attrs = lattr;
+    lcfg.numAttrs = pdl ? 1 : 0;
 #define DITSEP_TILE_LAUNCH(KS, RES, FAST)                                                                            \
   do {                                                                                                               \
-    if (p.in_ss)                                                                                                     \
-      conv_tc_tile_kernel<KS, RES, FAST, true><<<grid, tile_threads(true), plan->smem, st>>>(plan->mapA, plan->mapW, \
-                                                                                              plan->mapX, p);        \
-    else                                                                                                             \
-      conv_tc_tile_kernel<KS, RES, FAST, false><<<grid, tile_threads(false), plan->smem, st>>>(plan->mapA, plan->mapW, \
-                                                                                                plan->mapX, p);      \
+    if (p.in_ss) {                                                                                                   \
+      lcfg.blockDim = dim3(tile_threads(true));                                                                      \
+      DITSEP_CUDA(cudaLaunchKernelEx(&lcfg, conv_tc_tile_kernel<KS, RES, FAST, true>, plan->mapA, plan->mapW,        \
+                                     plan->mapX, p));                                                                \
+    } else {                                                                                                         \
+      lcfg.blockDim = dim3(tile_threads(false));                                                                     \
+      DITSEP_CUDA(cudaLaunchKernelEx(&lcfg, conv_tc_tile_kernel<KS, RES, FAST, false>, plan->mapA, plan->mapW,       \
+                                     plan->mapX, p));                                                                \
+    }                                                                                                                \
   } while (0)
     if (p.ksize == 3) {
       if (p.w_resident) { if (fast) DITSEP_TILE_LAUNCH(3, true, true); else DITSEP_TILE_LAUNCH(3, true, false); }

@@ -192,6 +192,7 @@ template <typename T>
 __global__ void __launch_bounds__(256) gn_apply_kernel(const T* __restrict__ x, int64_t HW, int C, int ld_x,
                                                        const float* __restrict__ scale_shift, int silu,
                                                        T* __restrict__ y, int ld_y, int cv, int ppb) {
+  griddep_launch_dependents();
   const int b = blockIdx.y;
   const int v = threadIdx.x % cv, pp = threadIdx.x / cv;
   if (pp >= ppb) return;
@@ -238,6 +239,7 @@ template <typename T>
 __global__ void __launch_bounds__(256) gn_small_kernel(const T* __restrict__ x, int64_t HW, int C, int ld_x, int G,
                                                        const float* __restrict__ gamma, const float* __restrict__ beta,
                                                        float eps, int silu, T* __restrict__ y, int ld_y) {
+  griddep_launch_dependents();
   __shared__ float red[2][256 * 8];     // [sum | sum of squares][pixel lane][channel] (ppb * C = 2048 floats each)
   __shared__ double chan[2][256];
   __shared__ double grp[2][64];
@@ -374,6 +376,7 @@ __global__ void __launch_bounds__(256, DITSEP_FIR_MINB) fir_down_kernel(const T*
                                                           const float* __restrict__ scale_shift, T* __restrict__ out_x,
                                                           int ld_ox, T* __restrict__ out_h, int ld_oh, int seg_rows,
                                                           int n_seg, int64_t total) {
+  griddep_launch_dependents();
   const int cv = C / 8, Ho = H / 2, Wo = W / 2;
   const int64_t idx = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
   if (idx >= total) return;
@@ -433,6 +436,7 @@ __global__ void __launch_bounds__(256) fir_up_kernel(const T* __restrict__ x, in
                                                      const float* __restrict__ scale_shift, T* __restrict__ out_x,
                                                      int ld_ox, T* __restrict__ out_h, int ld_oh, int seg_rows, int n_seg,
                                                      int64_t total) {
+  griddep_launch_dependents();
   const int cv = C / 8, Ho = 2 * H, Wo = 2 * W;
   const int64_t idx = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
   if (idx >= total) return;
@@ -653,6 +657,7 @@ __global__ void __launch_bounds__(256) fir_narrow_px_kernel(const float* __restr
 template <int C>
 __global__ void __launch_bounds__(256) split_hilo_kernel(const float* __restrict__ x, int64_t npix, bf16* __restrict__ out,
                                                          int ld) {
+  griddep_launch_dependents();
   constexpr int kVec = (3 * C + 7) / 8;
   for (int64_t pix = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; pix < npix; pix += (int64_t)gridDim.x * blockDim.x) {
     float xv[C], f[kVec * 8];
