@@ -109,14 +109,15 @@ __device__ __forceinline__ float silu_f(float x) {
   return x * r;
 }
 
-// SiLU with ONE MUFU: x * sigmoid(x) = h + h * tanh(h), h = x / 2 (FMUL, MUFU.TANH, FFMA).  tanh.approx.f32 is good to
-// ~2^-11 relative, i.e. an absolute error of |h| * 5e-4 on the result: below bf16 rounding for positive outputs, up to a
-// few bf16 ulps on the small negative tail.  Used only where the result is rounded to bf16 anyway AND the MUFU pipe is
-// the bottleneck (the conv kernel's in-shared-memory GroupNorm transform).
 // Programmatic dependent launch, primary side: lets a dependent kernel launched with the programmatic-stream-
 // serialization attribute (the conv tile kernel) be scheduled as this grid's CTAs retire.  A no-op otherwise.
 __device__ __forceinline__ void griddep_launch_dependents() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
 
+// SiLU with ONE MUFU: x * sigmoid(x) = h + h * tanh(h), h = x / 2 (FMUL, MUFU.TANH, FFMA).  tanh.approx.f32 is good to
+// ~2^-11 relative, i.e. an absolute error of |h| * 5e-4 on the result: below bf16 rounding for positive outputs, up to a
+// few bf16 ulps on the small negative tail.  Used only where the result is rounded to bf16 anyway AND the MUFU pipe is
+// the bottleneck (the conv kernel's in-shared-memory GroupNorm transform; the bf16 FIR kernels, which activate every
+// input element two (down) or three (up) times).
 __device__ __forceinline__ float silu_tanh_f(float x) {
   const float h = 0.5f * x;
   float t;
