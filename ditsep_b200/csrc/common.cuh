@@ -7,6 +7,8 @@
 #include <atomic>
 #include <cstdarg>
 #include <cstdio>
+#include <cstdlib>
+#include <cstring>
 
 #include "../../include/ditsep_b200.h"
 
@@ -112,6 +114,32 @@ __device__ __forceinline__ float silu_f(float x) {
 // Programmatic dependent launch, primary side: lets a dependent kernel launched with the programmatic-stream-
 // serialization attribute (the conv tile kernel) be scheduled as this grid's CTAs retire.  A no-op otherwise.
 __device__ __forceinline__ void griddep_launch_dependents() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
+
+// Secondary side: nothing below this call may run before the previous kernel in the stream has completed and its
+// writes are visible.  A no-op for a kernel launched without the attribute.
+__device__ __forceinline__ void griddep_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+
+// Host side: launch with programmatic stream serialization (the kernel must call griddep_wait() before it touches
+// global memory).  DITSEP_PDL=0 launches plainly.
+inline bool pdl_enabled() {
+  static const bool on = !(getenv("DITSEP_PDL") && strcmp(getenv("DITSEP_PDL"), "0") == 0);
+  return on;
+}
+template <typename... KArgs, typename... Args>
+inline cudaError_t launch_pdl(void (*kernel)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t st,
+                              Args&&... args) {
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  attr[0].val.programmaticStreamSerializationAllowed = 1;
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = grid;
+  cfg.blockDim = block;
+  cfg.dynamicSmemBytes = smem;
+  cfg.stream = st;
+  cfg.attrs = attr;
+  cfg.numAttrs = pdl_enabled() ? 1 : 0;
+  return cudaLaunchKernelEx(&cfg, kernel, static_cast<KArgs>(args)...);
+}
 
 // SiLU with ONE MUFU: x * sigmoid(x) = h + h * tanh(h), h = x / 2 (FMUL, MUFU.TANH, FFMA).  tanh.approx.f32 is good to
 // ~2^-11 relative, i.e. an absolute error of |h| * 5e-4 on the result: below bf16 rounding for positive outputs, up to a

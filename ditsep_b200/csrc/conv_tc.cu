@@ -72,9 +72,7 @@ struct ConvTcParams {
 // Programmatic dependent launch: the tile kernel may start while the kernel before it in the stream drains (that
 // kernel calls griddep_launch_dependents early).  Everything before griddep_wait() -- barrier init, TMEM allocation,
 // tensor-map prefetch, the resident filter preload (static data) -- overlaps that tail; no thread touches a tensor the
-// predecessor writes, or writes anything at all to global memory, before it.
-__device__ __forceinline__ void griddep_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
-
+// predecessor writes, or writes anything at all to global memory, before it (griddep_wait: common.cuh).
 __device__ __forceinline__ void trace_stamp(const ConvTcParams& p, uint32_t it, int slot) {
   if (p.trace && blockIdx.x < kTraceCtas && blockIdx.y == 0 && it < kTraceTiles)
     p.trace[((int64_t)blockIdx.x * kTraceTiles + it) * 16 + slot] = clock64();
@@ -195,6 +193,7 @@ __device__ __noinline__ void epilogue16_slow(const ConvTcParams& p, const uint32
 __global__ void __launch_bounds__(kThreads) conv_tc_kernel(const __grid_constant__ CUtensorMap mapA,
                                                            const __grid_constant__ CUtensorMap mapW,
                                                            const ConvTcParams p) {
+  griddep_launch_dependents();
   extern __shared__ uint8_t smem_raw[];
   __shared__ __align__(8) uint64_t bar_full[kMaxStages];
   __shared__ __align__(8) uint64_t bar_empty[kMaxStages];
@@ -232,6 +231,7 @@ __global__ void __launch_bounds__(kThreads) conv_tc_kernel(const __grid_constant
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem_acc = tmem_base_slot;
+  griddep_wait();  // launched with programmatic stream serialization: the set-up above overlaps the predecessor
 
   if (warp == 0) {
     if (lane == 0) {
@@ -1111,7 +1111,7 @@ extern "C" int ditsep_conv_tc_run_gn(const ditsep_conv_plan* plan, const float* 
                       (!residual || (res_dtype == DITSEP_BF16 && (ld_res & 7) == 0 &&
                                      (reinterpret_cast<uintptr_t>(residual) & 15) == 0));
     // launched with the programmatic-stream-serialization attribute (see griddep_wait); DITSEP_PDL=0 turns it off
-    static const bool pdl = !(getenv("DITSEP_PDL") && strcmp(getenv("DITSEP_PDL"), "0") == 0);
+    const bool pdl = pdl_enabled();
     cudaLaunchAttribute lattr[1];
     lattr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
     lattr[0].val.programmaticStreamSerializationAllowed = 1;
@@ -1144,6 +1144,6 @@ extern "C" int ditsep_conv_tc_run_gn(const ditsep_conv_plan* plan, const float* 
     return check_launch("conv_tc_tile_kernel");
   }
   dim3 grid((unsigned)((int64_t)p.tiles_x * p.tiles_y * p.tiles_b), (unsigned)p.n_tiles);
-  conv_tc_kernel<<<grid, kThreads, plan->smem, (cudaStream_t)stream>>>(plan->mapA, plan->mapW, p);
+  DITSEP_CUDA(launch_pdl(conv_tc_kernel, grid, dim3(kThreads), plan->smem, (cudaStream_t)stream, plan->mapA, plan->mapW, p));
   return check_launch("conv_tc_kernel");
 }

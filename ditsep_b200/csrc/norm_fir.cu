@@ -120,6 +120,8 @@ __global__ void __launch_bounds__(256) gn_finalize_srcs_kernel(const StatsSrcs s
                                                                const float* __restrict__ gamma,
                                                                const float* __restrict__ beta, float eps,
                                                                float* __restrict__ scale_shift) {
+  griddep_launch_dependents();
+  griddep_wait();
   extern __shared__ double sh[];  // [nj][nch][2]
   __shared__ double grp[32][2];
   const int b = blockIdx.y;
@@ -193,6 +195,7 @@ __global__ void __launch_bounds__(256) gn_apply_kernel(const T* __restrict__ x, 
                                                        const float* __restrict__ scale_shift, int silu,
                                                        T* __restrict__ y, int ld_y, int cv, int ppb) {
   griddep_launch_dependents();
+  griddep_wait();
   const int b = blockIdx.y;
   const int v = threadIdx.x % cv, pp = threadIdx.x / cv;
   if (pp >= ppb) return;
@@ -240,6 +243,7 @@ __global__ void __launch_bounds__(256) gn_small_kernel(const T* __restrict__ x, 
                                                        const float* __restrict__ gamma, const float* __restrict__ beta,
                                                        float eps, int silu, T* __restrict__ y, int ld_y) {
   griddep_launch_dependents();
+  griddep_wait();
   __shared__ float red[2][256 * 8];     // [sum | sum of squares][pixel lane][channel] (ppb * C = 2048 floats each)
   __shared__ double chan[2][256];
   __shared__ double grp[2][64];
@@ -886,8 +890,8 @@ extern "C" int ditsep_gn_finalize(const ditsep_stats_src* host_srcs, int n_srcs,
   if (gpc > 32) gpc = 32;
   const int threads = 256, nj = threads / (gpc * cpg) > 0 ? threads / (gpc * cpg) : 1;
   dim3 grid((unsigned)ceil_div(G, gpc), (unsigned)B);
-  gn_finalize_srcs_kernel<<<grid, threads, (size_t)(2 * nj * gpc * cpg) * sizeof(double), (cudaStream_t)stream>>>(
-      srcs, HW, C, G, gpc, gamma, beta, eps, scale_shift);
+  DITSEP_CUDA(launch_pdl(gn_finalize_srcs_kernel, grid, dim3(threads), (size_t)(2 * nj * gpc * cpg) * sizeof(double),
+                         (cudaStream_t)stream, srcs, HW, C, G, gpc, gamma, beta, eps, scale_shift));
   return check_launch("gn_finalize_srcs_kernel");
 }
 
@@ -900,9 +904,11 @@ extern "C" int ditsep_gn_small(const void* x, int dtype, int B, int64_t HW, int 
   DITSEP_REQUIRE(B > 0 && HW > 0 && HW <= 4096, "gn_small: meant for small images (HW=%lld)", (long long)HW);
   cudaStream_t st = (cudaStream_t)stream;
   if (dtype == DITSEP_F32)
-    gn_small_kernel<float><<<B, 256, 0, st>>>((const float*)x, HW, C, ld_x, G, gamma, beta, eps, silu, (float*)y, ld_y);
+    DITSEP_CUDA(launch_pdl(gn_small_kernel<float>, dim3(B), dim3(256), 0, st, (const float*)x, HW, C, ld_x, G, gamma, beta, eps,
+                           silu, (float*)y, ld_y));
   else if (dtype == DITSEP_BF16)
-    gn_small_kernel<bf16><<<B, 256, 0, st>>>((const bf16*)x, HW, C, ld_x, G, gamma, beta, eps, silu, (bf16*)y, ld_y);
+    DITSEP_CUDA(launch_pdl(gn_small_kernel<bf16>, dim3(B), dim3(256), 0, st, (const bf16*)x, HW, C, ld_x, G, gamma, beta, eps,
+                           silu, (bf16*)y, ld_y));
   else
     DITSEP_REQUIRE(false, "gn_small: unknown dtype %d", dtype);
   return check_launch("gn_small_kernel");
@@ -923,9 +929,11 @@ extern "C" int ditsep_gn_apply(const void* x, int dtype, int B, int64_t HW, int 
   dim3 grid((unsigned)gx, (unsigned)B);
   cudaStream_t st = (cudaStream_t)stream;
   if (dtype == DITSEP_F32)
-    gn_apply_kernel<float><<<grid, 256, 0, st>>>((const float*)x, HW, C, ld_x, scale_shift, silu, (float*)y, ld_y, cv, ppb);
+    DITSEP_CUDA(launch_pdl(gn_apply_kernel<float>, grid, dim3(256), 0, st, (const float*)x, HW, C, ld_x, scale_shift, silu,
+                           (float*)y, ld_y, cv, ppb));
   else if (dtype == DITSEP_BF16)
-    gn_apply_kernel<bf16><<<grid, 256, 0, st>>>((const bf16*)x, HW, C, ld_x, scale_shift, silu, (bf16*)y, ld_y, cv, ppb);
+    DITSEP_CUDA(launch_pdl(gn_apply_kernel<bf16>, grid, dim3(256), 0, st, (const bf16*)x, HW, C, ld_x, scale_shift, silu,
+                           (bf16*)y, ld_y, cv, ppb));
   else
     DITSEP_REQUIRE(false, "gn_apply: unknown dtype %d", dtype);
   return check_launch("gn_apply_kernel");
