@@ -23,6 +23,7 @@ __global__ void __launch_bounds__(256) attention_kernel(const T* __restrict__ q,
                                                         const T* __restrict__ v, int S, int ld, T* __restrict__ o,
                                                         int ld_o, float scale) {
   griddep_launch_dependents();
+  griddep_wait();
   constexpr int C = CPL * 32;
   extern __shared__ __align__(16) float sm[];
   float* Ks = sm;                                   // [kKTile][C + 1]
@@ -144,8 +145,8 @@ static int launch_attention(const void* q, const void* k, const void* v, int B, 
   size_t smem = (size_t)(kKTile * (C + 1) + kKTile * C + kQTile * C + kAttWarps * kQPerWarp * kKTile) * sizeof(float);
   DITSEP_CUDA(cudaFuncSetAttribute(attention_kernel<T, CPL>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   dim3 grid(ceil_div(S, kQTile), B);
-  attention_kernel<T, CPL><<<grid, 256, smem, st>>>((const T*)q, (const T*)k, (const T*)v, S, ld, (T*)o, ld_o,
-                                                    1.0f / sqrtf((float)C));
+  DITSEP_CUDA(launch_pdl<2>(attention_kernel<T, CPL>, dim3(grid), dim3(256), smem, st, (const T*)q, (const T*)k, (const T*)v, S, ld, (T*)o,
+                         ld_o, 1.0f / sqrtf((float)C)));
   return check_launch("attention_kernel");
 }
 

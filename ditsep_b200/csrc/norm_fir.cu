@@ -25,6 +25,8 @@ namespace ditsep {
 template <typename T>
 __global__ void __launch_bounds__(256) gn_partial_kernel(const T* __restrict__ x, int64_t HW, int C, int ld, int cv,
                                                          int ppb, float* __restrict__ partial) {
+  griddep_launch_dependents();
+  griddep_wait();
   extern __shared__ float red[];  // [ppb][C][2]
   const int b = blockIdx.y, split = blockIdx.x, nsplit = gridDim.x;
   const int v = threadIdx.x % cv, pp = threadIdx.x / cv;
@@ -386,6 +388,7 @@ __global__ void __launch_bounds__(256, DITSEP_FIR_MINB) fir_down_kernel(const T*
                                                           int ld_ox, T* __restrict__ out_h, int ld_oh, int seg_rows,
                                                           int n_seg, int64_t total) {
   griddep_launch_dependents();
+  griddep_wait();
   const int cv = C / 8, Ho = H / 2, Wo = W / 2;
   const int64_t idx = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
   if (idx >= total) return;
@@ -446,6 +449,7 @@ __global__ void __launch_bounds__(256) fir_up_kernel(const T* __restrict__ x, in
                                                      int ld_ox, T* __restrict__ out_h, int ld_oh, int seg_rows, int n_seg,
                                                      int64_t total) {
   griddep_launch_dependents();
+  griddep_wait();
   const int cv = C / 8, Ho = 2 * H, Wo = 2 * W;
   const int64_t idx = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
   if (idx >= total) return;
@@ -596,6 +600,8 @@ __global__ void __launch_bounds__(256) fir_narrow_kernel(const T* __restrict__ x
 template <int C>
 __global__ void __launch_bounds__(256) fir_narrow_px_kernel(const float* __restrict__ x, int H, int W, int ld_x, int up,
                                                             float* __restrict__ out, int ld_o, int64_t npix_out) {
+  griddep_launch_dependents();
+  griddep_wait();
   static_assert(C % 2 == 0, "float2 path");
   const int Ho = up ? 2 * H : H / 2, Wo = up ? 2 * W : W / 2;
   const float kd[4] = {0.125f, 0.375f, 0.375f, 0.125f};
@@ -841,9 +847,9 @@ static int launch_gn_partial(const void* x, int dtype, int B, int64_t HW, int C,
   dim3 grid(nsplit, B);
   size_t smem = (size_t)ppb * C * 2 * sizeof(float);
   if (dtype == DITSEP_F32)
-    gn_partial_kernel<float><<<grid, 256, smem, st>>>((const float*)x, HW, C, ld, cv, ppb, partial);
+    DITSEP_CUDA(launch_pdl<2>(gn_partial_kernel<float>, dim3(grid), dim3(256), smem, st, (const float*)x, HW, C, ld, cv, ppb, partial));
   else if (dtype == DITSEP_BF16)
-    gn_partial_kernel<bf16><<<grid, 256, smem, st>>>((const bf16*)x, HW, C, ld, cv, ppb, partial);
+    DITSEP_CUDA(launch_pdl<2>(gn_partial_kernel<bf16>, dim3(grid), dim3(256), smem, st, (const bf16*)x, HW, C, ld, cv, ppb, partial));
   else
     DITSEP_REQUIRE(false, "gn partial sums: unknown dtype %d", dtype);
   return check_launch("gn_partial_kernel");
@@ -950,9 +956,9 @@ static int fir_dispatch(const T* x, int B, int H, int W, int C, int ld_x, int up
       if ((C == 6 || C == 4 || C == 8) && ld_x % 2 == 0 && ld_ox % 2 == 0 && (reinterpret_cast<uintptr_t>(x) & 7) == 0 &&
           (reinterpret_cast<uintptr_t>(out_x) & 7) == 0) {
         const int64_t npix = total / C;
-        if (C == 6) fir_narrow_px_kernel<6><<<grid_for(npix), 256, 0, st>>>(x, H, W, ld_x, up, out_x, ld_ox, npix);
-        else if (C == 4) fir_narrow_px_kernel<4><<<grid_for(npix), 256, 0, st>>>(x, H, W, ld_x, up, out_x, ld_ox, npix);
-        else fir_narrow_px_kernel<8><<<grid_for(npix), 256, 0, st>>>(x, H, W, ld_x, up, out_x, ld_ox, npix);
+        if (C == 6) DITSEP_CUDA(launch_pdl<2>(fir_narrow_px_kernel<6>, dim3(grid_for(npix)), dim3(256), 0, st, x, H, W, ld_x, up, out_x, ld_ox, npix));
+        else if (C == 4) DITSEP_CUDA(launch_pdl<2>(fir_narrow_px_kernel<4>, dim3(grid_for(npix)), dim3(256), 0, st, x, H, W, ld_x, up, out_x, ld_ox, npix));
+        else DITSEP_CUDA(launch_pdl<2>(fir_narrow_px_kernel<8>, dim3(grid_for(npix)), dim3(256), 0, st, x, H, W, ld_x, up, out_x, ld_ox, npix));
         return check_launch("fir_narrow_px_kernel");
       }
     }
@@ -971,15 +977,15 @@ static int fir_dispatch(const T* x, int B, int H, int W, int C, int ld_x, int up
   const unsigned grid = (unsigned)((total + 255) / 256);
   if (up) {
     if (ss)
-      fir_up_kernel<T, true><<<grid, 256, 0, st>>>(x, H, W, C, ld_x, ss, out_x, ld_ox, out_h, ld_oh, seg_rows, n_seg, total);
+      DITSEP_CUDA(launch_pdl<2>(fir_up_kernel<T, true>, dim3(grid), dim3(256), 0, st, x, H, W, C, ld_x, ss, out_x, ld_ox, out_h, ld_oh, seg_rows, n_seg, total));
     else
-      fir_up_kernel<T, false><<<grid, 256, 0, st>>>(x, H, W, C, ld_x, ss, out_x, ld_ox, out_h, ld_oh, seg_rows, n_seg, total);
+      DITSEP_CUDA(launch_pdl<2>(fir_up_kernel<T, false>, dim3(grid), dim3(256), 0, st, x, H, W, C, ld_x, ss, out_x, ld_ox, out_h, ld_oh, seg_rows, n_seg, total));
     return check_launch("fir_up_kernel");
   }
   if (ss)
-    fir_down_kernel<T, true><<<grid, 256, 0, st>>>(x, H, W, C, ld_x, ss, out_x, ld_ox, out_h, ld_oh, seg_rows, n_seg, total);
+    DITSEP_CUDA(launch_pdl<2>(fir_down_kernel<T, true>, dim3(grid), dim3(256), 0, st, x, H, W, C, ld_x, ss, out_x, ld_ox, out_h, ld_oh, seg_rows, n_seg, total));
   else
-    fir_down_kernel<T, false><<<grid, 256, 0, st>>>(x, H, W, C, ld_x, ss, out_x, ld_ox, out_h, ld_oh, seg_rows, n_seg, total);
+    DITSEP_CUDA(launch_pdl<2>(fir_down_kernel<T, false>, dim3(grid), dim3(256), 0, st, x, H, W, C, ld_x, ss, out_x, ld_ox, out_h, ld_oh, seg_rows, n_seg, total));
   return check_launch("fir_down_kernel");
 }
 
