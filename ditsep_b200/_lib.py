@@ -36,12 +36,13 @@ SIGNATURES = {
     "ditsep_launch_count": (c_int64, []),
     "ditsep_note_launches": (None, [c_int64]),
     "ditsep_pc_corrector": (c_int, [C.POINTER(SdeParams), c_void_p, c_void_p, c_void_p, c_uint64, c_uint64, c_void_p,
-                                    c_void_p, c_int, c_int64, c_void_p]),
+                                    c_void_p, c_int, c_int64, c_void_p, c_void_p]),
     "ditsep_pc_predictor": (c_int, [C.POINTER(SdeParams), c_void_p, c_void_p, c_void_p, c_uint64, c_uint64, c_void_p,
-                                    c_void_p, c_void_p, c_int, c_int64, c_void_p]),
+                                    c_void_p, c_void_p, c_int, c_int64, c_void_p, c_void_p]),
     "ditsep_pc_prior": (c_int, [C.POINTER(SdeParams), c_void_p, c_void_p, c_uint64, c_uint64, c_void_p, c_int, c_int64,
-                                c_void_p]),
+                                c_void_p, c_void_p]),
     "ditsep_philox_normal": (c_int, [c_void_p, c_int64, c_uint64, c_uint64, c_void_p]),
+    "ditsep_box_muller": (c_int, [c_void_p, c_void_p, c_int64, c_void_p]),
     "ditsep_stft_compress": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_int64, c_int,
                                      c_float, c_float, c_int, c_void_p]),
     "ditsep_expand_istft": (c_int, [c_void_p, c_void_p, c_void_p, c_int, c_int, c_int64, c_int, c_float, c_float,

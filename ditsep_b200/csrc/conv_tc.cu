@@ -30,6 +30,7 @@
 //    independent of the batch size.
 //  * conv_tc_kernel (smaller images, where a 128-pixel tile spans several images): one TMA box
 //    per (tap, 64-channel block), one tile per CTA.
+#include <atomic>
 #include <cstdlib>
 #include <cstring>
 #include <type_traits>
@@ -1042,8 +1043,12 @@ extern "C" int ditsep_conv_tc_plan_create_sc(ditsep_conv_plan** plan, const void
       DITSEP_REQUIRE(false, "conv_tc: cuTensorMapEncodeTiled(shortcut input) failed with %d", (int)r);
     }
   }
-  static bool attr_set = false;
-  if (!attr_set) {
+  // cudaFuncAttributeMaxDynamicSharedMemorySize is a PER-DEVICE attribute: one flag per device ordinal
+  static std::atomic<bool> attr_set[64];
+  int attr_dev = 0;
+  DITSEP_CUDA(cudaGetDevice(&attr_dev));
+  const bool attr_known = attr_dev >= 0 && attr_dev < 64;
+  if (!attr_known || !attr_set[attr_dev].load(std::memory_order_acquire)) {
     DITSEP_CUDA(cudaFuncSetAttribute(conv_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                      1024 + 192 * 1024));
 #define DITSEP_TILE_ATTR(KS, RES, FAST)                                                                              \
@@ -1055,7 +1060,7 @@ extern "C" int ditsep_conv_tc_plan_create_sc(ditsep_conv_plan** plan, const void
     DITSEP_TILE_ATTR(1, false, false); DITSEP_TILE_ATTR(3, true, true); DITSEP_TILE_ATTR(3, true, false);
     DITSEP_TILE_ATTR(3, false, true); DITSEP_TILE_ATTR(3, false, false);
 #undef DITSEP_TILE_ATTR
-    attr_set = true;
+    if (attr_known) attr_set[attr_dev].store(true, std::memory_order_release);
   }
   *plan = pl;
   return 0;

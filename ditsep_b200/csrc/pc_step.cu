@@ -39,19 +39,25 @@ __device__ __forceinline__ uint4 philox4x32_10(uint4 ctr, uint2 key) {
   return ctr;
 }
 
-// 4 standard normals for state elements [4q, 4q+4) of draw `draw` (Box-Muller on 4 uniforms).
-__device__ __forceinline__ float4 philox_normal4(uint64_t q, uint64_t seed, uint64_t draw) {
-  uint4 r = philox4x32_10(make_uint4((uint32_t)q, (uint32_t)(q >> 32), (uint32_t)draw, (uint32_t)(draw >> 32)),
-                          make_uint2((uint32_t)seed, (uint32_t)(seed >> 32)));
+// Box-Muller on 4 uniform 32-bit words -> 4 standard normals.
+__device__ __forceinline__ float4 box_muller4(uint4 r) {
   const float k = 2.3283064365386963e-10f;  // 2^-32
   float u0 = ((float)r.x + 0.5f) * k, u1 = ((float)r.y + 0.5f) * k;
   float u2 = ((float)r.z + 0.5f) * k, u3 = ((float)r.w + 0.5f) * k;
-  // u in (0, 1]: (x + 0.5) * 2^-32 can round to 1.0f, never to 0.
-  float r0 = sqrtf(-2.0f * __logf(u0)), r1 = sqrtf(-2.0f * __logf(u2));
+  // u in (0, 1]: (x + 0.5) * 2^-32 can round to 1.0f, never to 0.  __logf is only specified to an ABSOLUTE error
+  // near 1 (2^-21.41 on [0.5, 2]), so it may return a tiny positive value for u = 1 - 2^-24: clamp, or the
+  // square root is NaN and poisons the whole mixture.
+  float r0 = sqrtf(fmaxf(0.0f, -2.0f * __logf(u0))), r1 = sqrtf(fmaxf(0.0f, -2.0f * __logf(u2)));
   float s0, c0, s1, c1;
   __sincosf(6.283185307179586f * u1, &s0, &c0);
   __sincosf(6.283185307179586f * u3, &s1, &c1);
   return make_float4(r0 * c0, r0 * s0, r1 * c1, r1 * s1);
+}
+
+// 4 standard normals for state elements [4q, 4q+4) of draw `draw`.
+__device__ __forceinline__ float4 philox_normal4(uint64_t q, uint64_t seed, uint64_t draw) {
+  return box_muller4(philox4x32_10(make_uint4((uint32_t)q, (uint32_t)(q >> 32), (uint32_t)draw, (uint32_t)(draw >> 32)),
+                                   make_uint2((uint32_t)seed, (uint32_t)(seed >> 32))));
 }
 
 // ---- per-mixture coefficients ----------------------------------------------------------
@@ -122,8 +128,11 @@ __global__ void __launch_bounds__(256) pc_update_kernel(ditsep_sde_params p, int
                                                         const float* __restrict__ noise, uint64_t seed,
                                                         uint64_t draw, const float* __restrict__ t,
                                                         const float* __restrict__ y, float* __restrict__ x_mean,
-                                                        int64_t L) {
+                                                        int64_t L, const int* __restrict__ lengths) {
   const int b = blockIdx.y;
+  // ragged batches: row b is a zero-padded signal of lengths[b] <= L samples; its state is kept at exactly zero past
+  // its end, so the STFT of the next score evaluation sees the same frames as a batch-1 run of that mixture alone
+  const int64_t len = lengths ? (int64_t)lengths[b] : L;
   const float tb = (mode == kPrior) ? 1.0f : t[b];
   const Coef c = make_coef(p, mode, tb);
   const int64_t nvec = (L + 3) / 4;
@@ -186,11 +195,12 @@ __global__ void __launch_bounds__(256) pc_update_kernel(ditsep_sde_params p, int
         zb += zv[i][j];
       }
       xb *= inv_n; sb *= inv_n; zb *= inv_n;
+      const bool live = l0 + j < len;
 #pragma unroll
       for (int i = 0; i < NS; ++i) {
         float m = c.a0 * xv[i][j] + c.a1 * xb + c.a2 * sv[i][j] + c.a3 * sb + c.a4 * yv[j];
-        xm[i][j] = m;
-        xo[i][j] = m + c.b0 * zv[i][j] + c.b1 * zb;
+        xm[i][j] = live ? m : 0.f;
+        xo[i][j] = live ? m + c.b0 * zv[i][j] + c.b1 * zb : 0.f;
       }
     }
 #pragma unroll
@@ -213,7 +223,7 @@ __global__ void __launch_bounds__(256) pc_update_kernel(ditsep_sde_params p, int
 
 static int launch_pc(const ditsep_sde_params* hp, int mode, float* x, const float* score, const float* noise,
                      uint64_t seed, uint64_t draw, const float* t, const float* y, float* x_mean, int B, int64_t L,
-                     void* stream) {
+                     const int* lengths, void* stream) {
   DITSEP_REQUIRE(hp != nullptr && x != nullptr, "pc_step: null params or state");
   DITSEP_REQUIRE(hp->n_src >= 1 && hp->n_src <= kMaxSrc, "pc_step: n_src=%d unsupported (1..%d)", hp->n_src, kMaxSrc);
   DITSEP_REQUIRE(hp->sde == DITSEP_SDE_MIX || hp->sde == DITSEP_SDE_OUVE, "pc_step: unknown sde %d", hp->sde);
@@ -232,10 +242,10 @@ static int launch_pc(const ditsep_sde_params* hp, int mode, float* x, const floa
   cudaStream_t st = (cudaStream_t)stream;
   const float* yy = (hp->sde == DITSEP_SDE_MIX && mode != kPrior) ? nullptr : y;
   switch (hp->n_src) {
-    case 1: pc_update_kernel<1><<<grid, block, 0, st>>>(*hp, mode, x, score, noise, seed, draw, t, yy, x_mean, L); break;
-    case 2: pc_update_kernel<2><<<grid, block, 0, st>>>(*hp, mode, x, score, noise, seed, draw, t, yy, x_mean, L); break;
-    case 3: pc_update_kernel<3><<<grid, block, 0, st>>>(*hp, mode, x, score, noise, seed, draw, t, yy, x_mean, L); break;
-    default: pc_update_kernel<4><<<grid, block, 0, st>>>(*hp, mode, x, score, noise, seed, draw, t, yy, x_mean, L); break;
+    case 1: pc_update_kernel<1><<<grid, block, 0, st>>>(*hp, mode, x, score, noise, seed, draw, t, yy, x_mean, L, lengths); break;
+    case 2: pc_update_kernel<2><<<grid, block, 0, st>>>(*hp, mode, x, score, noise, seed, draw, t, yy, x_mean, L, lengths); break;
+    case 3: pc_update_kernel<3><<<grid, block, 0, st>>>(*hp, mode, x, score, noise, seed, draw, t, yy, x_mean, L, lengths); break;
+    default: pc_update_kernel<4><<<grid, block, 0, st>>>(*hp, mode, x, score, noise, seed, draw, t, yy, x_mean, L, lengths); break;
   }
   return check_launch("pc_update_kernel");
 }
@@ -250,25 +260,32 @@ __global__ void philox_normal_kernel(float* out, int64_t n, uint64_t seed, uint6
   }
 }
 
+__global__ void box_muller_kernel(const uint32_t* bits, float* out, int64_t nvec) {
+  for (int64_t q = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; q < nvec; q += (int64_t)gridDim.x * blockDim.x) {
+    const uint4 r = *reinterpret_cast<const uint4*>(bits + 4 * q);
+    *reinterpret_cast<float4*>(out + 4 * q) = box_muller4(r);
+  }
+}
+
 }  // namespace ditsep
 
 using namespace ditsep;
 
 extern "C" int ditsep_pc_corrector(const ditsep_sde_params* host_p, float* x, const float* score, const float* noise,
                                    uint64_t seed, uint64_t draw, const float* t, float* x_mean, int B, int64_t L,
-                                   void* stream) {
-  return launch_pc(host_p, kCorrector, x, score, noise, seed, draw, t, nullptr, x_mean, B, L, stream);
+                                   const int* lengths, void* stream) {
+  return launch_pc(host_p, kCorrector, x, score, noise, seed, draw, t, nullptr, x_mean, B, L, lengths, stream);
 }
 
 extern "C" int ditsep_pc_predictor(const ditsep_sde_params* host_p, float* x, const float* score, const float* noise,
                                    uint64_t seed, uint64_t draw, const float* t, const float* y, float* x_mean, int B,
-                                   int64_t L, void* stream) {
-  return launch_pc(host_p, kPredictor, x, score, noise, seed, draw, t, y, x_mean, B, L, stream);
+                                   int64_t L, const int* lengths, void* stream) {
+  return launch_pc(host_p, kPredictor, x, score, noise, seed, draw, t, y, x_mean, B, L, lengths, stream);
 }
 
 extern "C" int ditsep_pc_prior(const ditsep_sde_params* host_p, float* x, const float* noise, uint64_t seed,
-                               uint64_t draw, const float* y, int B, int64_t L, void* stream) {
-  return launch_pc(host_p, kPrior, x, nullptr, noise, seed, draw, nullptr, y, nullptr, B, L, stream);
+                               uint64_t draw, const float* y, int B, int64_t L, const int* lengths, void* stream) {
+  return launch_pc(host_p, kPrior, x, nullptr, noise, seed, draw, nullptr, y, nullptr, B, L, lengths, stream);
 }
 
 extern "C" int ditsep_philox_normal(float* out, int64_t n, uint64_t seed, uint64_t draw, void* stream) {
@@ -278,4 +295,15 @@ extern "C" int ditsep_philox_normal(float* out, int64_t n, uint64_t seed, uint64
   if (grid > kNumSMs * 8) grid = kNumSMs * 8;
   philox_normal_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>(out, n, seed, draw);
   return check_launch("philox_normal_kernel");
+}
+
+extern "C" int ditsep_box_muller(const uint32_t* bits, float* out, int64_t n, void* stream) {
+  DITSEP_REQUIRE(bits && out && n > 0 && n % 4 == 0, "box_muller: n=%lld must be a positive multiple of 4", (long long)n);
+  DITSEP_REQUIRE(((reinterpret_cast<uintptr_t>(bits) | reinterpret_cast<uintptr_t>(out)) & 15) == 0,
+                 "box_muller: 16-byte alignment required");
+  const int64_t nvec = n / 4;
+  int grid = (int)((nvec + 255) / 256);
+  if (grid > kNumSMs * 8) grid = kNumSMs * 8;
+  box_muller_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>(bits, out, nvec);
+  return check_launch("box_muller_kernel");
 }

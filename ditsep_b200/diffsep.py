@@ -114,7 +114,12 @@ class DiffSepModel(_Base):
             samples, ns, intmet = [], [], []
             for i in range(int(math.ceil(M / minibatch))):
                 y_mini = y[i * minibatch:(i + 1) * minibatch]
-                sampler = factory(predictor_name, corrector_name, sde=sde, score_fn=self, y=y_mini, **kwargs)
+                kw_i = dict(kwargs)
+                if kw_i.get("seed") is not None:  # an explicit seed must not give every minibatch the same stream
+                    kw_i["seed"] = int(kw_i["seed"]) + 7919 * i
+                if kw_i.get("lengths") is not None:
+                    kw_i["lengths"] = kw_i["lengths"][i * minibatch:(i + 1) * minibatch]
+                sampler = factory(predictor_name, corrector_name, sde=sde, score_fn=self, y=y_mini, **kw_i)
                 sample, n, *other = sampler()
                 samples.append(sample)
                 ns.append(n)

@@ -238,8 +238,7 @@ class NcsnppEngine:
         """feat: (B, H, W, Cin) fp32 NHWC, with NCSN++'s ``2x-1`` (ncsnpp.py:348-350) already
         applied unless the model is ``centered``.  Returns the plan's output buffer
         (B, H, W, Cout) fp32 -- valid until the next call."""
-        if not feat.is_cuda and not ops.EMULATED:
-            raise ops.DitsepError("NCSNpp runs on sm_100a only; there is no CPU fallback")
+        ops.require_device(feat, "NCSNpp")
         if not affine_done and not self.m.centered:
             feat = 2 * feat - 1.0
         B, H, W, C = feat.shape
@@ -326,7 +325,7 @@ class _Plan:
         k = 0
         cur = skip_slot(k)
         hilo = w.get("conv3_hilo")
-        if hilo is not None and adt == torch.bfloat16 and not ops.EMULATED and ops.tc_enabled():
+        if hilo is not None and adt == torch.bfloat16 and ops.tc_enabled():
             # first layer on the tensor cores: 6 fp32 channels widened to [hi | lo | hi | 0] bf16 (ops.split_hilo);
             # channels >= 3*Cin0 are zeroed once here and never written again
             self.feat_tc = torch.zeros(B, H, W, hilo.cin, device=device, dtype=torch.bfloat16)
@@ -437,7 +436,7 @@ class _Plan:
         """3x3 / 1x1 conv with the fused epilogue; tcgen05 path when the shape allows it.  want_stats:
         GroupNorm will normalise `out` (alone or as part of a concat buffer) -- its per-channel sums come
         from the conv epilogue when the kernel can leave them, else from one explicit pass over `out`."""
-        use_tc = (cw.w_bf16 is not None and x.dtype == torch.bfloat16 and not ops.EMULATED and ops.tc_enabled())
+        use_tc = (cw.w_bf16 is not None and x.dtype == torch.bfloat16 and ops.tc_enabled())
         kw = {"bias_b": bias_b, "residual": residual, "out_scale": out_scale}
         plan = None
         if shortcut is not None:
@@ -608,7 +607,7 @@ class _Plan:
         eager pass it is captured into a CUDA graph and replayed: ~430 launches per evaluation become one
         graph launch (at batch 1 the host launch path, not the GPU, bounds an eager step).
         DITSEP_GRAPH=0 keeps it eager (debugging, per-launch timing)."""
-        if ops.EMULATED or os.environ.get("DITSEP_GRAPH", "1") == "0":
+        if not ops.graphs_enabled():
             return self.run_eager()
         if self._graph is None:
             if self._runs == 0:  # first call: plain launches (loads modules, surfaces launch errors eagerly)

@@ -19,14 +19,22 @@ from ._lib import DitsepError, SdeParams, check  # noqa: F401  (re-exported)
 
 F32, BF16 = 0, 1
 NUM_SMS = 148
-# Set only by tests/emu_ops.py, which swaps these wrappers for torch restatements so the host
-# logic (launch plans, buffer aliasing, sampler loop) can be checked on a CPU-only box.
-EMULATED = False
 
 
 def tc_enabled() -> bool:
     """tcgen05 convolution path on (default) unless DITSEP_DISABLE_TC=1 (debug aid)."""
     return os.environ.get("DITSEP_DISABLE_TC", "0") != "1"
+
+
+def graphs_enabled() -> bool:
+    """CUDA-graph replay of a launch plan (default) unless DITSEP_GRAPH=0 (debugging, per-launch timing)."""
+    return os.environ.get("DITSEP_GRAPH", "1") != "0"
+
+
+def require_device(t: torch.Tensor, what: str):
+    """The product path runs on sm_100a only: a CPU tensor is an error, never a fallback."""
+    if not t.is_cuda:
+        raise _lib.DitsepError(f"{what} runs on sm_100a only; there is no CPU fallback")
 
 _DT = {torch.float32: F32, torch.bfloat16: BF16}
 
@@ -89,37 +97,56 @@ def _state_dims(x: torch.Tensor, p: SdeParams) -> Tuple[int, int]:
     return B, L
 
 
-def pc_corrector(p: SdeParams, x, score, t, noise=None, seed=0, draw=0, x_mean=None):
+def _lengths(lengths, B: int):
+    if lengths is None:
+        return None
+    if lengths.dtype != torch.int32 or not lengths.is_contiguous() or lengths.numel() != B:
+        raise _lib.DitsepError("lengths must be a contiguous int32 tensor of B elements")
+    _cuda(lengths)
+    return lengths.data_ptr()
+
+
+def pc_corrector(p: SdeParams, x, score, t, noise=None, seed=0, draw=0, x_mean=None, lengths=None):
+    """lengths: optional (B,) int32 valid sample counts of a ragged batch (state kept at 0 past them)."""
     _cuda(x, score, t, noise, x_mean)
     for n, v in (("x", x), ("score", score), ("t", t), ("noise", noise), ("x_mean", x_mean)):
         _f32c(v, n)
     B, L = _state_dims(x, p)
     check(_lib.load().ditsep_pc_corrector(C.byref(p), _ptr(x), _ptr(score), _ptr(noise), seed, draw, _ptr(t),
-                                          _ptr(x_mean), B, L, _stream()), "pc_corrector")
+                                          _ptr(x_mean), B, L, _lengths(lengths, B), _stream()), "pc_corrector")
 
 
-def pc_predictor(p: SdeParams, x, score, t, y, noise=None, seed=0, draw=0, x_mean=None):
+def pc_predictor(p: SdeParams, x, score, t, y, noise=None, seed=0, draw=0, x_mean=None, lengths=None):
     _cuda(x, score, t, y, noise, x_mean)
     for n, v in (("x", x), ("score", score), ("t", t), ("y", y), ("noise", noise), ("x_mean", x_mean)):
         _f32c(v, n)
     B, L = _state_dims(x, p)
     check(_lib.load().ditsep_pc_predictor(C.byref(p), _ptr(x), _ptr(score), _ptr(noise), seed, draw, _ptr(t), _ptr(y),
-                                          _ptr(x_mean), B, L, _stream()), "pc_predictor")
+                                          _ptr(x_mean), B, L, _lengths(lengths, B), _stream()), "pc_predictor")
 
 
-def pc_prior(p: SdeParams, x, y, noise=None, seed=0, draw=0):
+def pc_prior(p: SdeParams, x, y, noise=None, seed=0, draw=0, lengths=None):
     _cuda(x, y, noise)
     for n, v in (("x", x), ("y", y), ("noise", noise)):
         _f32c(v, n)
     B, L = _state_dims(x, p)
-    check(_lib.load().ditsep_pc_prior(C.byref(p), _ptr(x), _ptr(noise), seed, draw, _ptr(y), B, L, _stream()),
-          "pc_prior")
+    check(_lib.load().ditsep_pc_prior(C.byref(p), _ptr(x), _ptr(noise), seed, draw, _ptr(y), B, L,
+                                      _lengths(lengths, B), _stream()), "pc_prior")
 
 
 def philox_normal(out: torch.Tensor, seed: int, draw: int):
     _cuda(out)
     _f32c(out, "out")
     check(_lib.load().ditsep_philox_normal(_ptr(out), out.numel(), seed, draw, _stream()), "philox_normal")
+
+
+def box_muller(bits: torch.Tensor, out: torch.Tensor):
+    """The Philox stream's uniform -> normal transform on caller-supplied words (int32 view of 32-bit patterns)."""
+    _cuda(bits, out)
+    _f32c(out, "out")
+    if bits.dtype != torch.int32 or not bits.is_contiguous() or bits.numel() != out.numel():
+        raise _lib.DitsepError("box_muller: bits must be a contiguous int32 tensor of out's size")
+    check(_lib.load().ditsep_box_muller(_ptr(bits), _ptr(out), out.numel(), _stream()), "box_muller")
 
 
 # ------------------------------------------------------------------ spectral

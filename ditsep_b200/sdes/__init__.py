@@ -26,17 +26,20 @@ __all__ = ["PredictorRegistry", "CorrectorRegistry", "SDERegistry", "Predictor",
 
 def get_pc_sampler(predictor_name, corrector_name, sde, score_fn, y, true_mean=None, denoise=True, eps=3e-2, snr=0.1,
                    corrector_steps=1, probability_flow: bool = False, intermediate=False, n_spkrs=2, noise_tape=None,
-                   seed=None, **kwargs):
-    """Create a Predictor-Corrector sampler (sdes/__init__.py:133-193)."""
+                   seed=None, lengths=None, **kwargs):
+    """Create a Predictor-Corrector sampler (sdes/__init__.py:133-193).  ``lengths``: optional (B,) valid sample
+    counts when ``y`` is a batch of zero-padded mixtures of different lengths (utils/shard.py)."""
     predictor_cls = PredictorRegistry.get_by_name(predictor_name)
     corrector_cls = CorrectorRegistry.get_by_name(corrector_name)
-    noise = NoiseSource(tape=noise_tape, seed=seed)
+    if lengths is not None:
+        lengths = torch.as_tensor(lengths, dtype=torch.int32).to(y.device).contiguous()
+    noise = NoiseSource(tape=noise_tape, seed=seed, lengths=lengths)
     predictor = predictor_cls(sde, score_fn, probability_flow=probability_flow, noise=noise)
     corrector = corrector_cls(sde, score_fn, snr=snr, n_steps=corrector_steps, noise=noise)
 
     def pc_sampler():
         im = [] if intermediate else None
-        noise.reset()
+        noise.begin_run()
         with torch.no_grad():
             shape = torch.Size((y.shape[0], n_spkrs, *y.shape[2:]))
             cond = true_mean if true_mean is not None else y

@@ -53,8 +53,10 @@ class _FusedLangevin(Corrector):
         for _ in range(self.n_steps):
             score = self.score_fn(x_out, t, *args)
             x_mean = torch.empty_like(x_out) if _want_mean else None
-            z, seed, draw = self._noise().next(x_out)
-            ops.pc_corrector(p, x_out, score.contiguous(), t.contiguous(), noise=z, seed=seed, draw=draw, x_mean=x_mean)
+            src = self._noise()
+            z, seed, draw = src.next(x_out)
+            ops.pc_corrector(p, x_out, score.contiguous(), t.contiguous(), noise=z, seed=seed, draw=draw, x_mean=x_mean,
+                             lengths=src.lengths)
         return x_out, x_mean
 
 

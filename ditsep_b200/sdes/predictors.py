@@ -59,9 +59,10 @@ class ReverseDiffusionPredictor(Predictor):
         p = self.sde.fused_params(n_src=x.shape[1])
         x_out = x if _inplace else x.clone()
         x_mean = torch.empty_like(x_out) if _want_mean else None
-        z, seed, draw = self._noise().next(x_out)
+        src = self._noise()
+        z, seed, draw = src.next(x_out)
         ops.pc_predictor(p, x_out, score.contiguous(), t.contiguous(), None if y is None else y.contiguous(), noise=z,
-                         seed=seed, draw=draw, x_mean=x_mean)
+                         seed=seed, draw=draw, x_mean=x_mean, lengths=src.lengths)
         return x_out, x_mean
 
 

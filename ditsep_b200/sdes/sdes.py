@@ -50,15 +50,23 @@ class NoiseSource:
     and predictor alternately); ``count`` numbers them in that order.
     """
 
-    def __init__(self, tape=None, seed=None):
+    def __init__(self, tape=None, seed=None, lengths=None):
         self.tape = tape
         if seed is None and tape is None:
             seed = int(torch.randint(0, 2 ** 62, (1,)).item())
         self.seed = 0 if seed is None else int(seed)
         self.count = 0
+        # ragged batch: (B,) int32 valid sample counts; the fused updates keep the state at 0 past them
+        self.lengths = lengths
 
-    def reset(self):
-        self.count = 0
+    def begin_run(self):
+        """Start of one sampler invocation.  A tape is replayed from draw 0 (parity runs number the draws per run);
+        the Philox stream is NOT rewound: like the reference's global generator, a second call of the same sampler
+        closure continues the stream and returns a fresh sample."""
+        if self.tape is not None:
+            self.count = 0
+
+    reset = begin_run
 
     def next(self, like: torch.Tensor):
         """Returns (noise tensor or None, seed, draw index)."""
@@ -246,7 +254,7 @@ class MixSDE(SDE):
         noise = NoiseSource() if noise is None else noise
         x = torch.empty((y.shape[0], 2, y.shape[2]), device=y.device, dtype=torch.float32)
         z, seed, draw = noise.next(x)
-        ops.pc_prior(self.fused_params(n_src=2), x, y.contiguous(), noise=z, seed=seed, draw=draw)
+        ops.pc_prior(self.fused_params(n_src=2), x, y.contiguous(), noise=z, seed=seed, draw=draw, lengths=noise.lengths)
         return x
 
     def prior_logp(self, z):
@@ -300,7 +308,8 @@ class OUVESDE(SDE):
         noise = NoiseSource() if noise is None else noise
         x = torch.empty(tuple(shape), device=y.device, dtype=torch.float32)
         z, seed, draw = noise.next(x)
-        ops.pc_prior(self.fused_params(n_src=shape[1]), x, y.contiguous(), noise=z, seed=seed, draw=draw)
+        ops.pc_prior(self.fused_params(n_src=shape[1]), x, y.contiguous(), noise=z, seed=seed, draw=draw,
+                     lengths=noise.lengths)
         return x
 
     def prior_logp(self, z):

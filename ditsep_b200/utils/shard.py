@@ -95,19 +95,57 @@ def gather_rows(rows: torch.Tensor, group=None) -> torch.Tensor:
     return out[torch.argsort(out[:, 0])]
 
 
+def ragged_tape(tape_for_mixture, indices: Sequence[int], lens: Sequence[int]):
+    """Noise tape of a ragged batch built from per-mixture tapes (parity runs): draw i of the batch is the stack of
+    every mixture's own draw i at its OWN length, zero-padded to the batch length -- so a mixture consumes the same
+    noise whether it runs alone or inside any batch.  tape_for_mixture(idx) -> callable (i, shape) -> tensor."""
+    tapes = [tape_for_mixture(i) for i in indices]
+
+    def tape(i, like):
+        z = torch.zeros(like.shape, dtype=torch.float32)
+        for r, (tp, n) in enumerate(zip(tapes, lens)):
+            z[r, :, :n] = tp(i, (1, like.shape[1], n))[0]
+        return z
+
+    return tape
+
+
+def normalize_ragged(mixtures: Sequence[torch.Tensor], batch: Sequence[int], device=None):
+    """Zero-padded (B, 1, T_max) batch of the mixtures `batch`, each standardised over ITS OWN samples (mean, unbiased
+    std clamped at 1e-5: src/utils/separate.py:56-62 applied per mixture as the reference's batch-1 evaluation does,
+    src/evaluate_mp.py:289,311); the padding stays exactly zero.  Returns (y, lengths int32 (B,), mean (B,1,1), std)."""
+    lens = [int(mixtures[i].shape[-1]) for i in batch]
+    t_run = max(lens)
+    y = torch.zeros(len(batch), 1, t_run)
+    mean, std = torch.zeros(len(batch), 1, 1), torch.ones(len(batch), 1, 1)
+    for r, i in enumerate(batch):
+        m = mixtures[i].reshape(-1).float().cpu()
+        mean[r], std[r] = m.mean(), m.std().clamp(min=1e-5)
+        y[r, 0, :lens[r]] = (m - mean[r, 0, 0]) / std[r, 0, 0]
+    lengths = torch.tensor(lens, dtype=torch.int32)
+    if device is not None:
+        y, lengths, mean, std = y.to(device), lengths.to(device), mean.to(device), std.to(device)
+    return y, lengths, mean, std
+
+
 def separate_sharded(model, mixtures: Sequence[torch.Tensor], references=None, max_batch: int = 32, device=None,
                      sampler_kwargs=None, seed: int = 0, rank: int = None, world_size: int = None,
-                     noise_tape_factory=None):
+                     noise_tape_factory=None, predictor: str = "reverse_diffusion", corrector: str = "ald2"):
     """Sweep over independent mixtures, batch-sharded over the ranks of the default process group.
 
     mixtures: list of (1, T_i) tensors (any lengths); references: optional list of (n_src, T_i).
     Every rank runs `model.get_pc_sampler` on its own length-bucketed batches (no collective inside), then the
     rows [idx, n_samples, si_sdr_0..n-1] are gathered once.  Returns (rows (n_total, 2 + n_src) on every rank,
-    {idx: separated (n_src, T_i)} for this rank's mixtures).  The Philox seed of a batch is derived from the global
-    index of its first mixture; with max_batch=1 the result is therefore independent of the world size
-    (tests/test_sharding_gloo.py), with larger batches it depends on the batch composition only through the noise."""
-    from . import denormalize_batch, normalize_batch
+    {idx: separated (n_src, T_i)} for this rank's mixtures).
 
+    Mixtures of one bucket (same padded STFT frame count) share a batch although their lengths differ by up to 8191
+    samples: each is standardised over its own samples, zero-padded, and the sampler is told the valid lengths
+    (`lengths=`), which keeps the state at zero past each mixture's end.  In exact arithmetic every mixture then sees
+    the frames, the GroupNorm statistics and the score of a batch-1 run of itself -- the reference's evaluation
+    (src/evaluate_mp.py:289,311); with a per-mixture noise tape (`ragged_tape`) the results are independent of
+    max_batch and of the world size (tests/test_sharding_gloo.py, tests/test_gpu_parity.py).
+    noise_tape_factory(idx) -> callable (i, shape) -> tensor: the tape of mixture idx (parity runs); default:
+    in-kernel Philox keyed by the global index of the batch's first mixture."""
     if world_size is None:
         world_size = dist.get_world_size() if dist.is_available() and dist.is_initialized() else 1
     if rank is None:
@@ -115,21 +153,16 @@ def separate_sharded(model, mixtures: Sequence[torch.Tensor], references=None, m
     kw = {"N": 30, "snr": 0.5, "corrector_steps": 1, "denoise": True}
     kw.update(sampler_kwargs or {})
     lengths = [int(m.shape[-1]) for m in mixtures]
-    n_src = int(getattr(model.sde, "ndim", 2))
+    n_src = int(kw.get("n_spkrs", getattr(model.sde, "ndim", 2)))
     rows, outs = [], {}
     for batch in batches_for_rank(lengths, world_size, rank, max_batch):
-        t_run = max(lengths[i] for i in batch)  # the longest length of the batch; shorter mixtures are zero-padded
-        y = torch.zeros(len(batch), 1, t_run)
-        for r, i in enumerate(batch):
-            y[r, 0, :lengths[i]] = mixtures[i].reshape(-1)
-        if device is not None:
-            y = y.to(device)
-        (yn, _), mean, std = normalize_batch((y, None))
-        noise = ({"noise_tape": noise_tape_factory(batch[0])} if noise_tape_factory is not None
-                 else {"seed": seed + 7919 * batch[0]})  # taped noise (parity runs) or in-kernel Philox
-        sampler = model.get_pc_sampler("reverse_diffusion", "ald2", yn, **noise, **kw)
+        yn, lens, mean, std = normalize_ragged(mixtures, batch, device)
+        noise = ({"noise_tape": ragged_tape(noise_tape_factory, batch, [lengths[i] for i in batch])}
+                 if noise_tape_factory is not None else {"seed": seed + 7919 * batch[0]})
+        ragged = len(set(lengths[i] for i in batch)) > 1
+        sampler = model.get_pc_sampler(predictor, corrector, yn, lengths=lens if ragged else None, **noise, **kw)
         x, _ = sampler()
-        x = denormalize_batch(x, mean, std)
+        x = x * std + mean
         for r, i in enumerate(batch):
             est = x[r, :, :lengths[i]]
             outs[i] = est

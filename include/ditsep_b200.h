@@ -56,22 +56,29 @@ void ditsep_note_launches(int64_t n);
  * noise: (B, n_src, L) tape draw, or NULL -> in-register Philox4x32-10 normals keyed by
  * (seed, draw): element e of the state uses counter (e/4, draw) lane e%4.
  * x is updated in place; x_mean (nullable) receives the noise-free update.
+ * lengths (nullable, (B,) int32): ragged batch -- row b is a zero-padded signal of lengths[b] <= L samples; x and
+ * x_mean are written as exactly 0 past it, so each mixture's STFT frames (and with them its score, GroupNorm
+ * statistics included) equal those of a batch-1 run of that mixture (the reference evaluates at batch 1,
+ * src/evaluate_mp.py:289,311).
  */
 /* AnnealedLangevinDynamics2.update_fn (mix, src/sdes/correctors.py:102-121) or
  * AnnealedLangevinDynamics.update_fn (ouve, correctors.py:70-84), one step. */
 int ditsep_pc_corrector(const ditsep_sde_params* host_p, float* x, const float* score, const float* noise,
                         uint64_t seed, uint64_t draw, const float* t, float* x_mean, int B, int64_t L,
-                        void* stream);
+                        const int* lengths, void* stream);
 /* ReverseDiffusionPredictor.update_fn (src/sdes/predictors.py:60-66) with
  * SDE.discretize / RSDE.discretize (src/sdes/sdes.py:94-108,165-173). */
 int ditsep_pc_predictor(const ditsep_sde_params* host_p, float* x, const float* score, const float* noise,
                         uint64_t seed, uint64_t draw, const float* t, const float* y, float* x_mean, int B,
-                        int64_t L, void* stream);
+                        int64_t L, const int* lengths, void* stream);
 /* MixSDE.prior_sampling (sdes.py:336-348, n_src must be 2) / OUVESDE.prior_sampling (:687-695). */
 int ditsep_pc_prior(const ditsep_sde_params* host_p, float* x, const float* noise, uint64_t seed, uint64_t draw,
-                    const float* y, int B, int64_t L, void* stream);
+                    const float* y, int B, int64_t L, const int* lengths, void* stream);
 /* Standard normals from the same Philox stream as above (tests / statistics). */
 int ditsep_philox_normal(float* out, int64_t n, uint64_t seed, uint64_t draw, void* stream);
+/* The uniform -> normal transform of that stream on caller-supplied 32-bit words (n % 4 == 0; word 4q, 4q+2 give
+ * the radii, 4q+1, 4q+3 the angles): lets a test feed the endpoint uniforms (0, 0xFFFFFFFF) and check for NaN. */
+int ditsep_box_muller(const uint32_t* bits, float* out, int64_t n, void* stream);
 
 /* ---- STFT + compression / expansion + iSTFT --------------------------------------
  * ScoreModelNCSNpp.pre_process (src/models/diffsep/score_models.py:107-116):

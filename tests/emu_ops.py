@@ -58,7 +58,7 @@ def _coef(p, mode, t):
     return c
 
 
-def _pc(p, mode, x, score, t, y, noise, x_mean):
+def _pc(p, mode, x, score, t, y, noise, x_mean, lengths=None):
     if noise is None:
         raise AssertionError("the CPU stand-in needs a noise tape (Philox lives in the kernel)")
     B = x.shape[0]
@@ -71,21 +71,26 @@ def _pc(p, mode, x, score, t, y, noise, x_mean):
     xb, sb, zb = (a.mean(dim=1, keepdim=True) for a in (xs, s, z))
     yy = 0.0 if y is None else y.double().reshape(B, 1, *x.shape[2:])
     m = v(c["a0"]) * xs + v(c["a1"]) * xb + v(c["a2"]) * s + v(c["a3"]) * sb + v(c["a4"]) * yy
-    x.copy_((m + v(c["b0"]) * z + v(c["b1"]) * zb).float())
+    xo = m + v(c["b0"]) * z + v(c["b1"]) * zb
+    if lengths is not None:  # ragged batch: state kept at exactly 0 past each row's length (csrc/pc_step.cu)
+        L = x[0, 0].numel()
+        live = (torch.arange(L)[None] < lengths.reshape(B, 1).long()).reshape(B, 1, *x.shape[2:])
+        xo, m = xo * live, m * live
+    x.copy_(xo.float())
     if x_mean is not None:
         x_mean.copy_(m.float())
 
 
-def pc_corrector(p, x, score, t, noise=None, seed=0, draw=0, x_mean=None):
-    _pc(p, "corrector", x, score, t, None, noise, x_mean)
+def pc_corrector(p, x, score, t, noise=None, seed=0, draw=0, x_mean=None, lengths=None):
+    _pc(p, "corrector", x, score, t, None, noise, x_mean, lengths)
 
 
-def pc_predictor(p, x, score, t, y, noise=None, seed=0, draw=0, x_mean=None):
-    _pc(p, "predictor", x, score, t, y if p.sde == 1 else None, noise, x_mean)
+def pc_predictor(p, x, score, t, y, noise=None, seed=0, draw=0, x_mean=None, lengths=None):
+    _pc(p, "predictor", x, score, t, y if p.sde == 1 else None, noise, x_mean, lengths)
 
 
-def pc_prior(p, x, y, noise=None, seed=0, draw=0):
-    _pc(p, "prior", x, None, None, y, noise, None)
+def pc_prior(p, x, y, noise=None, seed=0, draw=0, lengths=None):
+    _pc(p, "prior", x, None, None, y, noise, None, lengths)
 
 
 def philox_normal(out, seed, draw):
@@ -241,14 +246,16 @@ def output_layer(x, t, w, bias, out, scale_by_sigma):
 @contextlib.contextmanager
 def emulated_ops():
     """Swap the kernel wrappers for the stand-ins above (and back)."""
-    saved = {n: getattr(ops, n) for n in _NAMES}
-    saved_flag = ops.EMULATED
+    # the three policy hooks of ops: no tcgen05 plans, no CUDA graphs, CPU tensors accepted -- patched HERE, so the
+    # package itself carries no emulation switch
+    policy = {"tc_enabled": lambda: False, "graphs_enabled": lambda: False, "require_device": lambda t, what: None}
+    saved = {n: getattr(ops, n) for n in list(_NAMES) + list(policy)}
     try:
         for n in _NAMES:
             setattr(ops, n, globals()[n])
-        ops.EMULATED = True
+        for n, f in policy.items():
+            setattr(ops, n, f)
         yield
     finally:
         for n, f in saved.items():
             setattr(ops, n, f)
-        ops.EMULATED = saved_flag

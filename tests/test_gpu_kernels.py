@@ -75,6 +75,28 @@ def test_pc_philox_noise_is_standard_normal_and_keyed():
     assert rel(x.flatten(), z * std1) < 1e-5
 
 
+def test_box_muller_endpoint_uniforms_are_finite():
+    """Uniform words at and next to both ends of the range (u -> 1 makes __logf(u) ~ -6e-8, which the fast-math
+    intrinsic may return with the wrong sign: sqrt of a negative = NaN without the clamp) and a dense sweep of the top
+    2^16 words: every output finite, radius 0 at u = 1."""
+    ends = [0xFFFFFFFF, 0xFFFFFF00, 0xFFFFFE00, 0xFFFFFF7F, 0xFFFFFF80, 0, 1, 0x80000000]
+    top = torch.arange(0x100000000 - (1 << 16), 0x100000000, dtype=torch.int64)
+    words = torch.cat([torch.tensor(ends, dtype=torch.int64), top])
+    words = words[:words.numel() // 2 * 2]
+    # radii words (4q, 4q+2) take the test values; angle words a fixed pattern
+    bits = torch.empty(words.numel() * 2, dtype=torch.int64)
+    bits[0::2] = words
+    bits[1::2] = 0x12345678
+    bits32 = (bits & 0xFFFFFFFF).to(torch.int64)
+    bits32 = torch.where(bits32 >= 2 ** 31, bits32 - 2 ** 32, bits32).to(torch.int32).to(DEV)
+    out = torch.empty(bits32.numel(), device=DEV)
+    ops.box_muller(bits32, out)
+    assert torch.isfinite(out).all()
+    r = torch.hypot(out[0::2], out[1::2]).cpu()
+    assert float(r[0]) < 1e-3  # u = 1 -> radius ~ 0
+    assert float(r[5]) > 6.0    # u = 2^-33 -> radius sqrt(-2 ln u) ~ 6.76
+
+
 # ------------------------------------------------------------------ spectral
 @pytest.mark.parametrize("B,n_src,T", [(1, 2, 32000), (2, 2, 7810), (3, 3, 5001), (1, 1, 300)])
 @pytest.mark.parametrize("affine", [False, True])

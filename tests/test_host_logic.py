@@ -170,8 +170,8 @@ def test_c_abi_library_exports_every_declared_symbol():
     lib = _lib.load()  # raises if the .so is missing or a symbol is not exported
     for name in declared:
         assert getattr(lib, name) is not None
-    assert lib.ditsep_abi_version() == 1
+    assert lib.ditsep_abi_version() == 2
     assert isinstance(lib.ditsep_launch_count(), int)
     # argument validation happens before any CUDA call: errors come back as codes + text, not exceptions
-    rc = lib.ditsep_pc_corrector(None, None, None, None, 0, 0, None, None, 1, 8, None)
+    rc = lib.ditsep_pc_corrector(None, None, None, None, 0, 0, None, None, 1, 8, None, None)
     assert rc != 0 and b"null" in lib.ditsep_last_error()

@@ -11,7 +11,7 @@ import torch.multiprocessing as mp
 
 from ditsep_b200.utils import shard
 
-LENGTHS = [2048, 1500, 2048, 3000, 1500]
+LENGTHS = [2048, 1500, 2048, 3000, 1500, 1800, 2500, 1700]  # 1500..2500 share one frame bucket (64 frames)
 
 
 def _mixtures():
@@ -20,7 +20,7 @@ def _mixtures():
     return [s.sum(0, keepdim=True) for s in srcs], srcs
 
 
-def _run(rank, world, port, q):
+def _run(rank, world, port, q, max_batch=1):
     import sys
     here = os.path.dirname(os.path.abspath(__file__))
     sys.path[:0] = [here, os.path.dirname(here)]
@@ -33,9 +33,9 @@ def _run(rank, world, port, q):
     model, _, _ = build_model("fp32", N=2)
     mixes, srcs = _mixtures()
     with emulated_ops(), torch.no_grad():
-        rows, outs = shard.separate_sharded(model, mixes, references=srcs, max_batch=1,
+        rows, outs = shard.separate_sharded(model, mixes, references=srcs, max_batch=max_batch,
                                             sampler_kwargs={"N": 2}, rank=rank, world_size=world,
-                                            noise_tape_factory=lambda i: S.NoiseTape(4321 + i))
+                                            noise_tape_factory=lambda i: S.NoiseTape(4321 + i).draw)
     q.put((rank, rows.numpy().copy(), {k: v.numpy().copy() for k, v in outs.items()}))  # by value: the child exits
     if world > 1:
         dist.barrier()
@@ -50,11 +50,11 @@ def _free_port():
     return p
 
 
-def _launch(world):
+def _launch(world, max_batch=1):
     ctx = mp.get_context("spawn")
     q = ctx.Queue()
     port = _free_port()
-    procs = [ctx.Process(target=_run, args=(r, world, port, q)) for r in range(world)]
+    procs = [ctx.Process(target=_run, args=(r, world, port, q, max_batch)) for r in range(world)]
     for p in procs:
         p.start()
     got = []
@@ -112,3 +112,19 @@ def test_world_size_2_gloo_matches_single_process():
         for i, est in outs.items():
             assert est.shape == (2, LENGTHS[i])
             assert torch.equal(est, one[0][2][i])
+
+
+def test_ragged_batches_match_batch_1_runs():
+    """Mixtures of DIFFERENT lengths sharing a batch (one frame bucket, zero-padded, per-mixture statistics, state
+    masked past each length) give what each mixture gives alone at batch 1 with the same noise tape -- the
+    reference evaluates at batch 1 (src/evaluate_mp.py:289,311).  Round 1 normalised over the padding and let the
+    prior noise into it."""
+    one = _launch(1, max_batch=1)
+    rag = _launch(2, max_batch=4)
+    assert any(len({LENGTHS[i] for i in b}) > 1 for r in range(2) for b in shard.batches_for_rank(LENGTHS, 2, r, 4))
+    ref_outs = one[0][2]
+    for rank, rows, outs in rag:
+        assert torch.allclose(rows, one[0][1], atol=2e-3, rtol=0)       # SI-SDR rows, dB
+        for i, est in outs.items():
+            d = float((est - ref_outs[i]).norm() / ref_outs[i].norm())
+            assert est.shape == (2, LENGTHS[i]) and d < 2e-5, (i, d)    # fp32 emulation: summation order only
