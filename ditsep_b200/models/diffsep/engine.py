@@ -105,6 +105,10 @@ class _ConvW:
     def __init__(self, w_f32, bias, ksize, w_bf16=None):
         self.w, self.bias, self.ksize, self.w_bf16 = w_f32, bias, ksize, w_bf16
         self.cout, self.cin = w_f32.shape[0], w_f32.shape[2]
+        # ALGORITHMIC multiply-accumulates per output pixel (2*M*N*K convention of SURVEY.md 8d, K = taps * real Cin):
+        # what nn.Conv2d does in the reference, not what the packed operand executes (the hi/lo-widened first layer
+        # executes K = 576 for 54 real; a fused identity shortcut executes 64 extra columns for a plain add)
+        self.algo_macs = self.cout * w_f32.shape[1] * self.cin
 
 
 def _pack_conv(weight: torch.Tensor, bias: torch.Tensor, want_bf16: bool) -> _ConvW:
@@ -136,6 +140,7 @@ def _fuse_shortcut(main: _ConvW, sc: Optional[_ConvW], cx: int) -> Optional[_Con
         bias = (main.bias + sc.bias).contiguous()
     out = _ConvW(main.w, bias, main.ksize, wb)
     out.cx = cx
+    out.algo_macs = main.algo_macs + (0 if sc is None else main.cout * cx)  # Conv_2 is a real 1x1 conv; x + h is not
     return out
 
 
@@ -153,7 +158,9 @@ def _pack_conv_hilo(weight: torch.Tensor, bias: torch.Tensor, width: int = 64) -
     wb[:cout, :, 0:cin] = wh
     wb[:cout, :, cin:2 * cin] = wh
     wb[:cout, :, 2 * cin:3 * cin] = wl
-    return _ConvW(wb[:cout].float(), bias.detach().float().contiguous(), kh, wb)
+    out = _ConvW(wb[:cout].float(), bias.detach().float().contiguous(), kh, wb)
+    out.algo_macs = cout * kh * kw * cin
+    return out
 
 
 class NcsnppEngine:
@@ -474,6 +481,7 @@ class _Plan:
             if plan is None:
                 plan = ops.ConvTcPlan(x, cw.w_bf16, cw.cout, cw.ksize)
             self._tc_plans.append(plan)
+            plan.algo_flops = 2.0 * x.shape[0] * x.shape[1] * x.shape[2] * cw.algo_macs
             if want_stats and plan.stats_floats() > 0:
                 buf = torch.empty(plan.stats_floats(), device=self.device, dtype=torch.float32)
                 kw["stats"] = buf

@@ -128,6 +128,37 @@ def normalize_ragged(mixtures: Sequence[torch.Tensor], batch: Sequence[int], dev
     return y, lengths, mean, std
 
 
+def gather_waveforms(outs: Dict[int, torch.Tensor], lengths: Sequence[int], device, group=None) -> Dict[int, torch.Tensor]:
+    """All-gather of the separated waveforms (the optional second collective of SURVEY.md 8e).  outs: this rank's
+    {idx: (n_src, T_idx)}; every rank gets every mixture back.  ONE all_gather_into_tensor of a zero-padded
+    (n_local_max, 1 + n_src * T_max) block per rank (slot 0 carries the global index, -1 = padding)."""
+    if not (dist.is_available() and dist.is_initialized()) or dist.get_world_size(group) == 1:
+        return dict(outs)
+    world = dist.get_world_size(group)
+    t_max = max(int(n) for n in lengths)
+    n_src = next(iter(outs.values())).shape[0] if outs else 2
+    n = torch.tensor([len(outs), n_src], device=device, dtype=torch.int64)
+    dist.all_reduce(n, op=dist.ReduceOp.MAX, group=group)
+    n_max, n_src = int(n[0].item()), int(n[1].item())
+    block = torch.zeros(n_max, 1 + n_src * t_max, device=device, dtype=torch.float32)
+    block[:, 0] = -1.0
+    for r, (i, est) in enumerate(sorted(outs.items())):
+        block[r, 0] = float(i)
+        block[r, 1:].view(n_src, t_max)[:, :est.shape[-1]] = est.to(device)
+    if block.is_cuda:
+        full = torch.empty(world * n_max, block.shape[1], device=device, dtype=torch.float32)
+        dist.all_gather_into_tensor(full, block, group=group)
+    else:
+        parts = [torch.empty_like(block) for _ in range(world)]
+        dist.all_gather(parts, block, group=group)
+        full = torch.cat(parts, dim=0)
+    res = {}
+    for row in full[full[:, 0] >= 0]:
+        i = int(row[0].item())
+        res[i] = row[1:].view(n_src, t_max)[:, :int(lengths[i])]
+    return res
+
+
 def separate_sharded(model, mixtures: Sequence[torch.Tensor], references=None, max_batch: int = 32, device=None,
                      sampler_kwargs=None, seed: int = 0, rank: int = None, world_size: int = None,
                      noise_tape_factory=None, predictor: str = "reverse_diffusion", corrector: str = "ald2"):

@@ -150,7 +150,7 @@ def upsample_2d_ref(x: Tensor, k: Sequence[int] = (1, 3, 3, 1), factor: int = 2)
     pad ((p+1)//2 + factor - 1, p//2) with p = len(k) - factor)."""
     kk = _setup_kernel(k) * (factor ** 2)
     p = kk.shape[0] - factor
-    return upfirdn2d_ref(x, torch.tensor(kk), up=factor, down=1,
+    return upfirdn2d_ref(x, torch.tensor(kk, device=x.device, dtype=x.dtype), up=factor, down=1,
                          pad=((p + 1) // 2 + factor - 1, p // 2))
 
 
@@ -158,7 +158,8 @@ def downsample_2d_ref(x: Tensor, k: Sequence[int] = (1, 3, 3, 1), factor: int = 
     """up_or_down_sampling.py:242-273 (pad ((p+1)//2, p//2))."""
     kk = _setup_kernel(k)
     p = kk.shape[0] - factor
-    return upfirdn2d_ref(x, torch.tensor(kk), up=1, down=factor, pad=((p + 1) // 2, p // 2))
+    return upfirdn2d_ref(x, torch.tensor(kk, device=x.device, dtype=x.dtype), up=1, down=factor,
+                         pad=((p + 1) // 2, p // 2))
 
 
 def _gn(x: Tensor, sd, key: str) -> Tensor:

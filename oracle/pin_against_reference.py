@@ -169,24 +169,68 @@ def main():
             golden["score_c1_sub"] = out_ref[..., ::16].numpy()
             golden["score_c1_norm"] = np.array(float(out_ref.norm()))
 
+    # ---- b2. what bf16 arithmetic does to the REFERENCE itself ------------------------
+    # The reference under torch.autocast(bfloat16) on the same inputs, against its own fp32 output: the size of the
+    # error that is intrinsic to bf16 operands / activations for this weight set, independent of this repo's kernels.
+    mix, src = synth_mixtures(2, 2, 7810, seed=1234)
+    mixn, _, _ = S.normalize_batch_ref(mix)
+    xt = 0.5 * mixn + 0.3 * S.NoiseTape(99).draw(0, (2, 2, 7810))
+    t = torch.full((2,), 0.61)
+    with torch.no_grad():
+        out32 = ref(xt, t, mixn)
+        with torch.autocast("cpu", dtype=torch.bfloat16):
+            out16 = ref(xt, t, mixn)
+    e_ac = rel_l2(out16.float(), out32)
+    print(f"[b2] reference under torch.autocast(cpu, bfloat16) vs its own fp32 output (init_scale={args.init_scale:g}): "
+          f"rel-L2 = {e_ac:.3e}")
+    golden["ref_autocast_bf16_rel_l2"] = np.array(e_ac)
+
+    # ---- b3. C3 at its maximum: 10 s @ 16 kHz, W = 1280 frames -------------------------
+    if args.full:
+        T3 = 160000
+        mix, src = synth_mixtures(1, 2, T3, seed=1234)
+        mixn, _, _ = S.normalize_batch_ref(mix)
+        xt = 0.5 * mixn + 0.3 * S.NoiseTape(99).draw(0, (1, 2, T3))
+        t = torch.full((1,), 0.61)
+        with torch.no_grad():
+            t0 = time.perf_counter()
+            out_ref = ref(xt, t, mixn)
+            t_ref = time.perf_counter() - t0
+            out_orc = R.score_forward_ref(sd, cfg, xt, t, mixn)
+        print(f"[b3] score step C3 max (T={T3}, W=1280): rel-L2 oracle vs reference = {rel_l2(out_orc, out_ref):.3e}; "
+              f"reference {t_ref:.2f} s")
+        assert rel_l2(out_orc, out_ref) < 2e-5
+        golden["score_c3max_sub"] = out_ref[..., ::64].numpy()
+
     # ---- c. PC sampler, MixSDE + ald2, taped noise ---------------------------------
     def run_pair(T, B, N, tag):
         mix, src = synth_mixtures(B, 2, T, seed=1234)
         mixn, _, _ = S.normalize_batch_ref(mix)
         sde_ref = sdes.sdes.MixSDE(2, 2.0, 0.05, 0.5, N=N)
         tape = S.NoiseTape(4321)
+        ref_scores_sub = []  # the REFERENCE's score at every evaluation, every 64th sample (per-step rel-L2 gate)
+
+        def ref_recording(x, t, y):
+            out = ref(x, t, y)
+            ref_scores_sub.append(out[..., ::64].clone())
+            return out
+
         with TapedRandn(tape) as tr:
-            sampler = sdes.get_pc_sampler("reverse_diffusion", "ald2", sde=sde_ref, score_fn=ref, y=mixn,
+            sampler = sdes.get_pc_sampler("reverse_diffusion", "ald2", sde=sde_ref, score_fn=ref_recording, y=mixn,
                                           eps=0.03, snr=0.5, corrector_steps=1, denoise=True)
             t0 = time.perf_counter()
             x_ref, nfe = sampler()
             t_ref = time.perf_counter() - t0
             ndraws = tr.i
-        scores = []
+        scores, orc_sub = [], []
         x_orc, nfe2 = S.pc_sampler_ref(lambda x, t, y: R.score_forward_ref(sd, cfg, x, t, y),
                                        S.MixSDERef(2, 2.0, 0.05, 0.5, N=N), mixn, S.NoiseTape(4321),
                                        corrector="ald2", eps=0.03, snr=0.5,
-                                       on_score=lambda k, x, t, s: scores.append(float(s.norm())))
+                                       on_score=lambda k, x, t, s: (scores.append(float(s.norm())),
+                                                                    orc_sub.append(s[..., ::64].clone())))
+        worst = max(rel_l2(a, b) for a, b in zip(orc_sub, ref_scores_sub))
+        print(f"[c] sampler {tag}: worst per-step score rel-L2 oracle vs reference over {len(orc_sub)} evaluations = {worst:.3e}")
+        assert len(orc_sub) == len(ref_scores_sub) == 2 * N and worst < 1e-3
         e = rel_l2(x_orc, x_ref)
         sis_ref, _ = S.si_sdr_pit_ref(src, x_ref)
         sis_orc, _ = S.si_sdr_pit_ref(src, x_orc)
@@ -194,16 +238,17 @@ def main():
               f"SI-SDR ref {sis_ref.mean():.3f} dB oracle {sis_orc.mean():.3f} dB")
         assert nfe == nfe2 == 2 * N and ndraws == 1 + 2 * N
         assert e < 1e-3 and abs(float(sis_ref.mean() - sis_orc.mean())) < 0.01
-        return x_ref, scores, sis_ref
+        return x_ref, scores, sis_ref, torch.stack(ref_scores_sub).numpy()
 
-    x_ref, scores, sis = run_pair(7810, 2, 3, "small")
+    x_ref, scores, sis, sub = run_pair(7810, 2, 3, "small")
     golden["sampler_small_out"] = x_ref.numpy()
+    golden["sampler_small_scores_sub"] = sub
     golden["sampler_small_score_norms"] = np.array(scores)
     golden["sampler_small_sisdr"] = sis.numpy()
     if args.full:
-        x_ref, scores, sis = run_pair(32000, 1, 30, "C1")
+        x_ref, scores, sis, sub = run_pair(32000, 1, 30, "C1")
         np.savez_compressed(os.path.join(GOLDEN, f"sampler_c1{tag}.npz"), out=x_ref.numpy().astype(np.float32),
-                            score_norms=np.array(scores), sisdr=sis.numpy())
+                            score_norms=np.array(scores), sisdr=sis.numpy(), scores_sub=sub.astype(np.float32))
 
     # ---- d. OUVESDE + ald with a synthetic score function ---------------------------
     B, T, N = 2, 4096, 5
@@ -249,6 +294,28 @@ def main():
     print(f"[e] latent wrapper: rel-L2 {rel_l2(o_orc, o_ref):.3e}")
     assert rel_l2(o_orc, o_ref) < 2e-5
     golden["latent_out"] = o_ref.numpy()
+
+    # ---- e2. latent wrapper at the real C4 size (nf=128, ch_mult [1,2,2], L = 16 and 80, OUVE latent config) --------
+    if args.full:
+        bcfg4 = R.NCSNppConfig(nf=128, ch_mult=(1, 2, 2), num_res_blocks=2, attn_resolutions=(16,), image_size=64,
+                               num_channels_in=3, num_channels_out=2, centered=True)
+        sd4 = R.make_state_dict(bcfg4, seed=5, with_window=None, init_scale=args.init_scale)
+        lat4 = score_models.LatentScoreModelNCSNpp(
+            2, dict(_target_="models.diffsep.ncsnpp.NCSNpp", nf=128, ch_mult=[1, 2, 2], num_res_blocks=2,
+                    attn_resolutions=[16], resamp_with_conv=True, image_size=64, centered=True),
+            max_latent_length=4).eval()
+        lat4.load_state_dict(sd4, strict=True)
+        for L in (16, 80):
+            g = torch.Generator().manual_seed(100 + L)
+            xt = torch.randn(1, 2, 64, L, generator=g)
+            mx = torch.randn(1, 1, 64, L, generator=g)
+            t = torch.tensor([0.55])
+            with torch.no_grad():
+                o_ref = lat4(xt, t, mx)
+                o_orc = R.latent_score_forward_ref(sd4, bcfg4, xt, t, mx, max_latent_length=4)
+            print(f"[e2] latent wrapper nf=128 L={L}: rel-L2 oracle vs reference {rel_l2(o_orc, o_ref):.3e}")
+            assert rel_l2(o_orc, o_ref) < 2e-5
+            golden[f"latent_c4_L{L}"] = o_ref.numpy()
 
     np.savez_compressed(os.path.join(GOLDEN, f"reference_outputs{tag}.npz"), **golden)
     print("fixtures written to", GOLDEN)

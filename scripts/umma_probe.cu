@@ -17,14 +17,15 @@ __device__ __forceinline__ bool elect_one_sync() {
   return pred != 0;
 }
 
-__global__ void __launch_bounds__(128, 1) probe(int N, int mode, int iters, int sbo_bytes, long long* out) {
+__global__ void __launch_bounds__(128, 1) probe(int N, int mode, int iters, int sbo_bytes, long long* out, int M = 128,
+                                                int sbo_b_bytes = 1024) {
   extern __shared__ uint8_t raw[];
   __shared__ __align__(8) uint64_t bar2[2];
   __shared__ uint32_t tmem_slot;
   const uint32_t base = (smem_u32(raw) + 1023u) & ~1023u;
   // A: up to 24 KB region (16 groups of 8 rows, group pitch sbo_bytes <= 1536); B: 256 rows x 128 B after it
   const uint32_t a_addr = base, b_addr = base + 32768;
-  for (uint32_t i = threadIdx.x; i < (32768 + 32768) / 4; i += blockDim.x) {
+  for (uint32_t i = threadIdx.x; i < (32768 + 49152) / 4; i += blockDim.x) {
     uint32_t h = (i * 2654435761u) ^ (blockIdx.x * 40503u);
     // two bf16 values in [-1, 1): sign + exponent 0x3f00.. keeps them finite
     uint32_t v = (0x3f00u | (h & 0x80ffu)) | ((0x3f00u | ((h >> 16) & 0x80ffu)) << 16);
@@ -47,9 +48,9 @@ __global__ void __launch_bounds__(128, 1) probe(int N, int mode, int iters, int 
   const int wid = threadIdx.x >> 5;
   if (wid == 0 || (wid == 1 && (mode & 8))) {
     uint64_t& bar = bar2[wid];
-    const uint32_t idesc = (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(N >> 3) << 17) | ((128u >> 4) << 24);
+    const uint32_t idesc = (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(N >> 3) << 17) | (((uint32_t)M >> 4) << 24);
     const uint64_t hi_a = (uint64_t)((uint32_t)(sbo_bytes >> 4) | (1u << 14) | (2u << 29)) << 32;
-    const uint64_t hi_b = (uint64_t)(64u | (1u << 14) | (2u << 29)) << 32;
+    const uint64_t hi_b = (uint64_t)((uint32_t)(sbo_b_bytes >> 4) | (1u << 14) | (2u << 29)) << 32;
     const uint32_t lo_a = (a_addr >> 4) | (1u << 16), lo_b = (b_addr >> 4) | (1u << 16);
     const uint32_t a_tmem = tmem + 448 - ((mode & 4) ? 64 : 0);  // TS mode: A operand columns (128 lanes x 8 columns per K = 16), past the accumulators
     const bool ts = (mode & 1) != 0, alt = (mode & 2) != 0, cp = (mode & 4) != 0;
@@ -84,7 +85,9 @@ __global__ void __launch_bounds__(128, 1) probe(int N, int mode, int iters, int 
     }
     __syncwarp();
     uint32_t ok = 0;
+    const long long t_wait = clock64();
     while (!ok) {
+      if (clock64() - t_wait > 4000000000ll) __trap();  // ~2 s: a protocol error must not hang the GPU
       asm volatile(
           "{\n\t.reg .pred p;\n\tmbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\tselp.u32 %0, 1, 0, p;\n\t}"
           : "=r"(ok)
@@ -102,12 +105,96 @@ __global__ void __launch_bounds__(128, 1) probe(int N, int mode, int iters, int 
   }
 }
 
+// ---- cta_group::2: a CTA pair (cluster of 2) issues ONE MMA of M = 256 (128 rows of A and 128 lanes of D per CTA), B's N
+// rows split N/2 per CTA.  Only the leader (cluster rank 0) issues; the commit is multicast to both CTAs' barriers.
+__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(128, 1) probe2(int N, int mode, int iters, long long* out) {
+  extern __shared__ uint8_t raw[];
+  __shared__ __align__(8) uint64_t bar;
+  __shared__ uint32_t tmem_slot;
+  uint32_t rank;
+  asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(rank));
+  const uint32_t base = (smem_u32(raw) + 1023u) & ~1023u;
+  const uint32_t a_addr = base, b_addr = base + 32768;
+  for (uint32_t i = threadIdx.x; i < (32768 + 32768) / 4; i += blockDim.x) {
+    uint32_t h = (i * 2654435761u) ^ (blockIdx.x * 40503u);
+    uint32_t v = (0x3f00u | (h & 0x80ffu)) | ((0x3f00u | ((h >> 16) & 0x80ffu)) << 16);
+    reinterpret_cast<uint32_t*>(raw + (base - smem_u32(raw)))[i] = v;
+  }
+  if (threadIdx.x == 0) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(smem_u32(&bar)) : "memory");
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  if (threadIdx.x < 32) {
+    asm volatile("tcgen05.alloc.cta_group::2.sync.aligned.shared::cta.b32 [%0], 512;" ::"r"(smem_u32(&tmem_slot)) : "memory");
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::2.sync.aligned;" ::: "memory");
+  }
+  asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+  asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+  asm volatile("barrier.cluster.arrive.release.aligned;\n\tbarrier.cluster.wait.acquire.aligned;" ::: "memory");
+  asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+  const uint32_t tmem = tmem_slot;
+  if (threadIdx.x < 32) {
+    const uint32_t idesc = (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(N >> 3) << 17) | ((256u >> 4) << 24);
+    const uint64_t hi = (uint64_t)(64u | (1u << 14) | (2u << 29)) << 32;
+    const uint32_t lo_a = (a_addr >> 4) | (1u << 16), lo_b = (b_addr >> 4) | (1u << 16);
+    const uint32_t a_tmem = tmem + 448;
+    const bool ts = (mode & 1) != 0;
+    const long long t0 = clock64();
+    if (rank == 0 && elect_one_sync()) {
+#pragma unroll 1
+      for (int it = 0; it < iters; ++it) {
+#pragma unroll
+        for (int k = 0; k < 4; ++k) {
+          const uint64_t db = hi | (uint64_t)(lo_b + 2 * k);
+          if (ts) {
+            asm volatile(
+                "{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %3, 0;\n\t"
+                "tcgen05.mma.cta_group::2.kind::f16 [%0], [%1], %2, %4, p;\n\t}" ::"r"(tmem), "r"(a_tmem + 8 * k), "l"(db), "r"(1u),
+                "r"(idesc)
+                : "memory");
+          } else {
+            const uint64_t da = hi | (uint64_t)(lo_a + 2 * k);
+            asm volatile(
+                "{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %3, 0;\n\t"
+                "tcgen05.mma.cta_group::2.kind::f16 [%0], %1, %2, %4, p;\n\t}" ::"r"(tmem), "l"(da), "l"(db), "r"(1u), "r"(idesc)
+                : "memory");
+          }
+        }
+      }
+      asm volatile("tcgen05.commit.cta_group::2.mbarrier::arrive::one.shared::cluster.multicast::cluster.b64 [%0], %1;" ::"r"(
+                       smem_u32(&bar)),
+                   "h"((uint16_t)3)
+                   : "memory");
+    }
+    __syncwarp();
+    uint32_t ok = 0;
+    const long long t_wait = clock64();
+    while (!ok) {
+      if (clock64() - t_wait > 4000000000ll) __trap();  // ~2 s: a protocol error must not hang the GPU
+      asm volatile(
+          "{\n\t.reg .pred p;\n\tmbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\tselp.u32 %0, 1, 0, p;\n\t}"
+          : "=r"(ok)
+          : "r"(smem_u32(&bar)), "r"(0u)
+          : "memory");
+    }
+    const long long t1 = clock64();
+    if (threadIdx.x == 0 && rank == 0) out[blockIdx.x / 2] = t1 - t0;
+  }
+  asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+  asm volatile("barrier.cluster.arrive.release.aligned;\n\tbarrier.cluster.wait.acquire.aligned;" ::: "memory");
+  if (threadIdx.x < 32) {
+    asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+    asm volatile("tcgen05.dealloc.cta_group::2.sync.aligned.b32 %0, 512;" ::"r"(tmem) : "memory");
+  }
+}
+
 int main() {
   int sms = 148;
   cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, 0);
   long long* d_out;
   cudaMalloc(&d_out, sizeof(long long) * sms);
-  cudaFuncSetAttribute(probe, cudaFuncAttributeMaxDynamicSharedMemorySize, 70 * 1024);
+  cudaFuncSetAttribute(probe, cudaFuncAttributeMaxDynamicSharedMemorySize, 90 * 1024);
+  cudaFuncSetAttribute(probe2, cudaFuncAttributeMaxDynamicSharedMemorySize, 90 * 1024);
   const int iters = 2000;
   const int Ns[] = {16, 32, 64, 96, 128, 192, 256};
   const char* names[] = {"SS", "TS", "SS alt-acc", "TS alt-acc", "-", "TS+cp", "-", "TS+cp alt", "SS 2warps", "TS 2warps"};
@@ -118,7 +205,7 @@ int main() {
         if ((mode & 2) && 2 * N > 384) continue;
         if ((mode & 4) && N > 192) continue;
         if ((mode & 8) && N > 192) continue;
-        for (int rep = 0; rep < 2; ++rep) probe<<<sms, 128, 70 * 1024>>>(N, mode, iters, sbo, d_out);
+        for (int rep = 0; rep < 2; ++rep) probe<<<sms, 128, 90 * 1024>>>(N, mode, iters, sbo, d_out);
         cudaError_t e = cudaDeviceSynchronize();
         if (e != cudaSuccess) { printf("N=%d mode=%d: %s\n", N, mode, cudaGetErrorString(e)); return 1; }
         std::vector<long long> h(sms);
@@ -130,5 +217,34 @@ int main() {
       }
     }
   }
+  // ---- round 2: the questions behind the conv re-mapping ----------------------------------------
+  auto run1 = [&](const char* label, int N, int mode, int M, int sbo_b) {
+    for (int rep = 0; rep < 2; ++rep) probe<<<sms, 128, 90 * 1024>>>(N, mode, iters, 1024, d_out, M, sbo_b);
+    cudaError_t e = cudaDeviceSynchronize();
+    if (e != cudaSuccess) { printf("%s N=%d: %s\n", label, N, cudaGetErrorString(e)); exit(1); }
+    std::vector<long long> h(sms);
+    cudaMemcpy(h.data(), d_out, sizeof(long long) * sms, cudaMemcpyDeviceToHost);
+    std::sort(h.begin(), h.end());
+    const double per = (double)h[sms / 2] / (iters * 4.0), ideal = (double)M * N / 256.0;
+    printf("%-28s M=%3d N=%3d  %7.1f clk/MMA  (ideal %5.1f, %5.1f %%)\n", label, M, N, per, ideal, 100.0 * ideal / per);
+  };
+  for (int N : {64, 128, 256}) run1("M=64 SS", N, 0, 64, 1024);
+  for (int N : {64, 128, 256}) run1("M=64 TS", N, 1, 64, 1024);
+  for (int N : {80, 144, 160, 176, 208, 240}) run1("TS odd N", N, 1, 128, 1024);
+  for (int N : {128, 144, 256}) run1("TS, B groups 1280 B apart", N, 1, 128, 1280);
+  for (int N : {128, 144, 256}) run1("SS, B groups 1280 B apart", N, 0, 128, 1280);
+  for (int mode = 0; mode < 2; ++mode)
+    for (int N : {64, 128, 256}) {
+      for (int rep = 0; rep < 2; ++rep) probe2<<<sms / 2 * 2, 128, 90 * 1024>>>(N, mode, iters, d_out);
+      cudaError_t e = cudaDeviceSynchronize();
+      if (e != cudaSuccess) { printf("cta_group::2 mode %d N=%d: %s\n", mode, N, cudaGetErrorString(e)); return 1; }
+      const int pairs = sms / 2;
+      std::vector<long long> h(pairs);
+      cudaMemcpy(h.data(), d_out, sizeof(long long) * pairs, cudaMemcpyDeviceToHost);
+      std::sort(h.begin(), h.end());
+      const double per = (double)h[pairs / 2] / (iters * 4.0);
+      printf("cta_group::2 %s             M=256 N=%3d  %7.1f clk/MMA per pair (ideal %5.1f per SM, %5.1f %%)\n", mode ? "TS" : "SS", N, per,
+             N / 2.0, 100.0 * (N / 2.0) / per);
+    }
   return 0;
 }

@@ -4,11 +4,20 @@ inputs and the same noise tape.  north_star tolerances: per-step score rel-L2 <=
 fp32, <= 1e-2 in bf16; final SI-SDR within 0.05 dB.
 
 Weight sets (tests/conftest.py::golden): fp32 is held to 1e-3 on BOTH sets.  bf16 is held to the
-north-star 1e-2 on the trained-like set (init_scale 0.01); on the worst-case set (init_scale 1.0:
-~150 layers whose residual branches are as loud as the skip path) bf16 storage alone -- 2^-9 relative
-per stored activation, 4 roundings per res-block -- measures 2.3e-2 against the fp32 reference, so that
-set carries a documented 4e-2 bound for bf16 instead."""
-CASES = [("fp32", 1.0, "", 1e-3), ("fp32", 0.01, "_s0p01", 1e-3), ("bf16", 0.01, "_s0p01", 1e-2), ("bf16", 1.0, "", 4e-2)]
+north-star 1e-2 on the trained-like set (init_scale 0.01).  On the worst-case set (init_scale 1.0:
+~150 layers whose residual branches are as loud as the skip path) the tolerance is NOT self-granted: the
+pin script runs the UNMODIFIED REFERENCE under torch.autocast(bfloat16) on the same inputs and stores its
+rel-L2 against its own fp32 output (golden "ref_autocast_bf16_rel_l2": 3.3e-2 for this set, 1.3e-2 for
+the trained-like one); our bf16 path must be at least as close to the fp32 reference as the reference's own
+bf16 arithmetic is (measured: 2.3e-2).  bf16 error of that size is a property of the weight set."""
+CASES = [("fp32", 1.0, "", 1e-3), ("fp32", 0.01, "_s0p01", 1e-3), ("bf16", 0.01, "_s0p01", 1e-2), ("bf16", 1.0, "", None)]
+
+
+def _tol(golden, tag, tol):
+    """None -> the reference's own bf16-autocast error on this weight set (committed by the pin script)."""
+    if tol is not None:
+        return tol
+    return float(golden["ref" + tag]["ref_autocast_bf16_rel_l2"])
 import numpy as np
 import pytest
 import torch
@@ -24,6 +33,7 @@ DEV = "cuda"
 
 @pytest.mark.parametrize("precision,init_scale,tag,tol", CASES)
 def test_score_step_vs_reference_golden(golden, precision, init_scale, tag, tol):
+    tol = _tol(golden, tag, tol)
     model, sd, cfg = build_model(precision, DEV, init_scale=init_scale)
     xt, t, mixn = score_inputs(2, 7810)
     n0 = ops.launch_count()
@@ -57,34 +67,59 @@ def test_intermediate_activations_vs_oracle_fp32():
     assert rel_l2(out, ref) < 1e-3
 
 
-@pytest.mark.parametrize("precision,init_scale,tag", [("fp32", 1.0, ""), ("fp32", 0.01, "_s0p01"), ("bf16", 0.01, "_s0p01")])
-def test_sampler_small_vs_reference_golden(golden, precision, init_scale, tag):
+SAMPLER_CASES = [("fp32", 1.0, "", 1e-3), ("fp32", 0.01, "_s0p01", 1e-3), ("bf16", 0.01, "_s0p01", 1e-2),
+                 ("bf16", 1.0, "", None)]
+
+
+def _per_step_rel_l2(scores_sub, ref_sub):
+    """north_star: 'per-step score output relative L2' -- every evaluation of the trajectory, full sub-sampled
+    tensors (every 64th sample), not norms."""
+    assert len(scores_sub) == len(ref_sub)
+    return [rel_l2(a, torch.tensor(b)) for a, b in zip(scores_sub, ref_sub)]
+
+
+@pytest.mark.parametrize("precision,init_scale,tag,tol", SAMPLER_CASES)
+def test_sampler_small_vs_reference_golden(golden, precision, init_scale, tag, tol):
+    tol = _tol(golden, tag, tol)
     model, sd, cfg = build_model(precision, DEV, N=3, init_scale=init_scale)
     mixn, src = sampler_inputs(2, 7810)
-    sampler = model.get_pc_sampler("reverse_diffusion", "ald2", mixn.to(DEV), N=3, snr=0.5, corrector_steps=1,
-                                   denoise=True, noise_tape=S.NoiseTape(4321))
+    subs = []
+
+    def score_fn(x, t, y):
+        s = model(x, t, y)
+        subs.append(s[..., ::64].cpu())
+        return s
+
+    assert model.sde.N == 3
+    sampler = sdes.get_pc_sampler("reverse_diffusion", "ald2", sde=model.sde.copy(), score_fn=score_fn, y=mixn.to(DEV),
+                                  eps=0.03, snr=0.5, corrector_steps=1, denoise=True, noise_tape=S.NoiseTape(4321))
     x, nfe = sampler()
     assert nfe == 6
     ref = torch.tensor(golden["ref" + tag]["sampler_small_out"])
     e = rel_l2(x, ref)
+    steps = _per_step_rel_l2(subs, golden["ref" + tag]["sampler_small_scores_sub"])
     sis, _ = S.si_sdr_pit_ref(src, x.cpu())
     d = abs(float(sis.mean()) - float(golden["ref" + tag]["sampler_small_sisdr"].mean()))
-    print(f"sampler small {precision}: rel-L2 {e:.3e}, |dSI-SDR| {d:.4f} dB")
-    assert e < (1e-3 if precision == "fp32" else 3e-2)
+    print(f"sampler small {precision} init_scale={init_scale}: final rel-L2 {e:.3e}, worst per-step score rel-L2 "
+          f"{max(steps):.3e} (tol {tol:.1e}), |dSI-SDR| {d:.4f} dB")
+    assert max(steps) < tol
     assert d < 0.05
 
 
-@pytest.mark.parametrize("precision,init_scale,tag", [("fp32", 1.0, ""), ("fp32", 0.01, "_s0p01"), ("bf16", 0.01, "_s0p01")])
-def test_sampler_c1_vs_reference_golden(golden, precision, init_scale, tag):
+@pytest.mark.parametrize("precision,init_scale,tag,tol", SAMPLER_CASES)
+def test_sampler_c1_vs_reference_golden(golden, precision, init_scale, tag, tol):
     """Config C1 (BASELINE.json configs[0]): N=30, 4 s @ 8 kHz, batch 1, seeded noise tape.
-    The golden output is the reference sampler's; per-step score norms are the reference's."""
+    The golden output is the reference sampler's; the per-step gate is the rel-L2 of EVERY one of the 60 score
+    evaluations against the reference's own (sub-sampled) score tensor of that step."""
+    tol = _tol(golden, tag, tol)
     model, sd, cfg = build_model(precision, DEV, N=30, init_scale=init_scale)
     mixn, src = sampler_inputs(1, 32000)
-    norms = []
+    norms, subs = [], []
 
     def score_fn(x, t, y):
         s = model(x, t, y)
         norms.append(s.norm())
+        subs.append(s[..., ::64].cpu())
         return s
 
     sampler = sdes.get_pc_sampler("reverse_diffusion", "ald2", sde=model.sde.copy(), score_fn=score_fn, y=mixn.to(DEV),
@@ -98,10 +133,12 @@ def test_sampler_c1_vs_reference_golden(golden, precision, init_scale, tag):
     d = abs(float(sis.mean()) - float(sis_ref.mean()))
     nr = np.array([float(v) for v in norms])
     dn = np.abs(nr / golden["c1" + tag]["score_norms"] - 1).max()
-    print(f"sampler C1 {precision}: rel-L2 {e:.3e}, SI-SDR {float(sis.mean()):.3f} vs {float(sis_ref.mean()):.3f} dB, "
-          f"max per-step score-norm deviation {dn:.3e}")
+    steps = _per_step_rel_l2(subs, golden["c1" + tag]["scores_sub"])
+    print(f"sampler C1 {precision} init_scale={init_scale}: final rel-L2 {e:.3e}, SI-SDR {float(sis.mean()):.3f} vs "
+          f"{float(sis_ref.mean()):.3f} dB, worst per-step score rel-L2 {max(steps):.3e} at evaluation "
+          f"{int(np.argmax(steps))} (tol {tol:.1e}), max score-norm deviation {dn:.3e}")
     assert d < 0.05
-    assert dn < (1e-3 if precision == "fp32" else 1e-2)
+    assert max(steps) < tol
 
 
 def test_philox_sampler_is_seed_reproducible_and_statistically_sane():
@@ -192,3 +229,94 @@ def test_variable_length_16k_shape_vs_oracle():
         e = rel_l2(out, ref)
         print(f"C3-shaped score step {precision}: rel-L2 vs oracle = {e:.3e}")
         assert tuple(out.shape) == (1, 2, T) and e < tol
+
+
+# ------------------------------------------------------------------ round 2: the shapes VERDICT r1 listed as untested
+@pytest.mark.parametrize("precision,init_scale,tag,tol", [("fp32", 1.0, "", 1e-3), ("bf16", 0.01, "_s0p01", 1e-2)])
+def test_c3_max_length_vs_reference_golden(golden, precision, init_scale, tag, tol):
+    """Config C3 at its maximum: 10 s @ 16 kHz = 160000 samples -> 1253 frames -> W = 1280, against the REFERENCE's
+    committed output (every 64th sample)."""
+    model, sd, cfg = build_model(precision, DEV, init_scale=init_scale)
+    xt, t, mixn = score_inputs(1, 160000)
+    with torch.no_grad():
+        out = model(xt.to(DEV), t.to(DEV), mixn.to(DEV))
+    assert tuple(out.shape) == (1, 2, 160000)
+    e = rel_l2(out[..., ::64], torch.tensor(golden["ref" + tag]["score_c3max_sub"]))
+    print(f"C3 max (W=1280) score step {precision}: rel-L2 vs reference = {e:.3e}")
+    assert e < tol
+
+
+@pytest.mark.parametrize("precision,init_scale,tag,tol", [("fp32", 1.0, "", 1e-3), ("bf16", 0.01, "_s0p01", 1e-2),
+                                                          ("bf16", 1.0, "", None)])
+@pytest.mark.parametrize("L", [16, 80])
+def test_latent_real_size_vs_reference_golden(golden, precision, init_scale, tag, tol, L):
+    """Config C4 at its real size (config/latent_diffsep_ouve/model/default.yaml:16-28): nf=128, ch_mult [1,2,2],
+    centered, max_latent_length 4, latents (1, 3, 64, L) with L = 16 and 80, against the reference's output."""
+    from ditsep_b200.models.diffsep.score_models import LatentScoreModelNCSNpp
+    tol = _tol(golden, tag, tol)
+    bcfg = R.NCSNppConfig(nf=128, ch_mult=(1, 2, 2), num_res_blocks=2, attn_resolutions=(16,), image_size=64,
+                          num_channels_in=3, num_channels_out=2, centered=True)
+    sdl = R.make_state_dict(bcfg, seed=5, with_window=None, init_scale=init_scale)
+    lat = LatentScoreModelNCSNpp(2, dict(_target_="models.diffsep.ncsnpp.NCSNpp", nf=128, ch_mult=[1, 2, 2],
+                                         num_res_blocks=2, attn_resolutions=[16], resamp_with_conv=True, image_size=64,
+                                         centered=True, precision=precision), max_latent_length=4).eval()
+    lat.load_state_dict(sdl, strict=True)
+    lat = lat.to(DEV)
+    g = torch.Generator().manual_seed(100 + L)
+    xt = torch.randn(1, 2, 64, L, generator=g)
+    mx = torch.randn(1, 1, 64, L, generator=g)
+    t = torch.tensor([0.55])
+    with torch.no_grad():
+        out = lat(xt.to(DEV), t.to(DEV), mx.to(DEV))
+    e = rel_l2(out, torch.tensor(golden["ref" + tag][f"latent_c4_L{L}"]))
+    print(f"latent C4 nf=128 L={L} {precision} init_scale={init_scale}: rel-L2 vs reference = {e:.3e} (tol {tol:.1e})")
+    assert e < tol
+
+
+def test_separate_entry_points_on_gpu():
+    """`inference.separate.separate` (src/inference/separate.py:81-99) and `DiffSepModel.separate` (diffsep.py:82-98,
+    quirk Q1 included) through the CUDA path, against the oracle's sampler on the same tape."""
+    from ditsep_b200.inference.separate import scale_output, separate
+    model, sd, cfg = build_model("fp32", DEV, N=3)
+    mix = sampler_inputs(1, 6000)[0][0]  # (1, T), already standardised: normalize_batch is then (nearly) the identity
+    sep = separate(mix, model, dict(N=3, snr=0.5, corrector_steps=1, noise_tape=S.NoiseTape(3)), DEV)
+    assert sep.shape == (1, 2, 6000) and not sep.is_cuda
+    mixn, _, _ = S.normalize_batch_ref(mix[None])
+    x_ref, _ = S.pc_sampler_ref(lambda a, b, c: R.score_forward_ref(sd, cfg, a, b, c), S.MixSDERef(2, 2.0, 0.05, 0.5, N=3),
+                                mixn, S.NoiseTape(3), corrector="ald2", eps=0.03, snr=0.5)
+    ref = scale_output(mix[None], x_ref)
+    e = rel_l2(sep, ref)
+    print(f"inference.separate fp32: rel-L2 vs oracle = {e:.3e}")
+    assert e < 1e-3
+    res = model.separate(mix[None].to(DEV), noise_tape=S.NoiseTape(3), N=3)
+    assert isinstance(res, tuple) and res[1] == 6           # quirk Q1: the raw (x, nfe) of a second sampler run
+    assert rel_l2(res[0], x_ref) < 1e-3
+
+
+def test_ragged_sweep_matches_batch_1_on_gpu():
+    """separate_sharded with mixtures of different lengths in one batch (same 64-frame bucket) against the same
+    mixtures run one by one: per-mixture statistics + length-masked state make a ragged batch equivalent to the
+    reference's batch-1 evaluation (src/evaluate_mp.py:289,311); fp32, per-mixture noise tapes."""
+    from ditsep_b200.utils import shard
+    from ditsep_b200.utils.synth import synth_mixtures
+    model, sd, cfg = build_model("fp32", DEV, N=2)
+    lengths = [9000, 12000, 15000, 10500]          # all pad to 128 frames
+    assert len({shard.padded_frames(n) for n in lengths}) == 1
+    mix, src = synth_mixtures(4, 2, max(lengths), seed=77)
+    mixes = [mix[i, :, :n] for i, n in enumerate(lengths)]
+    refs = [src[i, :, :n] for i, n in enumerate(lengths)]
+    kw = dict(references=refs, device=DEV, sampler_kwargs={"N": 2}, rank=0, world_size=1,
+              noise_tape_factory=lambda i: S.NoiseTape(900 + i).draw)
+    rows1, outs1 = shard.separate_sharded(model, mixes, max_batch=1, **kw)
+    rows4, outs4 = shard.separate_sharded(model, mixes, max_batch=4, **kw)
+    for i in range(4):
+        e = rel_l2(outs4[i], outs1[i])
+        print(f"ragged batch vs batch-1, mixture {i} (T={lengths[i]}): rel-L2 = {e:.3e}")
+        assert outs4[i].shape == (2, lengths[i]) and e < 1e-4
+    assert torch.allclose(rows4, rows1, atol=1e-2)
+    # and batch-1 itself against the oracle run on that mixture alone
+    mixn, _, _ = S.normalize_batch_ref(mixes[1][None])
+    x_ref, _ = S.pc_sampler_ref(lambda a, b, c: R.score_forward_ref(sd, cfg, a, b, c), S.MixSDERef(2, 2.0, 0.05, 0.5, N=2),
+                                mixn, S.NoiseTape(901), corrector="ald2", eps=0.03, snr=0.5)
+    m, s_ = mixes[1].mean(), mixes[1].std().clamp(min=1e-5)
+    assert rel_l2(outs1[1], x_ref[0] * s_ + m) < 1e-3
