@@ -640,7 +640,11 @@ def library_baseline(name, B, dev):
         else:
             cfg = R.ScoreConfig()
             sd = {k: v.to(dev) for k, v in R.make_state_dict(cfg.backbone, seed=0).items()}
-            fwd = lambda xt, t, mx: R.score_forward_ref(sd, cfg, xt, t, mx)  # noqa: E731
+            def fwd(xt, t, mx):  # score_forward_ref, with the STFT ends in fp32 (torch.complex has no bf16) and only
+                feat, n_s, n_pad = R.pre_process_ref(torch.cat((xt, mx), dim=1), cfg, sd["stft.window"])  # the backbone
+                out = R.ncsnpp_forward_ref(sd, cfg.backbone, feat, t, "backbone.")                        # autocast
+                with torch.autocast("cuda", enabled=False):
+                    return R.post_process_ref(out.float(), n_s, n_pad, cfg, sd["stft.window"])
             shape_x, shape_m = (2, c["T"]), (1, c["T"])
         for b in sorted({1, B}):
             xt = torch.randn(b, *shape_x, device=dev)

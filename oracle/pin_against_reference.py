@@ -238,17 +238,34 @@ def main():
               f"SI-SDR ref {sis_ref.mean():.3f} dB oracle {sis_orc.mean():.3f} dB")
         assert nfe == nfe2 == 2 * N and ndraws == 1 + 2 * N
         assert e < 1e-3 and abs(float(sis_ref.mean() - sis_orc.mean())) < 0.01
-        return x_ref, scores, sis_ref, torch.stack(ref_scores_sub).numpy()
+        # the same reference sampler under torch.autocast(bfloat16), same tape: how far bf16 arithmetic moves the
+        # REFERENCE's own trajectory (per-step score rel-L2 against its fp32 run, SI-SDR shift).  This is the yardstick
+        # for the bf16 trajectory tests on weight sets where bf16 cannot meet 1e-2 (errors compound over 2N steps).
+        fp32_sub = list(ref_scores_sub)
+        ref_scores_sub.clear()
+        with TapedRandn(S.NoiseTape(4321)), torch.autocast("cpu", dtype=torch.bfloat16):
+            sampler = sdes.get_pc_sampler("reverse_diffusion", "ald2", sde=sdes.sdes.MixSDE(2, 2.0, 0.05, 0.5, N=N),
+                                          score_fn=lambda x, t, y: ref_recording(x.float(), t, y).float(), y=mixn,
+                                          eps=0.03, snr=0.5, corrector_steps=1, denoise=True)
+            x_ac, _ = sampler()
+        ac_steps = [rel_l2(a.float(), b) for a, b in zip(ref_scores_sub, fp32_sub)]
+        sis_ac, _ = S.si_sdr_pit_ref(src, x_ac.float())
+        ac = np.array([max(ac_steps), abs(float(sis_ac.mean() - sis_ref.mean())), rel_l2(x_ac.float(), x_ref)])
+        print(f"[c] sampler {tag}: reference under bf16 autocast vs its own fp32 run: worst per-step score rel-L2 "
+              f"{ac[0]:.3e}, |dSI-SDR| {ac[1]:.3f} dB, final rel-L2 {ac[2]:.3e}")
+        return x_ref, scores, sis_ref, torch.stack(fp32_sub).numpy(), ac
 
-    x_ref, scores, sis, sub = run_pair(7810, 2, 3, "small")
+    x_ref, scores, sis, sub, ac = run_pair(7810, 2, 3, "small")
     golden["sampler_small_out"] = x_ref.numpy()
     golden["sampler_small_scores_sub"] = sub
+    golden["sampler_small_autocast"] = ac  # [worst per-step rel-L2, |dSI-SDR| dB, final rel-L2] of the reference in bf16
     golden["sampler_small_score_norms"] = np.array(scores)
     golden["sampler_small_sisdr"] = sis.numpy()
     if args.full:
-        x_ref, scores, sis, sub = run_pair(32000, 1, 30, "C1")
+        x_ref, scores, sis, sub, ac = run_pair(32000, 1, 30, "C1")
         np.savez_compressed(os.path.join(GOLDEN, f"sampler_c1{tag}.npz"), out=x_ref.numpy().astype(np.float32),
-                            score_norms=np.array(scores), sisdr=sis.numpy(), scores_sub=sub.astype(np.float32))
+                            score_norms=np.array(scores), sisdr=sis.numpy(), scores_sub=sub.astype(np.float32),
+                            autocast=ac)
 
     # ---- d. OUVESDE + ald with a synthetic score function ---------------------------
     B, T, N = 2, 4096, 5
