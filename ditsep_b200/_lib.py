@@ -21,13 +21,13 @@ class SdeParams(C.Structure):
                 ("sigma_max", C.c_float), ("N", C.c_int32), ("snr", C.c_float)]
 
 
-class StatsSrc(C.Structure):
-    """ditsep_stats_src (include/ditsep_b200.h): where a producer left per-channel {sum, sumsq}."""
+class GnJob(C.Structure):
+    """ditsep_gn_job (include/ditsep_b200.h): one GroupNorm consumer of up to 4 fixed-point statistics sources."""
 
-    _fields_ = [("ptr", C.c_void_p), ("kind", C.c_int32), ("C", C.c_int32), ("ld", C.c_int32), ("n_part", C.c_int32)]
+    _fields_ = [("src_sums", C.c_void_p * 4), ("src_C", C.c_int32 * 4), ("n_src", C.c_int32), ("C", C.c_int32),
+                ("G", C.c_int32), ("eps", C.c_float), ("HW", C.c_int64), ("gamma", C.c_void_p), ("beta", C.c_void_p),
+                ("scale_shift", C.c_void_p)]
 
-
-STATS_NONE, STATS_SPLIT_SUMS = 0, 2
 
 # name -> (restype, argtypes); must list EVERY symbol of include/ditsep_b200.h
 SIGNATURES = {
@@ -47,11 +47,8 @@ SIGNATURES = {
                                      c_float, c_float, c_int, c_void_p]),
     "ditsep_expand_istft": (c_int, [c_void_p, c_void_p, c_void_p, c_int, c_int, c_int64, c_int, c_float, c_float,
                                     c_void_p]),
-    "ditsep_gn_stats": (c_int, [c_void_p, c_int, c_int, c_int64, c_int, c_int, c_int, c_void_p, c_void_p, c_float,
-                                c_void_p, c_int, c_void_p, c_void_p]),
-    "ditsep_gn_partial_sums": (c_int, [c_void_p, c_int, c_int, c_int64, c_int, c_int, c_void_p, c_int, c_void_p]),
-    "ditsep_gn_finalize": (c_int, [C.POINTER(StatsSrc), c_int, c_int, c_int64, c_int, c_void_p, c_void_p, c_float,
-                                   c_void_p, c_void_p]),
+    "ditsep_gn_sums": (c_int, [c_void_p, c_int, c_int, c_int64, c_int, c_int, c_void_p, c_void_p]),
+    "ditsep_gn_finalize": (c_int, [C.POINTER(GnJob), c_int, c_void_p]),
     "ditsep_gn_small": (c_int, [c_void_p, c_int, c_int, c_int64, c_int, c_int, c_int, c_void_p, c_void_p, c_float, c_int,
                                 c_void_p, c_int, c_void_p]),
     "ditsep_gn_apply": (c_int, [c_void_p, c_int, c_int, c_int64, c_int, c_int, c_void_p, c_int, c_void_p, c_int,
@@ -67,11 +64,9 @@ SIGNATURES = {
                                               c_int, c_int, c_void_p, c_int, c_int]),
     "ditsep_debug_conv_trace": (None, [c_void_p]),
     "ditsep_conv_tc_plan_destroy": (None, [c_void_p]),
-    "ditsep_conv_tc_stats_layout": (c_int, [c_void_p, C.POINTER(StatsSrc)]),
+    "ditsep_conv_tc_has_stats": (c_int, [c_void_p]),
     "ditsep_conv_tc_run": (c_int, [c_void_p, c_void_p, c_void_p, c_int, c_void_p, c_int, c_int, c_float, c_void_p,
                                    c_int, c_int, c_void_p, c_void_p]),
-    "ditsep_conv_tc_run_gn": (c_int, [c_void_p, c_void_p, c_int, c_void_p, c_void_p, c_int, c_void_p, c_int, c_int,
-                                      c_float, c_void_p, c_int, c_int, c_void_p, c_void_p]),
     "ditsep_attention": (c_int, [c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_int, c_int, c_void_p, c_int,
                                  c_void_p]),
     "ditsep_temb_mlp": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_int,

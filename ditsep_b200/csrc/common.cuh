@@ -167,6 +167,22 @@ __device__ __forceinline__ float warp_max(float v) {
   return v;
 }
 
+// ---- order-independent fixed-point sums (GroupNorm statistics) --------------------------------------------------
+// A sum is kept as two 64-bit integers {integer part, fraction in units of 2^-32}; a float v is split EXACTLY
+// (floorf(v) and v - floorf(v) are exact in fp32; bits below 2^-32 of the fraction are dropped) and both parts are
+// added with integer atomics.  Integer addition commutes, so the total does not depend on the order in which CTAs
+// arrive: statistics are bit-reproducible and batch-invariant, with no per-CTA partial buffers and no finalize pass
+// over hundreds of partials.  Range |sum| < 2^62, resolution 2^-32 absolute per addend.
+__device__ __forceinline__ void fx_add(long long* dst, float v) {
+  const float fl = floorf(v);
+  const float fr = v - fl;  // in [0, 1), exact
+  atomicAdd(reinterpret_cast<unsigned long long*>(dst), (unsigned long long)(long long)fl);
+  atomicAdd(reinterpret_cast<unsigned long long*>(dst + 1), (unsigned long long)(fr * 4294967296.0f));
+}
+__device__ __forceinline__ double fx_value(const long long* p) {
+  return (double)p[0] + (double)p[1] * (1.0 / 4294967296.0);
+}
+
 inline int ceil_div(int64_t a, int64_t b) { return (int)((a + b - 1) / b); }
 
 }  // namespace ditsep

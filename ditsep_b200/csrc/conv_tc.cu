@@ -62,11 +62,9 @@ struct ConvTcParams {
   // tile kernel
   int num_tiles, tiles_per_image, chunks, w_resident, a_stages, w_stages;
   int halo, row_pitch, a_rows, a_stage_bytes;
-  const float* in_ss;      // nullable: per-(image, input channel) scale / shift [B][2][Cin] applied to the INPUT tile
-  int in_silu;             //   in shared memory before the MMAs read it: a = silu?(x * scale + shift), zero outside the image
   int xchunks;             // fused shortcut: 64-channel blocks of a second input x accumulated as a 1x1 tap (0 = none)
-  float* stats;            // nullable: partial sums [B][segs_per_image][4][ld_part][2]
-  int seg_len, segs_per_image, ld_part;
+  long long* stats;        // nullable: fixed-point per-channel sums [B][Cout][4] (common.cuh fx_add), ADDED to
+  int seg_len, segs_per_image;
   long long* trace;        // debug (ditsep_debug_conv_trace): [4 CTAs][kTraceTiles][8] clock64 stamps, else nullptr
 };
 
@@ -300,12 +298,13 @@ __global__ void __launch_bounds__(kThreads) conv_tc_kernel(const __grid_constant
 
 // ---- kernel 2: 8 x 16 pixel tiles with halo, persistent CTAs over contiguous segment ranges ----
 constexpr int kTileW = 8, kTileH = 16;
-// Warps: 0 TMA producer, 1 TMEM allocator + MMA issuer (even tiles), 2 MMA issuer (odd tiles), 3 idle; then, in the
-// kXf instantiation only, 4-7: GroupNorm + SiLU of the landed A tiles in place in shared memory; then 16 epilogue warps.
-// 20 warps x 96 registers fill the register file; the kXf variant runs 24 warps x 80 registers.
-constexpr int kXformWarp0 = 4, kXformWarps = 4;
+// Warps: 0 TMA producer, 1 TMEM allocator + MMA issuer (even tiles), 2 MMA issuer (odd tiles), 3 idle; then 16 epilogue
+// warps.  20 warps x 96 registers fill the register file.  (Round 1 also carried four warps that applied the INPUT's
+// GroupNorm + SiLU to the landed A tiles in shared memory; measured slower than a separate pass and removed --
+// DESIGN.md, negative results.)
+constexpr int kCtrlWarps = 4;
 constexpr int kEpiWarps = 16;   // warp w: TMEM lane quadrant w % 4, output channels [16*((w-4)/4), +16)
-constexpr int tile_threads(bool xf) { return ((xf ? 8 : 4) + kEpiWarps) * 32; }
+constexpr int kTileThreads = (kCtrlWarps + kEpiWarps) * 32;
 constexpr int kMaxAStages = 4, kMaxWStages = 4;
 constexpr int kTileMaxBN = 64;
 
@@ -341,15 +340,14 @@ struct TileWalk {
   }
 };
 
-template <int KS, bool kRes, bool kFast, bool kXf>
-__global__ void __launch_bounds__(tile_threads(kXf), 1) conv_tc_tile_kernel(const __grid_constant__ CUtensorMap mapA,
+template <int KS, bool kRes, bool kFast>
+__global__ void __launch_bounds__(kTileThreads, 1) conv_tc_tile_kernel(const __grid_constant__ CUtensorMap mapA,
                                                                        const __grid_constant__ CUtensorMap mapW,
                                                                        const __grid_constant__ CUtensorMap mapX,
                                                                        const __grid_constant__ ConvTcParams p) {
   constexpr int kTaps = KS * KS, kHalo = KS / 2, kRowPitch = kTileW + 2 * kHalo;
-  constexpr int kCtrlWarps = kXf ? 8 : 4;
   extern __shared__ uint8_t smem_raw[];
-  __shared__ __align__(8) uint64_t bar_a_full[kMaxAStages], bar_a_empty[kMaxAStages], bar_a_ready[kMaxAStages];
+  __shared__ __align__(8) uint64_t bar_a_full[kMaxAStages], bar_a_empty[kMaxAStages];
   __shared__ __align__(8) uint64_t bar_w_full[kMaxWStages], bar_w_empty[kMaxWStages];
   __shared__ __align__(8) uint64_t bar_w_res, bar_acc_full[2], bar_acc_empty[2], bar_turn[2];
   __shared__ uint32_t tmem_base_slot;
@@ -366,7 +364,6 @@ __global__ void __launch_bounds__(tile_threads(kXf), 1) conv_tc_tile_kernel(cons
     for (int s = 0; s < kMaxAStages; ++s) {
       mbar_init(smem_u32(&bar_a_full[s]), 1);
       mbar_init(smem_u32(&bar_a_empty[s]), 1);
-      mbar_init(smem_u32(&bar_a_ready[s]), kXformWarps);
     }
     for (int s = 0; s < kMaxWStages; ++s) {
       mbar_init(smem_u32(&bar_w_full[s]), 1);
@@ -499,7 +496,7 @@ __global__ void __launch_bounds__(tile_threads(kXf), 1) conv_tc_tile_kernel(cons
           const bool last_st = pos == nsteps - 1;
           const int widx = is_x ? nc * kTaps + (xfirst ? pos : pos - nc) : (xfirst ? pos - nx : pos) * kTaps;
           const uint32_t w_lo = w_base + (uint32_t)widx * w_step;
-          mbar_wait(smem_u32(kXf ? &bar_a_ready[sa] : &bar_a_full[sa]), pa);
+          mbar_wait(smem_u32(&bar_a_full[sa]), pa);
           if (last_st && lane == 0) mbar_arrive(smem_u32(&bar_turn[my ^ 1u]));  // the ring is the other warp's now
           tc_fence_after();
           if (pos == 0 && lane == 0) trace_stamp(p, it, 1);
@@ -548,7 +545,7 @@ __global__ void __launch_bounds__(tile_threads(kXf), 1) conv_tc_tile_kernel(cons
         const uint32_t tmem_d = tmem_acc + ab * (uint32_t)p.BN;
         uint32_t w_lo;
         for (int ch = 0; ch < p.chunks; ++ch) {
-          mbar_wait(smem_u32(kXf ? &bar_a_ready[sa] : &bar_a_full[sa]), pa);
+          mbar_wait(smem_u32(&bar_a_full[sa]), pa);
           tc_fence_after();
           const uint32_t a_lo = ((a_ring + (uint32_t)(sa * p.a_stage_bytes)) >> 4) | lbo;
           constexpr int kRow16 = 128 >> 4;
@@ -580,83 +577,6 @@ __global__ void __launch_bounds__(tile_threads(kXf), 1) conv_tc_tile_kernel(cons
             __syncwarp();
             if (++sw == p.w_stages) { sw = 0; pw ^= 1u; }
           }
-          if (++sa == p.a_stages) { sa = 0; pa ^= 1u; }
-        }
-      }
-    }
-  } else if (kXf && warp >= kXformWarp0 && warp < kXformWarp0 + kXformWarps) {
-    // GroupNorm + SiLU of the conv INPUT, fused: the producing layer stored the raw tensor; its normalisation
-    // (layerspp.py:297,318: act(GroupNorm(x))) is applied here to each landed A tile, in place in shared memory, before
-    // the MMAs read it -- instead of a separate pass that reads and rewrites the whole tensor in HBM.
-    // One thread = one 16-byte channel pack (fixed for its whole life: scale / shift in registers) of every 16th row of
-    // the halo box.  Pixels outside the image stay zero (TMA zero fill): the conv pads the ACTIVATED tensor.
-    if (kXf) {
-      griddep_wait();  // in_scale_shift comes from gn_finalize
-      const int t = (int)threadIdx.x - kXformWarp0 * 32;
-      const int lc = t & 7;
-      const bool xfirst = kRes && p.xchunks > 0 && p.a_stages >= p.xchunks + 2;
-      const int nsteps = p.chunks + (kRes ? p.xchunks : 0);
-      int sa = 0;
-      uint32_t pa = 0;
-      const bool silu = p.in_silu != 0;
-      TileWalk tw;
-      for (tw.init(p); !tw.done(); tw.next(p)) {
-        const int y0 = tw.ty * kTileH - kHalo, x0 = tw.tx * kTileW - kHalo;
-        for (int pos = 0; pos < nsteps; ++pos) {
-          const bool is_x = kRes && (xfirst ? pos < p.xchunks : pos >= p.chunks);
-          mbar_wait_sleep(smem_u32(&bar_a_full[sa]), pa);
-          if (!is_x) {
-            const int ch = xfirst ? pos - p.xchunks : pos;
-            float sc[8], sh[8];
-            const float* ssp = p.in_ss + ((int64_t)tw.b * 2) * p.Cin + ch * kBlockK + lc * 8;
-            Pack8<float>::load(ssp, sc);
-            Pack8<float>::load(ssp + p.Cin, sh);
-            // Four rows per trip, ALL loads before any store: with one load-compute-store per trip the compiler must
-            // keep every load behind the previous trip's store (same shared array), which serialised ~400-cycle
-            // dependent chains -- 4400 cycles per chunk against 2850 of MMA work (r1m / r1t).
-            const uint32_t stage_u32 = a_ring + (uint32_t)(sa * p.a_stage_bytes);
-            constexpr int kStep = kXformWarps * 4, kBatch = 4;
-            for (int r0 = t >> 3; r0 < p.a_rows; r0 += kStep * kBatch) {
-              uint4 raw[kBatch];
-              uint32_t addr[kBatch];
-              bool ok[kBatch];
-#pragma unroll
-              for (int u = 0; u < kBatch; ++u) {
-                const int r = r0 + u * kStep;
-                const int hy = r / kRowPitch, hx = r - hy * kRowPitch;
-                ok[u] = r < p.a_rows && (unsigned)(y0 + hy) < (unsigned)p.H && (unsigned)(x0 + hx) < (unsigned)p.W;
-                addr[u] = stage_u32 + (uint32_t)(r * 128 + ((lc ^ (r & 7)) << 4));  // 128-byte swizzle
-                raw[u] = make_uint4(0, 0, 0, 0);
-                if (ok[u])
-                  asm volatile("ld.shared.v4.u32 {%0, %1, %2, %3}, [%4];"
-                               : "=r"(raw[u].x), "=r"(raw[u].y), "=r"(raw[u].z), "=r"(raw[u].w)
-                               : "r"(addr[u]));
-              }
-#pragma unroll
-              for (int u = 0; u < kBatch; ++u) {
-                const uint32_t wv[4] = {raw[u].x, raw[u].y, raw[u].z, raw[u].w};
-                uint32_t o[4];
-#pragma unroll
-                for (int j = 0; j < 4; ++j) {
-                  float lo = fmaf(__uint_as_float(wv[j] << 16), sc[2 * j], sh[2 * j]);
-                  float hi = fmaf(__uint_as_float(wv[j] & 0xffff0000u), sc[2 * j + 1], sh[2 * j + 1]);
-                  if (silu) {
-                    lo = p.in_silu == 2 ? silu_tanh_f(lo) : silu_f(lo);
-                    hi = p.in_silu == 2 ? silu_tanh_f(hi) : silu_f(hi);
-                  }
-                  const __nv_bfloat162 hh = __floats2bfloat162_rn(lo, hi);
-                  o[j] = *reinterpret_cast<const uint32_t*>(&hh);
-                }
-                if (ok[u])
-                  asm volatile("st.shared.v4.u32 [%0], {%1, %2, %3, %4};" ::"r"(addr[u]), "r"(o[0]), "r"(o[1]), "r"(o[2]),
-                               "r"(o[3])
-                               : "memory");
-              }
-            }
-            asm volatile("fence.proxy.async.shared::cta;" ::: "memory");  // generic writes -> visible to the tensor core
-          }
-          __syncwarp();
-          if (lane == 0) mbar_arrive(smem_u32(&bar_a_ready[sa]));
           if (++sa == p.a_stages) { sa = 0; pa ^= 1u; }
         }
       }
@@ -819,10 +739,14 @@ __global__ void __launch_bounds__(tile_threads(kXf), 1) conv_tc_tile_kernel(cons
         s[0] += __shfl_xor_sync(0xffffffffu, s[0], 1);
         sq[0] += __shfl_xor_sync(0xffffffffu, sq[0], 1);
         const int c = ((lane >> 4) & 1) * 8 + ((lane >> 3) & 1) * 4 + ((lane >> 2) & 1) * 2 + ((lane >> 1) & 1);
-        if ((lane & 1) == 0 && has_cols) {  // partials [B][segs_per_image][4 quadrants][ld_part][2]
-          float2* dst = reinterpret_cast<float2*>(p.stats) +
-                        ((int64_t)(pb * p.segs_per_image + tw.sidx) * 4 + q) * p.ld_part + n0 + c0 + c;
-          *dst = make_float2(s[0], sq[0]);
+        // Order-independent fixed-point accumulation (fx_add): integer atomics commute, so the per-image sums -- and
+        // every bf16 rounding downstream -- are bit-reproducible and independent of the batch size and of which CTA
+        // handled which segment; what is added here (one fp32 partial per segment, quadrant and channel) is a function
+        // of the image shape only.
+        if ((lane & 1) == 0 && has_cols && n0 + c0 + c < p.Cout) {
+          long long* dst = p.stats + ((int64_t)pb * p.Cout + n0 + c0 + c) * 4;
+          fx_add(dst, s[0]);
+          fx_add(dst + 2, sq[0]);
         }
 #pragma unroll
         for (int j = 0; j < 16; ++j) s[j] = sq[j] = 0.f;
@@ -966,7 +890,6 @@ extern "C" int ditsep_conv_tc_plan_create_sc(ditsep_conv_plan** plan, const void
     p.bw = kTileW; p.bh = kTileH; p.bb = 1;
     if (cout_pad > kTileMaxBN) p.BN = kTileMaxBN;
     p.n_tiles = ceil_div(cout_pad, p.BN);
-    p.ld_part = p.n_tiles * p.BN;
     p.tmem_cols = pow2_ceil(2 * p.BN) < 32 ? 32 : pow2_ceil(2 * p.BN);
     const size_t w_tile = (size_t)p.BN * 128;
     const size_t budget = 222 * 1024;  // dynamic; static (barriers + reduction scratch) is ~2.3 KB
@@ -1051,11 +974,8 @@ extern "C" int ditsep_conv_tc_plan_create_sc(ditsep_conv_plan** plan, const void
   if (!attr_known || !attr_set[attr_dev].load(std::memory_order_acquire)) {
     DITSEP_CUDA(cudaFuncSetAttribute(conv_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                      1024 + 192 * 1024));
-#define DITSEP_TILE_ATTR(KS, RES, FAST)                                                                              \
-  DITSEP_CUDA(cudaFuncSetAttribute(conv_tc_tile_kernel<KS, RES, FAST, false>,                                       \
-                                   cudaFuncAttributeMaxDynamicSharedMemorySize, 224 * 1024));                       \
-  DITSEP_CUDA(cudaFuncSetAttribute(conv_tc_tile_kernel<KS, RES, FAST, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, \
-                                   224 * 1024))
+#define DITSEP_TILE_ATTR(KS, RES, FAST) \
+  DITSEP_CUDA(cudaFuncSetAttribute(conv_tc_tile_kernel<KS, RES, FAST>, cudaFuncAttributeMaxDynamicSharedMemorySize, 224 * 1024))
     DITSEP_TILE_ATTR(1, true, true); DITSEP_TILE_ATTR(1, true, false); DITSEP_TILE_ATTR(1, false, true);
     DITSEP_TILE_ATTR(1, false, false); DITSEP_TILE_ATTR(3, true, true); DITSEP_TILE_ATTR(3, true, false);
     DITSEP_TILE_ATTR(3, false, true); DITSEP_TILE_ATTR(3, false, false);
@@ -1071,32 +991,12 @@ extern "C" void ditsep_debug_conv_trace(void* buf) { g_conv_trace = reinterpret_
 
 extern "C" void ditsep_conv_tc_plan_destroy(ditsep_conv_plan* plan) { delete plan; }
 
-extern "C" int ditsep_conv_tc_stats_layout(const ditsep_conv_plan* plan, ditsep_stats_src* layout) {
-  DITSEP_REQUIRE(plan && layout, "conv_tc_stats_layout: null pointer");
-  memset(layout, 0, sizeof(*layout));
-  if (!plan->tile) return 0;  // kind stays DITSEP_STATS_NONE: this plan cannot produce statistics
-  // [B][segs_per_image][4 TMEM lane quadrants][ld][2]: one partial per (segment, quadrant)
-  layout->kind = DITSEP_STATS_SPLIT_SUMS;
-  layout->C = plan->p.Cout;
-  layout->ld = plan->p.ld_part;
-  layout->n_part = plan->p.segs_per_image * 4;
-  return 0;
-}
+extern "C" int ditsep_conv_tc_has_stats(const ditsep_conv_plan* plan) { return plan && plan->tile ? 1 : 0; }
 
 extern "C" int ditsep_conv_tc_run(const ditsep_conv_plan* plan, const float* bias, const float* bias_b, int ld_bias_b,
                                   const void* residual, int res_dtype, int ld_res, float out_scale, void* out,
-                                  int out_dtype, int ld_out, float* stats, void* stream) {
-  return ditsep_conv_tc_run_gn(plan, nullptr, 0, bias, bias_b, ld_bias_b, residual, res_dtype, ld_res, out_scale, out,
-                               out_dtype, ld_out, stats, stream);
-}
-
-extern "C" int ditsep_conv_tc_run_gn(const ditsep_conv_plan* plan, const float* in_scale_shift, int in_silu,
-                                     const float* bias, const float* bias_b, int ld_bias_b, const void* residual,
-                                     int res_dtype, int ld_res, float out_scale, void* out, int out_dtype, int ld_out,
-                                     float* stats, void* stream) {
+                                  int out_dtype, int ld_out, long long* stats, void* stream) {
   DITSEP_REQUIRE(plan && out, "conv_tc_run: null pointer");
-  DITSEP_REQUIRE(!in_scale_shift || plan->tile,
-                 "conv_tc_run_gn: the fused input GroupNorm needs the tile kernel (image >= 8 x 16)");
   DITSEP_REQUIRE(out_dtype == DITSEP_F32 || out_dtype == DITSEP_BF16, "conv_tc_run: unknown out dtype %d", out_dtype);
   DITSEP_REQUIRE(!residual || res_dtype == DITSEP_F32 || res_dtype == DITSEP_BF16, "conv_tc_run: unknown residual dtype");
   DITSEP_REQUIRE(ld_out >= plan->p.Cout, "conv_tc_run: ld_out=%d < Cout=%d", ld_out, plan->p.Cout);
@@ -1106,7 +1006,6 @@ extern "C" int ditsep_conv_tc_run_gn(const ditsep_conv_plan* plan, const float* 
   p.residual = residual; p.res_dtype = res_dtype; p.ld_res = ld_res;
   p.out_scale = out_scale; p.out = out; p.out_dtype = out_dtype; p.ld_out = ld_out;
   p.stats = stats;
-  p.in_ss = in_scale_shift; p.in_silu = in_silu;
   p.trace = g_conv_trace;
   if (plan->tile) {
     dim3 grid((unsigned)plan->grid_x, (unsigned)p.n_tiles);
@@ -1126,17 +1025,10 @@ extern "C" int ditsep_conv_tc_run_gn(const ditsep_conv_plan* plan, const float* 
     lcfg.stream = st;
     lcfg.attrs = lattr;
     lcfg.numAttrs = pdl ? 1 : 0;
-#define DITSEP_TILE_LAUNCH(KS, RES, FAST)                                                                            \
-  do {                                                                                                               \
-    if (p.in_ss) {                                                                                                   \
-      lcfg.blockDim = dim3(tile_threads(true));                                                                      \
-      DITSEP_CUDA(cudaLaunchKernelEx(&lcfg, conv_tc_tile_kernel<KS, RES, FAST, true>, plan->mapA, plan->mapW,        \
-                                     plan->mapX, p));                                                                \
-    } else {                                                                                                         \
-      lcfg.blockDim = dim3(tile_threads(false));                                                                     \
-      DITSEP_CUDA(cudaLaunchKernelEx(&lcfg, conv_tc_tile_kernel<KS, RES, FAST, false>, plan->mapA, plan->mapW,       \
-                                     plan->mapX, p));                                                                \
-    }                                                                                                                \
+#define DITSEP_TILE_LAUNCH(KS, RES, FAST)                                                                             \
+  do {                                                                                                                \
+    lcfg.blockDim = dim3(kTileThreads);                                                                               \
+    DITSEP_CUDA(cudaLaunchKernelEx(&lcfg, conv_tc_tile_kernel<KS, RES, FAST>, plan->mapA, plan->mapW, plan->mapX, p)); \
   } while (0)
     if (p.ksize == 3) {
       if (p.w_resident) { if (fast) DITSEP_TILE_LAUNCH(3, true, true); else DITSEP_TILE_LAUNCH(3, true, false); }

@@ -19,12 +19,13 @@
 namespace ditsep {
 
 // ------------------------------------------------------------------- GroupNorm statistics
-// grid (nsplit, B); block = cv * ppb threads (cv = C/8 channel packs, ppb pixels in flight).
-// Each thread keeps sum / sum-of-squares of its 8 channels in registers over its pixels.
-// partial: [B][nsplit][C][2].
+// Explicit statistics pass (for tensors whose producer left none): grid (nsplit, B); block = cv * ppb threads (cv = C/8
+// channel packs, ppb pixels in flight).  Each thread keeps sum / sum-of-squares of its 8 channels in registers over its
+// pixels; the CTA combines them in shared memory and ADDS one fp32 partial per channel to the fixed-point sums
+// [B][C][4] (fx_add).  nsplit is a function of the image shape only, so what is added never depends on the batch.
 template <typename T>
-__global__ void __launch_bounds__(256) gn_partial_kernel(const T* __restrict__ x, int64_t HW, int C, int ld, int cv,
-                                                         int ppb, float* __restrict__ partial) {
+__global__ void __launch_bounds__(256) gn_sums_kernel(const T* __restrict__ x, int64_t HW, int C, int ld, int cv, int ppb,
+                                                      long long* __restrict__ sums) {
   griddep_launch_dependents();
   griddep_wait();
   extern __shared__ float red[];  // [ppb][C][2]
@@ -59,133 +60,52 @@ __global__ void __launch_bounds__(256) gn_partial_kernel(const T* __restrict__ x
       a += red[(j * C + c) * 2];
       bq += red[(j * C + c) * 2 + 1];
     }
-    float* dst = partial + (((int64_t)b * nsplit + split) * C + c) * 2;
-    dst[0] = a;
-    dst[1] = bq;
+    long long* dst = sums + ((int64_t)b * C + c) * 4;
+    fx_add(dst, a);
+    fx_add(dst + 2, bq);
   }
 }
 
-// grid B, block 256: combine partials in double, produce per-(b,c) scale / shift.
-__global__ void __launch_bounds__(256) gn_finalize_kernel(const float* __restrict__ partial, int nsplit, int64_t HW, int C,
-                                                          int G, const float* __restrict__ gamma,
-                                                          const float* __restrict__ beta, float eps,
-                                                          float* __restrict__ scale_shift) {
-  extern __shared__ double sh[];  // [C][2] then [G][2]
-  double* chs = sh;
-  double* grp = sh + 2 * C;
-  const int b = blockIdx.x;
-  for (int c = threadIdx.x; c < C; c += blockDim.x) {
-    double a = 0.0, q = 0.0;
-    for (int s = 0; s < nsplit; ++s) {
-      const float* src = partial + (((int64_t)b * nsplit + s) * C + c) * 2;
-      a += (double)src[0];
-      q += (double)src[1];
-    }
-    chs[2 * c] = a;
-    chs[2 * c + 1] = q;
-  }
-  __syncthreads();
-  const int cpg = C / G;
+// Per-(b, c) scale / shift of one GroupNorm consumer from the fixed-point sums of up to 4 producers laid end to end
+// along the channel axis (torch.cat([h, skip], dim=1) feeding GroupNorm_0, ncsnpp.py:413 + layerspp.py:297).
+// One image per call; executed by a whole CTA (any block size).  The arithmetic from the exact integer sums on is
+// double precision in a fixed order: bit-reproducible.  grp: shared scratch of >= 2 * G doubles.
+__device__ __forceinline__ void gn_job_image(const ditsep_gn_job& job, int b, double* grp) {
+  const int C = job.C, G = job.G, cpg = C / G;
   for (int g = threadIdx.x; g < G; g += blockDim.x) {
     double a = 0.0, q = 0.0;
     for (int i = 0; i < cpg; ++i) {
-      a += chs[2 * (g * cpg + i)];
-      q += chs[2 * (g * cpg + i) + 1];
+      int cc = g * cpg + i, k = 0;
+      while (k < job.n_src - 1 && cc >= job.src_C[k]) {
+        cc -= job.src_C[k];
+        ++k;
+      }
+      const long long* sp = job.src_sums[k] + ((int64_t)b * job.src_C[k] + cc) * 4;
+      a += fx_value(sp);
+      q += fx_value(sp + 2);
     }
-    double n = (double)HW * cpg;
-    double mean = a / n;
+    const double n = (double)job.HW * cpg, mean = a / n;
     double var = q / n - mean * mean;
     if (var < 0.0) var = 0.0;
     grp[2 * g] = mean;
-    grp[2 * g + 1] = 1.0 / sqrt(var + (double)eps);
+    grp[2 * g + 1] = 1.0 / sqrt(var + (double)job.eps);
   }
   __syncthreads();
   for (int c = threadIdx.x; c < C; c += blockDim.x) {
     const int g = c / cpg;
-    double sc = grp[2 * g + 1] * (double)gamma[c];
-    scale_shift[((int64_t)b * 2) * C + c] = (float)sc;
-    scale_shift[((int64_t)b * 2 + 1) * C + c] = (float)((double)beta[c] - grp[2 * g] * sc);
+    const double sc = grp[2 * g + 1] * (double)job.gamma[c];
+    job.scale_shift[((int64_t)b * 2) * C + c] = (float)sc;
+    job.scale_shift[((int64_t)b * 2 + 1) * C + c] = (float)((double)job.beta[c] - grp[2 * g] * sc);
   }
+  __syncthreads();
 }
 
-// Per-channel {sum, sum of squares} left by the producers of the normalised tensor (up to 4
-// sources laid end to end along the channel axis, see ditsep_stats_src) -> per-(b,c) scale / shift.
-// grid (group chunks, B), block 256: a CTA owns gpc whole groups (nch = gpc * C/G channels) so that many
-// CTAs share the partial-sum traffic of one image (one CTA per image was latency-bound: 18 us for 8 MB,
-// r1e ncu).  Fixed summation order (a function of C, G and n_part only), double accumulation.
-struct StatsSrcs {
-  ditsep_stats_src s[4];
-  int n;
-};
-
-__global__ void __launch_bounds__(256) gn_finalize_srcs_kernel(const StatsSrcs srcs, int64_t HW, int C, int G, int gpc,
-                                                               const float* __restrict__ gamma,
-                                                               const float* __restrict__ beta, float eps,
-                                                               float* __restrict__ scale_shift) {
+// grid B, block 128: a few hundred bytes of sums per image (the round-1 finalize read ~8 MB of per-CTA partials).
+__global__ void __launch_bounds__(128) gn_finalize_kernel(const ditsep_gn_job job) {
   griddep_launch_dependents();
   griddep_wait();
-  extern __shared__ double sh[];  // [nj][nch][2]
-  __shared__ double grp[32][2];
-  const int b = blockIdx.y;
-  const int cpg = C / G;
-  const int g0 = blockIdx.x * gpc;
-  const int ng = min(gpc, G - g0);
-  const int c0 = g0 * cpg, nch = ng * cpg;
-  // thread -> (channel c of the chunk, slice j of nj): slice j adds partials j, j+nj, ...; the nj slice sums of
-  // a channel are then added in order
-  const int nj = max(1, (int)blockDim.x / (gpc * cpg));
-  for (int idx = threadIdx.x; idx < nj * nch; idx += blockDim.x) {
-    const int cl = idx % nch, j = idx / nch;
-    int cc = c0 + cl, i = 0;
-    while (i < srcs.n - 1 && cc >= srcs.s[i].C) {
-      cc -= srcs.s[i].C;
-      ++i;
-    }
-    const ditsep_stats_src& src = srcs.s[i];
-    double a = 0.0, q = 0.0;
-    const float2* sp = reinterpret_cast<const float2*>(src.ptr) + (int64_t)b * src.n_part * src.ld + cc;
-    int k = j;
-    for (; k + 7 * nj < src.n_part; k += 8 * nj) {  // 8 independent loads in flight, added in index order
-      float2 v[8];
-#pragma unroll
-      for (int u = 0; u < 8; ++u) v[u] = sp[(int64_t)(k + u * nj) * src.ld];
-#pragma unroll
-      for (int u = 0; u < 8; ++u) {
-        a += (double)v[u].x;
-        q += (double)v[u].y;
-      }
-    }
-    for (; k < src.n_part; k += nj) {
-      const float2 v = sp[(int64_t)k * src.ld];
-      a += (double)v.x;
-      q += (double)v.y;
-    }
-    sh[(j * nch + cl) * 2] = a;
-    sh[(j * nch + cl) * 2 + 1] = q;
-  }
-  __syncthreads();
-  if ((int)threadIdx.x < ng) {
-    const int g = threadIdx.x;
-    double a = 0.0, q = 0.0;
-    for (int i = 0; i < cpg; ++i)
-      for (int j = 0; j < nj; ++j) {
-        a += sh[(j * nch + g * cpg + i) * 2];
-        q += sh[(j * nch + g * cpg + i) * 2 + 1];
-      }
-    const double n = (double)HW * cpg;
-    const double mean = a / n;
-    double var = q / n - mean * mean;
-    if (var < 0.0) var = 0.0;
-    grp[g][0] = mean;
-    grp[g][1] = 1.0 / sqrt(var + (double)eps);
-  }
-  __syncthreads();
-  for (int cl = threadIdx.x; cl < nch; cl += blockDim.x) {
-    const int g = cl / cpg, c = c0 + cl;
-    const double sc = grp[g][1] * (double)gamma[c];
-    scale_shift[((int64_t)b * 2) * C + c] = (float)sc;
-    scale_shift[((int64_t)b * 2 + 1) * C + c] = (float)((double)beta[c] - grp[g][0] * sc);
-  }
+  __shared__ double grp[2 * 64];
+  gn_job_image(job, blockIdx.x, grp);
 }
 
 // ------------------------------------------------------------------- normalise + SiLU
@@ -836,69 +756,56 @@ static int grid_for(int64_t total, int threads = 256) {
 
 using namespace ditsep;
 
-static int launch_gn_partial(const void* x, int dtype, int B, int64_t HW, int C, int ld, float* partial, int nsplit,
-                             cudaStream_t st) {
-  DITSEP_REQUIRE(x && partial, "gn partial sums: null pointer");
-  DITSEP_REQUIRE(C % 8 == 0 && ld % 8 == 0 && C <= ld, "gn partial sums: C=%d ld=%d must be multiples of 8, C<=ld", C, ld);
-  DITSEP_REQUIRE(B > 0 && HW > 0 && nsplit > 0 && nsplit <= HW, "gn partial sums: bad B/HW/nsplit");
+// pixel splits of the explicit statistics pass: a function of the image shape only (batch invariance)
+static int gn_nsplit(int64_t HW, int C) {
+  const int ppb = 256 / (C / 8) > 0 ? 256 / (C / 8) : 1;
+  int64_t n = HW / ((int64_t)ppb * 8);
+  if (n < 1) n = 1;
+  if (n > 64) n = 64;
+  return (int)n;
+}
+
+extern "C" int ditsep_gn_sums(const void* x, int dtype, int B, int64_t HW, int C, int ld, long long* sums, void* stream) {
+  DITSEP_REQUIRE(x && sums, "gn_sums: null pointer");
+  DITSEP_REQUIRE(B > 0 && HW > 0 && C > 0 && C % 8 == 0 && C <= 2048 && ld >= C, "gn_sums: bad sizes B=%d HW=%lld C=%d ld=%d",
+                 B, (long long)HW, C, ld);
   const int cv = C / 8;
-  DITSEP_REQUIRE(cv <= 256, "gn partial sums: C=%d too wide", C);
-  const int ppb = 256 / cv;
-  dim3 grid(nsplit, B);
-  size_t smem = (size_t)ppb * C * 2 * sizeof(float);
-  if (dtype == DITSEP_F32)
-    DITSEP_CUDA(launch_pdl<2>(gn_partial_kernel<float>, dim3(grid), dim3(256), smem, st, (const float*)x, HW, C, ld, cv, ppb, partial));
-  else if (dtype == DITSEP_BF16)
-    DITSEP_CUDA(launch_pdl<2>(gn_partial_kernel<bf16>, dim3(grid), dim3(256), smem, st, (const bf16*)x, HW, C, ld, cv, ppb, partial));
-  else
-    DITSEP_REQUIRE(false, "gn partial sums: unknown dtype %d", dtype);
-  return check_launch("gn_partial_kernel");
-}
-
-extern "C" int ditsep_gn_partial_sums(const void* x, int dtype, int B, int64_t HW, int C, int ld, float* partial,
-                                      int nsplit, void* stream) {
-  return launch_gn_partial(x, dtype, B, HW, C, ld, partial, nsplit, (cudaStream_t)stream);
-}
-
-extern "C" int ditsep_gn_stats(const void* x, int dtype, int B, int64_t HW, int C, int ld, int G, const float* gamma,
-                               const float* beta, float eps, float* partial, int nsplit, float* scale_shift,
-                               void* stream) {
-  DITSEP_REQUIRE(gamma && beta && scale_shift, "gn_stats: null pointer");
-  DITSEP_REQUIRE(G > 0 && C % G == 0, "gn_stats: C=%d not divisible by G=%d", C, G);
+  int ppb = 256 / cv;
+  if (ppb < 1) ppb = 1;
+  DITSEP_REQUIRE(cv * ppb <= 256 && cv <= 256, "gn_sums: C=%d too wide", C);
+  const int nsplit = gn_nsplit(HW, C);
+  dim3 grid(nsplit, B), block(cv * ppb);
+  const size_t smem = (size_t)ppb * C * 2 * sizeof(float);
   cudaStream_t st = (cudaStream_t)stream;
-  if (int rc = launch_gn_partial(x, dtype, B, HW, C, ld, partial, nsplit, st)) return rc;
-  gn_finalize_kernel<<<B, 256, (size_t)(2 * C + 2 * G) * sizeof(double), st>>>(partial, nsplit, HW, C, G, gamma, beta,
-                                                                                eps, scale_shift);
-  return check_launch("gn_finalize_kernel");
+  if (dtype == DITSEP_F32)
+    DITSEP_CUDA(launch_pdl<2>(gn_sums_kernel<float>, grid, block, smem, st, (const float*)x, HW, C, ld, cv, ppb, sums));
+  else if (dtype == DITSEP_BF16)
+    DITSEP_CUDA(launch_pdl<2>(gn_sums_kernel<bf16>, grid, block, smem, st, (const bf16*)x, HW, C, ld, cv, ppb, sums));
+  else
+    DITSEP_REQUIRE(false, "gn_sums: unknown dtype %d", dtype);
+  return check_launch("gn_sums_kernel");
 }
 
-extern "C" int ditsep_gn_finalize(const ditsep_stats_src* host_srcs, int n_srcs, int B, int64_t HW, int G,
-                                  const float* gamma, const float* beta, float eps, float* scale_shift, void* stream) {
-  DITSEP_REQUIRE(host_srcs && gamma && beta && scale_shift, "gn_finalize: null pointer");
-  DITSEP_REQUIRE(n_srcs >= 1 && n_srcs <= 4, "gn_finalize: n_srcs=%d (1..4)", n_srcs);
-  StatsSrcs srcs;
-  srcs.n = n_srcs;
-  int C = 0;
-  for (int i = 0; i < n_srcs; ++i) {
-    const ditsep_stats_src& s = host_srcs[i];
-    DITSEP_REQUIRE(s.ptr && s.kind == DITSEP_STATS_SPLIT_SUMS, "gn_finalize: source %d has no statistics (kind %d)", i,
-                   s.kind);
-    DITSEP_REQUIRE(s.C > 0 && s.ld >= s.C && s.n_part > 0, "gn_finalize: source %d: bad C/ld/n_part", i);
-    srcs.s[i] = s;
-    C += s.C;
+static int check_gn_job(const ditsep_gn_job* j, const char* who) {
+  DITSEP_REQUIRE(j != nullptr, "%s: null job", who);
+  DITSEP_REQUIRE(j->n_src >= 1 && j->n_src <= 4, "%s: 1..4 statistics sources (got %d)", who, j->n_src);
+  int ctot = 0;
+  for (int i = 0; i < j->n_src; ++i) {
+    DITSEP_REQUIRE(j->src_sums[i] != nullptr && j->src_C[i] > 0, "%s: bad statistics source %d", who, i);
+    ctot += j->src_C[i];
   }
-  DITSEP_REQUIRE(B > 0 && HW > 0 && G > 0 && C % G == 0, "gn_finalize: bad sizes C=%d G=%d", C, G);
-  DITSEP_REQUIRE(C <= 512, "gn_finalize: C=%d too wide", C);
-  const int cpg = C / G;
-  DITSEP_REQUIRE(cpg <= 256, "gn_finalize: %d channels per group is too wide", cpg);
-  int gpc = 16 / cpg;  // ~16 channels per CTA
-  if (gpc < 1) gpc = 1;
-  if (gpc > 32) gpc = 32;
-  const int threads = 256, nj = threads / (gpc * cpg) > 0 ? threads / (gpc * cpg) : 1;
-  dim3 grid((unsigned)ceil_div(G, gpc), (unsigned)B);
-  DITSEP_CUDA(launch_pdl(gn_finalize_srcs_kernel, grid, dim3(threads), (size_t)(2 * nj * gpc * cpg) * sizeof(double),
-                         (cudaStream_t)stream, srcs, HW, C, G, gpc, gamma, beta, eps, scale_shift));
-  return check_launch("gn_finalize_srcs_kernel");
+  DITSEP_REQUIRE(ctot == j->C, "%s: sources cover %d channels, GroupNorm has %d", who, ctot, j->C);
+  DITSEP_REQUIRE(j->G > 0 && j->G <= 64 && j->C % j->G == 0, "%s: C=%d not divisible into G=%d groups (G <= 64)", who, j->C,
+                 j->G);
+  DITSEP_REQUIRE(j->HW > 0 && j->gamma && j->beta && j->scale_shift, "%s: null gamma / beta / scale_shift", who);
+  return 0;
+}
+
+extern "C" int ditsep_gn_finalize(const ditsep_gn_job* host_job, int B, void* stream) {
+  if (int rc = check_gn_job(host_job, "gn_finalize")) return rc;
+  DITSEP_REQUIRE(B > 0, "gn_finalize: B=%d", B);
+  DITSEP_CUDA(launch_pdl(gn_finalize_kernel, dim3(B), dim3(128), 0, (cudaStream_t)stream, *host_job));
+  return check_launch("gn_finalize_kernel");
 }
 
 extern "C" int ditsep_gn_small(const void* x, int dtype, int B, int64_t HW, int C, int ld_x, int G, const float* gamma,

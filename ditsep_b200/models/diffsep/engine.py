@@ -99,6 +99,29 @@ class _Pool:
         self.free.setdefault((tuple(t.shape), t.dtype), []).append(t)
 
 
+class _SumsArena:
+    """Fixed-point GroupNorm statistics buffers [B][C][4] int64 of one plan, carved from a few large chunks so that
+    ONE memset per chunk at the head of the launch list re-zeroes all of them (producers ADD with integer atomics)."""
+
+    CHUNK = 1 << 20  # int64 elements (8 MiB)
+
+    def __init__(self, device):
+        self.device, self.chunks, self.used = device, [], 0
+
+    def new(self, B: int, C: int) -> torch.Tensor:
+        n = B * C * 4
+        if not self.chunks or self.used + n > self.chunks[-1].numel():
+            self.chunks.append(torch.zeros(max(self.CHUNK, n), device=self.device, dtype=torch.int64))
+            self.used = 0
+        t = self.chunks[-1][self.used:self.used + n].view(B, C, 4)
+        self.used += n
+        return t
+
+    def zero(self):
+        for c in self.chunks:
+            c.zero_()
+
+
 class _ConvW:
     """Packed filter of one convolution."""
 
@@ -279,8 +302,7 @@ class _Plan:
         self.out = new(B, H, W, m.num_channels_out, dtype=f32)
         self.act_temb = new(B, 4 * nf, dtype=f32)
         self.dense = new(B, w["dense_rows"], dtype=f32)
-        cmax = max(max(s.in_ch, s.out_ch) for s in m.layout)
-        self.gn_partial = new(B * 64 * cmax * 2, dtype=f32)  # scratch of the unfused statistics pass
+        self.sums = _SumsArena(device)
         self._tc_plans = []
         self._graph, self._graph_launches, self._runs = None, 0, 0
         # (data_ptr, channels) of a produced NHWC view -> (statistics buffer, layout): where its producer
@@ -288,6 +310,7 @@ class _Plan:
         self.stat_src: Dict[Tuple[int, int], Tuple[torch.Tensor, object]] = {}
         add = self.steps.append
 
+        add((self.sums.zero, (), {}))  # statistics are accumulated with atomics: start every evaluation from zero
         # ---- time embedding (ncsnpp.py:325-346) + every res-block's Dense_0 (layerspp.py:316-317)
         add((ops.temb_mlp, (self.t, w["gfp"], *w["lin1"], *w["lin2"], self.act_temb), {}))
         add((ops.temb_dense, (self.act_temb, w["dense_w"], w["dense_b"], self.dense), {}))
@@ -456,24 +479,14 @@ class _Plan:
             except ops.DitsepError:
                 return False
         if in_ss is not None:
-            # conv(act(GroupNorm(x))) (layerspp.py:297-298,318-320): the tile kernel CAN normalise the landed tiles in
-            # shared memory (ops.ConvTcPlan.run in_ss, bit-identical to gn_apply + conv).  Measured at batch 32 (r1m, r1u)
-            # the fused variant is SLOWER -- 12.9-13.6 vs 11.7 ms per score step: four transform warps (one per
-            # scheduler) are issue-latency bound at ~5000 cycles per 64-channel chunk against 2850 of MMA work -- so it
-            # is opt-in (DITSEP_FUSE_GN=1; DITSEP_FUSE_GN_TANH=1 selects the one-MUFU SiLU) until the transform runs on
-            # the 16 epilogue warps
-            if use_tc and plan is None:
-                plan = ops.ConvTcPlan(x, cw.w_bf16, cw.cout, cw.ksize)
-            if plan is not None and plan.tile and os.environ.get("DITSEP_FUSE_GN", "0") == "1":
-                kw["in_ss"] = in_ss
-                kw["in_silu"] = (2 if os.environ.get("DITSEP_FUSE_GN_TANH", "0") == "1" else 1) if in_silu else 0
-            else:
-                act = x if gn_inplace else self.pool.get(tuple(x.shape), x.dtype)
-                self.steps.append((ops.gn_apply, (x, in_ss, in_silu, act), {}))
-                if act is not x:
-                    self.pool.put(act)  # free again once this conv has run (the launch list is sequential)
-                x = act
-                plan = None if shortcut is None else ops.ConvTcPlan(x, cw.w_bf16, cw.cout, cw.ksize, shortcut=shortcut)
+            # conv(act(GroupNorm(x))) (layerspp.py:297-298,318-320): one normalise + SiLU pass, then the convolution.
+            # (Applying it to the landed tiles inside the conv kernel was measured slower in round 1 and removed.)
+            act = x if gn_inplace else self.pool.get(tuple(x.shape), x.dtype)
+            self.steps.append((ops.gn_apply, (x, in_ss, in_silu, act), {}))
+            if act is not x:
+                self.pool.put(act)  # free again once this conv has run (the launch list is sequential)
+            x = act
+            plan = None if shortcut is None else ops.ConvTcPlan(x, cw.w_bf16, cw.cout, cw.ksize, shortcut=shortcut)
         key = (out.data_ptr(), out.shape[3])
         self.stat_src.pop(key, None)  # whatever was known about this view is stale now
         fused = False
@@ -482,10 +495,10 @@ class _Plan:
                 plan = ops.ConvTcPlan(x, cw.w_bf16, cw.cout, cw.ksize)
             self._tc_plans.append(plan)
             plan.algo_flops = 2.0 * x.shape[0] * x.shape[1] * x.shape[2] * cw.algo_macs
-            if want_stats and plan.stats_floats() > 0:
-                buf = torch.empty(plan.stats_floats(), device=self.device, dtype=torch.float32)
+            if want_stats and plan.tile:
+                buf = self.sums.new(x.shape[0], cw.cout)
                 kw["stats"] = buf
-                self.stat_src[key] = (buf, plan.stats_layout())
+                self.stat_src[key] = buf
                 fused = True
             self.steps.append((plan.run, (cw.bias, out), kw))
         else:
@@ -512,21 +525,20 @@ class _Plan:
             if hit is None:
                 srcs = None
                 break
-            if isinstance(hit[1][0], str):  # "lazy": the producer left no statistics: one explicit pass over its output, now
+            if isinstance(hit[1], tuple):  # "lazy": the producer left no statistics: one explicit pass over its output, now
                 t = hit[1][1]
-                Bt, Ht, Wt, Ct = t.shape
-                buf = torch.empty(ops.gn_partial_floats(Bt, Ht * Wt, Ct), device=self.device, dtype=torch.float32)
-                self.steps.append((ops.gn_partial_sums, (t, buf), {}))
-                val = (buf, ops.split_sums_layout(Ht * Wt, Ct))
-                self.stat_src[(t.data_ptr(), Ct)] = val
-                hit = (hit[0], val)
+                buf = self.sums.new(t.shape[0], t.shape[3])
+                self.steps.append((ops.gn_sums, (t, buf), {}))
+                self.stat_src[(t.data_ptr(), t.shape[3])] = buf
+                hit = (hit[0], buf)
             srcs.append(hit[1])
             ptr += hit[0] * x.element_size()
             left -= hit[0]
-        if srcs and len(srcs) <= 4:
-            self.steps.append((ops.gn_finalize, (srcs, B, H * W, G, gnw[0], gnw[1], 1e-6, ss), {}))
-        else:
-            self.steps.append((ops.gn_stats, (x, G, gnw[0], gnw[1], 1e-6, self.gn_partial, ss), {}))
+        if not srcs or len(srcs) > 4:  # unknown producers: one statistics pass over the whole view
+            buf = self.sums.new(B, C)
+            self.steps.append((ops.gn_sums, (x, buf), {}))
+            srcs = [buf]
+        self.steps.append((ops.gn_finalize, (srcs, B, H * W, G, gnw[0], gnw[1], 1e-6, ss), {}))
         return ss
 
     @staticmethod

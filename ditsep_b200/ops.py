@@ -175,54 +175,60 @@ def expand_istft(spec, window, out, exponent: float, factor: float):
 
 
 # ------------------------------------------------------------------ norm / resample
-def gn_nsplit(HW: int, C: int) -> int:
-    """Pixel splits of the statistics pass.  A function of the image shape only -- never of the batch --
-    so the summation order, and with it every bf16 rounding downstream, is batch-invariant."""
-    ppb = max(1, 256 // (C // 8))
-    return int(max(1, min(64, HW // (ppb * 8))))
+def new_sums(B: int, C: int, device) -> torch.Tensor:
+    """Zeroed fixed-point statistics buffer [B][C][4] int64 (include/ditsep_b200.h: value = int + frac * 2^-32).
+    Producers ADD to it: it must be zero again before the next score step (the engine zeroes one arena per step)."""
+    return torch.zeros(B, C, 4, device=device, dtype=torch.int64)
 
 
-def gn_stats(x, G: int, gamma, beta, eps: float, partial, scale_shift):
-    """x NHWC (B,H,W,C) -> scale_shift (B,2,C) f32.  partial: f32 scratch >= B*nsplit*C*2."""
-    _cuda(x, gamma, beta, partial, scale_shift)
+def _sums_ok(sums, B: int, C: int, who: str):
+    if sums.dtype != torch.int64 or not sums.is_contiguous() or sums.numel() != B * C * 4:
+        raise _lib.DitsepError(f"{who}: sums must be a contiguous int64 [B={B}][C={C}][4] tensor")
+
+
+def gn_sums(x, sums):
+    """ADDS the per-channel {sum, sum of squares} of x NHWC (B,H,W,C) to the fixed-point sums [B][C][4]."""
+    _cuda(x, sums)
     B, H, W, Cc = x.shape
-    nsplit = gn_nsplit(H * W, Cc)
-    if partial.numel() < B * nsplit * Cc * 2:
-        raise _lib.DitsepError("gn_stats: partial scratch too small")
-    check(_lib.load().ditsep_gn_stats(_ptr(x), _dt(x), B, H * W, Cc, nhwc_ld(x), G, _ptr(gamma), _ptr(beta), eps,
-                                      _ptr(partial), nsplit, _ptr(scale_shift), _stream()), "gn_stats")
+    _sums_ok(sums, B, Cc, "gn_sums")
+    check(_lib.load().ditsep_gn_sums(_ptr(x), _dt(x), B, H * W, Cc, nhwc_ld(x), _ptr(sums), _stream()), "gn_sums")
 
 
-def gn_partial_floats(B: int, HW: int, C: int) -> int:
-    return B * gn_nsplit(HW, C) * C * 2
-
-
-def split_sums_layout(HW: int, C: int) -> "_lib.StatsSrc":
-    """Statistics-source record (without pointer) of what gn_partial_sums leaves for an image of HW pixels."""
-    return _lib.StatsSrc(None, _lib.STATS_SPLIT_SUMS, C, C, gn_nsplit(HW, C))
-
-
-def gn_partial_sums(x, partial):
-    """Per-channel {sum, sumsq} partials of x NHWC (B,H,W,C) into `partial` (f32, >= gn_partial_floats),
-    laid out as split_sums_layout(H*W, C) says."""
-    _cuda(x, partial)
-    B, H, W, Cc = x.shape
-    nsplit = gn_nsplit(H * W, Cc)
-    if partial.dtype != torch.float32 or partial.numel() < B * nsplit * Cc * 2:
-        raise _lib.DitsepError("gn_partial_sums: partial scratch too small")
-    check(_lib.load().ditsep_gn_partial_sums(_ptr(x), _dt(x), B, H * W, Cc, nhwc_ld(x), _ptr(partial), nsplit,
-                                             _stream()), "gn_partial_sums")
+def make_gn_job(srcs, B: int, HW: int, G: int, gamma, beta, eps: float, scale_shift) -> "_lib.GnJob":
+    """srcs: 1..4 sums tensors [B][C_i][4] covering the normalised tensor's channels end to end -> ditsep_gn_job."""
+    _cuda(gamma, beta, scale_shift, *srcs)
+    if not 1 <= len(srcs) <= 4:
+        raise _lib.DitsepError("GroupNorm job: 1..4 statistics sources")
+    job = _lib.GnJob()
+    ctot = 0
+    for i, t in enumerate(srcs):
+        ci = t.shape[1]
+        _sums_ok(t, B, ci, "GroupNorm job")
+        job.src_sums[i] = t.data_ptr()
+        job.src_C[i] = ci
+        ctot += ci
+    if scale_shift.dtype != torch.float32 or not scale_shift.is_contiguous() or scale_shift.numel() != B * 2 * ctot:
+        raise _lib.DitsepError("GroupNorm job: scale_shift must be contiguous f32 (B, 2, C)")
+    job.n_src, job.C, job.G, job.eps, job.HW = len(srcs), ctot, G, eps, HW
+    job.gamma, job.beta, job.scale_shift = gamma.data_ptr(), beta.data_ptr(), scale_shift.data_ptr()
+    job._keep = (srcs, gamma, beta, scale_shift)
+    return job
 
 
 def gn_finalize(srcs, B: int, HW: int, G: int, gamma, beta, eps: float, scale_shift):
-    """srcs: 1..4 pairs (buffer, StatsSrc layout) covering the normalised tensor's channels end to end
-    (a producer's statistics buffer and how it is laid out) -> scale_shift (B, 2, C)."""
-    _cuda(gamma, beta, scale_shift, *(t for t, _ in srcs))
-    arr = (_lib.StatsSrc * len(srcs))()
-    for i, (t, lay) in enumerate(srcs):
-        arr[i] = _lib.StatsSrc(t.data_ptr(), lay.kind, lay.C, lay.ld, lay.n_part)
-    check(_lib.load().ditsep_gn_finalize(arr, len(srcs), B, HW, G, _ptr(gamma), _ptr(beta), eps, _ptr(scale_shift),
-                                         _stream()), "gn_finalize")
+    """scale_shift (B, 2, C) of GroupNorm(G, C) from the fixed-point sums of its producers (1..4 sources, end to end
+    along the channel axis)."""
+    job = make_gn_job(srcs, B, HW, G, gamma, beta, eps, scale_shift)
+    check(_lib.load().ditsep_gn_finalize(C.byref(job), B, _stream()), "gn_finalize")
+
+
+def gn_stats(x, G: int, gamma, beta, eps: float, scale_shift):
+    """x NHWC (B,H,W,C) -> scale_shift (B,2,C) f32: explicit statistics pass + finalize (allocates a sums buffer:
+    not for use inside a captured launch plan)."""
+    B, H, W, Cc = x.shape
+    sums = new_sums(B, Cc, x.device)
+    gn_sums(x, sums)
+    gn_finalize([sums], B, H * W, G, gamma, beta, eps, scale_shift)
 
 
 def gn_small(x, G: int, gamma, beta, eps: float, silu: bool, y):
@@ -306,38 +312,24 @@ class ConvTcPlan:
                                                             _ptr(w_bf16), Cout, ksize, _ptr(shortcut), shortcut.shape[3],
                                                             nhwc_ld(shortcut)), "conv_tc_plan_create_sc")
 
-    def stats_layout(self) -> "_lib.StatsSrc":
-        """Layout of the statistics partials this plan's run() can leave (kind STATS_NONE if it cannot);
-        ``ptr`` is left null for the caller to fill in."""
-        lay = _lib.StatsSrc()
-        check(_lib.load().ditsep_conv_tc_stats_layout(self._h, C.byref(lay)), "conv_tc_stats_layout")
-        return lay
-
-    def stats_floats(self) -> int:
-        lay = self.stats_layout()
-        return 0 if lay.kind == _lib.STATS_NONE else self.shape[0] * lay.n_part * lay.ld * 2
-
     @property
     def tile(self) -> bool:
-        """True when this plan runs the persistent tile kernel (fused statistics, fused input GroupNorm)."""
-        return self.stats_layout().kind != _lib.STATS_NONE
+        """True when this plan runs the persistent tile kernel (whose epilogue can leave GroupNorm statistics)."""
+        return bool(_lib.load().ditsep_conv_tc_has_stats(self._h))
 
-    def run(self, bias, out, bias_b=None, residual=None, out_scale: float = 1.0, stats=None, in_ss=None,
-            in_silu: bool = True):
-        """stats: f32 buffer of >= stats_floats() elements receiving the per-segment statistics partials.
-        in_ss: (B, 2, Cin) f32 scale / shift of the INPUT's GroupNorm, applied (+ SiLU if in_silu) to every A tile in
-        shared memory (ditsep_conv_tc_run_gn): the plan's input is then the raw, un-normalised tensor."""
-        _cuda(bias, out, bias_b, residual, stats, in_ss)
-        if stats is not None and (stats.dtype != torch.float32 or stats.numel() < max(1, self.stats_floats())):
-            raise _lib.DitsepError("conv_tc: statistics buffer too small (or this plan cannot produce statistics)")
-        if in_ss is not None and (in_ss.dtype != torch.float32 or not in_ss.is_contiguous()
-                                  or in_ss.numel() != self.shape[0] * 2 * self.Cin):
-            raise _lib.DitsepError("conv_tc: in_ss must be a contiguous f32 (B, 2, Cin) tensor")
-        check(_lib.load().ditsep_conv_tc_run_gn(self._h, _ptr(in_ss), int(in_silu), _ptr(bias), _ptr(bias_b),
+    def run(self, bias, out, bias_b=None, residual=None, out_scale: float = 1.0, stats=None):
+        """stats: fixed-point sums [B][Cout][4] int64 (new_sums) the epilogue ADDS the output's per-channel
+        {sum, sum of squares} to (tile-kernel plans only)."""
+        _cuda(bias, out, bias_b, residual, stats)
+        if stats is not None:
+            if not self.tile:
+                raise _lib.DitsepError("conv_tc: this plan (image below one 8x16 tile) cannot produce statistics")
+            _sums_ok(stats, self.shape[0], self.Cout, "conv_tc")
+        check(_lib.load().ditsep_conv_tc_run(self._h, _ptr(bias), _ptr(bias_b),
                                              0 if bias_b is None else bias_b.stride(0), _ptr(residual),
                                              0 if residual is None else _dt(residual),
                                              0 if residual is None else nhwc_ld(residual), out_scale, _ptr(out),
-                                                _dt(out), nhwc_ld(out), _ptr(stats), _stream()), "conv_tc_run")
+                                             _dt(out), nhwc_ld(out), _ptr(stats), _stream()), "conv_tc_run")
 
     def __del__(self):
         h = getattr(self, "_h", None)

@@ -97,35 +97,32 @@ int ditsep_expand_istft(const float* spec, const float* window, float* out, int 
                         float exponent, float factor, void* stream);
 
 /* ---- GroupNorm (+SiLU) -------------------------------------------------------------
- * nn.GroupNorm(G, C, eps=1e-6) statistics + affine folded to per-(b,c) scale/shift
- * (layerspp.py:269-271,283-285,297,318).  x: NHWC [B][HW][ld]; partial: scratch
- * (B*nsplit*C*2 floats); scale_shift out: [B][2][C] f32.  Summation order depends only on
- * (HW, C, nsplit), never on B: results are batch-invariant and bit-reproducible. */
-int ditsep_gn_stats(const void* x, int dtype, int B, int64_t HW, int C, int ld, int G, const float* gamma,
-                    const float* beta, float eps, float* partial, int nsplit, float* scale_shift, void* stream);
-/* First half of the above only: per-channel {sum, sum of squares} partials [B][nsplit][C][2]
- * (a DITSEP_STATS_SPLIT_SUMS source for ditsep_gn_finalize). */
-int ditsep_gn_partial_sums(const void* x, int dtype, int B, int64_t HW, int C, int ld, float* partial, int nsplit,
-                           void* stream);
+ * nn.GroupNorm(G, C, eps=1e-6) + SiLU (layerspp.py:269-271,283-285,297,318).
+ *
+ * Statistics travel as ORDER-INDEPENDENT FIXED-POINT SUMS: sums[B][C][4] int64 =
+ * {sum int, sum frac, sumsq int, sumsq frac}, value = int + frac * 2^-32.  Producers (the convolution epilogue,
+ * ditsep_gn_sums) split each fp32 partial exactly and ADD both parts with integer atomics; integer addition
+ * commutes, so the totals -- and every bf16 rounding downstream -- are bit-reproducible and independent of the
+ * batch size and of CTA scheduling.  A sums buffer must be ZERO before the first producer of a step adds to it. */
+/* Explicit statistics pass over x: NHWC [B][HW][ld] (for tensors whose producer left no sums). */
+int ditsep_gn_sums(const void* x, int dtype, int B, int64_t HW, int C, int ld, long long* sums, void* stream);
 
-/* Where the per-channel {sum, sum of squares} of a tensor (or of a channel range of a concat
- * buffer) were left by its producer. */
-#define DITSEP_STATS_NONE 0
-#define DITSEP_STATS_SPLIT_SUMS 2 /* [B][n_part][ld][2] partial sums: ditsep_gn_partial_sums (n_part = nsplit) or the
-                                     epilogue of ditsep_conv_tc_run (n_part = segments per image x 4, see
-                                     ditsep_conv_tc_stats_layout) */
+/* One GroupNorm consumer: per-(b,c) scale/shift [B][2][C] from the sums of up to 4 producers laid end to end along
+ * the channel axis (torch.cat([h, skip], dim=1) feeding GroupNorm_0, ncsnpp.py:413 + layerspp.py:297). */
 typedef struct {
-  const float* ptr;
-  int32_t kind;   /* DITSEP_STATS_* */
-  int32_t C;      /* channels this source covers (they are consecutive in the normalised tensor) */
-  int32_t ld;     /* channel stride of the source rows */
-  int32_t n_part; /* partials per image */
-} ditsep_stats_src;
-/* scale/shift of GroupNorm(G, C = sum of the sources' C) from up to 4 statistics sources laid end
- * to end along the channel axis (torch.cat([h, skip], dim=1) feeding GroupNorm_0, ncsnpp.py:413 +
- * layerspp.py:297).  Partials are added in a fixed order, in double. */
-int ditsep_gn_finalize(const ditsep_stats_src* host_srcs, int n_srcs, int B, int64_t HW, int G, const float* gamma,
-                       const float* beta, float eps, float* scale_shift, void* stream);
+  const long long* src_sums[4];
+  int32_t src_C[4];
+  int32_t n_src;
+  int32_t C;      /* = sum of src_C */
+  int32_t G;      /* groups, C % G == 0, G <= 64 */
+  float eps;
+  int64_t HW;     /* pixels per image */
+  const float* gamma;
+  const float* beta;
+  float* scale_shift;
+} ditsep_gn_job;
+/* scale/shift of one job (a tiny launch: B CTAs reading C * 32 bytes each). */
+int ditsep_gn_finalize(const ditsep_gn_job* host_job, int B, void* stream);
 /* GroupNorm statistics + normalise (+ SiLU) of SMALL images in one launch (one CTA per image; y may alias x):
  * act(GroupNorm(x)) of ResnetBlockBigGANpp.forward (layerspp.py:297,318) at the 16x16 .. 4x4 levels, where the
  * three-launch sequence gn_partial_sums -> gn_finalize -> gn_apply is pure launch latency.  HW <= 4096, C <= 256. */
@@ -170,12 +167,10 @@ int ditsep_split_hilo(const float* x, int64_t npix, int C, void* out_bf16, int l
  * 8 x 16 pixels run the tile kernel (one TMA box per 64-channel block brings an 8 x 16 pixel tile
  * plus its halo; the taps are shifted views of it; persistent CTAs over contiguous tile ranges,
  * filter resident in shared memory when it fits); smaller images one TMA box per tap.
- * `stats` (nullable, tile kernel only): the epilogue also leaves the per-image, per-channel
- * {sum, sum of squares} of the values it stores (the GroupNorm statistics of the output tensor,
- * layerspp.py:297,318) as per-CTA partials, so the consumer's GroupNorm needs no extra pass over
- * the tensor.  No atomics, and a summation order fixed by the image shape: bit-reproducible and
- * batch-invariant.  Size and layout: ditsep_conv_tc_stats_layout (B * n_part * ld * 2 floats; kind
- * DITSEP_STATS_NONE if the plan cannot produce them). */
+ * `stats` (nullable, tile kernel only: ditsep_conv_tc_has_stats): the epilogue also ADDS the per-image,
+ * per-channel {sum, sum of squares} of the values it stores (the GroupNorm statistics of the output tensor,
+ * layerspp.py:297,318) to the fixed-point sums [B][Cout][4] described above, so the consumer's GroupNorm needs
+ * no extra pass over the tensor. */
 typedef struct ditsep_conv_plan ditsep_conv_plan;
 int ditsep_conv_tc_plan_create(ditsep_conv_plan** plan, const void* in, int B, int H, int W, int Cin, int ld_in,
                                const void* w_bf16, int Cout, int ksize);
@@ -190,20 +185,10 @@ int ditsep_conv_tc_plan_create(ditsep_conv_plan** plan, const void* in, int B, i
 int ditsep_conv_tc_plan_create_sc(ditsep_conv_plan** plan, const void* in, int B, int H, int W, int Cin, int ld_in,
                                   const void* w_bf16, int Cout, int ksize, const void* x_sc, int Cx, int ld_x);
 void ditsep_conv_tc_plan_destroy(ditsep_conv_plan* plan);
-int ditsep_conv_tc_stats_layout(const ditsep_conv_plan* plan, ditsep_stats_src* layout);
+int ditsep_conv_tc_has_stats(const ditsep_conv_plan* plan);
 int ditsep_conv_tc_run(const ditsep_conv_plan* plan, const float* bias, const float* bias_b, int ld_bias_b,
                        const void* residual, int res_dtype, int ld_res, float out_scale, void* out, int out_dtype,
-                       int ld_out, float* stats, void* stream);
-
-/* Same, with the INPUT's GroupNorm (+ SiLU) fused: `in` holds the RAW tensor its producer stored, and every A tile is
- * normalised in shared memory after it lands and before the MMAs read it -- a = silu?(x * scale + shift) per
- * (image, input channel), zero outside the image (the conv pads the activated tensor) -- replacing the separate
- * ditsep_gn_apply pass of ResnetBlockBigGANpp.forward's act(GroupNorm_0(x)) / act(GroupNorm_1(h)) (layerspp.py:297,318).
- * in_scale_shift: [B][2][Cin] f32 from ditsep_gn_finalize / ditsep_gn_stats (NULL = plain ditsep_conv_tc_run);
- * a fused shortcut input (plan_create_sc) is NOT normalised.  Tile-kernel plans only (status 2 otherwise). */
-int ditsep_conv_tc_run_gn(const ditsep_conv_plan* plan, const float* in_scale_shift, int in_silu, const float* bias,
-                          const float* bias_b, int ld_bias_b, const void* residual, int res_dtype, int ld_res,
-                          float out_scale, void* out, int out_dtype, int ld_out, float* stats, void* stream);
+                       int ld_out, long long* stats, void* stream);
 
 /* Debug aid (scripts/trace_conv.py): while buf != NULL, the tile kernel's first 4 CTAs write clock64() stamps of their
  * first 96 tiles to buf ([4][96][16] int64: 0 accumulator free, 1 first A tile landed, 2 MMAs issued, 3 accumulator

@@ -68,7 +68,7 @@ for (H, Cin, Cout, k, cnt, fl) in CENSUS:
     res = torch.randn(B, H, W, Cout, generator=g).to(dev).to(odt) if "r" in fl else None
     bb = torch.randn(B, Cout, generator=g).to(dev) if "b" in fl else None
     plan = ops.ConvTcPlan(x, w, Cout, k)
-    stats = torch.empty(plan.stats_floats(), device=dev) if (fl and plan.stats_floats()) else None
+    stats = ops.new_sums(B, Cout, dev) if (fl and plan.tile) else None
     kw = dict(bias_b=bb, residual=res, out_scale=0.7071, stats=stats)
     us = timeit(lambda: plan.run(bias, out, **kw))
     # library arms: NCHW-shaped tensors in channels_last memory format (= NHWC), bias in the call

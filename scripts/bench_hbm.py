@@ -41,8 +41,8 @@ for (H, W, C) in [(256, 256, 64), (256, 256, 128), (128, 128, 128), (64, 64, 256
     ss = torch.randn(B, 2, C, device=dev)
     n = x.numel() * 2
     report(f"gn_apply+silu {H}x{W}x{C}", timeit(lambda: ops.gn_apply(x, ss, True, y)), 2 * n)
-    part = torch.empty(ops.gn_partial_floats(B, H * W, C), device=dev)
-    report(f"gn_partial_sums {H}x{W}x{C}", timeit(lambda: ops.gn_partial_sums(x, part)), n)
+    part = ops.new_sums(B, C, dev)
+    report(f"gn_sums {H}x{W}x{C}", timeit(lambda: ops.gn_sums(x, part)), n)
 for (H, W, C) in [(256, 256, 64), (128, 128, 128)]:
     x = torch.randn(B, H, W, C, device=dev).to(bf)
     ss = torch.randn(B, 2, C, device=dev)

@@ -20,7 +20,7 @@ odt = torch.float32 if f32 else torch.bfloat16
 out = torch.empty(B, H, H, Cout, device=dev, dtype=odt)
 res = torch.randn(B, H, H, Cout, device=dev).to(odt) if use_res else None
 plan = ops.ConvTcPlan(x, w, Cout, 3, shortcut=xs)
-stats = None if f32 else torch.empty(max(1, plan.stats_floats()), device=dev)
+stats = None if (f32 or not plan.tile) else ops.new_sums(B, Cout, dev)
 for _ in range(3):
     plan.run(bias, out, residual=res, stats=stats)
 torch.cuda.synchronize()

@@ -18,7 +18,7 @@ import torch.nn.functional as F
 from ditsep_b200 import ops
 
 _NAMES = ["pc_corrector", "pc_predictor", "pc_prior", "philox_normal", "stft_compress", "expand_istft", "gn_stats",
-          "gn_partial_sums", "gn_finalize", "gn_apply", "gn_small", "fir_resample", "conv_direct", "attention", "temb_mlp", "temb_dense", "output_layer"]
+          "gn_sums", "gn_finalize", "gn_apply", "gn_small", "fir_resample", "conv_direct", "attention", "temb_mlp", "temb_dense", "output_layer"]
 
 
 def _coef(p, mode, t):
@@ -127,38 +127,9 @@ def expand_istft(spec, window, out, exponent, factor):
     out.copy_(y[..., :T])
 
 
-def gn_stats(x, G, gamma, beta, eps, partial, scale_shift):
-    B, H, W, C = x.shape
-    xf = x.double().reshape(B, H * W, G, C // G)
-    mean = xf.mean(dim=(1, 3))
-    var = xf.var(dim=(1, 3), unbiased=False)
-    rstd = 1 / torch.sqrt(var + eps)
-    sc = rstd.repeat_interleave(C // G, dim=1) * gamma.double()
-    sh = beta.double() - mean.repeat_interleave(C // G, dim=1) * sc
-    scale_shift[:, 0].copy_(sc.float())
-    scale_shift[:, 1].copy_(sh.float())
-
-
-def gn_partial_sums(x, partial):
-    """ditsep_gn_partial_sums: [B][nsplit][C][2] partials; the stand-in puts everything in split 0."""
-    B, H, W, C = x.shape
-    ns = ops.gn_nsplit(H * W, C)
-    v = partial[:B * ns * C * 2].view(B, ns, C, 2)
-    v.zero_()
-    xf = x.double().reshape(B, H * W, C)
-    v[:, 0, :, 0] = xf.sum(dim=1).float()
-    v[:, 0, :, 1] = (xf * xf).sum(dim=1).float()
-
-
-def gn_finalize(srcs, B, HW, G, gamma, beta, eps, scale_shift):
-    """ditsep_gn_finalize for split-sums sources (the conv-partials kind only exists on the GPU)."""
-    sums = []
-    for t, lay in srcs:
-        assert lay.kind == 2, "CPU stand-in only knows split sums"
-        v = t[:B * lay.n_part * lay.ld * 2].view(B, lay.n_part, lay.ld, 2)[:, :, :lay.C].double().sum(dim=1)
-        sums.append(v)
-    s = torch.cat(sums, dim=1)  # (B, C, 2)
-    C = s.shape[1]
+def _gn_from_channel_sums(s, HW, G, gamma, beta, eps, scale_shift):
+    """s: (B, C, 2) double {sum, sum of squares} -> scale / shift, as gn_job_image of csrc/norm_fir.cu."""
+    B, C = s.shape[:2]
     cpg = C // G
     g = s.reshape(B, G, cpg, 2).sum(dim=2)
     n = HW * cpg
@@ -171,10 +142,45 @@ def gn_finalize(srcs, B, HW, G, gamma, beta, eps, scale_shift):
     scale_shift[:, 1].copy_(sh.float())
 
 
+def _fx_encode(v):
+    """double -> (int, frac * 2^32) pair of the fixed-point sums (common.cuh fx_add)."""
+    fl = torch.floor(v)
+    return fl.to(torch.int64), ((v - fl) * 4294967296.0).to(torch.int64)
+
+
+def _fx_decode(sums):
+    """[B][C][4] int64 -> (B, C, 2) double."""
+    d = sums.double()
+    return torch.stack((d[..., 0] + d[..., 1] / 4294967296.0, d[..., 2] + d[..., 3] / 4294967296.0), dim=-1)
+
+
+def gn_sums(x, sums):
+    """ditsep_gn_sums: ADDS per-channel {sum, sum of squares} to the fixed-point sums [B][C][4]."""
+    B, H, W, C = x.shape
+    xf = x.double().reshape(B, H * W, C)
+    for k, v in ((0, xf.sum(dim=1)), (2, (xf * xf).sum(dim=1))):
+        hi, lo = _fx_encode(v)
+        sums[..., k] += hi
+        sums[..., k + 1] += lo
+
+
+def gn_finalize(srcs, B, HW, G, gamma, beta, eps, scale_shift):
+    """ditsep_gn_finalize: sources laid end to end along the channel axis."""
+    s = torch.cat([_fx_decode(t) for t in srcs], dim=1)  # (B, C, 2)
+    _gn_from_channel_sums(s, HW, G, gamma, beta, eps, scale_shift)
+
+
+def gn_stats(x, G, gamma, beta, eps, scale_shift):
+    B, H, W, C = x.shape
+    xf = x.double().reshape(B, H * W, C)
+    _gn_from_channel_sums(torch.stack((xf.sum(dim=1), (xf * xf).sum(dim=1)), dim=-1), H * W, G, gamma, beta, eps,
+                          scale_shift)
+
+
 def gn_small(x, G, gamma, beta, eps, silu, y):
     B, H, W, C = x.shape
     ss = torch.empty(B, 2, C)
-    gn_stats(x, G, gamma, beta, eps, None, ss)
+    gn_stats(x, G, gamma, beta, eps, ss)
     gn_apply(x, ss, silu, y)
 
 

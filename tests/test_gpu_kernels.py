@@ -159,12 +159,22 @@ def test_groupnorm(C, ld, H, W, B, dtype):
     beta = 0.1 * torch.randn(C, generator=g(11))
     G = min(C // 4, 32)
     ss_ref = torch.empty(B, 2, C)
-    E.gn_stats(x, G, gamma, beta, 1e-6, None, ss_ref)
+    E.gn_stats(x, G, gamma, beta, 1e-6, ss_ref)
     xd = buf.to(DEV)[..., ld - C:]
     ss = torch.empty(B, 2, C, device=DEV)
-    partial = torch.empty((4 * 148 + B) * C * 4, device=DEV)
-    ops.gn_stats(xd, G, gamma.to(DEV), beta.to(DEV), 1e-6, partial, ss)
+    ops.gn_stats(xd, G, gamma.to(DEV), beta.to(DEV), 1e-6, ss)
     assert rel(ss, ss_ref) < 1e-5
+    # the fixed-point sums themselves: exact integers, so two passes are bit-identical and image b alone == in the batch
+    s1, s2 = ops.new_sums(B, C, DEV), ops.new_sums(B, C, DEV)
+    ops.gn_sums(xd, s1)
+    ops.gn_sums(xd, s2)
+    assert torch.equal(s1, s2)
+    sb = ops.new_sums(1, C, DEV)
+    ops.gn_sums(xd[B - 1:], sb)
+    assert torch.equal(sb[0], s1[B - 1])
+    tot = E._fx_decode(s1.cpu())
+    xf = x.double().reshape(B, H * W, C)
+    assert rel(tot[..., 1], (xf * xf).sum(dim=1)) < 1e-5
     for silu in (False, True):
         y_ref = torch.empty(B, H, W, C, dtype=dtype)
         E.gn_apply(x, ss_ref, silu, y_ref)
@@ -289,10 +299,9 @@ TC_CASES = [
 ]
 
 
-def _conv_partials_to_sums(buf, lay, B):
-    """Host restatement of how ditsep_gn_finalize reads split sums [B][n_part][ld][2]."""
-    v = buf[:B * lay.n_part * lay.ld * 2].cpu().double().view(B, lay.n_part, lay.ld, 2)
-    return v[:, :, :lay.C].sum(dim=1)
+def _conv_sums(buf):
+    """Fixed-point sums [B][C][4] int64 -> (B, C, 2) double {sum, sum of squares}."""
+    return E._fx_decode(buf.cpu())
 
 
 @pytest.mark.parametrize("B,H,W,Cin,ld_extra,Cout,k", TC_CASES)
@@ -309,44 +318,38 @@ def test_conv_tc(B, H, W, Cin, ld_extra, Cout, k):
     xd = xb.to(DEV)[..., ld_extra:]
     plan = ops.ConvTcPlan(xd, wpad.to(DEV), Cout, k)
     out = torch.empty(B, H, W, Cout, device=DEV)
-    lay = plan.stats_layout()
     tile_kernel = H >= 16 and W >= 8
-    assert (lay.kind != 0) == tile_kernel
-    stats_buf = torch.full((max(1, plan.stats_floats()),), float("nan"), device=DEV) if tile_kernel else None
+    assert plan.tile == tile_kernel
+    stats_buf = ops.new_sums(B, Cout, DEV) if tile_kernel else None
     plan.run(bias.to(DEV), out, bias_b=bias_b.to(DEV)[:, 5:], residual=res.to(DEV), out_scale=0.7, stats=stats_buf)
     torch.cuda.synchronize()
     # same bf16 operands, fp32 accumulation on both sides: only summation order differs
     assert rel(out, ref) < 2e-5, rel(out, ref)
     if tile_kernel:
         # fused GroupNorm statistics of the stored output: per-image, per-channel sum and sum of squares
-        sums = _conv_partials_to_sums(stats_buf, lay, B)
+        sums = _conv_sums(stats_buf)
         o = out.double().cpu()
         assert rel(sums[..., 1], (o * o).sum(dim=(1, 2))) < 1e-5
         assert float(((sums[..., 0] - o.sum(dim=(1, 2))).abs() / o.abs().sum(dim=(1, 2))).max()) < 1e-5
         G = min(max(Cout // 4, 1), 32) if Cout % 4 == 0 else 1
         gamma, beta = 1 + 0.1 * torch.randn(Cout, generator=g(1)), 0.1 * torch.randn(Cout, generator=g(2))
         ss_ref = torch.empty(B, 2, Cout)
-        E.gn_stats(out.cpu(), G, gamma, beta, 1e-6, None, ss_ref)
+        E.gn_stats(out.cpu(), G, gamma, beta, 1e-6, ss_ref)
         ss = torch.empty(B, 2, Cout, device=DEV)
-        ops.gn_finalize([(stats_buf, lay)], B, H * W, G, gamma.to(DEV), beta.to(DEV), 1e-6, ss)
+        ops.gn_finalize([stats_buf], B, H * W, G, gamma.to(DEV), beta.to(DEV), 1e-6, ss)
         assert rel(ss, ss_ref) < 1e-4, rel(ss, ss_ref)
-        # bit-reproducible (no atomics): a second run leaves identical partials, and every slot is written
-        again = torch.full_like(stats_buf, float("nan"))
+        # bit-reproducible although accumulated with atomics (integer adds commute): a second run gives identical sums
+        again = ops.new_sums(B, Cout, DEV)
         plan.run(bias.to(DEV), out, bias_b=bias_b.to(DEV)[:, 5:], residual=res.to(DEV), out_scale=0.7, stats=again)
-        n = B * lay.n_part * lay.ld * 2
-        assert not torch.isnan(stats_buf[:n].view(B, lay.n_part, lay.ld, 2)[:, :, :lay.C]).any()
-        assert torch.equal(stats_buf[:n].view(B, lay.n_part, lay.ld, 2)[:, :, :lay.C],
-                           again[:n].view(B, lay.n_part, lay.ld, 2)[:, :, :lay.C])
-        if B > 1:  # batch-invariant: image B-1 alone leaves the same partials as inside the batch
+        assert torch.equal(stats_buf, again)
+        if B > 1:  # batch-invariant: image B-1 alone leaves the same sums as inside the batch
             plan1 = ops.ConvTcPlan(xd[B - 1:], wpad.to(DEV), Cout, k)
-            st1 = torch.empty(plan1.stats_floats(), device=DEV)
+            st1 = ops.new_sums(1, Cout, DEV)
             out1 = torch.empty(1, H, W, Cout, device=DEV)
             plan1.run(bias.to(DEV), out1, bias_b=bias_b.to(DEV)[B - 1:, 5:], residual=res.to(DEV)[B - 1:], out_scale=0.7,
                       stats=st1)
             assert torch.equal(out1, out[B - 1:])
-            n1 = lay.n_part * lay.ld * 2
-            assert torch.equal(st1[:n1].view(lay.n_part, lay.ld, 2)[:, :lay.C],
-                               stats_buf[:n].view(B, lay.n_part, lay.ld, 2)[B - 1, :, :lay.C])
+            assert torch.equal(st1[0], stats_buf[B - 1])
     else:
         with pytest.raises(ops.DitsepError):
             plan.run(bias.to(DEV), out, stats=torch.zeros(16, device=DEV))
@@ -385,8 +388,7 @@ def test_conv_tc_fused_shortcut(B, H, W, Cin, Cout, Cx, k, ld_extra):
     wpad[:Cout, k * k * Cin:] = wsc.reshape(Cout, -1)
     hd, xd = h.to(DEV), xbuf.to(DEV)[..., ld_extra:]
     plan = ops.ConvTcPlan(hd, wpad.to(DEV), Cout, k, shortcut=xd)
-    lay = plan.stats_layout()
-    stats_buf = torch.zeros(max(1, plan.stats_floats()), device=DEV)
+    stats_buf = ops.new_sums(B, Cout, DEV)
     out = torch.empty(B, H, W, Cout, device=DEV)
     plan.run(bias.to(DEV), out, bias_b=bias_b.to(DEV), out_scale=0.7, stats=stats_buf)
     sc = torch.empty(B, H, W, Cout)
@@ -394,7 +396,7 @@ def test_conv_tc_fused_shortcut(B, H, W, Cin, Cout, Cx, k, ld_extra):
     ref = torch.empty(B, H, W, Cout)
     E.conv_direct(h.float(), wm.float(), bias, ref, k, bias_b=bias_b, residual=sc, out_scale=0.7)
     assert rel(out, ref) < 2e-5, rel(out, ref)
-    sums = _conv_partials_to_sums(stats_buf, lay, B)
+    sums = _conv_sums(stats_buf)
     o = out.double().cpu()
     assert rel(sums[..., 1], (o * o).sum(dim=(1, 2))) < 1e-5
     # bf16 output + second run bit-identical
@@ -405,120 +407,25 @@ def test_conv_tc_fused_shortcut(B, H, W, Cin, Cout, Cx, k, ld_extra):
     assert torch.equal(outb, outb2) and rel(outb.float(), ref) < 4e-3
 
 
-@pytest.mark.parametrize("B,H,W,Cin,Cout,Cx,k,silu", [
-    (2, 32, 24, 64, 64, 0, 3, True),
-    (3, 40, 17, 128, 64, 0, 3, True),      # two K chunks, ragged width (tiles hang over the right edge)
-    (2, 16, 16, 128, 384, 0, 1, False),    # attention q/k/v projection: GroupNorm without SiLU, 1x1
-    (2, 48, 32, 64, 64, 128, 3, True),     # with a fused shortcut (which must NOT be normalised)
-    (1, 16, 8, 256, 128, 0, 3, True),      # streamed filter (not resident), smallest image of the tile kernel
-])
-def test_conv_tc_fused_input_groupnorm(B, H, W, Cin, Cout, Cx, k, silu):
-    """ditsep_conv_tc_run_gn: conv(silu?(x * scale + shift)) with the normalisation applied to the landed tiles in
-    shared memory must equal gn_apply followed by the plain conv on the same device -- bit for bit."""
-    x = torch.randn(B, H, W, Cin, generator=g(90)).to(torch.bfloat16).to(DEV)
-    ss = torch.stack([1.0 + 0.3 * torch.randn(B, Cin, generator=g(91)), 0.5 * torch.randn(B, Cin, generator=g(92))],
-                     dim=1).contiguous().to(DEV)
-    cp = (Cout + 15) // 16 * 16
-    w = torch.zeros(cp, k * k * Cin + Cx, dtype=torch.bfloat16)
-    w[:Cout] = (torch.randn(Cout, k * k * Cin + Cx, generator=g(93)) / math.sqrt(k * k * Cin)).to(torch.bfloat16)
-    w = w.to(DEV)
-    xs = torch.randn(B, H, W, Cx, generator=g(94)).to(torch.bfloat16).to(DEV) if Cx else None
-    bias = (0.1 * torch.randn(Cout, generator=g(95))).to(DEV)
-    act = torch.empty_like(x)
-    ops.gn_apply(x, ss, silu, act)
-    ref_plan = ops.ConvTcPlan(act, w, Cout, k, shortcut=xs)
-    ref = torch.empty(B, H, W, Cout, device=DEV, dtype=torch.bfloat16)
-    ref_plan.run(bias, ref)
-    plan = ops.ConvTcPlan(x, w, Cout, k, shortcut=xs)
-    assert plan.tile
-    st = torch.zeros(max(1, plan.stats_floats()), device=DEV)
-    st_ref = torch.zeros_like(st)
-    out = torch.empty_like(ref)
-    plan.run(bias, out, in_ss=ss, in_silu=silu, stats=st)
-    ref_plan.run(bias, ref, stats=st_ref)
-    assert torch.equal(out, ref), rel(out.float(), ref.float())
-    assert torch.equal(st, st_ref)
-    # and against the fp32 definition (bf16 rounding of the activation + output only)
-    a32 = x.float().cpu() * ss[:, 0].cpu()[:, None, None, :] + ss[:, 1].cpu()[:, None, None, :]
-    a32 = torch.nn.functional.silu(a32) if silu else a32
-    full = torch.empty(B, H, W, Cout)
-    wm = w[:Cout, :k * k * Cin].float().cpu().reshape(Cout, k * k, Cin)
-    E.conv_direct(a32, wm, bias.cpu(), full, k)
-    if Cx:
-        sc = torch.empty(B, H, W, Cout)
-        E.conv_direct(xs.float().cpu(), w[:Cout, k * k * Cin:].float().cpu().reshape(Cout, 1, Cx), torch.zeros(Cout), sc, 1)
-        full += sc
-    assert rel(out.float().cpu(), full) < 6e-3
-
-
-def test_conv_tc_fused_input_groupnorm_needs_tile_kernel():
-    x = torch.randn(2, 4, 4, 64, device=DEV).to(torch.bfloat16)
-    w = torch.zeros(64, 9 * 64, device=DEV, dtype=torch.bfloat16)
-    plan = ops.ConvTcPlan(x, w, 64, 3)
-    assert not plan.tile
-    with pytest.raises(ops.DitsepError):
-        plan.run(torch.zeros(64, device=DEV), torch.empty(2, 4, 4, 64, device=DEV),
-                 in_ss=torch.zeros(2, 2, 64, device=DEV))
-
-
-def test_conv_tc_fused_shortcut_refuses_what_it_cannot_fuse():
-    x = torch.randn(1, 16, 16, 256, device=DEV).to(torch.bfloat16)
-    w = torch.zeros(128, 9 * 256 + 256, device=DEV, dtype=torch.bfloat16)
-    with pytest.raises(ops.DitsepError):   # 9 x 256 x 64 filter does not fit shared memory: no resident mode
-        ops.ConvTcPlan(x, w, 128, 3, shortcut=x)
-    xs = torch.randn(2, 4, 4, 64, device=DEV).to(torch.bfloat16)
-    ws = torch.zeros(64, 9 * 64 + 64, device=DEV, dtype=torch.bfloat16)
-    with pytest.raises(ops.DitsepError):   # image below one 8 x 16 tile
-        ops.ConvTcPlan(xs, ws, 64, 3, shortcut=xs)
-
-
-def test_first_layer_hilo_split_on_tensor_cores():
-    """ops.split_hilo + the [wh | wh | wl] filter (engine._pack_conv_hilo): the 6-channel fp32 input conv run by the
-    tcgen05 kernel must match the fp32 convolution to fp32-class accuracy, not bf16-class."""
-    from ditsep_b200.models.diffsep.engine import _pack_conv_hilo
-    B, H, W, Cin, Cout = 2, 32, 24, 6, 64
-    x = torch.randn(B, H, W, Cin, generator=g(70))
-    weight = torch.randn(Cout, Cin, 3, 3, generator=g(71)) / math.sqrt(9 * Cin)
-    bias = 0.1 * torch.randn(Cout, generator=g(72))
-    wide = torch.zeros(B, H, W, 64, device=DEV, dtype=torch.bfloat16)  # channels >= 24 are the caller's zeros
-    wide[..., :24] = 7.0
-    ops.split_hilo(x.to(DEV), wide)
-    hi = x.to(torch.bfloat16)
-    lo = (x - hi.float()).to(torch.bfloat16)
-    assert torch.equal(wide[..., :6].cpu(), hi) and torch.equal(wide[..., 6:12].cpu(), lo)
-    assert torch.equal(wide[..., 12:18].cpu(), hi) and not wide[..., 18:].any()
-    cw = _pack_conv_hilo(weight.to(DEV), bias.to(DEV))
-    assert cw.cout == Cout and cw.cin == 64
-    plan = ops.ConvTcPlan(wide, cw.w_bf16, Cout, 3)
-    out = torch.empty(B, H, W, Cout, device=DEV)
-    plan.run(cw.bias, out)
-    ref = torch.empty(B, H, W, Cout)
-    E.conv_direct(x, weight.permute(0, 2, 3, 1).reshape(Cout, 9, Cin).contiguous(), bias, ref, 3)
-    e = rel(out, ref)
-    print(f"hi/lo first layer vs fp32 conv: rel-L2 {e:.3e}")
-    assert e < 5e-5, e
-
-
 def test_gn_finalize_concat_sources():
     """GroupNorm over torch.cat([h, skip]) (ncsnpp.py:413) from two producers' statistics: a conv
-    epilogue's partials for h (128 ch) and an explicit split-sums pass for skip (64 ch); 6-channel groups
-    straddle the boundary."""
+    epilogue's sums for h (128 ch) and an explicit statistics pass for skip (64 ch); 6-channel groups straddle the
+    boundary."""
     B, H, W = 2, 32, 16
     buf, w, bias, _, _ = _conv_case(B, H, W, 64, 128, 3, 61)
     cat = torch.zeros(B, H, W, 192, device=DEV, dtype=torch.bfloat16)
     plan = ops.ConvTcPlan(buf.to(DEV).to(torch.bfloat16), w.to(DEV).to(torch.bfloat16), 128, 3)
-    st = torch.empty(plan.stats_floats(), device=DEV)
+    st = ops.new_sums(B, 128, DEV)
     plan.run(bias.to(DEV), cat[..., :128], stats=st)
     skip = torch.randn(B, H, W, 64, generator=g(62)).to(DEV).to(torch.bfloat16)
     cat[..., 128:] = skip
-    part = torch.empty(ops.gn_partial_floats(B, H * W, 64), device=DEV)
-    ops.gn_partial_sums(cat[..., 128:], part)
+    part = ops.new_sums(B, 64, DEV)
+    ops.gn_sums(cat[..., 128:], part)
     gamma, beta = 1 + 0.1 * torch.randn(192, generator=g(1)), 0.1 * torch.randn(192, generator=g(2))
     ss = torch.empty(B, 2, 192, device=DEV)
-    ops.gn_finalize([(st, plan.stats_layout()), (part, ops.split_sums_layout(H * W, 64))], B, H * W, 32,
-                    gamma.to(DEV), beta.to(DEV), 1e-6, ss)
+    ops.gn_finalize([st, part], B, H * W, 32, gamma.to(DEV), beta.to(DEV), 1e-6, ss)
     ss_ref = torch.empty(B, 2, 192)
-    E.gn_stats(cat.float().cpu(), 32, gamma, beta, 1e-6, None, ss_ref)
+    E.gn_stats(cat.float().cpu(), 32, gamma, beta, 1e-6, ss_ref)
     assert rel(ss, ss_ref) < 1e-4, rel(ss, ss_ref)
 
 

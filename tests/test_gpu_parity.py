@@ -71,6 +71,18 @@ SAMPLER_CASES = [("fp32", 1.0, "", 1e-3), ("fp32", 0.01, "_s0p01", 1e-3), ("bf16
                  ("bf16", 1.0, "", None)]
 
 
+def _traj_tol(g, key, tol):
+    """Tolerances of a whole trajectory (errors compound over 2N evaluations): the north-star numbers where a
+    tolerance is given; else what the REFERENCE's own bf16 arithmetic does to the reference's trajectory on this
+    weight set (pin script: reference sampler under torch.autocast(bfloat16), same tape, against its fp32 run) --
+    [worst per-step score rel-L2, |dSI-SDR| dB].  Measured for init_scale 1.0: 1.4e-1 / 0.17 dB (N=3) and
+    2.9e-1 / 1.3 dB (C1, N=30) for the reference, 8.8e-2 / 0.17 dB and 2.3e-1 / 0.74 dB for this path."""
+    if tol is not None:
+        return tol, 0.05
+    ac = g[key]
+    return float(ac[0]), max(0.05, float(ac[1]))
+
+
 def _per_step_rel_l2(scores_sub, ref_sub):
     """north_star: 'per-step score output relative L2' -- every evaluation of the trajectory, full sub-sampled
     tensors (every 64th sample), not norms."""
@@ -80,7 +92,7 @@ def _per_step_rel_l2(scores_sub, ref_sub):
 
 @pytest.mark.parametrize("precision,init_scale,tag,tol", SAMPLER_CASES)
 def test_sampler_small_vs_reference_golden(golden, precision, init_scale, tag, tol):
-    tol = _tol(golden, tag, tol)
+    tol, tol_db = _traj_tol(golden["ref" + tag], "sampler_small_autocast", tol)
     model, sd, cfg = build_model(precision, DEV, N=3, init_scale=init_scale)
     mixn, src = sampler_inputs(2, 7810)
     subs = []
@@ -103,7 +115,7 @@ def test_sampler_small_vs_reference_golden(golden, precision, init_scale, tag, t
     print(f"sampler small {precision} init_scale={init_scale}: final rel-L2 {e:.3e}, worst per-step score rel-L2 "
           f"{max(steps):.3e} (tol {tol:.1e}), |dSI-SDR| {d:.4f} dB")
     assert max(steps) < tol
-    assert d < 0.05
+    assert d < tol_db
 
 
 @pytest.mark.parametrize("precision,init_scale,tag,tol", SAMPLER_CASES)
@@ -111,7 +123,7 @@ def test_sampler_c1_vs_reference_golden(golden, precision, init_scale, tag, tol)
     """Config C1 (BASELINE.json configs[0]): N=30, 4 s @ 8 kHz, batch 1, seeded noise tape.
     The golden output is the reference sampler's; the per-step gate is the rel-L2 of EVERY one of the 60 score
     evaluations against the reference's own (sub-sampled) score tensor of that step."""
-    tol = _tol(golden, tag, tol)
+    tol, tol_db = _traj_tol(golden["c1" + tag], "autocast", tol)
     model, sd, cfg = build_model(precision, DEV, N=30, init_scale=init_scale)
     mixn, src = sampler_inputs(1, 32000)
     norms, subs = [], []
@@ -137,7 +149,7 @@ def test_sampler_c1_vs_reference_golden(golden, precision, init_scale, tag, tol)
     print(f"sampler C1 {precision} init_scale={init_scale}: final rel-L2 {e:.3e}, SI-SDR {float(sis.mean()):.3f} vs "
           f"{float(sis_ref.mean()):.3f} dB, worst per-step score rel-L2 {max(steps):.3e} at evaluation "
           f"{int(np.argmax(steps))} (tol {tol:.1e}), max score-norm deviation {dn:.3e}")
-    assert d < 0.05
+    assert d < tol_db
     assert max(steps) < tol
 
 
