@@ -153,20 +153,39 @@ def predictor_rd_ref(sde, x, t, y, score, noise):
     return x_mean + _pad(G, x) * noise, x_mean
 
 
+def schedule_timesteps_ref(schedule: Optional[str], T: float, eps: float, N: int) -> Tensor:
+    """Time grids: ``linspace(T, eps, N)`` of get_pc_sampler (src/sdes/__init__.py:175), or the N + 1 point grids of
+    get_pc_scheduled_sampler (:96-117)."""
+    import math
+    if schedule is None:
+        return torch.linspace(T, eps, N)
+    if schedule == "linear":
+        return torch.linspace(T, eps, N + 1)
+    if schedule == "log":
+        return torch.logspace(math.log(T) / math.log(10), math.log(eps) / math.log(10), N + 1, base=10)
+    if schedule == "revlog":
+        return torch.logspace(math.log(eps) / math.log(10), math.log(T) / math.log(10), N + 1, base=10).flip(dims=(0,))
+    raise NotImplementedError(f"Schedule '{schedule}' does not exist")
+
+
 def pc_sampler_ref(score_fn, sde, y: Tensor, noise: NoiseFn, corrector: str = "ald2",
                    eps: float = 3e-2, snr: float = 0.5, corrector_steps: int = 1, denoise: bool = True,
-                   n_spkrs: int = 2, on_score: Optional[Callable] = None) -> Tuple[Tensor, int]:
+                   n_spkrs: int = 2, on_score: Optional[Callable] = None,
+                   schedule: Optional[str] = None) -> Tuple[Tensor, int]:
     """``get_pc_sampler`` closure (src/sdes/__init__.py:168-191) with the
     ``reverse_diffusion`` predictor.  Noise draw order (quirk Q3): #0 prior, then per
     step i: corrector draws 1+2i.., predictor draw; 1 + N*(corrector_steps+1) draws.
     ``on_score(k, x, t, score)`` is called after each of the N*(corrector_steps+1)
-    score evaluations."""
+    score evaluations.
+    ``schedule`` ("linear" | "log" | "revlog"): the time grid of ``get_pc_scheduled_sampler``
+    (src/sdes/__init__.py:49-130) instead: N + 1 points of which the first N are visited; the step size the
+    reference computes from the grid never reaches ``discretize`` (quirk Q2), so dt stays 1/N."""
     with torch.no_grad():
         shape = (y.shape[0], n_spkrs, *y.shape[2:])
         draw = 0
         z = noise(draw, torch.empty(shape)); draw += 1
         xt = sde.prior_sampling(y, z)
-        timesteps = torch.linspace(sde.T, eps, sde.N)
+        timesteps = schedule_timesteps_ref(schedule, sde.T, eps, sde.N)
         k = 0
         xt_mean = xt
         for i in range(sde.N):

@@ -24,4 +24,5 @@ def golden():
     return {"ref": np.load(os.path.join(d, "reference_outputs.npz")),
             "c1": np.load(os.path.join(d, "sampler_c1.npz")),
             "ref_s0p01": np.load(os.path.join(d, "reference_outputs_s0p01.npz")),
-            "c1_s0p01": np.load(os.path.join(d, "sampler_c1_s0p01.npz"))}
+            "c1_s0p01": np.load(os.path.join(d, "sampler_c1_s0p01.npz")),
+            "variants": np.load(os.path.join(d, "variants.npz"))}

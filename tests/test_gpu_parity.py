@@ -332,3 +332,24 @@ def test_ragged_sweep_matches_batch_1_on_gpu():
                                 mixn, S.NoiseTape(901), corrector="ald2", eps=0.03, snr=0.5)
     m, s_ = mixes[1].mean(), mixes[1].std().clamp(min=1e-5)
     assert rel_l2(outs1[1], x_ref[0] * s_ + m) < 1e-3
+
+
+@pytest.mark.parametrize("schedule", ["linear", "log", "revlog"])
+def test_scheduled_sampler_vs_reference_golden(golden, schedule):
+    """get_pc_scheduled_sampler (src/sdes/__init__.py:49-130) on the fused update kernels against the reference's output
+    (closed-form score, taped noise), and through DiffSepModel.get_pc_sampler(schedule=...) (diffsep.py:623-695)."""
+    y = torch.randn(2, 1, 4096, generator=torch.Generator().manual_seed(5))
+
+    def toy_score(x, t, yy):
+        return -(x - 0.5 * yy) / (0.1 + t[:, None, None]) + 0.05 * torch.sin(3 * x)
+
+    x, nfe = sdes.get_pc_scheduled_sampler("reverse_diffusion", "ald2", sde=sdes.MixSDE(2, 2.0, 0.05, 0.5, N=6),
+                                           score_fn=toy_score, y=y.to(DEV), eps=0.03, snr=0.5, corrector_steps=1,
+                                           denoise=True, schedule=schedule, noise_tape=S.NoiseTape(80))()
+    assert nfe == 12
+    ref = torch.tensor(golden["variants"][f"scheduled_{schedule}"])
+    assert float((x.cpu() - ref).abs().max()) < 2e-5 * float(ref.abs().max())
+    model, sd, cfg = build_model("bf16", DEV, N=2)
+    xs, n = model.get_pc_sampler("reverse_diffusion", "ald2", sampler_inputs(1, 4096)[0].to(DEV), N=2, schedule=schedule,
+                                 snr=0.5, seed=3)()
+    assert n == 4 and torch.isfinite(xs).all()

@@ -175,3 +175,23 @@ def test_c_abi_library_exports_every_declared_symbol():
     # argument validation happens before any CUDA call: errors come back as codes + text, not exceptions
     rc = lib.ditsep_pc_corrector(None, None, None, None, 0, 0, None, None, 1, 8, None, None)
     assert rc != 0 and b"null" in lib.ditsep_last_error()
+
+
+@pytest.mark.parametrize("schedule", ["linear", "log", "revlog"])
+def test_scheduled_sampler_host_logic_vs_reference_golden(golden, schedule):
+    """get_pc_scheduled_sampler (src/sdes/__init__.py:49-130) through the emulated kernels against the REFERENCE's
+    output (oracle/pin_variants.py): time grids, N + 1 points, dt = 1/N quirk, draw numbering."""
+    y = torch.randn(2, 1, 4096, generator=torch.Generator().manual_seed(5))
+
+    def toy_score(x, t, yy):
+        return -(x - 0.5 * yy) / (0.1 + t[:, None, None]) + 0.05 * torch.sin(3 * x)
+
+    with emulated_ops():
+        x, nfe = sdes.get_pc_scheduled_sampler("reverse_diffusion", "ald2", sde=sdes.MixSDE(2, 2.0, 0.05, 0.5, N=6),
+                                               score_fn=toy_score, y=y, eps=0.03, snr=0.5, corrector_steps=1,
+                                               denoise=True, schedule=schedule, noise_tape=S.NoiseTape(80))()
+    assert nfe == 12
+    assert float((x - torch.tensor(golden["variants"][f"scheduled_{schedule}"])).abs().max()) < 1e-4
+    with emulated_ops(), pytest.raises(NotImplementedError):
+        sdes.get_pc_scheduled_sampler("reverse_diffusion", "ald2", sde=sdes.MixSDE(2, 2.0, 0.05, 0.5, N=2), score_fn=toy_score,
+                                      y=y, schedule="cosine", noise_tape=S.NoiseTape(1))()
