@@ -358,7 +358,7 @@ def run_sweep(args, dev, world, rank):
     import torch.distributed as dist
 
     from common import build_model
-    from ditsep_b200 import ops
+    from ditsep_b200 import evaluate, ops
     from ditsep_b200.utils import shard
     from ditsep_b200.utils.synth import synth_mixtures
 
@@ -380,8 +380,11 @@ def run_sweep(args, dev, world, rank):
     def one_sweep(seed):
         t0 = torch.cuda.Event(enable_timing=True); t1 = torch.cuda.Event(enable_timing=True)
         t0.record()
-        rows, outs = shard.separate_sharded(model, mixtures, references=refs, max_batch=B, device=dev, seed=seed,
-                                            rank=rank, world_size=world)
+        # the evaluation driver (reference row schema, SI-SDR / SIR / SAR with PIT on the device, summary)
+        rows, summary, outs = evaluate.evaluate_sweep(model, mixtures, refs, fs=16000, N=N_STEPS_SDE, snr=0.5,
+                                                      corrector_steps=1, denoise=True, max_batch=B, device=dev,
+                                                      seed=seed, perceptual=False)
+        rows = (rows, summary)
         t1.record()
         wav = shard.gather_waveforms(outs, lengths, dev) if world > 1 else None
         return rows, t0, t1, wav
@@ -408,7 +411,8 @@ def run_sweep(args, dev, world, rank):
     launches = ops.launch_count() - n0
     if rank == 0:
         value = n_mix * args.steps / (float(ms.item()) * 1e-3)
-        sdr = rows[:, 2:].mean().item()
+        results, summary = rows
+        assert sorted(results) == list(range(n_mix)) and all(r["nfe"] == NFE for r in results.values())
         line = {"metric": METRIC, "value": value, "unit": "mixtures/s", "n_gpus": world, "steps": args.steps,
                 "warmup": 1, "ms_per_step": float(ms.item()) / args.steps, "higher_is_better": True,
                 "scaling": "strong", "vs_baseline": None, "dtype": "bf16" if precision == "bf16" else "f32",
@@ -420,7 +424,8 @@ def run_sweep(args, dev, world, rank):
                         "d2h_bytes_per_step": 0},
                 "gpu_launches": launches,
                 "per_rank_busy_ms": [float(b.item()) for b in allbusy],
-                "mean_si_sdr_db_random_weights": sdr}
+                "summary_random_weights": {k: summary[k] for k in ("si_sdr", "si_sir", "si_sar", "nfe", "runtime",
+                                                                   "len_s", "number")}}
         print(json.dumps(line), flush=True)
     if world > 1:
         dist.barrier()

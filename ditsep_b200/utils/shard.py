@@ -161,7 +161,8 @@ def gather_waveforms(outs: Dict[int, torch.Tensor], lengths: Sequence[int], devi
 
 def separate_sharded(model, mixtures: Sequence[torch.Tensor], references=None, max_batch: int = 32, device=None,
                      sampler_kwargs=None, seed: int = 0, rank: int = None, world_size: int = None,
-                     noise_tape_factory=None, predictor: str = "reverse_diffusion", corrector: str = "ald2"):
+                     noise_tape_factory=None, predictor: str = "reverse_diffusion", corrector: str = "ald2",
+                     row_fn=None):
     """Sweep over independent mixtures, batch-sharded over the ranks of the default process group.
 
     mixtures: list of (1, T_i) tensors (any lengths); references: optional list of (n_src, T_i).
@@ -176,7 +177,13 @@ def separate_sharded(model, mixtures: Sequence[torch.Tensor], references=None, m
     (src/evaluate_mp.py:289,311); with a per-mixture noise tape (`ragged_tape`) the results are independent of
     max_batch and of the world size (tests/test_sharding_gloo.py, tests/test_gpu_parity.py).
     noise_tape_factory(idx) -> callable (i, shape) -> tensor: the tape of mixture idx (parity runs); default:
-    in-kernel Philox keyed by the global index of the batch's first mixture."""
+    in-kernel Philox keyed by the global index of the batch's first mixture.
+    row_fn(idx, est (n_src, T_i) de-normalised, nfe, runtime_s) -> list of floats: replaces the default row (the
+    evaluation driver, ditsep_b200/evaluate.py, uses it for the reference's row schema); runtime_s = the batch's
+    sampler wall time (device synchronised) divided by the batch size.  sampler_kwargs may carry `schedule`
+    ("linear" / "log" / "revlog": the scheduled sampler, diffsep.py:100-106 here, src/diffsep.py:404-441 there)."""
+    import time
+
     if world_size is None:
         world_size = dist.get_world_size() if dist.is_available() and dist.is_initialized() else 1
     if rank is None:
@@ -192,11 +199,20 @@ def separate_sharded(model, mixtures: Sequence[torch.Tensor], references=None, m
                  if noise_tape_factory is not None else {"seed": seed + 7919 * batch[0]})
         ragged = len(set(lengths[i] for i in batch)) > 1
         sampler = model.get_pc_sampler(predictor, corrector, yn, lengths=lens if ragged else None, **noise, **kw)
-        x, _ = sampler()
+        if yn.is_cuda:
+            torch.cuda.synchronize(yn.device)
+        t0 = time.perf_counter()
+        x, nfe = sampler()
+        if yn.is_cuda:
+            torch.cuda.synchronize(yn.device)
+        t_run = (time.perf_counter() - t0) / len(batch)
         x = x * std + mean
         for r, i in enumerate(batch):
             est = x[r, :, :lengths[i]]
             outs[i] = est
+            if row_fn is not None:
+                rows.append([float(v) for v in row_fn(i, est, nfe, t_run)])
+                continue
             row = [float(i), float(lengths[i])]
             if references is not None:
                 ref = references[i].to(est.device)[None]
@@ -206,5 +222,10 @@ def separate_sharded(model, mixtures: Sequence[torch.Tensor], references=None, m
                 row += [float("nan")] * n_src
             rows.append(row)
     dev = device if device is not None else "cpu"
-    table = torch.tensor(rows, dtype=torch.float32, device=dev).reshape(-1, 2 + n_src)
+    width = len(rows[0]) if rows else 2 + n_src
+    if row_fn is not None and dist.is_available() and dist.is_initialized() and world_size > 1:
+        w = torch.tensor([width], device=dev, dtype=torch.int64)   # a rank with no mixtures learns the width
+        dist.all_reduce(w, op=dist.ReduceOp.MAX)
+        width = int(w.item())
+    table = torch.tensor(rows, dtype=torch.float32, device=dev).reshape(-1, width)
     return gather_rows(table), outs

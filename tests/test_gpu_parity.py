@@ -353,3 +353,30 @@ def test_scheduled_sampler_vs_reference_golden(golden, schedule):
     xs, n = model.get_pc_sampler("reverse_diffusion", "ald2", sampler_inputs(1, 4096)[0].to(DEV), N=2, schedule=schedule,
                                  snr=0.5, seed=3)()
     assert n == 4 and torch.isfinite(xs).all()
+
+
+def test_evaluate_sweep_on_gpu_vs_oracle_metrics(tmp_path):
+    """The f1 evaluation driver on the device: reference row schema, device-side SI-SDR / SIR / SAR + permutation
+    against the numpy restatement (oracle/metrics_ref.py) on the signals it returns, schedule override, JSON dump."""
+    import json
+    from ditsep_b200 import evaluate as E
+    from ditsep_b200.utils.synth import synth_mixtures
+    from oracle import metrics_ref as M
+    model, _, _ = build_model("bf16", DEV, N=2)
+    lengths = [9000, 12000, 20000, 10500, 16000]
+    mix, src = synth_mixtures(5, 2, max(lengths), seed=78)
+    mixes = [mix[i, :, :n] for i, n in enumerate(lengths)]
+    refs = [src[i, :, :n] for i, n in enumerate(lengths)]
+    res, summ, outs = E.evaluate_sweep(model, mixes, refs, fs=8000, N=2, max_batch=4, device=DEV, seed=3,
+                                       output_dir=str(tmp_path))
+    assert sorted(res) == list(range(5)) and summ["number"] == 5 and summ["nfe"] == 4
+    for i, row in res.items():
+        assert tuple(row) == E.ROW_KEYS and row["nfe"] == 4 and row["runtime"] > 0
+        o_sdr, o_sir, o_sar, o_perm = M.si_bss_eval_ref(refs[i].numpy(), outs[i].float().cpu().numpy())
+        assert o_perm.tolist() == [0, 1]                           # returned signals are already in target order
+        for key, want in (("si_sdr", o_sdr), ("si_sir", o_sir), ("si_sar", o_sar)):
+            assert abs(torch.tensor(row[key][0]) - torch.tensor(want)).max() < 2e-3, (i, key, row[key], want)
+    assert json.load(open(tmp_path / "test_summary.json"))["number"] == 5
+    res_l, _, _ = E.evaluate_sweep(model, mixes, refs, fs=8000, N=3, corrector_steps=2, schedule="log", max_batch=4,
+                                   device=DEV, seed=3)
+    assert res_l[0]["nfe"] == 9
