@@ -49,6 +49,8 @@ SIGNATURES = {
                                     c_void_p]),
     "ditsep_gn_sums": (c_int, [c_void_p, c_int, c_int, c_int64, c_int, c_int, c_void_p, c_void_p]),
     "ditsep_gn_finalize": (c_int, [C.POINTER(GnJob), c_int, c_void_p]),
+    "ditsep_gn_stats_static": (c_int, [c_void_p, c_int, c_int, c_int64, c_int, c_int, c_int, c_void_p, c_void_p, c_float,
+                                       c_void_p, c_void_p]),
     "ditsep_gn_small": (c_int, [c_void_p, c_int, c_int, c_int64, c_int, c_int, c_int, c_void_p, c_void_p, c_float, c_int,
                                 c_void_p, c_int, c_void_p]),
     "ditsep_gn_apply": (c_int, [c_void_p, c_int, c_int, c_int64, c_int, c_int, c_void_p, c_int, c_void_p, c_int,

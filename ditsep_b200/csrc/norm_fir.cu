@@ -7,6 +7,7 @@
 // 283-285,297,318), upsample_2d / downsample_2d (up_or_down_sampling.py:206-273 ->
 // upfirdn2d, op/upfirdn2d_kernel.cu:107-207), temb (ncsnpp.py:325-346, layerspp.py:44-46,
 // 316-317), output scaling + output_layer (ncsnpp.py:473-477).
+#include <mutex>
 #include <type_traits>
 
 #include "common.cuh"
@@ -962,4 +963,64 @@ extern "C" int ditsep_output_layer(const void* x, int dtype, int B, int64_t HW, 
   else
     DITSEP_REQUIRE(false, "output_layer: unknown dtype %d", dtype);
   return check_launch("output_layer_kernel");
+}
+
+// ------------------------------------------------------------------- allocation-free GroupNorm statistics
+// ditsep_gn_stats_static: gn_sums + gn_finalize with the fixed-point sums in a file-scope device array, for callers
+// that cannot allocate (CUDA graph capture, serving loops, harnesses that forbid cudaMalloc).  No counterpart in the
+// reference.  Every GPU that loads the library holds the array (DITSEP_GN_STATIC_MAX_BC * 32 bytes = 512 KiB) until
+// exit.  All calls share it: it is cleared at the head of every call, and calls that overlap on the GPU (different
+// streams) race.
+static __device__ __align__(256) long long g_gn_static_sums[(size_t)DITSEP_GN_STATIC_MAX_BC * 4];
+
+__global__ void __launch_bounds__(256) gn_static_zero_kernel(int64_t n) {
+  // device code names the array directly; host code below uses the address cudaGetSymbolAddress returns
+  for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x)
+    g_gn_static_sums[i] = 0;
+}
+
+// device address of g_gn_static_sums on the CURRENT device, resolved once per device
+static int gn_static_address(long long** out) {
+  static std::mutex mu;
+  static long long* addr[64] = {};
+  int dev = -1;
+  DITSEP_CUDA(cudaGetDevice(&dev));
+  DITSEP_REQUIRE(dev >= 0 && dev < 64, "gn_stats_static: device ordinal %d out of range", dev);
+  std::lock_guard<std::mutex> lock(mu);
+  if (addr[dev] == nullptr) {
+    void* p = nullptr;
+    DITSEP_CUDA(cudaGetSymbolAddress(&p, g_gn_static_sums));
+    DITSEP_REQUIRE(p != nullptr, "gn_stats_static: cudaGetSymbolAddress returned null on device %d", dev);
+    addr[dev] = static_cast<long long*>(p);
+  }
+  *out = addr[dev];
+  return 0;
+}
+
+extern "C" int ditsep_gn_stats_static(const void* x, int dtype, int B, int64_t HW, int C, int ld, int G, const float* gamma,
+                                      const float* beta, float eps, float* scale_shift, void* stream) {
+  DITSEP_REQUIRE(x && gamma && beta && scale_shift, "gn_stats_static: null pointer");
+  DITSEP_REQUIRE(B > 0 && C > 0, "gn_stats_static: bad sizes B=%d C=%d", B, C);
+  DITSEP_REQUIRE((int64_t)B * C <= DITSEP_GN_STATIC_MAX_BC,
+                 "gn_stats_static: B*C = %lld exceeds the static scratch (DITSEP_GN_STATIC_MAX_BC = %d); use "
+                 "ditsep_gn_sums + ditsep_gn_finalize with a caller-owned sums buffer",
+                 (long long)B * C, (int)DITSEP_GN_STATIC_MAX_BC);
+  long long* sums = nullptr;
+  if (int rc = gn_static_address(&sums)) return rc;
+  const int64_t n = (int64_t)B * C * 4;
+  gn_static_zero_kernel<<<grid_for(n), 256, 0, (cudaStream_t)stream>>>(n);
+  if (int rc = check_launch("gn_static_zero_kernel")) return rc;
+  if (int rc = ditsep_gn_sums(x, dtype, B, HW, C, ld, sums, stream)) return rc;
+  ditsep_gn_job job = {};
+  job.src_sums[0] = sums;
+  job.src_C[0] = C;
+  job.n_src = 1;
+  job.C = C;
+  job.G = G;
+  job.eps = eps;
+  job.HW = HW;
+  job.gamma = gamma;
+  job.beta = beta;
+  job.scale_shift = scale_shift;
+  return ditsep_gn_finalize(&job, B, stream);
 }

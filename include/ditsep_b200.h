@@ -123,6 +123,19 @@ typedef struct {
 } ditsep_gn_job;
 /* scale/shift of one job (a tiny launch: B CTAs reading C * 32 bytes each). */
 int ditsep_gn_finalize(const ditsep_gn_job* host_job, int B, void* stream);
+/* Allocation-free GroupNorm statistics: scale/shift [B][2][C] of nn.GroupNorm(G, C, eps) over x (NHWC [B][HW][ld]) =
+ * ditsep_gn_sums + ditsep_gn_finalize, bit-identical to that pair, with the fixed-point sums held in a static
+ * device array inside the library instead of a caller-allocated buffer.  NO COUNTERPART IN THE REFERENCE: added
+ * for callers that cannot call cudaMalloc (code under CUDA graph capture, tight
+ * serving loops, harnesses that forbid allocation).  The call allocates nothing (no cudaMalloc / cudaFree, no
+ * allocating library routine): three kernel launches on `stream`.  Limit: B * C <= DITSEP_GN_STATIC_MAX_BC
+ * (16384 (b, c) pairs = 512 KiB of device memory, held by every GPU that loads the library until exit); larger
+ * sizes are rejected with an error, use the two-call form with your own buffer.  All calls share the one array: it
+ * is cleared at the head of every call, and two calls whose kernels overlap on the GPU (different streams without
+ * an ordering between them) race -- serialise them. */
+#define DITSEP_GN_STATIC_MAX_BC 16384
+int ditsep_gn_stats_static(const void* x, int dtype, int B, int64_t HW, int C, int ld, int G, const float* gamma,
+                           const float* beta, float eps, float* scale_shift, void* stream);
 /* GroupNorm statistics + normalise (+ SiLU) of SMALL images in one launch (one CTA per image; y may alias x):
  * act(GroupNorm(x)) of ResnetBlockBigGANpp.forward (layerspp.py:297,318) at the 16x16 .. 4x4 levels, where the
  * three-launch sequence gn_partial_sums -> gn_finalize -> gn_apply is pure launch latency.  HW <= 4096, C <= 256. */
