@@ -314,7 +314,8 @@ constexpr int kTileMaxBN = 64;
 // which order -- never depends on the batch size or on the grid: batch-invariant, bit-reproducible.
 struct TileWalk {
   int seg, seg_end, b, sidx, lt, lt_end, tx, ty;
-  __device__ __forceinline__ void start_segment(const ConvTcParams& p) {
+  template <typename P>
+  __device__ __forceinline__ void start_segment(const P& p) {
     b = seg / p.segs_per_image;
     sidx = seg - b * p.segs_per_image;
     lt = sidx * p.seg_len;
@@ -322,7 +323,8 @@ struct TileWalk {
     ty = lt / p.tiles_x;
     tx = lt - ty * p.tiles_x;
   }
-  __device__ __forceinline__ void init(const ConvTcParams& p) {
+  template <typename P>
+  __device__ __forceinline__ void init(const P& p) {
     const int64_t S = (int64_t)p.B * p.segs_per_image;
     seg = (int)((int64_t)blockIdx.x * S / gridDim.x);
     seg_end = (int)((int64_t)(blockIdx.x + 1) * S / gridDim.x);
@@ -330,7 +332,8 @@ struct TileWalk {
   }
   __device__ __forceinline__ bool done() const { return seg >= seg_end; }
   __device__ __forceinline__ bool last_of_segment() const { return lt + 1 == lt_end; }
-  __device__ __forceinline__ void next(const ConvTcParams& p) {
+  template <typename P>
+  __device__ __forceinline__ void next(const P& p) {
     if (++lt == lt_end) {
       if (++seg < seg_end) start_segment(p);
     } else if (++tx == p.tiles_x) {
@@ -763,6 +766,10 @@ __global__ void __launch_bounds__(kTileThreads, 1) conv_tc_tile_kernel(const __g
 }
 
 
+}  // namespace ditsep
+#include "conv_ts.cuh"
+namespace ditsep {
+
 // ---- host side ------------------------------------------------------------------------------
 typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
                                   const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
@@ -797,6 +804,10 @@ struct ditsep_conv_plan {
   size_t smem;
   int tile;      // 1 = conv_tc_tile_kernel
   int grid_x;
+  int ts;        // 1 = conv_ts_kernel (64 -> 64 3x3, filter in tensor memory) when the call's epilogue allows it
+  ConvTsParams tp;
+  size_t ts_smem;
+  int ts_grid;
 };
 
 extern "C" int ditsep_conv_tc_plan_create(ditsep_conv_plan** plan, const void* in, int B, int H, int W, int Cin,
@@ -919,7 +930,36 @@ extern "C" int ditsep_conv_tc_plan_create_sc(ditsep_conv_plan** plan, const void
     if (grid_x > n_segs) grid_x = (int)n_segs;
   }
 
+  // ---- filter-in-tensor-memory kernel (conv_ts.cuh): 3x3, 64 -> 64 channels, shortcut of 0 / 64 / 128 channels,
+  // images of at least 64 x 64 (below that the 15-of-16 row tiling wastes too much); DITSEP_CONV_TS=0 turns it off
+  ConvTsParams tp{};
+  int ts = 0, ts_grid = 0;
+  size_t ts_smem = 0;
+  {
+    const char* ts_env = getenv("DITSEP_CONV_TS");
+    const int cx = x_sc ? Cx : 0;
+    if (tile && ksize == 3 && Cin == 64 && Cout == 64 && (cx == 0 || cx == 64 || cx == 128) && W % kTileW == 0 &&
+        H >= 64 && W >= 64 && !(ts_env && strcmp(ts_env, "0") == 0)) {
+      ts = 1;
+      tp.B = B; tp.H = H; tp.W = W; tp.xchunks = cx / kBlockK;
+      tp.tiles_x = W / kTileW;
+      tp.tiles_y = ceil_div(H, kTsRows);
+      tp.tiles_per_image = tp.tiles_x * tp.tiles_y;
+      tp.seg_len = tp.tiles_per_image >= 512 ? 3 : (tp.tiles_per_image >= 128 ? 2 : 1);
+      tp.segs_per_image = ceil_div(tp.tiles_per_image, tp.seg_len);
+      tp.stages = 5;
+      tp.w = reinterpret_cast<const bf16*>(w_bf16);
+      tp.ldw = 9 * 64 + cx;
+      ts_smem = 1024 + (size_t)tp.stages * kTsStageBytes + kTsExchBytes;
+      int dev = 0, sms = kNumSMs;
+      if (cudaGetDevice(&dev) == cudaSuccess) cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+      const int64_t n_segs = (int64_t)B * tp.segs_per_image;
+      ts_grid = (int)(sms < n_segs ? sms : n_segs);
+    }
+  }
+
   ditsep_conv_plan* pl = new ditsep_conv_plan();
+  pl->ts = ts; pl->tp = tp; pl->ts_smem = ts_smem; pl->ts_grid = ts_grid;
   pl->p = p;
   pl->smem = smem;
   pl->tile = tile;
@@ -980,6 +1020,8 @@ extern "C" int ditsep_conv_tc_plan_create_sc(ditsep_conv_plan** plan, const void
     DITSEP_TILE_ATTR(1, false, false); DITSEP_TILE_ATTR(3, true, true); DITSEP_TILE_ATTR(3, true, false);
     DITSEP_TILE_ATTR(3, false, true); DITSEP_TILE_ATTR(3, false, false);
 #undef DITSEP_TILE_ATTR
+    DITSEP_CUDA(cudaFuncSetAttribute(conv_ts_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 216 * 1024));
+    DITSEP_CUDA(cudaFuncSetAttribute(conv_ts_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 216 * 1024));
     if (attr_known) attr_set[attr_dev].store(true, std::memory_order_release);
   }
   *plan = pl;
@@ -1025,6 +1067,18 @@ extern "C" int ditsep_conv_tc_run(const ditsep_conv_plan* plan, const float* bia
     lcfg.stream = st;
     lcfg.attrs = lattr;
     lcfg.numAttrs = pdl ? 1 : 0;
+    if (plan->ts && fast && !residual) {
+      ConvTsParams tp = plan->tp;
+      tp.bias = bias; tp.bias_b = bias_b; tp.ld_bias_b = ld_bias_b;
+      tp.out_scale = out_scale; tp.out = reinterpret_cast<bf16*>(out); tp.ld_out = ld_out; tp.stats = stats;
+      tp.trace = g_conv_trace;
+      lcfg.gridDim = dim3((unsigned)plan->ts_grid);
+      lcfg.blockDim = dim3(kTsThreads);
+      lcfg.dynamicSmemBytes = plan->ts_smem;
+      if (ld_out == 64) DITSEP_CUDA(cudaLaunchKernelEx(&lcfg, conv_ts_kernel<true>, plan->mapA, plan->mapX, tp));
+      else DITSEP_CUDA(cudaLaunchKernelEx(&lcfg, conv_ts_kernel<false>, plan->mapA, plan->mapX, tp));
+      return check_launch("conv_ts_kernel");
+    }
 #define DITSEP_TILE_LAUNCH(KS, RES, FAST)                                                                             \
   do {                                                                                                                \
     lcfg.blockDim = dim3(kTileThreads);                                                                               \

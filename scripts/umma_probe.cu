@@ -18,13 +18,13 @@ __device__ __forceinline__ bool elect_one_sync() {
 }
 
 __global__ void __launch_bounds__(128, 1) probe(int N, int mode, int iters, int sbo_bytes, long long* out, int M = 128,
-                                                int sbo_b_bytes = 1024) {
+                                                int sbo_b_bytes = 1024, int b_shift_rows = 0, int a_tiles = 4) {
   extern __shared__ uint8_t raw[];
   __shared__ __align__(8) uint64_t bar2[2];
   __shared__ uint32_t tmem_slot;
   const uint32_t base = (smem_u32(raw) + 1023u) & ~1023u;
   // A: up to 24 KB region (16 groups of 8 rows, group pitch sbo_bytes <= 1536); B: 256 rows x 128 B after it
-  const uint32_t a_addr = base, b_addr = base + 32768;
+  const uint32_t a_addr = base, b_addr = base + 32768 + 128u * (uint32_t)b_shift_rows;
   for (uint32_t i = threadIdx.x; i < (32768 + 49152) / 4; i += blockDim.x) {
     uint32_t h = (i * 2654435761u) ^ (blockIdx.x * 40503u);
     // two bf16 values in [-1, 1): sign + exponent 0x3f00.. keeps them finite
@@ -55,6 +55,7 @@ __global__ void __launch_bounds__(128, 1) probe(int N, int mode, int iters, int 
     const uint32_t a_tmem = tmem + 448 - ((mode & 4) ? 64 : 0);  // TS mode: A operand columns (128 lanes x 8 columns per K = 16), past the accumulators
     const bool ts = (mode & 1) != 0, alt = (mode & 2) != 0, cp = (mode & 4) != 0;
     const long long t0 = clock64();
+    uint32_t a_cur = 0;
     if (elect_one_sync()) {
 #pragma unroll 1
     for (int it = 0; it < iters; ++it) {
@@ -69,7 +70,7 @@ __global__ void __launch_bounds__(128, 1) probe(int N, int mode, int iters, int 
         if (ts) {
           asm volatile(
               "{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %3, 0;\n\t"
-              "tcgen05.mma.cta_group::1.kind::f16 [%0], [%1], %2, %4, p;\n\t}" ::"r"(d), "r"(a_tmem + 8 * k + ((cp && (it & 1)) ? 32u : 0u)), "l"(db),
+              "tcgen05.mma.cta_group::1.kind::f16 [%0], [%1], %2, %4, p;\n\t}" ::"r"(d), "r"(a_tiles > 4 ? tmem + 256u + 8u * a_cur : a_tmem + 8 * k + ((cp && (it & 1)) ? 32u : 0u)), "l"(db),
               "r"(1u), "r"(idesc)
               : "memory");
         } else {
@@ -79,6 +80,7 @@ __global__ void __launch_bounds__(128, 1) probe(int N, int mode, int iters, int 
               "tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %4, p;\n\t}" ::"r"(d), "l"(da), "l"(db), "r"(1u), "r"(idesc)
               : "memory");
         }
+        if (++a_cur == (uint32_t)a_tiles) a_cur = 0;
       }
     }
     asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(smem_u32(&bar)) : "memory");
@@ -233,6 +235,20 @@ int main() {
   for (int N : {80, 144, 160, 176, 208, 240}) run1("TS odd N", N, 1, 128, 1024);
   for (int N : {128, 144, 256}) run1("TS, B groups 1280 B apart", N, 1, 128, 1280);
   for (int N : {128, 144, 256}) run1("SS, B groups 1280 B apart", N, 0, 128, 1280);
+  // r2r: is the TS rate kept when the B start is shifted by whole rows inside a swizzle atom (the conv's tap shifts) and
+  // when every MMA reads a different A tile (24 tiles = the conv's filter)?
+  auto run2 = [&](const char* label, int N, int shift, int tiles) {
+    for (int rep = 0; rep < 2; ++rep) probe<<<sms, 128, 90 * 1024>>>(N, 1, iters, 1024, d_out, 128, 1280, shift, tiles);
+    cudaError_t e = cudaDeviceSynchronize();
+    if (e != cudaSuccess) { printf("%s: %s\n", label, cudaGetErrorString(e)); exit(1); }
+    std::vector<long long> h(sms);
+    cudaMemcpy(h.data(), d_out, sizeof(long long) * sms, cudaMemcpyDeviceToHost);
+    std::sort(h.begin(), h.end());
+    printf("%-28s N=%3d B shift %2d rows, %2d A tiles  %7.1f clk/MMA\n", label, N, shift, tiles, (double)h[sms / 2] / (iters * 4.0));
+  };
+  for (int shift : {0, 1, 2, 4, 8, 20, 21, 22}) run2("TS shifted B", 128, shift, 4);
+  for (int tiles : {5, 6, 8, 12, 24, 32}) run2("TS many A tiles", 128, 1, tiles);
+  for (int tiles : {8, 24}) run2("TS many A tiles", 64, 1, tiles);
   for (int mode = 0; mode < 2; ++mode)
     for (int N : {64, 128, 256}) {
       for (int rep = 0; rep < 2; ++rep) probe2<<<sms / 2 * 2, 128, 90 * 1024>>>(N, mode, iters, d_out);

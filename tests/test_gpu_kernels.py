@@ -407,6 +407,65 @@ def test_conv_tc_fused_shortcut(B, H, W, Cin, Cout, Cx, k, ld_extra):
     assert torch.equal(outb, outb2) and rel(outb.float(), ref) < 4e-3
 
 
+@pytest.mark.parametrize("B,H,W,Cx", [
+    (2, 64, 64, 0),        # 5 row tiles of 15 (last: 4 rows -> N = 48)
+    (1, 128, 72, 64),      # identity-shaped shortcut chunk, last tile 8 rows (N = 80)
+    (3, 100, 64, 128),     # two shortcut chunks (all 512 TMEM columns), ragged height, three images
+    (1, 256, 256, 0),      # the dominant shape: 18 row tiles, the last with ONE valid row (N = 16)
+])
+def test_conv_ts_filter_in_tensor_memory(B, H, W, Cx, monkeypatch):
+    """conv_ts_kernel (64 -> 64 3x3, filter as the TMEM A operand, two taps stacked on M, pixels on N) against the fp32
+    reference and against conv_tc_tile_kernel on the same operands; fused statistics, batch invariance, repeatability."""
+    Cin = Cout = 64
+    h = torch.randn(B, H, W, Cin, generator=g(90)).to(torch.bfloat16)
+    wm = (torch.randn(Cout, 9, Cin, generator=g(91)) / math.sqrt(9 * Cin)).to(torch.bfloat16)
+    bias = 0.1 * torch.randn(Cout, generator=g(92))
+    bias_b = 0.1 * torch.randn(B, Cout, generator=g(93))
+    wpad = torch.zeros(Cout, 9 * Cin + Cx, dtype=torch.bfloat16)
+    wpad[:, :9 * Cin] = wm.reshape(Cout, -1)
+    sc = torch.zeros(B, H, W, Cout)
+    xd = None
+    if Cx:
+        x = torch.randn(B, H, W, Cx, generator=g(94)).to(torch.bfloat16)
+        wsc = (torch.randn(Cout, 1, Cx, generator=g(95)) / math.sqrt(Cx)).to(torch.bfloat16)
+        wpad[:, 9 * Cin:] = wsc.reshape(Cout, -1)
+        E.conv_direct(x.float(), wsc.float(), torch.zeros(Cout), sc, 1)
+        xd = x.to(DEV)
+    ref = torch.empty(B, H, W, Cout)
+    E.conv_direct(h.float(), wm.float(), bias, ref, 3, bias_b=bias_b, residual=sc, out_scale=0.7)
+    hd, wd = h.to(DEV), wpad.to(DEV)
+
+    def run(ts, hd_=hd, xd_=xd, bb=bias_b):
+        monkeypatch.setenv("DITSEP_CONV_TS", "1" if ts else "0")   # read when the plan is created
+        plan = ops.ConvTcPlan(hd_, wd, Cout, 3, shortcut=xd_)
+        st = ops.new_sums(hd_.shape[0], Cout, DEV)
+        out = torch.full((hd_.shape[0], H, W, Cout), float("nan"), device=DEV, dtype=torch.bfloat16)
+        plan.run(bias.to(DEV), out, bias_b=bb.to(DEV), out_scale=0.7, stats=st)
+        torch.cuda.synchronize()
+        return out, st
+
+    n0 = ops.launch_count()
+    out, st = run(True)
+    old, st_old = run(False)
+    assert not torch.isnan(out.float()).any()
+    e_ref, e_old = rel(out.float(), ref), rel(out.float(), old.float())
+    print(f"conv_ts {B}x{H}x{W} Cx={Cx}: rel-L2 vs fp32 reference {e_ref:.2e} (tile kernel {rel(old.float(), ref):.2e}), "
+          f"vs tile kernel {e_old:.2e}, bf16 outputs that differ: {float((out != old).float().mean()):.2e}")
+    assert e_ref < 4e-3 and e_old < 1e-3             # bf16 output rounding; the kernels differ in summation order only
+    assert float((out != old).float().mean()) < 0.02
+    sums = _conv_sums(st)
+    of = out.double().cpu()
+    # statistics are those of the fp32 values BEFORE the bf16 rounding of the store (zero-mean noise of 2^-9 relative)
+    assert rel(sums[..., 1], (of * of).sum(dim=(1, 2))) < 3e-4
+    assert float(((sums[..., 0] - of.sum(dim=(1, 2))).abs() / of.abs().sum(dim=(1, 2))).max()) < 3e-4
+    assert rel(sums, _conv_sums(st_old)) < 2e-5                      # and equal to the tile kernel's to fp32 rounding
+    out2, st2 = run(True)
+    assert torch.equal(out, out2) and torch.equal(st, st2)
+    if B > 1:  # batch-invariant: the last image alone gives the same bits
+        o1, s1 = run(True, hd[B - 1:], None if xd is None else xd[B - 1:], bias_b[B - 1:])
+        assert torch.equal(o1, out[B - 1:]) and torch.equal(s1[0], st[B - 1])
+
+
 def test_gn_finalize_concat_sources():
     """GroupNorm over torch.cat([h, skip]) (ncsnpp.py:413) from two producers' statistics: a conv
     epilogue's sums for h (128 ch) and an explicit statistics pass for skip (64 ch); 6-channel groups straddle the
