@@ -19,7 +19,7 @@ BUILD = os.path.join(HERE, "_build")
 LIB = os.path.join(HERE, "libditsep_b200.so")
 SOURCES = ["lib.cu", "pc_step.cu", "spectral.cu", "norm_fir.cu", "conv_direct.cu", "attention.cu", "conv_tc.cu"]
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-O3", "-lineinfo", "-std=c++17", "-Xcompiler", "-fPIC",
-              "--expt-relaxed-constexpr", "-Xptxas", "-v"]
+              "--expt-relaxed-constexpr", "-Xptxas", "-v"] + os.environ.get("DITSEP_NVCC_EXTRA", "").split()
 
 
 def _nvcc() -> str:

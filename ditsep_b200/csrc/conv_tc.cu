@@ -953,8 +953,8 @@ extern "C" int ditsep_conv_tc_plan_create_sc(ditsep_conv_plan** plan, const void
       ts_smem = 1024 + (size_t)tp.stages * kTsStageBytes + kTsExchBytes;
       int dev = 0, sms = kNumSMs;
       if (cudaGetDevice(&dev) == cudaSuccess) cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
-      const int64_t n_segs = (int64_t)B * tp.segs_per_image;
-      ts_grid = (int)(sms < n_segs ? sms : n_segs);
+      const int64_t n_t = (int64_t)B * tp.tiles_per_image;
+      ts_grid = (int)(sms < n_t ? sms : n_t);
     }
   }
 

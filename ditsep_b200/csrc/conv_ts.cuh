@@ -57,6 +57,52 @@ struct ConvTsParams {
   long long* trace;      // debug (ditsep_debug_conv_trace): [4 CTAs][kTraceTiles][16] clock64 stamps, else nullptr
 };
 
+// Packed fp32 pairs in a 64-bit register (sm_100: add / fma on two fp32 lanes per instruction).
+__device__ __forceinline__ uint64_t f2_pack(float lo, float hi) {
+  uint64_t r;
+  asm("mov.b64 %0, {%1, %2};" : "=l"(r) : "f"(lo), "f"(hi));
+  return r;
+}
+__device__ __forceinline__ void f2_unpack(uint64_t v, float& lo, float& hi) {
+  asm("mov.b64 {%0, %1}, %2;" : "=f"(lo), "=f"(hi) : "l"(v));
+}
+__device__ __forceinline__ uint64_t f2_add(uint64_t a, uint64_t b) {
+  uint64_t d;
+  asm("add.rn.f32x2 %0, %1, %2;" : "=l"(d) : "l"(a), "l"(b));
+  return d;
+}
+__device__ __forceinline__ uint64_t f2_fma(uint64_t a, uint64_t b, uint64_t c) {
+  uint64_t d;
+  asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(d) : "l"(a), "l"(b), "l"(c));
+  return d;
+}
+
+// CTA c walks the tiles [c*T/G, (c+1)*T/G) of the B * tiles_per_image tiles (x fastest, then y, then image): divisions
+// once at the start, increments afterwards.  The statistics are accumulated as fixed-point integers per TILE (below),
+// so no unit coarser than a tile has to be kept together for batch invariance.
+struct TsWalk {
+  int left, b, tx, ty;
+  template <typename P>
+  __device__ __forceinline__ void init(const P& p) {
+    const int64_t T = (int64_t)p.B * p.tiles_per_image;
+    const int t0 = (int)((int64_t)blockIdx.x * T / gridDim.x);
+    left = (int)((int64_t)(blockIdx.x + 1) * T / gridDim.x) - t0;
+    b = t0 / p.tiles_per_image;
+    const int r = t0 - b * p.tiles_per_image;
+    ty = r / p.tiles_x;
+    tx = r - ty * p.tiles_x;
+  }
+  __device__ __forceinline__ bool done() const { return left <= 0; }
+  template <typename P>
+  __device__ __forceinline__ void next(const P& p) {
+    --left;
+    if (++tx == p.tiles_x) {
+      tx = 0;
+      if (++ty == p.tiles_y) { ty = 0; ++b; }
+    }
+  }
+};
+
 // Per-tile clock64 stamps (scripts/trace_conv.py) only in builds with -DDITSEP_TS_TRACE: each call site costs the
 // 16 epilogue warps three instructions per tile otherwise.
 __device__ __forceinline__ void ts_stamp(const ConvTsParams& p, uint32_t it, int slot) {
@@ -73,7 +119,6 @@ __global__ void __launch_bounds__(kTsThreads, 1) conv_ts_kernel(const __grid_con
   extern __shared__ uint8_t smem_raw[];
   __shared__ __align__(8) uint64_t bar_full[kTsMaxStages], bar_empty[kTsMaxStages];
   __shared__ __align__(8) uint64_t bar_acc_full[2], bar_acc_empty[2], bar_turn[2];
-  __shared__ __align__(16) float seg_part[2][8][64][2];  // [segment parity][warp slot][channel][sum | sumsq]
   __shared__ uint32_t tmem_base_slot;
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -143,7 +188,7 @@ __global__ void __launch_bounds__(kTsThreads, 1) conv_ts_kernel(const __grid_con
       griddep_wait();  // the activations are the predecessor's output
       int sa = 0;
       uint32_t pa = 1;  // "empty" barriers start free
-      TileWalk tw;
+      TsWalk tw;
       uint32_t itp = 0;
       for (tw.init(p); !tw.done(); tw.next(p), ++itp) {
         const int x0 = tw.tx * kTileW, y0 = tw.ty * kTsRows;
@@ -177,7 +222,7 @@ __global__ void __launch_bounds__(kTsThreads, 1) conv_ts_kernel(const __grid_con
     constexpr uint32_t kRow16 = 128 >> 4;
     int sa = 0;
     uint32_t pa = 0, it = 0;
-    TileWalk tw;
+    TsWalk tw;
     for (tw.init(p); !tw.done(); tw.next(p), ++it) {
       if ((it & 1u) != my) {  // the other warp's tile: step over its stages
         for (int i = 0; i < nsteps; ++i)
@@ -246,18 +291,38 @@ __global__ void __launch_bounds__(kTsThreads, 1) conv_ts_kernel(const __grid_con
     const float osc = p.out_scale;
     // byte stride between pixels of the output: a compile-time constant for dense tensors (immediate store offsets)
     const int64_t pix_bytes = kDense ? 128 : (int64_t)p.ld_out * 2;
-    float s = 0.f, sq = 0.f, cb = 0.f;
+    float cb = 0.f;
+    uint64_t cb2 = 0ull;
+    // statistics of this thread's channel: fixed-point {integer, fraction * 2^32} of sum and sum of squares (fx_add's
+    // format), accumulated per TILE from an fp32 partial that depends on the tile only -> order-independent, batch-invariant
+    long long fx_s = 0, fx_sf = 0, fx_q = 0, fx_qf = 0;
+    const uint64_t osc2 = f2_pack(osc, osc);
     int cur_b = -1;
-    uint32_t it = 0, nseg = 0;
-    TileWalk tw;
+    uint32_t it = 0;
+    // the image's sums get this thread's fixed-point totals when the CTA moves to the next image and at the end
+    auto flush_stats = [&](const int b) {
+      if (p.stats) {
+        unsigned long long* d = reinterpret_cast<unsigned long long*>(p.stats + ((int64_t)b * 64 + co) * 4);
+        atomicAdd(d, (unsigned long long)fx_s);
+        atomicAdd(d + 1, (unsigned long long)fx_sf);
+        atomicAdd(d + 2, (unsigned long long)fx_q);
+        atomicAdd(d + 3, (unsigned long long)fx_qf);
+        fx_s = fx_sf = fx_q = fx_qf = 0;
+      }
+    };
+    TsWalk tw;
     for (tw.init(p); !tw.done(); tw.next(p), ++it) {
       const int pb = tw.b;
+      if (etid == 0) ts_stamp(p, it, 9);
+      uint64_t s2 = 0ull, sq2 = 0ull;  // this tile's partial sums, packed fp32 pairs (even | odd pixels of a row)
       if (pb != cur_b) {
+        if (cur_b >= 0) flush_stats(cur_b);
         cur_b = pb;
         float a = 0.f;
         if (p.bias) a += __ldg(p.bias + co);
         if (p.bias_b) a += __ldg(p.bias_b + (int64_t)pb * p.ld_bias_b + co);
         cb = a * osc;  // out = fma(acc, scale, (bias + bias_b) * scale)
+        cb2 = f2_pack(cb, cb);
       }
       const uint32_t ab = it & 1u;
       mbar_wait_sleep(smem_u32(&bar_acc_full[ab]), (it >> 1) & 1u);
@@ -291,44 +356,46 @@ __global__ void __launch_bounds__(kTsThreads, 1) conv_ts_kernel(const __grid_con
       };
       if (is_b) send(v0, v1); else send(v2, v3);
       named_bar_sync(1 + pair, 64);
+      if (etid == 0) ts_stamp(p, it, 7);
+      // Packed fp32x2 arithmetic (add.rn.f32x2 / fma.rn.f32x2: two IEEE operations per instruction, same bits as the
+      // scalar forms): the SM is issue-bound here -- 16 epilogue warps share the four schedulers with the two
+      // MMA-issuing warps, whose issue latency sets the tensor pipe's feed rate (profiles/r2s).
       auto finish = [&](const uint32_t (&v)[8], const int i) {
         const int g = gout + i, y = tw.ty * kTsRows + g;
         if (g < kTsRows && y < p.H) {
           const float4 e0 = exr[2 * i], e1 = exr[2 * i + 1];
-          const float e[8] = {e0.x, e0.y, e0.z, e0.w, e1.x, e1.y, e1.z, e1.w};
+          const uint64_t e[4] = {f2_pack(e0.x, e0.y), f2_pack(e0.z, e0.w), f2_pack(e1.x, e1.y), f2_pack(e1.z, e1.w)};
           uint8_t* op = reinterpret_cast<uint8_t*>(p.out + ((int64_t)(pb * p.H + y) * p.W + tw.tx * kTileW) * p.ld_out + co);
 #pragma unroll
-          for (int j = 0; j < 8; ++j) {
-            const float f = fmaf(__uint_as_float(v[j]) + e[j], osc, cb);
-            *reinterpret_cast<bf16*>(op + j * pix_bytes) = __float2bfloat16_rn(f);
-            s += f;
-            sq = fmaf(f, f, sq);
+          for (int jj = 0; jj < 4; ++jj) {
+            const uint64_t a = f2_add(f2_pack(__uint_as_float(v[2 * jj]), __uint_as_float(v[2 * jj + 1])), e[jj]);
+            const uint64_t f = f2_fma(a, osc2, cb2);
+            s2 = f2_add(s2, f);
+            sq2 = f2_fma(f, f, sq2);
+            float f0, f1;
+            f2_unpack(f, f0, f1);
+            const __nv_bfloat162 h = __floats2bfloat162_rn(f0, f1);  // .x (low half) = f0
+            const uint32_t hb = *reinterpret_cast<const uint32_t*>(&h);
+            *reinterpret_cast<uint16_t*>(op + (2 * jj) * pix_bytes) = (uint16_t)hb;
+            *reinterpret_cast<uint16_t*>(op + (2 * jj + 1) * pix_bytes) = (uint16_t)(hb >> 16);
           }
         }
       };
-      if (is_b) { finish(v2, 0); finish(v3, 1); } else { finish(v0, 0); finish(v1, 1); }
+      if (is_b) { finish(v2, 0); finish(v3, 1); } else { finish(v0, 0); if (etid == 0) ts_stamp(p, it, 8); finish(v1, 1); }
       if (etid == 0) ts_stamp(p, it, 5);
-      if (p.stats && tw.last_of_segment()) {
-        // 8 threads (warp slots) hold partials of one channel: combine them in shared memory in a FIXED order (what is
-        // summed, and how, depends on the segment only: batch-invariant), then one fixed-point add per channel and
-        // statistic.  Buffers alternate per segment: a buffer is rewritten two segments later, after the barrier of the
-        // segment in between, which its readers reach only once they are done.
-        float (*sp)[64][2] = seg_part[nseg & 1u];
-        const int slot = k * 2 + (is_b ? 1 : 0);
-        sp[slot][co][0] = s;
-        sp[slot][co][1] = sq;
-        s = sq = 0.f;
-        named_bar_sync(9, kEpiWarps * 32);
-        if (etid < 128) {
-          const int c = etid >> 1, w = etid & 1;
-          float a = 0.f;
-#pragma unroll
-          for (int i = 0; i < 8; ++i) a += sp[i][c][w];
-          fx_add(p.stats + ((int64_t)pb * 64 + c) * 4 + 2 * w, a);
-        }
-        ++nseg;
+      if (p.stats) {
+        float sa, sb, qa2, qb2;
+        f2_unpack(s2, sa, sb);
+        f2_unpack(sq2, qa2, qb2);
+        const float ts = sa + sb, tq = qa2 + qb2;
+        const float fs = floorf(ts), fq = floorf(tq);
+        fx_s += (long long)fs;
+        fx_sf += (long long)((ts - fs) * 4294967296.0f);
+        fx_q += (long long)fq;
+        fx_qf += (long long)((tq - fq) * 4294967296.0f);
       }
     }
+    if (cur_b >= 0) flush_stats(cur_b);
   }
   tc_fence_before();
   __syncthreads();

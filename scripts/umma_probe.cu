@@ -18,10 +18,12 @@ __device__ __forceinline__ bool elect_one_sync() {
 }
 
 __global__ void __launch_bounds__(128, 1) probe(int N, int mode, int iters, int sbo_bytes, long long* out, int M = 128,
-                                                int sbo_b_bytes = 1024, int b_shift_rows = 0, int a_tiles = 4) {
+                                                int sbo_b_bytes = 1024, int b_shift_rows = 0, int a_tiles = 4, int hammer = 0) {
   extern __shared__ uint8_t raw[];
   __shared__ __align__(8) uint64_t bar2[2];
   __shared__ uint32_t tmem_slot;
+  __shared__ volatile int stop_flag;
+  if (threadIdx.x == 0) stop_flag = 0;
   const uint32_t base = (smem_u32(raw) + 1023u) & ~1023u;
   // A: up to 24 KB region (16 groups of 8 rows, group pitch sbo_bytes <= 1536); B: 256 rows x 128 B after it
   const uint32_t a_addr = base, b_addr = base + 32768 + 128u * (uint32_t)b_shift_rows;
@@ -98,6 +100,36 @@ __global__ void __launch_bounds__(128, 1) probe(int N, int mode, int iters, int 
     }
     const long long t1 = clock64();
     if (threadIdx.x == 0) out[blockIdx.x] = (mode & 8) ? (t1 - t0) / 2 : (t1 - t0);  // dual issue: per MMA of the pair
+    if (threadIdx.x == 0) stop_flag = 1;
+  } else if (hammer) {
+    // r2t: what slows queued MMAs inside the conv kernel?  Warps 1-3 load one resource while warp 0 issues:
+    // 1 = ld.shared.v4, 2 = st.shared.v4 (A region: the TS MMAs read only B), 3 = tcgen05.ld of the accumulator columns,
+    // 4 = ALU only (issue slots)
+    uint32_t acc = threadIdx.x;
+    const uint32_t my = a_addr + (threadIdx.x - 32) * 16;
+    while (!stop_flag) {
+#pragma unroll 1
+      for (int r = 0; r < 16; ++r) {
+        if (hammer == 1) {
+          uint32_t x0, x1, x2, x3;
+          asm volatile("ld.shared.v4.u32 {%0,%1,%2,%3}, [%4];" : "=r"(x0), "=r"(x1), "=r"(x2), "=r"(x3) : "r"(my + (r & 7) * 1536));
+          acc += x0 ^ x1 ^ x2 ^ x3;
+        } else if (hammer == 2) {
+          asm volatile("st.shared.v4.u32 [%0], {%1,%1,%1,%1};" ::"r"(my + (r & 7) * 1536), "r"(acc) : "memory");
+        } else if (hammer == 3) {
+          uint32_t v[8];
+          asm volatile("tcgen05.ld.sync.aligned.32x32b.x8.b32 {%0, %1, %2, %3, %4, %5, %6, %7}, [%8];"
+                       : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]), "=r"(v[4]), "=r"(v[5]), "=r"(v[6]), "=r"(v[7])
+                       : "r"(tmem + ((uint32_t)(wid * 32) << 16) + (uint32_t)(r * 8)));
+          asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+          acc += v[0] ^ v[7];
+        } else {
+#pragma unroll
+          for (int u = 0; u < 16; ++u) acc = acc * 3u + 1u;
+        }
+      }
+    }
+    if (acc == 0x12345678u) out[0] = acc;
   }
   asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
   __syncthreads();
@@ -247,6 +279,17 @@ int main() {
     printf("%-28s N=%3d B shift %2d rows, %2d A tiles  %7.1f clk/MMA\n", label, N, shift, tiles, (double)h[sms / 2] / (iters * 4.0));
   };
   for (int shift : {0, 1, 2, 4, 8, 20, 21, 22}) run2("TS shifted B", 128, shift, 4);
+  for (int hm : {0, 1, 2, 3, 4}) {
+    for (int rep = 0; rep < 2; ++rep) probe<<<sms, 128, 90 * 1024>>>(128, 1, iters, 1024, d_out, 128, 1280, 1, 24, hm);
+    cudaError_t e = cudaDeviceSynchronize();
+    if (e != cudaSuccess) { printf("hammer %d: %s\n", hm, cudaGetErrorString(e)); exit(1); }
+    std::vector<long long> h(sms);
+    cudaMemcpy(h.data(), d_out, sizeof(long long) * sms, cudaMemcpyDeviceToHost);
+    std::sort(h.begin(), h.end());
+    printf("TS N=128 with 3 warps hammering %-22s %7.1f clk/MMA\n",
+           hm == 0 ? "nothing" : hm == 1 ? "ld.shared.v4" : hm == 2 ? "st.shared.v4" : hm == 3 ? "tcgen05.ld (acc cols)" : "ALU",
+           (double)h[sms / 2] / (iters * 4.0));
+  }
   for (int tiles : {5, 6, 8, 12, 24, 32}) run2("TS many A tiles", 128, 1, tiles);
   for (int tiles : {8, 24}) run2("TS many A tiles", 64, 1, tiles);
   for (int mode = 0; mode < 2; ++mode)
