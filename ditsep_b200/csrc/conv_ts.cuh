@@ -21,12 +21,18 @@
 // Tensor memory (all 512 columns): [0, 256) two 128-column fp32 accumulators; [256, 448) the filter: 24 A tiles of 8
 // columns (4 K slices x 6 MMAs); [448, 512) up to 8 A tiles of the shortcut filter.
 //
-// Epilogue: channels sit on TMEM LANES (thread = channel), pixels on columns.  Warp (q, k): lane quadrant q, column
-// group k (4 row groups).  Quadrants 0/1 hold half a, 2/3 half b of the same channels; the partner warps (q, k) and
-// (q + 2, k) exchange half of their columns through shared memory (one 64-thread named barrier per tile) and each
-// finishes two of the pair's four output rows: scale + bias, bf16 store (64 contiguous bytes per warp and pixel),
-// GroupNorm statistics in registers (no cross-lane reduction: a thread IS a channel), flushed per segment through
-// shared-memory fixed-point sums (fx_add) so the global atomics stay one per channel, segment and CTA.
+// Epilogue: channels sit on TMEM LANES (thread = channel), pixels on columns.  Two groups of 8 warps take the tiles in
+// turn (group = accumulator = tile parity); a warp (lane quadrant q, column half kh) covers 64 columns in two passes of
+// 4 row groups and hands the accumulator back as soon as both passes are in registers.  Quadrants 0/1 hold half a, 2/3
+// half b of the same channels; the partner warps (q, kh) and (q + 2, kh) exchange half of their columns through shared
+// memory (64-thread named barriers) and each finishes two of a pass's four output rows: scale + bias in packed fp32x2
+// arithmetic, bf16 store (64 contiguous bytes per warp and pixel), GroupNorm statistics in registers (no cross-lane
+// reduction: a thread IS a channel) -- one fp32 partial per thread and TILE, converted to fixed point at once and
+// carried as integers, so the per-image totals are bit-reproducible and independent of the batch size and of how
+// the tiles are dealt to CTAs; they reach global memory when the CTA moves to another image.
+//
+// Measured (profiles/r2w_conv_ts.txt): 1655 cycles per tile of 120 output pixels = 24 MMAs x 69 cycles, i.e. the
+// kernel runs at the tensor pipe's TS rate; under sustained load the SM clock drops to ~1.3-1.6 GHz (power cap).
 #pragma once
 
 namespace ditsep {
@@ -122,6 +128,14 @@ __global__ void __launch_bounds__(kTsThreads, 1) conv_ts_kernel(const __grid_con
   __shared__ uint32_t tmem_base_slot;
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+#ifdef DITSEP_TS_TRACE
+  if (threadIdx.x == 0 && p.trace && blockIdx.x < kTraceCtas) {
+    unsigned long long gt;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(gt));
+    p.trace[(int64_t)blockIdx.x * kTraceTiles * 16 + 10] = clock64();
+    p.trace[(int64_t)blockIdx.x * kTraceTiles * 16 + 12] = (long long)gt;
+  }
+#endif
   const uint32_t ring = (smem_u32(smem_raw) + 1023u) & ~1023u;
   float* const exch = reinterpret_cast<float*>(smem_raw + (ring - smem_u32(smem_raw)) + (size_t)p.stages * kTsStageBytes);
   const int nx = p.xchunks, nsteps = nx + 1;
@@ -134,7 +148,7 @@ __global__ void __launch_bounds__(kTsThreads, 1) conv_ts_kernel(const __grid_con
     for (int s = 0; s < 2; ++s) {
       mbar_init(smem_u32(&bar_turn[s]), 1);
       mbar_init(smem_u32(&bar_acc_full[s]), 1);
-      mbar_init(smem_u32(&bar_acc_empty[s]), kEpiWarps);
+      mbar_init(smem_u32(&bar_acc_empty[s]), kEpiWarps / 2);  // one arrival per warp of the accumulator's group
     }
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
@@ -278,16 +292,18 @@ __global__ void __launch_bounds__(kTsThreads, 1) conv_ts_kernel(const __grid_con
   }
   else if (warp >= kCtrlWarps) {
     griddep_wait();  // bias_b, out and the statistics buffer are shared with earlier kernels
-    const int q = warp & 3, k = (warp - kCtrlWarps) >> 2;
+    // Two GROUPS of 8 warps (4 lane quadrants x 2 column halves) take the tiles in turn (group = accumulator = tile
+    // parity): the groups run out of phase, so one group's TMEM-load / barrier latencies sit under the other's
+    // arithmetic, and the per-tile bookkeeping is paid by 8 warps instead of 16.  A warp covers its 64 columns in two
+    // passes of 32 (4 row groups each) and hands the accumulator back after the second pass's loads.
+    const int e = warp - kCtrlWarps;
+    const int q = warp & 3, grp = e >> 3, kh = (e >> 2) & 1;
     const bool is_b = q >= 2;
     const int qa = q & 1, co = qa * 32 + lane;  // this thread's output channel
-    const int pair = k * 2 + qa;                // partner warps (qa, k) and (qa + 2, k) share named barrier 1 + pair
+    const int pair = grp * 4 + kh * 2 + qa;     // partner warps (qa, kh) and (qa + 2, kh) share named barrier 1 + pair
     float* const ex = exch + pair * (2 * 2 * 32 * kTsExchRow) + lane * kTsExchRow;
-    const uint32_t lane_addr = tmem + ((uint32_t)(q * 32) << 16);
-    // half a reads row groups 4k .. 4k+3, half b the groups one further (out(g) = Da(g) + Db(g + 1))
-    const int g0 = 4 * k + (is_b ? 1 : 0);
-    const int gout = 4 * k + (is_b ? 2 : 0);    // first of the two output row groups this warp finishes
-    const int etid = (warp - kCtrlWarps) * 32 + lane;
+    const uint32_t lane_addr = tmem + ((uint32_t)(q * 32) << 16) + (uint32_t)grp * (uint32_t)kTsN;
+    const int etid = e * 32 + lane;
     const float osc = p.out_scale;
     // byte stride between pixels of the output: a compile-time constant for dense tensors (immediate store offsets)
     const int64_t pix_bytes = kDense ? 128 : (int64_t)p.ld_out * 2;
@@ -312,6 +328,7 @@ __global__ void __launch_bounds__(kTsThreads, 1) conv_ts_kernel(const __grid_con
     };
     TsWalk tw;
     for (tw.init(p); !tw.done(); tw.next(p), ++it) {
+      if ((it & 1u) != (uint32_t)grp) continue;  // the other group's tile
       const int pb = tw.b;
       if (etid == 0) ts_stamp(p, it, 9);
       uint64_t s2 = 0ull, sq2 = 0ull;  // this tile's partial sums, packed fp32 pairs (even | odd pixels of a row)
@@ -324,51 +341,49 @@ __global__ void __launch_bounds__(kTsThreads, 1) conv_ts_kernel(const __grid_con
         cb = a * osc;  // out = fma(acc, scale, (bias + bias_b) * scale)
         cb2 = f2_pack(cb, cb);
       }
-      const uint32_t ab = it & 1u;
-      mbar_wait_sleep(smem_u32(&bar_acc_full[ab]), (it >> 1) & 1u);
+      mbar_wait_sleep(smem_u32(&bar_acc_full[grp]), (it >> 1) & 1u);
       tc_fence_after();
       if (etid == 0) ts_stamp(p, it, 3);
-      uint32_t v0[8], v1[8], v2[8], v3[8];
-      const uint32_t col = lane_addr + ab * (uint32_t)kTsN + (uint32_t)(g0 * 8);
-      tmem_ld8_nowait(col, v0);
-      tmem_ld8_nowait(col + 8u, v1);
-      tmem_ld8_nowait(col + 16u, v2);
-      if (g0 + 3 < 16) {  // half b of the last column group: row group 16 does not exist (output row 15 is not produced)
-        tmem_ld8_nowait(col + 24u, v3);
-      } else {
+      uint8_t* const otile = reinterpret_cast<uint8_t*>(p.out + ((int64_t)(pb * p.H + tw.ty * kTsRows) * p.W + tw.tx * kTileW) * p.ld_out + co);
+      const int64_t row_bytes = (int64_t)p.W * p.ld_out * 2;
+      const int rows_valid = min(kTsRows, p.H - tw.ty * kTsRows);
+      // Both passes' accumulator columns are read before any output is produced, so that the accumulator goes back to
+      // the MMA warps ~300 cycles after it filled (r2v trace: holding it through the first pass cost 800 cycles per
+      // tile on the MMA side).  Of a pass's 32 values a thread keeps the 16 it finishes; the other 16 go to the partner.
+      auto ld_pass = [&](const int ps, uint32_t (&v0)[8], uint32_t (&v1)[8], uint32_t (&v2)[8], uint32_t (&v3)[8]) {
+        const int g0 = 4 * (2 * kh + ps) + (is_b ? 1 : 0);  // half b reads one row group further: out(g) = Da(g) + Db(g + 1)
+        const uint32_t col = lane_addr + (uint32_t)(g0 * 8);
+        tmem_ld8_nowait(col, v0);
+        tmem_ld8_nowait(col + 8u, v1);
+        tmem_ld8_nowait(col + 16u, v2);
+        if (g0 + 3 < 16) {  // half b of the last column group: row group 16 does not exist (output row 15 is not produced)
+          tmem_ld8_nowait(col + 24u, v3);
+        } else {
 #pragma unroll
-        for (int j = 0; j < 8; ++j) v3[j] = 0u;
-      }
-      tmem_ld_wait();
-      tc_fence_before();
-      __syncwarp();
-      if (lane == 0) mbar_arrive(smem_u32(&bar_acc_empty[ab]));  // accumulator handed back
-      if (etid == 0) ts_stamp(p, it, 4);
-      // exchange: half a sends its rows 2,3 and finishes rows 0,1 of the pair; half b sends 0,1 and finishes 2,3.
-      // Buffer = [channel][16 pixels + 4]: every thread moves its 16 values as four float4, conflict-free.
-      float4* const exw = reinterpret_cast<float4*>(ex + ((it & 1u) * 2 + (is_b ? 1 : 0)) * (32 * kTsExchRow));
-      const float4* const exr = reinterpret_cast<const float4*>(ex + ((it & 1u) * 2 + (is_b ? 0 : 1)) * (32 * kTsExchRow));
-      auto send = [&](const uint32_t (&lo)[8], const uint32_t (&hi)[8]) {
+          for (int j = 0; j < 8; ++j) v3[j] = 0u;
+        }
+        tmem_ld_wait();
+      };
+      // exchange buffer = [channel][16 pixels + 4]: a thread moves its 16 values as four float4, conflict-free
+      auto send = [&](const int ps, const uint32_t (&lo)[8], const uint32_t (&hi)[8]) {
+        float4* const exw = reinterpret_cast<float4*>(ex + (ps * 2 + (is_b ? 1 : 0)) * (32 * kTsExchRow));
         exw[0] = make_float4(__uint_as_float(lo[0]), __uint_as_float(lo[1]), __uint_as_float(lo[2]), __uint_as_float(lo[3]));
         exw[1] = make_float4(__uint_as_float(lo[4]), __uint_as_float(lo[5]), __uint_as_float(lo[6]), __uint_as_float(lo[7]));
         exw[2] = make_float4(__uint_as_float(hi[0]), __uint_as_float(hi[1]), __uint_as_float(hi[2]), __uint_as_float(hi[3]));
         exw[3] = make_float4(__uint_as_float(hi[4]), __uint_as_float(hi[5]), __uint_as_float(hi[6]), __uint_as_float(hi[7]));
       };
-      if (is_b) send(v0, v1); else send(v2, v3);
-      named_bar_sync(1 + pair, 64);
-      if (etid == 0) ts_stamp(p, it, 7);
       // Packed fp32x2 arithmetic (add.rn.f32x2 / fma.rn.f32x2: two IEEE operations per instruction, same bits as the
-      // scalar forms): the SM is issue-bound here -- 16 epilogue warps share the four schedulers with the two
-      // MMA-issuing warps, whose issue latency sets the tensor pipe's feed rate (profiles/r2s).
-      auto finish = [&](const uint32_t (&v)[8], const int i) {
-        const int g = gout + i, y = tw.ty * kTsRows + g;
-        if (g < kTsRows && y < p.H) {
+      // scalar forms): the SM is issue-bound here (profiles/r2s).
+      auto finish = [&](const int ps, const uint32_t (&v)[8], const int i) {
+        const int g = 4 * (2 * kh + ps) + (is_b ? 2 : 0) + i;  // half a finishes rows 0,1 of the pass, half b rows 2,3
+        if (g < rows_valid) {
+          const float4* const exr = reinterpret_cast<const float4*>(ex + (ps * 2 + (is_b ? 0 : 1)) * (32 * kTsExchRow));
           const float4 e0 = exr[2 * i], e1 = exr[2 * i + 1];
-          const uint64_t e[4] = {f2_pack(e0.x, e0.y), f2_pack(e0.z, e0.w), f2_pack(e1.x, e1.y), f2_pack(e1.z, e1.w)};
-          uint8_t* op = reinterpret_cast<uint8_t*>(p.out + ((int64_t)(pb * p.H + y) * p.W + tw.tx * kTileW) * p.ld_out + co);
+          const uint64_t ee[4] = {f2_pack(e0.x, e0.y), f2_pack(e0.z, e0.w), f2_pack(e1.x, e1.y), f2_pack(e1.z, e1.w)};
+          uint8_t* op = otile + g * row_bytes;
 #pragma unroll
           for (int jj = 0; jj < 4; ++jj) {
-            const uint64_t a = f2_add(f2_pack(__uint_as_float(v[2 * jj]), __uint_as_float(v[2 * jj + 1])), e[jj]);
+            const uint64_t a = f2_add(f2_pack(__uint_as_float(v[2 * jj]), __uint_as_float(v[2 * jj + 1])), ee[jj]);
             const uint64_t f = f2_fma(a, osc2, cb2);
             s2 = f2_add(s2, f);
             sq2 = f2_fma(f, f, sq2);
@@ -381,7 +396,24 @@ __global__ void __launch_bounds__(kTsThreads, 1) conv_ts_kernel(const __grid_con
           }
         }
       };
-      if (is_b) { finish(v2, 0); finish(v3, 1); } else { finish(v0, 0); if (etid == 0) ts_stamp(p, it, 8); finish(v1, 1); }
+      auto tile_body = [&](auto isb) {
+        constexpr bool kB = decltype(isb)::value;
+        uint32_t v0[8], v1[8], v2[8], v3[8], w0[8], w1[8], w2[8], w3[8];
+        ld_pass(0, v0, v1, v2, v3);
+        if (kB) send(0, v0, v1); else send(0, v2, v3);
+        ld_pass(1, w0, w1, w2, w3);
+        tc_fence_before();
+        __syncwarp();
+        if (lane == 0) mbar_arrive(smem_u32(&bar_acc_empty[grp]));  // accumulator handed back
+        if (etid == 0) ts_stamp(p, it, 4);
+        if (kB) send(1, w0, w1); else send(1, w2, w3);
+        named_bar_sync(1 + pair, 64);
+        if (etid == 0) ts_stamp(p, it, 7);
+        if (kB) { finish(0, v2, 0); finish(0, v3, 1); finish(1, w2, 0); finish(1, w3, 1); }
+        else { finish(0, v0, 0); finish(0, v1, 1); finish(1, w0, 0); finish(1, w1, 1); }
+        named_bar_sync(1 + pair, 64);  // the partner has read this tile's buffers: they may be rewritten
+      };
+      if (is_b) tile_body(std::true_type{}); else tile_body(std::false_type{});
       if (etid == 0) ts_stamp(p, it, 5);
       if (p.stats) {
         float sa, sb, qa2, qb2;
@@ -399,6 +431,14 @@ __global__ void __launch_bounds__(kTsThreads, 1) conv_ts_kernel(const __grid_con
   }
   tc_fence_before();
   __syncthreads();
+#ifdef DITSEP_TS_TRACE
+  if (threadIdx.x == 0 && p.trace && blockIdx.x < kTraceCtas) {
+    unsigned long long gt;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(gt));
+    p.trace[(int64_t)blockIdx.x * kTraceTiles * 16 + 11] = clock64();
+    p.trace[(int64_t)blockIdx.x * kTraceTiles * 16 + 13] = (long long)gt;
+  }
+#endif
   if (warp == 1) {
     __syncwarp();
     tc_fence_after();
