@@ -18,7 +18,7 @@ class SdeParams(C.Structure):
     """ditsep_sde_params (include/ditsep_b200.h)."""
 
     _fields_ = [("sde", C.c_int32), ("n_src", C.c_int32), ("p0", C.c_float), ("sigma_min", C.c_float),
-                ("sigma_max", C.c_float), ("N", C.c_int32), ("snr", C.c_float)]
+                ("sigma_max", C.c_float), ("N", C.c_int32), ("snr", C.c_float), ("elem_scale", C.c_void_p)]
 
 
 class GnJob(C.Structure):
@@ -41,6 +41,9 @@ SIGNATURES = {
                                     c_void_p, c_void_p, c_int, c_int64, c_void_p, c_void_p]),
     "ditsep_pc_prior": (c_int, [C.POINTER(SdeParams), c_void_p, c_void_p, c_uint64, c_uint64, c_void_p, c_int, c_int64,
                                 c_void_p, c_void_p]),
+    "ditsep_pc_langevin": (c_int, [c_int, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_int64, c_void_p,
+                                   c_void_p]),
+    "ditsep_energy_envelope": (c_int, [c_void_p, c_void_p, c_int, c_int64, c_int, c_void_p]),
     "ditsep_philox_normal": (c_int, [c_void_p, c_int64, c_uint64, c_uint64, c_void_p]),
     "ditsep_box_muller": (c_int, [c_void_p, c_void_p, c_int64, c_void_p]),
     "ditsep_stft_compress": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_int64, c_int,

@@ -17,7 +17,7 @@ void set_error(const char* fmt, ...) {
 
 }  // namespace ditsep
 
-extern "C" int ditsep_abi_version(void) { return 2; }  // 2: ragged-batch lengths on the pc_* entries, box_muller
+extern "C" int ditsep_abi_version(void) { return 3; }  // 2: ragged-batch lengths on the pc_* entries, box_muller; 3: ditsep_sde_params.elem_scale, pc_langevin, energy_envelope
 extern "C" const char* ditsep_last_error(void) { return ditsep::g_err; }
 extern "C" int64_t ditsep_launch_count(void) { return ditsep::g_launches.load(); }
 extern "C" void ditsep_note_launches(int64_t n) { ditsep::g_launches.fetch_add(n); }

@@ -61,10 +61,15 @@ __device__ __forceinline__ float4 philox_normal4(uint64_t q, uint64_t seed, uint
 }
 
 // ---- per-mixture coefficients ----------------------------------------------------------
-enum Mode { kCorrector = 0, kPredictor = 1, kPrior = 2 };
+enum Mode { kCorrector = 0, kPredictor = 1, kPrior = 2, kLangevin = 3 };
 
 __device__ __forceinline__ Coef make_coef(const ditsep_sde_params& p, int mode, float t) {
   Coef c = {1.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+  if (mode == kLangevin) {  // t = the batch-wide step size eps: x_mean = x + eps s, x = x_mean + sqrt(2 eps) z
+    c.a2 = t;
+    c.b0 = sqrtf(2.0f * t);
+    return c;
+  }
   const float ratio = p.sigma_max / p.sigma_min;
   const float logsig = logf(ratio);
   const float dt = 1.0f / (float)p.N;
@@ -133,8 +138,11 @@ __global__ void __launch_bounds__(256) pc_update_kernel(ditsep_sde_params p, int
   // ragged batches: row b is a zero-padded signal of lengths[b] <= L samples; its state is kept at exactly zero past
   // its end, so the STFT of the next score evaluation sees the same frames as a batch-1 run of that mixture alone
   const int64_t len = lengths ? (int64_t)lengths[b] : L;
-  const float tb = (mode == kPrior) ? 1.0f : t[b];
+  const float tb = (mode == kPrior) ? 1.0f : (mode == kLangevin ? t[0] : t[b]);
   const Coef c = make_coef(p, mode, tb);
+  // PriorMixSDE (sdes.py:453-472,519-531): the diffusion carries a per-mixture, per-sample envelope m[b][l], i.e. the
+  // score terms scale with m^2 and the noise terms with m
+  const float* __restrict__ env = p.elem_scale ? p.elem_scale + (int64_t)b * L : nullptr;
   const int64_t nvec = (L + 3) / 4;
   const float inv_n = 1.0f / (float)NS;
   for (int64_t q = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; q < nvec; q += (int64_t)gridDim.x * blockDim.x) {
@@ -196,11 +204,13 @@ __global__ void __launch_bounds__(256) pc_update_kernel(ditsep_sde_params p, int
       }
       xb *= inv_n; sb *= inv_n; zb *= inv_n;
       const bool live = l0 + j < len;
+      const float ev = (env && l0 + j < L) ? __ldg(env + l0 + j) : 1.0f;
+      const float ev2 = ev * ev;
 #pragma unroll
       for (int i = 0; i < NS; ++i) {
-        float m = c.a0 * xv[i][j] + c.a1 * xb + c.a2 * sv[i][j] + c.a3 * sb + c.a4 * yv[j];
+        float m = c.a0 * xv[i][j] + c.a1 * xb + ev2 * (c.a2 * sv[i][j] + c.a3 * sb) + c.a4 * yv[j];
         xm[i][j] = live ? m : 0.f;
-        xo[i][j] = live ? m + c.b0 * zv[i][j] + c.b1 * zb : 0.f;
+        xo[i][j] = live ? m + ev * (c.b0 * zv[i][j] + c.b1 * zb) : 0.f;
       }
     }
 #pragma unroll
@@ -226,12 +236,12 @@ static int launch_pc(const ditsep_sde_params* hp, int mode, float* x, const floa
                      const int* lengths, void* stream) {
   DITSEP_REQUIRE(hp != nullptr && x != nullptr, "pc_step: null params or state");
   DITSEP_REQUIRE(hp->n_src >= 1 && hp->n_src <= kMaxSrc, "pc_step: n_src=%d unsupported (1..%d)", hp->n_src, kMaxSrc);
-  DITSEP_REQUIRE(hp->sde == DITSEP_SDE_MIX || hp->sde == DITSEP_SDE_OUVE, "pc_step: unknown sde %d", hp->sde);
+  DITSEP_REQUIRE(mode == kLangevin || hp->sde == DITSEP_SDE_MIX || hp->sde == DITSEP_SDE_OUVE, "pc_step: unknown sde %d", hp->sde);
   DITSEP_REQUIRE(B > 0 && L > 0, "pc_step: empty state B=%d L=%lld", B, (long long)L);
   DITSEP_REQUIRE(mode == kPrior || (score != nullptr && t != nullptr), "pc_step: score/t required");
-  DITSEP_REQUIRE(!(hp->sde == DITSEP_SDE_MIX && mode == kPrior && hp->n_src != 2),
+  DITSEP_REQUIRE(!(hp->sde == DITSEP_SDE_MIX && mode == kPrior && hp->n_src != 2 && hp->elem_scale == nullptr),
                  "MixSDE.prior_sampling supports exactly 2 sources (reference sdes.py:346), got %d", hp->n_src);
-  DITSEP_REQUIRE((mode == kCorrector) || y != nullptr || (hp->sde == DITSEP_SDE_MIX && mode == kPredictor),
+  DITSEP_REQUIRE((mode == kCorrector) || (mode == kLangevin) || y != nullptr || (hp->sde == DITSEP_SDE_MIX && mode == kPredictor),
                  "pc_step: y required");
   const int64_t nvec = (L + 3) / 4;
   int gx = (int)((nvec + 255) / 256);
@@ -240,7 +250,7 @@ static int launch_pc(const ditsep_sde_params* hp, int mode, float* x, const floa
   if (gx < 1) gx = 1;
   dim3 grid(gx, B), block(256);
   cudaStream_t st = (cudaStream_t)stream;
-  const float* yy = (hp->sde == DITSEP_SDE_MIX && mode != kPrior) ? nullptr : y;
+  const float* yy = ((hp->sde == DITSEP_SDE_MIX && mode != kPrior) || mode == kLangevin) ? nullptr : y;
   switch (hp->n_src) {
     case 1: pc_update_kernel<1><<<grid, block, 0, st>>>(*hp, mode, x, score, noise, seed, draw, t, yy, x_mean, L, lengths); break;
     case 2: pc_update_kernel<2><<<grid, block, 0, st>>>(*hp, mode, x, score, noise, seed, draw, t, yy, x_mean, L, lengths); break;
@@ -286,6 +296,54 @@ extern "C" int ditsep_pc_predictor(const ditsep_sde_params* host_p, float* x, co
 extern "C" int ditsep_pc_prior(const ditsep_sde_params* host_p, float* x, const float* noise, uint64_t seed,
                                uint64_t draw, const float* y, int B, int64_t L, const int* lengths, void* stream) {
   return launch_pc(host_p, kPrior, x, nullptr, noise, seed, draw, nullptr, y, nullptr, B, L, lengths, stream);
+}
+
+extern "C" int ditsep_pc_langevin(int n_src, float* x, const float* score, const float* noise, const float* step,
+                                  float* x_mean, int B, int64_t L, const int* lengths, void* stream) {
+  DITSEP_REQUIRE(noise != nullptr && step != nullptr, "pc_langevin: the step size depends on the noise draw: pass both");
+  ditsep_sde_params p = {};
+  p.sde = DITSEP_SDE_MIX;
+  p.n_src = n_src;
+  p.sigma_min = 1.f;
+  p.sigma_max = 2.f;
+  p.N = 1;
+  return launch_pc(&p, kLangevin, x, score, noise, 0, 0, step, nullptr, x_mean, B, L, lengths, stream);
+}
+
+// ---- PriorMixSDE's energy envelope -------------------------------------------------------------
+// out[b][l] = 0.5 sqrt(max(1e-4, (1/k) sum_{j = l - k/2}^{l - k/2 + k - 1} mix[b][j]^2)), zeros outside [0, L)
+// (avg_pool1d(mix^2, k, stride 1, padding k // 2) with the padding counted, sdes.py:480-492).  One block per 1024
+// outputs: the squares it needs (1024 + k - 1) go to shared memory once, every thread then walks its window.
+namespace ditsep {
+__global__ void __launch_bounds__(256) energy_envelope_kernel(const float* __restrict__ mix, float* __restrict__ out,
+                                                              int64_t L, int k) {
+  extern __shared__ float sq[];
+  const int b = blockIdx.y;
+  const int64_t l0 = (int64_t)blockIdx.x * 1024;
+  const int n = 1024 + k - 1;
+  for (int i = threadIdx.x; i < n; i += blockDim.x) {
+    const int64_t j = l0 - k / 2 + i;
+    const float v = (j >= 0 && j < L) ? mix[(int64_t)b * L + j] : 0.f;
+    sq[i] = v * v;
+  }
+  __syncthreads();
+  const float inv = 1.0f / (float)k;
+  for (int o = threadIdx.x; o < 1024; o += blockDim.x) {
+    if (l0 + o >= L) break;
+    float a = 0.f;
+    for (int j = 0; j < k; ++j) a += sq[o + j];
+    out[(int64_t)b * L + l0 + o] = 0.5f * sqrtf(fmaxf(a * inv, 1e-4f));
+  }
+}
+}  // namespace ditsep
+
+extern "C" int ditsep_energy_envelope(const float* mix, float* out, int B, int64_t L, int avg_len, void* stream) {
+  DITSEP_REQUIRE(mix && out && B > 0 && L > 0, "energy_envelope: empty input");
+  DITSEP_REQUIRE(avg_len >= 1 && avg_len <= 4096, "energy_envelope: avg_len=%d (1..4096)", avg_len);
+  dim3 grid((unsigned)((L + 1023) / 1024), (unsigned)B);
+  const size_t smem = (size_t)(1024 + avg_len - 1) * sizeof(float);
+  energy_envelope_kernel<<<grid, 256, smem, (cudaStream_t)stream>>>(mix, out, L, avg_len);
+  return check_launch("energy_envelope_kernel");
 }
 
 extern "C" int ditsep_philox_normal(float* out, int64_t n, uint64_t seed, uint64_t draw, void* stream) {

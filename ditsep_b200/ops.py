@@ -134,6 +134,27 @@ def pc_prior(p: SdeParams, x, y, noise=None, seed=0, draw=0, lengths=None):
                                       _lengths(lengths, B), _stream()), "pc_prior")
 
 
+def pc_langevin(n_src: int, x, score, noise, step, x_mean=None, lengths=None):
+    """One LangevinCorrector step with the batch-wide step size read from the 1-element device tensor `step`."""
+    _cuda(x, score, noise, step, x_mean)
+    for n, v in (("x", x), ("score", score), ("noise", noise), ("step", step), ("x_mean", x_mean)):
+        _f32c(v, n)
+    B = x.shape[0]
+    L = x.numel() // (B * n_src)
+    check(_lib.load().ditsep_pc_langevin(n_src, _ptr(x), _ptr(score), _ptr(noise), _ptr(step), _ptr(x_mean), B, L,
+                                         _lengths(lengths, B), _stream()), "pc_langevin")
+
+
+def energy_envelope(mix: torch.Tensor, out: torch.Tensor, avg_len: int):
+    """PriorMixSDE's per-sample diffusion envelope: out (B,1,L) = 0.5 sqrt(max(box_avg_len(mix^2), 1e-4))."""
+    _cuda(mix, out)
+    _f32c(mix, "mix")
+    _f32c(out, "out")
+    B = mix.shape[0]
+    check(_lib.load().ditsep_energy_envelope(_ptr(mix), _ptr(out), B, mix.numel() // B, int(avg_len), _stream()),
+          "energy_envelope")
+
+
 def philox_normal(out: torch.Tensor, seed: int, draw: int):
     _cuda(out)
     _f32c(out, "out")

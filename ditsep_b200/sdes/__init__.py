@@ -17,10 +17,10 @@ import torch
 
 from .correctors import Corrector, CorrectorRegistry
 from .predictors import Predictor, PredictorRegistry, ReverseDiffusionPredictor
-from .sdes import SDE, MixSDE, NoiseSource, OUVESDE, SDERegistry
+from .sdes import SDE, MixSDE, NoiseSource, OUVESDE, PriorMixSDE, SDERegistry
 
 __all__ = ["PredictorRegistry", "CorrectorRegistry", "SDERegistry", "Predictor", "Corrector", "SDE", "MixSDE",
-           "OUVESDE", "NoiseSource", "ReverseDiffusionPredictor", "get_pc_sampler", "get_pc_scheduled_sampler",
+           "PriorMixSDE", "OUVESDE", "NoiseSource", "ReverseDiffusionPredictor", "get_pc_sampler", "get_pc_scheduled_sampler",
            "get_ode_sampler", "get_sb_sampler"]
 
 

@@ -56,7 +56,7 @@ class ReverseDiffusionPredictor(Predictor):
         update its own state in place and skip the x_mean store when it is not consumed."""
         y = args[0] if args else None
         score = self.score_fn(x, t, *args)
-        p = self.sde.fused_params(n_src=x.shape[1])
+        p = self.sde.fused_params(n_src=x.shape[1], y=y)
         x_out = x if _inplace else x.clone()
         x_mean = torch.empty_like(x_out) if _want_mean else None
         src = self._noise()
@@ -67,9 +67,12 @@ class ReverseDiffusionPredictor(Predictor):
 
 
 @PredictorRegistry.register("euler_maruyama")
-class EulerMaruyamaPredictor(Predictor):
-    def update_fn(self, x, t, *args, **kwargs):
-        raise NotImplementedError("euler_maruyama is outside the fused PC-sampler hot path (SURVEY.md 8f item 2)")
+class EulerMaruyamaPredictor(ReverseDiffusionPredictor):
+    """predictors.py:42-57: x_mean = x - (drift - g^2 score) dt, x = x_mean + g sqrt(dt) z over the continuous reverse
+    SDE (sdes.py:131-160).  With the reference's `discretize` (drift dt, g sqrt(dt): sdes.py:94-108) and its dt, which is
+    1/N for both (the `getattr(kwargs, "dt", ...)` on a dict, quirk Q2), this is term by term the reverse-diffusion
+    update, so it runs the same fused kernel row; pinned against the reference's own euler_maruyama run
+    (tests/golden/variants.npz, `em_*`)."""
 
 
 @PredictorRegistry.register("none")

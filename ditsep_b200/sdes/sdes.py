@@ -112,8 +112,9 @@ class SDE(abc.ABC):
     def copy(self):
         pass
 
-    def fused_params(self, snr: float = 0.0, n_src: int = 2) -> SdeParams:
-        """Scalars of this SDE for the fused update kernel (ditsep_sde_params)."""
+    def fused_params(self, snr: float = 0.0, n_src: int = 2, y=None) -> SdeParams:
+        """Scalars of this SDE for the fused update kernel (ditsep_sde_params); y: the conditioning mixture (only
+        PriorMixSDE's coefficients depend on it)."""
         raise NotImplementedError(f"SDE class {self.__class__.__name__} has no fused sm_100a update kernel")
 
     def discretize(self, x, t, *args, **kwargs):
@@ -144,8 +145,8 @@ class SDE(abc.ABC):
             def T(self):
                 return T
 
-            def fused_params(self, snr: float = 0.0, n_src: int = 2):
-                return fused_fn(snr, n_src)
+            def fused_params(self, snr: float = 0.0, n_src: int = 2, y=None):
+                return fused_fn(snr, n_src, y=y)
 
             def sde(self, x, t, *args):
                 parts = self.rsde_parts(x, t, *args)
@@ -203,7 +204,7 @@ class MixSDE(SDE):
     def T(self):
         return 1.0
 
-    def fused_params(self, snr: float = 0.0, n_src: int = None) -> SdeParams:
+    def fused_params(self, snr: float = 0.0, n_src: int = None, y=None) -> SdeParams:
         return SdeParams(SDE_MIX, self.ndim if n_src is None else n_src, float(self.d_lambda), float(self.sigma_min),
                          float(self.sigma_max), int(self.N), float(snr))
 
@@ -261,6 +262,78 @@ class MixSDE(SDE):
         raise NotImplementedError("prior_logp for OU SDE not yet implemented!")
 
 
+@SDERegistry.register("priormix")
+class PriorMixSDE(MixSDE):
+    """MixSDE with a mixture-dependent diffusion (sdes.py:354-592): g(t, b, l) = g_mix(t) m[b, l], where
+    m = 0.5 sqrt(max(box_avg_len(mix^2), 1e-4)) is a running energy envelope of the conditioning mixture (:480-492).
+    Nothing else changes, so every closed form of MixSDE carries over with the factor m: terms linear in the diffusion
+    (the noise of the prior, the corrector and the predictor; the marginal std L) scale by m, terms quadratic in it (the
+    score terms) by m^2.  The fused kernel takes m as `ditsep_sde_params.elem_scale`; m is computed once per mixture
+    tensor (`ditsep_energy_envelope`) and cached."""
+
+    def __init__(self, ndim, d_lambda, sigma_min, sigma_max, N=1000, avg_len=510):
+        super().__init__(ndim, d_lambda, sigma_min, sigma_max, N=N)
+        self.avg_len = avg_len
+        self._env_key, self._env = None, None
+
+    def copy(self):
+        return PriorMixSDE(self.ndim, self.d_lambda, self.sigma_min, self.sigma_max, N=self.N, avg_len=self.avg_len)
+
+    def _std_sigma_mix(self, mix):
+        """(B, 1, L) envelope m of `mix` (B, 1, L); one kernel launch per distinct mixture tensor."""
+        key = (mix.data_ptr(), tuple(mix.shape), mix._version, str(mix.device))
+        if key != self._env_key:
+            if mix.dim() != 3 or mix.shape[1] != 1:
+                raise ValueError(f"PriorMixSDE needs a one-channel mixture (B, 1, L), got {tuple(mix.shape)}")
+            env = torch.empty(mix.shape, device=mix.device, dtype=torch.float32)
+            ops.energy_envelope(mix.float().contiguous(), env, self.avg_len)
+            self._env_key, self._env = key, env
+        return self._env
+
+    def fused_params(self, snr: float = 0.0, n_src: int = None, y=None) -> SdeParams:
+        if y is None:
+            raise ValueError("PriorMixSDE's coefficients depend on the mixture: pass y")
+        p = super().fused_params(snr, n_src)
+        env = self._std_sigma_mix(y)
+        p.elem_scale = env.data_ptr()
+        p._keep = env  # the struct holds a raw device pointer
+        return p
+
+    def sde(self, x, t, mix):
+        drift, g = super().sde(x, t)
+        g = g[(...,) + (None,) * (x.ndim - g.ndim)]
+        return drift, g * torch.broadcast_to(self._std_sigma_mix(mix), x.shape)
+
+    def _std(self, t, mix):
+        """(B, n, n, L): the matrix square root of the covariance, per sample."""
+        return super()._std(t)[..., None] * self._std_sigma_mix(mix)[:, None, :, :]
+
+    def marginal_prob(self, x0, t, mix):
+        self.send_to(x0.device)
+        return self._mean(x0, t), self._std(t, mix)
+
+    @staticmethod
+    def mult_std(std, x):
+        return torch.einsum("bcdt,bdt->bct", std, x)
+
+    @staticmethod
+    def mult_std_inv(std, x):
+        return torch.linalg.solve(std.permute(0, 3, 1, 2), x.permute(0, 2, 1)[..., None])[..., 0].permute(0, 2, 1).contiguous()
+
+    def prior_sampling(self, shape, mix, noise: NoiseSource = None):
+        """x_T = 0.5 mix + m L(T) z for a one-channel mixture (sdes.py:566-589)."""
+        if shape != mix.shape:
+            warnings.warn(f"Target shape {shape} does not match shape of mix {mix.shape}! Ignoring target shape.")
+        if mix.shape[1] != 1:
+            raise NotImplementedError("PriorMixSDE.prior_sampling: only the one-channel mixture form has a fused kernel")
+        noise = NoiseSource() if noise is None else noise
+        x = torch.empty((mix.shape[0], self.ndim, mix.shape[2]), device=mix.device, dtype=torch.float32)
+        z, seed, draw = noise.next(x)
+        ops.pc_prior(self.fused_params(n_src=self.ndim, y=mix), x, mix.contiguous(), noise=z, seed=seed, draw=draw,
+                     lengths=noise.lengths)
+        return x
+
+
 @SDERegistry.register("ouve")
 class OUVESDE(SDE):
     """dx = theta (y - x) dt + g(t) dw (sdes.py:595-698)."""
@@ -280,7 +353,7 @@ class OUVESDE(SDE):
     def T(self):
         return 1
 
-    def fused_params(self, snr: float = 0.0, n_src: int = 2) -> SdeParams:
+    def fused_params(self, snr: float = 0.0, n_src: int = 2, y=None) -> SdeParams:
         return SdeParams(SDE_OUVE, int(n_src), float(self.theta), float(self.sigma_min), float(self.sigma_max),
                          int(self.N), float(snr))
 

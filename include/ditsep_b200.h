@@ -41,6 +41,9 @@ typedef struct {
   float sigma_max;
   int32_t N;       /* discretisation steps; dt = 1/N always (reference quirk, sdes.py:104) */
   float snr;       /* corrector snr */
+  const float* elem_scale; /* nullable, DEVICE pointer (B, 1, L): per-mixture, per-sample multiplier of the diffusion
+                              (PriorMixSDE's energy envelope, sdes.py:453-472): score terms scale with its square, noise
+                              terms with it.  ABI v3. */
 } ditsep_sde_params;
 
 int ditsep_abi_version(void);
@@ -75,6 +78,13 @@ int ditsep_pc_predictor(const ditsep_sde_params* host_p, float* x, const float* 
 int ditsep_pc_prior(const ditsep_sde_params* host_p, float* x, const float* noise, uint64_t seed, uint64_t draw,
                     const float* y, int B, int64_t L, const int* lengths, void* stream);
 /* Standard normals from the same Philox stream as above (tests / statistics). */
+/* LangevinCorrector.update_fn, one step (correctors.py:43-55): x_mean = x + eps score, x = x_mean + sqrt(2 eps) noise with
+ * ONE step size eps for the whole batch, read from DEVICE memory (*step): it depends on the batch means of |score| and
+ * |noise| (the host side forms it with two reductions), which is why the noise must be given explicitly. */
+int ditsep_pc_langevin(int n_src, float* x, const float* score, const float* noise, const float* step, float* x_mean,
+                       int B, int64_t L, const int* lengths, void* stream);
+/* PriorMixSDE._std_sigma_mix (sdes.py:480-492): out (B, 1, L) = 0.5 sqrt(max(box_{avg_len}(mix^2), 1e-4)). */
+int ditsep_energy_envelope(const float* mix, float* out, int B, int64_t L, int avg_len, void* stream);
 int ditsep_philox_normal(float* out, int64_t n, uint64_t seed, uint64_t draw, void* stream);
 /* The uniform -> normal transform of that stream on caller-supplied 32-bit words (n % 4 == 0; word 4q, 4q+2 give
  * the radii, 4q+1, 4q+3 the angles): lets a test feed the endpoint uniforms (0, 0xFFFFFFFF) and check for NaN. */

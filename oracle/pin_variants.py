@@ -34,6 +34,25 @@ def main():
         print(f"scheduled sampler '{schedule}': nfe {nfe}, max abs err oracle vs reference {err:.3e}")
         assert nfe == nfe2 == 2 * N and err < 1e-4
         golden[f"scheduled_{schedule}"] = x_ref.numpy()
+    # f2, second half: euler_maruyama predictor, langevin corrector, PriorMixSDE (registry name "priormix")
+    cases = {
+        "em_ald2_mix": ("euler_maruyama", "ald2", lambda: sdes.sdes.MixSDE(2, 2.0, 0.05, 0.5, N=N), lambda: S.MixSDERef(2, 2.0, 0.05, 0.5, N=N)),
+        "rd_langevin_mix": ("reverse_diffusion", "langevin", lambda: sdes.sdes.MixSDE(2, 2.0, 0.05, 0.5, N=N), lambda: S.MixSDERef(2, 2.0, 0.05, 0.5, N=N)),
+        "rd_ald2_priormix": ("reverse_diffusion", "ald2", lambda: sdes.sdes.PriorMixSDE(2, 2.0, 0.05, 0.5, N=N), lambda: S.PriorMixSDERef(2, 2.0, 0.05, 0.5, N=N)),
+        "em_ald2_priormix_avg64": ("euler_maruyama", "ald2", lambda: sdes.sdes.PriorMixSDE(2, 2.0, 0.05, 0.5, N=N, avg_len=64), lambda: S.PriorMixSDERef(2, 2.0, 0.05, 0.5, N=N, avg_len=64)),
+    }
+    import warnings
+    for name, (pred, corr, mk_ref, mk_orc) in cases.items():
+        with TapedRandn(S.NoiseTape(81)), warnings.catch_warnings():
+            warnings.simplefilter("ignore")
+            x_ref, nfe = sdes.get_pc_sampler(pred, corr, sde=mk_ref(), score_fn=toy_score, y=y, eps=0.03, snr=0.5,
+                                             corrector_steps=1, denoise=True)()
+        x_orc, nfe2 = S.pc_sampler_ref(toy_score, mk_orc(), y, S.NoiseTape(81), corrector=corr, eps=0.03, snr=0.5, predictor=pred)
+        err = float((x_orc - x_ref).abs().max())
+        print(f"{name}: nfe {nfe}, max abs err oracle vs reference {err:.3e}, |x| max {float(x_ref.abs().max()):.3f}")
+        assert nfe == nfe2 == 2 * N and err < 1e-4
+        golden[name] = x_ref.numpy()
+    golden["variants_y"] = y.numpy()
     np.savez_compressed(os.path.join(GOLDEN, "variants.npz"), **golden)
     print("written", os.path.join(GOLDEN, "variants.npz"))
 

@@ -92,6 +92,39 @@ class MixSDERef:
         return mean + self.std(t) @ noise
 
 
+class PriorMixSDERef(MixSDERef):
+    """sdes.py:354-592: MixSDE whose diffusion is scaled, per mixture and per sample, by an energy envelope of the
+    mixture: sigma_mix = 0.5 sqrt(max(box_avg_len(mix^2), 1e-4)) (:480-492: avg_pool1d, stride 1, padding avg_len // 2,
+    zeros counted; the extra output sample of an even window is dropped)."""
+
+    def __init__(self, ndim=2, d_lambda=2.0, sigma_min=0.05, sigma_max=0.5, N=30, avg_len=510):
+        super().__init__(ndim, d_lambda, sigma_min, sigma_max, N)
+        self.avg_len = avg_len
+
+    def sigma_mix(self, mix):
+        k = self.avg_len
+        m = torch.nn.functional.avg_pool1d(mix ** 2, kernel_size=k, stride=1, padding=k // 2)
+        m = m.clamp(min=1e-4).sqrt()
+        if k % 2 == 0:
+            m = m[..., :-1]
+        return 0.5 * m
+
+    def sde_env(self, x, t, mix):
+        """:453-472: drift as MixSDE, diffusion (B, ndim, L) = g(t) * sigma_mix."""
+        drift, g = self.sde(x, t)
+        return drift, _pad(g, x) * torch.broadcast_to(self.sigma_mix(mix), x.shape)
+
+    def std_env(self, t, mix):
+        """:519-531: L(t)[b] (ndim x ndim) times sigma_mix[b, 0, l] -> (B, ndim, ndim, L)."""
+        return self.std(t)[..., None] * self.sigma_mix(mix)[:, None, :, :]
+
+    def prior_sampling(self, y, noise: Tensor):
+        """:566-589 with a one-channel mixture: 0.5 y + L(T) sigma_mix z."""
+        t = torch.ones((y.shape[0],)) * self.T
+        mean = torch.broadcast_to(0.5 * y, (y.shape[0], self.ndim, y.shape[2]))
+        return mean + torch.einsum("bcdt,bdt->bct", self.std_env(t, y), noise)
+
+
 class OUVESDERef:
     """sdes.py:595-698."""
 
@@ -133,6 +166,25 @@ def corrector_ald2_ref(sde: MixSDERef, x, t, score, noise, snr):
     return x_mean + (2 * snr * L) @ noise, x_mean
 
 
+def corrector_ald2_env_ref(sde: "PriorMixSDERef", x, t, y, score, noise, snr):
+    """correctors.py:102-121 with PriorMixSDE's 4-D L (mult_std = einsum 'bcdt,bdt->bct', sdes.py:532-534)."""
+    L = sde.std_env(t, y)
+    mul = lambda a, v: torch.einsum("bcdt,bdt->bct", a, v)
+    grad = mul(L, mul(L, score))
+    x_mean = x + 2 * snr ** 2 * grad
+    return x_mean + mul(2 * snr * L, noise), x_mean
+
+
+def corrector_langevin_ref(x, score, noise, snr):
+    """correctors.py:35-55 for one step: ONE step size for the whole batch from the batch means of the per-mixture
+    norms, eps = 2 (snr mean|z| / mean|score|)^2; x_mean = x + eps score; x = x_mean + sqrt(2 eps) z."""
+    gn = torch.norm(score.reshape(score.shape[0], -1), dim=-1).mean()
+    zn = torch.norm(noise.reshape(noise.shape[0], -1), dim=-1).mean()
+    step = (snr * zn / gn) ** 2 * 2
+    x_mean = x + step * score
+    return x_mean + noise * torch.sqrt(step * 2), x_mean
+
+
 def corrector_ald_ref(sde, x, t, score, noise, snr):
     """correctors.py:70-84 for one step with a scalar std (OUVESDE)."""
     std = sde.std(t)
@@ -145,12 +197,28 @@ def predictor_rd_ref(sde, x, t, y, score, noise):
     """predictors.py:60-66 + sdes.py:94-108,165-173.  dt is always 1/N (the
     ``getattr(kwargs, "dt", ...)`` on a dict never finds the key -- quirk Q2)."""
     dt = 1 / sde.N
-    drift, diffusion = sde.sde(x, t) if isinstance(sde, MixSDERef) else sde.sde(x, t, y)
+    if isinstance(sde, PriorMixSDERef):
+        drift, diffusion = sde.sde_env(x, t, y)
+    else:
+        drift, diffusion = sde.sde(x, t) if isinstance(sde, MixSDERef) else sde.sde(x, t, y)
     f = drift * dt
     G = diffusion * torch.sqrt(torch.tensor(dt))
     rev_f = f - _pad(G, f) ** 2 * score
     x_mean = x - rev_f
     return x_mean + _pad(G, x) * noise, x_mean
+
+
+def predictor_em_ref(sde, x, t, y, score, noise):
+    """predictors.py:42-57 (euler_maruyama) over the reverse SDE of sdes.py:131-160: x_mean = x - (drift - g^2 score) dt,
+    x = x_mean + g sqrt(dt) z, dt = 1/N (the same dict-getattr quirk).  Algebraically the reverse-diffusion update."""
+    dt = 1.0 / sde.N
+    if isinstance(sde, PriorMixSDERef):
+        drift, g = sde.sde_env(x, t, y)
+    else:
+        drift, g = sde.sde(x, t) if isinstance(sde, MixSDERef) else sde.sde(x, t, y)
+    total = drift - _pad(g, x) ** 2 * score
+    x_mean = x + total * (-dt)
+    return x_mean + _pad(g, x) * np.sqrt(dt) * noise, x_mean
 
 
 def schedule_timesteps_ref(schedule: Optional[str], T: float, eps: float, N: int) -> Tensor:
@@ -171,7 +239,7 @@ def schedule_timesteps_ref(schedule: Optional[str], T: float, eps: float, N: int
 def pc_sampler_ref(score_fn, sde, y: Tensor, noise: NoiseFn, corrector: str = "ald2",
                    eps: float = 3e-2, snr: float = 0.5, corrector_steps: int = 1, denoise: bool = True,
                    n_spkrs: int = 2, on_score: Optional[Callable] = None,
-                   schedule: Optional[str] = None) -> Tuple[Tensor, int]:
+                   schedule: Optional[str] = None, predictor: str = "reverse_diffusion") -> Tuple[Tensor, int]:
     """``get_pc_sampler`` closure (src/sdes/__init__.py:168-191) with the
     ``reverse_diffusion`` predictor.  Noise draw order (quirk Q3): #0 prior, then per
     step i: corrector draws 1+2i.., predictor draw; 1 + N*(corrector_steps+1) draws.
@@ -196,8 +264,12 @@ def pc_sampler_ref(score_fn, sde, y: Tensor, noise: NoiseFn, corrector: str = "a
                     on_score(k, xt, vec_t, s)
                 k += 1
                 z = noise(draw, xt); draw += 1
-                if corrector == "ald2":
+                if corrector == "ald2" and isinstance(sde, PriorMixSDERef):
+                    xt, xt_mean = corrector_ald2_env_ref(sde, xt, vec_t, y, s, z, snr)
+                elif corrector == "ald2":
                     xt, xt_mean = corrector_ald2_ref(sde, xt, vec_t, s, z, snr)
+                elif corrector == "langevin":
+                    xt, xt_mean = corrector_langevin_ref(xt, s, z, snr)
                 elif corrector == "ald":
                     xt, xt_mean = corrector_ald_ref(sde, xt, vec_t, s, z, snr)
                 else:
@@ -207,7 +279,8 @@ def pc_sampler_ref(score_fn, sde, y: Tensor, noise: NoiseFn, corrector: str = "a
                 on_score(k, xt, vec_t, s)
             k += 1
             z = noise(draw, xt); draw += 1
-            xt, xt_mean = predictor_rd_ref(sde, xt, vec_t, y, s, z)
+            step = predictor_em_ref if predictor == "euler_maruyama" else predictor_rd_ref
+            xt, xt_mean = step(sde, xt, vec_t, y, s, z)
         return (xt_mean if denoise else xt), sde.N * (corrector_steps + 1)
 
 

@@ -17,7 +17,7 @@ import torch.nn.functional as F
 
 from ditsep_b200 import ops
 
-_NAMES = ["pc_corrector", "pc_predictor", "pc_prior", "philox_normal", "stft_compress", "expand_istft", "gn_stats",
+_NAMES = ["pc_corrector", "pc_predictor", "pc_prior", "pc_langevin", "energy_envelope", "philox_normal", "stft_compress", "expand_istft", "gn_stats",
           "gn_sums", "gn_finalize", "gn_apply", "gn_small", "fir_resample", "conv_direct", "attention", "temb_mlp", "temb_dense", "output_layer"]
 
 
@@ -70,8 +70,10 @@ def _pc(p, mode, x, score, t, y, noise, x_mean, lengths=None):
     z = noise.double()
     xb, sb, zb = (a.mean(dim=1, keepdim=True) for a in (xs, s, z))
     yy = 0.0 if y is None else y.double().reshape(B, 1, *x.shape[2:])
-    m = v(c["a0"]) * xs + v(c["a1"]) * xb + v(c["a2"]) * s + v(c["a3"]) * sb + v(c["a4"]) * yy
-    xo = m + v(c["b0"]) * z + v(c["b1"]) * zb
+    env = getattr(p, "_keep", None)  # PriorMixSDE: the tensor behind ditsep_sde_params.elem_scale
+    ev = 1.0 if env is None else env.double().reshape(B, 1, *x.shape[2:])
+    m = v(c["a0"]) * xs + v(c["a1"]) * xb + ev * ev * (v(c["a2"]) * s + v(c["a3"]) * sb) + v(c["a4"]) * yy
+    xo = m + ev * (v(c["b0"]) * z + v(c["b1"]) * zb)
     if lengths is not None:  # ragged batch: state kept at exactly 0 past each row's length (csrc/pc_step.cu)
         L = x[0, 0].numel()
         live = (torch.arange(L)[None] < lengths.reshape(B, 1).long()).reshape(B, 1, *x.shape[2:])
@@ -91,6 +93,24 @@ def pc_predictor(p, x, score, t, y, noise=None, seed=0, draw=0, x_mean=None, len
 
 def pc_prior(p, x, y, noise=None, seed=0, draw=0, lengths=None):
     _pc(p, "prior", x, None, None, y, noise, None, lengths)
+
+
+def pc_langevin(n_src, x, score, noise, step, x_mean=None, lengths=None):
+    eps = step.double().reshape(())
+    m = x.double() + eps * score.double()
+    xo = m + torch.sqrt(2 * eps) * noise.double()
+    x.copy_(xo.float())
+    if x_mean is not None:
+        x_mean.copy_(m.float())
+
+
+def energy_envelope(mix, out, avg_len):
+    """csrc/pc_step.cu::energy_envelope_kernel: zero-padded box sum of mix^2 over [l - k/2, l - k/2 + k), in double."""
+    B, L = mix.shape[0], mix.numel() // mix.shape[0]
+    sq = torch.nn.functional.pad(mix.double().reshape(B, L) ** 2, (avg_len // 2, avg_len - 1 - avg_len // 2))
+    cs = torch.cat([torch.zeros(B, 1, dtype=torch.float64), sq.cumsum(dim=1)], dim=1)
+    box = (cs[:, avg_len:] - cs[:, :-avg_len]) / avg_len
+    out.copy_((0.5 * box.clamp(min=1e-4).sqrt()).float().reshape(out.shape))
 
 
 def philox_normal(out, seed, draw):

@@ -170,7 +170,7 @@ def test_c_abi_library_exports_every_declared_symbol():
     lib = _lib.load()  # raises if the .so is missing or a symbol is not exported
     for name in declared:
         assert getattr(lib, name) is not None
-    assert lib.ditsep_abi_version() == 2
+    assert lib.ditsep_abi_version() == 3
     assert isinstance(lib.ditsep_launch_count(), int)
     # argument validation happens before any CUDA call: errors come back as codes + text, not exceptions
     rc = lib.ditsep_pc_corrector(None, None, None, None, 0, 0, None, None, 1, 8, None, None)
@@ -195,3 +195,46 @@ def test_scheduled_sampler_host_logic_vs_reference_golden(golden, schedule):
     with emulated_ops(), pytest.raises(NotImplementedError):
         sdes.get_pc_scheduled_sampler("reverse_diffusion", "ald2", sde=sdes.MixSDE(2, 2.0, 0.05, 0.5, N=2), score_fn=toy_score,
                                       y=y, schedule="cosine", noise_tape=S.NoiseTape(1))()
+
+
+VARIANTS = {
+    "em_ald2_mix": ("euler_maruyama", "ald2", lambda: sdes.MixSDE(2, 2.0, 0.05, 0.5, N=6)),
+    "rd_langevin_mix": ("reverse_diffusion", "langevin", lambda: sdes.MixSDE(2, 2.0, 0.05, 0.5, N=6)),
+    "rd_ald2_priormix": ("reverse_diffusion", "ald2", lambda: sdes.PriorMixSDE(2, 2.0, 0.05, 0.5, N=6)),
+    "em_ald2_priormix_avg64": ("euler_maruyama", "ald2", lambda: sdes.PriorMixSDE(2, 2.0, 0.05, 0.5, N=6, avg_len=64)),
+}
+
+
+def variant_score(x, t, yy):
+    return -(x - 0.5 * yy) / (0.1 + t[:, None, None]) + 0.05 * torch.sin(3 * x)
+
+
+@pytest.mark.parametrize("name", sorted(VARIANTS))
+def test_sampler_variants_host_logic_vs_reference_golden(golden, name):
+    """SURVEY 8f-2, second half: euler_maruyama predictor, langevin corrector and PriorMixSDE through the emulated kernels
+    against the REFERENCE's outputs (oracle/pin_variants.py runs the unmodified reference with the same tape)."""
+    pred, corr, mk = VARIANTS[name]
+    y = torch.tensor(golden["variants"]["variants_y"])
+    with emulated_ops():
+        x, nfe = sdes.get_pc_sampler(pred, corr, sde=mk(), score_fn=variant_score, y=y, eps=0.03, snr=0.5,
+                                     corrector_steps=1, denoise=True, noise_tape=S.NoiseTape(81))()
+    ref = torch.tensor(golden["variants"][name])
+    assert nfe == 12
+    assert float((x - ref).abs().max()) < 2e-4 * max(1.0, float(ref.abs().max()))
+
+
+def test_priormix_registry_and_off_path_helpers():
+    """`priormix` resolves through the SDE registry (src/sdes/sdes.py:354) and its marginal matches the oracle restatement."""
+    from oracle import sampler_ref as SR
+    sde = sdes.SDERegistry.get_by_name("priormix")(2, 2.0, 0.05, 0.5, N=5, avg_len=33)
+    ref = SR.PriorMixSDERef(2, 2.0, 0.05, 0.5, N=5, avg_len=33)
+    g = torch.Generator().manual_seed(2)
+    mix, x0, t = torch.randn(2, 1, 700, generator=g), torch.randn(2, 2, 700, generator=g), torch.tensor([0.3, 0.8])
+    with emulated_ops():
+        mean, std = sde.marginal_prob(x0, t, mix)
+        drift, diff = sde.sde(x0, t, mix)
+        z = torch.randn(2, 2, 700, generator=g)
+        back = sde.mult_std_inv(std, sde.mult_std(std, z))
+    assert torch.allclose(std, ref.std_env(t, mix), atol=1e-6) and torch.allclose(mean, ref.mean(x0, t), atol=1e-6)
+    assert torch.allclose(diff, ref.sde_env(x0, t, mix)[1], atol=1e-6) and torch.allclose(back, z, atol=1e-4)
+    assert isinstance(sde.copy(), sdes.PriorMixSDE) and sde.copy().avg_len == 33
