@@ -8,7 +8,12 @@
 // channel accumulation with P broadcast from shared memory.  The attention FLOPs are 0.15 %
 // of the step, so this stays on the CUDA cores; the q/k/v/out projections
 // (NIN = 1x1 conv) run on the tensor-core convolution path.
+#include <atomic>
+#include <cstdlib>
+#include <cstring>
+
 #include "common.cuh"
+#include "attention_tc.cuh"
 
 namespace ditsep {
 
@@ -150,6 +155,59 @@ static int launch_attention(const void* q, const void* k, const void* v, int B, 
   return check_launch("attention_kernel");
 }
 
+// ---- tensor-core path (attention_tc.cuh): bf16, C = 128 / 256, at least one full key tile ----------------------------
+typedef CUresult (*AttEncodeFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*,
+                                const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
+                                CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+static AttEncodeFn att_encode_fn() {
+  static AttEncodeFn fn = nullptr;
+  if (fn) return fn;
+  void* sym = nullptr;
+  cudaDriverEntryPointQueryResult qres;
+  if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &sym, cudaEnableDefault, &qres) != cudaSuccess ||
+      qres != cudaDriverEntryPointSuccess)
+    return nullptr;
+  fn = reinterpret_cast<AttEncodeFn>(sym);
+  return fn;
+}
+
+// (C, S, B) view of one of q / k / v: rows of one image are `ld` elements apart; rows past S are zero-filled by TMA
+static int att_map(CUtensorMap* map, const void* p, int B, int S, int C, int ld, int rows) {
+  AttEncodeFn enc = att_encode_fn();
+  DITSEP_REQUIRE(enc != nullptr, "attention: cuTensorMapEncodeTiled not available from the driver");
+  cuuint64_t gdim[3] = {(cuuint64_t)C, (cuuint64_t)S, (cuuint64_t)B};
+  cuuint64_t gstr[2] = {(cuuint64_t)ld * 2, (cuuint64_t)S * ld * 2};
+  cuuint32_t box[3] = {64u, (cuuint32_t)rows, 1u};
+  cuuint32_t estr[3] = {1, 1, 1};
+  CUresult r = enc(map, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 3, const_cast<void*>(p), gdim, gstr, box, estr,
+                   CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                   CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  DITSEP_REQUIRE(r == CUDA_SUCCESS, "attention: cuTensorMapEncodeTiled failed with %d", (int)r);
+  return 0;
+}
+
+template <int C, int kKeys>
+static int launch_attention_tc(const void* q, const void* k, const void* v, int B, int S, int ld, void* o, int ld_o,
+                               cudaStream_t st) {
+  CUtensorMap mq, mk, mv;
+  if (int rc = att_map(&mq, q, B, S, C, ld, kAtQ)) return rc;
+  if (int rc = att_map(&mk, k, B, S, C, ld, kKeys)) return rc;
+  if (int rc = att_map(&mv, v, B, S, C, ld, kKeys)) return rc;
+  const size_t smem = 1024 + (size_t)(C / 64) * kAtQ * 128 + 4 * (size_t)(C / 64) * kKeys * 128 + (size_t)(kKeys / 64) * kAtQ * 128;
+  static std::atomic<bool> attr_set[64];
+  int dev = 0;
+  DITSEP_CUDA(cudaGetDevice(&dev));
+  if (dev < 0 || dev >= 64 || !attr_set[dev].load(std::memory_order_acquire)) {
+    DITSEP_CUDA(cudaFuncSetAttribute(attention_tc_kernel<C, kKeys>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    if (dev >= 0 && dev < 64) attr_set[dev].store(true, std::memory_order_release);
+  }
+  dim3 grid(ceil_div(S, kAtQ), B);
+  DITSEP_CUDA(launch_pdl<2>(attention_tc_kernel<C, kKeys>, grid, dim3(kAtThreads), smem, st, mq, mk, mv, S, (bf16*)o, ld_o,
+                            1.0f / sqrtf((float)C)));
+  return check_launch("attention_tc_kernel");
+}
+
 }  // namespace ditsep
 
 using namespace ditsep;
@@ -161,6 +219,17 @@ extern "C" int ditsep_attention(const void* q, const void* k, const void* v, int
   DITSEP_REQUIRE(C == 64 || C == 128 || C == 256, "attention: C=%d unsupported (64, 128, 256)", C);
   DITSEP_REQUIRE(ld_qkv % 8 == 0 && ld_qkv >= C && ld_o >= C, "attention: bad strides");
   cudaStream_t st = (cudaStream_t)stream;
+  {
+    // tcgen05 kernel: bf16, C = 128 / 256, 16-byte aligned operands, a sequence of at least 64 tokens
+    // (DITSEP_ATTN_TC=0 keeps the CUDA-core kernel: debug aid and the comparison arm of the tests)
+    const char* env = getenv("DITSEP_ATTN_TC");
+    const bool aligned = ((reinterpret_cast<uintptr_t>(q) | reinterpret_cast<uintptr_t>(k) | reinterpret_cast<uintptr_t>(v) |
+                           reinterpret_cast<uintptr_t>(o)) & 15) == 0 && ld_o % 8 == 0;
+    if (dtype == DITSEP_BF16 && (C == 128 || C == 256) && S >= 64 && aligned && !(env && strcmp(env, "0") == 0)) {
+      if (C == 128) return launch_attention_tc<128, 128>(q, k, v, B, S, ld_qkv, o, ld_o, st);
+      return launch_attention_tc<256, 64>(q, k, v, B, S, ld_qkv, o, ld_o, st);
+    }
+  }
 #define CASE(T, CPL) return launch_attention<T, CPL>(q, k, v, B, S, ld_qkv, o, ld_o, st)
   if (dtype == DITSEP_F32) {
     if (C == 64) CASE(float, 2);

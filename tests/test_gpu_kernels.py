@@ -517,6 +517,30 @@ def test_attention(B, H, W, C, dtype):
     assert rel(out.float(), ref.float()) < (2e-5 if dtype == torch.float32 else 6e-3)
 
 
+@pytest.mark.parametrize("B,H,W,C", [(2, 16, 16, 128), (8, 16, 80, 128), (3, 16, 20, 256), (2, 12, 9, 128), (1, 16, 5, 256),
+                                     (2, 8, 8, 128)])
+def test_attention_tensor_core_kernel(B, H, W, C, monkeypatch):
+    """attention_tc_kernel (tcgen05: Q K^T and P V as UMMA tiles, V as an MN-major operand, two-pass softmax) against the
+    fp32 torch statement and against the CUDA-core kernel; q / k / v are slices of one fused projection buffer, S is
+    256 (C2), 1280 (C3 at its maximum), 320 (C4, C = 256) and sequences that are not multiples of the key tile."""
+    qkv = torch.randn(B, H, W, 3 * C, generator=g(41)).to(torch.bfloat16)
+    qkv[..., :C] *= 3.0                                  # peaky softmax rows as well as flat ones
+    ref = torch.empty(B, H, W, C)
+    E.attention(qkv[..., :C].float(), qkv[..., C:2 * C].float(), qkv[..., 2 * C:].float(), ref)
+    d = qkv.to(DEV)
+    n0 = ops.launch_count()
+    out = torch.full((B, H, W, C), float("nan"), device=DEV, dtype=torch.bfloat16)
+    ops.attention(d[..., :C], d[..., C:2 * C], d[..., 2 * C:], out)
+    monkeypatch.setenv("DITSEP_ATTN_TC", "0")
+    old = torch.empty_like(out)
+    ops.attention(d[..., :C], d[..., C:2 * C], d[..., 2 * C:], old)
+    torch.cuda.synchronize()
+    e, e_old = rel(out.float(), ref), rel(old.float(), ref)
+    print(f"attention_tc B={B} S={H * W} C={C}: rel-L2 vs fp32 {e:.2e} (CUDA-core kernel {e_old:.2e})")
+    assert not torch.isnan(out.float()).any()
+    assert e < 6e-3 and e < 2.0 * e_old + 1e-3
+
+
 def test_temb_and_output_layer():
     B, nf = 3, 64
     t = torch.tensor([1.0, 0.4, 0.03])
