@@ -555,8 +555,9 @@ def profile_score_step(model, name, B, dev, latent):
                 x = a[0]
                 n_el = x.shape[0] * x.shape[1] * x.shape[2] * x.shape[3]
                 e = x.element_size()
-                if nm == "gn_apply":
+                if nm in ("gn_apply", "gn_apply_srcs"):                # (_srcs: scale / shift folded in the same launch)
                     by = 2.0 * n_el * e                                   # read x, write act(GN(x))
+                    nm = "gn_apply"
                 elif nm == "gn_partial_sums":
                     by = 1.0 * n_el * e
                 elif nm == "fir_resample":

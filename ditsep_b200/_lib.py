@@ -56,6 +56,7 @@ SIGNATURES = {
                                        c_void_p, c_void_p]),
     "ditsep_gn_small": (c_int, [c_void_p, c_int, c_int, c_int64, c_int, c_int, c_int, c_void_p, c_void_p, c_float, c_int,
                                 c_void_p, c_int, c_void_p]),
+    "ditsep_gn_apply_job": (c_int, [c_void_p, c_int, c_int, c_int64, C.POINTER(GnJob), c_int, c_int, c_void_p, c_int, c_void_p]),
     "ditsep_gn_apply": (c_int, [c_void_p, c_int, c_int, c_int64, c_int, c_int, c_void_p, c_int, c_void_p, c_int,
                                 c_void_p]),
     "ditsep_fir_resample": (c_int, [c_void_p, c_int, c_int, c_int, c_int, c_int, c_int, c_int, c_void_p, c_void_p,

@@ -71,19 +71,32 @@ __global__ void __launch_bounds__(256) gn_sums_kernel(const T* __restrict__ x, i
 // along the channel axis (torch.cat([h, skip], dim=1) feeding GroupNorm_0, ncsnpp.py:413 + layerspp.py:297).
 // One image per call; executed by a whole CTA (any block size).  The arithmetic from the exact integer sums on is
 // double precision in a fixed order: bit-reproducible.  grp: shared scratch of >= 2 * G doubles.
-__device__ __forceinline__ void gn_job_image(const ditsep_gn_job& job, int b, double* grp) {
+// Every channel's four words are fetched by a thread of its own first (ONE L2 round trip for the whole image; the
+// first version walked a group's channels serially: cpg dependent round trips, ~5 us per image), then a thread per
+// group adds its channels in ascending order.
+constexpr int kGnMaxC = 512;
+
+template <bool kToShared>
+__device__ __forceinline__ void gn_job_image(const ditsep_gn_job& job, int b, double* chan, double* grp, float* ss_out) {
   const int C = job.C, G = job.G, cpg = C / G;
+  for (int c = threadIdx.x; c < C; c += blockDim.x) {
+    int cc = c, k = 0;
+    while (k < job.n_src - 1 && cc >= job.src_C[k]) {
+      cc -= job.src_C[k];
+      ++k;
+    }
+    const longlong2* sp = reinterpret_cast<const longlong2*>(job.src_sums[k] + ((int64_t)b * job.src_C[k] + cc) * 4);
+    const longlong2 s = sp[0], q = sp[1];
+    const long long sv[2] = {s.x, s.y}, qv[2] = {q.x, q.y};
+    chan[2 * c] = fx_value(sv);
+    chan[2 * c + 1] = fx_value(qv);
+  }
+  __syncthreads();
   for (int g = threadIdx.x; g < G; g += blockDim.x) {
     double a = 0.0, q = 0.0;
     for (int i = 0; i < cpg; ++i) {
-      int cc = g * cpg + i, k = 0;
-      while (k < job.n_src - 1 && cc >= job.src_C[k]) {
-        cc -= job.src_C[k];
-        ++k;
-      }
-      const long long* sp = job.src_sums[k] + ((int64_t)b * job.src_C[k] + cc) * 4;
-      a += fx_value(sp);
-      q += fx_value(sp + 2);
+      a += chan[2 * (g * cpg + i)];
+      q += chan[2 * (g * cpg + i) + 1];
     }
     const double n = (double)job.HW * cpg, mean = a / n;
     double var = q / n - mean * mean;
@@ -95,8 +108,14 @@ __device__ __forceinline__ void gn_job_image(const ditsep_gn_job& job, int b, do
   for (int c = threadIdx.x; c < C; c += blockDim.x) {
     const int g = c / cpg;
     const double sc = grp[2 * g + 1] * (double)job.gamma[c];
-    job.scale_shift[((int64_t)b * 2) * C + c] = (float)sc;
-    job.scale_shift[((int64_t)b * 2 + 1) * C + c] = (float)((double)job.beta[c] - grp[2 * g] * sc);
+    const float fs = (float)sc, fh = (float)((double)job.beta[c] - grp[2 * g] * sc);
+    if (kToShared) {
+      ss_out[c] = fs;
+      ss_out[C + c] = fh;
+    } else {
+      job.scale_shift[((int64_t)b * 2) * C + c] = fs;
+      job.scale_shift[((int64_t)b * 2 + 1) * C + c] = fh;
+    }
   }
   __syncthreads();
 }
@@ -105,26 +124,40 @@ __device__ __forceinline__ void gn_job_image(const ditsep_gn_job& job, int b, do
 __global__ void __launch_bounds__(128) gn_finalize_kernel(const ditsep_gn_job job) {
   griddep_launch_dependents();
   griddep_wait();
+  __shared__ double chan[2 * kGnMaxC];
   __shared__ double grp[2 * 64];
-  gn_job_image(job, blockIdx.x, grp);
+  gn_job_image<false>(job, blockIdx.x, chan, grp, nullptr);
 }
 
 // ------------------------------------------------------------------- normalise + SiLU
 // grid (blocks per image, B); block = cv * ppb threads (cv = C/8 channel packs, ppb pixels in flight).  A thread
 // keeps ONE channel pack for its whole life, so the per-(b,c) scale / shift sit in registers and the loop body is
 // load 16 B (bf16) -> 8 fma + SiLU -> store 16 B, four pixels in flight per thread.
-template <typename T>
+// kJob: the per-(b, c) scale / shift are formed by the CTA itself from the producers' fixed-point sums (the gn_finalize
+// arithmetic, ~1 us per CTA) instead of being read from a buffer a separate launch wrote: 51 of the 63 gn_finalize
+// launches of a score step disappear.
+template <typename T, bool kJob>
 __global__ void __launch_bounds__(256) gn_apply_kernel(const T* __restrict__ x, int64_t HW, int C, int ld_x,
-                                                       const float* __restrict__ scale_shift, int silu,
-                                                       T* __restrict__ y, int ld_y, int cv, int ppb) {
+                                                       const float* __restrict__ scale_shift, const ditsep_gn_job job,
+                                                       int silu, T* __restrict__ y, int ld_y, int cv, int ppb) {
   griddep_launch_dependents();
   griddep_wait();
   const int b = blockIdx.y;
   const int v = threadIdx.x % cv, pp = threadIdx.x / cv;
-  if (pp >= ppb) return;
   float sc[8], sh[8];
-  Pack8<float>::load(scale_shift + ((int64_t)b * 2) * C + v * 8, sc);
-  Pack8<float>::load(scale_shift + ((int64_t)b * 2 + 1) * C + v * 8, sh);
+  if (kJob) {
+    __shared__ double chan[2 * kGnMaxC];
+    __shared__ double grp[2 * 64];
+    __shared__ __align__(16) float ss_s[2 * kGnMaxC];
+    gn_job_image<true>(job, b, chan, grp, ss_s);
+    if (pp >= ppb) return;
+    Pack8<float>::load(ss_s + v * 8, sc);
+    Pack8<float>::load(ss_s + C + v * 8, sh);
+  } else {
+    if (pp >= ppb) return;
+    Pack8<float>::load(scale_shift + ((int64_t)b * 2) * C + v * 8, sc);
+    Pack8<float>::load(scale_shift + ((int64_t)b * 2 + 1) * C + v * 8, sh);
+  }
   const T* xb = x + (int64_t)b * HW * ld_x + v * 8;
   T* yb = y + (int64_t)b * HW * ld_y + v * 8;
   const int64_t stride = (int64_t)gridDim.x * ppb;
@@ -787,7 +820,7 @@ extern "C" int ditsep_gn_sums(const void* x, int dtype, int B, int64_t HW, int C
   return check_launch("gn_sums_kernel");
 }
 
-static int check_gn_job(const ditsep_gn_job* j, const char* who) {
+static int check_gn_job(const ditsep_gn_job* j, const char* who, bool need_out = true) {
   DITSEP_REQUIRE(j != nullptr, "%s: null job", who);
   DITSEP_REQUIRE(j->n_src >= 1 && j->n_src <= 4, "%s: 1..4 statistics sources (got %d)", who, j->n_src);
   int ctot = 0;
@@ -798,7 +831,8 @@ static int check_gn_job(const ditsep_gn_job* j, const char* who) {
   DITSEP_REQUIRE(ctot == j->C, "%s: sources cover %d channels, GroupNorm has %d", who, ctot, j->C);
   DITSEP_REQUIRE(j->G > 0 && j->G <= 64 && j->C % j->G == 0, "%s: C=%d not divisible into G=%d groups (G <= 64)", who, j->C,
                  j->G);
-  DITSEP_REQUIRE(j->HW > 0 && j->gamma && j->beta && j->scale_shift, "%s: null gamma / beta / scale_shift", who);
+  DITSEP_REQUIRE(j->C <= kGnMaxC, "%s: C=%d exceeds %d", who, j->C, kGnMaxC);
+  DITSEP_REQUIRE(j->HW > 0 && j->gamma && j->beta && (j->scale_shift || !need_out), "%s: null gamma / beta / scale_shift", who);
   return 0;
 }
 
@@ -828,9 +862,8 @@ extern "C" int ditsep_gn_small(const void* x, int dtype, int B, int64_t HW, int 
   return check_launch("gn_small_kernel");
 }
 
-extern "C" int ditsep_gn_apply(const void* x, int dtype, int B, int64_t HW, int C, int ld_x, const float* scale_shift,
-                               int silu, void* y, int ld_y, void* stream) {
-  DITSEP_REQUIRE(x && y && scale_shift, "gn_apply: null pointer");
+static int launch_gn_apply(const void* x, int dtype, int B, int64_t HW, int C, int ld_x, const float* scale_shift,
+                           const ditsep_gn_job* job, int silu, void* y, int ld_y, void* stream) {
   DITSEP_REQUIRE(C % 8 == 0 && ld_x % 8 == 0 && ld_y % 8 == 0, "gn_apply: C/ld must be multiples of 8");
   const int cv = C / 8;
   DITSEP_REQUIRE(cv <= 256, "gn_apply: C=%d too wide", C);
@@ -842,15 +875,39 @@ extern "C" int ditsep_gn_apply(const void* x, int dtype, int B, int64_t HW, int 
   if (gx < 1) gx = 1;
   dim3 grid((unsigned)gx, (unsigned)B);
   cudaStream_t st = (cudaStream_t)stream;
+  const ditsep_gn_job none = {};
+#define DITSEP_GN_APPLY(T)                                                                                              \
+  do {                                                                                                                  \
+    if (job)                                                                                                            \
+      DITSEP_CUDA(launch_pdl(gn_apply_kernel<T, true>, grid, dim3(256), 0, st, (const T*)x, HW, C, ld_x, scale_shift, *job, \
+                             silu, (T*)y, ld_y, cv, ppb));                                                              \
+    else                                                                                                                \
+      DITSEP_CUDA(launch_pdl(gn_apply_kernel<T, false>, grid, dim3(256), 0, st, (const T*)x, HW, C, ld_x, scale_shift, none, \
+                             silu, (T*)y, ld_y, cv, ppb));                                                              \
+  } while (0)
   if (dtype == DITSEP_F32)
-    DITSEP_CUDA(launch_pdl(gn_apply_kernel<float>, grid, dim3(256), 0, st, (const float*)x, HW, C, ld_x, scale_shift, silu,
-                           (float*)y, ld_y, cv, ppb));
+    DITSEP_GN_APPLY(float);
   else if (dtype == DITSEP_BF16)
-    DITSEP_CUDA(launch_pdl(gn_apply_kernel<bf16>, grid, dim3(256), 0, st, (const bf16*)x, HW, C, ld_x, scale_shift, silu,
-                           (bf16*)y, ld_y, cv, ppb));
+    DITSEP_GN_APPLY(bf16);
   else
     DITSEP_REQUIRE(false, "gn_apply: unknown dtype %d", dtype);
+#undef DITSEP_GN_APPLY
   return check_launch("gn_apply_kernel");
+}
+
+extern "C" int ditsep_gn_apply(const void* x, int dtype, int B, int64_t HW, int C, int ld_x, const float* scale_shift,
+                               int silu, void* y, int ld_y, void* stream) {
+  DITSEP_REQUIRE(x && y && scale_shift, "gn_apply: null pointer");
+  return launch_gn_apply(x, dtype, B, HW, C, ld_x, scale_shift, nullptr, silu, y, ld_y, stream);
+}
+
+extern "C" int ditsep_gn_apply_job(const void* x, int dtype, int B, int64_t HW, const ditsep_gn_job* host_job, int ld_x,
+                                   int silu, void* y, int ld_y, void* stream) {
+  DITSEP_REQUIRE(x && y, "gn_apply_job: null pointer");
+  if (int rc = check_gn_job(host_job, "gn_apply_job", false)) return rc;
+  DITSEP_REQUIRE(host_job->HW == HW, "gn_apply_job: the job normalises %lld pixels per image, the tensor has %lld",
+                 (long long)host_job->HW, (long long)HW);
+  return launch_gn_apply(x, dtype, B, HW, host_job->C, ld_x, nullptr, host_job, silu, y, ld_y, stream);
 }
 
 template <typename T>

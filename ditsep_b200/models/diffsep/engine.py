@@ -122,6 +122,16 @@ class _SumsArena:
             c.zero_()
 
 
+@dataclass
+class _GnSrcs:
+    """A GroupNorm whose scale / shift have not been materialised: the producers' fixed-point sums (1..4 sources laid
+    end to end along the channel axis) + the layer's parameters.  gn_apply folds them itself (ops.gn_apply_srcs)."""
+    srcs: list
+    G: int
+    gamma: torch.Tensor
+    beta: torch.Tensor
+
+
 class _ConvW:
     """Packed filter of one convolution."""
 
@@ -482,7 +492,11 @@ class _Plan:
             # conv(act(GroupNorm(x))) (layerspp.py:297-298,318-320): one normalise + SiLU pass, then the convolution.
             # (Applying it to the landed tiles inside the conv kernel was measured slower in round 1 and removed.)
             act = x if gn_inplace else self.pool.get(tuple(x.shape), x.dtype)
-            self.steps.append((ops.gn_apply, (x, in_ss, in_silu, act), {}))
+            if isinstance(in_ss, _GnSrcs):  # scale / shift formed inside the apply kernel from the producers' sums
+                self.steps.append((ops.gn_apply_srcs, (x, in_ss.srcs, in_ss.G, in_ss.gamma, in_ss.beta, 1e-6, in_silu, act),
+                                   {"cache": {}}))
+            else:
+                self.steps.append((ops.gn_apply, (x, in_ss, in_silu, act), {}))
             if act is not x:
                 self.pool.put(act)  # free again once this conv has run (the launch list is sequential)
             x = act
@@ -509,13 +523,14 @@ class _Plan:
             self.stat_src[key] = ("lazy", out)
         return True
 
-    def _scale_shift(self, x, gnw) -> torch.Tensor:
+    def _scale_shift(self, x, gnw, want_tensor: bool = False):
         """GroupNorm(min(C/4,32), C, eps=1e-6) of the NHWC view x folded to per-(b,c) scale/shift
         (layerspp.py:269-271,297,318).  Uses the producers' recorded sums when every channel range of
-        x has one (a concat buffer = [main path | skip]); otherwise one statistics pass over x."""
+        x has one (a concat buffer = [main path | skip]); otherwise one statistics pass over x.
+        want_tensor: the consumer reads a (B, 2, C) buffer (the FIR kernels): one gn_finalize launch writes it.
+        Otherwise the sums themselves are returned (_GnSrcs) and the consumer -- gn_apply -- folds them itself."""
         B, H, W, C = x.shape
         G = min(C // 4, 32)
-        ss = torch.empty(B, 2, C, device=self.device, dtype=torch.float32)
         srcs, ptr, left = [], x.data_ptr(), C
         while left > 0:
             hit = None
@@ -538,6 +553,12 @@ class _Plan:
             buf = self.sums.new(B, C)
             self.steps.append((ops.gn_sums, (x, buf), {}))
             srcs = [buf]
+        # Folding the finalize arithmetic into gn_apply (ops.gn_apply_srcs) was MEASURED SLOWER (r2zd: 48.6 vs 50.3
+        # mixtures/s; every CTA of the apply kernel pays the ~5 us prologue, and a 2-wave grid pays it twice, where the
+        # separate launch hides under its predecessor's tail): opt-in only.
+        if not want_tensor and C <= 512 and os.environ.get("DITSEP_GN_FOLD", "0") == "1":
+            return _GnSrcs(srcs, G, gnw[0], gnw[1])
+        ss = torch.empty(B, 2, C, device=self.device, dtype=torch.float32)
         self.steps.append((ops.gn_finalize, (srcs, B, H * W, G, gnw[0], gnw[1], 1e-6, ss), {}))
         return ss
 
@@ -560,7 +581,7 @@ class _Plan:
         B, H, W, cin = x.shape
         cout = spec.out_ch
         small0 = self._small(x) and not (spec.up or spec.down)
-        ss0 = None if small0 else self._scale_shift(x, w[f"gn{i}a"])
+        ss0 = None if small0 else self._scale_shift(x, w[f"gn{i}a"], want_tensor=bool(spec.up or spec.down))
         if spec.up or spec.down:
             Ho, Wo = (2 * H, 2 * W) if spec.up else (H // 2, W // 2)
             xr = pool.get((B, Ho, Wo, cin), self.adt)

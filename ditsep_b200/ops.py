@@ -228,10 +228,12 @@ def make_gn_job(srcs, B: int, HW: int, G: int, gamma, beta, eps: float, scale_sh
         job.src_sums[i] = t.data_ptr()
         job.src_C[i] = ci
         ctot += ci
-    if scale_shift.dtype != torch.float32 or not scale_shift.is_contiguous() or scale_shift.numel() != B * 2 * ctot:
+    if scale_shift is not None and (scale_shift.dtype != torch.float32 or not scale_shift.is_contiguous()
+                                    or scale_shift.numel() != B * 2 * ctot):
         raise _lib.DitsepError("GroupNorm job: scale_shift must be contiguous f32 (B, 2, C)")
     job.n_src, job.C, job.G, job.eps, job.HW = len(srcs), ctot, G, eps, HW
-    job.gamma, job.beta, job.scale_shift = gamma.data_ptr(), beta.data_ptr(), scale_shift.data_ptr()
+    job.gamma, job.beta = gamma.data_ptr(), beta.data_ptr()
+    job.scale_shift = None if scale_shift is None else scale_shift.data_ptr()
     job._keep = (srcs, gamma, beta, scale_shift)
     return job
 
@@ -241,6 +243,29 @@ def gn_finalize(srcs, B: int, HW: int, G: int, gamma, beta, eps: float, scale_sh
     along the channel axis)."""
     job = make_gn_job(srcs, B, HW, G, gamma, beta, eps, scale_shift)
     check(_lib.load().ditsep_gn_finalize(C.byref(job), B, _stream()), "gn_finalize")
+
+
+def gn_apply_job(x, job, silu: bool, y):
+    """y = act(GroupNorm(x)) with the scale / shift formed inside the kernel from the job's fixed-point sums
+    (make_gn_job with scale_shift=None): gn_finalize + gn_apply in one launch."""
+    _cuda(x, y)
+    B, H, W, Cc = x.shape
+    if y.dtype != x.dtype or job.C != Cc:
+        raise _lib.DitsepError("gn_apply_job: dtype / channel mismatch")
+    check(_lib.load().ditsep_gn_apply_job(_ptr(x), _dt(x), B, H * W, C.byref(job), nhwc_ld(x), int(silu), _ptr(y),
+                                          nhwc_ld(y), _stream()), "gn_apply_job")
+
+
+def gn_apply_srcs(x, srcs, G: int, gamma, beta, eps: float, silu: bool, y, cache: dict = None):
+    """y = act(GroupNorm(G)(x)) straight from the producers' sums `srcs` (see gn_finalize): ONE launch, no scale / shift
+    buffer.  cache: a dict owned by the caller's launch plan; the ditsep_gn_job struct is built on the first call."""
+    job = None if cache is None else cache.get("job")
+    if job is None:
+        B, H, W, _ = x.shape
+        job = make_gn_job(srcs, B, H * W, G, gamma, beta, eps, None)
+        if cache is not None:
+            cache["job"] = job
+    gn_apply_job(x, job, silu, y)
 
 
 def gn_stats(x, G: int, gamma, beta, eps: float, scale_shift):

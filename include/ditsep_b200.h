@@ -152,6 +152,10 @@ int ditsep_gn_stats_static(const void* x, int dtype, int B, int64_t HW, int C, i
 int ditsep_gn_small(const void* x, int dtype, int B, int64_t HW, int C, int ld_x, int G, const float* gamma,
                     const float* beta, float eps, int silu, void* y, int ld_y, void* stream);
 
+/* ditsep_gn_finalize + ditsep_gn_apply in one launch: every CTA forms the scale / shift of its image from the job's sums
+ * itself (host_job->scale_shift is not used and may be NULL).  C = host_job->C. */
+int ditsep_gn_apply_job(const void* x, int dtype, int B, int64_t HW, const ditsep_gn_job* host_job, int ld_x, int silu,
+                        void* y, int ld_y, void* stream);
 /* y = act(x*scale + shift), act = SiLU if silu else identity.  y: NHWC with stride ld_y. */
 int ditsep_gn_apply(const void* x, int dtype, int B, int64_t HW, int C, int ld_x, const float* scale_shift,
                     int silu, void* y, int ld_y, void* stream);

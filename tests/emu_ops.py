@@ -18,7 +18,7 @@ import torch.nn.functional as F
 from ditsep_b200 import ops
 
 _NAMES = ["pc_corrector", "pc_predictor", "pc_prior", "pc_langevin", "energy_envelope", "philox_normal", "stft_compress", "expand_istft", "gn_stats",
-          "gn_sums", "gn_finalize", "gn_apply", "gn_small", "fir_resample", "conv_direct", "attention", "temb_mlp", "temb_dense", "output_layer"]
+          "gn_sums", "gn_finalize", "gn_apply", "gn_apply_srcs", "gn_small", "fir_resample", "conv_direct", "attention", "temb_mlp", "temb_dense", "output_layer"]
 
 
 def _coef(p, mode, t):
@@ -188,6 +188,13 @@ def gn_finalize(srcs, B, HW, G, gamma, beta, eps, scale_shift):
     """ditsep_gn_finalize: sources laid end to end along the channel axis."""
     s = torch.cat([_fx_decode(t) for t in srcs], dim=1)  # (B, C, 2)
     _gn_from_channel_sums(s, HW, G, gamma, beta, eps, scale_shift)
+
+
+def gn_apply_srcs(x, srcs, G, gamma, beta, eps, silu, y, cache=None):
+    B, H, W, C = x.shape
+    ss = torch.empty(B, 2, C)
+    gn_finalize(srcs, B, H * W, G, gamma, beta, eps, ss)
+    gn_apply(x, ss, silu, y)
 
 
 def gn_stats(x, G, gamma, beta, eps, scale_shift):

@@ -466,6 +466,30 @@ def test_conv_ts_filter_in_tensor_memory(B, H, W, Cx, monkeypatch):
         assert torch.equal(o1, out[B - 1:]) and torch.equal(s1[0], st[B - 1])
 
 
+@pytest.mark.parametrize("dtype", [torch.float32, torch.bfloat16])
+def test_gn_apply_srcs_equals_finalize_then_apply(dtype):
+    """ditsep_gn_apply_job (scale / shift folded inside the apply kernel from two producers' sums) is bit-identical to
+    gn_finalize followed by gn_apply."""
+    B, H, W, C1, C2 = 3, 24, 16, 128, 64
+    x = torch.randn(B, H, W, C1 + C2, generator=g(70)).to(DEV).to(dtype)
+    s1, s2 = ops.new_sums(B, C1, DEV), ops.new_sums(B, C2, DEV)
+    ops.gn_sums(x[..., :C1], s1)
+    ops.gn_sums(x[..., C1:], s2)
+    C = C1 + C2
+    gamma, beta = (1 + 0.1 * torch.randn(C, generator=g(71))).to(DEV), (0.1 * torch.randn(C, generator=g(72))).to(DEV)
+    ss = torch.empty(B, 2, C, device=DEV)
+    ops.gn_finalize([s1, s2], B, H * W, 32, gamma, beta, 1e-6, ss)
+    want = torch.empty_like(x)
+    ops.gn_apply(x, ss, True, want)
+    got, cache = torch.empty_like(x), {}
+    for _ in range(2):  # second call reuses the cached job struct
+        got.fill_(float("nan"))
+        ops.gn_apply_srcs(x, [s1, s2], 32, gamma, beta, 1e-6, True, got, cache=cache)
+    assert torch.equal(got, want)
+    ref = torch.nn.functional.silu(torch.nn.functional.group_norm(x.float().permute(0, 3, 1, 2), 32, gamma, beta, 1e-6))
+    assert rel(got.float().permute(0, 3, 1, 2), ref) < (2e-5 if dtype == torch.float32 else 5e-3)
+
+
 def test_gn_finalize_concat_sources():
     """GroupNorm over torch.cat([h, skip]) (ncsnpp.py:413) from two producers' statistics: a conv
     epilogue's sums for h (128 ch) and an explicit statistics pass for skip (64 ch); 6-channel groups straddle the
