@@ -141,8 +141,13 @@ __global__ void __launch_bounds__(256) stft_compress_kernel(const float* __restr
         // |X|^e e^{j arg X} * factor = X * |X|^(e-1) * factor
         float mag2 = X.x * X.x + X.y * X.y;
         float sc = 0.f;
-        if (mag2 > 0.f) sc = (exponent == 0.5f) ? factor * rsqrtf(sqrtf(mag2)) : factor * powf(mag2, 0.5f * (exponent - 1.0f));
-        if (exponent == 1.0f) sc = factor;
+        if (exponent == 0.f) {  // transform="log" (score_models.py:49-51): log1p(|X|) e^{j arg X} * |factor|
+          const float mag = sqrtf(mag2);
+          sc = mag > 0.f ? fabsf(factor) * log1pf(mag) / mag : 0.f;
+        } else {
+          if (mag2 > 0.f) sc = (exponent == 0.5f) ? factor * rsqrtf(sqrtf(mag2)) : factor * powf(mag2, 0.5f * (exponent - 1.0f));
+          if (exponent == 1.0f) sc = factor;
+        }
         re = X.x * sc;
         im = X.y * sc;
       }
@@ -187,7 +192,7 @@ __global__ void __launch_bounds__(256) expand_istft_kernel(const float* __restri
   float2* zbuf = scratch + warp * 2 * kBins;
   float2* xbuf = zbuf + kBins;
   const float inv_factor = 1.0f / fabsf(factor);
-  const float pw = 1.0f / exponent - 1.0f;
+  const float pw = exponent > 0.f ? 1.0f / exponent - 1.0f : 0.f;
   for (int item = warp; item < kIF * n_src; item += kWarps) {
     const int src = item % n_src, fl = item / n_src;
     const int f = f0 - 3 + fl;
@@ -201,7 +206,12 @@ __global__ void __launch_bounds__(256) expand_istft_kernel(const float* __restri
       float re = px[src] * inv_factor, im = px[n_src + src] * inv_factor;
       float mag2 = re * re + im * im;
       float sc = 1.0f;
-      if (exponent != 1.0f) sc = (mag2 > 0.f) ? ((exponent == 0.5f) ? sqrtf(mag2) : powf(mag2, 0.5f * pw)) : 0.f;
+      if (exponent == 0.f) {  // transform="log" backwards (score_models.py:66-68): (exp(|Y|) - 1) e^{j arg Y}
+        const float mag = sqrtf(mag2);
+        sc = mag > 0.f ? expm1f(mag) / mag : 0.f;
+      } else if (exponent != 1.0f) {
+        sc = (mag2 > 0.f) ? ((exponent == 0.5f) ? sqrtf(mag2) : powf(mag2, 0.5f * pw)) : 0.f;
+      }
       xbuf[k] = make_float2(re * sc, im * sc);
     }
     __syncwarp();
@@ -260,7 +270,7 @@ extern "C" int ditsep_stft_compress(const float* xt, const float* mix, const flo
   const int n_frames = 1 + (int)((T + (kNfft - kHop)) / kHop);
   DITSEP_REQUIRE(W % kFT == 0 && W >= n_frames, "stft_compress: W=%d must be a multiple of %d and >= %d frames", W,
                  kFT, n_frames);
-  DITSEP_REQUIRE(exponent > 0.f, "stft_compress: exponent must be > 0");
+  DITSEP_REQUIRE(exponent >= 0.f, "stft_compress: exponent must be > 0 (power law) or 0 (log1p transform)");
   const int NC = n_src + 1, C2 = 2 * NC;
   size_t smem = kNfft * 8 + (kNfft + 2) * 4 + (size_t)(NC * kSigLen + ((NC * kSigLen) & 1)) * 4 +
                 (size_t)kWarps * 2 * kBins * 8 + (size_t)kBins * (kFT * C2 + 1) * 4;
@@ -286,7 +296,7 @@ extern "C" int ditsep_expand_istft(const float* spec, const float* window, float
   DITSEP_REQUIRE(B > 0 && T > 0 && n_src >= 1 && n_src <= 4, "expand_istft: bad sizes");
   const int n_frames = 1 + (int)((T + (kNfft - kHop)) / kHop);
   DITSEP_REQUIRE(W >= n_frames, "expand_istft: W=%d < %d frames", W, n_frames);
-  DITSEP_REQUIRE(exponent > 0.f && factor != 0.f, "expand_istft: bad exponent/factor");
+  DITSEP_REQUIRE(exponent >= 0.f && factor != 0.f, "expand_istft: bad exponent/factor (exponent 0 = log1p transform)");
   size_t smem = kNfft * 8 + (kNfft + 2) * 4 + (size_t)kWarps * 2 * kBins * 8 + (size_t)n_src * kIF * kNfft * 4;
   dim3 grid(ceil_div(T + kHalf, (int64_t)kHop * kIT), B);
   DITSEP_CUDA(cudaFuncSetAttribute(expand_istft_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));

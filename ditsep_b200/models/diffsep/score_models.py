@@ -113,7 +113,9 @@ class ScoreModelNCSNpp(torch.nn.Module):
             return abs(float(self.spec_abs_exponent)), float(self.spec_factor)
         if self.transform == "none":
             return 1.0, 1.0
-        raise NotImplementedError("transform='log' has no fused sm_100a kernel (no DiffSep config uses it)")
+        if self.transform == "log":  # log1p(|X|) e^{j arg X} * |factor| (score_models.py:49-51,66-68): exponent 0 in the C ABI
+            return 0.0, abs(float(self.spec_factor))
+        raise ValueError("transform must be one of 'exponent'|'log'|'none'")
 
     # ------------------------------------------------------------------ reference helper API
     def pad(self, x):

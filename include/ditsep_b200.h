@@ -95,6 +95,8 @@ int ditsep_box_muller(const uint32_t* bits, float* out, int64_t n, void* stream)
  * cat(xt, mix) -> right pad n_fft-hop -> STFT(n_fft=510, hop=128, periodic Hann, centre
  * zero pad, onesided) -> |X|^e e^{j arg X} * factor -> channels [Re c0..cn, Im c0..cn]
  * -> frames zero-padded to W; optional NCSNpp "2x-1" (ncsnpp.py:348-350) folded in.
+ * exponent == 0 selects transform="log" instead (score_models.py:49-51,66-68): log1p(|X|) e^{j arg X} * |factor|, and
+ * (exp(|S / factor|) - 1) e^{j arg S} on the way back; exponent == 1 with factor 1 is transform="none".
  * xt: (B, n_src, T) f32, mix: (B, 1, T) f32, window: (510,) f32.
  * feat: NHWC [B][256][W][2(n_src+1)] of `dtype`.  n_frames = 1 + (T+382)/128 <= W. */
 int ditsep_stft_compress(const float* xt, const float* mix, const float* window, void* feat, int dtype, int B,
@@ -224,7 +226,9 @@ void ditsep_debug_conv_trace(void* buf);
 
 /* ---- attention (single head, all H*W tokens) ------------------------------------------
  * AttnBlockpp.forward core (layerspp.py:88-92): o = softmax(q k^T / sqrt(C)) v per image.
- * q, k, v, o: NHWC [B][S][ld] with C channels. */
+ * q, k, v, o: NHWC [B][S][ld] with C channels.  bf16 with C = 128 / 256, S >= 64 and 16-byte aligned operands runs on
+ * the tensor cores (tcgen05: Q K^T and P V as UMMA tiles, V as an MN-major operand; csrc/attention_tc.cuh); fp32, C = 64
+ * and shorter sequences run the CUDA-core flash kernel.  C in {64, 128, 256}. */
 int ditsep_attention(const void* q, const void* k, const void* v, int dtype, int B, int S, int C, int ld_qkv,
                      void* o, int ld_o, void* stream);
 

@@ -125,7 +125,9 @@ def stft_compress(xt, mix, window, feat, exponent, factor, affine):
     z = F.pad(x.reshape(B * C, T), (255, 255 + 382))
     s = torch.stft(z, 510, hop_length=128, win_length=510, window=window, center=False, onesided=True,
                    return_complex=True).reshape(B, C, 256, -1)
-    if exponent != 1:
+    if exponent == 0:
+        s = torch.log1p(s.abs()) * torch.exp(1j * s.angle())
+    elif exponent != 1:
         s = s.abs() ** exponent * torch.exp(1j * s.angle())
     s = s * factor
     f = torch.cat((s.real, s.imag), dim=1)  # (B, 2C, 256, frames)
@@ -140,7 +142,9 @@ def expand_istft(spec, window, out, exponent, factor):
     frames = 1 + (T + 382) // 128
     s = spec[:, :, :frames, :].permute(0, 3, 1, 2)  # (B, 2n, 256, frames)
     c = torch.complex(s[:, :n].contiguous(), s[:, n:].contiguous()) / abs(factor)
-    if exponent != 1:
+    if exponent == 0:
+        c = (torch.exp(c.abs()) - 1) * torch.exp(1j * c.angle())
+    elif exponent != 1:
         c = c.abs() ** (1 / exponent) * torch.exp(1j * c.angle())
     y = torch.istft(c.reshape(B * n, 256, frames), 510, hop_length=128, win_length=510, window=window, center=True,
                     onesided=True).reshape(B, n, -1)

@@ -136,6 +136,30 @@ def test_expand_istft(B, n_src, T):
     assert rel(out, ref) < 2e-5, rel(out, ref)
 
 
+def test_spectral_log_transform():
+    """transform="log" (score_models.py:49-51,66-68): exponent 0 in the C ABI = log1p(|X|) e^{j arg X} |factor| and back."""
+    B, n_src, T = 2, 2, 7810
+    xt, mix = torch.randn(B, n_src, T, generator=g(8)), torch.randn(B, 1, T, generator=g(9))
+    win = torch.hann_window(510)
+    frames = 1 + (T + 382) // 128
+    W = (frames + 63) // 64 * 64
+    ref = torch.empty(B, 256, W, 2 * (n_src + 1))
+    E.stft_compress(xt, mix, win, ref, 0.0, 0.15, False)
+    out = torch.empty(B, 256, W, 2 * (n_src + 1), device=DEV)
+    ops.stft_compress(xt.to(DEV), mix.to(DEV), win.to(DEV), out, 0.0, 0.15, False)
+    assert rel(out, ref) < 2e-5, rel(out, ref)
+    spec = 0.1 * torch.randn(B, 256, W, 2 * n_src, generator=g(10))
+    back_ref = torch.empty(B, n_src, T)
+    E.expand_istft(spec, win, back_ref, 0.0, 0.15)
+    back = torch.empty(B, n_src, T, device=DEV)
+    ops.expand_istft(spec.to(DEV), win.to(DEV), back, 0.0, 0.15)
+    assert rel(back, back_ref) < 2e-5, rel(back, back_ref)
+    # round trip through both kernels: expand(compress(x)) == x
+    rt = torch.empty(B, n_src, T, device=DEV)
+    ops.expand_istft(out[..., [0, 1, 3, 4]].contiguous(), win.to(DEV), rt, 0.0, 0.15)
+    assert rel(rt, xt) < 1e-4
+
+
 def test_stft_roundtrip_full_size():
     """size-independent property at the benchmark shape: iSTFT(expand(compress(STFT(x)))) == x."""
     B, n, T = 32, 2, 32000
