@@ -17,7 +17,7 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 BUILD = os.path.join(HERE, "_build")
 LIB = os.path.join(HERE, "libditsep_b200.so")
-SOURCES = ["lib.cu", "pc_step.cu", "spectral.cu", "norm_fir.cu", "conv_direct.cu", "attention.cu", "conv_tc.cu"]
+SOURCES = ["lib.cu", "pc_step.cu", "spectral.cu", "norm_fir.cu", "conv_direct.cu", "attention.cu", "conv_tc.cu", "conv1d.cu"]
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-O3", "-lineinfo", "-std=c++17", "-Xcompiler", "-fPIC",
               "--expt-relaxed-constexpr", "-Xptxas", "-v"] + os.environ.get("DITSEP_NVCC_EXTRA", "").split()
 

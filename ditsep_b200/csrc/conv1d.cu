@@ -1,0 +1,327 @@
+// 1-D convolutions of the Oobleck VAE (LatentDiffSep.encode / decode, src/diffsep_latent.py:107-128, over
+// stable_audio_tools/models/autoencoders.py:59-85,228-357) on the tensor cores (tcgen05 / TMEM, TMA-fed implicit GEMM),
+// plus the two one-channel end convolutions and the VAE bottleneck on CUDA cores.
+//
+// Activations are [B][T][C] bf16 (time-major, channels contiguous = the GEMM K axis).  ONE kernel covers the network's
+// three convolution forms through a "view factor" s of the input, [B][T][C] read as [B][T/s][s*C] (a free reshape of
+// a dense tensor):
+//   * dilated k = 7 and k = 1 / 3 convolutions (s = 1): tap k reads row t + k*d - p;
+//   * strided convolutions (kernel 2s, stride s, padding s/2; EncoderBlock :241-242): x[t*s + k - p] = X[t + m][r*C + c]
+//     with k - p = s*m + r -- three row shifts m = -1, 0, 1 over channel ranges of the view, no strided gather;
+//   * transposed convolutions (kernel 2s, stride s, padding s/2; DecoderBlock :262-264) as their polyphase form: output
+//     phase f of row j is x[j] w[f] + x[j-1] w[f+s], i.e. a 2-tap convolution (d = -1) with s*Cout output channels; the
+//     rows (j, f) flattened are the output shifted by the padding, so the consumer reads a VIEW of the buffer
+//     (batch stride and row offset are explicit everywhere).
+// GEMM view: M = 128 output rows of one signal, N = 128 output channels, K = taps * Cin walked in 64-channel blocks; per
+// block one TMA box of A (128 rows x 64 channels of the view) and one of the filter [Cout][taps*Cin]; fp32 accumulation
+// in TMEM; epilogue thread = output row: + bias, + residual, then the raw value and / or ELU of it (the next
+// convolution's input: the network's ELUs never cost a pass of their own), bf16 or fp32.
+#include <atomic>
+#include <cstdlib>
+
+#include "tc_ptx.cuh"
+
+namespace ditsep {
+
+constexpr int kC1Stages = 5;
+constexpr int kC1Threads = 192;   // warp 0: TMA, warp 1: TMEM + MMA, warps 2-5: epilogue (TMEM lane quadrant = warp & 3)
+constexpr int kC1BN = 128;
+
+struct Conv1dParams {
+  int B, T_out, Cin, Cout, taps, dil, pad, s;  // s: view factor (rows of the view = T / s, channels = s * Cin)
+  const float* bias;                           // nullable, [Cout]
+  const bf16* residual;                        // nullable, rows ld_res apart, signals bs_res apart
+  int ld_res;
+  int64_t bs_res;
+  void* out;                                   // nullable: the raw result
+  void* out_act;                               // nullable: ELU of it
+  int out_f32;                                 // 1: out is fp32 (out_act stays bf16)
+  int ld_out;
+  int64_t bs_out;                              // elements between signals of out / out_act
+};
+
+__device__ __forceinline__ float elu_f(float x) { return x > 0.f ? x : expm1f(x); }
+
+__global__ void __launch_bounds__(kC1Threads) conv1d_tc_kernel(const __grid_constant__ CUtensorMap mapA,
+                                                               const __grid_constant__ CUtensorMap mapW,
+                                                               const Conv1dParams p) {
+  extern __shared__ uint8_t smem_raw[];
+  __shared__ __align__(8) uint64_t bar_full[kC1Stages], bar_empty[kC1Stages], bar_accum;
+  __shared__ uint32_t tmem_slot;
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const uint32_t ring = (smem_u32(smem_raw) + 1023u) & ~1023u;
+  constexpr uint32_t kA = 128 * 128, kStage = kA + kC1BN * 128;
+  const int tiles_t = (p.T_out + 127) / 128;
+  const int b = blockIdx.x / tiles_t, t0 = (blockIdx.x - b * tiles_t) * 128;
+  const int n0 = blockIdx.y * kC1BN;
+  const int kc_per_tap = p.Cin / 64, num_kb = p.taps * kc_per_tap;
+
+  if (threadIdx.x == 0) {
+    for (int s = 0; s < kC1Stages; ++s) {
+      mbar_init(smem_u32(&bar_full[s]), 1);
+      mbar_init(smem_u32(&bar_empty[s]), 1);
+    }
+    mbar_init(smem_u32(&bar_accum), 1);
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  if (warp == 1) tmem_alloc(smem_u32(&tmem_slot), (uint32_t)kC1BN);
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem = tmem_slot;
+
+  if (warp == 0) {
+    if (lane == 0) {
+      for (int kb = 0; kb < num_kb; ++kb) {
+        const int st = kb % kC1Stages;
+        mbar_wait(smem_u32(&bar_empty[st]), (((uint32_t)(kb / kC1Stages)) & 1u) ^ 1u);
+        const int k = kb / kc_per_tap, ci0 = (kb - k * kc_per_tap) * 64;
+        // tap k reads input sample t*s + q, q = k*d - p = s*m + r (0 <= r < s): row t + m, channels [r*Cin + ci0, +64) of the view
+        const int q = k * p.dil - p.pad;
+        const int m = (q >= 0) ? q / p.s : -((-q + p.s - 1) / p.s);
+        const int r = q - m * p.s;
+        const uint32_t full = smem_u32(&bar_full[st]);
+        const uint32_t dst = ring + (uint32_t)st * kStage;
+        mbar_expect_tx(full, kStage);
+        tma_load_3d(dst, &mapA, full, r * p.Cin + ci0, t0 + m, b);   // rows outside [0, T/s) are zero-filled: the padding
+        tma_load_2d(dst + kA, &mapW, full, kb * 64, n0);
+      }
+    }
+  } else if (warp == 1) {
+    if (lane == 0) {
+      const uint32_t idesc = (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(kC1BN >> 3) << 17) | ((uint32_t)(128 >> 4) << 24);
+      for (int kb = 0; kb < num_kb; ++kb) {
+        const int st = kb % kC1Stages;
+        mbar_wait(smem_u32(&bar_full[st]), ((uint32_t)(kb / kC1Stages)) & 1u);
+        tc_fence_after();
+        const uint32_t a = ring + (uint32_t)st * kStage;
+        const uint64_t da = make_sw128_desc(a), db = make_sw128_desc(a + kA);
+#pragma unroll
+        for (int kk = 0; kk < 4; ++kk) umma_bf16(tmem, da + (uint64_t)(2 * kk), db + (uint64_t)(2 * kk), idesc, (kb | kk) != 0);
+        umma_commit(smem_u32(&bar_empty[st]));
+      }
+      umma_commit(smem_u32(&bar_accum));
+    }
+  } else {
+    const int qd = warp & 3;
+    const int t = t0 + qd * 32 + lane;
+    const bool valid = t < p.T_out;
+    mbar_wait_sleep(smem_u32(&bar_accum), 0);
+    tc_fence_after();
+    const uint32_t lane_addr = tmem + ((uint32_t)(qd * 32) << 16);
+    const int64_t row_o = (int64_t)b * p.bs_out + (int64_t)t * p.ld_out;
+    const bf16* res = p.residual ? p.residual + (int64_t)b * p.bs_res + (int64_t)t * p.ld_res : nullptr;
+#pragma unroll 1
+    for (int c0 = 0; c0 < kC1BN; c0 += 16) {
+      uint32_t v[16];
+      tmem_ld16(lane_addr + (uint32_t)c0, v);
+      const int co = n0 + c0;
+      if (!valid || co >= p.Cout) continue;
+#pragma unroll
+      for (int h = 0; h < 2; ++h) {  // two packs of 8 channels
+        const int c = co + 8 * h;
+        float f[8];
+#pragma unroll
+        for (int j = 0; j < 8; ++j) f[j] = __uint_as_float(v[8 * h + j]);
+        if (p.bias) {
+          const float4 b0 = __ldg(reinterpret_cast<const float4*>(p.bias + c));
+          const float4 b1 = __ldg(reinterpret_cast<const float4*>(p.bias + c + 4));
+          f[0] += b0.x; f[1] += b0.y; f[2] += b0.z; f[3] += b0.w;
+          f[4] += b1.x; f[5] += b1.y; f[6] += b1.z; f[7] += b1.w;
+        }
+        if (res) {
+          float r8[8];
+          Pack8<bf16>::load(res + c, r8);
+#pragma unroll
+          for (int j = 0; j < 8; ++j) f[j] += r8[j];
+        }
+        if (p.out) {
+          if (p.out_f32) Pack8<float>::store(reinterpret_cast<float*>(p.out) + row_o + c, f);
+          else Pack8<bf16>::store(reinterpret_cast<bf16*>(p.out) + row_o + c, f);
+        }
+        if (p.out_act) {
+          // ELU of the value AS STORED (bf16-rounded when the raw output is bf16): what a separate pass over `out` would see
+          float a[8];
+#pragma unroll
+          for (int j = 0; j < 8; ++j) a[j] = elu_f(p.out_f32 || !p.out ? f[j] : __bfloat162float(__float2bfloat16_rn(f[j])));
+          Pack8<bf16>::store(reinterpret_cast<bf16*>(p.out_act) + row_o + c, a);
+        }
+      }
+    }
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 1) {
+    tc_fence_after();
+    tmem_dealloc(tmem, (uint32_t)kC1BN);
+  }
+}
+
+// ---- the one-channel ends and the bottleneck (CUDA cores: 7 MACs per output) ---------------------------------------------
+// first layer: (B, T) fp32 -> [B][T][C] bf16 raw + ELU; w [C][7], bias [C]
+__global__ void __launch_bounds__(256) conv1d_in_kernel(const float* __restrict__ x, const float* __restrict__ w,
+                                                        const float* __restrict__ bias, bf16* __restrict__ out,
+                                                        bf16* __restrict__ out_act, int T, int C) {
+  const int b = blockIdx.y;
+  const int64_t n = (int64_t)T * (C / 8);
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
+    const int cv = (int)(i % (C / 8)), t = (int)(i / (C / 8));
+    float xs[7];
+#pragma unroll
+    for (int k = 0; k < 7; ++k) {
+      const int tt = t + k - 3;
+      xs[k] = (tt >= 0 && tt < T) ? x[(int64_t)b * T + tt] : 0.f;
+    }
+    float f[8], a[8];
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+      const int c = cv * 8 + j;
+      float acc = bias ? bias[c] : 0.f;
+#pragma unroll
+      for (int k = 0; k < 7; ++k) acc = fmaf(w[c * 7 + k], xs[k], acc);
+      f[j] = acc;
+      a[j] = elu_f(__bfloat162float(__float2bfloat16_rn(acc)));
+    }
+    const int64_t o = ((int64_t)b * T + t) * C + cv * 8;
+    Pack8<bf16>::store(out + o, f);
+    Pack8<bf16>::store(out_act + o, a);
+  }
+}
+
+// last layer: ELU'd [B][T][C] bf16 (rows ld apart, signals bs apart) -> tanh(conv7) (B, T) fp32; w [7][C], no bias.
+// One warp per output sample: lanes split the channels, 7 taps each, shuffle reduction.
+__global__ void __launch_bounds__(256) conv1d_out_kernel(const bf16* __restrict__ x, int ld, int64_t bs,
+                                                         const float* __restrict__ w, float* __restrict__ out, int T, int C,
+                                                         int final_tanh) {
+  const int b = blockIdx.y, lane = threadIdx.x & 31;
+  const int wpb = blockDim.x >> 5;
+  for (int t = blockIdx.x * wpb + (threadIdx.x >> 5); t < T; t += gridDim.x * wpb) {
+    float acc = 0.f;
+    for (int k = 0; k < 7; ++k) {
+      const int tt = t + k - 3;
+      if (tt < 0 || tt >= T) continue;
+      const bf16* row = x + (int64_t)b * bs + (int64_t)tt * ld;
+      for (int c = lane * 2; c < C; c += 64) {
+        const __nv_bfloat162 v = *reinterpret_cast<const __nv_bfloat162*>(row + c);
+        acc = fmaf(__low2float(v), w[k * C + c], acc);
+        acc = fmaf(__high2float(v), w[k * C + c + 1], acc);
+      }
+    }
+    acc = warp_sum(acc);
+    if (lane == 0) out[(int64_t)b * T + t] = final_tanh ? tanhf(acc) : acc;
+  }
+}
+
+// VAE bottleneck (bottleneck.py:57-65): pre [B][T][2L] fp32 (mean | scale) + noise (B, L, T) fp32 -> z (B, L, T) fp32
+__global__ void vae_sample_kernel(const float* __restrict__ pre, const float* __restrict__ noise, float* __restrict__ z,
+                                  int T, int L, int64_t n) {
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
+    const int t = (int)(i % T), l = (int)((i / T) % L);
+    const int64_t b = i / ((int64_t)T * L);
+    const float* row = pre + (b * T + t) * (2 * L);
+    const float sc = row[L + l];
+    const float sp = sc > 20.f ? sc : log1pf(expf(sc));  // softplus (torch threshold 20)
+    z[i] = noise[i] * (sp + 1e-4f) + row[l];
+  }
+}
+
+typedef CUresult (*C1EncodeFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*,
+                               const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
+                               CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+static C1EncodeFn c1_encode_fn() {
+  static C1EncodeFn fn = nullptr;
+  if (fn) return fn;
+  void* sym = nullptr;
+  cudaDriverEntryPointQueryResult qres;
+  if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &sym, cudaEnableDefault, &qres) != cudaSuccess ||
+      qres != cudaDriverEntryPointSuccess)
+    return nullptr;
+  fn = reinterpret_cast<C1EncodeFn>(sym);
+  return fn;
+}
+
+}  // namespace ditsep
+
+using namespace ditsep;
+
+extern "C" int ditsep_conv1d_tc(const void* x, int B, int T_in, int Cin, int64_t bs_in, const void* w_bf16, int Cout, int taps,
+                                int dil, int pad, int s_view, int T_out, const float* bias, const void* residual, int ld_res,
+                                int64_t bs_res, void* out, void* out_act, int out_f32, int ld_out, int64_t bs_out,
+                                void* stream) {
+  DITSEP_REQUIRE(x && w_bf16 && (out || out_act), "conv1d_tc: null pointer");
+  DITSEP_REQUIRE(B > 0 && T_in > 0 && T_out > 0 && taps >= 1, "conv1d_tc: empty problem");
+  DITSEP_REQUIRE(Cin % 64 == 0 && Cout % 16 == 0, "conv1d_tc: Cin=%d must be a multiple of 64, Cout=%d of 16", Cin, Cout);
+  DITSEP_REQUIRE(s_view >= 1 && T_in % s_view == 0, "conv1d_tc: T_in=%d must be a multiple of the view factor %d", T_in, s_view);
+  DITSEP_REQUIRE(ld_out % 8 == 0 && (!residual || ld_res % 8 == 0) && bs_in % 8 == 0 && bs_out % 8 == 0,
+                 "conv1d_tc: strides must be multiples of 8 elements");
+  DITSEP_REQUIRE(((reinterpret_cast<uintptr_t>(x) | reinterpret_cast<uintptr_t>(w_bf16) | reinterpret_cast<uintptr_t>(out) |
+                   reinterpret_cast<uintptr_t>(out_act) | reinterpret_cast<uintptr_t>(residual)) & 15) == 0,
+                 "conv1d_tc: operands must be 16-byte aligned");
+  C1EncodeFn enc = c1_encode_fn();
+  DITSEP_REQUIRE(enc != nullptr, "conv1d_tc: cuTensorMapEncodeTiled not available from the driver");
+  CUtensorMap mapA, mapW;
+  {
+    cuuint64_t gdim[3] = {(cuuint64_t)s_view * Cin, (cuuint64_t)(T_in / s_view), (cuuint64_t)B};
+    cuuint64_t gstr[2] = {(cuuint64_t)s_view * Cin * 2, (cuuint64_t)bs_in * 2};
+    cuuint32_t box[3] = {64u, 128u, 1u}, estr[3] = {1, 1, 1};
+    CUresult r = enc(&mapA, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 3, const_cast<void*>(x), gdim, gstr, box, estr,
+                     CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                     CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    DITSEP_REQUIRE(r == CUDA_SUCCESS, "conv1d_tc: cuTensorMapEncodeTiled(activations) failed with %d", (int)r);
+  }
+  {
+    const int K = taps * Cin;
+    const int cout_pad = (Cout + kC1BN - 1) / kC1BN * kC1BN;
+    (void)cout_pad;
+    cuuint64_t gdim[2] = {(cuuint64_t)K, (cuuint64_t)Cout};
+    cuuint64_t gstr[1] = {(cuuint64_t)K * 2};
+    cuuint32_t box[2] = {64u, (cuuint32_t)kC1BN}, estr[2] = {1, 1};
+    CUresult r = enc(&mapW, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void*>(w_bf16), gdim, gstr, box, estr,
+                     CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                     CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    DITSEP_REQUIRE(r == CUDA_SUCCESS, "conv1d_tc: cuTensorMapEncodeTiled(filter) failed with %d", (int)r);
+  }
+  Conv1dParams p{};
+  p.B = B; p.T_out = T_out; p.Cin = Cin; p.Cout = Cout; p.taps = taps; p.dil = dil; p.pad = pad; p.s = s_view;
+  p.bias = bias; p.residual = reinterpret_cast<const bf16*>(residual); p.ld_res = ld_res; p.bs_res = bs_res;
+  p.out = out; p.out_act = out_act; p.out_f32 = out_f32; p.ld_out = ld_out; p.bs_out = bs_out;
+  const size_t smem = 1024 + (size_t)kC1Stages * (128 * 128 + kC1BN * 128);
+  static std::atomic<bool> attr_set[64];
+  int dev = 0;
+  DITSEP_CUDA(cudaGetDevice(&dev));
+  if (dev < 0 || dev >= 64 || !attr_set[dev].load(std::memory_order_acquire)) {
+    DITSEP_CUDA(cudaFuncSetAttribute(conv1d_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    if (dev >= 0 && dev < 64) attr_set[dev].store(true, std::memory_order_release);
+  }
+  dim3 grid((unsigned)(((T_out + 127) / 128) * B), (unsigned)((Cout + kC1BN - 1) / kC1BN));
+  conv1d_tc_kernel<<<grid, kC1Threads, smem, (cudaStream_t)stream>>>(mapA, mapW, p);
+  return check_launch("conv1d_tc_kernel");
+}
+
+extern "C" int ditsep_conv1d_in(const float* x, const float* w, const float* bias, void* out, void* out_act, int B, int T,
+                                int C, void* stream) {
+  DITSEP_REQUIRE(x && w && out && out_act && B > 0 && T > 0 && C % 8 == 0, "conv1d_in: bad arguments");
+  int64_t n = (int64_t)T * (C / 8);
+  int gx = (int)((n + 255) / 256);
+  if (gx > kNumSMs * 8) gx = kNumSMs * 8;
+  conv1d_in_kernel<<<dim3(gx, B), 256, 0, (cudaStream_t)stream>>>(x, w, bias, (bf16*)out, (bf16*)out_act, T, C);
+  return check_launch("conv1d_in_kernel");
+}
+
+extern "C" int ditsep_conv1d_out(const void* x, int ld, int64_t bs, const float* w, float* out, int B, int T, int C,
+                                 int final_tanh, void* stream) {
+  DITSEP_REQUIRE(x && w && out && B > 0 && T > 0 && C % 64 == 0, "conv1d_out: bad arguments");
+  int gx = (T + 7) / 8;
+  if (gx > kNumSMs * 16) gx = kNumSMs * 16;
+  conv1d_out_kernel<<<dim3(gx, B), 256, 0, (cudaStream_t)stream>>>((const bf16*)x, ld, bs, w, out, T, C, final_tanh);
+  return check_launch("conv1d_out_kernel");
+}
+
+extern "C" int ditsep_vae_sample(const float* pre, const float* noise, float* z, int B, int T, int L, void* stream) {
+  DITSEP_REQUIRE(pre && noise && z && B > 0 && T > 0 && L > 0, "vae_sample: bad arguments");
+  const int64_t n = (int64_t)B * T * L;
+  int gx = (int)((n + 255) / 256);
+  if (gx > kNumSMs * 8) gx = kNumSMs * 8;
+  vae_sample_kernel<<<gx, 256, 0, (cudaStream_t)stream>>>(pre, noise, z, T, L, n);
+  return check_launch("vae_sample_kernel");
+}

@@ -387,6 +387,48 @@ class ConvTcPlan:
             self._h = None
 
 
+# ------------------------------------------------------------------ Oobleck VAE (1-D convolutions)
+def conv1d_tc(x, T_in: int, bs_in: int, w_bf16, Cout: int, taps: int, dil: int, pad: int, s_view: int, T_out: int, bias=None,
+              residual=None, ld_res: int = 0, bs_res: int = 0, out=None, out_act=None, ld_out: int = 0, bs_out: int = 0):
+    """ditsep_conv1d_tc on explicit views: x / residual / out / out_act are bf16 (out may be fp32) tensors whose data_ptr is
+    the view's first row; rows are ld apart (x: dense, ld = Cin), signals bs apart.  See include/ditsep_b200.h."""
+    _cuda(x, w_bf16, bias, residual, out, out_act)
+    B = x.shape[0]
+    Cin = w_bf16.shape[1] // taps
+    if x.dtype != torch.bfloat16 or w_bf16.dtype != torch.bfloat16 or not w_bf16.is_contiguous():
+        raise _lib.DitsepError("conv1d_tc: bf16 activations and packed bf16 weights required")
+    out_f32 = int(out is not None and out.dtype == torch.float32)
+    check(_lib.load().ditsep_conv1d_tc(_ptr(x), B, T_in, Cin, bs_in, _ptr(w_bf16), Cout, taps, dil, pad, s_view, T_out,
+                                       _ptr(bias), _ptr(residual), ld_res, bs_res, _ptr(out), _ptr(out_act), out_f32, ld_out,
+                                       bs_out, _stream()), "conv1d_tc")
+
+
+def conv1d_in(x, w, bias, out, out_act):
+    """x (B, T) f32 -> conv7 (1 -> C) -> out / ELU(out), [B][T][C] bf16."""
+    _cuda(x, w, bias, out, out_act)
+    _f32c(x, "x")
+    B, T = x.shape
+    check(_lib.load().ditsep_conv1d_in(_ptr(x), _ptr(w), _ptr(bias), _ptr(out), _ptr(out_act), B, T, out.shape[-1], _stream()),
+          "conv1d_in")
+
+
+def conv1d_out(x, T: int, ld: int, bs: int, w, out, final_tanh: bool = True):
+    """ELU'd activations (view: rows ld, signals bs apart) -> conv7 (C -> 1) -> tanh -> out (B, T) f32."""
+    _cuda(x, w, out)
+    _f32c(out, "out")
+    check(_lib.load().ditsep_conv1d_out(_ptr(x), ld, bs, _ptr(w), _ptr(out), out.shape[0], T, w.shape[1], int(final_tanh),
+                                        _stream()), "conv1d_out")
+
+
+def vae_sample(pre, noise, z):
+    """pre [B][T][2L] f32 (mean | scale), noise / z (B, L, T) f32: z = noise * (softplus(scale) + 1e-4) + mean."""
+    _cuda(pre, noise, z)
+    for n, v in (("pre", pre), ("noise", noise), ("z", z)):
+        _f32c(v, n)
+    B, L, T = z.shape
+    check(_lib.load().ditsep_vae_sample(_ptr(pre), _ptr(noise), _ptr(z), B, T, L, _stream()), "vae_sample")
+
+
 # ------------------------------------------------------------------ attention / temb / output
 def attention(q, k, v, o):
     """q,k,v,o: NHWC views (B,H,W,C) sharing one pixel stride for q/k/v."""

@@ -232,6 +232,34 @@ void ditsep_debug_conv_trace(void* buf);
 int ditsep_attention(const void* q, const void* k, const void* v, int dtype, int B, int S, int C, int ld_qkv,
                      void* o, int ld_o, void* stream);
 
+/* ---- Oobleck VAE ------------------------------------------------------
+ * 1-D convolutions of LatentDiffSep.encode / decode (src/diffsep_latent.py:107-128; OobleckEncoder / OobleckDecoder,
+ * stable_audio_tools/models/autoencoders.py:59-85,228-357) on the tensor cores.  x: [B][T_in][Cin] bf16, DENSE rows
+ * (ld = Cin), signals bs_in elements apart; w_bf16: [Cout][taps * Cin] (tap-major); tap k reads input sample
+ * t * s_view + k * dil - pad (zero outside [0, T_in)), for t in [0, T_out).  The three forms of the network:
+ *   dilated / plain convolution:   s_view 1, taps 7 / 3 / 1, dil d, pad d * (taps - 1) / 2, T_out = T_in
+ *   strided (kernel 2s, stride s): s_view s, taps 2s, dil 1, pad s / 2, T_out = T_in / s
+ *   transposed (kernel 2s, stride s, padding s / 2) in polyphase form: s_view 1, taps 2, dil -1, pad 0, T_out = T_in + 1,
+ *     Cout = s * C with w[f * C + co][m * Cin + ci] = W[ci][co][f + s * m]; the buffer's rows (j, f), flattened, are the
+ *     output delayed by s / 2 samples: the consumer reads it from row s / 2 on (bs = (T_in + 1) * s * C).
+ * Epilogue: + bias[Cout] (nullable) + residual (nullable, bf16, rows ld_res / signals bs_res apart); `out` (nullable)
+ * receives the value (bf16, or fp32 when out_f32), `out_act` (nullable) ELU of it in bf16 -- the next convolution's
+ * input, so the network's ELUs cost no pass of their own.  Rows ld_out, signals bs_out elements apart. */
+int ditsep_conv1d_tc(const void* x, int B, int T_in, int Cin, int64_t bs_in, const void* w_bf16, int Cout, int taps,
+                     int dil, int pad, int s_view, int T_out, const float* bias, const void* residual, int ld_res,
+                     int64_t bs_res, void* out, void* out_act, int out_f32, int ld_out, int64_t bs_out, void* stream);
+/* OobleckEncoder's first layer: x (B, T) fp32 -> conv7 (1 -> C channels, w [C][7], bias [C]) -> out, out_act = ELU(out),
+ * both [B][T][C] bf16. */
+int ditsep_conv1d_in(const float* x, const float* w, const float* bias, void* out, void* out_act, int B, int T, int C,
+                     void* stream);
+/* OobleckDecoder's last layer: x = ELU'd activations [B][T][C] bf16 (rows ld, signals bs apart) -> conv7 (C -> 1, w [7][C],
+ * no bias) -> tanh (when final_tanh) -> out (B, T) fp32. */
+int ditsep_conv1d_out(const void* x, int ld, int64_t bs, const float* w, float* out, int B, int T, int C, int final_tanh,
+                      void* stream);
+/* VAEBottleneck.encode (bottleneck.py:57-65): pre [B][T][2L] fp32 = (mean | scale), noise (B, L, T) fp32 ->
+ * z (B, L, T) = noise * (softplus(scale) + 1e-4) + mean. */
+int ditsep_vae_sample(const float* pre, const float* noise, float* z, int B, int T, int L, void* stream);
+
 /* ---- time embedding ---------------------------------------------------------------------
  * ncsnpp.py:325-346 + layerspp.py:44-46: act_temb = SiLU(Linear2(SiLU(Linear1(
  * [sin, cos](2 pi W log t))))) -- the SiLU every res-block applies before Dense_0

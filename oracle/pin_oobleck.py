@@ -72,7 +72,7 @@ def main():
     golden = {}
     # (name, channels, c_mults, strides, encoder latent (mean | scale), samples): a small net with all five stages, and
     # the real oobleck_finetune.json widths (128 .. 2048 channels) on a short signal
-    for name, ch, cm, st, lat, T in (("small", 64, [1, 2, 2], [2, 4, 8], 32, 3000),
+    for name, ch, cm, st, lat, T in (("small", 64, [1, 2, 2], [2, 4, 8], 128, 3000),
                                      ("real", 128, [1, 2, 4, 8, 16], [2, 4, 4, 8, 8], 128, 4096)):
         torch.manual_seed(0)
         enc = A.OobleckEncoder(in_channels=1, channels=ch, c_mults=cm, strides=st, latent_dim=lat).eval()
