@@ -29,6 +29,7 @@ constexpr int kC1BN = 128;
 
 struct Conv1dParams {
   int B, T_out, Cin, Cout, taps, dil, pad, s;  // s: view factor (rows of the view = T / s, channels = s * Cin)
+  int bt, bb;                                  // M tile = bt output rows of bb consecutive signals (bt * bb == 128)
   const float* bias;                           // nullable, [Cout]
   const bf16* residual;                        // nullable, rows ld_res apart, signals bs_res apart
   int ld_res;
@@ -51,8 +52,9 @@ __global__ void __launch_bounds__(kC1Threads) conv1d_tc_kernel(const __grid_cons
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const uint32_t ring = (smem_u32(smem_raw) + 1023u) & ~1023u;
   constexpr uint32_t kA = 128 * 128, kStage = kA + kC1BN * 128;
-  const int tiles_t = (p.T_out + 127) / 128;
-  const int b = blockIdx.x / tiles_t, t0 = (blockIdx.x - b * tiles_t) * 128;
+  // short signals (the deep levels: 16 rows per signal) share an M tile: bt rows of bb consecutive signals
+  const int tiles_t = (p.T_out + p.bt - 1) / p.bt;
+  const int b0 = (blockIdx.x / tiles_t) * p.bb, t0 = (blockIdx.x % tiles_t) * p.bt;
   const int n0 = blockIdx.y * kC1BN;
   const int kc_per_tap = p.Cin / 64, num_kb = p.taps * kc_per_tap;
 
@@ -83,7 +85,7 @@ __global__ void __launch_bounds__(kC1Threads) conv1d_tc_kernel(const __grid_cons
         const uint32_t full = smem_u32(&bar_full[st]);
         const uint32_t dst = ring + (uint32_t)st * kStage;
         mbar_expect_tx(full, kStage);
-        tma_load_3d(dst, &mapA, full, r * p.Cin + ci0, t0 + m, b);   // rows outside [0, T/s) are zero-filled: the padding
+        tma_load_3d(dst, &mapA, full, r * p.Cin + ci0, t0 + m, b0);  // rows outside [0, T/s) are zero-filled: the padding
         tma_load_2d(dst + kA, &mapW, full, kb * 64, n0);
       }
     }
@@ -104,8 +106,9 @@ __global__ void __launch_bounds__(kC1Threads) conv1d_tc_kernel(const __grid_cons
     }
   } else {
     const int qd = warp & 3;
-    const int t = t0 + qd * 32 + lane;
-    const bool valid = t < p.T_out;
+    const int row = qd * 32 + lane;
+    const int b = b0 + row / p.bt, t = t0 + row % p.bt;
+    const bool valid = t < p.T_out && b < p.B;
     mbar_wait_sleep(smem_u32(&bar_accum), 0);
     tc_fence_after();
     const uint32_t lane_addr = tmem + ((uint32_t)(qd * 32) << 16);
@@ -259,11 +262,14 @@ extern "C" int ditsep_conv1d_tc(const void* x, int B, int T_in, int Cin, int64_t
                  "conv1d_tc: operands must be 16-byte aligned");
   C1EncodeFn enc = c1_encode_fn();
   DITSEP_REQUIRE(enc != nullptr, "conv1d_tc: cuTensorMapEncodeTiled not available from the driver");
+  int bt = 128;
+  while (bt > 8 && bt / 2 >= T_out) bt /= 2;   // smallest power of two >= T_out, at least 8
+  const int bb = 128 / bt;
   CUtensorMap mapA, mapW;
   {
     cuuint64_t gdim[3] = {(cuuint64_t)s_view * Cin, (cuuint64_t)(T_in / s_view), (cuuint64_t)B};
     cuuint64_t gstr[2] = {(cuuint64_t)s_view * Cin * 2, (cuuint64_t)bs_in * 2};
-    cuuint32_t box[3] = {64u, 128u, 1u}, estr[3] = {1, 1, 1};
+    cuuint32_t box[3] = {64u, (cuuint32_t)bt, (cuuint32_t)bb}, estr[3] = {1, 1, 1};
     CUresult r = enc(&mapA, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 3, const_cast<void*>(x), gdim, gstr, box, estr,
                      CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
                      CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
@@ -283,6 +289,7 @@ extern "C" int ditsep_conv1d_tc(const void* x, int B, int T_in, int Cin, int64_t
   }
   Conv1dParams p{};
   p.B = B; p.T_out = T_out; p.Cin = Cin; p.Cout = Cout; p.taps = taps; p.dil = dil; p.pad = pad; p.s = s_view;
+  p.bt = bt; p.bb = bb;
   p.bias = bias; p.residual = reinterpret_cast<const bf16*>(residual); p.ld_res = ld_res; p.bs_res = bs_res;
   p.out = out; p.out_act = out_act; p.out_f32 = out_f32; p.ld_out = ld_out; p.bs_out = bs_out;
   const size_t smem = 1024 + (size_t)kC1Stages * (128 * 128 + kC1BN * 128);
@@ -293,7 +300,7 @@ extern "C" int ditsep_conv1d_tc(const void* x, int B, int T_in, int Cin, int64_t
     DITSEP_CUDA(cudaFuncSetAttribute(conv1d_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     if (dev >= 0 && dev < 64) attr_set[dev].store(true, std::memory_order_release);
   }
-  dim3 grid((unsigned)(((T_out + 127) / 128) * B), (unsigned)((Cout + kC1BN - 1) / kC1BN));
+  dim3 grid((unsigned)(((T_out + bt - 1) / bt) * ((B + bb - 1) / bb)), (unsigned)((Cout + kC1BN - 1) / kC1BN));
   conv1d_tc_kernel<<<grid, kC1Threads, smem, (cudaStream_t)stream>>>(mapA, mapW, p);
   return check_launch("conv1d_tc_kernel");
 }

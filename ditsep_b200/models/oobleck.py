@@ -67,6 +67,7 @@ class OobleckVAE:
         self.hop_length = int(math.prod(strides))
         self.device = torch.device(device)
         self._w = None
+        self._plans = {}
 
     # ------------------------------------------------------------------ weights
     def load_state_dict(self, sd: Dict[str, torch.Tensor], strict: bool = True):
@@ -106,6 +107,7 @@ class OobleckVAE:
             if extra:
                 raise KeyError(f"OobleckVAE.load_state_dict: unexpected keys {extra[:4]} ...")
         self._w = w
+        self._plans = {}
         return self
 
     def _weights(self):
@@ -115,66 +117,50 @@ class OobleckVAE:
 
     # ------------------------------------------------------------------ building blocks ([B][T][C] bf16, views explicit)
     @staticmethod
-    def _conv(c: _Conv, x, T_in, bs_in, T_out, residual=None, res_geom=(0, 0), out=None, out_act=None, ld_out=0, bs_out=0):
-        ops.conv1d_tc(x, T_in, bs_in, c.w, c.cout, c.taps, c.dil, c.pad, c.s_view, T_out, bias=c.bias, residual=residual,
-                      ld_res=res_geom[0], bs_res=res_geom[1], out=out, out_act=out_act, ld_out=ld_out, bs_out=bs_out)
+    def _conv(plan, c: _Conv, x, T_in, bs_in, T_out, residual=None, res_geom=(0, 0), out=None, out_act=None, ld_out=0, bs_out=0):
+        plan.add(ops.conv1d_tc, x, T_in, bs_in, c.w, c.cout, c.taps, c.dil, c.pad, c.s_view, T_out, bias=c.bias,
+                 residual=residual, ld_res=res_geom[0], bs_res=res_geom[1], out=out, out_act=out_act, ld_out=ld_out,
+                 bs_out=bs_out)
 
-    def _res_units(self, w, tag, h, a, T, C, bs):
+    def _res_units(self, plan, w, tag, h, a, T, C, bs):
         """Three residual units (dilations 1, 3, 9) on the stream h with a = ELU(h), both views of rows C / signals bs
         apart: t = ELU(conv7_d(a)); h += conv1(t); a = ELU(h) -- all in the two convolutions' epilogues, in place."""
         B = h.shape[0]
         t = torch.empty(B, T, C, device=h.device, dtype=torch.bfloat16)
         for j in range(3):
-            self._conv(w[f"{tag}_ru{j}a"], a, T, bs, T, out_act=t, ld_out=C, bs_out=T * C)
-            self._conv(w[f"{tag}_ru{j}b"], t, T, T * C, T, residual=h, res_geom=(C, bs), out=h, out_act=a, ld_out=C, bs_out=bs)
+            self._conv(plan, w[f"{tag}_ru{j}a"], a, T, bs, T, out_act=t, ld_out=C, bs_out=T * C)
+            self._conv(plan, w[f"{tag}_ru{j}b"], t, T, T * C, T, residual=h, res_geom=(C, bs), out=h, out_act=a, ld_out=C,
+                       bs_out=bs)
 
-    # ------------------------------------------------------------------ encoder / bottleneck / decoder
-    @torch.no_grad()
-    def encode(self, audio: torch.Tensor, noise: Optional[torch.Tensor] = None, seed: int = 0,
-               skip_bottleneck: bool = False) -> torch.Tensor:
-        """AudioAutoencoder.encode (autoencoders.py:440-485) without pretransform: audio (B, 1, T), T a multiple of the hop.
-        noise: the bottleneck's randn draw (B, latent, T / hop) (parity runs); default: the library's Philox stream."""
-        w = self._weights()
-        ops.require_device(audio, "OobleckVAE.encode")
-        B, one, T = audio.shape
-        if one != 1 or T % self.hop_length:
-            raise ValueError(f"OobleckVAE.encode: (B, 1, T) with T a multiple of {self.hop_length}, got {tuple(audio.shape)}")
-        dev, C = audio.device, self.c_mults[0] * self.channels
+    # ------------------------------------------------------------------ launch plans (one per shape, CUDA-graph replayed)
+    def _encode_plan(self, B: int, T: int, dev):
+        w, plan = self._weights(), _Plan(dev)
+        C = self.c_mults[0] * self.channels
+        plan.x = torch.empty(B, T, device=dev, dtype=torch.float32)
         h = torch.empty(B, T, C, device=dev, dtype=torch.bfloat16)
         a = torch.empty_like(h)
-        ops.conv1d_in(audio.reshape(B, T).float().contiguous(), w["enc_in"][0], w["enc_in"][1], h, a)
+        plan.add(ops.conv1d_in, plan.x, w["enc_in"][0], w["enc_in"][1], h, a)
         for i, s in enumerate(self.strides):
-            self._res_units(w, f"enc{i}", h, a, T, C, T * C)
+            self._res_units(plan, w, f"enc{i}", h, a, T, C, T * C)
             Cn, Tn = self.c_mults[i + 1] * self.channels, T // s
             hn = torch.empty(B, Tn, Cn, device=dev, dtype=torch.bfloat16)
             an = torch.empty_like(hn)
-            self._conv(w[f"enc{i}_down"], a, T, T * C, Tn, out=hn, out_act=an, ld_out=Cn, bs_out=Tn * Cn)
+            self._conv(plan, w[f"enc{i}_down"], a, T, T * C, Tn, out=hn, out_act=an, ld_out=Cn, bs_out=Tn * Cn)
             h, a, T, C = hn, an, Tn, Cn
-        pre = torch.empty(B, T, self.enc_latent, device=dev, dtype=torch.float32)
-        self._conv(w["enc_out"], a, T, T * C, T, out=pre, ld_out=self.enc_latent, bs_out=T * self.enc_latent)
-        if skip_bottleneck:
-            return pre.permute(0, 2, 1).contiguous()
-        if noise is None:
-            noise = torch.empty(B, self.latent, T, device=dev, dtype=torch.float32)
-            ops.philox_normal(noise, seed, 0)
-        z = torch.empty(B, self.latent, T, device=dev, dtype=torch.float32)
-        ops.vae_sample(pre, noise.float().contiguous(), z)
-        return z
+        plan.pre = torch.empty(B, T, self.enc_latent, device=dev, dtype=torch.float32)
+        self._conv(plan, w["enc_out"], a, T, T * C, T, out=plan.pre, ld_out=self.enc_latent, bs_out=T * self.enc_latent)
+        plan.noise = torch.empty(B, self.latent, T, device=dev, dtype=torch.float32)
+        plan.z = torch.empty(B, self.latent, T, device=dev, dtype=torch.float32)
+        plan.add(ops.vae_sample, plan.pre, plan.noise, plan.z)
+        return plan
 
-    @torch.no_grad()
-    def decode(self, latents: torch.Tensor) -> torch.Tensor:
-        """AudioAutoencoder.decode (autoencoders.py:487-528): latents (B, latent, T') -> (B, 1, T' * hop)."""
-        w = self._weights()
-        ops.require_device(latents, "OobleckVAE.decode")
-        B, L, T = latents.shape
-        if L != self.latent:
-            raise ValueError(f"OobleckVAE.decode: {self.latent} latent channels expected, got {L}")
-        dev = latents.device
-        zin = latents.permute(0, 2, 1).contiguous().to(torch.bfloat16)            # [B][T'][latent]
-        C = self.c_mults[-1] * self.channels
+    def _decode_plan(self, B: int, T: int, dev):
+        w, plan = self._weights(), _Plan(dev)
+        L, C = self.latent, self.c_mults[-1] * self.channels
+        plan.zin = torch.empty(B, T, L, device=dev, dtype=torch.bfloat16)            # [B][T'][latent]
         h = torch.empty(B, T, C, device=dev, dtype=torch.bfloat16)
         a = torch.empty_like(h)
-        self._conv(w["dec_in"], zin, T, T * L, T, out=h, out_act=a, ld_out=C, bs_out=T * C)
+        self._conv(plan, w["dec_in"], plan.zin, T, T * L, T, out=h, out_act=a, ld_out=C, bs_out=T * C)
         bs = T * C
         for idx, i in enumerate(range(len(self.strides), 0, -1)):
             s, Cn = self.strides[i - 1], self.c_mults[i - 1] * self.channels
@@ -182,13 +168,90 @@ class OobleckVAE:
             # that starts s / 2 rows in (signals (T + 1) * s * Cn apart)
             hb = torch.empty(B, (T + 1) * s, Cn, device=dev, dtype=torch.bfloat16)
             ab = torch.empty_like(hb)
-            self._conv(w[f"dec{idx}_up"], a, T, bs, T + 1, out=hb, out_act=ab, ld_out=s * Cn, bs_out=(T + 1) * s * Cn)
+            self._conv(plan, w[f"dec{idx}_up"], a, T, bs, T + 1, out=hb, out_act=ab, ld_out=s * Cn, bs_out=(T + 1) * s * Cn)
             h, a = hb[:, s // 2:], ab[:, s // 2:]
             T, C, bs = T * s, Cn, (T + 1) * s * Cn
-            self._res_units(w, f"dec{idx}", h, a, T, C, bs)
-        out = torch.empty(B, T, device=dev, dtype=torch.float32)
-        ops.conv1d_out(a, T, C, bs, w["dec_out"], out, self.final_tanh)
-        return out[:, None, :]
+            self._res_units(plan, w, f"dec{idx}", h, a, T, C, bs)
+        plan.out = torch.empty(B, T, device=dev, dtype=torch.float32)
+        plan.add(ops.conv1d_out, a, T, C, bs, w["dec_out"], plan.out, self.final_tanh)
+        return plan
+
+    def _plan(self, kind: str, B: int, T: int, dev):
+        key = (kind, B, T, str(dev))
+        if key not in self._plans:
+            if len(self._plans) >= 8:  # a handful of shapes per run; drop the oldest rather than grow without bound
+                self._plans.pop(next(iter(self._plans)))
+            self._plans[key] = (self._encode_plan if kind == "enc" else self._decode_plan)(B, T, dev)
+        return self._plans[key]
+
+    # ------------------------------------------------------------------ encoder / bottleneck / decoder
+    @torch.no_grad()
+    def encode(self, audio: torch.Tensor, noise: Optional[torch.Tensor] = None, seed: int = 0,
+               skip_bottleneck: bool = False) -> torch.Tensor:
+        """AudioAutoencoder.encode (autoencoders.py:440-485) without pretransform: audio (B, 1, T), T a multiple of the hop.
+        noise: the bottleneck's randn draw (B, latent, T / hop) (parity runs); default: the library's Philox stream."""
+        ops.require_device(audio, "OobleckVAE.encode")
+        B, one, T = audio.shape
+        if one != 1 or T % self.hop_length:
+            raise ValueError(f"OobleckVAE.encode: (B, 1, T) with T a multiple of {self.hop_length}, got {tuple(audio.shape)}")
+        plan = self._plan("enc", B, T, audio.device)
+        plan.x.copy_(audio.reshape(B, T))
+        if noise is None:
+            ops.philox_normal(plan.noise, seed, 0)
+        else:
+            plan.noise.copy_(noise)
+        plan.run()
+        return plan.pre.permute(0, 2, 1).contiguous() if skip_bottleneck else plan.z.clone()
+
+    @torch.no_grad()
+    def decode(self, latents: torch.Tensor) -> torch.Tensor:
+        """AudioAutoencoder.decode (autoencoders.py:487-528): latents (B, latent, T') -> (B, 1, T' * hop)."""
+        ops.require_device(latents, "OobleckVAE.decode")
+        B, L, T = latents.shape
+        if L != self.latent:
+            raise ValueError(f"OobleckVAE.decode: {self.latent} latent channels expected, got {L}")
+        plan = self._plan("dec", B, T, latents.device)
+        plan.zin.copy_(latents.permute(0, 2, 1))
+        plan.run()
+        return plan.out.clone()[:, None, :]
+
+
+class _Plan:
+    """A fixed launch list over buffers it owns: eager on the first call, then captured into a CUDA graph and replayed
+    (tensor maps are kernel parameters, so they are baked in; DITSEP_GRAPH=0 keeps it eager) -- the launch-plan idiom of
+    models/diffsep/engine.py.  ~70 - 110 launches of 10 - 100 us each are host-bound otherwise."""
+
+    def __init__(self, device):
+        self.steps, self.device, self._graph, self._runs, self._graph_launches = [], device, None, 0, 0
+
+    def add(self, fn, *args, **kwargs):
+        self.steps.append((fn, args, kwargs))
+
+    def run_eager(self):
+        for fn, args, kwargs in self.steps:
+            fn(*args, **kwargs)
+
+    def run(self):
+        if not ops.graphs_enabled():
+            return self.run_eager()
+        if self._graph is None:
+            if self._runs == 0:
+                self._runs = 1
+                return self.run_eager()
+            n0 = ops.launch_count()
+            g = torch.cuda.CUDAGraph()
+            cur = torch.cuda.current_stream()
+            side = torch.cuda.Stream(device=self.device)
+            side.wait_stream(cur)
+            with torch.cuda.stream(side):
+                with torch.cuda.graph(g, stream=side, capture_error_mode="thread_local"):
+                    self.run_eager()
+            cur.wait_stream(side)
+            self._graph = g
+            self._graph_launches = ops.launch_count() - n0
+            ops.note_launches(-self._graph_launches)
+        self._graph.replay()
+        ops.note_launches(self._graph_launches)
 
 
 class LatentCodec:

@@ -17,7 +17,7 @@ import torch.nn.functional as F
 
 from ditsep_b200 import ops
 
-_NAMES = ["pc_corrector", "pc_predictor", "pc_prior", "pc_langevin", "energy_envelope", "philox_normal", "stft_compress", "expand_istft", "gn_stats",
+_NAMES = ["conv1d_tc", "conv1d_in", "conv1d_out", "vae_sample", "pc_corrector", "pc_predictor", "pc_prior", "pc_langevin", "energy_envelope", "philox_normal", "stft_compress", "expand_istft", "gn_stats",
           "gn_sums", "gn_finalize", "gn_apply", "gn_apply_srcs", "gn_small", "fir_resample", "conv_direct", "attention", "temb_mlp", "temb_dense", "output_layer"]
 
 
@@ -111,6 +111,58 @@ def energy_envelope(mix, out, avg_len):
     cs = torch.cat([torch.zeros(B, 1, dtype=torch.float64), sq.cumsum(dim=1)], dim=1)
     box = (cs[:, avg_len:] - cs[:, :-avg_len]) / avg_len
     out.copy_((0.5 * box.clamp(min=1e-4).sqrt()).float().reshape(out.shape))
+
+
+def _view(t, B, rows, C, ld, bs):
+    """The (B, rows, C) view the C ABI describes by (first row pointer, row stride ld, signal stride bs)."""
+    return torch.as_strided(t, (B, rows, C), (bs, ld, 1), t.storage_offset())
+
+
+def conv1d_tc(x, T_in, bs_in, w_bf16, Cout, taps, dil, pad, s_view, T_out, bias=None, residual=None, ld_res=0, bs_res=0,
+              out=None, out_act=None, ld_out=0, bs_out=0):
+    """ditsep_conv1d_tc: out[t] = sum_k W_k x[t * s + k * dil - pad] (zero outside [0, T_in)), fp32 accumulation of the bf16
+    operands, + bias + residual; raw and / or ELU output through the views."""
+    B = x.shape[0]
+    Cin = w_bf16.shape[1] // taps
+    xv = _view(x, B, T_in, Cin, Cin, bs_in).float()
+    w = w_bf16.float().reshape(Cout, taps, Cin)
+    t = torch.arange(T_out)
+    acc = torch.zeros(B, T_out, Cout)
+    for k in range(taps):
+        idx = t * s_view + k * dil - pad
+        ok = (idx >= 0) & (idx < T_in)
+        g = torch.zeros(B, T_out, Cin)
+        g[:, ok] = xv[:, idx[ok]]
+        acc += g @ w[:, k].t()
+    if bias is not None:
+        acc += bias
+    if residual is not None:
+        acc += _view(residual, B, T_out, Cout, ld_res, bs_res).float()
+    stored = acc
+    if out is not None:
+        _view(out, B, T_out, Cout, ld_out, bs_out).copy_(acc)
+        stored = _view(out, B, T_out, Cout, ld_out, bs_out).float()
+    if out_act is not None:
+        _view(out_act, B, T_out, Cout, ld_out, bs_out).copy_(F.elu(stored))
+
+
+def conv1d_in(x, w, bias, out, out_act):
+    y = F.conv1d(x[:, None].float(), w[:, None].float(), bias, padding=3).permute(0, 2, 1)
+    out.copy_(y)
+    out_act.copy_(F.elu(out.float()))
+
+
+def conv1d_out(x, T, ld, bs, w, out, final_tanh=True):
+    B, C = out.shape[0], w.shape[1]
+    xv = _view(x, B, T, C, ld, bs).float().permute(0, 2, 1)
+    y = F.conv1d(xv, w.t()[None].float(), None, padding=3)[:, 0]
+    out.copy_(torch.tanh(y) if final_tanh else y)
+
+
+def vae_sample(pre, noise, z):
+    L = z.shape[1]
+    mean, scale = pre[..., :L].permute(0, 2, 1), pre[..., L:].permute(0, 2, 1)
+    z.copy_(noise * (F.softplus(scale) + 1e-4) + mean)
 
 
 def philox_normal(out, seed, draw):

@@ -99,3 +99,28 @@ def test_oobleck_vae_vs_reference_golden(oob, name):
     z1, _ = codec.encode(mix, seed=5)
     z2, _ = codec.encode(mix, seed=5)
     assert torch.equal(z1, z2) and not torch.equal(z1, z)
+
+
+def test_latent_separate_end_to_end_on_gpu(oob):
+    """LatentDiffSepModel.separate (src/diffsep_latent.py:472-487) on the device: VAE encode -> latent "ald" sampler over the
+    OUVE SDE -> VAE decode equals the same three calls made by hand; shapes and trimming as the reference's."""
+    from ditsep_b200.diffsep_latent import LatentDiffSepModel, latent_default_config
+    from oracle import ncsnpp_ref as R
+    from oracle import sampler_ref as S
+    ch, lat, T, cm, st = _cfg(oob, "small")
+    vae = OobleckVAE(ch, cm, st, lat, device=DEV).load_state_dict(O.make_state_dict(ch, cm, st, lat, seed=7))
+    model = LatentDiffSepModel(latent_default_config(nf=32, N=3, precision="bf16"), vae=vae)
+    bcfg = R.NCSNppConfig(nf=32, ch_mult=(1, 2, 2), num_res_blocks=2, attn_resolutions=(16,), image_size=64,
+                          num_channels_in=3, num_channels_out=2, centered=True)
+    model.score_model.load_state_dict(R.make_state_dict(bcfg, seed=5, with_window=None), strict=True)
+    model = model.to(DEV).eval()
+    mix = torch.tensor(oob["small_mix"]).to(DEV)
+    noise = torch.tensor(oob["small_noise"]).to(DEV)
+    with torch.no_grad():
+        est, nfe = model.separate(mix, target_dim=T, noise=noise, noise_tape=S.NoiseTape(3))
+        z, _ = model.encode(mix, noise=noise)
+        x, nfe2 = model.get_pc_sampler("reverse_diffusion", "ald", z, N=3, snr=0.5, corrector_steps=1,
+                                       noise_tape=S.NoiseTape(3))()
+        byhand = model.decode(x, T)
+    assert nfe == nfe2 == 6 and est.shape == (2, 2, T) and torch.isfinite(est).all()
+    assert torch.equal(est, byhand)
