@@ -24,7 +24,8 @@
 namespace ditsep {
 
 constexpr int kC1Stages = 5;
-constexpr int kC1Threads = 192;   // warp 0: TMA, warp 1: TMEM + MMA, warps 2-5: epilogue (TMEM lane quadrant = warp & 3)
+constexpr int kC1Threads = 320;   // warp 0: TMA, warp 1: TMEM + MMA, warps 2-9: epilogue (TMEM lane quadrant warp & 3,
+                                  // channel half (warp - 2) >> 2)
 constexpr int kC1BN = 128;
 
 struct Conv1dParams {
@@ -41,7 +42,59 @@ struct Conv1dParams {
   int64_t bs_out;                              // elements between signals of out / out_act
 };
 
-__device__ __forceinline__ float elu_f(float x) { return x > 0.f ? x : expm1f(x); }
+// ELU for values that are rounded to bf16 right after: exp through one MUFU (ex2.approx).  The cancellation in
+// exp(x) - 1 near 0 costs ~1e-7 absolute, far below the bf16 step at the magnitudes where it matters (the epilogue is
+// the convolution kernels' critical path: expm1f is ~25 instructions per element).
+__device__ __forceinline__ float elu_f(float x) {
+  float e;
+  asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(e) : "f"(x * 1.4426950408889634f));
+  return x > 0.f ? x : e - 1.0f;
+}
+
+// Epilogue of one 128-row accumulator tile: the calling thread owns output row t of signal b (TMEM lane of lane_addr)
+// and walks the 128 output channels from n0 in packs of 16: + bias, + residual, raw and / or ELU output.
+__device__ __forceinline__ void c1_epilogue(const Conv1dParams& p, uint32_t lane_addr, int b, int t, int n0, int half) {
+  const bool valid = t < p.T_out && b < p.B;
+  const int64_t row_o = (int64_t)b * p.bs_out + (int64_t)t * p.ld_out;
+  const bf16* res = p.residual ? p.residual + (int64_t)b * p.bs_res + (int64_t)t * p.ld_res : nullptr;
+#pragma unroll 1
+  for (int c0 = half * (kC1BN / 2); c0 < (half + 1) * (kC1BN / 2); c0 += 16) {
+    uint32_t v[16];
+    tmem_ld16(lane_addr + (uint32_t)c0, v);
+    const int co = n0 + c0;
+    if (!valid || co >= p.Cout) continue;
+#pragma unroll
+    for (int h = 0; h < 2; ++h) {  // two packs of 8 channels
+      const int c = co + 8 * h;
+      float f[8];
+#pragma unroll
+      for (int j = 0; j < 8; ++j) f[j] = __uint_as_float(v[8 * h + j]);
+      if (p.bias) {
+        const float4 b0 = __ldg(reinterpret_cast<const float4*>(p.bias + c));
+        const float4 b1 = __ldg(reinterpret_cast<const float4*>(p.bias + c + 4));
+        f[0] += b0.x; f[1] += b0.y; f[2] += b0.z; f[3] += b0.w;
+        f[4] += b1.x; f[5] += b1.y; f[6] += b1.z; f[7] += b1.w;
+      }
+      if (res) {
+        float r8[8];
+        Pack8<bf16>::load(res + c, r8);
+#pragma unroll
+        for (int j = 0; j < 8; ++j) f[j] += r8[j];
+      }
+      if (p.out) {
+        if (p.out_f32) Pack8<float>::store(reinterpret_cast<float*>(p.out) + row_o + c, f);
+        else Pack8<bf16>::store(reinterpret_cast<bf16*>(p.out) + row_o + c, f);
+      }
+      if (p.out_act) {
+        // ELU of the value AS STORED (bf16-rounded when the raw output is bf16): what a separate pass over `out` would see
+        float a[8];
+#pragma unroll
+        for (int j = 0; j < 8; ++j) a[j] = elu_f(p.out_f32 || !p.out ? f[j] : __bfloat162float(__float2bfloat16_rn(f[j])));
+        Pack8<bf16>::store(reinterpret_cast<bf16*>(p.out_act) + row_o + c, a);
+      }
+    }
+  }
+}
 
 __global__ void __launch_bounds__(kC1Threads) conv1d_tc_kernel(const __grid_constant__ CUtensorMap mapA,
                                                                const __grid_constant__ CUtensorMap mapW,
@@ -108,55 +161,127 @@ __global__ void __launch_bounds__(kC1Threads) conv1d_tc_kernel(const __grid_cons
     const int qd = warp & 3;
     const int row = qd * 32 + lane;
     const int b = b0 + row / p.bt, t = t0 + row % p.bt;
-    const bool valid = t < p.T_out && b < p.B;
     mbar_wait_sleep(smem_u32(&bar_accum), 0);
     tc_fence_after();
-    const uint32_t lane_addr = tmem + ((uint32_t)(qd * 32) << 16);
-    const int64_t row_o = (int64_t)b * p.bs_out + (int64_t)t * p.ld_out;
-    const bf16* res = p.residual ? p.residual + (int64_t)b * p.bs_res + (int64_t)t * p.ld_res : nullptr;
-#pragma unroll 1
-    for (int c0 = 0; c0 < kC1BN; c0 += 16) {
-      uint32_t v[16];
-      tmem_ld16(lane_addr + (uint32_t)c0, v);
-      const int co = n0 + c0;
-      if (!valid || co >= p.Cout) continue;
-#pragma unroll
-      for (int h = 0; h < 2; ++h) {  // two packs of 8 channels
-        const int c = co + 8 * h;
-        float f[8];
-#pragma unroll
-        for (int j = 0; j < 8; ++j) f[j] = __uint_as_float(v[8 * h + j]);
-        if (p.bias) {
-          const float4 b0 = __ldg(reinterpret_cast<const float4*>(p.bias + c));
-          const float4 b1 = __ldg(reinterpret_cast<const float4*>(p.bias + c + 4));
-          f[0] += b0.x; f[1] += b0.y; f[2] += b0.z; f[3] += b0.w;
-          f[4] += b1.x; f[5] += b1.y; f[6] += b1.z; f[7] += b1.w;
-        }
-        if (res) {
-          float r8[8];
-          Pack8<bf16>::load(res + c, r8);
-#pragma unroll
-          for (int j = 0; j < 8; ++j) f[j] += r8[j];
-        }
-        if (p.out) {
-          if (p.out_f32) Pack8<float>::store(reinterpret_cast<float*>(p.out) + row_o + c, f);
-          else Pack8<bf16>::store(reinterpret_cast<bf16*>(p.out) + row_o + c, f);
-        }
-        if (p.out_act) {
-          // ELU of the value AS STORED (bf16-rounded when the raw output is bf16): what a separate pass over `out` would see
-          float a[8];
-#pragma unroll
-          for (int j = 0; j < 8; ++j) a[j] = elu_f(p.out_f32 || !p.out ? f[j] : __bfloat162float(__float2bfloat16_rn(f[j])));
-          Pack8<bf16>::store(reinterpret_cast<bf16*>(p.out_act) + row_o + c, a);
-        }
-      }
-    }
+    c1_epilogue(p, tmem + ((uint32_t)(qd * 32) << 16), b, t, n0, (warp - 2) >> 2);
   }
   tc_fence_before();
   __syncthreads();
   if (warp == 1) {
     tc_fence_after();
     tmem_dealloc(tmem, (uint32_t)kC1BN);
+  }
+}
+
+// ---- stride-1 convolutions of long signals: one halo load per channel block --------------------------------------------
+// conv1d_tc_kernel re-fetches its 128 activation rows once per tap and streams the whole filter for one 128 x 128 tile:
+// 64 flop per byte from L2 (150 TFLOP/s measured, r2zf).  Here a CTA owns kC1NM * 128 consecutive output rows: per
+// 64-channel block it loads those rows PLUS the taps' reach once ((taps - 1) * |d| extra rows); tap k's A operand is the
+// same shared-memory tile read through a descriptor whose start is shifted by whole rows (the tile kernel's trick, in one
+// dimension the row groups stay 1024 bytes apart), and every filter block feeds kC1NM accumulators.
+constexpr int kC1NM = 2;
+constexpr int kC1ABox = 64;   // rows per TMA box of the halo tile
+constexpr int kC1WStages = 2;   // 2 x 40 KB halo tiles + 2 x 16 KB filter blocks = 112 KB: two CTAs per SM, so one CTA's
+                                // epilogue runs under the other's MMAs
+
+__global__ void __launch_bounds__(kC1Threads) conv1d_halo_kernel(const __grid_constant__ CUtensorMap mapA,
+                                                                 const __grid_constant__ CUtensorMap mapW,
+                                                                 const Conv1dParams p, int lo, int a_boxes) {
+  extern __shared__ uint8_t smem_raw[];
+  __shared__ __align__(8) uint64_t bar_a_full[2], bar_a_empty[2], bar_w_full[kC1WStages], bar_w_empty[kC1WStages], bar_accum;
+  __shared__ uint32_t tmem_slot;
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const uint32_t base = (smem_u32(smem_raw) + 1023u) & ~1023u;
+  const uint32_t a_bytes = (uint32_t)a_boxes * kC1ABox * 128;      // multiple of 8 KB
+  const uint32_t w_ring = base + 2 * a_bytes;
+  constexpr uint32_t kW = kC1BN * 128;
+  constexpr int kRows = kC1NM * 128;
+  const int tiles_t = (p.T_out + kRows - 1) / kRows;
+  const int b = blockIdx.x / tiles_t, t0 = (blockIdx.x - b * tiles_t) * kRows;
+  const int n0 = blockIdx.y * kC1BN;
+  const int chunks = p.Cin / 64;
+
+  if (threadIdx.x == 0) {
+    for (int s = 0; s < 2; ++s) {
+      mbar_init(smem_u32(&bar_a_full[s]), 1);
+      mbar_init(smem_u32(&bar_a_empty[s]), 1);
+    }
+    for (int s = 0; s < kC1WStages; ++s) {
+      mbar_init(smem_u32(&bar_w_full[s]), 1);
+      mbar_init(smem_u32(&bar_w_empty[s]), 1);
+    }
+    mbar_init(smem_u32(&bar_accum), 1);
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  if (warp == 1) tmem_alloc(smem_u32(&tmem_slot), (uint32_t)(kC1NM * kC1BN));
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem = tmem_slot;
+
+  if (warp == 0) {
+    if (lane == 0) {
+      int sw = 0;
+      uint32_t pw = 1;
+      for (int ch = 0; ch < chunks; ++ch) {
+        const int sa = ch & 1;
+        mbar_wait(smem_u32(&bar_a_empty[sa]), (((uint32_t)(ch >> 1)) & 1u) ^ 1u);
+        const uint32_t afull = smem_u32(&bar_a_full[sa]);
+        mbar_expect_tx(afull, a_bytes);
+        for (int i = 0; i < a_boxes; ++i)  // rows t0 + lo + 64 i ..; outside [0, T) zero-filled: the padding
+          tma_load_3d(base + (uint32_t)sa * a_bytes + (uint32_t)i * (kC1ABox * 128), &mapA, afull, ch * 64, t0 + lo + i * kC1ABox, b);
+        for (int k = 0; k < p.taps; ++k) {
+          mbar_wait(smem_u32(&bar_w_empty[sw]), pw);
+          const uint32_t wfull = smem_u32(&bar_w_full[sw]);
+          mbar_expect_tx(wfull, kW);
+          tma_load_2d(w_ring + (uint32_t)sw * kW, &mapW, wfull, k * p.Cin + ch * 64, n0);
+          if (++sw == kC1WStages) { sw = 0; pw ^= 1u; }
+        }
+      }
+    }
+  } else if (warp == 1) {
+    if (lane == 0) {
+      const uint32_t idesc = (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(kC1BN >> 3) << 17) | ((uint32_t)(128 >> 4) << 24);
+      int sw = 0;
+      uint32_t pw = 0;
+      for (int ch = 0; ch < chunks; ++ch) {
+        const int sa = ch & 1;
+        mbar_wait(smem_u32(&bar_a_full[sa]), ((uint32_t)(ch >> 1)) & 1u);
+        tc_fence_after();
+        const uint32_t a0 = base + (uint32_t)sa * a_bytes;
+        for (int k = 0; k < p.taps; ++k) {
+          mbar_wait(smem_u32(&bar_w_full[sw]), pw);
+          tc_fence_after();
+          const uint64_t db = make_sw128_desc(w_ring + (uint32_t)sw * kW);
+          const uint32_t shift = (uint32_t)(k * p.dil - p.pad - lo);  // rows: tap k of output row t reads tile row (t - t0) + shift
+#pragma unroll
+          for (int j = 0; j < kC1NM; ++j) {
+            const uint64_t da = make_sw128_desc(a0 + (shift + (uint32_t)j * 128u) * 128u);
+#pragma unroll
+            for (int kk = 0; kk < 4; ++kk)
+              umma_bf16(tmem + (uint32_t)(j * kC1BN), da + (uint64_t)(2 * kk), db + (uint64_t)(2 * kk), idesc, (ch | k | kk) != 0);
+          }
+          umma_commit(smem_u32(&bar_w_empty[sw]));
+          if (++sw == kC1WStages) { sw = 0; pw ^= 1u; }
+        }
+        umma_commit(smem_u32(&bar_a_empty[sa]));
+      }
+      umma_commit(smem_u32(&bar_accum));
+    }
+  } else {
+    const int qd = warp & 3;
+    mbar_wait_sleep(smem_u32(&bar_accum), 0);
+    tc_fence_after();
+#pragma unroll 1
+    for (int j = 0; j < kC1NM; ++j)
+      c1_epilogue(p, tmem + ((uint32_t)(qd * 32) << 16) + (uint32_t)(j * kC1BN), b, t0 + j * 128 + qd * 32 + lane, n0,
+                  (warp - 2) >> 2);
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 1) {
+    tc_fence_after();
+    tmem_dealloc(tmem, (uint32_t)(kC1NM * kC1BN));
   }
 }
 
@@ -262,6 +387,13 @@ extern "C" int ditsep_conv1d_tc(const void* x, int B, int T_in, int Cin, int64_t
                  "conv1d_tc: operands must be 16-byte aligned");
   C1EncodeFn enc = c1_encode_fn();
   DITSEP_REQUIRE(enc != nullptr, "conv1d_tc: cuTensorMapEncodeTiled not available from the driver");
+  // long stride-1 signals: the halo kernel (DITSEP_CONV1D_HALO=0 keeps the per-tap kernel: comparison arm of the tests)
+  const int q_first = -pad, q_last = (taps - 1) * dil - pad;
+  const int lo = q_first < q_last ? q_first : q_last, hi = q_first < q_last ? q_last : q_first;
+  const int a_rows = kC1NM * 128 + (hi - lo);
+  const int a_boxes = (a_rows + kC1ABox - 1) / kC1ABox;
+  const char* halo_env = getenv("DITSEP_CONV1D_HALO");
+  const bool halo = s_view == 1 && T_out >= kC1NM * 128 && a_boxes <= 10 && !(halo_env && halo_env[0] == '0');
   int bt = 128;
   while (bt > 8 && bt / 2 >= T_out) bt /= 2;   // smallest power of two >= T_out, at least 8
   const int bb = 128 / bt;
@@ -269,7 +401,7 @@ extern "C" int ditsep_conv1d_tc(const void* x, int B, int T_in, int Cin, int64_t
   {
     cuuint64_t gdim[3] = {(cuuint64_t)s_view * Cin, (cuuint64_t)(T_in / s_view), (cuuint64_t)B};
     cuuint64_t gstr[2] = {(cuuint64_t)s_view * Cin * 2, (cuuint64_t)bs_in * 2};
-    cuuint32_t box[3] = {64u, (cuuint32_t)bt, (cuuint32_t)bb}, estr[3] = {1, 1, 1};
+    cuuint32_t box[3] = {64u, (cuuint32_t)(halo ? kC1ABox : bt), (cuuint32_t)(halo ? 1 : bb)}, estr[3] = {1, 1, 1};
     CUresult r = enc(&mapA, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 3, const_cast<void*>(x), gdim, gstr, box, estr,
                      CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
                      CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
@@ -292,6 +424,19 @@ extern "C" int ditsep_conv1d_tc(const void* x, int B, int T_in, int Cin, int64_t
   p.bt = bt; p.bb = bb;
   p.bias = bias; p.residual = reinterpret_cast<const bf16*>(residual); p.ld_res = ld_res; p.bs_res = bs_res;
   p.out = out; p.out_act = out_act; p.out_f32 = out_f32; p.ld_out = ld_out; p.bs_out = bs_out;
+  if (halo) {
+    const size_t hsmem = 1024 + 2 * (size_t)a_boxes * kC1ABox * 128 + (size_t)kC1WStages * kC1BN * 128;
+    static std::atomic<bool> hattr[64];
+    int hdev = 0;
+    DITSEP_CUDA(cudaGetDevice(&hdev));
+    if (hdev < 0 || hdev >= 64 || !hattr[hdev].load(std::memory_order_acquire)) {
+      DITSEP_CUDA(cudaFuncSetAttribute(conv1d_halo_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 1024 + 2 * 10 * kC1ABox * 128 + kC1WStages * kC1BN * 128));
+      if (hdev >= 0 && hdev < 64) hattr[hdev].store(true, std::memory_order_release);
+    }
+    dim3 hgrid((unsigned)(((T_out + kC1NM * 128 - 1) / (kC1NM * 128)) * B), (unsigned)((Cout + kC1BN - 1) / kC1BN));
+    conv1d_halo_kernel<<<hgrid, kC1Threads, hsmem, (cudaStream_t)stream>>>(mapA, mapW, p, lo, a_boxes);
+    return check_launch("conv1d_halo_kernel");
+  }
   const size_t smem = 1024 + (size_t)kC1Stages * (128 * 128 + kC1BN * 128);
   static std::atomic<bool> attr_set[64];
   int dev = 0;
