@@ -331,10 +331,41 @@ def run_ours(args):
                 "e2e": {"value": e2e, "unit": "mixtures/s", "h2d_bytes_per_step": n_in, "d2h_bytes_per_step": n_out},
                 "gpu_launches": launches, "clocks": clk, "roofline": roofline, "roofline_hbm": roofline_hbm,
                 "library_baseline": lib, "cpu_baseline": base}
+        if latent and world == 1:
+            line["vae"] = time_vae(B, c["L"], dev)
         print(json.dumps(line), flush=True)
     if world > 1:
         dist.barrier()
         dist.destroy_process_group()
+
+
+def time_vae(B, L, dev):
+    """C4 companion number: the Oobleck VAE either side of the latent sampler (LatentDiffSep.encode / decode,
+    oobleck_finetune.json widths, random weights) on B mixtures of L * 2048 samples; not part of `value` (the metric is
+    the sampler), reported so that the latent pipeline's whole cost is visible."""
+    import torch
+
+    from ditsep_b200.models.oobleck import OobleckVAE
+    from oracle import oobleck_ref as O
+
+    ch, cm, st, lat = 128, [1, 2, 4, 8, 16], [2, 4, 4, 8, 8], 128
+    vae = OobleckVAE(ch, cm, st, lat, device=dev).load_state_dict(O.make_state_dict(ch, cm, st, lat, seed=7))
+    x = 0.3 * torch.randn(B, 1, L * 2048, device=dev)
+    z = torch.randn(2 * B, lat // 2, L, device=dev)
+    out = {}
+    for name, fn in (("encode", lambda: vae.encode(x, seed=1)), ("decode_2src", lambda: vae.decode(z))):
+        for _ in range(2):
+            fn()
+        torch.cuda.synchronize()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for _ in range(3):
+            fn()
+        e1.record()
+        torch.cuda.synchronize()
+        out[name + "_ms_per_mixture"] = e0.elapsed_time(e1) / 3 / B
+    out["note"] = "weights: oracle.oobleck_ref.make_state_dict (the weight generator is test infrastructure; the VAE runs in the library)"
+    return out
 
 
 # ----------------------------------------------------------------------------------- C5: the sweep, as designed
