@@ -482,9 +482,12 @@ def rooflines(model, name, B, dev, latent, value_per_gpu, hbm, tf_sust, peak_src
     roofline = {"bound": "tensor", "kernel": "conv class (tcgen05 implicit GEMM + CUDA-core narrow layers)",
                 "achieved": achieved, "peak": tf_sust, "unit": "TFLOP/s", "frac": achieved / tf_sust,
                 "flops": "algorithmic (nn.Conv2d 2*M*N*K, real Cin/Cout; identity shortcuts and operand padding = 0)",
-                "peak_source": f"{peak_src} bf16_tflops_sustained", "traffic": None,
-                "traffic_from_profile": "profiles/: ncu --set full capture of the dominant conv launch "
-                                        "(dram__bytes_read.sum + dram__bytes_write.sum per launch)",
+                "peak_source": f"{peak_src} bf16_tflops_sustained",
+                # DRAM bytes of ONE launch of the dominant kernel (conv_ts_kernel, 256x256 64->64, batch 32) from the committed
+                # ncu --set full capture of this kernel: 321.2 MB read + 227.4 MB written against 536.9 MB algorithmic
+                "traffic": 548.6e6 if (name == "C2" and B == 32) else None,
+                "traffic_from_profile": "profiles/r2w_conv_ts.txt: ncu --set full capture of the dominant conv launch "
+                                        "(dram__bytes_read.sum + dram__bytes_write.sum per launch); not re-measured by this run",
                 "conv_share_of_score_step": conv_ms / total_ms if total_ms else None,
                 "score_step_ms_event_sum": total_ms,
                 "whole_path_frac": value_per_gpu * NFE * c["gflop"] * 1e9 / (tf_sust * 1e12)}

@@ -1020,8 +1020,10 @@ extern "C" int ditsep_conv_tc_plan_create_sc(ditsep_conv_plan** plan, const void
     DITSEP_TILE_ATTR(1, false, false); DITSEP_TILE_ATTR(3, true, true); DITSEP_TILE_ATTR(3, true, false);
     DITSEP_TILE_ATTR(3, false, true); DITSEP_TILE_ATTR(3, false, false);
 #undef DITSEP_TILE_ATTR
-    DITSEP_CUDA(cudaFuncSetAttribute(conv_ts_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 216 * 1024));
-    DITSEP_CUDA(cudaFuncSetAttribute(conv_ts_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 216 * 1024));
+    DITSEP_CUDA(cudaFuncSetAttribute(conv_ts_kernel<0>, cudaFuncAttributeMaxDynamicSharedMemorySize, 216 * 1024));
+    DITSEP_CUDA(cudaFuncSetAttribute(conv_ts_kernel<64>, cudaFuncAttributeMaxDynamicSharedMemorySize, 216 * 1024));
+    DITSEP_CUDA(cudaFuncSetAttribute(conv_ts_kernel<128>, cudaFuncAttributeMaxDynamicSharedMemorySize, 216 * 1024));
+    DITSEP_CUDA(cudaFuncSetAttribute(conv_ts_kernel<192>, cudaFuncAttributeMaxDynamicSharedMemorySize, 216 * 1024));
     if (attr_known) attr_set[attr_dev].store(true, std::memory_order_release);
   }
   *plan = pl;
@@ -1075,8 +1077,10 @@ extern "C" int ditsep_conv_tc_run(const ditsep_conv_plan* plan, const float* bia
       lcfg.gridDim = dim3((unsigned)plan->ts_grid);
       lcfg.blockDim = dim3(kTsThreads);
       lcfg.dynamicSmemBytes = plan->ts_smem;
-      if (ld_out == 64) DITSEP_CUDA(cudaLaunchKernelEx(&lcfg, conv_ts_kernel<true>, plan->mapA, plan->mapX, tp));
-      else DITSEP_CUDA(cudaLaunchKernelEx(&lcfg, conv_ts_kernel<false>, plan->mapA, plan->mapX, tp));
+      if (ld_out == 64) DITSEP_CUDA(cudaLaunchKernelEx(&lcfg, conv_ts_kernel<64>, plan->mapA, plan->mapX, tp));
+      else if (ld_out == 128) DITSEP_CUDA(cudaLaunchKernelEx(&lcfg, conv_ts_kernel<128>, plan->mapA, plan->mapX, tp));
+      else if (ld_out == 192) DITSEP_CUDA(cudaLaunchKernelEx(&lcfg, conv_ts_kernel<192>, plan->mapA, plan->mapX, tp));
+      else DITSEP_CUDA(cudaLaunchKernelEx(&lcfg, conv_ts_kernel<0>, plan->mapA, plan->mapX, tp));
       return check_launch("conv_ts_kernel");
     }
 #define DITSEP_TILE_LAUNCH(KS, RES, FAST)                                                                             \

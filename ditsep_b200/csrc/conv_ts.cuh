@@ -118,7 +118,8 @@ __device__ __forceinline__ void ts_stamp(const ConvTsParams& p, uint32_t it, int
 #endif
 }
 
-template <bool kDense>  // kDense: ld_out == 64 (pixel stride of the output a compile-time constant)
+template <int kLd>  // kLd: the output's pixel stride in elements as a compile-time constant (64, 128, 192: dense tensors
+                    // and the U-Net's concat buffers), or 0 = read it from the parameters (one 64-bit add per store)
 __global__ void __launch_bounds__(kTsThreads, 1) conv_ts_kernel(const __grid_constant__ CUtensorMap mapA,
                                                                 const __grid_constant__ CUtensorMap mapX,
                                                                 const __grid_constant__ ConvTsParams p) {
@@ -306,7 +307,7 @@ __global__ void __launch_bounds__(kTsThreads, 1) conv_ts_kernel(const __grid_con
     const int etid = e * 32 + lane;
     const float osc = p.out_scale;
     // byte stride between pixels of the output: a compile-time constant for dense tensors (immediate store offsets)
-    const int64_t pix_bytes = kDense ? 128 : (int64_t)p.ld_out * 2;
+    const int64_t pix_bytes = kLd ? (int64_t)kLd * 2 : (int64_t)p.ld_out * 2;
     float cb = 0.f;
     uint64_t cb2 = 0ull;
     // statistics of this thread's channel: fixed-point {integer, fraction * 2^32} of sum and sum of squares (fx_add's

@@ -431,13 +431,13 @@ def test_conv_tc_fused_shortcut(B, H, W, Cin, Cout, Cx, k, ld_extra):
     assert torch.equal(outb, outb2) and rel(outb.float(), ref) < 4e-3
 
 
-@pytest.mark.parametrize("B,H,W,Cx", [
-    (2, 64, 64, 0),        # 5 row tiles of 15 (last: 4 rows -> N = 48)
-    (1, 128, 72, 64),      # identity-shaped shortcut chunk, last tile 8 rows (N = 80)
-    (3, 100, 64, 128),     # two shortcut chunks (all 512 TMEM columns), ragged height, three images
-    (1, 256, 256, 0),      # the dominant shape: 18 row tiles, the last with ONE valid row (N = 16)
+@pytest.mark.parametrize("B,H,W,Cx,ld_out", [
+    (2, 64, 64, 0, 128),       # 5 row tiles of 15 (last: 4 rows -> N = 48); output = a slice of a concat buffer
+    (1, 128, 72, 64, 192),     # identity-shaped shortcut chunk, last tile 8 rows (N = 80)
+    (3, 100, 64, 128, 80),     # two shortcut chunks (all 512 TMEM columns), ragged height, three images, run-time stride
+    (1, 256, 256, 0, 64),      # the dominant shape: 18 row tiles, the last with ONE valid row (N = 16)
 ])
-def test_conv_ts_filter_in_tensor_memory(B, H, W, Cx, monkeypatch):
+def test_conv_ts_filter_in_tensor_memory(B, H, W, Cx, ld_out, monkeypatch):
     """conv_ts_kernel (64 -> 64 3x3, filter as the TMEM A operand, two taps stacked on M, pixels on N) against the fp32
     reference and against conv_tc_tile_kernel on the same operands; fused statistics, batch invariance, repeatability."""
     Cin = Cout = 64
@@ -463,10 +463,12 @@ def test_conv_ts_filter_in_tensor_memory(B, H, W, Cx, monkeypatch):
         monkeypatch.setenv("DITSEP_CONV_TS", "1" if ts else "0")   # read when the plan is created
         plan = ops.ConvTcPlan(hd_, wd, Cout, 3, shortcut=xd_)
         st = ops.new_sums(hd_.shape[0], Cout, DEV)
-        out = torch.full((hd_.shape[0], H, W, Cout), float("nan"), device=DEV, dtype=torch.bfloat16)
+        buf = torch.full((hd_.shape[0], H, W, ld_out), float("nan"), device=DEV, dtype=torch.bfloat16)
+        out = buf[..., ld_out - Cout:]                          # compile-time strides 64 / 128 / 192, or the run-time path
         plan.run(bias.to(DEV), out, bias_b=bb.to(DEV), out_scale=0.7, stats=st)
         torch.cuda.synchronize()
-        return out, st
+        assert ld_out == Cout or torch.isnan(buf[..., :ld_out - Cout].float()).all()   # nothing written beside the slice
+        return out.contiguous(), st
 
     n0 = ops.launch_count()
     out, st = run(True)
