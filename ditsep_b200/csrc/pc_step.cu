@@ -346,6 +346,129 @@ extern "C" int ditsep_energy_envelope(const float* mix, float* out, int B, int64
   return check_launch("energy_envelope_kernel");
 }
 
+// ---- Schroedinger-bridge sampler step ----------------------------------------------------------
+// One launch per sampler step (get_sb_sampler, sdes/__init__.py:284-389) with DiffSepOU's EDM preconditioning
+// (diffsep.py:813-828) folded in.  coef row of sample b: [w_prev, w_est, w_y, w_z, c_skip, c_out, f_div, c_in_next]:
+//   est = c_skip x + c_out (f / f_div)                    (c_skip = 0, c_out = f_div = 1: est = f)
+//   x'  = (w_prev x + w_est est) + w_y y | w_z z           (the reference's evaluation order, unfused roundings)
+//   x_in = c_in_next x',  y_in = c_in_next y               (the NEXT network evaluation's scaled inputs)
+namespace ditsep {
+__global__ void __launch_bounds__(256) sb_step_kernel(const float* __restrict__ x, const float* __restrict__ f,
+                                                      const float* __restrict__ y, const float* __restrict__ noise,
+                                                      int use_noise, uint64_t seed, uint64_t draw,
+                                                      const float* __restrict__ coef, float* __restrict__ x_out,
+                                                      float* __restrict__ x_in, float* __restrict__ y_in,
+                                                      float* __restrict__ est_out, int n_src, int64_t L,
+                                                      const int* __restrict__ lengths) {
+  const int b = blockIdx.y;
+  const int64_t len = lengths ? (int64_t)lengths[b] : L;
+  const float* cb = coef + (int64_t)b * 8;
+  const float w_prev = cb[0], w_est = cb[1], w_y = cb[2], w_z = cb[3];
+  const float c_skip = cb[4], c_out = cb[5], f_div = cb[6], c_in = cb[7];
+  const int64_t nvec = (L + 3) / 4;
+  const bool vec = (L & 3) == 0;
+  for (int64_t q = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; q < nvec; q += (int64_t)gridDim.x * blockDim.x) {
+    const int64_t l0 = q * 4;
+    float yv[4] = {0.f, 0.f, 0.f, 0.f};
+    if (y) {
+      const int64_t off = (int64_t)b * L + l0;
+      if (vec) {
+        float4 a = __ldg(reinterpret_cast<const float4*>(y + off));
+        yv[0] = a.x; yv[1] = a.y; yv[2] = a.z; yv[3] = a.w;
+      } else {
+#pragma unroll
+        for (int j = 0; j < 4; ++j) yv[j] = (l0 + j < L) ? y[off + j] : 0.f;
+      }
+      if (y_in) {
+        float o[4];
+#pragma unroll
+        for (int j = 0; j < 4; ++j) o[j] = (l0 + j < len) ? __fmul_rn(c_in, yv[j]) : 0.f;
+        if (vec) *reinterpret_cast<float4*>(y_in + off) = make_float4(o[0], o[1], o[2], o[3]);
+        else
+          for (int j = 0; j < 4; ++j)
+            if (l0 + j < L) y_in[off + j] = o[j];
+      }
+    }
+    for (int i = 0; i < n_src; ++i) {
+      const int64_t off = ((int64_t)b * n_src + i) * L + l0;
+      float xv[4], fv[4] = {0.f, 0.f, 0.f, 0.f}, zv[4] = {0.f, 0.f, 0.f, 0.f};
+      if (vec) {
+        float4 a = *reinterpret_cast<const float4*>(x + off);
+        xv[0] = a.x; xv[1] = a.y; xv[2] = a.z; xv[3] = a.w;
+        if (f) {
+          float4 s = __ldg(reinterpret_cast<const float4*>(f + off));
+          fv[0] = s.x; fv[1] = s.y; fv[2] = s.z; fv[3] = s.w;
+        }
+        if (use_noise && noise) {
+          float4 z = __ldg(reinterpret_cast<const float4*>(noise + off));
+          zv[0] = z.x; zv[1] = z.y; zv[2] = z.z; zv[3] = z.w;
+        }
+      } else {
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+          const bool ok = l0 + j < L;
+          xv[j] = ok ? x[off + j] : 0.f;
+          fv[j] = (ok && f) ? f[off + j] : 0.f;
+          zv[j] = (ok && use_noise && noise) ? noise[off + j] : 0.f;
+        }
+      }
+      if (use_noise && !noise) {
+        float4 z = philox_normal4((uint64_t)(((int64_t)b * n_src + i) * nvec + q), seed, draw);
+        zv[0] = z.x; zv[1] = z.y; zv[2] = z.z; zv[3] = z.w;
+      }
+      float xo[4], eo[4], uo[4];
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        const bool live = l0 + j < len;
+        const float est = f ? __fadd_rn(__fmul_rn(c_skip, xv[j]), __fmul_rn(c_out, __fdiv_rn(fv[j], f_div))) : 0.f;
+        float v = __fadd_rn(__fmul_rn(w_prev, xv[j]), __fmul_rn(w_est, est));
+        v = __fadd_rn(v, use_noise ? __fmul_rn(w_z, zv[j]) : __fmul_rn(w_y, yv[j]));
+        eo[j] = live ? est : 0.f;
+        xo[j] = live ? v : 0.f;
+        uo[j] = live ? __fmul_rn(c_in, v) : 0.f;
+      }
+      if (vec) {
+        if (x_out) *reinterpret_cast<float4*>(x_out + off) = make_float4(xo[0], xo[1], xo[2], xo[3]);
+        if (x_in) *reinterpret_cast<float4*>(x_in + off) = make_float4(uo[0], uo[1], uo[2], uo[3]);
+        if (est_out) *reinterpret_cast<float4*>(est_out + off) = make_float4(eo[0], eo[1], eo[2], eo[3]);
+      } else {
+#pragma unroll
+        for (int j = 0; j < 4; ++j)
+          if (l0 + j < L) {
+            if (x_out) x_out[off + j] = xo[j];
+            if (x_in) x_in[off + j] = uo[j];
+            if (est_out) est_out[off + j] = eo[j];
+          }
+      }
+    }
+  }
+}
+}  // namespace ditsep
+
+extern "C" int ditsep_sb_step(const float* x, const float* f, const float* y, const float* noise, int use_noise,
+                              uint64_t seed, uint64_t draw, const float* coef, float* x_out, float* x_in, float* y_in,
+                              float* est_out, int B, int n_src, int64_t L, const int* lengths, void* stream) {
+  DITSEP_REQUIRE(x != nullptr && coef != nullptr, "sb_step: null state or coefficient table");
+  DITSEP_REQUIRE(B > 0 && L > 0 && n_src >= 1 && n_src <= 64, "sb_step: bad shape B=%d n_src=%d L=%lld", B, n_src, (long long)L);
+  DITSEP_REQUIRE(x_out || x_in || y_in || est_out, "sb_step: no output requested");
+  DITSEP_REQUIRE(use_noise || y != nullptr, "sb_step: the ODE update (use_noise = 0) needs the mixture y");
+  DITSEP_REQUIRE(!y_in || y != nullptr, "sb_step: y_in requested without y");
+  if ((L & 3) == 0) {
+    uintptr_t a = reinterpret_cast<uintptr_t>(x) | reinterpret_cast<uintptr_t>(f) | reinterpret_cast<uintptr_t>(y) |
+                  reinterpret_cast<uintptr_t>(noise) | reinterpret_cast<uintptr_t>(x_out) |
+                  reinterpret_cast<uintptr_t>(x_in) | reinterpret_cast<uintptr_t>(y_in) | reinterpret_cast<uintptr_t>(est_out);
+    DITSEP_REQUIRE((a & 15) == 0, "sb_step: 16-byte aligned buffers required when L %% 4 == 0");
+  }
+  const int64_t nvec = (L + 3) / 4;
+  int gx = (int)((nvec + 255) / 256);
+  int maxgx = (kNumSMs * 8 + B - 1) / B;
+  if (gx > maxgx) gx = maxgx;
+  if (gx < 1) gx = 1;
+  ditsep::sb_step_kernel<<<dim3(gx, B), 256, 0, (cudaStream_t)stream>>>(x, f, y, noise, use_noise, seed, draw, coef, x_out,
+                                                                       x_in, y_in, est_out, n_src, L, lengths);
+  return check_launch("sb_step_kernel");
+}
+
 extern "C" int ditsep_philox_normal(float* out, int64_t n, uint64_t seed, uint64_t draw, void* stream) {
   DITSEP_REQUIRE(out != nullptr && n > 0, "philox_normal: empty output");
   int64_t nvec = (n + 3) / 4;

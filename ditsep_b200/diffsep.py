@@ -3,7 +3,8 @@
 Only the inference side of the reference Lightning module is on the hot path and is kept:
 ``__init__`` (diffsep.py:28-80: build score model + SDE from the Hydra config),
 ``forward`` (:341-343), ``separate`` (:82-98), ``get_pc_sampler`` (:623-695),
-``normalize_batch`` / ``denormalize_batch``, ``eval(no_ema=...)``.  Training losses, EMA
+``normalize_batch`` / ``denormalize_batch``, ``eval(no_ema=...)``; and of ``DiffSepOU`` (:729-1217) its EDM-preconditioned
+``forward``, ``separate`` and ``get_sb_sampler``.  Training losses, EMA
 and optimiser plumbing are out of scope.  pytorch_lightning,
 hydra and omegaconf are optional: plain dicts / namespaces work as configs.
 """
@@ -131,6 +132,122 @@ class DiffSepModel(_Base):
             return samples, ns
 
         return batched_sampling_fn
+
+
+class DiffSepOU(DiffSepModel):
+    """Inference side of the reference's second Lightning module (diffsep.py:729-1217): the same score network behind
+    an ``OUVESDE`` (PC sampler with the "ald" corrector) or an ``SBVESDE`` -- then ``forward`` wraps the network in the
+    EDM preconditioning (:813-828) and ``separate`` runs the Schroedinger-bridge sampler (:1204-1217)."""
+
+    def __init__(self, config):
+        super().__init__(config)
+        model_cfg = self.config.model
+        self.is_edm = isinstance(self.sde, sdes.SBVESDE)
+        if self.is_edm:
+            self.network_scaling = getattr(model_cfg, "network_scaling", "1/sigma")
+            self.c_in = self.c_out = self.c_skip = getattr(model_cfg, "c", "edm")
+            self.sigma_data = getattr(model_cfg, "sigma_data", 0.1)
+
+    # -- coefficients (diffsep.py:1165-1202).  The reference's forward always passes a non-empty pad_dim, which selects
+    # the first branch of each; the other (pad_dim=None) branches are different formulae and are kept as they are.
+    def _c_in(self, t, pad_dim=None):
+        if self.c_in == "1":
+            return 1.0
+        if self.c_in == "edm":
+            sigma = self.sde._std(t)
+            if pad_dim:
+                return (self.sigma_data ** 2 / (sigma ** 2 + self.sigma_data ** 2))[pad_dim]
+            return 1.0 / torch.sqrt(sigma ** 2 + self.sigma_data ** 2)
+        raise ValueError("Invalid c_in type: {}".format(self.c_in))
+
+    def _c_out(self, t, pad_dim=None):
+        if self.c_out == "1":
+            return 1.0
+        if self.c_out == "sigma":
+            return self.sde._std(t)
+        if self.c_out == "1/sigma":
+            return 1.0 / self.sde._std(t)[pad_dim] if pad_dim else 1.0 / self.sde._std(t)
+        if self.c_out == "edm":
+            sigma = self.sde._std(t)
+            v = (sigma * self.sigma_data) / torch.sqrt(self.sigma_data ** 2 + sigma ** 2)
+            return v[pad_dim] if pad_dim else v
+        raise ValueError("Invalid c_out type: {}".format(self.c_out))
+
+    def _c_skip(self, t, pad_dim=None):
+        if self.c_skip == "0":
+            return 0.0
+        if self.c_skip == "edm":
+            sigma = self.sde._std(t)
+            if pad_dim:
+                return (sigma ** 2 / (sigma ** 2 + self.sigma_data ** 2))[pad_dim]
+            return self.sigma_data ** 2 / (sigma ** 2 + self.sigma_data ** 2)
+        raise ValueError("Invalid c_skip type: {}".format(self.c_skip))
+
+    def edm_table(self, times: torch.Tensor):
+        """(len(times), 4) f32 CPU rows [c_in, c_skip, c_out, f_div] of ``forward`` at each time (what
+        ``ops.sb_step`` folds in), or None when this model is not preconditioned."""
+        if not self.is_edm:
+            return None
+        t = times.detach().to("cpu", torch.float32).reshape(-1)
+        pad = (...,)
+        one = torch.ones_like(t)
+        if self.network_scaling == "1/sigma":
+            div = self.sde._std(t)
+        elif self.network_scaling == "1/t":
+            div = t
+        else:
+            div = one
+        return torch.stack([one * self._c_in(t, pad), one * self._c_skip(t, pad), one * self._c_out(t, pad), div], dim=1)
+
+    def forward(self, xt, time, mix):
+        if not self.is_edm:
+            return self.score_model(xt, time, mix)
+        from . import ops
+        B = xt.shape[0]
+        tab = self.edm_table(time.reshape(-1)[:1].expand(B) if time.numel() == 1 else time).to(xt.device)
+        xt = xt.to(torch.float32).contiguous()
+        mix = mix.to(torch.float32).contiguous()
+        coef = torch.zeros(2, B, 8, device=xt.device)
+        coef[0, :, 0] = 1.0  # start-up row: x_in = c_in x, y_in = c_in y
+        coef[0, :, 5:7] = 1.0
+        coef[0, :, 7] = tab[:, 0]
+        coef[1, :, 1] = 1.0  # x' = est = c_skip x + c_out (F / f_div)
+        coef[1, :, 4:7] = tab[:, 1:4]
+        coef[1, :, 7] = 1.0
+        x_in, y_in = torch.empty_like(xt), torch.empty_like(mix)
+        ops.sb_step(xt, None, mix, coef[0], x_in=x_in, y_in=y_in)
+        f = self.score_model(x_in, time, y_in).contiguous()
+        out = torch.empty_like(xt)
+        ops.sb_step(xt, f, mix, coef[1], est=out)
+        return out
+
+    def separate(self, mix, **kwargs):
+        """diffsep.py:1204-1217: SB sampler for an SBVESDE, else reverse-diffusion + "ald" PC sampler; the result tuple
+        is returned as the sampler gives it (not denormalised)."""
+        (mix, _), *stats = self.normalize_batch((mix, None))
+        sampler_kwargs = dict(_to_plain(self.config.model.sampler))
+        sampler_kwargs.update(kwargs)
+        if self.is_edm:
+            sampler = self.get_sb_sampler(self.sde, mix, **sampler_kwargs)
+        else:
+            sampler = self.get_pc_sampler("reverse_diffusion", "ald", mix, **sampler_kwargs)
+        return sampler()
+
+    def get_sb_sampler(self, sde, y, sampler_type="ode", N=None, **kwargs):
+        """diffsep.py:1159-1163 (the sde argument is only read for its N; the module's own SDE is copied)."""
+        N = sde.N if N is None else N
+        sde = self.sde.copy()
+        sde.N = N
+        return sdes.get_sb_sampler(sde, self, y=y, sampler_type=sampler_type, **kwargs)
+
+
+def sb_default_config(nf=64, N=30, precision=None, fs=8000):
+    """src/config/diffsep_sb/model/default.yaml as a plain dict: the hot-path network behind SBVESDE(k=2.6, c=0.4)."""
+    cfg = default_config(nf=nf, n_src=2, N=N, precision=precision, fs=fs)
+    cfg["model"]["sde"] = {"_target_": "sdes.SBVESDE", "ndim": 2, "k": 2.6, "c": 0.4, "eps": 1e-8, "N": N,
+                           "sampler_type": "ode"}
+    cfg["model"]["sampler"] = {"N": N}
+    return cfg
 
 
 def default_config(nf=64, n_src=2, N=30, precision=None, fs=8000):

@@ -30,6 +30,8 @@ _TARGET_ALIASES = {
         "ditsep_b200.models.diffsep.score_models.LatentScoreModelNCSNpp",
     "sdes.MixSDE": "ditsep_b200.sdes.MixSDE", "sdes.sdes.MixSDE": "ditsep_b200.sdes.MixSDE",
     "sdes.OUVESDE": "ditsep_b200.sdes.OUVESDE", "sdes.sdes.OUVESDE": "ditsep_b200.sdes.OUVESDE",
+    "sdes.PriorMixSDE": "ditsep_b200.sdes.PriorMixSDE", "sdes.sdes.PriorMixSDE": "ditsep_b200.sdes.PriorMixSDE",
+    "sdes.SBVESDE": "ditsep_b200.sdes.SBVESDE", "sdes.sdes.SBVESDE": "ditsep_b200.sdes.SBVESDE",
 }
 
 

@@ -155,6 +155,29 @@ def energy_envelope(mix: torch.Tensor, out: torch.Tensor, avg_len: int):
           "energy_envelope")
 
 
+def sb_step(x, f, y, coef, *, x_out=None, x_in=None, y_in=None, est=None, noise=None, use_noise=False, seed=0, draw=0,
+            lengths=None):
+    """One Schroedinger-bridge sampler update with the EDM preconditioning folded in (ditsep_sb_step):
+    coef (B, 8) f32 device rows [w_prev, w_est, w_y, w_z, c_skip, c_out, f_div, c_in_next]."""
+    _cuda(x, f, y, coef, x_out, x_in, y_in, est, noise)
+    for n, v in (("x", x), ("f", f), ("y", y), ("coef", coef), ("x_out", x_out), ("x_in", x_in), ("y_in", y_in),
+                 ("est", est), ("noise", noise)):
+        _f32c(v, n)
+    B, n_src = x.shape[0], x.shape[1]
+    L = x.numel() // (B * n_src)
+    if coef.shape != (B, 8):
+        raise _lib.DitsepError(f"sb_step: coef must be ({B}, 8), got {tuple(coef.shape)}")
+    for n, v in (("f", f), ("x_out", x_out), ("x_in", x_in), ("est", est), ("noise", noise)):
+        if v is not None and v.numel() != x.numel():
+            raise _lib.DitsepError(f"sb_step: {n} has {v.numel()} elements, the state has {x.numel()}")
+    for n, v in (("y", y), ("y_in", y_in)):
+        if v is not None and v.numel() != B * L:
+            raise _lib.DitsepError(f"sb_step: {n} has {v.numel()} elements, expected (B, 1, L) = {B * L}")
+    check(_lib.load().ditsep_sb_step(_ptr(x), _ptr(f), _ptr(y), _ptr(noise), int(bool(use_noise)), seed, draw, _ptr(coef),
+                                     _ptr(x_out), _ptr(x_in), _ptr(y_in), _ptr(est), B, n_src, L, _lengths(lengths, B),
+                                     _stream()), "sb_step")
+
+
 def philox_normal(out: torch.Tensor, seed: int, draw: int):
     _cuda(out)
     _f32c(out, "out")

@@ -17,10 +17,10 @@ import torch
 
 from .correctors import Corrector, CorrectorRegistry
 from .predictors import Predictor, PredictorRegistry, ReverseDiffusionPredictor
-from .sdes import SDE, MixSDE, NoiseSource, OUVESDE, PriorMixSDE, SDERegistry
+from .sdes import SDE, MixSDE, NoiseSource, OUVESDE, PriorMixSDE, SBVESDE, SDERegistry
 
 __all__ = ["PredictorRegistry", "CorrectorRegistry", "SDERegistry", "Predictor", "Corrector", "SDE", "MixSDE",
-           "PriorMixSDE", "OUVESDE", "NoiseSource", "ReverseDiffusionPredictor", "get_pc_sampler", "get_pc_scheduled_sampler",
+           "PriorMixSDE", "OUVESDE", "SBVESDE", "NoiseSource", "ReverseDiffusionPredictor", "get_pc_sampler", "get_pc_scheduled_sampler",
            "get_ode_sampler", "get_sb_sampler"]
 
 
@@ -125,5 +125,59 @@ def get_ode_sampler(*args, **kwargs):
     raise NotImplementedError("PF-ODE sampler (sdes/__init__.py:196-281) is SURVEY.md 8f item 2, not built yet")
 
 
-def get_sb_sampler(*args, **kwargs):
-    raise NotImplementedError("SB sampler (sdes/__init__.py:284-389) is SURVEY.md 8f item 2, not built yet")
+def get_sb_sampler(sde, model, y: torch.Tensor, eps=1e-4, n_steps=50, sampler_type="ode", pad_dim=None, noise_tape=None,
+                   seed=None, lengths=None, **kwargs):
+    """Schroedinger-bridge samplers (sdes/__init__.py:284-389): first-order "sde" (:288-333) or "ode" (:335-382)
+    discretisation on ``linspace(T, eps, N + 1)``, state initialised with the mixture repeated twice (the reference
+    hard-codes two sources), returning ``(x, n_steps)`` -- the ARGUMENT n_steps (default 50), like the reference.
+
+    Each step is one network evaluation plus ONE ``ops.sb_step`` launch.  If ``model`` exposes ``edm_table(times)``
+    and ``score_model`` (``DiffSepOU`` with an ``SBVESDE``), the EDM preconditioning of ``DiffSepOU.forward``
+    (diffsep.py:813-828) is folded into that launch as well: it also emits the c_in-scaled inputs of the next
+    evaluation, so the raw network is called directly.  Any other callable ``model(xt, time, y)`` is used as is.
+    ``noise_tape`` / ``seed`` / ``lengths`` as in ``get_pc_sampler`` ("sde" draws one tensor per step: draw i at
+    step i)."""
+    from .. import ops
+    if sampler_type not in ("sde", "ode"):
+        raise ValueError("Invalid type. Choose 'ode' or 'sde'.")
+    if lengths is not None:
+        lengths = torch.as_tensor(lengths, dtype=torch.int32).to(y.device).contiguous()
+    noise = NoiseSource(tape=noise_tape, seed=seed, lengths=lengths)
+    use_noise = sampler_type == "sde"
+
+    def sampler():
+        noise.begin_run()
+        with torch.no_grad():
+            B, N = y.shape[0], sde.N
+            yc = y.to(torch.float32).contiguous()
+            time_steps = torch.linspace(sde.T, eps, N + 1)
+            # coefficient rows [w_prev, w_est, w_y, w_z, c_skip, c_out, f_div, c_in_next]; row 0 is the start-up call
+            # that only forms the first evaluation's scaled inputs, row i + 1 belongs to step i
+            coef = torch.zeros(N + 1, 8)
+            coef[0, 0] = 1.0
+            coef[:, 5:] = 1.0
+            coef[1:, :4] = sde.step_table(time_steps, sampler_type)
+            edm = getattr(model, "edm_table", None)
+            edm = edm(time_steps[1:]) if edm is not None else None  # (N, 4): c_in, c_skip, c_out, f_div at each evaluation
+            if edm is not None:
+                coef[1:, 4:7] = edm[:, 1:4]
+                coef[:N, 7] = edm[:, 0]
+            coef = coef[:, None, :].expand(N + 1, B, 8).contiguous().to(y.device)
+            vec_ts = time_steps[1:, None].expand(N, B).contiguous().to(y.device)
+            xt = yc.repeat(1, 2, 1)
+            if edm is not None:
+                x_in, y_in = torch.empty_like(xt), torch.empty_like(yc)
+                ops.sb_step(xt, None, yc, coef[0], x_in=x_in, y_in=y_in, lengths=lengths)
+            for i in range(N):
+                z, sd, draw = noise.next(xt) if use_noise else (None, 0, 0)
+                if edm is not None:
+                    f = model.score_model(x_in, vec_ts[i], y_in).contiguous()
+                    ops.sb_step(xt, f, yc, coef[i + 1], x_out=xt, x_in=x_in, y_in=y_in, noise=z, use_noise=use_noise,
+                                seed=sd, draw=draw, lengths=lengths)
+                else:
+                    f = model(xt, vec_ts[i], y).to(torch.float32).contiguous()
+                    ops.sb_step(xt, f, yc, coef[i + 1], x_out=xt, noise=z, use_noise=use_noise, seed=sd, draw=draw,
+                                lengths=lengths)
+            return xt, n_steps
+
+    return sampler

@@ -387,3 +387,84 @@ class OUVESDE(SDE):
 
     def prior_logp(self, z):
         raise NotImplementedError("prior_logp for OU SDE not yet implemented!")
+
+
+@SDERegistry.register("sbve")
+class SBVESDE(SDE):
+    """Schroedinger bridge with a variance-exploding diffusion g(t) = sqrt(c) k^t, alpha = 1 (sdes.py:701-779; Jukic et
+    al., "Schroedinger Bridge for Generative Speech Enhancement", 2024).  The closed forms below are per-batch scalars
+    (a handful of flops on (B,) tensors) and stay in torch; the per-sample work of the samplers built on them runs in
+    ``ops.sb_step``, which takes the coefficient tables ``step_table`` prepares."""
+
+    def __init__(self, k, c, N=50, eps=1e-8, sampler_type="ode", **ignored_kwargs):
+        super().__init__(N)
+        self.k = k
+        self.c = c
+        self.N = N
+        self.eps = eps
+        self.sampler_type = sampler_type
+
+    def copy(self):
+        return SBVESDE(self.k, self.c, N=self.N)  # like the reference (:730), eps and sampler_type go back to defaults
+
+    @property
+    def T(self):
+        return 1
+
+    def sde(self, x, y, t):
+        return 0.0, torch.sqrt(torch.tensor(self.c)) * self.k ** t
+
+    def _sigmas_alphas(self, t):
+        """sdes.py:741-752, fp32 like the reference."""
+        alpha_t = torch.ones_like(t)
+        alpha_T = torch.ones_like(t)
+        log_k = torch.log(torch.tensor(self.k))
+        sigma_t = torch.sqrt((self.c * (self.k ** (2 * t) - 1.0)) / (2 * log_k))
+        sigma_T = torch.sqrt((self.c * (self.k ** (2 * self.T) - 1.0)) / (2 * log_k))
+        alpha_bart = alpha_t / (alpha_T + self.eps)
+        sigma_bart = torch.sqrt(sigma_T ** 2 - sigma_t ** 2 + self.eps)
+        return sigma_t, sigma_T, sigma_bart, alpha_t, alpha_T, alpha_bart
+
+    def _mean(self, x0, y, t):
+        sigma_t, sigma_T, sigma_bart, alpha_t, alpha_T, alpha_bart = self._sigmas_alphas(t)
+        w_xt = alpha_t * sigma_bart ** 2 / (sigma_T ** 2 + self.eps)
+        w_yt = alpha_bart * sigma_t ** 2 / (sigma_T ** 2 + self.eps)
+        pad_dim = (...,) + (None,) * (x0.ndim - t.ndim)
+        return w_xt[pad_dim] * x0 + w_yt[pad_dim] * y
+
+    def _std(self, t):
+        sigma_t, sigma_T, sigma_bart, alpha_t, alpha_T, alpha_bart = self._sigmas_alphas(t)
+        return (alpha_t * sigma_bart * sigma_t) / (sigma_T + self.eps)
+
+    def marginal_prob(self, x0, y, t):
+        return self._mean(x0, y, t), self._std(t)
+
+    def prior_sampling(self, shape, y, noise: NoiseSource = None):
+        if shape != y.shape:
+            warnings.warn(f"Target shape {shape} does not match shape of y {y.shape}! Ignoring target shape.")
+        return y
+
+    def prior_logp(self, z):
+        raise NotImplementedError("prior_logp for SBVE SDE not yet implemented!")
+
+    def step_table(self, time_steps: torch.Tensor, sampler_type: str) -> torch.Tensor:
+        """(N, 4) f32 rows [w_prev, w_est, w_y, w_z] of the first-order SB discretisation on the grid ``time_steps``
+        (N + 1 points, CPU), formed with the reference's own expressions (sdes/__init__.py:305-309 "sde", :353-364
+        "ode"); the last "sde" step has w_z = 0 (:325-326)."""
+        ts = time_steps.detach().to("cpu", torch.float32)
+        sig, sig_T, sigb, al, al_T, _ = self._sigmas_alphas(ts[1:])
+        sig_p, _, sigb_p, al_p, _, _ = self._sigmas_alphas(ts[:-1])
+        zero = torch.zeros_like(sig)
+        if sampler_type == "sde":
+            w_prev = al * sig ** 2 / (al_p * sig_p ** 2 + self.eps)
+            tmp = 1 - sig ** 2 / (sig_p ** 2 + self.eps)
+            w_est = al * tmp
+            w_z = al * sig * torch.sqrt(tmp)
+            w_z[-1] = 0.0
+            return torch.stack([w_prev, w_est, zero, w_z], dim=1)
+        if sampler_type == "ode":
+            w_prev = al * sig * sigb / (al_p * sig_p * sigb_p + self.eps)
+            w_est = al / (sig_T ** 2 + self.eps) * (sigb ** 2 - sigb_p * sig * sigb / (sig_p + self.eps))
+            w_mix = al / (al_T * sig_T ** 2 + self.eps) * (sig ** 2 - sig_p * sig * sigb / (sigb_p + self.eps))
+            return torch.stack([w_prev, w_est, w_mix, zero], dim=1)
+        raise ValueError("Invalid type. Choose 'ode' or 'sde'.")

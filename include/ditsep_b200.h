@@ -85,6 +85,18 @@ int ditsep_pc_langevin(int n_src, float* x, const float* score, const float* noi
                        int B, int64_t L, const int* lengths, void* stream);
 /* PriorMixSDE._std_sigma_mix (sdes.py:480-492): out (B, 1, L) = 0.5 sqrt(max(box_{avg_len}(mix^2), 1e-4)). */
 int ditsep_energy_envelope(const float* mix, float* out, int B, int64_t L, int avg_len, void* stream);
+/* One step of the Schroedinger-bridge samplers (get_sb_sampler, src/sdes/__init__.py:284-389: sde_sampler :288-333,
+ * ode_sampler :335-382) with DiffSepOU.forward's EDM preconditioning (src/diffsep.py:813-828, coefficients :1165-1202)
+ * folded into the same pass.  x, f: (B, n_src, L) f32 state and raw network output (f may be NULL: est = 0);
+ * y: (B, 1, L) mixture; coef: DEVICE (B, 8) f32 rows [w_prev, w_est, w_y, w_z, c_skip, c_out, f_div, c_in_next]:
+ *     est = c_skip x + c_out (f / f_div)          (c_skip = 0, c_out = f_div = 1 for an un-preconditioned model)
+ *     x'  = w_prev x + w_est est + (use_noise ? w_z z : w_y y)      z: `noise` (tape) or Philox(seed, draw)
+ *     x_in = c_in_next x',  y_in = c_in_next y    (the scaled inputs of the NEXT network evaluation)
+ * evaluated in the reference's order with individually rounded products.  Outputs x_out (may alias x), x_in, y_in,
+ * est_out are each optional (at least one); rows are kept at 0 past lengths[b] when lengths is given. */
+int ditsep_sb_step(const float* x, const float* f, const float* y, const float* noise, int use_noise, uint64_t seed,
+                   uint64_t draw, const float* coef, float* x_out, float* x_in, float* y_in, float* est_out, int B,
+                   int n_src, int64_t L, const int* lengths, void* stream);
 int ditsep_philox_normal(float* out, int64_t n, uint64_t seed, uint64_t draw, void* stream);
 /* The uniform -> normal transform of that stream on caller-supplied 32-bit words (n % 4 == 0; word 4q, 4q+2 give
  * the radii, 4q+1, 4q+3 the angles): lets a test feed the endpoint uniforms (0, 0xFFFFFFFF) and check for NaN. */

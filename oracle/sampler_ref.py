@@ -10,6 +10,8 @@ TEST INFRASTRUCTURE (see ``oracle/__init__.py``).  Restates
 * ``AnnealedLangevinDynamics.update_fn``    -- src/sdes/correctors.py:70-84
 * ``get_pc_sampler``         -- src/sdes/__init__.py:133-193
 * ``normalize_batch``        -- src/utils/separate.py:56-67
+* ``SBVESDE``, ``get_sb_sampler``, ``DiffSepOU.forward`` (EDM preconditioning)
+                             -- src/sdes/sdes.py:701-779, src/sdes/__init__.py:284-389, src/diffsep.py:813-828,1165-1202
 
 with the matrix algebra written out the way the reference does it (2x2 / nxn
 ``std @ x`` products), NOT in the closed form the CUDA kernel uses, so that the
@@ -282,6 +284,94 @@ def pc_sampler_ref(score_fn, sde, y: Tensor, noise: NoiseFn, corrector: str = "a
             step = predictor_em_ref if predictor == "euler_maruyama" else predictor_rd_ref
             xt, xt_mean = step(sde, xt, vec_t, y, s, z)
         return (xt_mean if denoise else xt), sde.N * (corrector_steps + 1)
+
+
+# --------------------------------------------------------------------------- Schroedinger bridge
+class SBVESDERef:
+    """``SBVESDE`` (src/sdes/sdes.py:701-779): variance-exploding Schroedinger bridge, g(t) = sqrt(c) k^t, alpha = 1."""
+
+    def __init__(self, k: float = 2.6, c: float = 0.4, N: int = 50, eps: float = 1e-8):
+        self.k, self.c, self.N, self.eps = k, c, N, eps
+        self.T = 1
+
+    def sigmas_alphas(self, t: Tensor):
+        """sdes.py:741-752; everything in fp32 tensors like the reference."""
+        alpha_t = torch.ones_like(t)
+        alpha_T = torch.ones_like(t)
+        log_k = torch.log(torch.tensor(self.k))
+        sigma_t = torch.sqrt((self.c * (self.k ** (2 * t) - 1.0)) / (2 * log_k))
+        sigma_T = torch.sqrt((self.c * (self.k ** (2 * self.T) - 1.0)) / (2 * log_k))
+        alpha_bart = alpha_t / (alpha_T + self.eps)
+        sigma_bart = torch.sqrt(sigma_T ** 2 - sigma_t ** 2 + self.eps)
+        return sigma_t, sigma_T, sigma_bart, alpha_t, alpha_T, alpha_bart
+
+    def std(self, t: Tensor) -> Tensor:
+        """sdes.py:763-767."""
+        sigma_t, sigma_T, sigma_bart, alpha_t, _, _ = self.sigmas_alphas(t)
+        return (alpha_t * sigma_bart * sigma_t) / (sigma_T + self.eps)
+
+    def mean(self, x0: Tensor, y: Tensor, t: Tensor) -> Tensor:
+        """sdes.py:754-761."""
+        sigma_t, sigma_T, sigma_bart, alpha_t, _, alpha_bart = self.sigmas_alphas(t)
+        w_x = alpha_t * sigma_bart ** 2 / (sigma_T ** 2 + self.eps)
+        w_y = alpha_bart * sigma_t ** 2 / (sigma_T ** 2 + self.eps)
+        return _pad(w_x, x0) * x0 + _pad(w_y, x0) * y
+
+    def marginal_prob(self, x0, y, t):
+        return self.mean(x0, y, t), self.std(t)
+
+
+def edm_forward_ref(net, sde: SBVESDERef, xt: Tensor, time: Tensor, mix: Tensor, sigma_data: float = 0.1,
+                    network_scaling: str = "1/sigma") -> Tensor:
+    """``DiffSepOU.forward`` with an ``SBVESDE`` (src/diffsep.py:813-828) and the coefficient branches it actually
+    takes (``pad_dim`` is always a non-empty tuple there, :1165-1202): c_in = sd^2 / (s^2 + sd^2) (NOT the
+    1/sqrt form of the other branch), c_out = s sd / sqrt(sd^2 + s^2), c_skip = s^2 / (s^2 + sd^2)."""
+    s = sde.std(time)
+    c_in = _pad(sigma_data ** 2 / (s ** 2 + sigma_data ** 2), xt)
+    c_out = _pad((s * sigma_data) / torch.sqrt(sigma_data ** 2 + s ** 2), xt)
+    c_skip = _pad(s ** 2 / (s ** 2 + sigma_data ** 2), xt)
+    F = net(c_in * xt, time, c_in * mix)
+    if network_scaling == "1/sigma":
+        F = F / _pad(s, xt)
+    elif network_scaling == "1/t":
+        F = F / _pad(time, xt)
+    return c_skip * xt + c_out * F
+
+
+def sb_sampler_ref(sde: SBVESDERef, model, y: Tensor, noise: Optional[NoiseFn] = None, eps: float = 1e-4,
+                   n_steps: int = 50, sampler_type: str = "ode") -> Tuple[Tensor, int]:
+    """``get_sb_sampler`` closures (src/sdes/__init__.py:284-389): first-order SB-SDE / SB-ODE discretisation on
+    ``linspace(T, eps, N + 1)``, state initialised with the mixture repeated twice; the returned count is the
+    ``n_steps`` ARGUMENT (default 50), not the number of network evaluations (N) -- reproduced.  The SDE variant
+    draws one noise tensor per step (draw i at step i), unused at the last step where its weight is 0."""
+    with torch.no_grad():
+        xt = y.repeat(1, 2, 1)
+        ts = torch.linspace(sde.T, eps, sde.N + 1)
+        B = xt.shape[0]
+        sig_p, sig_T, sigb_p, al_p, al_T, _ = sde.sigmas_alphas(ts[0] * torch.ones(B))
+        for i, t in enumerate(ts[1:]):
+            time = t * torch.ones(B)
+            sig, sig_T, sigb, al, al_T, _ = sde.sigmas_alphas(time)
+            est = model(xt, time, y)
+            if sampler_type == "sde":
+                w_prev = al * sig ** 2 / (al_p * sig_p ** 2 + sde.eps)
+                tmp = 1 - sig ** 2 / (sig_p ** 2 + sde.eps)
+                w_est = al * tmp
+                w_z = al * sig * torch.sqrt(tmp)
+                z = noise(i, xt)
+                if i == sde.N - 1:
+                    xt = _pad(w_prev, xt) * xt + _pad(w_est, xt) * est + 0.0 * z
+                else:
+                    xt = _pad(w_prev, xt) * xt + _pad(w_est, xt) * est + _pad(w_z, xt) * z
+            elif sampler_type == "ode":
+                w_prev = al * sig * sigb / (al_p * sig_p * sigb_p + sde.eps)
+                w_est = al / (sig_T ** 2 + sde.eps) * (sigb ** 2 - sigb_p * sig * sigb / (sig_p + sde.eps))
+                w_mix = al / (al_T * sig_T ** 2 + sde.eps) * (sig ** 2 - sig_p * sig * sigb / (sigb_p + sde.eps))
+                xt = _pad(w_prev, xt) * xt + _pad(w_est, xt) * est + _pad(w_mix, xt) * y
+            else:
+                raise ValueError("Invalid type. Choose 'ode' or 'sde'.")
+            sig_p, sigb_p, al_p = sig, sigb, al
+        return xt, n_steps
 
 
 def normalize_batch_ref(mix: Tensor):

@@ -17,7 +17,7 @@ import torch.nn.functional as F
 
 from ditsep_b200 import ops
 
-_NAMES = ["conv1d_tc", "conv1d_in", "conv1d_out", "vae_sample", "pc_corrector", "pc_predictor", "pc_prior", "pc_langevin", "energy_envelope", "philox_normal", "stft_compress", "expand_istft", "gn_stats",
+_NAMES = ["conv1d_tc", "conv1d_in", "conv1d_out", "vae_sample", "pc_corrector", "pc_predictor", "pc_prior", "pc_langevin", "energy_envelope", "sb_step", "philox_normal", "stft_compress", "expand_istft", "gn_stats",
           "gn_sums", "gn_finalize", "gn_apply", "gn_apply_srcs", "gn_small", "fir_resample", "conv_direct", "attention", "temb_mlp", "temb_dense", "output_layer"]
 
 
@@ -111,6 +111,31 @@ def energy_envelope(mix, out, avg_len):
     cs = torch.cat([torch.zeros(B, 1, dtype=torch.float64), sq.cumsum(dim=1)], dim=1)
     box = (cs[:, avg_len:] - cs[:, :-avg_len]) / avg_len
     out.copy_((0.5 * box.clamp(min=1e-4).sqrt()).float().reshape(out.shape))
+
+
+def sb_step(x, f, y, coef, *, x_out=None, x_in=None, y_in=None, est=None, noise=None, use_noise=False, seed=0, draw=0,
+            lengths=None):
+    """csrc/pc_step.cu::sb_step_kernel: est = c_skip x + c_out (f / f_div); x' = w_prev x + w_est est + (w_z z | w_y y);
+    x_in = c_in x', y_in = c_in y -- fp32, individually rounded products like the kernel."""
+    c = [coef[:, i].reshape(-1, 1, 1) for i in range(8)]
+    e = c[4] * x + c[5] * (f / c[6]) if f is not None else torch.zeros_like(x)
+    v = c[0] * x + c[1] * e
+    if use_noise:
+        if noise is None:
+            raise NotImplementedError("the Philox stream only exists on the device: CPU tests pass a noise tape")
+        v = v + c[3] * noise
+    else:
+        v = v + c[2] * y
+    if lengths is not None:
+        live = torch.arange(x.shape[-1])[None, None, :] < lengths.reshape(-1, 1, 1)
+        v, e = v * live, e * live
+    u = c[7] * v
+    yi = c[7] * y if y is not None else None
+    if lengths is not None and yi is not None:
+        yi = yi * live
+    for dst, src in ((x_in, u), (y_in, yi), (est, e), (x_out, v)):  # x_out last: it may alias x
+        if dst is not None:
+            dst.copy_(src.reshape(dst.shape))
 
 
 def _view(t, B, rows, C, ld, bs):

@@ -415,3 +415,90 @@ def test_energy_envelope_kernel_vs_torch():
         m = torch.nn.functional.avg_pool1d(mix.double() ** 2, kernel_size=k, stride=1, padding=k // 2).clamp(min=1e-4).sqrt()
         want = 0.5 * (m[..., :-1] if k % 2 == 0 else m)
         assert rel_l2(out, want.float()) < 1e-6
+
+
+# ------------------------------------------------------------------ Schroedinger-bridge samplers (last part)
+@pytest.mark.parametrize("kind", ["ode", "sde"])
+@pytest.mark.parametrize("precond", ["plain", "edm"])
+def test_sb_sampler_vs_reference_golden(golden, kind, precond):
+    """get_sb_sampler (src/sdes/__init__.py:284-389) on the device: one fused sb_step launch per step, with DiffSepOU's EDM
+    preconditioning folded in for "edm", against the unmodified reference's runs (tests/golden/sb.npz, same tape)."""
+    from test_host_logic import make_diffsep_ou, sb_toy_estimator, sb_toy_net
+    g = golden["sb"]
+    y = torch.tensor(g["sb_y"]).to(DEV)
+    if precond == "plain":
+        x, n = sdes.get_sb_sampler(sdes.SBVESDE(2.6, 0.4, N=6), sb_toy_estimator, y=y, sampler_type=kind,
+                                   noise_tape=S.NoiseTape(90))()
+    else:
+        model = make_diffsep_ou(sb_toy_net)
+        x, n = model.get_sb_sampler(model.sde, y, sampler_type=kind, noise_tape=S.NoiseTape(90))()
+        out = model(torch.tensor(g["edm_xt"]).to(DEV), torch.tensor(g["edm_t"]).to(DEV), y)
+        assert float((out.cpu() - torch.tensor(g["edm_out"])).abs().max()) < 2e-6
+    ref = torch.tensor(g[f"sb_{kind}_{precond}"])
+    e = rel_l2(x, ref)
+    print(f"sb {kind}/{precond}: rel-L2 vs reference {e:.3e}")
+    assert n == 50 and e < 1e-5
+    if kind == "sde":  # in-kernel Philox draws: reproducible per seed, different across seeds, finite
+        mk = (lambda s: sdes.get_sb_sampler(sdes.SBVESDE(2.6, 0.4, N=6), sb_toy_estimator, y=y, sampler_type="sde", seed=s)()[0])
+        a, b, c = mk(5), mk(5), mk(6)
+        assert torch.equal(a, b) and not torch.equal(a, c) and torch.isfinite(a).all()
+
+
+@pytest.mark.parametrize("B,n_src,L", [(3, 2, 4096), (2, 3, 1001), (1, 2, 7)])
+def test_sb_step_kernel_bit_exact_vs_emulation(B, n_src, L):
+    """csrc/pc_step.cu::sb_step_kernel against its fp32 restatement (tests/emu_ops.py): every product and sum is rounded
+    individually in the reference's order, so the comparison is bit-for-bit; vector and scalar-tail paths, ragged rows,
+    every optional output, and the Philox branch against the stand-alone Philox kernel."""
+    import emu_ops
+    g = torch.Generator().manual_seed(100 + L)
+    x, f, z = (torch.randn(B, n_src, L, generator=g) for _ in range(3))
+    y = torch.randn(B, 1, L, generator=g)
+    coef = torch.rand(B, 8, generator=g) + 0.25
+    lengths = torch.tensor([L, max(1, L - 5), max(1, L // 2)][:B], dtype=torch.int32)
+    for use_noise in (False, True):
+        for lens in (None, lengths):
+            want = {k: torch.full((B, n_src, L), float("nan")) for k in ("x_out", "x_in", "est")}
+            want["y_in"] = torch.full((B, 1, L), float("nan"))
+            emu_ops.sb_step(x, f, y, coef, noise=z, use_noise=use_noise, lengths=lens, **want)
+            got = {k: torch.full_like(v, float("nan")).to(DEV) for k, v in want.items()}
+            ops.sb_step(x.to(DEV), f.to(DEV), y.to(DEV), coef.to(DEV), noise=z.to(DEV), use_noise=use_noise,
+                        lengths=None if lens is None else lens.to(DEV), **got)
+            for k in want:
+                assert torch.equal(got[k].cpu(), want[k]), (k, use_noise, lens is not None)
+    # in place, no network output (the start-up call), Philox noise
+    xd = x.to(DEV).clone()
+    ops.sb_step(xd, None, y.to(DEV), coef.to(DEV), x_out=xd)
+    assert torch.equal(xd.cpu(), (coef[:, 0].view(-1, 1, 1) * x + coef[:, 1].view(-1, 1, 1) * torch.zeros_like(x))
+                       + coef[:, 2].view(-1, 1, 1) * y)
+    if L % 4 == 0:
+        unit = torch.zeros(B, 8)
+        unit[:, 3] = 1.0
+        unit[:, 5:] = 1.0
+        zd, zz = torch.empty(B, n_src, L, device=DEV), torch.empty(B, n_src, L, device=DEV)
+        ops.sb_step(x.to(DEV), None, None, unit.to(DEV), x_out=zd, use_noise=True, seed=77, draw=3)
+        ops.philox_normal(zz, 77, 3)
+        assert torch.equal(zd, zz + 0.0)
+    with pytest.raises(Exception):
+        ops.sb_step(x.to(DEV), f.to(DEV), None, coef.to(DEV), x_out=xd)  # ODE update without the mixture
+
+
+def test_diffsep_ou_sb_separation_vs_oracle():
+    """DiffSepOU (src/diffsep.py:729-1217) with the real NCSN++ behind an SBVESDE: `separate` (fused preconditioning, raw
+    network on the scaled inputs the step kernel emits) against the oracle's restatement of the reference loop around
+    the oracle network, fp32, and against the un-fused route through DiffSepOU.forward."""
+    from ditsep_b200.diffsep import DiffSepOU, sb_default_config
+    cfg = R.ScoreConfig(num_sources=2, backbone=R.NCSNppConfig(nf=64))
+    sd = R.make_state_dict(cfg.backbone, seed=0, init_scale=1.0)
+    model = DiffSepOU(sb_default_config(N=3, precision="fp32"))
+    model.score_model.load_state_dict(sd, strict=True)
+    model = model.to(DEV).eval()
+    assert model.is_edm and isinstance(model.sde, sdes.SBVESDE) and model.sde.N == 3
+    mixn, src = sampler_inputs(2, 7810)
+    x, n = model.separate(mixn.to(DEV))  # normalize_batch is idempotent on an already normalised batch up to rounding
+    x2, _ = sdes.get_sb_sampler(model.sde.copy(), lambda a, b, c: model(a, b, c), y=S.normalize_batch_ref(mixn)[0].to(DEV))()
+    sde_ref = S.SBVESDERef(2.6, 0.4, N=3)
+    net = lambda a, b, c: R.score_forward_ref(sd, cfg, a, b, c)  # noqa: E731
+    ref, _ = S.sb_sampler_ref(sde_ref, lambda a, b, c: S.edm_forward_ref(net, sde_ref, a, b, c), S.normalize_batch_ref(mixn)[0])
+    e, e2 = rel_l2(x, ref), rel_l2(x2, x)
+    print(f"DiffSepOU SB-ODE N=3 fp32: rel-L2 vs oracle {e:.3e}; fused vs un-fused route {e2:.3e}")
+    assert n == 50 and e < 1e-3 and e2 < 1e-5
