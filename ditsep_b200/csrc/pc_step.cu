@@ -61,7 +61,7 @@ __device__ __forceinline__ float4 philox_normal4(uint64_t q, uint64_t seed, uint
 }
 
 // ---- per-mixture coefficients ----------------------------------------------------------
-enum Mode { kCorrector = 0, kPredictor = 1, kPrior = 2, kLangevin = 3 };
+enum Mode { kCorrector = 0, kPredictor = 1, kPrior = 2, kLangevin = 3, kPerturb = 4 };
 
 __device__ __forceinline__ Coef make_coef(const ditsep_sde_params& p, int mode, float t) {
   Coef c = {1.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
@@ -93,6 +93,12 @@ __device__ __forceinline__ Coef make_coef(const ditsep_sde_params& p, int mode, 
       c.a1 = -lam * dt;
       c.a2 = G * G;
       c.b0 = G;
+    } else if (mode == kPerturb) {  // marginal sample: (A + e^{-lam t} Pn) x0 + L(t) z   (sdes.py:288-326)
+      const float e = expf(-lam * t);
+      c.a0 = e;
+      c.a1 = 1.0f - e;
+      c.b0 = r2;
+      c.b1 = r1 - r2;
     } else {  // prior: 0.5 y + L(T) z   (t = T = 1 passed by the host)
       c.a0 = 0.f;
       c.a4 = 0.5f;
@@ -114,6 +120,11 @@ __device__ __forceinline__ Coef make_coef(const ditsep_sde_params& p, int mode, 
       c.a4 = -th * dt;
       c.a2 = G * G;
       c.b0 = G;
+    } else if (mode == kPerturb) {  // e^{-theta t} x0 + (1 - e^{-theta t}) y + std(t) z   (sdes.py:662-685)
+      const float e = expf(-th * t);
+      c.a0 = e;
+      c.a4 = 1.0f - e;
+      c.b0 = std;
     } else {
       c.a0 = 0.f;
       c.a4 = 1.0f;
@@ -156,8 +167,12 @@ __global__ void __launch_bounds__(256) pc_update_kernel(ditsep_sde_params p, int
         if (mode != kPrior) {
           float4 a = *reinterpret_cast<const float4*>(x + off);
           xv[i][0] = a.x; xv[i][1] = a.y; xv[i][2] = a.z; xv[i][3] = a.w;
-          float4 s = __ldg(reinterpret_cast<const float4*>(score + off));
-          sv[i][0] = s.x; sv[i][1] = s.y; sv[i][2] = s.z; sv[i][3] = s.w;
+          if (score) {
+            float4 s = __ldg(reinterpret_cast<const float4*>(score + off));
+            sv[i][0] = s.x; sv[i][1] = s.y; sv[i][2] = s.z; sv[i][3] = s.w;
+          } else {
+            sv[i][0] = sv[i][1] = sv[i][2] = sv[i][3] = 0.f;
+          }
         }
         if (noise) {
           float4 z = __ldg(reinterpret_cast<const float4*>(noise + off));
@@ -168,7 +183,7 @@ __global__ void __launch_bounds__(256) pc_update_kernel(ditsep_sde_params p, int
         for (int j = 0; j < 4; ++j) {
           bool ok = l0 + j < L;
           xv[i][j] = (ok && mode != kPrior) ? x[off + j] : 0.f;
-          sv[i][j] = (ok && mode != kPrior) ? score[off + j] : 0.f;
+          sv[i][j] = (ok && mode != kPrior && score) ? score[off + j] : 0.f;
           zv[i][j] = (ok && noise) ? noise[off + j] : 0.f;
         }
       }
@@ -238,10 +253,12 @@ static int launch_pc(const ditsep_sde_params* hp, int mode, float* x, const floa
   DITSEP_REQUIRE(hp->n_src >= 1 && hp->n_src <= kMaxSrc, "pc_step: n_src=%d unsupported (1..%d)", hp->n_src, kMaxSrc);
   DITSEP_REQUIRE(mode == kLangevin || hp->sde == DITSEP_SDE_MIX || hp->sde == DITSEP_SDE_OUVE, "pc_step: unknown sde %d", hp->sde);
   DITSEP_REQUIRE(B > 0 && L > 0, "pc_step: empty state B=%d L=%lld", B, (long long)L);
-  DITSEP_REQUIRE(mode == kPrior || (score != nullptr && t != nullptr), "pc_step: score/t required");
+  DITSEP_REQUIRE(mode == kPrior || ((score != nullptr || mode == kPerturb) && t != nullptr), "pc_step: score/t required");
+  DITSEP_REQUIRE(mode != kPerturb || hp->elem_scale == nullptr, "pc_perturb: PriorMixSDE's envelope is not supported here");
   DITSEP_REQUIRE(!(hp->sde == DITSEP_SDE_MIX && mode == kPrior && hp->n_src != 2 && hp->elem_scale == nullptr),
                  "MixSDE.prior_sampling supports exactly 2 sources (reference sdes.py:346), got %d", hp->n_src);
-  DITSEP_REQUIRE((mode == kCorrector) || (mode == kLangevin) || y != nullptr || (hp->sde == DITSEP_SDE_MIX && mode == kPredictor),
+  DITSEP_REQUIRE((mode == kCorrector) || (mode == kLangevin) || y != nullptr ||
+                     (hp->sde == DITSEP_SDE_MIX && (mode == kPredictor || mode == kPerturb)),
                  "pc_step: y required");
   const int64_t nvec = (L + 3) / 4;
   int gx = (int)((nvec + 255) / 256);
@@ -296,6 +313,12 @@ extern "C" int ditsep_pc_predictor(const ditsep_sde_params* host_p, float* x, co
 extern "C" int ditsep_pc_prior(const ditsep_sde_params* host_p, float* x, const float* noise, uint64_t seed,
                                uint64_t draw, const float* y, int B, int64_t L, const int* lengths, void* stream) {
   return launch_pc(host_p, kPrior, x, nullptr, noise, seed, draw, nullptr, y, nullptr, B, L, lengths, stream);
+}
+
+extern "C" int ditsep_pc_perturb(const ditsep_sde_params* host_p, float* x, const float* noise, uint64_t seed,
+                                 uint64_t draw, const float* t, const float* y, float* x_mean, int B, int64_t L,
+                                 const int* lengths, void* stream) {
+  return launch_pc(host_p, kPerturb, x, nullptr, noise, seed, draw, t, y, x_mean, B, L, lengths, stream);
 }
 
 extern "C" int ditsep_pc_langevin(int n_src, float* x, const float* score, const float* noise, const float* step,
@@ -467,6 +490,117 @@ extern "C" int ditsep_sb_step(const float* x, const float* f, const float* y, co
   ditsep::sb_step_kernel<<<dim3(gx, B), 256, 0, (cudaStream_t)stream>>>(x, f, y, noise, use_noise, seed, draw, coef, x_out,
                                                                        x_in, y_in, est_out, n_src, L, lengths);
   return check_launch("sb_step_kernel");
+}
+
+// ---- denoising score-matching loss (forward value) ---------------------------------------------
+// loss[b] = mean over (source, sample) of (L(t_b) pred + z)^2 with L(t) = sqrt(ev1) A + sqrt(ev2) Pn (MixSDE) or std(t) I
+// (OUVESDE): DiffSepModel.compute_score_loss (src/diffsep.py:344-358: mult_std, MSELoss(L_score, -z), mean over the last
+// two axes).  z is read from `noise`, or regenerated from the Philox stream that ditsep_pc_perturb consumed (same seed,
+// draw and element numbering), so a perturb -> network -> loss pass never stores the noise.  Two launches with a fixed
+// reduction order (per-block partial sums in double, then one warp per mixture): bit-reproducible.
+namespace ditsep {
+constexpr int kLossMaxParts = 256;
+
+template <int NS>
+__global__ void __launch_bounds__(256) score_loss_partial_kernel(ditsep_sde_params p, const float* __restrict__ pred,
+                                                                 const float* __restrict__ noise, uint64_t seed,
+                                                                 uint64_t draw, const float* __restrict__ t,
+                                                                 double* __restrict__ partial, int64_t L) {
+  const int b = blockIdx.y;
+  const Coef c = make_coef(p, kPerturb, t[b]);
+  const int64_t nvec = (L + 3) / 4;
+  const bool vec = (L & 3) == 0;
+  const float inv_n = 1.0f / (float)NS;
+  double acc = 0.0;
+  for (int64_t q = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; q < nvec; q += (int64_t)gridDim.x * blockDim.x) {
+    const int64_t l0 = q * 4;
+    float pv[NS][4], zv[NS][4];
+#pragma unroll
+    for (int i = 0; i < NS; ++i) {
+      const int64_t off = ((int64_t)b * NS + i) * L + l0;
+      if (vec) {
+        float4 a = __ldg(reinterpret_cast<const float4*>(pred + off));
+        pv[i][0] = a.x; pv[i][1] = a.y; pv[i][2] = a.z; pv[i][3] = a.w;
+        if (noise) {
+          float4 z = __ldg(reinterpret_cast<const float4*>(noise + off));
+          zv[i][0] = z.x; zv[i][1] = z.y; zv[i][2] = z.z; zv[i][3] = z.w;
+        }
+      } else {
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+          const bool ok = l0 + j < L;
+          pv[i][j] = ok ? pred[off + j] : 0.f;
+          zv[i][j] = (ok && noise) ? noise[off + j] : 0.f;
+        }
+      }
+      if (!noise) {
+        float4 z = philox_normal4((uint64_t)(((int64_t)b * NS + i) * nvec + q), seed, draw);
+        zv[i][0] = z.x; zv[i][1] = z.y; zv[i][2] = z.z; zv[i][3] = z.w;
+      }
+    }
+    float part = 0.f;
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      if (l0 + j >= L) continue;
+      float pb = 0.f;
+#pragma unroll
+      for (int i = 0; i < NS; ++i) pb += pv[i][j];
+      pb *= inv_n;
+#pragma unroll
+      for (int i = 0; i < NS; ++i) {
+        const float v = c.b0 * pv[i][j] + c.b1 * pb + zv[i][j];
+        part += v * v;
+      }
+    }
+    acc += (double)part;
+  }
+  __shared__ double red[8];
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, o);
+  if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = acc;
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    double s = 0.0;
+#pragma unroll
+    for (int w = 0; w < 8; ++w) s += red[w];
+    partial[(int64_t)b * gridDim.x + blockIdx.x] = s;
+  }
+}
+
+__global__ void __launch_bounds__(32) score_loss_final_kernel(const double* __restrict__ partial, float* __restrict__ loss,
+                                                              int parts, double inv_count) {
+  const int b = blockIdx.x;
+  double s = 0.0;
+  for (int i = threadIdx.x; i < parts; i += 32) s += partial[(int64_t)b * parts + i];
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
+  if (threadIdx.x == 0) loss[b] = (float)(s * inv_count);
+}
+}  // namespace ditsep
+
+extern "C" int ditsep_score_loss(const ditsep_sde_params* hp, const float* pred, const float* noise, uint64_t seed,
+                                 uint64_t draw, const float* t, float* loss, double* workspace, int B, int64_t L,
+                                 void* stream) {
+  DITSEP_REQUIRE(hp && pred && t && loss && workspace, "score_loss: null argument");
+  DITSEP_REQUIRE(hp->sde == DITSEP_SDE_MIX || hp->sde == DITSEP_SDE_OUVE, "score_loss: unknown sde %d", hp->sde);
+  DITSEP_REQUIRE(hp->n_src >= 1 && hp->n_src <= kMaxSrc, "score_loss: n_src=%d unsupported (1..%d)", hp->n_src, kMaxSrc);
+  DITSEP_REQUIRE(hp->elem_scale == nullptr, "score_loss: PriorMixSDE's envelope is not supported here");
+  DITSEP_REQUIRE(B > 0 && L > 0, "score_loss: empty input B=%d L=%lld", B, (long long)L);
+  const int64_t nvec = (L + 3) / 4;
+  int parts = (int)((nvec + 1023) / 1024);  // ~4 vectors per thread
+  if (parts > kLossMaxParts) parts = kLossMaxParts;
+  if (parts < 1) parts = 1;
+  dim3 grid(parts, B);
+  cudaStream_t st = (cudaStream_t)stream;
+  switch (hp->n_src) {
+    case 1: score_loss_partial_kernel<1><<<grid, 256, 0, st>>>(*hp, pred, noise, seed, draw, t, workspace, L); break;
+    case 2: score_loss_partial_kernel<2><<<grid, 256, 0, st>>>(*hp, pred, noise, seed, draw, t, workspace, L); break;
+    case 3: score_loss_partial_kernel<3><<<grid, 256, 0, st>>>(*hp, pred, noise, seed, draw, t, workspace, L); break;
+    default: score_loss_partial_kernel<4><<<grid, 256, 0, st>>>(*hp, pred, noise, seed, draw, t, workspace, L); break;
+  }
+  if (int rc = check_launch("score_loss_partial_kernel")) return rc;
+  score_loss_final_kernel<<<B, 32, 0, st>>>(workspace, loss, parts, 1.0 / ((double)hp->n_src * (double)L));
+  return check_launch("score_loss_final_kernel");
 }
 
 extern "C" int ditsep_philox_normal(float* out, int64_t n, uint64_t seed, uint64_t draw, void* stream) {

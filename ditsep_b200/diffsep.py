@@ -80,9 +80,128 @@ class DiffSepModel(_Base):
         self.t_max = self.sde.T
         self.normalize_batch = utils.normalize_batch
         self.denormalize_batch = utils.denormalize_batch
+        # validation-side settings (diffsep.py:47-62); only read by the score-loss forward below
+        self.time_sampling_strategy = getattr(model_cfg, "time_sampling_strategy", "uniform")
+        self.init_hack = getattr(model_cfg, "init_hack", False)
+        self.init_hack_p = getattr(model_cfg, "init_hack_p", 1.0 / self.sde.N)
+        self.t_rev_init = getattr(model_cfg, "t_rev_init", 0.03)
+        self.train_source_order = getattr(model_cfg, "train_source_order", "random")
 
     def forward(self, xt, time, mix):
         return self.score_model(xt, time, mix)
+
+    # ---- score-matching loss, FORWARD VALUE only (diffsep.py:100-181, 296-358, 476-487) ----------------
+    # What validation_step logs as val/score_loss.  No backward kernels exist in this library: these run under no_grad.
+    def sample_time(self, x):
+        """diffsep.py:100-111."""
+        if self.time_sampling_strategy == "uniform":
+            return x.new_zeros(x.shape[0]).uniform_(self.t_eps, self.t_max)
+        if self.time_sampling_strategy == "varprop":
+            return self.sde.sample_time_varprop(x.shape[0], t_eps=self.t_eps, device=x.device)
+        raise NotImplementedError(f"No sampling strategy {self.time_sampling_strategy}")
+
+    def _draw(self, like, noise):
+        """The normal draw of one loss evaluation: `noise` (a tensor, parity runs) or the library's Philox stream."""
+        if noise is not None:
+            return noise.to(device=like.device, dtype=torch.float32).contiguous()
+        from . import ops
+        z = torch.empty_like(like, dtype=torch.float32)
+        ops.philox_normal(z, int(torch.randint(0, 2 ** 62, (1,)).item()), 0)
+        return z
+
+    def sample_prior(self, mix, target, time=None, noise=None):
+        """diffsep.py:113-181: (x_t, time, L, z).  The default branch (init_hack not in 1..4, which includes the
+        configured init_hack = 5) is one fused launch (ops.pc_perturb); the four "init hacks" that redefine the mean or
+        the noise near t = T are the reference's small (B, n, n) algebra around the same kernel's mean output."""
+        from . import ops
+        time = self.sample_time(target) if time is None else time
+        hack = self.init_hack if self.init_hack in (1, 2, 3, 4) else 0
+        z = self._draw(target, noise)
+        sel4 = None
+        if hack == 4:
+            sel4 = torch.rand_like(time) < 1 / self.sde.N
+            time = torch.where(sel4, time.new_ones(time.shape) * self.sde.T, time)
+        if hasattr(self.sde, "send_to"):
+            self.sde.send_to(target.device)
+        L = self.sde._std(time)
+        x_t = target.to(torch.float32).contiguous().clone()
+        mean = torch.empty_like(x_t) if hack else None
+        ops.pc_perturb(self.sde.fused_params(n_src=target.shape[1]), x_t, time.to(torch.float32).contiguous(),
+                       y=mix.to(torch.float32).contiguous(), noise=z, x_mean=mean)
+        if not hack:
+            return x_t, time, L, z
+        true_mix = torch.broadcast_to(mix, target.shape) / target.shape[1]
+        if hack in (1, 4):
+            sel = sel4 if hack == 4 else ~(time < self.sde.T - self.t_rev_init)
+            sel = torch.broadcast_to(sel[:, None, None], z.shape)
+            z = torch.where(sel, z + self.sde.mult_std_inv(L, true_mix - mean), z)
+            return mean + self.sde.mult_std(L, z), time, L, z
+        T, Tm = self.sde.T, self.sde.T - self.t_rev_init
+        beta = torch.clamp((time - Tm) / (T - Tm), min=0.0, max=1.0)[:, None, None]
+        x_t = true_mix * beta + mean * (1.0 - beta) + self.sde.mult_std(L, z)
+        if hack == 3:
+            z = self.sde.mult_std_inv(L, x_t - mean)
+        return x_t, time, L, z
+
+    def _loss_reduce(self, per_item):
+        """config.model.loss is torch.nn.MSELoss in every reference config; reduction "none" (init_hack 5..7,
+        diffsep.py:64-69) keeps (B,), the default "mean" gives the batch mean."""
+        loss_cfg = _to_plain(getattr(self.config.model, "loss", None)) or {}
+        reduction = "none" if self.init_hack in (5, 6, 7) else loss_cfg.get("reduction", "mean")
+        return per_item if reduction == "none" else per_item.mean()
+
+    @torch.no_grad()
+    def compute_score_loss(self, mix, target, time=None, noise=None):
+        """diffsep.py:344-358: E (L s(x_t, t) + z)^2; perturbation, network and ONE reduction kernel (ops.score_loss)."""
+        from . import ops
+        x_t, time, L, z = self.sample_prior(mix, target, time=time, noise=noise)
+        pred = self(x_t, time, mix).to(torch.float32).contiguous()
+        per_item = ops.score_loss(self.sde.fused_params(n_src=target.shape[1]), pred, time.to(torch.float32).contiguous(), noise=z)
+        return self._loss_reduce(per_item)
+
+    @torch.no_grad()
+    def compute_score_loss_init_hack_pit(self, mix, target, noise=None):
+        """diffsep.py:305-338: t = T, the state is the true mixture plus L z0 whatever the source order, and the loss is
+        the minimum over source permutations of the noise each permutation would explain."""
+        import itertools
+        from . import ops
+        time = mix.new_ones(mix.shape[0]) * self.sde.T
+        true_mix = torch.broadcast_to(mix, target.shape) / target.shape[1]
+        z0 = self._draw(target, noise)
+        p = self.sde.fused_params(n_src=target.shape[1])
+        losses = []
+        for perm in itertools.permutations(range(target.shape[1])):
+            mean, L = self.sde.marginal_prob(target[:, perm, :], time, mix)
+            z = (z0 + self.sde.mult_std_inv(L, true_mix - mean)).contiguous()
+            x_t = mean + self.sde.mult_std(L, z)
+            pred = self(x_t, time, mix).to(torch.float32).contiguous()
+            losses.append(ops.score_loss(p, pred, time, noise=z))
+        return torch.stack(losses, dim=1).min(dim=1).values
+
+    @torch.no_grad()
+    def train_step_init_5(self, mix, target, pit=None):
+        """diffsep.py:363-382 (forward value): a random subset (probability init_hack_p) takes the permutation-invariant
+        t = T loss, the rest the plain loss on randomly ordered sources."""
+        if pit is None:
+            pit = mix.new_zeros(mix.shape[0]).uniform_() < self.init_hack_p
+        losses = []
+        if pit.sum() > 0:
+            losses.append(self.compute_score_loss_init_hack_pit(mix[pit], target[pit]))
+        if pit.sum() != mix.shape[0]:
+            losses.append(self.compute_score_loss(mix[~pit], utils.shuffle_sources(target[~pit])))
+        return torch.cat(losses).mean()
+
+    @torch.no_grad()
+    def validation_score_loss(self, batch):
+        """The val/score_loss of validation_step (diffsep.py:476-487) for init_hack 5 and for the plain loss; the
+        memory-heavier PIT variants of init_hack 6 / 7 (:183-303) are not provided."""
+        (mix, target), *stats = self.normalize_batch(batch)
+        if self.init_hack in (6, 7):
+            raise NotImplementedError(f"init_hack = {self.init_hack}: compute_score_loss_with_pit[_allthetime] "
+                                      "(diffsep.py:183-303) is not built (SURVEY 8f-4)")
+        if self.init_hack == 5:
+            return self.train_step_init_5(mix, target)
+        return self.compute_score_loss(mix, target)
 
     def eval(self, no_ema=False):  # the reference swaps EMA weights in unless no_ema (diffsep.py:586-606)
         return super().train(False)

@@ -155,6 +155,31 @@ def energy_envelope(mix: torch.Tensor, out: torch.Tensor, avg_len: int):
           "energy_envelope")
 
 
+def pc_perturb(p: SdeParams, x, t, y=None, noise=None, seed=0, draw=0, x_mean=None):
+    """Marginal sample in place: x holds the clean sources on entry, mean(x0, t) + L(t) z on return (ditsep_pc_perturb)."""
+    _cuda(x, t, y, noise, x_mean)
+    for n, v in (("x", x), ("t", t), ("y", y), ("noise", noise), ("x_mean", x_mean)):
+        _f32c(v, n)
+    B, L = _state_dims(x, p)
+    check(_lib.load().ditsep_pc_perturb(C.byref(p), _ptr(x), _ptr(noise), seed, draw, _ptr(t), _ptr(y), _ptr(x_mean), B, L,
+                                        None, _stream()), "pc_perturb")
+
+
+def score_loss(p: SdeParams, pred, t, noise=None, seed=0, draw=0) -> torch.Tensor:
+    """(B,) f32: mean over (source, sample) of (L(t) pred + z)^2 (ditsep_score_loss); z = `noise` or the Philox draw."""
+    _cuda(pred, t, noise)
+    for n, v in (("pred", pred), ("t", t), ("noise", noise)):
+        _f32c(v, n)
+    B, L = _state_dims(pred, p)
+    if noise is not None and noise.numel() != pred.numel():
+        raise _lib.DitsepError("score_loss: noise must have the prediction's shape")
+    loss = torch.empty(B, device=pred.device, dtype=torch.float32)
+    work = torch.empty(256 * B, device=pred.device, dtype=torch.float64)
+    check(_lib.load().ditsep_score_loss(C.byref(p), _ptr(pred), _ptr(noise), seed, draw, _ptr(t), _ptr(loss), _ptr(work), B, L,
+                                        _stream()), "score_loss")
+    return loss
+
+
 def sb_step(x, f, y, coef, *, x_out=None, x_in=None, y_in=None, est=None, noise=None, use_noise=False, seed=0, draw=0,
             lengths=None):
     """One Schroedinger-bridge sampler update with the EDM preconditioning folded in (ditsep_sb_step):

@@ -240,6 +240,20 @@ class MixSDE(SDE):
         self.send_to(x0.device)
         return self._mean(x0, t), self._std(t)
 
+    def sample_time_varprop(self, n, t_eps=0.0, device=None):
+        """Times with density proportional to the noise standard deviation sqrt(_var(t)), by rejection under the
+        constant envelope sqrt(_var(T)) (sdes.py:261-275)."""
+        top = float(self._var(torch.tensor([float(self.T)], device=device)).sqrt())
+        kept, have = [], 0
+        while have < n:
+            m = 3 * (n - have)
+            t = torch.empty(m, device=device).uniform_(t_eps, self.T)
+            u = torch.empty(m, device=device).uniform_(0, top)
+            t = t[u < self._var(t).sqrt()]
+            kept.append(t)
+            have += t.shape[0]
+        return torch.cat(kept)[:n]
+
     @staticmethod
     def mult_std(std, x):
         return std @ x

@@ -1,4 +1,5 @@
-"""Batch standardisation helpers (mirror of src/utils/separate.py:56-67)."""
+"""Batch standardisation and source-order helpers (mirror of src/utils/separate.py)."""
+import torch
 
 
 def normalize_batch(batch):
@@ -16,3 +17,19 @@ def normalize_batch(batch):
 
 def denormalize_batch(x, mean, std):
     return x * std + mean
+
+
+def shuffle_sources(x):
+    """A different random source order per batch entry (src/utils/separate.py:3-21)."""
+    if x.ndim <= 1:
+        return x
+    order = torch.argsort(torch.rand(x.shape[:2], device=x.device), dim=1)
+    return torch.gather(x, 1, order.reshape(order.shape + (1,) * (x.ndim - 2)).expand_as(x))
+
+
+def power_order_sources(x):
+    """Sources ordered by increasing variance over the last axis (src/utils/separate.py:35-53)."""
+    if x.ndim <= 1:
+        return x
+    order = torch.argsort(torch.var(x, dim=-1), dim=1)
+    return torch.gather(x, 1, order.reshape(order.shape + (1,) * (x.ndim - 2)).expand_as(x))

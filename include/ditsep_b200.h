@@ -85,6 +85,19 @@ int ditsep_pc_langevin(int n_src, float* x, const float* score, const float* noi
                        int B, int64_t L, const int* lengths, void* stream);
 /* PriorMixSDE._std_sigma_mix (sdes.py:480-492): out (B, 1, L) = 0.5 sqrt(max(box_{avg_len}(mix^2), 1e-4)). */
 int ditsep_energy_envelope(const float* mix, float* out, int B, int64_t L, int avg_len, void* stream);
+/* Training / validation side (forward values only; no backward kernels are provided).
+ * ditsep_pc_perturb: the marginal sample of DiffSepModel.sample_prior's default branch (src/diffsep.py:113-121,176-181):
+ * x holds the clean sources x0 (B, n_src, L) on entry and x_t = mean(x0, t) + L(t) z on return, with
+ * MixSDE.marginal_prob / mult_std (src/sdes/sdes.py:288-330) or OUVESDE's (:662-685) in closed form; x_mean (optional)
+ * receives the mean; z from `noise` or Philox(seed, draw).  PriorMixSDE (elem_scale set) is rejected. */
+int ditsep_pc_perturb(const ditsep_sde_params* host_p, float* x, const float* noise, uint64_t seed, uint64_t draw,
+                      const float* t, const float* y, float* x_mean, int B, int64_t L, const int* lengths, void* stream);
+/* ditsep_score_loss: loss[b] = mean over (source, sample) of (L(t_b) pred + z)^2, i.e. compute_score_loss
+ * (src/diffsep.py:344-358: sde.mult_std, MSELoss(L_score, -z), mean over the last two axes).  z from `noise`, or
+ * regenerated from the Philox stream ditsep_pc_perturb consumed (same seed / draw).  workspace: DEVICE scratch of at
+ * least 256 * B doubles (per-block partial sums, reduced in a fixed order: bit-reproducible). */
+int ditsep_score_loss(const ditsep_sde_params* host_p, const float* pred, const float* noise, uint64_t seed, uint64_t draw,
+                      const float* t, float* loss, double* workspace, int B, int64_t L, void* stream);
 /* One step of the Schroedinger-bridge samplers (get_sb_sampler, src/sdes/__init__.py:284-389: sde_sampler :288-333,
  * ode_sampler :335-382) with DiffSepOU.forward's EDM preconditioning (src/diffsep.py:813-828, coefficients :1165-1202)
  * folded into the same pass.  x, f: (B, n_src, L) f32 state and raw network output (f may be NULL: est = 0);

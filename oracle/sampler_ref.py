@@ -10,6 +10,8 @@ TEST INFRASTRUCTURE (see ``oracle/__init__.py``).  Restates
 * ``AnnealedLangevinDynamics.update_fn``    -- src/sdes/correctors.py:70-84
 * ``get_pc_sampler``         -- src/sdes/__init__.py:133-193
 * ``normalize_batch``        -- src/utils/separate.py:56-67
+* ``sample_prior``, ``compute_score_loss``, ``compute_score_loss_init_hack_pit`` (forward values)
+                             -- src/diffsep.py:113-181, 305-358
 * ``SBVESDE``, ``get_sb_sampler``, ``DiffSepOU.forward`` (EDM preconditioning)
                              -- src/sdes/sdes.py:701-779, src/sdes/__init__.py:284-389, src/diffsep.py:813-828,1165-1202
 
@@ -372,6 +374,51 @@ def sb_sampler_ref(sde: SBVESDERef, model, y: Tensor, noise: Optional[NoiseFn] =
                 raise ValueError("Invalid type. Choose 'ode' or 'sde'.")
             sig_p, sigb_p, al_p = sig, sigb, al
         return xt, n_steps
+
+
+# --------------------------------------------------------------------------- score-matching loss, forward
+def sample_prior_ref(sde: MixSDERef, mix: Tensor, target: Tensor, time: Tensor, z: Tensor, init_hack=0,
+                     t_rev_init: float = 0.03, select4: Optional[Tensor] = None):
+    """``DiffSepModel.sample_prior`` (src/diffsep.py:113-181) with the time draw, the normal draw and (init_hack 4) the
+    Bernoulli selection passed in: returns (x_t, time, L, z)."""
+    true_mix = torch.broadcast_to(mix, target.shape) / target.shape[1]
+    if init_hack == 4:
+        time = torch.where(select4, torch.ones_like(time) * sde.T, time)
+    mean, L = sde.mean(target, time), sde.std(time)
+    if init_hack in (1, 4):
+        keep = (time < sde.T - t_rev_init) if init_hack == 1 else ~select4
+        keep = torch.broadcast_to(keep[:, None, None], z.shape)
+        z = torch.where(keep, z, z + torch.linalg.solve(L, true_mix - mean))
+        return mean + L @ z, time, L, z
+    if init_hack in (2, 3):
+        Tm = sde.T - t_rev_init
+        beta = torch.clamp((time - Tm) / (sde.T - Tm), min=0.0, max=1.0)[:, None, None]
+        x_t = true_mix * beta + mean * (1.0 - beta) + L @ z
+        if init_hack == 3:
+            z = torch.linalg.solve(L, x_t - mean)
+        return x_t, time, L, z
+    return mean + L @ z, time, L, z
+
+
+def score_loss_ref(model, sde: MixSDERef, mix: Tensor, target: Tensor, time: Tensor, z: Tensor, **hack) -> Tensor:
+    """``compute_score_loss`` (src/diffsep.py:344-358) with MSELoss(reduction="none"): (B,) per-item means."""
+    x_t, time, L, z = sample_prior_ref(sde, mix, target, time, z, **hack)
+    pred = model(x_t, time, mix)
+    return ((L @ pred) - (-z)).square().mean(dim=(-2, -1))
+
+
+def score_loss_init_hack_pit_ref(model, sde: MixSDERef, mix: Tensor, target: Tensor, z0: Tensor) -> Tensor:
+    """``compute_score_loss_init_hack_pit`` (src/diffsep.py:305-338)."""
+    import itertools
+    time = torch.ones(mix.shape[0]) * sde.T
+    true_mix = torch.broadcast_to(mix, target.shape) / target.shape[1]
+    losses = []
+    for perm in itertools.permutations(range(target.shape[1])):
+        mean, L = sde.mean(target[:, perm, :], time), sde.std(time)
+        z = z0 + torch.linalg.solve(L, true_mix - mean)
+        pred = model(mean + L @ z, time, mix)
+        losses.append(((L @ pred) + z).square().mean(dim=(-2, -1)))
+    return torch.stack(losses, dim=1).min(dim=1).values
 
 
 def normalize_batch_ref(mix: Tensor):

@@ -26,4 +26,5 @@ def golden():
             "ref_s0p01": np.load(os.path.join(d, "reference_outputs_s0p01.npz")),
             "c1_s0p01": np.load(os.path.join(d, "sampler_c1_s0p01.npz")),
             "variants": np.load(os.path.join(d, "variants.npz")),
-            "sb": np.load(os.path.join(d, "sb.npz"))}
+            "sb": np.load(os.path.join(d, "sb.npz")),
+            "loss": np.load(os.path.join(d, "loss.npz"))}

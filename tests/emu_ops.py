@@ -17,7 +17,7 @@ import torch.nn.functional as F
 
 from ditsep_b200 import ops
 
-_NAMES = ["conv1d_tc", "conv1d_in", "conv1d_out", "vae_sample", "pc_corrector", "pc_predictor", "pc_prior", "pc_langevin", "energy_envelope", "sb_step", "philox_normal", "stft_compress", "expand_istft", "gn_stats",
+_NAMES = ["conv1d_tc", "conv1d_in", "conv1d_out", "vae_sample", "pc_corrector", "pc_predictor", "pc_prior", "pc_langevin", "pc_perturb", "score_loss", "energy_envelope", "sb_step", "philox_normal", "stft_compress", "expand_istft", "gn_stats",
           "gn_sums", "gn_finalize", "gn_apply", "gn_apply_srcs", "gn_small", "fir_resample", "conv_direct", "attention", "temb_mlp", "temb_dense", "output_layer"]
 
 
@@ -41,6 +41,9 @@ def _coef(p, mode, t):
         elif mode == "predictor":
             G = p.sigma_min * ratio ** t * math.sqrt(2 * logsig) * math.sqrt(dt)
             c.update(a0=z + 1 + lam * dt, a1=z - lam * dt, a2=G * G, b0=G)
+        elif mode == "perturb":
+            e = torch.exp(-lam * t)
+            c.update(a0=e, a1=1 - e, b0=r2, b1=r1 - r2)
         else:
             c.update(a0=z, a4=z + 0.5, b0=r2, b1=r1 - r2)
     else:
@@ -53,6 +56,9 @@ def _coef(p, mode, t):
         elif mode == "predictor":
             G = p.sigma_min * ratio ** t * math.sqrt(2 * logsig) * math.sqrt(dt)
             c.update(a0=z + 1 + th * dt, a4=z - th * dt, a2=G * G, b0=G)
+        elif mode == "perturb":
+            e = torch.exp(-th * t)
+            c.update(a0=e, a4=1 - e, b0=std)
         else:
             c.update(a0=z, a4=z + 1, b0=std)
     return c
@@ -93,6 +99,22 @@ def pc_predictor(p, x, score, t, y, noise=None, seed=0, draw=0, x_mean=None, len
 
 def pc_prior(p, x, y, noise=None, seed=0, draw=0, lengths=None):
     _pc(p, "prior", x, None, None, y, noise, None, lengths)
+
+
+def pc_perturb(p, x, t, y=None, noise=None, seed=0, draw=0, x_mean=None):
+    _pc(p, "perturb", x, None, t, y if p.sde == 1 else None, noise, x_mean)
+
+
+def score_loss(p, pred, t, noise=None, seed=0, draw=0):
+    """csrc/pc_step.cu::score_loss_*_kernel: mean over (source, sample) of (b0 pred + b1 mean_src(pred) + z)^2."""
+    if noise is None:
+        raise AssertionError("the CPU stand-in needs the noise tensor (Philox lives in the kernel)")
+    B = pred.shape[0]
+    c = _coef(p, "perturb", t.double())
+    v = lambda a: a.reshape(B, *([1] * (pred.ndim - 1)))  # noqa: E731
+    pr = pred.double()
+    r = v(c["b0"]) * pr + v(c["b1"]) * pr.mean(dim=1, keepdim=True) + noise.double()
+    return r.square().flatten(1).mean(dim=1).float()
 
 
 def pc_langevin(n_src, x, score, noise, step, x_mean=None, lengths=None):

@@ -502,3 +502,65 @@ def test_diffsep_ou_sb_separation_vs_oracle():
     e, e2 = rel_l2(x, ref), rel_l2(x2, x)
     print(f"DiffSepOU SB-ODE N=3 fp32: rel-L2 vs oracle {e:.3e}; fused vs un-fused route {e2:.3e}")
     assert n == 50 and e < 1e-3 and e2 < 1e-5
+
+
+# ------------------------------------------------------------------ score-matching loss, forward values
+def test_score_loss_forward_vs_reference_golden(golden):
+    """sample_prior / compute_score_loss / init-hack PIT loss (src/diffsep.py:113-181, 305-358) through the perturbation and
+    reduction kernels against the unmodified reference's values (tests/golden/loss.npz)."""
+    from test_host_logic import check_loss_against_reference
+    check_loss_against_reference(golden["loss"], DEV)
+
+
+@pytest.mark.parametrize("kind,n_src,L", [("mix", 2, 4096), ("mix", 3, 1001), ("ouve", 2, 2048), ("ouve", 1, 515)])
+def test_perturb_and_loss_kernels_vs_emulation(kind, n_src, L):
+    """ditsep_pc_perturb / ditsep_score_loss against their double-precision restatement, vector and scalar-tail paths,
+    1..3 sources, both SDEs; the Philox path regenerates in the loss kernel exactly the draw the perturbation used."""
+    import emu_ops
+    B = 3
+    g = torch.Generator().manual_seed(7 + L)
+    x0, z, pred = (torch.randn(B, n_src, L, generator=g) for _ in range(3))
+    y = torch.randn(B, 1, L, generator=g)
+    t = torch.tensor([0.04, 0.5, 1.0])
+    sde = sdes.MixSDE(n_src, 2.0, 0.05, 0.5, N=30) if kind == "mix" else sdes.OUVESDE(1.5, 0.05, 0.5, N=30)
+    p = sde.fused_params(n_src=n_src)
+    want_x, want_m = x0.clone(), torch.empty_like(x0)
+    emu_ops.pc_perturb(p, want_x, t, y=y, noise=z, x_mean=want_m)
+    got_x, got_m = x0.to(DEV).clone(), torch.empty_like(x0, device=DEV)
+    ops.pc_perturb(p, got_x, t.to(DEV), y=y.to(DEV), noise=z.to(DEV), x_mean=got_m)
+    assert rel_l2(got_x, want_x) < 2e-6 and rel_l2(got_m, want_m) < 2e-6
+    if kind == "mix":  # against the class's own matrix form (marginal_prob / mult_std, host torch)
+        mean, Lm = sde.marginal_prob(x0, t)
+        assert rel_l2(got_x, mean + sde.mult_std(Lm, z)) < 2e-6
+    want = emu_ops.score_loss(p, pred, t, noise=z)
+    got = ops.score_loss(p, pred.to(DEV), t.to(DEV), noise=z.to(DEV))
+    got2 = ops.score_loss(p, pred.to(DEV), t.to(DEV), noise=z.to(DEV))
+    assert float(((got.cpu() - want) / want).abs().max()) < 2e-6 and torch.equal(got, got2)
+    if L % 4 == 0:
+        zz = torch.empty(B, n_src, L, device=DEV)
+        ops.philox_normal(zz, 123, 9)
+        a, b = x0.to(DEV).clone(), x0.to(DEV).clone()
+        ops.pc_perturb(p, a, t.to(DEV), y=y.to(DEV), noise=zz)
+        ops.pc_perturb(p, b, t.to(DEV), y=y.to(DEV), seed=123, draw=9)
+        assert torch.equal(a, b)
+        assert torch.equal(ops.score_loss(p, pred.to(DEV), t.to(DEV), noise=zz),
+                           ops.score_loss(p, pred.to(DEV), t.to(DEV), seed=123, draw=9))
+
+
+def test_validation_score_loss_with_the_real_network_vs_oracle():
+    """compute_score_loss with the NCSN++ behind it (fp32, T = 7810) against the oracle's restatement around the oracle
+    network on the same time vector and noise; validation_score_loss (init_hack 5) runs end to end."""
+    model, sd, cfg = build_model("fp32", DEV, N=30)
+    from ditsep_b200.utils.synth import synth_mixtures
+    (mixn, tgt), *_ = model.normalize_batch(synth_mixtures(2, 2, 7810, seed=1234))
+    time = torch.tensor([0.3, 0.9])
+    z = S.NoiseTape(72).draw(0, tgt.shape)
+    model.init_hack = 5
+    got = model.compute_score_loss(mixn.to(DEV), tgt.to(DEV), time=time.to(DEV), noise=z.to(DEV))
+    net = lambda a, b, c: R.score_forward_ref(sd, cfg, a, b, c)  # noqa: E731
+    want = S.score_loss_ref(net, S.MixSDERef(2, 2.0, 0.05, 0.5, N=30), mixn, tgt, time, z)
+    print(f"score loss with the real network: {got.tolist()} vs oracle {want.tolist()}")
+    assert got.shape == (2,) and float(((got.cpu() - want) / want).abs().max()) < 1e-3
+    torch.manual_seed(0)
+    v = model.validation_score_loss((mixn.to(DEV), tgt.to(DEV)))
+    assert v.ndim == 0 and torch.isfinite(v)
