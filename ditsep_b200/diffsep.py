@@ -156,7 +156,8 @@ class DiffSepModel(_Base):
         from . import ops
         x_t, time, L, z = self.sample_prior(mix, target, time=time, noise=noise)
         pred = self(x_t, time, mix).to(torch.float32).contiguous()
-        per_item = ops.score_loss(self.sde.fused_params(n_src=target.shape[1]), pred, time.to(torch.float32).contiguous(), noise=z)
+        per_item = ops.score_loss(self.sde.fused_params(n_src=target.shape[1]), pred, time.to(torch.float32).contiguous(),
+                                  noise=z.contiguous())  # linalg.solve (init_hack 1 / 3 / 4) returns column-major batches
         return self._loss_reduce(per_item)
 
     @torch.no_grad()
