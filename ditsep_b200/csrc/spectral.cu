@@ -16,6 +16,7 @@
 // (src/models/diffsep/score_models.py:41-124) over torchaudio Spectrogram /
 // InverseSpectrogram (= torch.stft / torch.istft, center=True, pad_mode="constant").
 #include "common.cuh"
+#include "dft_codelets.cuh"
 
 namespace ditsep {
 
@@ -41,6 +42,45 @@ __device__ __forceinline__ void fill_table(float2* tab) {
 // 255-point complex DFT of zbuf (in place, via ybuf), executed by one warp.
 // kInverse uses conjugated twiddles (no 1/255 scaling).  Index maps: n = 17 n1 + n2,
 // k = k1 + 15 k2;  Z[k] = sum_n2 W17^{n2 k2} W255^{n2 k1} sum_n1 z[17 n1 + n2] W15^{n1 k1}.
+#ifndef DITSEP_DFT_CODELETS
+#define DITSEP_DFT_CODELETS 1
+#endif
+#if DITSEP_DFT_CODELETS
+// Register-resident sub-transforms (csrc/dft_codelets.cuh, generated): lane n2 < 17 runs one straight-line 15-point DFT
+// (Good-Thomas 3 x 5, literal twiddles) over its column, lane k1 < 15 one paired 17-point DFT over its row; the only
+// table reads left are the 15 inter-pass twiddles per lane.  ~750 warp instructions per transform against ~2600 for
+// the table-driven loops below (kept behind -DDITSEP_DFT_CODELETS=0 for A/B timing).  The inverse is the forward
+// transform of the input with real and imaginary parts swapped, swapped back on the way out.
+template <bool kInverse>
+__device__ __forceinline__ void warp_dft255(float2* zbuf, float2* ybuf, const float2* tab, int lane) {
+  if (lane < 17) {
+    float2 in[15], out[15];
+#pragma unroll
+    for (int n1 = 0; n1 < 15; ++n1) {
+      const float2 v = zbuf[17 * n1 + lane];
+      in[n1] = kInverse ? make_float2(v.y, v.x) : v;
+    }
+    dft15(in, out);
+    int tw = 0;
+#pragma unroll
+    for (int k1 = 0; k1 < 15; ++k1) {
+      ybuf[k1 * 17 + lane] = cmul(out[k1], tab[tw]);  // W255^{n2 k1} = tab[2 n2 k1 mod 510]
+      tw += 2 * lane;
+      if (tw >= kNfft) tw -= kNfft;
+    }
+  }
+  __syncwarp();
+  if (lane < 15) {
+    float2 in[17], out[17];
+#pragma unroll
+    for (int n2 = 0; n2 < 17; ++n2) in[n2] = ybuf[lane * 17 + n2];
+    dft17(in, out);
+#pragma unroll
+    for (int k2 = 0; k2 < 17; ++k2) zbuf[lane + 15 * k2] = kInverse ? make_float2(out[k2].y, out[k2].x) : out[k2];
+  }
+  __syncwarp();
+}
+#else
 template <bool kInverse>
 __device__ __forceinline__ void warp_dft255(float2* zbuf, float2* ybuf, const float2* tab, int lane) {
   for (int idx = lane; idx < kHalf; idx += 32) {
@@ -82,6 +122,7 @@ __device__ __forceinline__ void warp_dft255(float2* zbuf, float2* ybuf, const fl
   }
   __syncwarp();
 }
+#endif
 
 // ------------------------------------------------------------------------------- forward
 constexpr int kFT = 8;                               // frames per block

@@ -61,7 +61,7 @@ def gen_dft5(v, tag):
 
 def gen_dft15():
     L = ["// out[k] = sum_n in[n] e^{-2 pi i n k / 15}",
-         "DFT_HD inline void dft15(const float2 (&in)[15], float2 (&out)[15]) {",
+         "DFT_HD void dft15(const float2 (&in)[15], float2 (&out)[15]) {",
          "  float2 t[3][5];  // t[n1][n2] = in[(5 n1 + 3 n2) mod 15]"]
     for n1 in range(3):
         for n2 in range(5):
@@ -79,7 +79,7 @@ def gen_dft15():
 
 def gen_dft17():
     L = ["// out[k] = sum_n in[n] e^{-2 pi i n k / 17}",
-         "DFT_HD inline void dft17(const float2 (&in)[17], float2 (&out)[17]) {",
+         "DFT_HD void dft17(const float2 (&in)[17], float2 (&out)[17]) {",
          "  float2 a[9], b[9];"]
     for n in range(1, 9):
         L.append(f"  a[{n}] = make_float2(in[{n}].x + in[{17 - n}].x, in[{n}].y + in[{17 - n}].y);")
@@ -110,7 +110,7 @@ HEADER = """// GENERATED by scripts/gen_dft_codelets.py -- do not edit; regenera
 #if defined(__CUDACC__)
 #define DFT_HD __host__ __device__ __forceinline__
 #else
-#define DFT_HD
+#define DFT_HD inline
 struct float2 { float x, y; };
 static inline float2 make_float2(float x, float y) { float2 r; r.x = x; r.y = y; return r; }
 #endif
