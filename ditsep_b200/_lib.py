@@ -48,6 +48,8 @@ SIGNATURES = {
                                   c_int, c_int64, c_void_p, c_void_p]),
     "ditsep_score_loss": (c_int, [C.POINTER(SdeParams), c_void_p, c_void_p, c_uint64, c_uint64, c_void_p, c_void_p, c_void_p,
                                   c_int, c_int64, c_void_p]),
+    "ditsep_score_loss_sigma": (c_int, [c_void_p, c_void_p, c_uint64, c_uint64, c_void_p, c_void_p, c_void_p, c_int, c_int,
+                                        c_int64, c_void_p]),
     "ditsep_sb_step": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_uint64, c_uint64, c_void_p, c_void_p,
                                c_void_p, c_void_p, c_void_p, c_int, c_int, c_int64, c_void_p, c_void_p]),
     "ditsep_conv1d_tc": (c_int, [c_void_p, c_int, c_int, c_int, c_int64, c_void_p, c_int, c_int, c_int, c_int, c_int, c_int,

@@ -373,7 +373,7 @@ extern "C" int ditsep_energy_envelope(const float* mix, float* out, int B, int64
 // One launch per sampler step (get_sb_sampler, sdes/__init__.py:284-389) with DiffSepOU's EDM preconditioning
 // (diffsep.py:813-828) folded in.  coef row of sample b: [w_prev, w_est, w_y, w_z, c_skip, c_out, f_div, c_in_next]:
 //   est = c_skip x + c_out (f / f_div)                    (c_skip = 0, c_out = f_div = 1: est = f)
-//   x'  = (w_prev x + w_est est) + w_y y | w_z z           (the reference's evaluation order, unfused roundings)
+//   x'  = (w_prev x + w_est est) + w_y y | w_z z | both     (the reference's evaluation order, unfused roundings)
 //   x_in = c_in_next x',  y_in = c_in_next y               (the NEXT network evaluation's scaled inputs)
 namespace ditsep {
 __global__ void __launch_bounds__(256) sb_step_kernel(const float* __restrict__ x, const float* __restrict__ f,
@@ -445,7 +445,8 @@ __global__ void __launch_bounds__(256) sb_step_kernel(const float* __restrict__ 
         const bool live = l0 + j < len;
         const float est = f ? __fadd_rn(__fmul_rn(c_skip, xv[j]), __fmul_rn(c_out, __fdiv_rn(fv[j], f_div))) : 0.f;
         float v = __fadd_rn(__fmul_rn(w_prev, xv[j]), __fmul_rn(w_est, est));
-        v = __fadd_rn(v, use_noise ? __fmul_rn(w_z, zv[j]) : __fmul_rn(w_y, yv[j]));
+        if (use_noise != 1) v = __fadd_rn(v, __fmul_rn(w_y, yv[j]));  // 0: ODE update; 2: marginal sample (mean first, then noise)
+        if (use_noise != 0) v = __fadd_rn(v, __fmul_rn(w_z, zv[j]));
         eo[j] = live ? est : 0.f;
         xo[j] = live ? v : 0.f;
         uo[j] = live ? __fmul_rn(c_in, v) : 0.f;
@@ -474,7 +475,8 @@ extern "C" int ditsep_sb_step(const float* x, const float* f, const float* y, co
   DITSEP_REQUIRE(x != nullptr && coef != nullptr, "sb_step: null state or coefficient table");
   DITSEP_REQUIRE(B > 0 && L > 0 && n_src >= 1 && n_src <= 64, "sb_step: bad shape B=%d n_src=%d L=%lld", B, n_src, (long long)L);
   DITSEP_REQUIRE(x_out || x_in || y_in || est_out, "sb_step: no output requested");
-  DITSEP_REQUIRE(use_noise || y != nullptr, "sb_step: the ODE update (use_noise = 0) needs the mixture y");
+  DITSEP_REQUIRE(use_noise >= 0 && use_noise <= 2, "sb_step: use_noise=%d (0: y term, 1: noise term, 2: both)", use_noise);
+  DITSEP_REQUIRE(use_noise == 1 || y != nullptr, "sb_step: the y term (use_noise = 0 or 2) needs the mixture y");
   DITSEP_REQUIRE(!y_in || y != nullptr, "sb_step: y_in requested without y");
   if ((L & 3) == 0) {
     uintptr_t a = reinterpret_cast<uintptr_t>(x) | reinterpret_cast<uintptr_t>(f) | reinterpret_cast<uintptr_t>(y) |
@@ -505,9 +507,12 @@ template <int NS>
 __global__ void __launch_bounds__(256) score_loss_partial_kernel(ditsep_sde_params p, const float* __restrict__ pred,
                                                                  const float* __restrict__ noise, uint64_t seed,
                                                                  uint64_t draw, const float* __restrict__ t,
+                                                                 const float* __restrict__ sigma,
                                                                  double* __restrict__ partial, int64_t L) {
   const int b = blockIdx.y;
-  const Coef c = make_coef(p, kPerturb, t[b]);
+  Coef c = {1.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+  if (sigma) c.b0 = sigma[b];  // scalar std per mixture given by the caller (SBVESDE: closed form kept on the host)
+  else c = make_coef(p, kPerturb, t[b]);
   const int64_t nvec = (L + 3) / 4;
   const bool vec = (L & 3) == 0;
   const float inv_n = 1.0f / (float)NS;
@@ -578,11 +583,11 @@ __global__ void __launch_bounds__(32) score_loss_final_kernel(const double* __re
 }
 }  // namespace ditsep
 
-extern "C" int ditsep_score_loss(const ditsep_sde_params* hp, const float* pred, const float* noise, uint64_t seed,
-                                 uint64_t draw, const float* t, float* loss, double* workspace, int B, int64_t L,
-                                 void* stream) {
-  DITSEP_REQUIRE(hp && pred && t && loss && workspace, "score_loss: null argument");
-  DITSEP_REQUIRE(hp->sde == DITSEP_SDE_MIX || hp->sde == DITSEP_SDE_OUVE, "score_loss: unknown sde %d", hp->sde);
+static int launch_score_loss(const ditsep_sde_params* hp, const float* pred, const float* noise, uint64_t seed,
+                             uint64_t draw, const float* t, const float* sigma, float* loss, double* workspace, int B,
+                             int64_t L, void* stream) {
+  DITSEP_REQUIRE(hp && pred && (t || sigma) && loss && workspace, "score_loss: null argument");
+  DITSEP_REQUIRE(sigma || hp->sde == DITSEP_SDE_MIX || hp->sde == DITSEP_SDE_OUVE, "score_loss: unknown sde %d", hp->sde);
   DITSEP_REQUIRE(hp->n_src >= 1 && hp->n_src <= kMaxSrc, "score_loss: n_src=%d unsupported (1..%d)", hp->n_src, kMaxSrc);
   DITSEP_REQUIRE(hp->elem_scale == nullptr, "score_loss: PriorMixSDE's envelope is not supported here");
   DITSEP_REQUIRE(B > 0 && L > 0, "score_loss: empty input B=%d L=%lld", B, (long long)L);
@@ -593,14 +598,34 @@ extern "C" int ditsep_score_loss(const ditsep_sde_params* hp, const float* pred,
   dim3 grid(parts, B);
   cudaStream_t st = (cudaStream_t)stream;
   switch (hp->n_src) {
-    case 1: score_loss_partial_kernel<1><<<grid, 256, 0, st>>>(*hp, pred, noise, seed, draw, t, workspace, L); break;
-    case 2: score_loss_partial_kernel<2><<<grid, 256, 0, st>>>(*hp, pred, noise, seed, draw, t, workspace, L); break;
-    case 3: score_loss_partial_kernel<3><<<grid, 256, 0, st>>>(*hp, pred, noise, seed, draw, t, workspace, L); break;
-    default: score_loss_partial_kernel<4><<<grid, 256, 0, st>>>(*hp, pred, noise, seed, draw, t, workspace, L); break;
+    case 1: score_loss_partial_kernel<1><<<grid, 256, 0, st>>>(*hp, pred, noise, seed, draw, t, sigma, workspace, L); break;
+    case 2: score_loss_partial_kernel<2><<<grid, 256, 0, st>>>(*hp, pred, noise, seed, draw, t, sigma, workspace, L); break;
+    case 3: score_loss_partial_kernel<3><<<grid, 256, 0, st>>>(*hp, pred, noise, seed, draw, t, sigma, workspace, L); break;
+    default: score_loss_partial_kernel<4><<<grid, 256, 0, st>>>(*hp, pred, noise, seed, draw, t, sigma, workspace, L); break;
   }
   if (int rc = check_launch("score_loss_partial_kernel")) return rc;
   score_loss_final_kernel<<<B, 32, 0, st>>>(workspace, loss, parts, 1.0 / ((double)hp->n_src * (double)L));
   return check_launch("score_loss_final_kernel");
+}
+
+extern "C" int ditsep_score_loss(const ditsep_sde_params* hp, const float* pred, const float* noise, uint64_t seed,
+                                 uint64_t draw, const float* t, float* loss, double* workspace, int B, int64_t L,
+                                 void* stream) {
+  DITSEP_REQUIRE(t != nullptr, "score_loss: null time vector");
+  return launch_score_loss(hp, pred, noise, seed, draw, t, nullptr, loss, workspace, B, L, stream);
+}
+
+extern "C" int ditsep_score_loss_sigma(const float* pred, const float* noise, uint64_t seed, uint64_t draw,
+                                       const float* sigma, float* loss, double* workspace, int B, int n_src, int64_t L,
+                                       void* stream) {
+  DITSEP_REQUIRE(sigma != nullptr, "score_loss_sigma: null sigma");
+  ditsep_sde_params p = {};
+  p.sde = DITSEP_SDE_OUVE;
+  p.n_src = n_src;
+  p.sigma_min = 1.f;
+  p.sigma_max = 2.f;
+  p.N = 1;
+  return launch_score_loss(&p, pred, noise, seed, draw, nullptr, sigma, loss, workspace, B, L, stream);
 }
 
 extern "C" int ditsep_philox_normal(float* out, int64_t n, uint64_t seed, uint64_t draw, void* stream) {

@@ -341,6 +341,81 @@ class DiffSepOU(DiffSepModel):
         ops.sb_step(xt, f, mix, coef[1], est=out)
         return out
 
+    # ---- score-matching loss, FORWARD VALUE only (diffsep.py:796-811, 832-899, 931-942) -------------------
+    def sample_time(self, x):
+        return x.new_zeros(x.shape[0]).uniform_(self.t_eps, self.t_max)
+
+    def sample_prior(self, mix, target, time=None, noise=None):
+        """diffsep.py:800-811: x_t = mean(target, mix, t) + std(t) z, returned with (time, sigma broadcastable, z).  One
+        fused launch either way: the OU perturbation row of the PC coefficient table (OUVESDE) or ops.sb_step in its
+        "mean, then noise" mode with SBVESDE's host-side closed forms as the coefficient row."""
+        from . import ops
+        time = self.sample_time(target) if time is None else time
+        z = self._draw(target, noise)
+        tgt = target.to(torch.float32).contiguous()
+        mixc = mix.to(torch.float32).contiguous()
+        std = self.sde._std(time)
+        if self.is_edm:
+            sigma_t, sigma_T, sigma_bart, alpha_t, alpha_T, alpha_bart = self.sde._sigmas_alphas(time)
+            coef = torch.zeros(target.shape[0], 8, device=target.device)
+            coef[:, 0] = alpha_t * sigma_bart ** 2 / (sigma_T ** 2 + self.sde.eps)    # w_xt (sdes.py:757)
+            coef[:, 2] = alpha_bart * sigma_t ** 2 / (sigma_T ** 2 + self.sde.eps)    # w_yt (:758)
+            coef[:, 3] = std
+            coef[:, 5:] = 1.0
+            x_t = torch.empty_like(tgt)
+            ops.sb_step(tgt.reshape(tgt.shape[0], tgt.shape[1], -1), None, mixc, coef, x_out=x_t, noise=z, use_noise=2)
+        else:
+            x_t = tgt.clone()
+            ops.pc_perturb(self.sde.fused_params(n_src=target.shape[1]), x_t, time.to(torch.float32).contiguous(), y=mixc,
+                           noise=z)
+        return x_t, time, std[(...,) + (None,) * (x_t.ndim - std.ndim)], z
+
+    def _step(self, y, x, time=None, noise=None):
+        x_t, t, sigma, z = self.sample_prior(y, x, time=time, noise=noise)
+        return self(x_t, t, y), sigma, z
+
+    def _per_source_loss(self, pred, sigma, z):
+        """mean over the trailing axes of (sigma pred + z)^2 -> (B, n_src), the reference's
+        `loss.mean(dim=tuple(range(2 - loss.ndim, 0)))` of an un-reduced MSELoss (diffsep.py:839-840)."""
+        from . import ops
+        B, C = pred.shape[:2]
+        flat = pred.to(torch.float32).contiguous().reshape(B * C, 1, -1)
+        sig = sigma.reshape(B).to(torch.float32).repeat_interleave(C).contiguous()
+        return ops.score_loss_sigma(flat, sig, noise=z.contiguous().reshape(B * C, 1, -1)).reshape(B, C)
+
+    @torch.no_grad()
+    def compute_score_loss(self, y, x, time=None, noise=None):
+        """diffsep.py:836-841; (B, n_src) for the un-reduced loss of init_hack 5, else the scalar mean."""
+        pred, sigma, z = self._step(y, x, time=time, noise=noise)
+        return self._loss_reduce(self._per_source_loss(pred, sigma, z))
+
+    @torch.no_grad()
+    def compute_score_loss_init_hack_pit(self, mix, target, noise=None):
+        """diffsep.py:843-869 for the OU SDE.  With an SBVESDE the reference multiplies a (B,) std into a (B, C, T) tensor
+        (`sigma = std if self.is_edm`, :854) and fails for B > 1; its SB config never reaches it (init_hack_p = 0)."""
+        import itertools
+        if self.is_edm:
+            raise NotImplementedError("compute_score_loss_init_hack_pit with an SBVESDE: shape error in the reference "
+                                      "(src/diffsep.py:854-858); the diffsep_sb config sets init_hack_p = 0")
+        time = mix.new_ones(mix.shape[0]) * self.sde.T
+        z0 = self._draw(target, noise)
+        losses = []
+        for perm in itertools.permutations(range(target.shape[1])):
+            mean, std = self.sde.marginal_prob(target[:, perm, ...], time, mix)
+            sigma = std[(...,) + (None,) * (mix.ndim - time.ndim)]
+            z = z0 + (mix - mean) / sigma
+            pred = self(mix + sigma * z0, time, mix)
+            losses.append(self._per_source_loss(pred, sigma, z))
+        return torch.stack(losses, dim=1).min(dim=1).values
+
+    @torch.no_grad()
+    def validation_score_loss(self, batch):
+        """The val/score_loss of DiffSepOU.validation_step (diffsep.py:931-942)."""
+        (mix, target), *stats = self.normalize_batch(batch)
+        if self.init_hack == 5:
+            return self.train_step_init_5(mix, target)
+        return self.compute_score_loss(mix, target)
+
     def separate(self, mix, **kwargs):
         """diffsep.py:1204-1217: SB sampler for an SBVESDE, else reverse-diffusion + "ald" PC sampler; the result tuple
         is returned as the sampler gives it (not denormalised)."""

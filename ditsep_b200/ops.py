@@ -180,6 +180,24 @@ def score_loss(p: SdeParams, pred, t, noise=None, seed=0, draw=0) -> torch.Tenso
     return loss
 
 
+def score_loss_sigma(pred, sigma, noise=None, seed=0, draw=0) -> torch.Tensor:
+    """(B,) f32: mean over everything but the batch axis of (sigma[b] pred + z)^2 (ditsep_score_loss_sigma)."""
+    _cuda(pred, sigma, noise)
+    for n, v in (("pred", pred), ("sigma", sigma), ("noise", noise)):
+        _f32c(v, n)
+    B, n_src = pred.shape[0], pred.shape[1]
+    L = pred.numel() // (B * n_src)
+    if sigma.numel() != B or (noise is not None and noise.numel() != pred.numel()):
+        raise _lib.DitsepError("score_loss_sigma: sigma must be (B,), noise must have the prediction's shape")
+    if not 1 <= n_src <= 4:
+        raise _lib.DitsepError(f"score_loss_sigma: {n_src} sources (1..4)")
+    loss = torch.empty(B, device=pred.device, dtype=torch.float32)
+    work = torch.empty(256 * B, device=pred.device, dtype=torch.float64)
+    check(_lib.load().ditsep_score_loss_sigma(_ptr(pred), _ptr(noise), seed, draw, _ptr(sigma), _ptr(loss), _ptr(work), B, n_src, L,
+                                              _stream()), "score_loss_sigma")
+    return loss
+
+
 def sb_step(x, f, y, coef, *, x_out=None, x_in=None, y_in=None, est=None, noise=None, use_noise=False, seed=0, draw=0,
             lengths=None):
     """One Schroedinger-bridge sampler update with the EDM preconditioning folded in (ditsep_sb_step):
@@ -198,7 +216,7 @@ def sb_step(x, f, y, coef, *, x_out=None, x_in=None, y_in=None, est=None, noise=
     for n, v in (("y", y), ("y_in", y_in)):
         if v is not None and v.numel() != B * L:
             raise _lib.DitsepError(f"sb_step: {n} has {v.numel()} elements, expected (B, 1, L) = {B * L}")
-    check(_lib.load().ditsep_sb_step(_ptr(x), _ptr(f), _ptr(y), _ptr(noise), int(bool(use_noise)), seed, draw, _ptr(coef),
+    check(_lib.load().ditsep_sb_step(_ptr(x), _ptr(f), _ptr(y), _ptr(noise), int(use_noise), seed, draw, _ptr(coef),
                                      _ptr(x_out), _ptr(x_in), _ptr(y_in), _ptr(est), B, n_src, L, _lengths(lengths, B),
                                      _stream()), "sb_step")
 

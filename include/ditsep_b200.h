@@ -98,12 +98,17 @@ int ditsep_pc_perturb(const ditsep_sde_params* host_p, float* x, const float* no
  * least 256 * B doubles (per-block partial sums, reduced in a fixed order: bit-reproducible). */
 int ditsep_score_loss(const ditsep_sde_params* host_p, const float* pred, const float* noise, uint64_t seed, uint64_t draw,
                       const float* t, float* loss, double* workspace, int B, int64_t L, void* stream);
+/* The same reduction with the per-mixture standard deviation given by the caller: loss[b] = mean (sigma[b] pred + z)^2,
+ * DiffSepOU.compute_score_loss (src/diffsep.py:836-841) for SDEs whose closed forms stay on the host (SBVESDE). */
+int ditsep_score_loss_sigma(const float* pred, const float* noise, uint64_t seed, uint64_t draw, const float* sigma,
+                            float* loss, double* workspace, int B, int n_src, int64_t L, void* stream);
 /* One step of the Schroedinger-bridge samplers (get_sb_sampler, src/sdes/__init__.py:284-389: sde_sampler :288-333,
  * ode_sampler :335-382) with DiffSepOU.forward's EDM preconditioning (src/diffsep.py:813-828, coefficients :1165-1202)
  * folded into the same pass.  x, f: (B, n_src, L) f32 state and raw network output (f may be NULL: est = 0);
  * y: (B, 1, L) mixture; coef: DEVICE (B, 8) f32 rows [w_prev, w_est, w_y, w_z, c_skip, c_out, f_div, c_in_next]:
  *     est = c_skip x + c_out (f / f_div)          (c_skip = 0, c_out = f_div = 1 for an un-preconditioned model)
- *     x'  = w_prev x + w_est est + (use_noise ? w_z z : w_y y)      z: `noise` (tape) or Philox(seed, draw)
+ *     x'  = w_prev x + w_est est + (use_noise == 0: w_y y | 1: w_z z | 2: w_y y + w_z z)   z: `noise` or Philox(seed, draw)
+ *           (2 = the marginal sample mean(x0, y, t) + sigma z of DiffSepOU.sample_prior, src/diffsep.py:800-811)
  *     x_in = c_in_next x',  y_in = c_in_next y    (the scaled inputs of the NEXT network evaluation)
  * evaluated in the reference's order with individually rounded products.  Outputs x_out (may alias x), x_in, y_in,
  * est_out are each optional (at least one); rows are kept at 0 past lengths[b] when lengths is given. */

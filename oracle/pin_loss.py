@@ -2,7 +2,8 @@
 container only).
 
 ``python -m oracle.pin_loss`` calls the unmodified reference ``DiffSepModel.sample_prior`` (src/diffsep.py:113-181, every
-init_hack branch), ``compute_score_loss`` (:344-358) and ``compute_score_loss_init_hack_pit`` (:305-338) UNBOUND on a
+init_hack branch), ``compute_score_loss`` (:344-358), ``compute_score_loss_init_hack_pit`` (:305-338) and the ``DiffSepOU`` counterparts
+(:800-811, 832-869; OUVESDE and SBVESDE, the latter through the reference's EDM ``forward``) UNBOUND on a
 namespace that carries the attributes they read (the Lightning constructor needs hydra / omegaconf / torch_ema, absent
 here), with a closed-form score network, a fixed time vector and taped normal draws; asserts the oracle against them and
 writes the REFERENCE's outputs to tests/golden/loss.npz."""
@@ -76,6 +77,49 @@ def main():
     print(f"init-hack PIT loss: oracle vs reference max abs err {err:.2e}; {pit.tolist()}")
     assert err < 1e-5
     golden["loss_pit"] = pit.numpy()
+
+    # ---- DiffSepOU (src/diffsep.py:796-869): scalar-std SDEs; the SBVESDE goes through the reference's own EDM forward
+    DiffSepOU = sys.modules["diffsep"].DiffSepOU
+    from oracle.pin_sb import toy_net
+
+    def ou_namespace(sde, edm):
+        class NS(types.SimpleNamespace):
+            def __call__(self, xt, t, y):
+                return DiffSepOU.forward(self, xt, t, y)
+
+        ns = NS(sde=sde, is_edm=edm, sample_time=lambda x: time.clone(), loss=torch.nn.MSELoss(reduction="none"),
+                score_model=toy_net if edm else toy_score, network_scaling="1/sigma", sigma_data=0.1, c_in="edm",
+                c_out="edm", c_skip="edm")
+        for name in ("_c_in", "_c_out", "_c_skip", "sample_prior", "_step"):
+            setattr(ns, name, types.MethodType(getattr(DiffSepOU, name), ns))
+        return ns
+
+    for tag, mk_ref, orc_sde, edm in (
+            ("ouve", lambda: sdes.sdes.OUVESDE(theta=1.5, sigma_min=0.05, sigma_max=0.5, N=30), S.OUVESDERef(1.5, 0.05, 0.5, N=30), False),
+            ("sbve", lambda: sdes.sdes.SBVESDE(2.6, 0.4, N=30), S.SBVESDERef(2.6, 0.4, N=30), True)):
+        ns = ou_namespace(mk_ref(), edm)
+        with TapedRandn(S.NoiseTape(73)):
+            x_t, t_out, sigma, z = DiffSepOU.sample_prior(ns, mix, target)
+        with TapedRandn(S.NoiseTape(73)):
+            loss = DiffSepOU.compute_score_loss(ns, mix, target)
+        z0 = S.NoiseTape(73).draw(0, target.shape)
+        model_o = (lambda a, b, c: S.edm_forward_ref(toy_net, orc_sde, a, b, c)) if edm else toy_score
+        x_o, sigma_o = S.ou_sample_prior_ref(orc_sde, mix, target, time, z0)
+        loss_o = S.ou_score_loss_ref(model_o, orc_sde, mix, target, time, z0)
+        errs = [float((a - b).abs().max()) for a, b in ((x_t, x_o), (sigma, sigma_o), (loss, loss_o))]
+        print(f"DiffSepOU / {tag}: oracle vs reference max abs err x_t {errs[0]:.2e} sigma {errs[1]:.2e} loss {errs[2]:.2e}; "
+              f"loss {loss.tolist()}")
+        assert max(errs) < 1e-5 * max(1.0, float(loss.abs().max())) and tuple(loss.shape) == (B, 2)
+        golden.update({f"ou_{tag}_xt": x_t.numpy(), f"ou_{tag}_sigma": sigma.numpy(), f"ou_{tag}_loss": loss.numpy()})
+    ns = ou_namespace(sdes.sdes.OUVESDE(theta=1.5, sigma_min=0.05, sigma_max=0.5, N=30), False)
+    with TapedRandn(S.NoiseTape(74)):
+        pit = DiffSepOU.compute_score_loss_init_hack_pit(ns, mix, target)
+    pit_o = S.ou_score_loss_init_hack_pit_ref(toy_score, S.OUVESDERef(1.5, 0.05, 0.5, N=30), mix, target,
+                                              S.NoiseTape(74).draw(0, target.shape))
+    err = float((pit - pit_o).abs().max())
+    print(f"DiffSepOU / ouve init-hack PIT loss: oracle vs reference max abs err {err:.2e}; {pit.tolist()}")
+    assert err < 1e-5 * max(1.0, float(pit.abs().max())) and tuple(pit.shape) == (B, 2)
+    golden["ou_ouve_pit"] = pit.numpy()
     np.savez_compressed(os.path.join(GOLDEN, "loss.npz"), **golden)
     print("written", os.path.join(GOLDEN, "loss.npz"))
 

@@ -149,6 +149,11 @@ class OUVESDERef:
         s, th, ls = self.sigma_min, self.theta, self.logsig
         return torch.sqrt(s ** 2 * torch.exp(-2 * th * t) * (torch.exp(2 * (th + ls) * t) - 1) * ls / (th + ls))
 
+    def mean(self, x0, t, y):
+        """:662-668: e^{-theta t} x0 + (1 - e^{-theta t}) y."""
+        e = _pad(torch.exp(-self.theta * t), x0)
+        return e * x0 + (1 - e) * y
+
     def prior_sampling(self, y, noise: Tensor):
         """:687-695: y + randn(shape) * std(1)."""
         std = self.std(torch.ones((y.shape[0],)))
@@ -418,6 +423,36 @@ def score_loss_init_hack_pit_ref(model, sde: MixSDERef, mix: Tensor, target: Ten
         z = z0 + torch.linalg.solve(L, true_mix - mean)
         pred = model(mean + L @ z, time, mix)
         losses.append(((L @ pred) + z).square().mean(dim=(-2, -1)))
+    return torch.stack(losses, dim=1).min(dim=1).values
+
+
+def ou_sample_prior_ref(sde, mix: Tensor, target: Tensor, time: Tensor, z: Tensor):
+    """``DiffSepOU.sample_prior`` (src/diffsep.py:800-811) for an ``OUVESDERef`` or ``SBVESDERef``: (x_t, sigma)."""
+    if isinstance(sde, SBVESDERef):
+        mean, std = sde.marginal_prob(target, mix, time)
+    else:
+        mean, std = sde.mean(target, time, mix), sde.std(time)
+    sigma = _pad(std, mean)
+    return mean + sigma * z, sigma
+
+
+def ou_score_loss_ref(model, sde, mix: Tensor, target: Tensor, time: Tensor, z: Tensor) -> Tensor:
+    """``DiffSepOU.compute_score_loss`` (src/diffsep.py:836-841) with MSELoss(reduction="none"): (B, n_src)."""
+    x_t, sigma = ou_sample_prior_ref(sde, mix, target, time, z)
+    loss = (model(x_t, time, mix) * sigma + z).square()
+    return loss.mean(dim=tuple(range(2 - loss.ndim, 0)))
+
+
+def ou_score_loss_init_hack_pit_ref(model, sde: OUVESDERef, mix: Tensor, target: Tensor, z0: Tensor) -> Tensor:
+    """``DiffSepOU.compute_score_loss_init_hack_pit`` (src/diffsep.py:843-869), OU branch."""
+    import itertools
+    time = torch.ones(mix.shape[0]) * sde.T
+    losses = []
+    for perm in itertools.permutations(range(target.shape[1])):
+        mean, sigma = sde.mean(target[:, perm, ...], time, mix), _pad(sde.std(time), mix)
+        z = z0 + (mix - mean) / sigma
+        loss = (model(mix + sigma * z0, time, mix) * sigma + z).square()
+        losses.append(loss.mean(dim=tuple(range(2 - loss.ndim, 0))))
     return torch.stack(losses, dim=1).min(dim=1).values
 
 

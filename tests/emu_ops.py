@@ -17,7 +17,7 @@ import torch.nn.functional as F
 
 from ditsep_b200 import ops
 
-_NAMES = ["conv1d_tc", "conv1d_in", "conv1d_out", "vae_sample", "pc_corrector", "pc_predictor", "pc_prior", "pc_langevin", "pc_perturb", "score_loss", "energy_envelope", "sb_step", "philox_normal", "stft_compress", "expand_istft", "gn_stats",
+_NAMES = ["conv1d_tc", "conv1d_in", "conv1d_out", "vae_sample", "pc_corrector", "pc_predictor", "pc_prior", "pc_langevin", "pc_perturb", "score_loss", "score_loss_sigma", "energy_envelope", "sb_step", "philox_normal", "stft_compress", "expand_istft", "gn_stats",
           "gn_sums", "gn_finalize", "gn_apply", "gn_apply_srcs", "gn_small", "fir_resample", "conv_direct", "attention", "temb_mlp", "temb_dense", "output_layer"]
 
 
@@ -117,6 +117,14 @@ def score_loss(p, pred, t, noise=None, seed=0, draw=0):
     return r.square().flatten(1).mean(dim=1).float()
 
 
+def score_loss_sigma(pred, sigma, noise=None, seed=0, draw=0):
+    if noise is None:
+        raise AssertionError("the CPU stand-in needs the noise tensor (Philox lives in the kernel)")
+    B = pred.shape[0]
+    r = sigma.double().reshape(B, *([1] * (pred.ndim - 1))) * pred.double() + noise.double()
+    return r.square().flatten(1).mean(dim=1).float()
+
+
 def pc_langevin(n_src, x, score, noise, step, x_mean=None, lengths=None):
     eps = step.double().reshape(())
     m = x.double() + eps * score.double()
@@ -142,12 +150,12 @@ def sb_step(x, f, y, coef, *, x_out=None, x_in=None, y_in=None, est=None, noise=
     c = [coef[:, i].reshape(-1, 1, 1) for i in range(8)]
     e = c[4] * x + c[5] * (f / c[6]) if f is not None else torch.zeros_like(x)
     v = c[0] * x + c[1] * e
-    if use_noise:
+    if int(use_noise) != 1:
+        v = v + c[2] * y
+    if int(use_noise) != 0:
         if noise is None:
             raise NotImplementedError("the Philox stream only exists on the device: CPU tests pass a noise tape")
         v = v + c[3] * noise
-    else:
-        v = v + c[2] * y
     if lengths is not None:
         live = torch.arange(x.shape[-1])[None, None, :] < lengths.reshape(-1, 1, 1)
         v, e = v * live, e * live

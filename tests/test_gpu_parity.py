@@ -578,3 +578,17 @@ def test_validation_score_loss_with_the_real_network_vs_oracle():
     torch.manual_seed(0)
     v = model.validation_score_loss((mixn.to(DEV), tgt.to(DEV)))
     assert v.ndim == 0 and torch.isfinite(v)
+
+
+def test_diffsep_ou_score_loss_vs_reference_golden(golden):
+    """DiffSepOU's loss forward (src/diffsep.py:800-869) on the device: OU perturbation row / sb_step "mean, then noise" mode
+    + ditsep_score_loss_sigma against the reference's values (tests/golden/loss.npz)."""
+    from test_host_logic import check_ou_loss_against_reference
+    check_ou_loss_against_reference(golden["loss"], DEV)
+    # Philox draw regenerated inside the reduction == the materialised draw
+    g = torch.Generator().manual_seed(3)
+    pred = torch.randn(4, 1, 4096, generator=g).to(DEV)
+    sig = (torch.rand(4, generator=g) + 0.1).to(DEV)
+    z = torch.empty_like(pred)
+    ops.philox_normal(z, 31, 2)
+    assert torch.equal(ops.score_loss_sigma(pred, sig, noise=z), ops.score_loss_sigma(pred, sig, seed=31, draw=2))

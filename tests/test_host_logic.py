@@ -386,3 +386,54 @@ def test_score_loss_forward_host_logic_vs_reference_golden(golden):
     assert torch.equal(sh.sum(dim=1), x.sum(dim=1)) or float((sh.sum(dim=1) - x.sum(dim=1)).abs().max()) < 1e-5
     t = sdes.MixSDE(2, 2.0, 0.05, 0.5, N=30).sample_time_varprop(500, t_eps=0.03)
     assert t.shape == (500,) and float(t.min()) >= 0.03 and float(t.max()) <= 1.0 and float(t.mean()) > 0.55
+
+
+def make_diffsep_ou_loss_model(kind):
+    """DiffSepOU for the loss tests: closed-form score (OUVESDE) or closed-form raw network behind the EDM forward (SBVESDE)."""
+    from ditsep_b200.diffsep import DiffSepOU
+    if kind == "sbve":
+        m = make_diffsep_ou(sb_toy_net, N=30)
+        m.config = type("Cfg", (), {"model": type("M", (), {"loss": {"_target_": "torch.nn.MSELoss"}, "sampler": {"N": 30}})()})()
+    else:
+        class Toy(DiffSepOU):
+            def forward(self, xt, time, mix):
+                return loss_toy_score(xt, time, mix)
+
+        base = make_loss_model(5)
+        m = Toy.__new__(Toy)
+        torch.nn.Module.__init__(m)
+        m.__dict__.update({k: v for k, v in base.__dict__.items() if not k.startswith("_")})
+        m.sde, m.is_edm = sdes.OUVESDE(theta=1.5, sigma_min=0.05, sigma_max=0.5, N=30), False
+    m.t_eps, m.t_max, m.init_hack, m.init_hack_p, m.t_rev_init = 0.03, 1, 5, 0.0, 0.03
+    m.time_sampling_strategy, m.train_source_order = "uniform", "random"
+    return m
+
+
+def check_ou_loss_against_reference(g, device):
+    mix, target, time, _ = loss_inputs(g, device)
+    z0 = S.NoiseTape(73).draw(0, target.shape).to(device)
+    for kind in ("ouve", "sbve"):
+        m = make_diffsep_ou_loss_model(kind)
+        x_t, t_out, sigma, z = m.sample_prior(mix, target, time=time.clone(), noise=z0)
+        loss = m.compute_score_loss(mix, target, time=time.clone(), noise=z0)
+        for name, got in (("xt", x_t), ("sigma", sigma), ("loss", loss)):
+            ref = torch.tensor(g[f"ou_{kind}_{name}"])
+            assert tuple(got.shape) == tuple(ref.shape), (kind, name, got.shape, ref.shape)
+            assert float((got.cpu() - ref).abs().max()) < 2e-5 * max(1.0, float(ref.abs().max())), (kind, name)
+    m = make_diffsep_ou_loss_model("ouve")
+    pit = m.compute_score_loss_init_hack_pit(mix, target, noise=S.NoiseTape(74).draw(0, target.shape).to(device))
+    assert float((pit.cpu() - torch.tensor(g["ou_ouve_pit"])).abs().max()) < 2e-5
+    with pytest.raises(NotImplementedError):
+        make_diffsep_ou_loss_model("sbve").compute_score_loss_init_hack_pit(mix, target, noise=z0)
+
+
+def test_diffsep_ou_score_loss_host_logic_vs_reference_golden(golden):
+    """DiffSepOU.sample_prior / compute_score_loss / init-hack PIT loss (src/diffsep.py:800-869) for OUVESDE and SBVESDE
+    through the emulated kernels against the unmodified reference's values (oracle/pin_loss.py)."""
+    with emulated_ops():
+        check_ou_loss_against_reference(golden["loss"], "cpu")
+        m = make_diffsep_ou_loss_model("ouve")
+        m._draw = lambda like, noise: torch.randn_like(like)
+        mix, target, _, _ = loss_inputs(golden["loss"])
+        v = m.validation_score_loss((mix, target))
+        assert v.ndim == 0 and torch.isfinite(v)
