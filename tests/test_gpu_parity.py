@@ -465,16 +465,19 @@ def test_sb_step_kernel_bit_exact_vs_emulation(B, n_src, L):
     y = torch.randn(B, 1, L, generator=g)
     coef = torch.rand(B, 8, generator=g) + 0.25
     lengths = torch.tensor([L, max(1, L - 5), max(1, L // 2)][:B], dtype=torch.int32)
-    for use_noise in (False, True):
+    for use_noise in (0, 1, 2):
         for lens in (None, lengths):
             want = {k: torch.full((B, n_src, L), float("nan")) for k in ("x_out", "x_in", "est")}
             want["y_in"] = torch.full((B, 1, L), float("nan"))
             emu_ops.sb_step(x, f, y, coef, noise=z, use_noise=use_noise, lengths=lens, **want)
-            got = {k: torch.full_like(v, float("nan")).to(DEV) for k, v in want.items()}
+            # outputs are interior views of larger buffers: the guard words either side must come back untouched
+            guard = {k: torch.full((v.numel() + 512,), 12345.0, device=DEV) for k, v in want.items()}
+            got = {k: guard[k][256:256 + v.numel()].view(v.shape) for k, v in want.items()}
             ops.sb_step(x.to(DEV), f.to(DEV), y.to(DEV), coef.to(DEV), noise=z.to(DEV), use_noise=use_noise,
                         lengths=None if lens is None else lens.to(DEV), **got)
             for k in want:
                 assert torch.equal(got[k].cpu(), want[k]), (k, use_noise, lens is not None)
+                assert bool((guard[k][:256] == 12345.0).all()) and bool((guard[k][-256:] == 12345.0).all()), k
     # in place, no network output (the start-up call), Philox noise
     xd = x.to(DEV).clone()
     ops.sb_step(xd, None, y.to(DEV), coef.to(DEV), x_out=xd)
@@ -540,8 +543,12 @@ def test_perturb_and_loss_kernels_vs_emulation(kind, n_src, L):
     p = sde.fused_params(n_src=n_src)
     want_x, want_m = x0.clone(), torch.empty_like(x0)
     emu_ops.pc_perturb(p, want_x, t, y=y, noise=z, x_mean=want_m)
-    got_x, got_m = x0.to(DEV).clone(), torch.empty_like(x0, device=DEV)
+    gx, gm = (torch.full((x0.numel() + 512,), 12345.0, device=DEV) for _ in range(2))  # guard words around both outputs
+    got_x, got_m = gx[256:256 + x0.numel()].view(x0.shape), gm[256:256 + x0.numel()].view(x0.shape)
+    got_x.copy_(x0)
     ops.pc_perturb(p, got_x, t.to(DEV), y=y.to(DEV), noise=z.to(DEV), x_mean=got_m)
+    for gbuf in (gx, gm):
+        assert bool((gbuf[:256] == 12345.0).all()) and bool((gbuf[-256:] == 12345.0).all())
     assert rel_l2(got_x, want_x) < 2e-6 and rel_l2(got_m, want_m) < 2e-6
     if kind == "mix":  # against the class's own matrix form (marginal_prob / mult_std, host torch)
         mean, Lm = sde.marginal_prob(x0, t)
