@@ -180,6 +180,83 @@ class DiffSepModel(_Base):
         return torch.stack(losses, dim=1).min(dim=1).values
 
     @torch.no_grad()
+    def compute_score_loss_with_pit(self, mix, target, time=None, noise=None, select=None):
+        """diffsep.py:183-258: x_t is built around the mean of ONE randomly chosen source order; where the other orders'
+        means are within `mmnr_thresh_pit` dB of the noise, the loss is the minimum over the orders (each order explains
+        x_t with its own noise), elsewhere the plain loss.  Returns the losses of the PIT items followed by those of the
+        others, like the reference.  The network output does not depend on the order, so it is evaluated once per item
+        (the reference replicates the same input n_perm times)."""
+        import itertools
+        from . import ops
+        time = self.sample_time(target) if time is None else time
+        perms = list(itertools.permutations(range(target.shape[1])))
+        means, L = [], None
+        for p in perms:
+            mean, L = self.sde.marginal_prob(target[:, p, :], time, mix)
+            means.append(mean)
+        means = torch.stack(means, dim=1)  # (batch, perm, src, samples)
+        z = self._draw(target, noise)
+        Lz = self.sde.mult_std(L, z)
+        mean_select = utils.select_elem_at_random(means, dim=1, select=select)
+        xt = (mean_select + Lz[:, None, ...])[:, 0]
+        err = means - mean_select
+        n_elems = (means.shape[1] - 1) * means.shape[2] * means.shape[3]
+        err_pow = err.square().sum(dim=(1, 2, 3)) / n_elems
+        noise_pow = Lz.square().mean(dim=(1, 2))
+        mmnr = 10.0 * torch.log10(err_pow / noise_pow.clamp(min=1e-5))
+        select_pit = mmnr < self.config.model.mmnr_thresh_pit
+        pred = self(xt.contiguous(), time, mix).to(torch.float32).contiguous()
+        par = self.sde.fused_params(n_src=target.shape[1])
+        tc = time.to(torch.float32).contiguous()
+        plain = ops.score_loss(par, pred, tc, noise=z.contiguous())
+        per_perm = torch.stack([ops.score_loss(par, pred, tc, noise=(z + self.sde.mult_std_inv(L, err[:, k])).contiguous())
+                                for k in range(len(perms))], dim=1)
+        return torch.cat([per_perm[select_pit].min(dim=-1).values, plain[~select_pit]])
+
+    @torch.no_grad()
+    def compute_score_loss_with_pit_allthetime(self, mix, target, time=None, noise=None, shuffle=True):
+        """diffsep.py:260-303: x_t around a randomly ordered target; the loss is the minimum over the source orders of the
+        noise each order would need (z_p = z_0 + L^{-1}(mean_0 - mean_p)).  One network evaluation (x_t does not
+        depend on p; the reference recomputes it per order)."""
+        import itertools
+        from . import ops
+        time = self.sample_time(target) if time is None else time
+        if shuffle:
+            target = utils.shuffle_sources(target)
+        mean_0, L = self.sde.marginal_prob(target, time, mix)
+        z0 = self._draw(target, noise)
+        x_t = mean_0 + self.sde.mult_std(L, z0)
+        pred = self(x_t, time, mix).to(torch.float32).contiguous()
+        par = self.sde.fused_params(n_src=target.shape[1])
+        tc = time.to(torch.float32).contiguous()
+        losses = []
+        for p in itertools.permutations(range(target.shape[1])):
+            mean_p, _ = self.sde.marginal_prob(target[:, p, :], time, mix)
+            z_p = (z0 + self.sde.mult_std_inv(L, mean_0 - mean_p)).contiguous()
+            losses.append(ops.score_loss(par, pred, tc, noise=z_p))
+        return torch.stack(losses, dim=0).min(dim=0).values
+
+    def _train_step_init(self, mix, target, rest_fn, pit=None):
+        """diffsep.py:363-420: a random subset (probability init_hack_p) takes the t = T permutation-invariant loss, the
+        rest `rest_fn`; the mean over all items."""
+        if pit is None:
+            pit = mix.new_zeros(mix.shape[0]).uniform_() < self.init_hack_p
+        losses = []
+        if pit.sum() > 0:
+            losses.append(self.compute_score_loss_init_hack_pit(mix[pit], target[pit]))
+        if pit.sum() != mix.shape[0]:
+            losses.append(rest_fn(mix[~pit], target[~pit]))
+        return torch.cat(losses).mean()
+
+    @torch.no_grad()
+    def train_step_init_6(self, mix, target, pit=None):
+        return self._train_step_init(mix, target, lambda m, t: self.compute_score_loss_with_pit(m, utils.shuffle_sources(t)), pit)
+
+    @torch.no_grad()
+    def train_step_init_7(self, mix, target, pit=None):
+        return self._train_step_init(mix, target, self.compute_score_loss_with_pit_allthetime, pit)
+
+    @torch.no_grad()
     def train_step_init_5(self, mix, target, pit=None):
         """diffsep.py:363-382 (forward value): a random subset (probability init_hack_p) takes the permutation-invariant
         t = T loss, the rest the plain loss on randomly ordered sources."""
@@ -194,12 +271,12 @@ class DiffSepModel(_Base):
 
     @torch.no_grad()
     def validation_score_loss(self, batch):
-        """The val/score_loss of validation_step (diffsep.py:476-487) for init_hack 5 and for the plain loss; the
-        memory-heavier PIT variants of init_hack 6 / 7 (:183-303) are not provided."""
+        """The val/score_loss of validation_step (diffsep.py:476-487): init_hack 5 / 6 / 7 or the plain loss."""
         (mix, target), *stats = self.normalize_batch(batch)
-        if self.init_hack in (6, 7):
-            raise NotImplementedError(f"init_hack = {self.init_hack}: compute_score_loss_with_pit[_allthetime] "
-                                      "(diffsep.py:183-303) is not built (SURVEY 8f-4)")
+        if self.init_hack == 7:
+            return self.train_step_init_7(mix, target)
+        if self.init_hack == 6:
+            return self.train_step_init_6(mix, target)
         if self.init_hack == 5:
             return self.train_step_init_5(mix, target)
         return self.compute_score_loss(mix, target)

@@ -1,4 +1,4 @@
 from .registry import Registry
-from .separate import denormalize_batch, normalize_batch, power_order_sources, shuffle_sources
+from .separate import denormalize_batch, normalize_batch, power_order_sources, select_elem_at_random, shuffle_sources
 
 __all__ = ["Registry", "normalize_batch", "denormalize_batch"]

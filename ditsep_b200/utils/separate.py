@@ -33,3 +33,13 @@ def power_order_sources(x):
         return x
     order = torch.argsort(torch.var(x, dim=-1), dim=1)
     return torch.gather(x, 1, order.reshape(order.shape + (1,) * (x.ndim - 2)).expand_as(x))
+
+
+def select_elem_at_random(x, dim=-1, batch_dim=0, select=None):
+    """One element along `dim`, drawn independently per batch entry, the axis kept with size 1
+    (src/utils/separate.py:24-32).  `select`: the (batch,) indices to use instead of a random draw (parity runs)."""
+    if select is None:
+        select = torch.randint(x.shape[dim], size=(x.shape[batch_dim],), device=x.device)
+    x = x.movedim(dim, -1)
+    idx = select.to(x.device).reshape((-1,) + (1,) * (x.ndim - 1)).expand(x.shape[:-1] + (1,))
+    return torch.gather(x, -1, idx).movedim(-1, dim)

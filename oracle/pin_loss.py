@@ -78,6 +78,31 @@ def main():
     assert err < 1e-5
     golden["loss_pit"] = pit.numpy()
 
+    # ---- the two remaining PIT variants (src/diffsep.py:183-303); their random choices are pinned: the order selection of
+    # utils.select_elem_at_random by a fixed index vector, utils.shuffle_sources by the identity
+    import utils as ref_utils
+    sel = torch.tensor([1, 0, 1, 0])
+    golden["loss_pit_select"] = sel.numpy()
+
+    def fixed_select(x, dim=-1, batch_dim=0):
+        x = x.moveaxis(dim, -1)
+        idx = torch.broadcast_to(sel[(...,) + (None,) * (x.ndim - 1)], x.shape[:-1] + (1,))
+        return torch.gather(x, dim=-1, index=idx).moveaxis(-1, dim)
+
+    ref_utils.select_elem_at_random, ref_utils.shuffle_sources = fixed_select, (lambda x: x)
+    ns = Callable(**namespace(6).__dict__)
+    ns.config = types.SimpleNamespace(model=types.SimpleNamespace(mmnr_thresh_pit=-9.5))  # items 0-2 plain, item 3 PIT (-9.93 dB)
+    with TapedRandn(S.NoiseTape(75)):
+        wp = DiffSepModel.compute_score_loss_with_pit(ns, mix, target)
+    with TapedRandn(S.NoiseTape(76)):
+        wa = DiffSepModel.compute_score_loss_with_pit_allthetime(ns, mix, target)
+    wp_o = S.score_loss_with_pit_ref(toy_score, orc, mix, target, time, S.NoiseTape(75).draw(0, target.shape), sel, -9.5)
+    wa_o = S.score_loss_with_pit_allthetime_ref(toy_score, orc, mix, target, time, S.NoiseTape(76).draw(0, target.shape))
+    e1, e2 = float((wp - wp_o).abs().max()), float((wa - wa_o).abs().max())
+    print(f"with_pit: oracle vs reference max abs err {e1:.2e}; {wp.tolist()}\nwith_pit_allthetime: {e2:.2e}; {wa.tolist()}")
+    assert e1 < 1e-5 and e2 < 1e-5 and wp.shape == wa.shape == (B,)
+    golden.update(loss_with_pit=wp.numpy(), loss_with_pit_allthetime=wa.numpy())
+
     # ---- DiffSepOU (src/diffsep.py:796-869): scalar-std SDEs; the SBVESDE goes through the reference's own EDM forward
     DiffSepOU = sys.modules["diffsep"].DiffSepOU
     from oracle.pin_sb import toy_net

@@ -426,6 +426,43 @@ def score_loss_init_hack_pit_ref(model, sde: MixSDERef, mix: Tensor, target: Ten
     return torch.stack(losses, dim=1).min(dim=1).values
 
 
+def score_loss_with_pit_ref(model, sde: MixSDERef, mix: Tensor, target: Tensor, time: Tensor, z: Tensor, select: Tensor,
+                            mmnr_thresh_pit: float = -10.0) -> Tensor:
+    """``compute_score_loss_with_pit`` (src/diffsep.py:183-258) with the time draw, the normal draw and the random
+    order selection (``select``: (B,) indices into the permutation list) passed in.  Written per item, NOT with the
+    reference's batched broadcast / flatten bookkeeping; PIT items first, like the reference's ``torch.cat``."""
+    import itertools
+    perms = list(itertools.permutations(range(target.shape[1])))
+    L = sde.std(time)
+    means = torch.stack([sde.mean(target[:, p, :], time) for p in perms], dim=1)
+    Lz = L @ z
+    pit, reg = [], []
+    for b in range(target.shape[0]):
+        m_sel = means[b, int(select[b])]
+        x_t = m_sel + Lz[b]
+        err = means[b] - m_sel
+        err_pow = err.square().sum() / ((len(perms) - 1) * err.shape[1] * err.shape[2])
+        mmnr = 10.0 * torch.log10(err_pow / Lz[b].square().mean().clamp(min=1e-5))
+        pred = model(x_t[None], time[b:b + 1], mix[b:b + 1])[0]
+        if mmnr < mmnr_thresh_pit:
+            pit.append(torch.stack([((L[b] @ pred) + z[b] + torch.linalg.solve(L[b], e)).square().mean() for e in err]).min())
+        else:
+            reg.append(((L[b] @ pred) + z[b]).square().mean())
+    return torch.stack(pit + reg)
+
+
+def score_loss_with_pit_allthetime_ref(model, sde: MixSDERef, mix: Tensor, target: Tensor, time: Tensor, z0: Tensor) -> Tensor:
+    """``compute_score_loss_with_pit_allthetime`` (src/diffsep.py:260-303) without the source shuffle."""
+    import itertools
+    mean_0, L = sde.mean(target, time), sde.std(time)
+    pred = model(mean_0 + L @ z0, time, mix)
+    losses = []
+    for p in itertools.permutations(range(target.shape[1])):
+        z_p = z0 + torch.linalg.solve(L, mean_0 - sde.mean(target[:, p, :], time))
+        losses.append(((L @ pred) + z_p).square().mean(dim=(-2, -1)))
+    return torch.stack(losses, dim=0).min(dim=0).values
+
+
 def ou_sample_prior_ref(sde, mix: Tensor, target: Tensor, time: Tensor, z: Tensor):
     """``DiffSepOU.sample_prior`` (src/diffsep.py:800-811) for an ``OUVESDERef`` or ``SBVESDERef``: (x_t, sigma)."""
     if isinstance(sde, SBVESDERef):

@@ -364,6 +364,15 @@ def check_loss_against_reference(g, device):
             assert float((got.cpu() - ref).abs().max()) < tol, (hack, name)
     pit = make_loss_model(5, device).compute_score_loss_init_hack_pit(mix, target, noise=S.NoiseTape(71).draw(0, target.shape).to(device))
     assert float((pit.cpu() - torch.tensor(g["loss_pit"])).abs().max()) < 2e-5
+    # the two batch-PIT variants (diffsep.py:183-303): order selection / shuffle pinned like in the reference run
+    m = make_loss_model(6, device)
+    m.config.model.mmnr_thresh_pit = -9.5  # items 0-2 take the plain loss, item 3 (-9.93 dB) the PIT branch, listed first
+    wp = m.compute_score_loss_with_pit(mix, target, time=time.clone(), noise=S.NoiseTape(75).draw(0, target.shape).to(device),
+                                       select=torch.tensor(g["loss_pit_select"]).to(device))
+    wa = m.compute_score_loss_with_pit_allthetime(mix, target, time=time.clone(), shuffle=False,
+                                                  noise=S.NoiseTape(76).draw(0, target.shape).to(device))
+    assert float((wp.cpu() - torch.tensor(g["loss_with_pit"])).abs().max()) < 2e-5
+    assert float((wa.cpu() - torch.tensor(g["loss_with_pit_allthetime"])).abs().max()) < 2e-5
 
 
 def test_score_loss_forward_host_logic_vs_reference_golden(golden):
@@ -376,9 +385,11 @@ def test_score_loss_forward_host_logic_vs_reference_golden(golden):
         m._draw = lambda like, noise: torch.randn_like(like)  # Philox lives on the device
         v = m.validation_score_loss((mix, target))
         assert v.ndim == 0 and torch.isfinite(v)
-        m.init_hack = 6
-        with pytest.raises(NotImplementedError):
-            m.validation_score_loss((mix, target))
+        for hack in (6, 7):  # init_hack 6 / 7: the same subset split around the two batch-PIT losses
+            m.init_hack = hack
+            m.config.model.mmnr_thresh_pit = -10.0
+            v = m.validation_score_loss((mix, target))
+            assert v.ndim == 0 and torch.isfinite(v)
     from ditsep_b200.utils import power_order_sources, shuffle_sources
     x = torch.randn(5, 3, 40) * torch.tensor([3.0, 1.0, 2.0])[None, :, None]
     assert torch.equal(power_order_sources(x), x[:, [1, 2, 0]])
