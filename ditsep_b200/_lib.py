@@ -61,6 +61,8 @@ SIGNATURES = {
     "ditsep_box_muller": (c_int, [c_void_p, c_void_p, c_int64, c_void_p]),
     "ditsep_stft_compress": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_int64, c_int,
                                      c_float, c_float, c_int, c_void_p]),
+    "ditsep_stft_compress_cached": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_int64, c_int,
+                                     c_float, c_float, c_int, c_void_p, c_int, c_void_p]),
     "ditsep_expand_istft": (c_int, [c_void_p, c_void_p, c_void_p, c_int, c_int, c_int64, c_int, c_float, c_float,
                                     c_void_p]),
     "ditsep_gn_sums": (c_int, [c_void_p, c_int, c_int, c_int64, c_int, c_int, c_void_p, c_void_p]),

@@ -133,7 +133,11 @@ template <typename T>
 __global__ void __launch_bounds__(256) stft_compress_kernel(const float* __restrict__ xt, const float* __restrict__ mix,
                                                             const float* __restrict__ window, T* __restrict__ feat,
                                                             int n_src, int64_t Tlen, int W, int n_frames,
-                                                            float exponent, float factor, int affine) {
+                                                            float exponent, float factor, int affine,
+                                                            float2* __restrict__ mix_cache, int mix_mode) {
+  // mix_mode: 0 = no cache; 1 = also write the mixture channel's finished (Re, Im) to mix_cache [B][W][256]; 2 = read
+  // it from there instead of transforming the mixture again (it does not change during a sampler run: a third of the
+  // transforms of every score evaluation)
   extern __shared__ __align__(16) unsigned char smem_raw[];
   const int NC = n_src + 1, C2 = 2 * NC;
   float2* tab = reinterpret_cast<float2*>(smem_raw);
@@ -162,6 +166,16 @@ __global__ void __launch_bounds__(256) stft_compress_kernel(const float* __restr
   for (int item = warp; item < kFT * NC; item += kWarps) {
     const int fl = item % kFT, ch = item / kFT;
     const int f = f0 + fl;
+    const bool is_mix = ch == n_src;
+    float2* const cache_row = mix_mode ? mix_cache + ((int64_t)b * W + f) * kBins : nullptr;
+    if (is_mix && mix_mode == 2) {
+      for (int k = lane; k < kBins; k += 32) {
+        const float2 v = cache_row[k];
+        ostage[k * (kFT * C2 + 1) + fl * C2 + ch] = v.x;
+        ostage[k * (kFT * C2 + 1) + fl * C2 + NC + ch] = v.y;
+      }
+      continue;
+    }
     if (f < n_frames) {
       const float* s = sig + ch * kSigLen + fl * kHop;
       for (int m = lane; m < kHalf; m += 32)
@@ -198,6 +212,7 @@ __global__ void __launch_bounds__(256) stft_compress_kernel(const float* __restr
       }
       ostage[k * (kFT * C2 + 1) + fl * C2 + ch] = re;  // +1: odd row stride, conflict-free over k
       ostage[k * (kFT * C2 + 1) + fl * C2 + NC + ch] = im;
+      if (is_mix && mix_mode == 1) cache_row[k] = make_float2(re, im);
     }
     __syncwarp();
   }
@@ -302,10 +317,13 @@ __global__ void __launch_bounds__(256) expand_istft_kernel(const float* __restri
 
 using namespace ditsep;
 
-extern "C" int ditsep_stft_compress(const float* xt, const float* mix, const float* window, void* feat, int dtype,
-                                    int B, int n_src, int64_t T, int W, float exponent, float factor,
-                                    int affine_2x_minus_1, void* stream) {
+static int launch_stft_compress(const float* xt, const float* mix, const float* window, void* feat, int dtype, int B,
+                                int n_src, int64_t T, int W, float exponent, float factor, int affine_2x_minus_1,
+                                float* mix_cache, int mix_mode, void* stream) {
   DITSEP_REQUIRE(xt && mix && window && feat, "stft_compress: null pointer");
+  DITSEP_REQUIRE(mix_mode >= 0 && mix_mode <= 2 && (mix_mode == 0 || mix_cache != nullptr),
+                 "stft_compress: mix_mode=%d (0 none, 1 fill, 2 use) needs a cache buffer", mix_mode);
+  DITSEP_REQUIRE((reinterpret_cast<uintptr_t>(mix_cache) & 7) == 0, "stft_compress: mix_cache must be 8-byte aligned");
   DITSEP_REQUIRE(B > 0 && T > 0 && n_src >= 1 && n_src <= 4, "stft_compress: bad sizes B=%d T=%lld n_src=%d", B,
                  (long long)T, n_src);
   const int n_frames = 1 + (int)((T + (kNfft - kHop)) / kHop);
@@ -320,15 +338,31 @@ extern "C" int ditsep_stft_compress(const float* xt, const float* mix, const flo
   if (dtype == DITSEP_F32) {
     DITSEP_CUDA(cudaFuncSetAttribute(stft_compress_kernel<float>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     stft_compress_kernel<float><<<grid, 256, smem, st>>>(xt, mix, window, (float*)feat, n_src, T, W, n_frames, exponent,
-                                                         factor, affine_2x_minus_1);
+                                                         factor, affine_2x_minus_1, reinterpret_cast<float2*>(mix_cache),
+                                                         mix_mode);
   } else if (dtype == DITSEP_BF16) {
     DITSEP_CUDA(cudaFuncSetAttribute(stft_compress_kernel<bf16>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     stft_compress_kernel<bf16><<<grid, 256, smem, st>>>(xt, mix, window, (bf16*)feat, n_src, T, W, n_frames, exponent,
-                                                        factor, affine_2x_minus_1);
+                                                        factor, affine_2x_minus_1, reinterpret_cast<float2*>(mix_cache),
+                                                        mix_mode);
   } else {
     DITSEP_REQUIRE(false, "stft_compress: unknown dtype %d", dtype);
   }
   return check_launch("stft_compress_kernel");
+}
+
+extern "C" int ditsep_stft_compress(const float* xt, const float* mix, const float* window, void* feat, int dtype,
+                                    int B, int n_src, int64_t T, int W, float exponent, float factor,
+                                    int affine_2x_minus_1, void* stream) {
+  return launch_stft_compress(xt, mix, window, feat, dtype, B, n_src, T, W, exponent, factor, affine_2x_minus_1, nullptr, 0,
+                              stream);
+}
+
+extern "C" int ditsep_stft_compress_cached(const float* xt, const float* mix, const float* window, void* feat, int dtype,
+                                           int B, int n_src, int64_t T, int W, float exponent, float factor,
+                                           int affine_2x_minus_1, float* mix_cache, int mix_mode, void* stream) {
+  return launch_stft_compress(xt, mix, window, feat, dtype, B, n_src, T, W, exponent, factor, affine_2x_minus_1, mix_cache,
+                              mix_mode, stream);
 }
 
 extern "C" int ditsep_expand_istft(const float* spec, const float* window, float* out, int B, int n_src, int64_t T,

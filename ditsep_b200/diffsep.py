@@ -90,6 +90,12 @@ class DiffSepModel(_Base):
     def forward(self, xt, time, mix):
         return self.score_model(xt, time, mix)
 
+    def note_constant_mixture(self, mix):
+        """Sampler hook (sdes/__init__.py): `mix` is passed unchanged to every evaluation of the coming run."""
+        hook = getattr(self.score_model, "note_constant_mixture", None)
+        if hook is not None:
+            hook(mix)
+
     # ---- score-matching loss, FORWARD VALUE only (SURVEY 8f-4; diffsep.py:100-181, 296-358, 476-487) ----------------
     # What validation_step logs as val/score_loss.  No backward kernels exist in this library: these run under no_grad.
     def sample_time(self, x):

@@ -237,16 +237,22 @@ def box_muller(bits: torch.Tensor, out: torch.Tensor):
 
 
 # ------------------------------------------------------------------ spectral
-def stft_compress(xt, mix, window, feat, exponent: float, factor: float, affine: bool):
-    """xt (B,n,T), mix (B,1,T) f32 -> feat NHWC (B,256,W,2(n+1)) f32|bf16 (dense)."""
-    _cuda(xt, mix, window, feat)
+def stft_compress(xt, mix, window, feat, exponent: float, factor: float, affine: bool, mix_cache=None, mix_mode: int = 0):
+    """xt (B,n,T), mix (B,1,T) f32 -> feat NHWC (B,256,W,2(n+1)) f32|bf16 (dense).  mix_cache (B, W, 256, 2) f32 with
+    mix_mode 1 (fill) / 2 (use): the mixture channel's transform kept across the evaluations of a sampler run."""
+    _cuda(xt, mix, window, feat, mix_cache)
     for n, v in (("xt", xt), ("mix", mix), ("window", window)):
         _f32c(v, n)
     B, n_src, T = xt.shape
     if not feat.is_contiguous() or feat.shape[0] != B or feat.shape[1] != 256 or feat.shape[3] != 2 * (n_src + 1):
         raise _lib.DitsepError(f"feat must be dense (B,256,W,{2 * (n_src + 1)}), got {tuple(feat.shape)}")
-    check(_lib.load().ditsep_stft_compress(_ptr(xt), _ptr(mix), _ptr(window), _ptr(feat), _dt(feat), B, n_src, T,
-                                           feat.shape[2], exponent, factor, int(affine), _stream()), "stft_compress")
+    if mix_mode:
+        _f32c(mix_cache, "mix_cache")
+        if mix_cache is None or tuple(mix_cache.shape) != (B, feat.shape[2], 256, 2):
+            raise _lib.DitsepError(f"mix_cache must be ({B}, {feat.shape[2]}, 256, 2) float32")
+    check(_lib.load().ditsep_stft_compress_cached(_ptr(xt), _ptr(mix), _ptr(window), _ptr(feat), _dt(feat), B, n_src, T,
+                                                  feat.shape[2], exponent, factor, int(affine), _ptr(mix_cache),
+                                                  int(mix_mode), _stream()), "stft_compress")
 
 
 def expand_istft(spec, window, out, exponent: float, factor: float):

@@ -24,6 +24,14 @@ __all__ = ["PredictorRegistry", "CorrectorRegistry", "SDERegistry", "Predictor",
            "get_ode_sampler", "get_sb_sampler"]
 
 
+def _note_constant_mixture(score_fn, y):
+    """Tell a score model of this package that `y` conditions every evaluation of the run unchanged (it may then keep
+    y's transform, models/diffsep/score_models.py::note_constant_mixture); any other callable is left alone."""
+    hook = getattr(score_fn, "note_constant_mixture", None)
+    if hook is not None:
+        hook(y)
+
+
 def get_pc_sampler(predictor_name, corrector_name, sde, score_fn, y, true_mean=None, denoise=True, eps=3e-2, snr=0.1,
                    corrector_steps=1, probability_flow: bool = False, intermediate=False, n_spkrs=2, noise_tape=None,
                    seed=None, lengths=None, **kwargs):
@@ -40,6 +48,7 @@ def get_pc_sampler(predictor_name, corrector_name, sde, score_fn, y, true_mean=N
     def pc_sampler():
         im = [] if intermediate else None
         noise.begin_run()
+        _note_constant_mixture(score_fn, y)
         with torch.no_grad():
             shape = torch.Size((y.shape[0], n_spkrs, *y.shape[2:]))
             cond = true_mean if true_mean is not None else y
@@ -58,6 +67,7 @@ def get_pc_sampler(predictor_name, corrector_name, sde, score_fn, y, true_mean=N
                                                   _want_mean=intermediate or (last and denoise))
             x_result = xt_mean if denoise else xt
             ns = sde.N * (corrector.n_steps + 1)
+            _note_constant_mixture(score_fn, None)
             if intermediate:
                 return x_result, ns, im
             return x_result, ns
@@ -98,6 +108,7 @@ def get_pc_scheduled_sampler(predictor_name, corrector_name, sde, score_fn, y, d
     def pc_sampler():
         im = [] if intermediate else None
         noise.begin_run()
+        _note_constant_mixture(score_fn, y)
         with torch.no_grad():
             cond = true_mean if true_mean is not None else y
             xt = sde.prior_sampling(cond.shape, cond, noise=noise).to(cond.device)
@@ -114,6 +125,7 @@ def get_pc_scheduled_sampler(predictor_name, corrector_name, sde, score_fn, y, d
                                                   _want_mean=intermediate or (last and denoise))
             x_result = xt_mean if denoise else xt
             ns = sde.N * (corrector.n_steps + 1)
+            _note_constant_mixture(score_fn, None)
             if intermediate:
                 return x_result, ns, im
             return x_result, ns

@@ -132,6 +132,13 @@ int ditsep_box_muller(const uint32_t* bits, float* out, int64_t n, void* stream)
 int ditsep_stft_compress(const float* xt, const float* mix, const float* window, void* feat, int dtype, int B,
                          int n_src, int64_t T, int W, float exponent, float factor, int affine_2x_minus_1,
                          void* stream);
+/* The same with the mixture channel's finished (Re, Im) kept across calls: mix_cache is a caller-owned DEVICE buffer of
+ * B * W * 256 * 2 floats; mix_mode 1 transforms everything and fills it, mix_mode 2 reads the mixture channel from it
+ * and transforms only the n_src source channels (the mixture does not change between the score evaluations of one
+ * sampler run: score_models.py:126-131 re-transforms cat(xt, mix) every call), mix_mode 0 = ditsep_stft_compress. */
+int ditsep_stft_compress_cached(const float* xt, const float* mix, const float* window, void* feat, int dtype, int B,
+                                int n_src, int64_t T, int W, float exponent, float factor, int affine_2x_minus_1,
+                                float* mix_cache, int mix_mode, void* stream);
 /* ScoreModelNCSNpp.post_process (score_models.py:118-124): net output NHWC
  * [B][256][W][2 n_src] f32 (channel k pairs with k+n_src) -> /factor -> |S|^{1/e} e^{j arg S}
  * -> iSTFT (torch.istft centre=True) -> first T samples.  out: (B, n_src, T) f32. */

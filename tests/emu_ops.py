@@ -224,7 +224,7 @@ def philox_normal(out, seed, draw):
     out.normal_(generator=torch.Generator().manual_seed(seed * 1000003 + draw))
 
 
-def stft_compress(xt, mix, window, feat, exponent, factor, affine):
+def stft_compress(xt, mix, window, feat, exponent, factor, affine, mix_cache=None, mix_mode=0):
     """ditsep_stft_compress: right pad 382, STFT 510/128 centre zero pad, |X|^e e^{j arg} f,
     [Re.., Im..], frames zero-padded to W, optional 2x-1 over the whole tile."""
     x = torch.cat((xt, mix), dim=1)

@@ -621,3 +621,43 @@ def test_temb_and_output_layer():
 def test_cpu_tensors_are_rejected():
     with pytest.raises(ops.DitsepError):
         ops.gn_apply(torch.zeros(1, 2, 2, 8), torch.zeros(1, 2, 8), True, torch.zeros(1, 2, 2, 8))
+
+
+def test_stft_mixture_cache_modes_and_hook():
+    """ditsep_stft_compress_cached: mode 1 fills the mixture channel's cache and writes the same features as the plain
+    call, mode 2 reads it back bit-for-bit while the sources change; the score model only uses it for a tensor a
+    sampler announced (note_constant_mixture) and refills after an in-place change of that tensor."""
+    import torch
+    from common import build_model, score_inputs
+    from ditsep_b200 import ops
+    dev = "cuda"
+    B, T, W = 3, 9000, 128
+    g = torch.Generator().manual_seed(8)
+    xt, xt2 = (torch.randn(B, 2, T, generator=g).to(dev) for _ in range(2))
+    mix = torch.randn(B, 1, T, generator=g).to(dev)
+    win = torch.hann_window(510).to(dev)
+    for dt in (torch.float32, torch.bfloat16):
+        plain, filled, used, plain2 = (torch.empty(B, 256, W, 6, device=dev, dtype=dt) for _ in range(4))
+        cache = torch.full((B, W, 256, 2), float("nan"), device=dev)
+        ops.stft_compress(xt, mix, win, plain, 0.5, 0.15, True)
+        ops.stft_compress(xt, mix, win, filled, 0.5, 0.15, True, mix_cache=cache, mix_mode=1)
+        assert torch.equal(plain, filled) and torch.isfinite(cache).all()
+        ops.stft_compress(xt2, mix, win, plain2, 0.5, 0.15, True)
+        ops.stft_compress(xt2, torch.zeros_like(mix), win, used, 0.5, 0.15, True, mix_cache=cache, mix_mode=2)  # mixture NOT read
+        assert torch.equal(plain2.float(), used.float())
+    model, _, _ = build_model("bf16", dev, N=2)
+    xs, t, mixn = (a.to(dev) for a in score_inputs(2, 7810))
+    sm = model.score_model
+    with torch.no_grad():
+        ref = model(xs, t, mixn)
+        assert getattr(sm, "_mixc", None) is None          # nothing announced: no cache
+        model.note_constant_mixture(mixn)
+        a = model(xs, t, mixn)                              # fills
+        assert sm._mixc is not None and sm._mixc["ref"] is mixn
+        b = model(xs, t, mixn)                              # served from the cache
+        assert torch.equal(a, ref) and torch.equal(b, ref)
+        mixn.mul_(0.5)                                      # in-place change: version bump -> refill
+        c = model(xs, t, mixn)
+        model.note_constant_mixture(None)
+        d = model(xs, t, mixn)
+        assert torch.equal(c, d) and not torch.equal(c, ref) and sm._mixc is None
